@@ -1,0 +1,162 @@
+/* b200attn — C ABI of the B200-native paged-KV attention path.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no torch types, no C++
+ * exceptions.  Every entry point replaces one piece of the reference
+ * (foundation-model-stack/vllm-triton-backend) hot path; the reference location
+ * each one stands in for is cited beside it (paths relative to the reference
+ * checkout).  The reference-side binding a maintainer would add is shown in
+ * INTEGRATION.md (ctypes, because the reference host code is Python).
+ *
+ * Conventions
+ *  - all data pointers are DEVICE pointers unless the name ends in `_host`;
+ *  - strides are in ELEMENTS of the tensor's dtype;
+ *  - the library allocates nothing, never synchronises, never reads device
+ *    data on the host and launches only on the stream it is given, so every
+ *    call can be captured in a CUDA graph (grids depend on host ints only);
+ *  - return value: 0 on success, a B200ATTN_E_* code otherwise;
+ *    b200attn_last_error() returns a thread-local description.
+ */
+#ifndef B200ATTN_H_
+#define B200ATTN_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200ATTN_ABI_VERSION 1
+
+typedef struct CUstream_st* b200attn_stream_t; /* == cudaStream_t */
+
+enum b200attn_dtype {
+  B200ATTN_BF16 = 0,
+  B200ATTN_F16 = 1,
+  B200ATTN_F32 = 2,
+  B200ATTN_FP8_E4M3 = 3
+};
+
+enum b200attn_status {
+  B200ATTN_OK = 0,
+  B200ATTN_E_BAD_DTYPE = 1,
+  B200ATTN_E_BAD_SHAPE = 2,
+  B200ATTN_E_ALIGNMENT = 3,
+  B200ATTN_E_WORKSPACE = 4,
+  B200ATTN_E_UNSUPPORTED = 5,
+  B200ATTN_E_CUDA = 6,
+  B200ATTN_E_NULL = 7
+};
+
+/* Which kernel the unified entry point runs.  AUTO mirrors the reference
+ * dispatch `max_seqlen_q > 1 -> 2D else 3D`
+ * (ibm-triton-lib/ibm_triton_lib/kernels/triton_unified_attention.py:884). */
+enum b200attn_path {
+  B200ATTN_PATH_AUTO = 0,
+  B200ATTN_PATH_GENERIC = 1, /* SIMT kernel: any head size / group size (correctness net) */
+  B200ATTN_PATH_PREFILL = 2, /* "2D": varlen / prefix / chunked / mixed batches        */
+  B200ATTN_PATH_DECODE = 3,  /* "3D": split-KV GQA-packed decode + segment reduce       */
+  B200ATTN_PATH_PREFILL_TC = 4 /* tcgen05/TMEM flash-attention (bf16/f16, D=128)       */
+};
+
+/* ---- K1: KV-cache scatter write -------------------------------------------
+ * Replaces torch.ops._C_cache_ops.reshape_and_cache_flash as called at
+ * ibm-triton-lib/ibm_triton_lib/backend/triton_attn.py:396-405
+ * (kernel: vllm/csrc/cache_kernels.cu:286-358, host wrapper :700-738).
+ *
+ * For i in [0, num_tokens), slot = slot_mapping[i], slot >= 0:
+ *   k_cache[slot / block_size][slot % block_size][h][:] = f(key[i][h][:])
+ * f = copy when kv_dtype == src_dtype, or e4m3_rn_satfinite(float(x) / *scale)
+ * when kv_dtype == B200ATTN_FP8_E4M3.  num_tokens is slot_mapping's length
+ * (cache_kernels.cu:709-719).  k_scale / v_scale: device fp32 scalars (may be
+ * NULL when not quantising).
+ */
+int b200attn_reshape_and_cache_flash(
+    const void* key, const void* value, void* k_cache, void* v_cache,
+    const int64_t* slot_mapping, int64_t num_tokens, int32_t num_kv_heads,
+    int32_t head_size, int32_t block_size, int64_t key_stride0,
+    int64_t value_stride0, int64_t kc_block_stride, int64_t kc_slot_stride,
+    int64_t kc_head_stride, int64_t vc_block_stride, int64_t vc_slot_stride,
+    int64_t vc_head_stride, int32_t src_dtype, int32_t kv_dtype,
+    const float* k_scale, const float* v_scale, b200attn_stream_t stream);
+
+/* ---- K2/K3: paged attention -----------------------------------------------
+ * Replaces `unified_attention` (triton_unified_attention.py:839-1030): the 2D
+ * kernel (:275-523), the 3D split-KV kernel (:526-754) and `reduce_segments`
+ * (:757-836).  Field meanings follow the reference launcher's arguments.
+ */
+typedef struct b200attn_attention_params {
+  void* out;                   /* [T, Hq, D]  q_dtype                              */
+  const void* q;               /* [T, Hq, D]  innermost contiguous                 */
+  const void* k_cache;         /* [NB, bs, Hkv, D] view, innermost contiguous      */
+  const void* v_cache;
+  const int32_t* block_tables; /* [B, >=ceil(max_seqlen_k/bs)]                     */
+  const int32_t* seq_lens;     /* [B]  context + new tokens ("seqused_k")          */
+  const int32_t* cu_seqlens_q; /* [B+1]                                            */
+  const float* alibi_slopes;   /* [Hq] or NULL                                     */
+  const float* k_scale;        /* device scalar ("k_descale" element 0) or NULL=1  */
+  const float* v_scale;
+  const float* sinks;          /* reserved (NULL)                                  */
+  float softmax_scale;
+  float softcap;               /* 0 = off                                          */
+  int32_t sliding_window;      /* 0 = off; = 1 + window_size[0] (:915)             */
+  int32_t num_tokens;          /* T                                                */
+  int32_t num_seqs;            /* B                                                */
+  int32_t num_q_heads;
+  int32_t num_kv_heads;
+  int32_t head_size;
+  int32_t block_size;
+  int32_t max_seqlen_q;
+  int32_t max_seqlen_k;
+  int32_t q_dtype;             /* enum b200attn_dtype: BF16 / F16 (F32: generic)   */
+  int32_t kv_dtype;            /* == q_dtype, or FP8_E4M3                          */
+  int32_t path;                /* enum b200attn_path                               */
+  int32_t reserved0;
+  int64_t num_blocks;          /* NB (extent of the cache views)                   */
+  int64_t q_stride0, q_stride1;
+  int64_t out_stride0, out_stride1;
+  int64_t bt_stride0;
+  int64_t kc_block_stride, kc_slot_stride, kc_head_stride;
+  int64_t vc_block_stride, vc_slot_stride, vc_head_stride;
+  void* workspace;             /* split-KV partials; caller-owned                  */
+  uint64_t workspace_bytes;
+} b200attn_attention_params;
+
+/* Bytes of workspace b200attn_unified_attention may need for this shape
+ * (replaces the per-call torch.empty of segm_output/segm_max/segm_expsum,
+ * triton_unified_attention.py:950-971).  Host ints only. */
+uint64_t b200attn_workspace_bytes(int32_t num_tokens, int32_t num_seqs,
+                                  int32_t num_q_heads, int32_t num_kv_heads,
+                                  int32_t head_size);
+
+int b200attn_unified_attention(const b200attn_attention_params* p,
+                               b200attn_stream_t stream);
+
+/* ---- K4 (optional): static per-tensor FP8 quantisation of Q ----------------
+ * Replaces ops.scaled_fp8_quant(query, layer._q_scale) at triton_attn.py:417
+ * (vllm/csrc/quantization/w8a8/fp8/common.cu:11-29):
+ *   out[i] = e4m3_rn_satfinite(float(in[i]) * (1 / *scale)).
+ */
+int b200attn_scaled_fp8_quant(void* out_fp8, const void* in, int64_t num_rows,
+                              int64_t row_elems, int64_t in_row_stride,
+                              int32_t src_dtype, const float* scale,
+                              b200attn_stream_t stream);
+
+/* ---- introspection ---------------------------------------------------------*/
+int b200attn_abi_version(void);
+const char* b200attn_last_error(void);
+/* Number of kernels this library launched on the calling thread since the last
+ * reset (bench.py reports it as `gpu_launches`). */
+uint64_t b200attn_launch_count(void);
+void b200attn_reset_launch_count(void);
+/* Name of the kernel variant the last attention call on this thread ran. */
+const char* b200attn_last_kernel(void);
+/* Tuning knobs (process-wide; 0 = library default).  Used by the benchmark
+ * sweeps; not needed for correctness. */
+void b200attn_set_tuning(int32_t decode_heads_per_cta, int32_t decode_ctas_per_sm,
+                         int32_t decode_stages, int32_t reserved);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200ATTN_H_ */
