@@ -28,6 +28,12 @@ extern "C" {
 
 #define B200ATTN_ABI_VERSION 1
 
+#if defined(__GNUC__)
+#define B200ATTN_API __attribute__((visibility("default")))
+#else
+#define B200ATTN_API
+#endif
+
 typedef struct CUstream_st* b200attn_stream_t; /* == cudaStream_t */
 
 enum b200attn_dtype {
@@ -71,7 +77,7 @@ enum b200attn_path {
  * (cache_kernels.cu:709-719).  k_scale / v_scale: device fp32 scalars (may be
  * NULL when not quantising).
  */
-int b200attn_reshape_and_cache_flash(
+B200ATTN_API int b200attn_reshape_and_cache_flash(
     const void* key, const void* value, void* k_cache, void* v_cache,
     const int64_t* slot_mapping, int64_t num_tokens, int32_t num_kv_heads,
     int32_t head_size, int32_t block_size, int64_t key_stride0,
@@ -125,11 +131,11 @@ typedef struct b200attn_attention_params {
 /* Bytes of workspace b200attn_unified_attention may need for this shape
  * (replaces the per-call torch.empty of segm_output/segm_max/segm_expsum,
  * triton_unified_attention.py:950-971).  Host ints only. */
-uint64_t b200attn_workspace_bytes(int32_t num_tokens, int32_t num_seqs,
+B200ATTN_API uint64_t b200attn_workspace_bytes(int32_t num_tokens, int32_t num_seqs,
                                   int32_t num_q_heads, int32_t num_kv_heads,
                                   int32_t head_size);
 
-int b200attn_unified_attention(const b200attn_attention_params* p,
+B200ATTN_API int b200attn_unified_attention(const b200attn_attention_params* p,
                                b200attn_stream_t stream);
 
 /* ---- K4 (optional): static per-tensor FP8 quantisation of Q ----------------
@@ -137,23 +143,23 @@ int b200attn_unified_attention(const b200attn_attention_params* p,
  * (vllm/csrc/quantization/w8a8/fp8/common.cu:11-29):
  *   out[i] = e4m3_rn_satfinite(float(in[i]) * (1 / *scale)).
  */
-int b200attn_scaled_fp8_quant(void* out_fp8, const void* in, int64_t num_rows,
+B200ATTN_API int b200attn_scaled_fp8_quant(void* out_fp8, const void* in, int64_t num_rows,
                               int64_t row_elems, int64_t in_row_stride,
                               int32_t src_dtype, const float* scale,
                               b200attn_stream_t stream);
 
 /* ---- introspection ---------------------------------------------------------*/
-int b200attn_abi_version(void);
-const char* b200attn_last_error(void);
+B200ATTN_API int b200attn_abi_version(void);
+B200ATTN_API const char* b200attn_last_error(void);
 /* Number of kernels this library launched on the calling thread since the last
  * reset (bench.py reports it as `gpu_launches`). */
-uint64_t b200attn_launch_count(void);
-void b200attn_reset_launch_count(void);
+B200ATTN_API uint64_t b200attn_launch_count(void);
+B200ATTN_API void b200attn_reset_launch_count(void);
 /* Name of the kernel variant the last attention call on this thread ran. */
-const char* b200attn_last_kernel(void);
+B200ATTN_API const char* b200attn_last_kernel(void);
 /* Tuning knobs (process-wide; 0 = library default).  Used by the benchmark
  * sweeps; not needed for correctness. */
-void b200attn_set_tuning(int32_t decode_heads_per_cta, int32_t decode_ctas_per_sm,
+B200ATTN_API void b200attn_set_tuning(int32_t decode_heads_per_cta, int32_t decode_ctas_per_sm,
                          int32_t decode_stages, int32_t reserved);
 
 #ifdef __cplusplus

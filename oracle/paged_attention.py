@@ -73,8 +73,8 @@ def unified_attention_ref(
     for b in range(len(sl)):
         q0, q1 = cu[b], cu[b + 1]
         q_len, kv_len = q1 - q0, sl[b]
-        if q_len == 0:
-            continue
+        if q_len == 0 or kv_len == 0:
+            continue  # nothing visible: output stays 0 (reduce_segments :828)
         ctx = kv_len - q_len  # :374
         qb = q[q0:q1].to(torch.float32)  # [q, Hq, D]
         k = _dequant(gather_kv(k_cache, block_table[b], kv_len), k_scale, cdt)

@@ -1,0 +1,76 @@
+"""The C-ABI library loads without a GPU/driver and exports every symbol that
+include/b200attn.h declares (no compute calls here)."""
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    from vllm_triton_backend_b200 import _cabi
+
+    if not os.path.exists(_cabi.LIB_PATH):
+        from vllm_triton_backend_b200.build import build
+
+        build()
+    return _cabi.load_library()
+
+
+def _declared_symbols():
+    text = open(os.path.join(ROOT, "include", "b200attn.h")).read()
+    return sorted(set(re.findall(r"B200ATTN_API[^;(]*?\b(b200attn_\w+)\s*\(", text)))
+
+
+def test_header_declares_the_expected_entry_points():
+    from vllm_triton_backend_b200 import _cabi
+
+    assert _declared_symbols() == sorted(_cabi.EXPORTED_SYMBOLS)
+
+
+def test_every_declared_symbol_is_exported(lib):
+    for sym in _declared_symbols():
+        assert getattr(lib, sym) is not None, sym
+
+
+def test_abi_version_and_host_only_calls(lib):
+    assert lib.b200attn_abi_version() == 1
+    # workspace size is a function of host ints only
+    a = lib.b200attn_workspace_bytes(64, 64, 32, 8, 128)
+    b = lib.b200attn_workspace_bytes(128, 128, 32, 8, 128)
+    assert 0 < a < b
+    lib.b200attn_reset_launch_count()
+    assert lib.b200attn_launch_count() == 0
+
+
+def test_params_struct_matches_header_layout():
+    """ctypes mirror and the C struct must agree field by field."""
+    from vllm_triton_backend_b200._cabi import AttentionParams
+
+    text = open(os.path.join(ROOT, "include", "b200attn.h")).read()
+    body = text.split("typedef struct b200attn_attention_params {")[1].split("} b200attn_attention_params;")[0]
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    names = []
+    for decl in body.split(";"):
+        decl = decl.strip()
+        if not decl:
+            continue
+        for part in decl.split(","):
+            names.append(re.findall(r"(\w+)\s*$", part.strip())[0])
+    assert names == [f[0] for f in AttentionParams._fields_]
+
+
+def test_null_params_is_an_error_code_not_a_crash(lib):
+    assert lib.b200attn_unified_attention(None, None) != 0
+    assert b"null" in lib.b200attn_last_error()
+
+
+def test_missing_library_fails_loudly(monkeypatch, tmp_path):
+    from vllm_triton_backend_b200 import _cabi
+
+    monkeypatch.setattr(_cabi, "_lib", None)
+    monkeypatch.setattr(_cabi, "LIB_PATH", str(tmp_path / "nope.so"))
+    with pytest.raises(ImportError, match="no CPU/PyTorch fallback"):
+        _cabi.load_library()

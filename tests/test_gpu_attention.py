@@ -1,0 +1,260 @@
+"""K2/K3 parity on the GPU against the CPU oracle and the reference golden
+vectors (tolerances from BASELINE.json: bf16 max-abs 2e-2 / rtol 1e-2, FP8 KV 6e-2).
+All calls go through the C ABI (ops.unified_attention -> libb200attn.so)."""
+import pytest
+import torch
+
+from helpers import (BF16_ATOL, BF16_RTOL, FP8_ATOL, assert_close, golden_attn_files, load_golden_attn,
+                     make_paged_inputs)
+from oracle.paged_attention import unified_attention_ref
+
+pytestmark = pytest.mark.gpu
+
+GENERIC, PREFILL, DECODE_OR_AUTO = 1, 2, None
+
+
+def _run(inp, scale, path, window=0, softcap=0.0, alibi=None, k_scale=None, v_scale=None, dtype=None):
+    from vllm_triton_backend_b200 import _cabi, ops
+
+    dev = "cuda"
+    q = inp["q"].to(dev) if dtype is None else inp["q"].to(dev, dtype)
+    kc, vc = inp["k_cache"], inp["v_cache"]
+    if dtype is not None and kc.dtype != torch.float8_e4m3fn:
+        kc, vc = kc.to(dtype), vc.to(dtype)
+    kc, vc = kc.to(dev), vc.to(dev)
+    out = torch.full_like(q, float("nan"))
+    q_lens = (inp["cu_seqlens_q"][1:] - inp["cu_seqlens_q"][:-1])
+    max_q = int(q_lens.max())
+    force = path
+    if path == PREFILL and max_q > 1:
+        force = 22
+    ops.unified_attention(
+        q=q, k=kc, v=vc, out=out, cu_seqlens_q=inp["cu_seqlens_q"].to(dev), max_seqlen_q=max_q,
+        seqused_k=inp["seq_lens"].to(dev), max_seqlen_k=int(inp["seq_lens"].max()), softmax_scale=scale, causal=True,
+        window_size=(window - 1, 0) if window > 0 else (-1, -1), block_table=inp["block_table"].to(dev),
+        softcap=softcap, q_descale=None,
+        k_descale=None if k_scale is None else torch.tensor([k_scale], dtype=torch.float32, device=dev),
+        v_descale=None if v_scale is None else torch.tensor([v_scale], dtype=torch.float32, device=dev),
+        alibi_slopes=None if alibi is None else alibi.to(dev), force_selection=force,
+    )
+    torch.cuda.synchronize()
+    return out.cpu(), _cabi.last_kernel()
+
+
+def _oracle(inp, scale, window=0, softcap=0.0, alibi=None, k_scale=1.0, v_scale=1.0, dtype=None):
+    q = inp["q"] if dtype is None else inp["q"].to(dtype)
+    kc, vc = inp["k_cache"], inp["v_cache"]
+    if dtype is not None and kc.dtype != torch.float8_e4m3fn:
+        kc, vc = kc.to(dtype), vc.to(dtype)
+    return unified_attention_ref(
+        q, kc, vc, inp["cu_seqlens_q"], inp["seq_lens"], inp["block_table"], scale, sliding_window=window,
+        softcap=softcap, alibi_slopes=alibi, k_scale=k_scale, v_scale=v_scale, out_dtype=torch.float32,
+    )
+
+
+# ---------------------------------------------------------------------------------
+# golden vectors produced by the reference Triton kernels
+# ---------------------------------------------------------------------------------
+@pytest.mark.parametrize("path", golden_attn_files(), ids=lambda p: p.split("attn_")[-1][:-4])
+def test_golden_native_dtype_generic_kernel(path):
+    """fp32/fp16 inputs as the reference ran them; SIMT kernel; tight tolerance."""
+    c = load_golden_attn(path)
+    out, kern = _run(c, c["scale"], GENERIC, window=c["window"], softcap=c["softcap"], alibi=c["alibi_slopes"])
+    assert kern == "attn_generic"
+    tight = c["dtype"] == torch.float32
+    assert_close(out, c["out_triton"], atol=1e-4 if tight else 2e-3, rtol=1e-4 if tight else 2e-3, what=c["name"])
+
+
+@pytest.mark.parametrize("path", golden_attn_files(), ids=lambda p: p.split("attn_")[-1][:-4])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_golden_tensor_core_kernels(path, dtype):
+    """Same inputs cast to bf16/fp16 through the kernel the dispatcher picks."""
+    c = load_golden_attn(path)
+    out, kern = _run(c, c["scale"], DECODE_OR_AUTO, window=c["window"], softcap=c["softcap"], alibi=c["alibi_slopes"],
+                     dtype=dtype)
+    assert kern in ("decode_reduce", "attn_prefill_mma", "attn_prefill_tc"), kern
+    # golden inputs live on the fp16 grid; bf16 casts them, so compare with the oracle on the cast inputs too
+    assert_close(out, _oracle(c, c["scale"], c["window"], c["softcap"], c["alibi_slopes"], dtype=dtype),
+                 atol=BF16_ATOL, rtol=BF16_RTOL, what=c["name"] + " vs oracle")
+    if dtype == torch.float16:
+        assert_close(out, c["out_triton"], atol=BF16_ATOL, rtol=BF16_RTOL, what=c["name"] + " vs reference kernels")
+
+
+# ---------------------------------------------------------------------------------
+# decode (3D path)
+# ---------------------------------------------------------------------------------
+DECODE_SHAPES = [
+    # (kv lens, Hq, Hkv, D, block_size)
+    ([512, 512, 512, 512], 32, 8, 128, 16),          # C1
+    ([1328, 18, 463, 1, 16, 17, 2011], 8, 2, 128, 16),
+    ([523, 37, 2011], 4, 4, 128, 16),                # MHA (group 1)
+    ([300, 4096, 129], 64, 8, 128, 16),              # 70B-shaped, group 8
+    ([700, 33], 16, 1, 128, 32),                     # MQA-16 -> two n-tiles
+    ([257, 1000], 8, 2, 64, 16),
+    ([257, 1000], 8, 2, 256, 16),
+    ([90, 3000, 5], 32, 8, 128, 128),
+]
+
+
+@pytest.mark.parametrize("lens,Hq,Hkv,D,bs", DECODE_SHAPES)
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("interleaved", [False, True])
+def test_decode_matches_oracle(lens, Hq, Hkv, D, bs, dtype, interleaved):
+    inp = make_paged_inputs([(1, n) for n in lens], Hq, Hkv, D, bs, dtype=dtype, seed=len(lens) + D, interleaved=interleaved)
+    scale = D ** -0.5
+    out, kern = _run(inp, scale, DECODE_OR_AUTO)
+    assert kern == "decode_reduce", kern
+    assert_close(out, _oracle(inp, scale), atol=BF16_ATOL, rtol=BF16_RTOL, what="decode")
+    assert not torch.isnan(out).any()
+
+
+@pytest.mark.parametrize("hpc", [1, 2, 4, 8])
+@pytest.mark.parametrize("tma_split", [0, 1])
+def test_decode_split_and_head_grouping_invariance(hpc, tma_split):
+    """Result must not depend on how KV is cut across CTAs / warps / TMA boxes."""
+    from vllm_triton_backend_b200 import _cabi
+
+    lens = [4096, 100, 1777, 16, 3000, 15, 2048, 640]
+    inp = make_paged_inputs([(1, n) for n in lens], 32, 8, 128, 16, dtype=torch.bfloat16, seed=3)
+    scale = 128 ** -0.5
+    try:
+        _cabi.set_tuning(hpc, 0, 0, tma_split)
+        out, _ = _run(inp, scale, DECODE_OR_AUTO)
+    finally:
+        _cabi.set_tuning(0, 0, 0, 0)
+    assert_close(out, _oracle(inp, scale), atol=BF16_ATOL, rtol=BF16_RTOL, what=f"hpc={hpc}")
+
+
+@pytest.mark.parametrize("feature", ["window", "softcap", "alibi", "all"])
+@pytest.mark.parametrize("D", [64, 128])
+def test_decode_features(feature, D):
+    lens = [1328, 18, 463, 200, 64, 65]
+    Hq, Hkv = 8, 2
+    inp = make_paged_inputs([(1, n) for n in lens], Hq, Hkv, D, 16, dtype=torch.bfloat16, seed=11)
+    window = 128 if feature in ("window", "all") else 0
+    softcap = 50.0 if feature in ("softcap", "all") else 0.0
+    alibi = torch.tensor([2.0 ** (-(i + 1)) for i in range(Hq)]) if feature in ("alibi", "all") else None
+    scale = D ** -0.5
+    out, kern = _run(inp, scale, DECODE_OR_AUTO, window=window, softcap=softcap, alibi=alibi)
+    assert kern == "decode_reduce"
+    assert_close(out, _oracle(inp, scale, window, softcap, alibi), atol=BF16_ATOL, rtol=BF16_RTOL, what=feature)
+
+
+@pytest.mark.parametrize("scales", [(0.5, 0.5), (0.37, 0.21), (1.0, 1.0)])
+@pytest.mark.parametrize("Hq,Hkv", [(64, 8), (8, 1), (32, 8)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_decode_fp8_kv(scales, Hq, Hkv, dtype):
+    lens = [2049, 333, 16, 1]
+    inp = make_paged_inputs([(1, n) for n in lens], Hq, Hkv, 128, 16, dtype=dtype, seed=5,
+                            kv_dtype=torch.float8_e4m3fn, k_scale=scales[0], v_scale=scales[1])
+    scale = 128 ** -0.5
+    out, kern = _run(inp, scale, DECODE_OR_AUTO, k_scale=scales[0], v_scale=scales[1])
+    assert kern == "decode_reduce"
+    assert_close(out, _oracle(inp, scale, k_scale=scales[0], v_scale=scales[1]), atol=FP8_ATOL, rtol=BF16_RTOL, what="fp8 decode")
+
+
+def test_decode_ignores_garbage_beyond_seq_len():
+    """Slots past seq_len in the last page (and unused pages) may hold NaN/Inf."""
+    lens = [17, 100, 1]
+    inp = make_paged_inputs([(1, n) for n in lens], 8, 2, 128, 16, dtype=torch.bfloat16, seed=9)
+    ref = _oracle(inp, 0.1)
+    bt = inp["block_table"]
+    for b, n in enumerate(lens):
+        page = int(bt[b, (n - 1) // 16])
+        inp["k_cache"][page, n % 16 if n % 16 else 16:] = float("nan")
+        inp["v_cache"][page, n % 16 if n % 16 else 16:] = float("inf")
+    out, _ = _run(inp, 0.1, DECODE_OR_AUTO)
+    assert_close(out, ref, atol=BF16_ATOL, rtol=BF16_RTOL, what="garbage tail")
+
+
+def test_decode_empty_and_single_token_sequences():
+    inp = make_paged_inputs([(1, 1), (1, 0), (1, 2), (1, 16)], 8, 2, 128, 16, dtype=torch.bfloat16, seed=2)
+    out, _ = _run(inp, 0.3, DECODE_OR_AUTO)
+    ref = _oracle(inp, 0.3)
+    ref[1] = 0  # no visible key: reduce_segments returns 0 (reference :828)
+    assert_close(out, ref, atol=BF16_ATOL, rtol=BF16_RTOL, what="tiny")
+
+
+# ---------------------------------------------------------------------------------
+# prefill / prefix / chunked / mixed (2D path)
+# ---------------------------------------------------------------------------------
+MIXED = [
+    # (q, kv) lens as in vllm/tests/kernels/attention/test_triton_unified_attention.py:85
+    ([(1, 1328), (5, 18), (129, 463)], 4, 4, 128, 16),
+    ([(1, 1328), (5, 18), (129, 463)], 8, 2, 128, 16),
+    ([(1, 523), (1, 37), (1, 2011)], 8, 2, 256, 16),
+    ([(1, 1328), (5, 18), (129, 463)], 8, 2, 256, 16),
+    ([(200, 200), (64, 64), (1, 1), (77, 300)], 32, 8, 128, 16),   # fresh prompts + prefix hit
+    ([(512, 1536), (33, 33), (1, 700), (1, 9)], 32, 8, 128, 32),   # chunked continuation + decodes
+    ([(100, 100), (3, 50)], 40, 8, 64, 16),                        # group 5 (not a power of two)
+    ([(70, 70), (129, 129)], 16, 1, 128, 16),                      # MQA 16
+]
+
+
+@pytest.mark.parametrize("lens,Hq,Hkv,D,bs", MIXED)
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_prefill_mixed_matches_oracle(lens, Hq, Hkv, D, bs, dtype):
+    inp = make_paged_inputs(lens, Hq, Hkv, D, bs, dtype=dtype, seed=Hq + D, interleaved=True)
+    scale = D ** -0.5
+    out, kern = _run(inp, scale, PREFILL)
+    assert kern == "attn_prefill_mma", kern
+    assert_close(out, _oracle(inp, scale), atol=BF16_ATOL, rtol=BF16_RTOL, what="prefill")
+
+
+@pytest.mark.parametrize("feature", ["window", "softcap", "alibi", "all"])
+def test_prefill_features(feature):
+    lens = [(1, 1328), (5, 18), (129, 463), (300, 300)]
+    Hq, Hkv, D = 8, 2, 128
+    inp = make_paged_inputs(lens, Hq, Hkv, D, 16, dtype=torch.bfloat16, seed=21)
+    window = 64 if feature in ("window", "all") else 0
+    softcap = 50.0 if feature in ("softcap", "all") else 0.0
+    alibi = torch.tensor([2.0 ** (-(i + 1)) for i in range(Hq)]) if feature in ("alibi", "all") else None
+    scale = D ** -0.5
+    out, _ = _run(inp, scale, PREFILL, window=window, softcap=softcap, alibi=alibi)
+    assert_close(out, _oracle(inp, scale, window, softcap, alibi), atol=BF16_ATOL, rtol=BF16_RTOL, what=feature)
+
+
+@pytest.mark.parametrize("scales", [(0.5, 0.5), (0.37, 0.21)])
+def test_prefill_fp8_kv(scales):
+    lens = [(1, 523), (64, 200), (130, 130)]
+    inp = make_paged_inputs(lens, 16, 2, 128, 16, dtype=torch.bfloat16, seed=6, kv_dtype=torch.float8_e4m3fn,
+                            k_scale=scales[0], v_scale=scales[1])
+    scale = 128 ** -0.5
+    out, _ = _run(inp, scale, PREFILL, k_scale=scales[0], v_scale=scales[1])
+    assert_close(out, _oracle(inp, scale, k_scale=scales[0], v_scale=scales[1]), atol=FP8_ATOL, rtol=BF16_RTOL, what="fp8 prefill")
+
+
+def test_decode_batch_through_prefill_kernel_matches_decode_kernel():
+    """force_selection=2 sends a decode-only batch down the 2D kernel (reference :884)."""
+    lens = [1328, 18, 463, 2011]
+    inp = make_paged_inputs([(1, n) for n in lens], 32, 8, 128, 16, dtype=torch.bfloat16, seed=8)
+    a, ka = _run(inp, 0.088, DECODE_OR_AUTO)
+    b, kb = _run(inp, 0.088, PREFILL)
+    assert ka == "decode_reduce" and kb == "attn_prefill_mma"
+    assert_close(a, b, atol=1e-2, rtol=1e-2, what="2D vs 3D")
+
+
+# ---------------------------------------------------------------------------------
+# shapes only the SIMT kernel takes
+# ---------------------------------------------------------------------------------
+@pytest.mark.parametrize("D", [32, 80, 96, 120])
+def test_odd_head_sizes_run_on_the_generic_kernel(D):
+    lens = [(1, 100), (7, 40), (33, 33)]
+    inp = make_paged_inputs(lens, 8, 2, D, 16, dtype=torch.bfloat16, seed=D)
+    out, kern = _run(inp, D ** -0.5, DECODE_OR_AUTO)
+    assert kern == "attn_generic"
+    assert_close(out, _oracle(inp, D ** -0.5), atol=BF16_ATOL, rtol=BF16_RTOL, what=f"D={D}")
+
+
+def test_reference_argument_checks():
+    from vllm_triton_backend_b200 import ops
+
+    inp = make_paged_inputs([(1, 10)], 4, 4, 64, 16, device="cuda")
+    kw = dict(q=inp["q"], k=inp["k_cache"], v=inp["v_cache"], out=torch.empty_like(inp["q"]),
+              cu_seqlens_q=inp["cu_seqlens_q"], max_seqlen_q=1, seqused_k=inp["seq_lens"], max_seqlen_k=10,
+              softmax_scale=1.0, window_size=(-1, -1), block_table=inp["block_table"], softcap=0,
+              k_descale=None, v_descale=None)
+    with pytest.raises(AssertionError, match="causal"):
+        ops.unified_attention(causal=False, q_descale=None, **kw)
+    with pytest.raises(AssertionError, match="Q scales"):
+        ops.unified_attention(causal=True, q_descale=torch.ones(1, device="cuda"), **kw)

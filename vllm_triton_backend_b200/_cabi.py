@@ -1,0 +1,117 @@
+"""ctypes binding of libb200attn.so (the C ABI declared in include/b200attn.h).
+
+The library is the product: if it is missing this module raises — there is no
+CPU or PyTorch fallback for the kernels.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import POINTER, Structure, c_char_p, c_float, c_int32, c_int64, c_uint64, c_void_p
+
+_PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG_DIR, "libb200attn.so")
+
+# enum b200attn_dtype
+BF16, F16, F32, FP8_E4M3 = 0, 1, 2, 3
+# enum b200attn_path
+PATH_AUTO, PATH_GENERIC, PATH_PREFILL, PATH_DECODE, PATH_PREFILL_TC = 0, 1, 2, 3, 4
+
+STATUS_NAMES = {
+    0: "OK", 1: "E_BAD_DTYPE", 2: "E_BAD_SHAPE", 3: "E_ALIGNMENT", 4: "E_WORKSPACE", 5: "E_UNSUPPORTED",
+    6: "E_CUDA", 7: "E_NULL",
+}
+
+EXPORTED_SYMBOLS = [
+    "b200attn_reshape_and_cache_flash",
+    "b200attn_workspace_bytes",
+    "b200attn_unified_attention",
+    "b200attn_scaled_fp8_quant",
+    "b200attn_abi_version",
+    "b200attn_last_error",
+    "b200attn_launch_count",
+    "b200attn_reset_launch_count",
+    "b200attn_last_kernel",
+    "b200attn_set_tuning",
+]
+
+
+class AttentionParams(Structure):
+    """Mirror of `b200attn_attention_params` (include/b200attn.h)."""
+
+    _fields_ = [
+        ("out", c_void_p), ("q", c_void_p), ("k_cache", c_void_p), ("v_cache", c_void_p),
+        ("block_tables", c_void_p), ("seq_lens", c_void_p), ("cu_seqlens_q", c_void_p),
+        ("alibi_slopes", c_void_p), ("k_scale", c_void_p), ("v_scale", c_void_p), ("sinks", c_void_p),
+        ("softmax_scale", c_float), ("softcap", c_float), ("sliding_window", c_int32),
+        ("num_tokens", c_int32), ("num_seqs", c_int32), ("num_q_heads", c_int32), ("num_kv_heads", c_int32),
+        ("head_size", c_int32), ("block_size", c_int32), ("max_seqlen_q", c_int32), ("max_seqlen_k", c_int32),
+        ("q_dtype", c_int32), ("kv_dtype", c_int32), ("path", c_int32), ("reserved0", c_int32),
+        ("num_blocks", c_int64), ("q_stride0", c_int64), ("q_stride1", c_int64),
+        ("out_stride0", c_int64), ("out_stride1", c_int64), ("bt_stride0", c_int64),
+        ("kc_block_stride", c_int64), ("kc_slot_stride", c_int64), ("kc_head_stride", c_int64),
+        ("vc_block_stride", c_int64), ("vc_slot_stride", c_int64), ("vc_head_stride", c_int64),
+        ("workspace", c_void_p), ("workspace_bytes", c_uint64),
+    ]
+
+
+class B200AttnError(RuntimeError):
+    def __init__(self, code: int, message: str):
+        super().__init__(f"b200attn {STATUS_NAMES.get(code, code)}: {message}")
+        self.code = code
+
+
+_lib = None
+
+
+def load_library() -> ctypes.CDLL:
+    """Loads the in-tree library; raises if it was not built (no fallback)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `python -m vllm_triton_backend_b200.build` "
+            "(nvcc, sm_100a). There is no CPU/PyTorch fallback for these kernels."
+        )
+    lib = ctypes.CDLL(LIB_PATH)
+    lib.b200attn_reshape_and_cache_flash.restype = c_int32
+    lib.b200attn_reshape_and_cache_flash.argtypes = (
+        [c_void_p] * 5 + [c_int64, c_int32, c_int32, c_int32] + [c_int64] * 8 + [c_int32, c_int32, c_void_p, c_void_p, c_void_p]
+    )
+    lib.b200attn_workspace_bytes.restype = c_uint64
+    lib.b200attn_workspace_bytes.argtypes = [c_int32] * 5
+    lib.b200attn_unified_attention.restype = c_int32
+    lib.b200attn_unified_attention.argtypes = [POINTER(AttentionParams), c_void_p]
+    lib.b200attn_scaled_fp8_quant.restype = c_int32
+    lib.b200attn_scaled_fp8_quant.argtypes = [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int32, c_void_p, c_void_p]
+    lib.b200attn_abi_version.restype = c_int32
+    lib.b200attn_last_error.restype = c_char_p
+    lib.b200attn_launch_count.restype = c_uint64
+    lib.b200attn_reset_launch_count.restype = None
+    lib.b200attn_last_kernel.restype = c_char_p
+    lib.b200attn_set_tuning.restype = None
+    lib.b200attn_set_tuning.argtypes = [c_int32] * 4
+    _lib = lib
+    return lib
+
+
+def check(code: int) -> None:
+    if code != 0:
+        raise B200AttnError(code, load_library().b200attn_last_error().decode())
+
+
+def launch_count() -> int:
+    return int(load_library().b200attn_launch_count())
+
+
+def reset_launch_count() -> None:
+    load_library().b200attn_reset_launch_count()
+
+
+def last_kernel() -> str:
+    return load_library().b200attn_last_kernel().decode()
+
+
+def set_tuning(decode_heads_per_cta: int = 0, decode_ctas_per_sm: int = 0, decode_stages: int = 0, reserved: int = 0):
+    load_library().b200attn_set_tuning(decode_heads_per_cta, decode_ctas_per_sm, decode_stages, reserved)

@@ -1,0 +1,279 @@
+"""vLLM V1 attention backend over the b200attn CUDA library.
+
+Host-side mirror of the reference plugin's backend module
+(ibm-triton-lib/ibm_triton_lib/backend/triton_attn.py): same three classes —
+metadata + builder (:60-233), backend (:236-285), impl (:288-470) — with the same
+argument meanings and error behaviour, written against the interface of the
+vLLM that is installed here (0.22: `vllm.v1.attention.backend`, split
+`do_kv_cache_update`, builder `(kv_cache_spec, layer_names, vllm_config, device)`).
+
+Differences from the reference, all deliberate:
+  * the cache write and the attention run in libb200attn.so (no Triton, no
+    `_C_cache_ops`); a missing library is an ImportError, never a fallback;
+  * split-KV workspaces are allocated once by the builder instead of per call
+    (reference kernels/triton_unified_attention.py:950-971);
+  * Q stays bf16/fp16 with an FP8 KV cache (the reference's fp8-Q branch drops
+    k_scale/v_scale), so `supports_quant_query_input=False`.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import ClassVar, Optional
+
+import torch
+
+from vllm.v1.attention.backend import (
+    AttentionBackend,
+    AttentionCGSupport,
+    AttentionImpl,
+    AttentionMetadataBuilder,
+    AttentionType,
+    CommonAttentionMetadata,
+    MultipleOf,
+)
+
+from .. import ops
+
+BACKEND_NAME = "B200_ATTN"
+BACKEND_PATH = "vllm_triton_backend_b200.backend.attn.B200AttentionBackend"
+
+
+@dataclass
+class B200AttentionMetadata:
+    # |---------- context_len ----------|-- query_len ---|   (seq_len = both)
+    num_actual_tokens: int  # tokens excluding padding
+    max_query_len: int
+    query_start_loc: torch.Tensor  # int32 [B+1] device
+    max_seq_len: int
+    seq_lens: torch.Tensor  # int32 [B] device
+    block_table: torch.Tensor  # int32 [B, MB] device
+    slot_mapping: torch.Tensor  # int64 [T] device, padding = -1
+    workspace: torch.Tensor  # split-KV partials, allocated once by the builder
+
+    # cascade attention is never used (reference triton_attn.py:279-281)
+    use_cascade: bool = False
+    common_prefix_len: int = 0
+    cu_prefix_query_lens: Optional[torch.Tensor] = None
+    prefix_kv_lens: Optional[torch.Tensor] = None
+    suffix_kv_lens: Optional[torch.Tensor] = None
+
+
+class B200AttentionMetadataBuilder(AttentionMetadataBuilder[B200AttentionMetadata]):
+    # full CUDA graphs: grids depend on host ints only (reference :107, :229-233)
+    _cudagraph_support: ClassVar[AttentionCGSupport] = AttentionCGSupport.ALWAYS
+
+    def __init__(self, kv_cache_spec, layer_names, vllm_config, device):
+        super().__init__(kv_cache_spec, layer_names, vllm_config, device)
+        self.block_size = kv_cache_spec.block_size
+        model_config = vllm_config.model_config
+        parallel_config = vllm_config.parallel_config
+        self.num_heads_q = model_config.get_num_attention_heads(parallel_config)
+        self.num_heads_kv = model_config.get_num_kv_heads(parallel_config)
+        self.headdim = model_config.get_head_size()
+        max_num_seqs = vllm_config.scheduler_config.max_num_seqs
+        nbytes = ops.workspace_bytes(max_num_seqs, max_num_seqs, self.num_heads_q, self.num_heads_kv, self.headdim)
+        self.workspace = torch.empty(nbytes, dtype=torch.uint8, device=device)
+
+    def build_for_cudagraph_capture(self, common_attn_metadata: CommonAttentionMetadata) -> B200AttentionMetadata:
+        attn_metadata = self.build(0, common_attn_metadata)
+        # capture with seq_lens = 1 so it is fast (reference :120-128); the captured
+        # grid does not depend on the lengths.
+        attn_metadata.seq_lens.fill_(1)
+        return attn_metadata
+
+    def build(self, common_prefix_len: int, common_attn_metadata: CommonAttentionMetadata,
+              fast_build: bool = False) -> B200AttentionMetadata:
+        m = common_attn_metadata
+        return B200AttentionMetadata(
+            num_actual_tokens=m.num_actual_tokens,
+            max_query_len=m.max_query_len,
+            query_start_loc=m.query_start_loc,
+            max_seq_len=m.max_seq_len,
+            seq_lens=m.seq_lens,
+            block_table=m.block_table_tensor,
+            slot_mapping=m.slot_mapping,
+            workspace=self.workspace,
+            use_cascade=False,
+            common_prefix_len=common_prefix_len,
+        )
+
+
+class B200AttentionBackend(AttentionBackend):
+    accept_output_buffer: bool = True
+    supported_dtypes: ClassVar[list] = [torch.float16, torch.bfloat16]
+    supported_kv_cache_dtypes: ClassVar[list] = ["auto", "float16", "bfloat16", "fp8", "fp8_e4m3"]
+    # vLLM >= 0.11 calls do_kv_cache_update before forward
+    forward_includes_kv_cache_update: bool = False
+
+    @staticmethod
+    def get_supported_kernel_block_sizes():
+        return [MultipleOf(16)]
+
+    @classmethod
+    def supports_block_size(cls, block_size) -> bool:
+        return block_size is None or block_size % 16 == 0
+
+    @classmethod
+    def get_supported_head_sizes(cls) -> list[int]:
+        return [32, 64, 96, 128, 160, 192, 224, 256]  # reference :241-242
+
+    @classmethod
+    def validate_head_size(cls, head_size: int) -> None:
+        supported = cls.get_supported_head_sizes()
+        if head_size not in supported:
+            raise ValueError(  # reference :245-254
+                f"Head size {head_size} is not supported by {cls.__name__.removesuffix('Backend')}. "
+                f"Supported head sizes are: {supported}."
+            )
+
+    @staticmethod
+    def get_name() -> str:
+        return BACKEND_NAME
+
+    @staticmethod
+    def get_impl_cls():
+        return B200AttentionImpl
+
+    @staticmethod
+    def get_metadata_cls():
+        return B200AttentionMetadata
+
+    @staticmethod
+    def get_builder_cls():
+        return B200AttentionMetadataBuilder
+
+    @staticmethod
+    def get_kv_cache_shape(num_blocks: int, block_size: int, num_kv_heads: int, head_size: int,
+                           cache_dtype_str: str = "auto") -> tuple[int, ...]:
+        if block_size % 16 != 0:
+            raise ValueError("Block size must be a multiple of 16.")  # reference :275-276
+        # K and V planes are separate: each (page, kv-head-group) tile the decode
+        # kernel streams is one contiguous TMA box, and K/V of a page do not share
+        # DRAM rows.  (The reference plugin used this layout too, :277.)
+        return (2, num_blocks, block_size, num_kv_heads, head_size)
+
+    @staticmethod
+    def use_cascade_attention(*args, **kwargs) -> bool:
+        return False
+
+    @classmethod
+    def supports_attn_type(cls, attn_type: str) -> bool:
+        return attn_type == AttentionType.DECODER
+
+    @classmethod
+    def supports_compute_capability(cls, capability) -> bool:
+        return capability.major >= 10  # sm_100a kernels only
+
+    @classmethod
+    def supports_sink(cls) -> bool:
+        return False
+
+
+def split_kv_cache(kv_cache: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor]:
+    """K/V views [NB, bs, Hkv, D] of either allocation vLLM may hand us:
+    (2, NB, bs, Hkv, D) — ours / the reference plugin's — or (NB, 2, bs, Hkv, D)
+    (stock vLLM >= 0.11, block stride 2*bs*Hkv*D)."""
+    if kv_cache.shape[0] == 2 and kv_cache.dim() == 5 and kv_cache.shape[1] != 2:
+        return kv_cache.unbind(0)
+    if kv_cache.dim() == 5 and kv_cache.shape[1] == 2:
+        return kv_cache.unbind(1)
+    return kv_cache.unbind(0)
+
+
+class B200AttentionImpl(AttentionImpl):
+    def __init__(
+        self,
+        num_heads: int,
+        head_size: int,
+        scale: float,
+        num_kv_heads: Optional[int] = None,
+        alibi_slopes: Optional[list] = None,
+        sliding_window: Optional[int] = None,
+        kv_cache_dtype: str = "auto",
+        logits_soft_cap: Optional[float] = None,
+        attn_type: str = AttentionType.DECODER,
+        kv_sharing_target_layer_name: Optional[str] = None,
+        blocksparse_params=None,
+        sinks: Optional[torch.Tensor] = None,
+        **extra_impl_args,
+    ) -> None:
+        if blocksparse_params is not None:
+            raise ValueError("B200Attention does not support block-sparse attention.")  # reference :305-306
+        if sinks is not None:
+            raise NotImplementedError("attention sinks are not implemented for B200AttentionImpl")
+        self.num_heads = num_heads
+        self.head_size = head_size
+        self.scale = float(scale)
+        self.num_kv_heads = num_heads if num_kv_heads is None else num_kv_heads
+        self._alibi_slopes_host = None if alibi_slopes is None else torch.tensor(alibi_slopes, dtype=torch.float32)
+        self.alibi_slopes = None  # moved to the device on first use
+        self.sliding_window = (-1, -1) if sliding_window is None else (sliding_window - 1, 0)  # reference :314-317
+        self.kv_cache_dtype = kv_cache_dtype
+        self.logits_soft_cap = 0 if logits_soft_cap is None else logits_soft_cap  # 0 = off (:319-322)
+        self.kv_sharing_target_layer_name = kv_sharing_target_layer_name
+        self.num_queries_per_kv = self.num_heads // self.num_kv_heads
+        B200AttentionBackend.validate_head_size(head_size)
+        if attn_type != AttentionType.DECODER:
+            raise NotImplementedError(  # reference :331-337
+                "Encoder self-attention and encoder/decoder cross-attention are not implemented for B200AttentionImpl"
+            )
+        self.attn_type = attn_type
+        self.supports_quant_query_input = False
+        if kv_cache_dtype.startswith("fp8") and kv_cache_dtype not in ("fp8", "fp8_e4m3"):
+            raise NotImplementedError(f"kv_cache_dtype {kv_cache_dtype!r}: only fp8_e4m3 is implemented")
+
+    def _views(self, kv_cache: torch.Tensor):
+        key_cache, value_cache = split_kv_cache(kv_cache)
+        if self.kv_cache_dtype.startswith("fp8") and key_cache.dtype != torch.float8_e4m3fn:
+            key_cache = key_cache.view(torch.float8_e4m3fn)  # reference :407-409
+            value_cache = value_cache.view(torch.float8_e4m3fn)
+        return key_cache, value_cache
+
+    def do_kv_cache_update(self, layer, key, value, kv_cache, slot_mapping) -> None:
+        """Cache write, split out of forward by vLLM >= 0.11 (reference did it
+        inside forward, triton_attn.py:393-405)."""
+        if self.kv_sharing_target_layer_name is not None:
+            return
+        key_cache, value_cache = self._views(kv_cache)
+        ops.reshape_and_cache_flash(
+            key, value, key_cache, value_cache, slot_mapping, self.kv_cache_dtype, layer._k_scale, layer._v_scale
+        )
+
+    def forward(
+        self,
+        layer,
+        query: torch.Tensor,  # [num_tokens, num_heads, head_size]
+        key: torch.Tensor,
+        value: torch.Tensor,
+        kv_cache: torch.Tensor,
+        attn_metadata: B200AttentionMetadata,
+        output: Optional[torch.Tensor] = None,
+        output_scale: Optional[torch.Tensor] = None,
+        output_block_scale: Optional[torch.Tensor] = None,
+    ) -> torch.Tensor:
+        assert output is not None, "Output tensor must be provided."  # reference :366
+        if output_scale is not None or output_block_scale is not None:
+            raise NotImplementedError(  # reference :368-372
+                "fused output quantization is not yet supported for B200AttentionImpl"
+            )
+        if attn_metadata is None:
+            return output.fill_(0)  # profiling run (reference :374-376)
+        assert attn_metadata.use_cascade is False
+
+        n = attn_metadata.num_actual_tokens
+        key_cache, value_cache = self._views(kv_cache)
+        if self._alibi_slopes_host is not None and self.alibi_slopes is None:
+            self.alibi_slopes = self._alibi_slopes_host.to(query.device)
+        q = query[:n].view(-1, self.num_heads, self.head_size)
+        out = output[:n].view(-1, self.num_heads, self.head_size)
+        ops.unified_attention(
+            q=q, k=key_cache, v=value_cache, out=out,
+            cu_seqlens_q=attn_metadata.query_start_loc, max_seqlen_q=attn_metadata.max_query_len,
+            seqused_k=attn_metadata.seq_lens, max_seqlen_k=attn_metadata.max_seq_len,
+            softmax_scale=self.scale, causal=True, alibi_slopes=self.alibi_slopes,
+            window_size=self.sliding_window, block_table=attn_metadata.block_table,
+            softcap=self.logits_soft_cap, q_descale=None,  # not supported (reference :465)
+            k_descale=layer._k_scale, v_descale=layer._v_scale,  # element 0 is what the kernels read (:438)
+            workspace=attn_metadata.workspace,
+        )
+        return output

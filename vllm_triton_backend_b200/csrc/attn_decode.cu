@@ -1,0 +1,836 @@
+// K2: split-KV, GQA-packed paged decode attention for sm_100a, plus the segment
+// reduce (K2b).
+//
+// What it computes is what the reference's 3D path computes
+// (reference ibm-triton-lib/ibm_triton_lib/kernels/triton_unified_attention.py:
+//  kernel_unified_attention_3d :526-754, reduce_segments :757-836): for every
+// sequence with one query token, softmax(scale * q K^T + mask/bias) V over the
+// paged cache, partial results over KV ranges merged with the usual
+// (max, exp-sum) rescaling.  How it does it is new:
+//
+//  * HBM-bound design.  KV pages are streamed by TMA (cp.async.bulk.tensor, 5-D
+//    tiled map over the strided [NB, bs, Hkv, D] cache view, 128-byte swizzle)
+//    into a multi-stage shared-memory ring; one producer warp issues the copies
+//    from the block table, 8 (4 for D=256) consumer warps each own a 16-token x
+//    one-kv-head tile of every stage.
+//  * Tokens sit on the MMA M axis, the GQA group's query heads on N (=8), so a
+//    group of 4..8 heads costs one m16n8k16 per 16 tokens x 16 dims, K is read by
+//    plain ldmatrix and V by ldmatrix.trans; P^T is produced from the S^T
+//    accumulators with movmatrix.  FP8-e4m3 KV is dequantised in registers
+//    (cvt.rn.f16x2.e4m3x2) and k_scale / v_scale are folded into the softmax
+//    scale and the epilogue.
+//  * Split-KV without host sync: the flattened (sequence, head-group, KV-step)
+//    space is cut into equal contiguous ranges, one per CTA (grid = #SMs), from
+//    the device-side seq_lens; a CTA that covers a whole item writes the output
+//    directly, otherwise it writes an un-normalised partial that
+//    `decode_reduce_kernel` merges (slot = item + cta is collision free).
+#include "common.cuh"
+
+namespace b200attn {
+namespace {
+
+constexpr int kMaxStages = 8;
+
+struct DecodeParams {
+  b200attn_attention_params a;
+  int hpc;         // kv heads per CTA (divides num_kv_heads and NW)
+  int head_groups; // num_kv_heads / hpc
+  int tps;         // tokens per stage-step = NW*16/hpc
+  int box_slots;   // min(block_size, tps)
+  int boxes;       // tps / box_slots
+  int stages;
+  int tma_split;   // 0: one TMA op per (page box); 1: one per (page box, head, d-chunk)
+  int group;       // query heads per kv head
+  float* ws_acc;   // [slots][hpc*group][D]
+  float* ws_ml;    // [slots][hpc*group][2]  (max in log2 units, exp-sum)
+  int* ws_lo;      // [items] first cta of an item that needs reducing
+  int* ws_hi;      // [items] last cta, or -1 when the output was written directly
+};
+
+__device__ __forceinline__ float ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+struct ItemCursor {
+  int b, hg, step;       // current sequence, head group, step index (absolute, in units of tps tokens)
+  int first, n;          // first step and number of steps of sequence b
+  int seq_len;
+  int flat;              // flat index of the current step
+};
+
+__device__ __forceinline__ void seq_steps(const DecodeParams& P, int b, int& seq_len, int& first, int& n) {
+  seq_len = P.a.seq_lens[b];
+  int q_len = P.a.cu_seqlens_q ? (P.a.cu_seqlens_q[b + 1] - P.a.cu_seqlens_q[b]) : 1;
+  if (seq_len <= 0 || q_len <= 0) {
+    first = 0, n = 0;
+    return;
+  }
+  int lo_tok = 0;
+  if (P.a.sliding_window > 0) lo_tok = max(0, seq_len - P.a.sliding_window);
+  first = lo_tok / P.tps;
+  n = (seq_len + P.tps - 1) / P.tps - first;
+}
+
+// advance to the next step in (b, hg, step) order; returns false past the end
+__device__ __forceinline__ bool cursor_next(const DecodeParams& P, ItemCursor& c) {
+  c.flat++;
+  if (++c.step < c.first + c.n) return true;
+  if (++c.hg < P.head_groups) {
+    c.step = c.first;
+    return true;
+  }
+  c.hg = 0;
+  while (++c.b < P.a.num_seqs) {
+    seq_steps(P, c.b, c.seq_len, c.first, c.n);
+    if (c.n > 0) {
+      c.step = c.first;
+      return true;
+    }
+  }
+  return false;
+}
+
+template <int D, bool KV_FP8, bool MMA_BF16, bool Q_BF16, int NT, int NW>
+__global__ void __launch_bounds__((NW + 1) * 32, 1)
+attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_map,
+                   const __grid_constant__ CUtensorMap v_map) {
+  constexpr int ESZ = KV_FP8 ? 1 : 2;
+  constexpr int NDC = D * ESZ / 128;      // 128-byte chunks per row
+  constexpr int KSTEPS = D / 16;          // k16 steps of S = K Q^T
+  constexpr int MTILES = D / 16;          // m16 tiles of O^T = V^T P^T
+  constexpr int TILE_BYTES = 16 * D * ESZ;
+  constexpr int KV_STAGE_BYTES = NW * TILE_BYTES;  // K (or V) bytes per stage
+  static_assert(NDC >= 1, "row must be at least 128 bytes");
+
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  // [stages][K | V] then merge buffer, then barriers / scalars
+  uint8_t* stage_base = smem;
+  float* mbuf = reinterpret_cast<float*>(smem + (size_t)P.stages * 2 * KV_STAGE_BYTES);  // [NW][8][D]
+  float* ml_buf = mbuf + NW * 8 * D;                                                      // [NW][8][2]
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(ml_buf + NW * 8 * 2);
+  uint64_t* empty_bar = full_bar + kMaxStages;
+  int* s_part = reinterpret_cast<int*>(empty_bar + kMaxStages);  // [0]=begin [1]=end [2]=b [3]=hg [4]=step
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int gid = lane >> 2, t4 = lane & 3;
+
+  // ---- work partition (warp 0) and barrier init (warp 1) ----------------------
+  if (warp == 0) {
+    // total steps over all sequences
+    int total = 0;
+    for (int b0 = 0; b0 < P.a.num_seqs; b0 += 32) {
+      int b = b0 + lane, n = 0;
+      if (b < P.a.num_seqs) {
+        int sl, first;
+        seq_steps(P, b, sl, first, n);
+      }
+      total += n;
+    }
+    total = __reduce_add_sync(0xffffffffu, total);
+    const long long total_flat = (long long)total * P.head_groups;
+    const long long per = (total_flat + gridDim.x - 1) / gridDim.x;
+    long long begin = per * blockIdx.x;
+    long long end = begin + per;
+    if (begin > total_flat) begin = total_flat;
+    if (end > total_flat) end = total_flat;
+    // locate `begin`: largest b with HG * prefix(b) <= begin and n_b > 0 covering it
+    int fb = -1, fhg = 0, fstep = 0;
+    if (begin < end) {
+      long long run = 0;  // HG * sum of n over sequences before the chunk
+      for (int b0 = 0; b0 < P.a.num_seqs && fb < 0; b0 += 32) {
+        int b = b0 + lane, n = 0, first = 0, sl;
+        if (b < P.a.num_seqs) seq_steps(P, b, sl, first, n);
+        int incl = n;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          int v = __shfl_up_sync(0xffffffffu, incl, o);
+          if (lane >= o) incl += v;
+        }
+        const long long lo = run + (long long)(incl - n) * P.head_groups;
+        const long long hi = run + (long long)incl * P.head_groups;
+        const bool mine = n > 0 && begin >= lo && begin < hi;
+        const unsigned hit = __ballot_sync(0xffffffffu, mine);
+        if (hit) {
+          const int src = __ffs(hit) - 1;
+          const long long lo_s = __shfl_sync(0xffffffffu, lo, src);
+          const int n_s = __shfl_sync(0xffffffffu, n, src);
+          const int first_s = __shfl_sync(0xffffffffu, first, src);
+          fb = b0 + src;
+          const long long rem = begin - lo_s;
+          fhg = (int)(rem / n_s);
+          fstep = first_s + (int)(rem % n_s);
+        }
+        run += (long long)__shfl_sync(0xffffffffu, incl, 31) * P.head_groups;
+      }
+    }
+    if (lane == 0) {
+      s_part[0] = (int)begin;
+      s_part[1] = (fb < 0) ? (int)begin : (int)end;
+      s_part[2] = fb, s_part[3] = fhg, s_part[4] = fstep;
+    }
+  } else if (warp == 1 && lane == 0) {
+    for (int s = 0; s < P.stages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], NW);
+    }
+    fence_barrier_init();
+  }
+  __syncthreads();
+  const int my_begin = s_part[0], my_end = s_part[1];
+  if (my_begin >= my_end) return;
+
+  ItemCursor cur;
+  cur.b = s_part[2], cur.hg = s_part[3], cur.step = s_part[4], cur.flat = my_begin;
+  seq_steps(P, cur.b, cur.seq_len, cur.first, cur.n);
+
+  const int boxb = P.hpc * NDC * P.box_slots * 128;  // bytes of one TMA box (all heads, all chunks)
+
+  if (warp == NW) {
+    // ======================= producer warp ====================================
+    if (lane == 0) {
+      tma_prefetch_desc(&k_map);
+      tma_prefetch_desc(&v_map);
+      const uint64_t pol = policy_evict_first();
+      int stage = 0;
+      uint32_t phase = 0;
+      while (true) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        const int tok0 = cur.step * P.tps;
+        const int ntok = min(P.tps, cur.seq_len - tok0);
+        const int nbox = (ntok + P.box_slots - 1) / P.box_slots;
+        const int head0 = cur.hg * P.hpc;
+        const int32_t* bt = P.a.block_tables + (int64_t)cur.b * P.a.bt_stride0;
+        uint8_t* kdst = stage_base + (size_t)stage * 2 * KV_STAGE_BYTES;
+        uint8_t* vdst = kdst + KV_STAGE_BYTES;
+        mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)(2 * nbox * boxb));
+        for (int i = 0; i < nbox; ++i) {
+          const int tok = tok0 + i * P.box_slots;
+          const int page = bt[tok / P.a.block_size];
+          const int slot0 = tok % P.a.block_size;
+          if (P.tma_split == 0) {
+            tma_load_5d(kdst + (size_t)i * boxb, &k_map, &full_bar[stage], 0, slot0, 0, head0, page, pol);
+            tma_load_5d(vdst + (size_t)i * boxb, &v_map, &full_bar[stage], 0, slot0, 0, head0, page, pol);
+          } else {
+            for (int h = 0; h < P.hpc; ++h)
+              for (int dc = 0; dc < NDC; ++dc) {
+                const size_t off = (size_t)i * boxb + (size_t)(h * NDC + dc) * P.box_slots * 128;
+                tma_load_5d(kdst + off, &k_map, &full_bar[stage], 0, slot0, dc, head0 + h, page, pol);
+                tma_load_5d(vdst + off, &v_map, &full_bar[stage], 0, slot0, dc, head0 + h, page, pol);
+              }
+          }
+        }
+        if (++stage == P.stages) stage = 0, phase ^= 1;
+        if (cur.flat + 1 >= my_end) break;
+        cursor_next(P, cur);
+      }
+    }
+    return;
+  }
+
+  // ========================= consumer warps ====================================
+  const int h_local = warp % P.hpc;           // kv head within the CTA's head group
+  const int jtile = warp / P.hpc;             // 16-token group within the stage-step
+  const int tok_off = jtile * 16;
+  const int box_i = tok_off / P.box_slots;
+  const int slot_in_box = tok_off % P.box_slots;
+  const uint32_t tile_off =
+      (uint32_t)(box_i * boxb + h_local * NDC * P.box_slots * 128 + slot_in_box * 128);  // + dc*box_slots*128
+  const uint32_t dc_stride = (uint32_t)P.box_slots * 128;
+
+  const float k_scale = (KV_FP8 && P.a.k_scale) ? *P.a.k_scale : 1.0f;
+  const float v_scale = (KV_FP8 && P.a.v_scale) ? *P.a.v_scale : 1.0f;
+  const bool has_cap = P.a.softcap > 0.f;
+  const float inv_cap = has_cap ? 1.0f / P.a.softcap : 0.f;
+  const float qk_scale = P.a.softmax_scale * k_scale;  // natural units
+  const bool has_alibi = P.a.alibi_slopes != nullptr;
+
+  // ldmatrix lane geometry
+  const int lrow = (lane & 7);
+  uint32_t k_lane_off, v_lane_off;  // byte offsets inside a [rows][128B] sub-tile, before the chunk XOR
+  int k_chunk_sel, v_chunk_sel;     // which of the pair of 16-byte chunks this lane addresses
+  if constexpr (!KV_FP8) {
+    // K (non-trans): matrices {rows0-7,c},{rows8-15,c},{rows0-7,c+1},{rows8-15,c+1}
+    k_lane_off = (uint32_t)((lrow + 8 * ((lane >> 3) & 1)) * 128);
+    k_chunk_sel = lane >> 4;
+    // V (trans): matrices {tok0-7,c},{tok0-7,c+1},{tok8-15,c},{tok8-15,c+1}
+    v_lane_off = (uint32_t)((lrow + 8 * (lane >> 4)) * 128);
+    v_chunk_sel = (lane >> 3) & 1;
+  } else {
+    // fp8: both use {rows0-7,c},{rows8-15,c},{rows0-7,c+1},{rows8-15,c+1}
+    k_lane_off = (uint32_t)((lrow + 8 * ((lane >> 3) & 1)) * 128);
+    k_chunk_sel = lane >> 4;
+    v_lane_off = k_lane_off;
+    v_chunk_sel = k_chunk_sel;
+  }
+  const uint32_t swz = (uint32_t)lrow;  // row & 7 (sub-tiles start on 1024-byte boundaries)
+
+  uint32_t qf[KSTEPS][NT][2];
+  float oacc[MTILES][NT][4];
+  float m_run[NT][2], l_run[NT][2];
+  float slope[NT][2];
+
+  auto reset_state = [&]() {
+#pragma unroll
+    for (int mt = 0; mt < MTILES; ++mt)
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) oacc[mt][nt][i] = 0.f;
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) m_run[nt][0] = m_run[nt][1] = -INFINITY, l_run[nt][0] = l_run[nt][1] = 0.f;
+  };
+
+  auto load_q = [&]() {
+    const int kvh = cur.hg * P.hpc + h_local;
+    const int tq = P.a.cu_seqlens_q ? P.a.cu_seqlens_q[cur.b] : cur.b;
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+      const int hq_local = nt * 8 + gid;
+      const bool ok = hq_local < P.group;
+      const int hq = kvh * P.group + (ok ? hq_local : 0);
+      const char* qrow = static_cast<const char*>(P.a.q) + ((int64_t)tq * P.a.q_stride0 + (int64_t)hq * P.a.q_stride1) * 2;
+#pragma unroll
+      for (int ks = 0; ks < KSTEPS; ++ks) {
+        uint32_t w0 = 0, w1 = 0;
+        if (ok) {
+          if constexpr (!KV_FP8) {
+            w0 = *reinterpret_cast<const uint32_t*>(qrow + (16 * ks + 2 * t4) * 2);
+            w1 = *reinterpret_cast<const uint32_t*>(qrow + (16 * ks + 2 * t4 + 8) * 2);
+          } else {
+            // fp8 K: k16 step `ks` consumes dims 16ks+4t..+3 in this lane's slots
+            const uint2 w = *reinterpret_cast<const uint2*>(qrow + (16 * ks + 4 * t4) * 2);
+            w0 = w.x, w1 = w.y;
+          }
+          if constexpr (Q_BF16 && !MMA_BF16) {
+            // bf16 query, f16 tensor-core operands (fp8 KV path)
+            const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(&w0);
+            const __nv_bfloat162 b = *reinterpret_cast<const __nv_bfloat162*>(&w1);
+            const float2 fa = __bfloat1622float2(a), fb = __bfloat1622float2(b);
+            const float lim = 65504.f;
+            w0 = pack2<false>(fminf(fmaxf(fa.x, -lim), lim), fminf(fmaxf(fa.y, -lim), lim));
+            w1 = pack2<false>(fminf(fmaxf(fb.x, -lim), lim), fminf(fmaxf(fb.y, -lim), lim));
+          }
+        }
+        qf[ks][nt][0] = w0, qf[ks][nt][1] = w1;
+      }
+      if (has_alibi) {
+        const int h0 = nt * 8 + 2 * t4;
+        slope[nt][0] = (h0 < P.group) ? P.a.alibi_slopes[kvh * P.group + h0] : 0.f;
+        slope[nt][1] = (h0 + 1 < P.group) ? P.a.alibi_slopes[kvh * P.group + h0 + 1] : 0.f;
+      } else {
+        slope[nt][0] = slope[nt][1] = 0.f;
+      }
+    }
+  };
+
+  reset_state();
+  load_q();
+
+  int stage = 0;
+  uint32_t phase = 0;
+  while (true) {
+    const int tok0 = cur.step * P.tps + tok_off;  // first token of this warp's tile
+    mbar_wait(&full_bar[stage], phase);
+    if (tok0 < cur.seq_len) {
+      const uint32_t ktile = smem_u32(stage_base + (size_t)stage * 2 * KV_STAGE_BYTES) + tile_off;
+      const uint32_t vtile = ktile + KV_STAGE_BYTES;
+      const int valid = cur.seq_len - tok0;  // > 0; tokens >= valid are out of range
+      int win_lo = 0;                        // tokens < win_lo (tile-relative) are outside the sliding window
+      if (P.a.sliding_window > 0) win_lo = (cur.seq_len - P.a.sliding_window) - tok0;
+      const bool partial = valid < 16 || win_lo > 0;
+
+      // ---- S^T[16 tok][8 heads] = K Q^T ------------------------------------
+      float sacc[NT][4];
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) sacc[nt][0] = sacc[nt][1] = sacc[nt][2] = sacc[nt][3] = 0.f;
+      if constexpr (!KV_FP8) {
+#pragma unroll
+        for (int dc = 0; dc < NDC; ++dc) {
+#pragma unroll
+          for (int k4 = 0; k4 < 4; ++k4) {
+            uint32_t a[4];
+            const uint32_t chunk = (uint32_t)(2 * k4 + k_chunk_sel);
+            ldmatrix_x4(a, ktile + dc * dc_stride + k_lane_off + ((chunk ^ swz) << 4));
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt)
+              mma_16816<MMA_BF16>(sacc[nt], a, qf[dc * 4 + k4][nt][0], qf[dc * 4 + k4][nt][1]);
+          }
+        }
+      } else {
+#pragma unroll
+        for (int dc = 0; dc < NDC; ++dc) {
+#pragma unroll
+          for (int c2 = 0; c2 < 4; ++c2) {  // pairs of 16-byte chunks = pairs of k16 steps
+            uint32_t r[4];
+            const uint32_t chunk = (uint32_t)(2 * c2 + k_chunk_sel);
+            ldmatrix_x4(r, ktile + dc * dc_stride + k_lane_off + ((chunk ^ swz) << 4));
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+              uint32_t a[4];
+              a[0] = e4m3x2_to_f16x2((uint16_t)(r[2 * half] & 0xffffu));
+              a[1] = e4m3x2_to_f16x2((uint16_t)(r[2 * half + 1] & 0xffffu));
+              a[2] = e4m3x2_to_f16x2((uint16_t)(r[2 * half] >> 16));
+              a[3] = e4m3x2_to_f16x2((uint16_t)(r[2 * half + 1] >> 16));
+              const int ks = dc * 8 + c2 * 2 + half;
+#pragma unroll
+              for (int nt = 0; nt < NT; ++nt) mma_16816<false>(sacc[nt], a, qf[ks][nt][0], qf[ks][nt][1]);
+            }
+          }
+        }
+      }
+
+      // ---- online softmax (log2 domain) --------------------------------------
+      uint32_t pb[NT][2];
+      float alpha[NT][2];
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) {
+        float s[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          float x = sacc[nt][i] * qk_scale;
+          if (has_cap) x = softcap_fn(x, P.a.softcap, inv_cap);
+          s[i] = x * kLog2e;
+        }
+        if (has_alibi) {
+          // bias slope * (pos - ctx), ctx = seq_len - 1 for a decode token
+          const float p0 = (float)(tok0 + gid - (cur.seq_len - 1)), p1 = p0 + 8.f;
+          s[0] += slope[nt][0] * p0 * kLog2e, s[1] += slope[nt][1] * p0 * kLog2e;
+          s[2] += slope[nt][0] * p1 * kLog2e, s[3] += slope[nt][1] * p1 * kLog2e;
+        }
+        if (partial) {
+          const bool ok0 = gid < valid && gid >= win_lo, ok1 = gid + 8 < valid && gid + 8 >= win_lo;
+          if (!ok0) s[0] = s[1] = -INFINITY;
+          if (!ok1) s[2] = s[3] = -INFINITY;
+        }
+        float mx0 = fmaxf(s[0], s[2]), mx1 = fmaxf(s[1], s[3]);
+#pragma unroll
+        for (int o = 4; o < 32; o <<= 1) {
+          mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, o));
+          mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, o));
+        }
+        const float mn0 = fmaxf(m_run[nt][0], mx0), mn1 = fmaxf(m_run[nt][1], mx1);
+        const float mu0 = (mn0 == -INFINITY) ? 0.f : mn0, mu1 = (mn1 == -INFINITY) ? 0.f : mn1;
+        alpha[nt][0] = ex2(m_run[nt][0] - mu0), alpha[nt][1] = ex2(m_run[nt][1] - mu1);
+        m_run[nt][0] = mn0, m_run[nt][1] = mn1;
+        const float p0 = ex2(s[0] - mu0), p1 = ex2(s[1] - mu1), p2 = ex2(s[2] - mu0), p3 = ex2(s[3] - mu1);
+        l_run[nt][0] = l_run[nt][0] * alpha[nt][0] + p0 + p2;
+        l_run[nt][1] = l_run[nt][1] * alpha[nt][1] + p1 + p3;
+        // P^T fragments: transpose the two 8x8 (token x head) blocks
+        pb[nt][0] = movmatrix_trans(pack2<MMA_BF16>(p0, p1));
+        pb[nt][1] = movmatrix_trans(pack2<MMA_BF16>(p2, p3));
+      }
+      // rescale the accumulators (columns = heads 2t, 2t+1)
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) {
+        if (alpha[nt][0] != 1.f || alpha[nt][1] != 1.f) {
+#pragma unroll
+          for (int mt = 0; mt < MTILES; ++mt) {
+            oacc[mt][nt][0] *= alpha[nt][0], oacc[mt][nt][2] *= alpha[nt][0];
+            oacc[mt][nt][1] *= alpha[nt][1], oacc[mt][nt][3] *= alpha[nt][1];
+          }
+        }
+      }
+
+      // ---- O^T[D][8 heads] += V^T P^T -----------------------------------------
+      // token masks for the V fragments of a partial tile (garbage x 0 must not make NaN)
+      uint32_t vm_lo = 0xffffffffu, vm_hi = 0xffffffffu;
+      if (partial) {
+        const int ta = 2 * t4, tb = 2 * t4 + 8;
+        auto okt = [&](int tk) { return tk < valid && tk >= win_lo; };
+        vm_lo = (okt(ta) ? 0x0000ffffu : 0u) | (okt(ta + 1) ? 0xffff0000u : 0u);
+        vm_hi = (okt(tb) ? 0x0000ffffu : 0u) | (okt(tb + 1) ? 0xffff0000u : 0u);
+      }
+      if constexpr (!KV_FP8) {
+#pragma unroll
+        for (int dc = 0; dc < NDC; ++dc) {
+#pragma unroll
+          for (int m4 = 0; m4 < 4; ++m4) {
+            uint32_t a[4];
+            const uint32_t chunk = (uint32_t)(2 * m4 + v_chunk_sel);
+            ldmatrix_x4_trans(a, vtile + dc * dc_stride + v_lane_off + ((chunk ^ swz) << 4));
+            // a0:(d gid; tok 2t,2t+1) a1:(d gid+8; same) a2:(d gid; tok 2t+8,+9) a3:(d gid+8; ...)
+            if (partial) a[0] &= vm_lo, a[1] &= vm_lo, a[2] &= vm_hi, a[3] &= vm_hi;
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) mma_16816<MMA_BF16>(oacc[dc * 4 + m4][nt], a, pb[nt][0], pb[nt][1]);
+          }
+        }
+      } else {
+#pragma unroll
+        for (int dc = 0; dc < NDC; ++dc) {
+#pragma unroll
+          for (int c2 = 0; c2 < 4; ++c2) {
+            uint32_t r[4];
+            const uint32_t chunk = (uint32_t)(2 * c2 + v_chunk_sel);
+            ldmatrix_x4_trans(r, vtile + dc * dc_stride + v_lane_off + ((chunk ^ swz) << 4));
+            // r0: tokens 0-7 chunk c | r1: tokens 8-15 chunk c | r2, r3: chunk c+1
+            // each: [tok 2t: d0 d1 | tok 2t+1: d0 d1] with d0 = 16c + 2gid
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+              const uint32_t x0 = __byte_perm(r[2 * half], 0, 0x3120);      // [t d0, t+1 d0 | t d1, t+1 d1]
+              const uint32_t x1 = __byte_perm(r[2 * half + 1], 0, 0x3120);
+              uint32_t a[4];
+              a[0] = e4m3x2_to_f16x2((uint16_t)(x0 & 0xffffu));  // row gid   <-> d0, tokens 2t,2t+1
+              a[1] = e4m3x2_to_f16x2((uint16_t)(x0 >> 16));      // row gid+8 <-> d1
+              a[2] = e4m3x2_to_f16x2((uint16_t)(x1 & 0xffffu));  // tokens 2t+8, 2t+9
+              a[3] = e4m3x2_to_f16x2((uint16_t)(x1 >> 16));
+              if (partial) a[0] &= vm_lo, a[1] &= vm_lo, a[2] &= vm_hi, a[3] &= vm_hi;
+              const int mt = dc * 8 + c2 * 2 + half;
+#pragma unroll
+              for (int nt = 0; nt < NT; ++nt) mma_16816<false>(oacc[mt][nt], a, pb[nt][0], pb[nt][1]);
+            }
+          }
+        }
+      }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty_bar[stage]);
+    if (++stage == P.stages) stage = 0, phase ^= 1;
+
+    const bool item_end = (cur.step + 1 == cur.first + cur.n);
+    const bool last = (cur.flat + 1 >= my_end);
+    if (item_end || last) {
+      // ---------------- finalise this (sequence, head group) ------------------
+      const int item = cur.b * P.head_groups + cur.hg;
+      const int item_flat0 = cur.flat - (cur.step - cur.first);
+      const bool direct = item_flat0 >= my_begin && item_flat0 + cur.n <= my_end;
+      const bool has_first = item_flat0 >= my_begin;
+      const int tq = P.a.cu_seqlens_q ? P.a.cu_seqlens_q[cur.b] : cur.b;
+      const int wph = NW / P.hpc;  // warps per kv head
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) {
+        // exp-sums: add up the 8 row groups
+        float l0 = l_run[nt][0], l1 = l_run[nt][1];
+#pragma unroll
+        for (int o = 4; o < 32; o <<= 1) {
+          l0 += __shfl_xor_sync(0xffffffffu, l0, o);
+          l1 += __shfl_xor_sync(0xffffffffu, l1, o);
+        }
+        if (nt > 0) asm volatile("bar.sync 1, %0;" ::"r"(NW * 32));
+        float* mb = mbuf + warp * 8 * D;
+#pragma unroll
+        for (int mt = 0; mt < MTILES; ++mt) {
+          int d0, d1;
+          if constexpr (!KV_FP8) d0 = 16 * mt + gid, d1 = d0 + 8;
+          else d0 = 16 * mt + 2 * gid, d1 = d0 + 1;
+          mb[(2 * t4) * D + d0] = oacc[mt][nt][0];
+          mb[(2 * t4 + 1) * D + d0] = oacc[mt][nt][1];
+          mb[(2 * t4) * D + d1] = oacc[mt][nt][2];
+          mb[(2 * t4 + 1) * D + d1] = oacc[mt][nt][3];
+        }
+        if (gid == 0) {
+          ml_buf[(warp * 8 + 2 * t4) * 2] = m_run[nt][0], ml_buf[(warp * 8 + 2 * t4) * 2 + 1] = l0;
+          ml_buf[(warp * 8 + 2 * t4 + 1) * 2] = m_run[nt][1], ml_buf[(warp * 8 + 2 * t4 + 1) * 2 + 1] = l1;
+        }
+        asm volatile("bar.sync 1, %0;" ::"r"(NW * 32));
+        // combine the warps that share a kv head; NW*32 threads cover hpc*8*D values
+        const int nheads = min(8, P.group - nt * 8);
+        const int tid = threadIdx.x;
+        for (int e = tid; e < P.hpc * 8 * D; e += NW * 32) {
+          const int hl = e / (8 * D), col = (e / D) & 7, d = e % D;
+          if (col >= nheads) continue;
+          float M = -INFINITY;
+          for (int j = 0; j < wph; ++j) M = fmaxf(M, ml_buf[((hl + P.hpc * j) * 8 + col) * 2]);
+          float val = 0.f, L = 0.f;
+          for (int j = 0; j < wph; ++j) {
+            const int w = hl + P.hpc * j;
+            const float mw = ml_buf[(w * 8 + col) * 2];
+            const float sc = (mw == -INFINITY) ? 0.f : ex2(mw - M);
+            val += mbuf[(w * 8 + col) * D + d] * sc;
+            L += ml_buf[(w * 8 + col) * 2 + 1] * sc;
+          }
+          const int hq_in_cta = hl * P.group + nt * 8 + col;  // query head within the CTA's head group
+          if (direct) {
+            const int hq = cur.hg * P.hpc * P.group + hq_in_cta;
+            const float o = (L > 0.f) ? val * v_scale / L : 0.f;
+            char* orow = static_cast<char*>(P.a.out) + ((int64_t)tq * P.a.out_stride0 + (int64_t)hq * P.a.out_stride1) * 2;
+            if constexpr (Q_BF16) reinterpret_cast<__nv_bfloat16*>(orow)[d] = __float2bfloat16_rn(o);
+            else reinterpret_cast<__half*>(orow)[d] = __float2half_rn(o);
+          } else {
+            const int64_t slot = (int64_t)item + blockIdx.x;
+            const int64_t rec = slot * (P.hpc * P.group) + hq_in_cta;
+            P.ws_acc[rec * D + d] = val;
+            if (d == 0) P.ws_ml[rec * 2] = M, P.ws_ml[rec * 2 + 1] = L;
+          }
+        }
+      }
+      if (threadIdx.x == 0) {
+        if (direct) P.ws_hi[item] = -1;
+        else {
+          if (has_first) P.ws_lo[item] = blockIdx.x;
+          if (item_end) P.ws_hi[item] = blockIdx.x;
+        }
+      }
+      if (last) break;
+      asm volatile("bar.sync 1, %0;" ::"r"(NW * 32));  // merge buffers are reused by the next item
+      cursor_next(P, cur);
+      reset_state();
+      load_q();
+    } else {
+      cursor_next(P, cur);
+    }
+  }
+}
+
+// K2b: merge the partials of every item that was split across CTAs.
+template <bool Q_BF16>
+__global__ void __launch_bounds__(128) decode_reduce_kernel(const DecodeParams P) {
+  const int item = blockIdx.x;
+  const int b = item / P.head_groups, hg = item % P.head_groups;
+  int seq_len, first, n;
+  seq_steps(P, b, seq_len, first, n);
+  const int D = P.a.head_size;
+  const int q_len = P.a.cu_seqlens_q ? (P.a.cu_seqlens_q[b + 1] - P.a.cu_seqlens_q[b]) : 1;
+  if (q_len <= 0) return;
+  const int tq = P.a.cu_seqlens_q ? P.a.cu_seqlens_q[b] : b;
+  const int rec_heads = P.hpc * P.group;
+  const float v_scale = (P.a.kv_dtype == B200ATTN_FP8_E4M3 && P.a.v_scale) ? *P.a.v_scale : 1.0f;
+  int lo = 0, hi = -1;
+  const bool empty = (n == 0);
+  if (!empty) {
+    hi = P.ws_hi[item];
+    if (hi < 0) return;  // written directly by the decode kernel
+    lo = P.ws_lo[item];
+  }
+  for (int e = threadIdx.x; e < rec_heads * D; e += blockDim.x) {
+    const int hq_in = e / D, d = e % D;
+    float o = 0.f;
+    if (!empty) {
+      float M = -INFINITY;
+      for (int c = lo; c <= hi; ++c) M = fmaxf(M, P.ws_ml[(((int64_t)item + c) * rec_heads + hq_in) * 2]);
+      float val = 0.f, L = 0.f;
+      for (int c = lo; c <= hi; ++c) {
+        const int64_t rec = ((int64_t)item + c) * rec_heads + hq_in;
+        const float mw = P.ws_ml[rec * 2];
+        const float sc = (mw == -INFINITY) ? 0.f : ex2(mw - M);
+        val += P.ws_acc[rec * D + d] * sc;
+        L += P.ws_ml[rec * 2 + 1] * sc;
+      }
+      o = (L > 0.f) ? val * v_scale / L : 0.f;  // 0 when nothing is visible (reference :828)
+    }
+    const int hq = hg * rec_heads + hq_in;
+    char* orow = static_cast<char*>(P.a.out) + ((int64_t)tq * P.a.out_stride0 + (int64_t)hq * P.a.out_stride1) * 2;
+    if constexpr (Q_BF16) reinterpret_cast<__nv_bfloat16*>(orow)[d] = __float2bfloat16_rn(o);
+    else reinterpret_cast<__half*>(orow)[d] = __float2half_rn(o);
+  }
+}
+
+// ---- host side ------------------------------------------------------------------
+struct MapKey {
+  const void* base;
+  int64_t s_block, s_slot, s_head, nb;
+  int bs, hkv, d, esz, box_slots, box_heads, box_dc;
+  bool operator==(const MapKey& o) const {
+    return base == o.base && s_block == o.s_block && s_slot == o.s_slot && s_head == o.s_head && nb == o.nb &&
+           bs == o.bs && hkv == o.hkv && d == o.d && esz == o.esz && box_slots == o.box_slots &&
+           box_heads == o.box_heads && box_dc == o.box_dc;
+  }
+};
+struct MapEntry {
+  MapKey key;
+  CUtensorMap map;
+  bool used = false;
+};
+thread_local MapEntry g_map_cache[16];
+thread_local int g_map_next = 0;
+
+// 5-D view of a paged cache: (128-byte chunk elems, slot, chunk, head, block)
+int make_kv_map(CUtensorMap* out, const void* base, int esz, int D, int bs, int hkv, int64_t nb, int64_t s_block,
+                int64_t s_slot, int64_t s_head, int box_slots, int box_heads, int box_dc) {
+  MapKey key{base, s_block, s_slot, s_head, nb, bs, hkv, D, esz, box_slots, box_heads, box_dc};
+  for (auto& e : g_map_cache)
+    if (e.used && e.key == key) {
+      *out = e.map;
+      return B200ATTN_OK;
+    }
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn) {
+    set_error("decode: cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
+    return B200ATTN_E_CUDA;
+  }
+  const int epc = 128 / esz;
+  cuuint64_t dims[5] = {(cuuint64_t)epc, (cuuint64_t)bs, (cuuint64_t)(D * esz / 128), (cuuint64_t)hkv, (cuuint64_t)nb};
+  cuuint64_t strides[4] = {(cuuint64_t)(s_slot * esz), 128, (cuuint64_t)(s_head * esz), (cuuint64_t)(s_block * esz)};
+  cuuint32_t box[5] = {(cuuint32_t)epc, (cuuint32_t)box_slots, (cuuint32_t)box_dc, (cuuint32_t)box_heads, 1};
+  cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+  CUtensorMapDataType dt = esz == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_UINT16;
+  CUresult r = fn(out, dt, 5, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("decode: cuTensorMapEncodeTiled failed (%d) strides=(%lld,128,%lld,%lld)B box=(%d,%d,%d,%d,1)", (int)r,
+              (long long)strides[0], (long long)strides[2], (long long)strides[3], epc, box_slots, box_dc, box_heads);
+    return B200ATTN_E_CUDA;
+  }
+  MapEntry& e = g_map_cache[g_map_next];
+  g_map_next = (g_map_next + 1) % 16;
+  e.key = key, e.map = *out, e.used = true;
+  return B200ATTN_OK;
+}
+
+struct DecodeConfig {
+  int nw, nt, hpc, stages, smem_bytes, grid;
+};
+
+inline int pick_hpc(int hkv, int nw, int want) {
+  int hpc = 1;
+  for (int c = nw; c >= 1; c >>= 1)
+    if (hkv % c == 0 && (want <= 0 || c <= want)) {
+      hpc = c;
+      break;
+    }
+  return hpc;
+}
+
+template <int D, bool KV_FP8, bool MMA_BF16, bool Q_BF16, int NT, int NW>
+int launch_variant(const b200attn_attention_params& a, DecodeParams& P, cudaStream_t stream) {
+  constexpr int ESZ = KV_FP8 ? 1 : 2;
+  constexpr int NDC = D * ESZ / 128;
+  constexpr int KV_STAGE_BYTES = NW * 16 * D * ESZ;
+  const DeviceInfo& dev = device_info();
+  const Tuning& tn = tuning();
+  P.hpc = pick_hpc(a.num_kv_heads, NW, tn.decode_heads_per_cta > 0 ? tn.decode_heads_per_cta : NW);
+  P.head_groups = a.num_kv_heads / P.hpc;
+  P.tps = NW * 16 / P.hpc;
+  P.box_slots = a.block_size < P.tps ? a.block_size : P.tps;
+  P.boxes = P.tps / P.box_slots;
+  P.tma_split = tn.reserved & 1;
+  const int fixed = NW * 8 * D * 4 + NW * 8 * 2 * 4 + 2 * kMaxStages * 8 + 64 + 1024 /*alignment slack*/;
+  int stages = (dev.max_smem_optin - fixed) / (2 * KV_STAGE_BYTES);
+  if (stages > kMaxStages) stages = kMaxStages;
+  if (tn.decode_stages > 0 && tn.decode_stages < stages) stages = tn.decode_stages;
+  if (stages < 2) {
+    set_error("decode: not enough shared memory for 2 stages (D=%d)", D);
+    return B200ATTN_E_UNSUPPORTED;
+  }
+  P.stages = stages;
+  const int smem = fixed + stages * 2 * KV_STAGE_BYTES;
+
+  CUtensorMap kmap, vmap;
+  const int box_heads = P.tma_split ? 1 : P.hpc, box_dc = P.tma_split ? 1 : NDC;
+  int rc = make_kv_map(&kmap, a.k_cache, ESZ, D, a.block_size, a.num_kv_heads, a.num_blocks, a.kc_block_stride,
+                       a.kc_slot_stride, a.kc_head_stride, P.box_slots, box_heads, box_dc);
+  if (rc) return rc;
+  rc = make_kv_map(&vmap, a.v_cache, ESZ, D, a.block_size, a.num_kv_heads, a.num_blocks, a.vc_block_stride,
+                   a.vc_slot_stride, a.vc_head_stride, P.box_slots, box_heads, box_dc);
+  if (rc) return rc;
+
+  // grid: one CTA per SM, never more CTAs than the upper bound on steps
+  const long long max_steps =
+      (long long)a.num_seqs * P.head_groups * ((a.max_seqlen_k + P.tps - 1) / P.tps > 0 ? (a.max_seqlen_k + P.tps - 1) / P.tps : 1);
+  long long grid = dev.num_sms;
+  if (grid > max_steps) grid = max_steps;
+  if (grid < 1) grid = 1;
+
+  auto kern = attn_decode_kernel<D, KV_FP8, MMA_BF16, Q_BF16, NT, NW>;
+  static thread_local bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, dev.max_smem_optin);
+    if (e != cudaSuccess) {
+      set_error("decode: cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
+      return B200ATTN_E_CUDA;
+    }
+    attr_set = true;
+  }
+  kern<<<(unsigned)grid, (NW + 1) * 32, smem, stream>>>(P, kmap, vmap);
+  note_launch("attn_decode_split_kv");
+  rc = check_launch("attn_decode");
+  if (rc) return rc;
+  decode_reduce_kernel<Q_BF16><<<(unsigned)(a.num_seqs * P.head_groups), 128, 0, stream>>>(P);
+  note_launch("decode_reduce");
+  return check_launch("decode_reduce");
+}
+
+template <int D, int NT, int NW>
+int dispatch_types(const b200attn_attention_params& a, DecodeParams& P, cudaStream_t stream) {
+  const bool qbf = a.q_dtype == B200ATTN_BF16;
+  if (a.kv_dtype == B200ATTN_FP8_E4M3) {
+    if constexpr (D >= 128) {
+      return qbf ? launch_variant<D, true, false, true, NT, NW>(a, P, stream)
+                 : launch_variant<D, true, false, false, NT, NW>(a, P, stream);
+    } else {
+      set_error("decode: fp8 KV needs head_size >= 128");
+      return B200ATTN_E_UNSUPPORTED;
+    }
+  }
+  return qbf ? launch_variant<D, false, true, true, NT, NW>(a, P, stream)
+             : launch_variant<D, false, false, false, NT, NW>(a, P, stream);
+}
+
+inline bool pow2(int x) { return x > 0 && (x & (x - 1)) == 0; }
+
+}  // namespace
+
+uint64_t decode_workspace_bytes(int num_seqs, int num_q_heads, int num_kv_heads, int head_size) {
+  // slots <= items + ctas; records of (hpc*group) heads: bounded by
+  // (B*Hq + ctas*8*group) head-rows of (D + 2) floats, plus lo/hi per item.
+  const uint64_t group = (uint64_t)(num_q_heads / (num_kv_heads > 0 ? num_kv_heads : 1));
+  const uint64_t ctas = 160;  // >= SM count of any B200 SKU
+  const uint64_t rows = (uint64_t)num_seqs * num_q_heads + ctas * 8 * (group > 0 ? group : 1);
+  const uint64_t items = (uint64_t)num_seqs * num_kv_heads;
+  return rows * (uint64_t)(head_size + 2) * 4 + items * 8 + 1024;
+}
+
+bool decode_supported(const b200attn_attention_params& p, const char** why) {
+  auto no = [&](const char* w) { if (why) *why = w; return false; };
+  if (p.max_seqlen_q != 1) return no("max_seqlen_q != 1");
+  if (p.q_dtype != B200ATTN_BF16 && p.q_dtype != B200ATTN_F16) return no("query dtype must be bf16/f16");
+  if (p.kv_dtype != p.q_dtype && p.kv_dtype != B200ATTN_FP8_E4M3) return no("kv dtype");
+  if (p.head_size != 64 && p.head_size != 128 && p.head_size != 256) return no("head_size not in {64,128,256}");
+  if (p.kv_dtype == B200ATTN_FP8_E4M3 && p.head_size < 128) return no("fp8 KV needs head_size >= 128");
+  if (p.num_kv_heads <= 0 || p.num_q_heads % p.num_kv_heads) return no("heads");
+  const int g = p.num_q_heads / p.num_kv_heads;
+  if (g > 16 || (g > 8 && p.head_size == 256)) return no("GQA group too large for the decode kernel");
+  if (!pow2(p.block_size) || p.block_size < 16 || p.block_size > 256) return no("block_size not a power of two in [16,256]");
+  const int esz = p.kv_dtype == B200ATTN_FP8_E4M3 ? 1 : 2;
+  auto m16 = [&](int64_t s) { return (s * esz) % 16 == 0; };
+  if (!m16(p.kc_block_stride) || !m16(p.kc_slot_stride) || !m16(p.kc_head_stride) || !m16(p.vc_block_stride) ||
+      !m16(p.vc_slot_stride) || !m16(p.vc_head_stride))
+    return no("cache strides not 16-byte multiples");
+  if ((reinterpret_cast<uintptr_t>(p.k_cache) & 15) || (reinterpret_cast<uintptr_t>(p.v_cache) & 15)) return no("cache base alignment");
+  if ((reinterpret_cast<uintptr_t>(p.q) & 7) || (p.q_stride0 % 4) || (p.q_stride1 % 4)) return no("query alignment");
+  if (p.sinks) return no("sinks");
+  return true;
+}
+
+int launch_attn_decode(const b200attn_attention_params& a, cudaStream_t stream) {
+  const char* why = nullptr;
+  if (!decode_supported(a, &why)) {
+    set_error("decode: unsupported configuration (%s)", why);
+    return B200ATTN_E_UNSUPPORTED;
+  }
+  const uint64_t need = decode_workspace_bytes(a.num_seqs, a.num_q_heads, a.num_kv_heads, a.head_size);
+  if (!a.workspace || a.workspace_bytes < need) {
+    set_error("decode: workspace too small (%llu < %llu bytes)", (unsigned long long)a.workspace_bytes,
+              (unsigned long long)need);
+    return B200ATTN_E_WORKSPACE;
+  }
+  DecodeParams P;
+  P.a = a;
+  P.group = a.num_q_heads / a.num_kv_heads;
+  // carve the workspace: lo/hi first (items <= B*Hkv), then ml, then acc
+  const uint64_t items_max = (uint64_t)a.num_seqs * a.num_kv_heads;
+  char* w = static_cast<char*>(a.workspace);
+  P.ws_lo = reinterpret_cast<int*>(w);
+  P.ws_hi = P.ws_lo + items_max;
+  uint64_t off = ((items_max * 8 + 255) / 256) * 256;
+  const uint64_t group = (uint64_t)P.group;
+  const uint64_t rows = (uint64_t)a.num_seqs * a.num_q_heads + 160ull * 8 * group;
+  P.ws_ml = reinterpret_cast<float*>(w + off);
+  off += ((rows * 8 + 255) / 256) * 256;
+  P.ws_acc = reinterpret_cast<float*>(w + off);
+  if (off + rows * a.head_size * 4 > a.workspace_bytes) {
+    set_error("decode: workspace carve-out exceeds the buffer");
+    return B200ATTN_E_WORKSPACE;
+  }
+  const int nt = P.group > 8 ? 2 : 1;
+  switch (a.head_size) {
+    case 64: return nt == 1 ? dispatch_types<64, 1, 8>(a, P, stream) : dispatch_types<64, 2, 8>(a, P, stream);
+    case 128: return nt == 1 ? dispatch_types<128, 1, 8>(a, P, stream) : dispatch_types<128, 2, 8>(a, P, stream);
+    case 256: return dispatch_types<256, 1, 4>(a, P, stream);
+  }
+  return B200ATTN_E_UNSUPPORTED;
+}
+
+}  // namespace b200attn

@@ -1,0 +1,378 @@
+// K3 (general): varlen / prefix / chunked-prefill / mixed-batch paged attention.
+//
+// Computes what the reference's 2D kernel computes
+// (reference ibm-triton-lib/ibm_triton_lib/kernels/triton_unified_attention.py:
+//  kernel_unified_attention_2d :275-523): per (q-block, kv-head), rows of the
+// tile are (query token, query head of the GQA group) pairs, KV tiles are
+// gathered through the block table, causal + context mask, optional softcap /
+// sliding window / ALiBi, online softmax in fp32, acc / L epilogue.
+// The launch grid is the same host-int upper bound the reference uses
+// (T // BLOCK_Q + num_seqs q-blocks, :886-889) with the same binary search from
+// q-block to sequence (:32-52), so it needs no host sync and is graph safe.
+//
+// Implementation: 4 warps x 16 rows, 64-token KV tiles moved with cp.async into
+// XOR-swizzled shared memory (double buffered), mma.sync m16n8k16 with fp32
+// accumulation; FP8-e4m3 KV is converted to f16 on its way into shared memory
+// and the per-tensor scales are folded into the softmax scale / epilogue.
+// This kernel takes every head size in {64,128,256} and any GQA group <= 64; the
+// tcgen05/TMEM kernel in attn_prefill_tc.cu is the fast path for D=128.
+#include "common.cuh"
+
+namespace b200attn {
+namespace {
+
+constexpr int BM = 64, BN = 64, NWARPS = 4;
+
+__device__ __forceinline__ float ex2f(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// byte offset of 16-byte chunk `c` of row `r` in a [rows][ROWB] tile, XOR swizzled
+template <int ROWB> __device__ __forceinline__ uint32_t swz_off(int r, int c) {
+  return (uint32_t)(r * ROWB + ((c ^ (r & 7)) << 4));
+}
+
+template <int D, bool MMA_BF16, bool Q_BF16, bool KV_FP8>
+__global__ void __launch_bounds__(NWARPS * 32, (D <= 128) ? 2 : 1)
+attn_prefill_kernel(const b200attn_attention_params p, const int block_q, const int group) {
+  constexpr int ROWB = D * 2;           // smem row bytes (operands are 2-byte in smem)
+  constexpr int CPR = ROWB / 16;        // 16-byte chunks per row
+  constexpr int KSTEPS = D / 16;
+  constexpr int DT = D / 8;             // n8 tiles of the output
+  constexpr int TILE_B = BN * ROWB;
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint8_t* sQ = smem;                   // [BM][ROWB]
+  uint8_t* sK = sQ + BM * ROWB;         // [2][BN][ROWB]
+  uint8_t* sV = sK + 2 * TILE_B;        // [2][BN][ROWB]
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int gid = lane >> 2, t4 = lane & 3;
+  const int q_block_global = blockIdx.x, kvh = blockIdx.y;
+
+  // ---- q-block -> sequence (binary search over cu_seqlens_q // BLOCK_Q + idx) --
+  int left = 0, right = p.num_seqs;
+  while (left < right) {
+    const int mid = (left + right) >> 1;
+    const int mid_val = p.cu_seqlens_q[mid] / block_q + mid;
+    if (mid_val <= q_block_global) left = mid + 1; else right = mid;
+  }
+  const int b = left - 1;
+  const int q_start = p.cu_seqlens_q[b];
+  const int q_len = p.cu_seqlens_q[b + 1] - q_start;
+  const int q_block_local = q_block_global - (q_start / block_q + b);
+  if (q_block_local * block_q >= q_len) return;
+  const int seq_len = p.seq_lens[b];
+  const int ctx = seq_len - q_len;
+  const int qpos0 = q_block_local * block_q;                   // first query position of this block
+  const int qpos_last = min(qpos0 + block_q, q_len) - 1;       // last valid one
+  int kv_limit = min(ctx + qpos_last + 1, seq_len);            // keys [0, kv_limit) can be visible
+  int kv_first = 0;
+  if (p.sliding_window > 0) kv_first = max(0, ctx + qpos0 - p.sliding_window + 1);
+  const int tile0 = kv_first / BN;
+  const int n_tiles = (kv_limit + BN - 1) / BN - tile0;
+
+  const int32_t* bt = p.block_tables + (int64_t)b * p.bt_stride0;
+  const float k_scale = (KV_FP8 && p.k_scale) ? *p.k_scale : 1.0f;
+  const float v_scale = (KV_FP8 && p.v_scale) ? *p.v_scale : 1.0f;
+  const bool has_cap = p.softcap > 0.f;
+  const float inv_cap = has_cap ? 1.f / p.softcap : 0.f;
+  const float qk_scale = p.softmax_scale * k_scale;
+
+  // ---- load the Q tile: row r = (token r / group, head r % group) --------------
+  const int rows_used = block_q * group;
+  for (int idx = tid; idx < BM * CPR; idx += NWARPS * 32) {
+    const int r = idx / CPR, c = idx % CPR;
+    const int tok = qpos0 + r / group, hq = kvh * group + r % group;
+    const bool ok = r < rows_used && tok < q_len;
+    int4 v = make_int4(0, 0, 0, 0);
+    if (ok) {
+      const char* src = static_cast<const char*>(p.q) + ((int64_t)(q_start + tok) * p.q_stride0 + (int64_t)hq * p.q_stride1) * 2 + c * 16;
+      v = *reinterpret_cast<const int4*>(src);
+      if constexpr (Q_BF16 && !MMA_BF16) {
+        uint32_t* w = reinterpret_cast<uint32_t*>(&v);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float2 f = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&w[i]));
+          w[i] = pack2<false>(fminf(fmaxf(f.x, -65504.f), 65504.f), fminf(fmaxf(f.y, -65504.f), 65504.f));
+        }
+      }
+    }
+    *reinterpret_cast<int4*>(sQ + swz_off<ROWB>(r, c)) = v;
+  }
+
+  // ---- KV tile loader -----------------------------------------------------------
+  auto load_tile = [&](int tile, int buf) {
+    const int n0 = tile * BN;
+    uint8_t* dK = sK + buf * TILE_B;
+    uint8_t* dV = sV + buf * TILE_B;
+    if constexpr (!KV_FP8) {
+      for (int idx = tid; idx < BN * CPR; idx += NWARPS * 32) {
+        const int r = idx / CPR, c = idx % CPR;
+        const int pos = n0 + r;
+        const bool ok = pos < kv_limit;
+        const int64_t page = ok ? bt[pos / p.block_size] : 0;
+        const int slot = pos % p.block_size;
+        const char* ksrc = static_cast<const char*>(p.k_cache) +
+                           (page * p.kc_block_stride + (int64_t)slot * p.kc_slot_stride + (int64_t)kvh * p.kc_head_stride) * 2 + c * 16;
+        const char* vsrc = static_cast<const char*>(p.v_cache) +
+                           (page * p.vc_block_stride + (int64_t)slot * p.vc_slot_stride + (int64_t)kvh * p.vc_head_stride) * 2 + c * 16;
+        cp_async_16(smem_u32(dK + swz_off<ROWB>(r, c)), ksrc, ok);
+        cp_async_16(smem_u32(dV + swz_off<ROWB>(r, c)), vsrc, ok);
+      }
+    } else {
+      // 16 fp8 -> 16 f16 = two 16-byte smem chunks
+      constexpr int CPR8 = D / 16;
+      for (int idx = tid; idx < BN * CPR8; idx += NWARPS * 32) {
+        const int r = idx / CPR8, c8 = idx % CPR8;
+        const int pos = n0 + r;
+        const bool ok = pos < kv_limit;
+        int4 kraw = make_int4(0, 0, 0, 0), vraw = kraw;
+        if (ok) {
+          const int64_t page = bt[pos / p.block_size];
+          const int slot = pos % p.block_size;
+          kraw = *reinterpret_cast<const int4*>(static_cast<const char*>(p.k_cache) + page * p.kc_block_stride +
+                                                (int64_t)slot * p.kc_slot_stride + (int64_t)kvh * p.kc_head_stride + c8 * 16);
+          vraw = *reinterpret_cast<const int4*>(static_cast<const char*>(p.v_cache) + page * p.vc_block_stride +
+                                                (int64_t)slot * p.vc_slot_stride + (int64_t)kvh * p.vc_head_stride + c8 * 16);
+        }
+        const uint32_t* kw = reinterpret_cast<const uint32_t*>(&kraw);
+        const uint32_t* vw = reinterpret_cast<const uint32_t*>(&vraw);
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          int4 ko, vo;
+          ko.x = e4m3x2_to_f16x2((uint16_t)(kw[2 * h] & 0xffff)), ko.y = e4m3x2_to_f16x2((uint16_t)(kw[2 * h] >> 16));
+          ko.z = e4m3x2_to_f16x2((uint16_t)(kw[2 * h + 1] & 0xffff)), ko.w = e4m3x2_to_f16x2((uint16_t)(kw[2 * h + 1] >> 16));
+          vo.x = e4m3x2_to_f16x2((uint16_t)(vw[2 * h] & 0xffff)), vo.y = e4m3x2_to_f16x2((uint16_t)(vw[2 * h] >> 16));
+          vo.z = e4m3x2_to_f16x2((uint16_t)(vw[2 * h + 1] & 0xffff)), vo.w = e4m3x2_to_f16x2((uint16_t)(vw[2 * h + 1] >> 16));
+          *reinterpret_cast<int4*>(dK + swz_off<ROWB>(r, 2 * c8 + h)) = ko;
+          *reinterpret_cast<int4*>(dV + swz_off<ROWB>(r, 2 * c8 + h)) = vo;
+        }
+      }
+    }
+  };
+
+  if (n_tiles > 0) load_tile(tile0, 0);
+  cp_async_commit();
+
+  // ---- per-thread row bookkeeping (rows gid and gid+8 of this warp's 16) ---------
+  int row_qpos[2], row_ok[2];
+  float row_slope[2];
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const int r = warp * 16 + gid + 8 * i;
+    row_qpos[i] = qpos0 + r / group;
+    row_ok[i] = (r < rows_used) && (row_qpos[i] < q_len);
+    row_slope[i] = (p.alibi_slopes && row_ok[i]) ? p.alibi_slopes[kvh * group + r % group] : 0.f;
+  }
+  // rows of this warp span query positions [wq_min, wq_max]
+  const int wq_min = qpos0 + (warp * 16) / group;
+  const int wq_max = min(qpos0 + (warp * 16 + 15) / group, qpos_last);
+
+  float oacc[DT][4];
+#pragma unroll
+  for (int i = 0; i < DT; ++i) oacc[i][0] = oacc[i][1] = oacc[i][2] = oacc[i][3] = 0.f;
+  float m_run[2] = {-INFINITY, -INFINITY}, l_run[2] = {0.f, 0.f};
+  constexpr bool kQInRegs = (D <= 128);  // D=256: re-read Q fragments from smem to stay under 255 registers
+  uint32_t qf[kQInRegs ? KSTEPS : 1][4];
+  bool q_loaded = false;
+
+  for (int it = 0; it < n_tiles; ++it) {
+    const int buf = it & 1;
+    if (it + 1 < n_tiles) load_tile(tile0 + it + 1, buf ^ 1);
+    cp_async_commit();
+    cp_async_wait<1>();
+    __syncthreads();
+    if (kQInRegs && !q_loaded) {
+      // Q fragments stay in registers for the whole KV loop
+#pragma unroll
+      for (int ks = 0; ks < (kQInRegs ? KSTEPS : 1); ++ks) {
+        const int r = warp * 16 + (lane & 7) + 8 * ((lane >> 3) & 1);
+        const int c = 2 * ks + (lane >> 4);
+        ldmatrix_x4(qf[ks], smem_u32(sQ + swz_off<ROWB>(r, c)));
+      }
+      q_loaded = true;
+    }
+    const int n0 = (tile0 + it) * BN;
+    const uint32_t kb = smem_u32(sK + buf * TILE_B), vb = smem_u32(sV + buf * TILE_B);
+    // warp-level causal skip: nothing in this tile is visible to this warp's rows
+    const bool warp_live = (n0 <= ctx + wq_max) && (warp * 16 < rows_used);
+    if (warp_live) {
+      // ---- S = Q K^T : 16 x 64 ---------------------------------------------------
+      float sacc[BN / 8][4];
+#pragma unroll
+      for (int i = 0; i < BN / 8; ++i) sacc[i][0] = sacc[i][1] = sacc[i][2] = sacc[i][3] = 0.f;
+#pragma unroll
+      for (int ks = 0; ks < KSTEPS; ++ks) {
+        if constexpr (!kQInRegs) {
+          const int r = warp * 16 + (lane & 7) + 8 * ((lane >> 3) & 1);
+          ldmatrix_x4(qf[0], smem_u32(sQ + swz_off<ROWB>(r, 2 * ks + (lane >> 4))));
+        }
+        const uint32_t (&qa)[4] = qf[kQInRegs ? ks : 0];
+#pragma unroll
+        for (int np = 0; np < BN / 16; ++np) {  // pairs of n8 tiles
+          uint32_t r4[4];
+          // matrices: (tok 0-7, c) (tok 0-7, c+1) (tok 8-15, c) (tok 8-15, c+1)
+          const int r = np * 16 + (lane & 7) + 8 * (lane >> 4);
+          const int c = 2 * ks + ((lane >> 3) & 1);
+          ldmatrix_x4(r4, kb + swz_off<ROWB>(r, c));
+          mma_16816<MMA_BF16>(sacc[2 * np], qa, r4[0], r4[1]);
+          mma_16816<MMA_BF16>(sacc[2 * np + 1], qa, r4[2], r4[3]);
+        }
+      }
+      // ---- scale / softcap / bias / mask -----------------------------------------
+      const bool full = (n0 + BN <= ctx + wq_min + 1) && (n0 + BN <= kv_limit) &&
+                        (p.sliding_window <= 0 || (ctx + wq_max - n0) < p.sliding_window) && (warp * 16 + 16 <= rows_used) &&
+                        (qpos0 + (warp * 16 + 15) / group < q_len);
+      float mx[2] = {-INFINITY, -INFINITY};
+#pragma unroll
+      for (int nt = 0; nt < BN / 8; ++nt) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int ri = i >> 1;
+          const int pos = n0 + nt * 8 + 2 * t4 + (i & 1);
+          float x = sacc[nt][i] * qk_scale;
+          if (has_cap) x = softcap_fn(x, p.softcap, inv_cap);
+          if (!full) {
+            bool vis = row_ok[ri] && pos < ctx + row_qpos[ri] + 1 && pos < seq_len;
+            if (p.sliding_window > 0) vis = vis && (ctx + row_qpos[ri] - pos) < p.sliding_window;
+            if (!vis) x = -INFINITY;
+          }
+          if (p.alibi_slopes) x += row_slope[ri] * (float)(pos - ctx);
+          x *= kLog2e;
+          sacc[nt][i] = x;
+          mx[ri] = fmaxf(mx[ri], x);
+        }
+      }
+      float alpha[2], mu[2];
+#pragma unroll
+      for (int ri = 0; ri < 2; ++ri) {
+        mx[ri] = fmaxf(mx[ri], __shfl_xor_sync(0xffffffffu, mx[ri], 1));
+        mx[ri] = fmaxf(mx[ri], __shfl_xor_sync(0xffffffffu, mx[ri], 2));
+        const float mn = fmaxf(m_run[ri], mx[ri]);
+        mu[ri] = (mn == -INFINITY) ? 0.f : mn;
+        alpha[ri] = ex2f(m_run[ri] - mu[ri]);
+        m_run[ri] = mn;
+      }
+      float ls[2] = {0.f, 0.f};
+      uint32_t pa[BN / 16][4];
+#pragma unroll
+      for (int nt = 0; nt < BN / 8; ++nt) {
+        const float p0 = ex2f(sacc[nt][0] - mu[0]), p1 = ex2f(sacc[nt][1] - mu[0]);
+        const float p2 = ex2f(sacc[nt][2] - mu[1]), p3 = ex2f(sacc[nt][3] - mu[1]);
+        ls[0] += p0 + p1, ls[1] += p2 + p3;
+        // C fragments of n-tiles (2j, 2j+1) are the A fragment of k16 step j
+        pa[nt >> 1][(nt & 1) * 2 + 0] = pack2<MMA_BF16>(p0, p1);
+        pa[nt >> 1][(nt & 1) * 2 + 1] = pack2<MMA_BF16>(p2, p3);
+      }
+      l_run[0] = l_run[0] * alpha[0] + ls[0];
+      l_run[1] = l_run[1] * alpha[1] + ls[1];
+#pragma unroll
+      for (int dt = 0; dt < DT; ++dt) {
+        oacc[dt][0] *= alpha[0], oacc[dt][1] *= alpha[0];
+        oacc[dt][2] *= alpha[1], oacc[dt][3] *= alpha[1];
+      }
+      // ---- O += P V ----------------------------------------------------------------
+#pragma unroll
+      for (int kt = 0; kt < BN / 16; ++kt) {
+#pragma unroll
+        for (int dp = 0; dp < DT / 2; ++dp) {  // pairs of d n8-tiles
+          uint32_t r4[4];
+          // trans matrices: (tok 0-7, dchunk c) (tok 8-15, c) (tok 0-7, c+1) (tok 8-15, c+1)
+          const int r = kt * 16 + (lane & 7) + 8 * ((lane >> 3) & 1);
+          const int c = 2 * dp + (lane >> 4);
+          ldmatrix_x4_trans(r4, vb + swz_off<ROWB>(r, c));
+          mma_16816<MMA_BF16>(oacc[2 * dp], pa[kt], r4[0], r4[1]);
+          mma_16816<MMA_BF16>(oacc[2 * dp + 1], pa[kt], r4[2], r4[3]);
+        }
+      }
+    }
+    __syncthreads();
+  }
+  cp_async_wait<0>();
+
+  // ---- epilogue: acc / L --------------------------------------------------------
+#pragma unroll
+  for (int ri = 0; ri < 2; ++ri) {
+    float l = l_run[ri];
+    l += __shfl_xor_sync(0xffffffffu, l, 1);
+    l += __shfl_xor_sync(0xffffffffu, l, 2);
+    if (!row_ok[ri]) continue;
+    const int r = warp * 16 + gid + 8 * ri;
+    const int hq = kvh * group + r % group;
+    const float inv = (l > 0.f) ? v_scale / l : 0.f;
+    char* orow = static_cast<char*>(p.out) + ((int64_t)(q_start + row_qpos[ri]) * p.out_stride0 + (int64_t)hq * p.out_stride1) * 2;
+#pragma unroll
+    for (int dt = 0; dt < DT; ++dt) {
+      const float a = oacc[dt][2 * ri] * inv, c = oacc[dt][2 * ri + 1] * inv;
+      *reinterpret_cast<uint32_t*>(orow + (dt * 8 + 2 * t4) * 2) = pack2<Q_BF16>(a, c);
+    }
+  }
+}
+
+template <int D, bool MMA_BF16, bool Q_BF16, bool KV_FP8>
+int launch_variant(const b200attn_attention_params& a, cudaStream_t stream) {
+  const int group = a.num_q_heads / a.num_kv_heads;
+  const int block_q = BM / group;
+  const int smem = BM * D * 2 + 4 * BN * D * 2;
+  auto kern = attn_prefill_kernel<D, MMA_BF16, Q_BF16, KV_FP8>;
+  static thread_local bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) {
+      set_error("prefill: cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
+      return B200ATTN_E_CUDA;
+    }
+    attr_set = true;
+  }
+  const dim3 grid((unsigned)(a.num_tokens / block_q + a.num_seqs), (unsigned)a.num_kv_heads);
+  kern<<<grid, NWARPS * 32, smem, stream>>>(a, block_q, group);
+  note_launch("attn_prefill_mma");
+  return check_launch("attn_prefill");
+}
+
+template <int D>
+int dispatch_types(const b200attn_attention_params& a, cudaStream_t stream) {
+  const bool qbf = a.q_dtype == B200ATTN_BF16;
+  if (a.kv_dtype == B200ATTN_FP8_E4M3)
+    return qbf ? launch_variant<D, false, true, true>(a, stream) : launch_variant<D, false, false, true>(a, stream);
+  return qbf ? launch_variant<D, true, true, false>(a, stream) : launch_variant<D, false, false, false>(a, stream);
+}
+
+}  // namespace
+
+bool prefill_supported(const b200attn_attention_params& p, const char** why) {
+  auto no = [&](const char* w) { if (why) *why = w; return false; };
+  if (p.q_dtype != B200ATTN_BF16 && p.q_dtype != B200ATTN_F16) return no("query dtype must be bf16/f16");
+  if (p.kv_dtype != p.q_dtype && p.kv_dtype != B200ATTN_FP8_E4M3) return no("kv dtype");
+  if (p.head_size != 64 && p.head_size != 128 && p.head_size != 256) return no("head_size not in {64,128,256}");
+  if (p.num_kv_heads <= 0 || p.num_q_heads % p.num_kv_heads) return no("heads");
+  if (p.num_q_heads / p.num_kv_heads > BM) return no("GQA group > 64");
+  const int esz = p.kv_dtype == B200ATTN_FP8_E4M3 ? 1 : 2;
+  auto m16 = [&](int64_t s) { return (s * esz) % 16 == 0; };
+  if (!m16(p.kc_block_stride) || !m16(p.kc_slot_stride) || !m16(p.kc_head_stride) || !m16(p.vc_block_stride) ||
+      !m16(p.vc_slot_stride) || !m16(p.vc_head_stride))
+    return no("cache strides not 16-byte multiples");
+  if ((reinterpret_cast<uintptr_t>(p.k_cache) & 15) || (reinterpret_cast<uintptr_t>(p.v_cache) & 15)) return no("cache base alignment");
+  if ((reinterpret_cast<uintptr_t>(p.q) & 15) || (p.q_stride0 % 8) || (p.q_stride1 % 8)) return no("query alignment");
+  if ((reinterpret_cast<uintptr_t>(p.out) & 3) || (p.out_stride0 % 2) || (p.out_stride1 % 2)) return no("output alignment");
+  if (p.sinks) return no("sinks");
+  return true;
+}
+
+int launch_attn_prefill(const b200attn_attention_params& a, cudaStream_t stream) {
+  const char* why = nullptr;
+  if (!prefill_supported(a, &why)) {
+    set_error("prefill: unsupported configuration (%s)", why);
+    return B200ATTN_E_UNSUPPORTED;
+  }
+  switch (a.head_size) {
+    case 64: return dispatch_types<64>(a, stream);
+    case 128: return dispatch_types<128>(a, stream);
+    case 256: return dispatch_types<256>(a, stream);
+  }
+  return B200ATTN_E_UNSUPPORTED;
+}
+
+}  // namespace b200attn

@@ -1,0 +1,180 @@
+// extern "C" surface of libb200attn.so (declared in include/b200attn.h).
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+
+#include "common.cuh"
+
+namespace b200attn {
+
+namespace {
+thread_local char g_error[512] = "";
+thread_local uint64_t g_launches = 0;
+thread_local const char* g_last_kernel = "";
+Tuning g_tuning;
+}  // namespace
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_error, sizeof(g_error), fmt, ap);
+  va_end(ap);
+}
+
+void note_launch(const char* kernel_name) {
+  ++g_launches;
+  g_last_kernel = kernel_name;
+}
+
+int check_launch(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("%s: CUDA launch failed: %s", what, cudaGetErrorString(e));
+    return B200ATTN_E_CUDA;
+  }
+  return B200ATTN_OK;
+}
+
+Tuning& tuning() { return g_tuning; }
+
+const DeviceInfo& device_info() {
+  static DeviceInfo info;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return;
+    cudaDeviceGetAttribute(&info.num_sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaDeviceGetAttribute(&info.max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+    cudaDeviceGetAttribute(&info.cc_major, cudaDevAttrComputeCapabilityMajor, dev);
+    cudaDeviceGetAttribute(&info.cc_minor, cudaDevAttrComputeCapabilityMinor, dev);
+  });
+  return info;
+}
+
+EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+namespace {
+
+int validate_attention(const b200attn_attention_params& p) {
+  if (!p.out || !p.q || !p.k_cache || !p.v_cache || !p.block_tables || !p.seq_lens || !p.cu_seqlens_q) {
+    set_error("unified_attention: null pointer argument");
+    return B200ATTN_E_NULL;
+  }
+  if (p.num_seqs < 0 || p.num_tokens < 0 || p.num_q_heads <= 0 || p.num_kv_heads <= 0 || p.head_size <= 0 ||
+      p.block_size <= 0 || p.num_q_heads % p.num_kv_heads != 0) {
+    set_error("unified_attention: bad shape (T=%d B=%d Hq=%d Hkv=%d D=%d bs=%d)", p.num_tokens, p.num_seqs,
+              p.num_q_heads, p.num_kv_heads, p.head_size, p.block_size);
+    return B200ATTN_E_BAD_SHAPE;
+  }
+  if (p.q_dtype != B200ATTN_BF16 && p.q_dtype != B200ATTN_F16 && p.q_dtype != B200ATTN_F32) {
+    // the reference rejects q_descale and we keep queries unquantised
+    set_error("unified_attention: query dtype %d not supported (bf16, f16, f32)", p.q_dtype);
+    return B200ATTN_E_BAD_DTYPE;
+  }
+  if (p.kv_dtype != p.q_dtype && p.kv_dtype != B200ATTN_FP8_E4M3) {
+    set_error("unified_attention: kv dtype %d must equal the query dtype or be fp8_e4m3", p.kv_dtype);
+    return B200ATTN_E_BAD_DTYPE;
+  }
+  if (p.head_size > 256) {
+    set_error("unified_attention: head_size %d > 256", p.head_size);
+    return B200ATTN_E_BAD_SHAPE;
+  }
+  return B200ATTN_OK;
+}
+
+}  // namespace
+}  // namespace b200attn
+
+using namespace b200attn;
+
+extern "C" {
+
+int b200attn_abi_version(void) { return B200ATTN_ABI_VERSION; }
+const char* b200attn_last_error(void) { return g_error; }
+uint64_t b200attn_launch_count(void) { return g_launches; }
+void b200attn_reset_launch_count(void) { g_launches = 0; }
+const char* b200attn_last_kernel(void) { return g_last_kernel; }
+
+void b200attn_set_tuning(int32_t decode_heads_per_cta, int32_t decode_ctas_per_sm, int32_t decode_stages,
+                         int32_t reserved) {
+  g_tuning.decode_heads_per_cta = decode_heads_per_cta;
+  g_tuning.decode_ctas_per_sm = decode_ctas_per_sm;
+  g_tuning.decode_stages = decode_stages;
+  g_tuning.reserved = reserved;
+}
+
+int b200attn_reshape_and_cache_flash(const void* key, const void* value, void* k_cache, void* v_cache,
+                                     const int64_t* slot_mapping, int64_t num_tokens, int32_t num_kv_heads,
+                                     int32_t head_size, int32_t block_size, int64_t key_stride0, int64_t value_stride0,
+                                     int64_t kc_block_stride, int64_t kc_slot_stride, int64_t kc_head_stride,
+                                     int64_t vc_block_stride, int64_t vc_slot_stride, int64_t vc_head_stride,
+                                     int32_t src_dtype, int32_t kv_dtype, const float* k_scale, const float* v_scale,
+                                     b200attn_stream_t stream) {
+  return launch_cache_write(key, value, k_cache, v_cache, slot_mapping, num_tokens, num_kv_heads, head_size,
+                            block_size, key_stride0, value_stride0, kc_block_stride, kc_slot_stride, kc_head_stride,
+                            vc_block_stride, vc_slot_stride, vc_head_stride, src_dtype, kv_dtype, k_scale, v_scale,
+                            reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b200attn_scaled_fp8_quant(void* out_fp8, const void* in, int64_t num_rows, int64_t row_elems,
+                              int64_t in_row_stride, int32_t src_dtype, const float* scale,
+                              b200attn_stream_t stream) {
+  return launch_scaled_fp8_quant(out_fp8, in, num_rows, row_elems, in_row_stride, src_dtype, scale,
+                                 reinterpret_cast<cudaStream_t>(stream));
+}
+
+uint64_t b200attn_workspace_bytes(int32_t num_tokens, int32_t num_seqs, int32_t num_q_heads, int32_t num_kv_heads,
+                                  int32_t head_size) {
+  (void)num_tokens;
+  return decode_workspace_bytes(num_seqs, num_q_heads, num_kv_heads, head_size);
+}
+
+int b200attn_unified_attention(const b200attn_attention_params* pp, b200attn_stream_t s) {
+  if (!pp) {
+    set_error("unified_attention: null params");
+    return B200ATTN_E_NULL;
+  }
+  const b200attn_attention_params& p = *pp;
+  if (p.num_tokens == 0 || p.num_seqs == 0) return B200ATTN_OK;
+  int rc = validate_attention(p);
+  if (rc) return rc;
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(s);
+  switch (p.path) {
+    case B200ATTN_PATH_GENERIC: return launch_attn_generic(p, stream);
+    case B200ATTN_PATH_PREFILL: return launch_attn_prefill(p, stream);
+    case B200ATTN_PATH_DECODE: return launch_attn_decode(p, stream);
+    case B200ATTN_PATH_PREFILL_TC: return launch_attn_prefill_tc(p, stream);
+    case B200ATTN_PATH_AUTO: break;
+    default:
+      set_error("unified_attention: unknown path %d", p.path);
+      return B200ATTN_E_BAD_SHAPE;
+  }
+  // AUTO: reference dispatch (max_seqlen_q > 1 -> 2D else 3D,
+  // triton_unified_attention.py:884); shapes a tensor-core kernel does not take
+  // run the SIMT kernel (still CUDA; there is no CPU path).
+  const char* why = nullptr;
+  if (p.max_seqlen_q <= 1) {
+    if (decode_supported(p, &why) && p.workspace &&
+        p.workspace_bytes >= decode_workspace_bytes(p.num_seqs, p.num_q_heads, p.num_kv_heads, p.head_size))
+      return launch_attn_decode(p, stream);
+    if (prefill_supported(p, &why)) return launch_attn_prefill(p, stream);
+    return launch_attn_generic(p, stream);
+  }
+  if (prefill_tc_supported(p, &why)) return launch_attn_prefill_tc(p, stream);
+  if (prefill_supported(p, &why)) return launch_attn_prefill(p, stream);
+  return launch_attn_generic(p, stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,280 @@
+// K1: KV-cache scatter write (+ optional fused FP8-e4m3 quantise), K4: static
+// per-tensor FP8 quantisation of Q.
+//
+// Semantics follow the reference's cache write, reshape_and_cache_flash_kernel
+// (reference vllm/csrc/cache_kernels.cu:286-358): one source row per token,
+// slot < 0 skipped, fp8 = e4m3_rn_satfinite(float(x) / scale) with a true fp32
+// division (quant_utils.cuh:479-502).  The implementation is new: every thread
+// moves 16 bytes per store (ld.global.nc.v4 / st.global.v4), K and V rows of a
+// token go to different CTAs (grid.y), and the index math is 64-bit for any
+// block/slot/head stride (NHD, HND, K/V-interleaved allocations).
+#include "common.cuh"
+
+namespace b200attn {
+namespace {
+
+__device__ __forceinline__ int4 ld_nc_v4(const void* p) {
+  int4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void st_v4(void* p, const int4& v) {
+  asm volatile("st.global.v4.s32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ void st_v2(void* p, const int2& v) {
+  asm volatile("st.global.v2.s32 [%0], {%1,%2};" ::"l"(p), "r"(v.x), "r"(v.y) : "memory");
+}
+
+// x / scale, RNE, saturating; two values -> two e4m3 bytes
+__device__ __forceinline__ uint16_t quant2(float a, float b, float scale) {
+  float2 v = make_float2(__fdiv_rn(a, scale), __fdiv_rn(b, scale));
+  return (uint16_t)__nv_cvt_float2_to_fp8x2(v, __NV_SATFINITE, __NV_E4M3);
+}
+
+template <typename SrcT> __device__ __forceinline__ void unpack8(const int4& raw, float (&f)[8]);
+template <> __device__ __forceinline__ void unpack8<__nv_bfloat16>(const int4& raw, float (&f)[8]) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float2 t = __bfloat1622float2(h[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
+template <> __device__ __forceinline__ void unpack8<__half>(const int4& raw, float (&f)[8]) {
+  const __half2* h = reinterpret_cast<const __half2*>(&raw);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float2 t = __half22float2(h[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
+
+struct CacheWriteArgs {
+  const void* src[2];  // key, value
+  void* dst[2];        // k_cache, v_cache
+  const int64_t* slot_mapping;
+  int64_t src_stride0[2];
+  int64_t block_stride[2], slot_stride[2], head_stride[2];
+  const float* scale[2];
+  int num_kv_heads, head_size, block_size;
+};
+
+// Copy path: 16-byte vectors of kElemBytes-sized elements.
+template <int kElemBytes>
+__global__ void __launch_bounds__(256) cache_copy_vec_kernel(CacheWriteArgs a) {
+  constexpr int kVec = 16 / kElemBytes;
+  const int64_t token = blockIdx.x;
+  const int which = blockIdx.y;
+  const int64_t slot = a.slot_mapping[token];
+  if (slot < 0) return;  // padded token
+  const int64_t blk = slot / a.block_size, off = slot % a.block_size;
+  const char* src = static_cast<const char*>(a.src[which]) + token * a.src_stride0[which] * kElemBytes;
+  char* dst = static_cast<char*>(a.dst[which]) + (blk * a.block_stride[which] + off * a.slot_stride[which]) * kElemBytes;
+  const int vec_per_head = a.head_size / kVec;
+  const int n_vec = a.num_kv_heads * vec_per_head;
+  for (int v = threadIdx.x; v < n_vec; v += blockDim.x) {
+    const int h = v / vec_per_head, dv = v - h * vec_per_head;
+    int4 x = ld_nc_v4(src + (int64_t)v * 16);
+    st_v4(dst + ((int64_t)h * a.head_stride[which]) * kElemBytes + (int64_t)dv * 16, x);
+  }
+}
+
+// FP8 path, 16 elements per thread: two 16-byte loads, one 16-byte store.
+template <typename SrcT>
+__global__ void __launch_bounds__(256) cache_quant_vec16_kernel(CacheWriteArgs a) {
+  const int64_t token = blockIdx.x;
+  const int which = blockIdx.y;
+  const int64_t slot = a.slot_mapping[token];
+  if (slot < 0) return;
+  const float scale = *a.scale[which];
+  const int64_t blk = slot / a.block_size, off = slot % a.block_size;
+  const SrcT* src = static_cast<const SrcT*>(a.src[which]) + token * a.src_stride0[which];
+  uint8_t* dst = static_cast<uint8_t*>(a.dst[which]) + blk * a.block_stride[which] + off * a.slot_stride[which];
+  const int vec_per_head = a.head_size / 16;
+  const int n_vec = a.num_kv_heads * vec_per_head;
+  for (int v = threadIdx.x; v < n_vec; v += blockDim.x) {
+    const int h = v / vec_per_head, dv = v - h * vec_per_head;
+    int4 lo = ld_nc_v4(src + (int64_t)v * 16);
+    int4 hi = ld_nc_v4(src + (int64_t)v * 16 + 8);
+    float f[16];
+    unpack8<SrcT>(lo, *reinterpret_cast<float(*)[8]>(&f[0]));
+    unpack8<SrcT>(hi, *reinterpret_cast<float(*)[8]>(&f[8]));
+    uint32_t w[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      w[i] = (uint32_t)quant2(f[4 * i], f[4 * i + 1], scale) | ((uint32_t)quant2(f[4 * i + 2], f[4 * i + 3], scale) << 16);
+    }
+    st_v4(dst + (int64_t)h * a.head_stride[which] + dv * 16, make_int4(w[0], w[1], w[2], w[3]));
+  }
+}
+
+// Element-wise net for shapes/alignments the vector kernels do not take.
+template <typename SrcT, bool kQuant>
+__global__ void __launch_bounds__(256) cache_scalar_kernel(CacheWriteArgs a) {
+  const int64_t token = blockIdx.x;
+  const int which = blockIdx.y;
+  const int64_t slot = a.slot_mapping[token];
+  if (slot < 0) return;
+  const int64_t blk = slot / a.block_size, off = slot % a.block_size;
+  const SrcT* src = static_cast<const SrcT*>(a.src[which]) + token * a.src_stride0[which];
+  const int n = a.num_kv_heads * a.head_size;
+  const int64_t base = blk * a.block_stride[which] + off * a.slot_stride[which];
+  if constexpr (kQuant) {
+    const float scale = *a.scale[which];
+    uint8_t* dst = static_cast<uint8_t*>(a.dst[which]);
+    for (int e = threadIdx.x; e < n; e += blockDim.x) {
+      const int h = e / a.head_size, d = e - h * a.head_size;
+      float x = __fdiv_rn(to_float<SrcT>(src[e]), scale);
+      dst[base + (int64_t)h * a.head_stride[which] + d] = (uint8_t)__nv_cvt_float_to_fp8(x, __NV_SATFINITE, __NV_E4M3);
+    }
+  } else {
+    SrcT* dst = static_cast<SrcT*>(a.dst[which]);
+    for (int e = threadIdx.x; e < n; e += blockDim.x) {
+      const int h = e / a.head_size, d = e - h * a.head_size;
+      dst[base + (int64_t)h * a.head_stride[which] + d] = src[e];
+    }
+  }
+}
+
+// K4: out = e4m3(float(in) * (1/scale)), one CTA per row
+// (reference vllm/csrc/quantization/w8a8/fp8/common.cu:11-29, common.cuh:40-60)
+template <typename SrcT>
+__global__ void __launch_bounds__(256) scaled_fp8_quant_kernel(uint8_t* out, const SrcT* in, int64_t row_elems,
+                                                               int64_t in_row_stride, const float* scale) {
+  const int64_t row = blockIdx.x;
+  const float inv = 1.0f / *scale;
+  const SrcT* src = in + row * in_row_stride;
+  uint8_t* dst = out + row * row_elems;
+  for (int64_t e = threadIdx.x; e < row_elems; e += blockDim.x) {
+    float x = to_float<SrcT>(src[e]) * inv;
+    x = fmaxf(-448.0f, fminf(448.0f, x));
+    dst[e] = (uint8_t)__nv_cvt_float_to_fp8(x, __NV_SATFINITE, __NV_E4M3);
+  }
+}
+
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+}  // namespace
+
+int launch_cache_write(const void* key, const void* value, void* k_cache, void* v_cache, const int64_t* slot_mapping,
+                       int64_t num_tokens, int num_kv_heads, int head_size, int block_size, int64_t key_stride0,
+                       int64_t value_stride0, int64_t kc_block_stride, int64_t kc_slot_stride, int64_t kc_head_stride,
+                       int64_t vc_block_stride, int64_t vc_slot_stride, int64_t vc_head_stride, int src_dtype,
+                       int kv_dtype, const float* k_scale, const float* v_scale, cudaStream_t stream) {
+  if (num_tokens == 0) return B200ATTN_OK;
+  if (!key || !value || !k_cache || !v_cache || !slot_mapping) {
+    set_error("reshape_and_cache_flash: null pointer");
+    return B200ATTN_E_NULL;
+  }
+  if (num_kv_heads <= 0 || head_size <= 0 || block_size <= 0 || num_tokens < 0) {
+    set_error("reshape_and_cache_flash: bad shape (heads %d, head_size %d, block_size %d)", num_kv_heads, head_size,
+              block_size);
+    return B200ATTN_E_BAD_SHAPE;
+  }
+  const bool quant = (kv_dtype == B200ATTN_FP8_E4M3) && (src_dtype != B200ATTN_FP8_E4M3);
+  if (!quant && kv_dtype != src_dtype) {
+    set_error("reshape_and_cache_flash: kv_dtype %d must equal src_dtype %d or be fp8_e4m3", kv_dtype, src_dtype);
+    return B200ATTN_E_BAD_DTYPE;
+  }
+  if (quant && (src_dtype != B200ATTN_BF16 && src_dtype != B200ATTN_F16 && src_dtype != B200ATTN_F32)) {
+    set_error("reshape_and_cache_flash: unsupported source dtype %d", src_dtype);
+    return B200ATTN_E_BAD_DTYPE;
+  }
+  if (quant && (!k_scale || !v_scale)) {
+    set_error("reshape_and_cache_flash: fp8 cache needs k_scale and v_scale");
+    return B200ATTN_E_NULL;
+  }
+  CacheWriteArgs a;
+  a.src[0] = key, a.src[1] = value;
+  a.dst[0] = k_cache, a.dst[1] = v_cache;
+  a.slot_mapping = slot_mapping;
+  a.src_stride0[0] = key_stride0, a.src_stride0[1] = value_stride0;
+  a.block_stride[0] = kc_block_stride, a.block_stride[1] = vc_block_stride;
+  a.slot_stride[0] = kc_slot_stride, a.slot_stride[1] = vc_slot_stride;
+  a.head_stride[0] = kc_head_stride, a.head_stride[1] = vc_head_stride;
+  a.scale[0] = k_scale, a.scale[1] = v_scale;
+  a.num_kv_heads = num_kv_heads, a.head_size = head_size, a.block_size = block_size;
+
+  const int sb = dtype_bytes(src_dtype), kb = dtype_bytes(kv_dtype);
+  if (sb == 0 || kb == 0) {
+    set_error("reshape_and_cache_flash: bad dtype");
+    return B200ATTN_E_BAD_DTYPE;
+  }
+  auto mult = [](int64_t x, int64_t m) { return x % m == 0; };
+  const dim3 grid((unsigned)num_tokens, 2);
+  const int n_elems = num_kv_heads * head_size;
+
+  if (!quant) {
+    const int vec = 16 / sb;
+    const bool vec_ok = mult(head_size, vec) && aligned16(key) && aligned16(value) && aligned16(k_cache) &&
+                        aligned16(v_cache) && mult(key_stride0, vec) && mult(value_stride0, vec) &&
+                        mult(kc_block_stride, vec) && mult(kc_slot_stride, vec) && mult(kc_head_stride, vec) &&
+                        mult(vc_block_stride, vec) && mult(vc_slot_stride, vec) && mult(vc_head_stride, vec);
+    if (vec_ok) {
+      int threads = n_elems / vec;
+      threads = threads < 32 ? 32 : (threads > 256 ? 256 : ((threads + 31) / 32) * 32);
+      if (sb == 2) cache_copy_vec_kernel<2><<<grid, threads, 0, stream>>>(a);
+      else if (sb == 4) cache_copy_vec_kernel<4><<<grid, threads, 0, stream>>>(a);
+      else cache_copy_vec_kernel<1><<<grid, threads, 0, stream>>>(a);
+      note_launch("cache_copy_vec");
+    } else {
+      int threads = n_elems > 256 ? 256 : ((n_elems + 31) / 32) * 32;
+      if (src_dtype == B200ATTN_BF16) cache_scalar_kernel<__nv_bfloat16, false><<<grid, threads, 0, stream>>>(a);
+      else if (src_dtype == B200ATTN_F16) cache_scalar_kernel<__half, false><<<grid, threads, 0, stream>>>(a);
+      else if (src_dtype == B200ATTN_F32) cache_scalar_kernel<float, false><<<grid, threads, 0, stream>>>(a);
+      else cache_scalar_kernel<uint8_t, false><<<grid, threads, 0, stream>>>(a);
+      note_launch("cache_copy_scalar");
+    }
+  } else {
+    const bool vec_ok = sb == 2 && mult(head_size, 16) && aligned16(key) && aligned16(value) && aligned16(k_cache) &&
+                        aligned16(v_cache) && mult(key_stride0, 8) && mult(value_stride0, 8) &&
+                        mult(kc_block_stride, 16) && mult(kc_slot_stride, 16) && mult(kc_head_stride, 16) &&
+                        mult(vc_block_stride, 16) && mult(vc_slot_stride, 16) && mult(vc_head_stride, 16);
+    if (vec_ok) {
+      int threads = n_elems / 16;
+      threads = threads < 32 ? 32 : (threads > 256 ? 256 : ((threads + 31) / 32) * 32);
+      if (src_dtype == B200ATTN_BF16) cache_quant_vec16_kernel<__nv_bfloat16><<<grid, threads, 0, stream>>>(a);
+      else cache_quant_vec16_kernel<__half><<<grid, threads, 0, stream>>>(a);
+      note_launch("cache_quant_vec16");
+    } else {
+      int threads = n_elems > 256 ? 256 : ((n_elems + 31) / 32) * 32;
+      if (src_dtype == B200ATTN_BF16) cache_scalar_kernel<__nv_bfloat16, true><<<grid, threads, 0, stream>>>(a);
+      else if (src_dtype == B200ATTN_F16) cache_scalar_kernel<__half, true><<<grid, threads, 0, stream>>>(a);
+      else cache_scalar_kernel<float, true><<<grid, threads, 0, stream>>>(a);
+      note_launch("cache_quant_scalar");
+    }
+  }
+  return check_launch("reshape_and_cache_flash");
+}
+
+int launch_scaled_fp8_quant(void* out, const void* in, int64_t rows, int64_t row_elems, int64_t in_row_stride,
+                            int src_dtype, const float* scale, cudaStream_t stream) {
+  if (rows == 0 || row_elems == 0) return B200ATTN_OK;
+  if (!out || !in || !scale) {
+    set_error("scaled_fp8_quant: null pointer");
+    return B200ATTN_E_NULL;
+  }
+  int threads = row_elems > 256 ? 256 : (int)((row_elems + 31) / 32) * 32;
+  uint8_t* o = static_cast<uint8_t*>(out);
+  if (src_dtype == B200ATTN_BF16)
+    scaled_fp8_quant_kernel<__nv_bfloat16><<<(unsigned)rows, threads, 0, stream>>>(
+        o, static_cast<const __nv_bfloat16*>(in), row_elems, in_row_stride, scale);
+  else if (src_dtype == B200ATTN_F16)
+    scaled_fp8_quant_kernel<__half><<<(unsigned)rows, threads, 0, stream>>>(o, static_cast<const __half*>(in),
+                                                                            row_elems, in_row_stride, scale);
+  else if (src_dtype == B200ATTN_F32)
+    scaled_fp8_quant_kernel<float><<<(unsigned)rows, threads, 0, stream>>>(o, static_cast<const float*>(in), row_elems,
+                                                                           in_row_stride, scale);
+  else {
+    set_error("scaled_fp8_quant: unsupported source dtype %d", src_dtype);
+    return B200ATTN_E_BAD_DTYPE;
+  }
+  note_launch("scaled_fp8_quant");
+  return check_launch("scaled_fp8_quant");
+}
+
+}  // namespace b200attn

@@ -1,0 +1,242 @@
+"""Host-side operators: the reference's call signatures over the C ABI.
+
+* `reshape_and_cache_flash(...)` has the argument list of
+  `torch.ops._C_cache_ops.reshape_and_cache_flash` as the reference calls it
+  (ibm-triton-lib/ibm_triton_lib/backend/triton_attn.py:396-405).
+* `unified_attention(...)` has the keyword names of the reference launcher
+  (ibm-triton-lib/ibm_triton_lib/kernels/triton_unified_attention.py:839-860) so
+  `scripts/callers/unified_triton.py:61-82` and the upstream tests can call it
+  unchanged, and mirrors its checks and its 2D/3D dispatch (:861-867, :884).
+
+PyTorch is used for device memory and streams only; the arithmetic runs in
+libb200attn.so.  Nothing here falls back to PyTorch or the CPU.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional, Tuple
+
+import torch
+
+from . import _cabi
+from ._cabi import AttentionParams
+
+_DTYPE = {
+    torch.bfloat16: _cabi.BF16,
+    torch.float16: _cabi.F16,
+    torch.float32: _cabi.F32,
+    torch.float8_e4m3fn: _cabi.FP8_E4M3,
+    torch.uint8: _cabi.FP8_E4M3,  # vLLM allocates fp8 caches as uint8
+}
+
+_workspaces: dict = {}
+_scalar_cache: dict = {}
+
+
+def _stream_ptr(t: torch.Tensor) -> int:
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def _require_cuda(*tensors: torch.Tensor) -> None:
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError(
+                "b200attn operators run on CUDA tensors only (there is no CPU fallback); got a tensor on " f"{t.device}"
+            )
+
+
+def _scalar_tensor(value, device) -> torch.Tensor:
+    """fp32 device scalar for a host float (cached; device tensors pass through)."""
+    if isinstance(value, torch.Tensor):
+        if value.dtype != torch.float32:
+            raise ValueError("scales must be float32 tensors")
+        return value
+    key = (str(device), float(value))
+    t = _scalar_cache.get(key)
+    if t is None:
+        t = torch.tensor([float(value)], dtype=torch.float32, device=device)
+        _scalar_cache[key] = t
+    return t
+
+
+def workspace_bytes(num_tokens: int, num_seqs: int, num_q_heads: int, num_kv_heads: int, head_size: int) -> int:
+    return int(_cabi.load_library().b200attn_workspace_bytes(num_tokens, num_seqs, num_q_heads, num_kv_heads, head_size))
+
+
+def get_workspace(device, nbytes: int) -> torch.Tensor:
+    """Grow-only per-device split-KV workspace (replaces the reference's per-call
+    torch.empty of segm_output/segm_max/segm_expsum, triton_unified_attention.py:950-971)."""
+    key = str(device)
+    ws = _workspaces.get(key)
+    if ws is None or ws.numel() < nbytes:
+        if torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("b200attn workspace must be allocated before CUDA-graph capture (pass workspace=...)")
+        ws = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+        _workspaces[key] = ws
+    return ws
+
+
+def reshape_and_cache_flash(
+    key: torch.Tensor,  # [>=T, Hkv, D]
+    value: torch.Tensor,
+    key_cache: torch.Tensor,  # [NB, bs, Hkv, D] view (any block stride; NHD or HND strides)
+    value_cache: torch.Tensor,
+    slot_mapping: torch.Tensor,  # int64 [T]
+    kv_cache_dtype: str,
+    k_scale,
+    v_scale,
+) -> None:
+    _require_cuda(key, value, key_cache, value_cache, slot_mapping)
+    if slot_mapping.dtype != torch.int64:
+        raise ValueError("slot_mapping must be int64")
+    if key.dim() != 3 or key_cache.dim() != 4:
+        raise ValueError("key must be [T, Hkv, D] and key_cache [NB, bs, Hkv, D]")
+    if key.stride(2) != 1 or key.stride(1) != key.shape[2] or value.stride(2) != 1 or value.stride(1) != value.shape[2]:
+        raise ValueError("key/value rows must be contiguous in (head, dim)")
+    if key_cache.stride(3) != 1 or value_cache.stride(3) != 1:
+        raise ValueError("cache head_dim must be the contiguous dimension")
+    src_dt = _DTYPE.get(key.dtype)
+    fp8 = kv_cache_dtype.startswith("fp8")
+    if fp8:
+        if kv_cache_dtype not in ("fp8", "fp8_e4m3"):
+            raise ValueError(f"unsupported kv_cache_dtype {kv_cache_dtype!r} (fp8_e4m3 only)")
+        if key_cache.element_size() != 1:
+            raise ValueError("fp8 kv cache must be a 1-byte tensor")
+        kv_dt = _cabi.FP8_E4M3
+        ks = _scalar_tensor(k_scale, key.device)
+        vs = _scalar_tensor(v_scale, key.device)
+        ks_ptr, vs_ptr = ks.data_ptr(), vs.data_ptr()
+    else:
+        if key_cache.dtype != key.dtype:
+            raise ValueError(f"kv cache dtype {key_cache.dtype} != key dtype {key.dtype} with kv_cache_dtype={kv_cache_dtype!r}")
+        kv_dt = src_dt
+        ks_ptr = vs_ptr = None
+    if src_dt is None:
+        raise ValueError(f"unsupported key dtype {key.dtype}")
+    lib = _cabi.load_library()
+    _, bs, hkv, d = key_cache.shape
+    _cabi.check(
+        lib.b200attn_reshape_and_cache_flash(
+            key.data_ptr(), value.data_ptr(), key_cache.data_ptr(), value_cache.data_ptr(), slot_mapping.data_ptr(),
+            slot_mapping.shape[0], hkv, d, bs, key.stride(0), value.stride(0),
+            key_cache.stride(0), key_cache.stride(1), key_cache.stride(2),
+            value_cache.stride(0), value_cache.stride(1), value_cache.stride(2),
+            src_dt, kv_dt, ks_ptr, vs_ptr, _stream_ptr(key),
+        )
+    )
+
+
+def scaled_fp8_quant(x: torch.Tensor, scale: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Static per-tensor FP8 quantisation (`ops.scaled_fp8_quant(x, scale)`,
+    reference triton_attn.py:417). x: [rows, n]."""
+    _require_cuda(x, scale)
+    if x.dim() != 2 or x.stride(1) != 1:
+        raise ValueError("x must be 2-D with a contiguous last dimension")
+    out = torch.empty(x.shape, dtype=torch.float8_e4m3fn, device=x.device)
+    _cabi.check(
+        _cabi.load_library().b200attn_scaled_fp8_quant(
+            out.data_ptr(), x.data_ptr(), x.shape[0], x.shape[1], x.stride(0), _DTYPE[x.dtype], scale.data_ptr(), _stream_ptr(x)
+        )
+    )
+    return out, scale
+
+
+def build_attention_params(
+    q, k, v, out, cu_seqlens_q, max_seqlen_q, seqused_k, max_seqlen_k, softmax_scale, window_size, block_table,
+    softcap, k_descale, v_descale, alibi_slopes, path, workspace,
+) -> AttentionParams:
+    if q.dim() != 3 or k.dim() != 4 or v.dim() != 4:
+        raise ValueError("q must be [T, Hq, D]; k, v must be [NB, bs, Hkv, D]")
+    if q.stride(2) != 1 or out.stride(2) != 1 or k.stride(3) != 1 or v.stride(3) != 1:
+        raise ValueError("innermost dimension of q/out/k/v must be contiguous")
+    if block_table.dtype != torch.int32 or seqused_k.dtype != torch.int32 or cu_seqlens_q.dtype != torch.int32:
+        raise ValueError("block_table, seqused_k and cu_seqlens_q must be int32")
+    if out.dtype != q.dtype:
+        raise ValueError("out dtype must equal q dtype")
+    q_dt, kv_dt = _DTYPE.get(q.dtype), _DTYPE.get(k.dtype)
+    if q_dt is None or q_dt == _cabi.FP8_E4M3:
+        raise ValueError(f"unsupported query dtype {q.dtype}")
+    if kv_dt is None or v.dtype != k.dtype:
+        raise ValueError(f"unsupported kv cache dtypes {k.dtype}/{v.dtype}")
+    p = AttentionParams()
+    p.out, p.q, p.k_cache, p.v_cache = out.data_ptr(), q.data_ptr(), k.data_ptr(), v.data_ptr()
+    p.block_tables, p.seq_lens, p.cu_seqlens_q = block_table.data_ptr(), seqused_k.data_ptr(), cu_seqlens_q.data_ptr()
+    p.alibi_slopes = alibi_slopes.data_ptr() if alibi_slopes is not None else None
+    p.k_scale = k_descale.data_ptr() if k_descale is not None else None
+    p.v_scale = v_descale.data_ptr() if v_descale is not None else None
+    p.sinks = None
+    p.softmax_scale = float(softmax_scale)
+    p.softcap = float(softcap or 0.0)
+    p.sliding_window = int(1 + window_size[0]) if window_size is not None else 0  # reference :915
+    p.num_tokens, p.num_seqs = q.shape[0], seqused_k.shape[0]
+    p.num_q_heads, p.num_kv_heads, p.head_size = q.shape[1], k.shape[2], q.shape[2]
+    p.block_size = v.shape[1]
+    p.max_seqlen_q, p.max_seqlen_k = int(max_seqlen_q), int(max_seqlen_k)
+    p.q_dtype, p.kv_dtype, p.path = q_dt, kv_dt, path
+    p.num_blocks = k.shape[0]
+    p.q_stride0, p.q_stride1 = q.stride(0), q.stride(1)
+    p.out_stride0, p.out_stride1 = out.stride(0), out.stride(1)
+    p.bt_stride0 = block_table.stride(0)
+    p.kc_block_stride, p.kc_slot_stride, p.kc_head_stride = k.stride(0), k.stride(1), k.stride(2)
+    p.vc_block_stride, p.vc_slot_stride, p.vc_head_stride = v.stride(0), v.stride(1), v.stride(2)
+    if workspace is not None:
+        p.workspace, p.workspace_bytes = workspace.data_ptr(), workspace.numel() * workspace.element_size()
+    else:
+        p.workspace, p.workspace_bytes = None, 0
+    return p
+
+
+def unified_attention(
+    q: torch.Tensor,  # [T, Hq, D]
+    k: torch.Tensor,  # key cache   [NB, bs, Hkv, D]
+    v: torch.Tensor,  # value cache [NB, bs, Hkv, D]
+    out: torch.Tensor,  # [T, Hq, D]
+    cu_seqlens_q: torch.Tensor,  # int32 [B+1]
+    max_seqlen_q: int,
+    seqused_k: torch.Tensor,  # int32 [B]
+    max_seqlen_k: int,
+    softmax_scale: float,
+    causal: bool,
+    window_size,  # (sliding_window - 1, 0) or (-1, -1)
+    block_table: torch.Tensor,  # int32 [B, MB]
+    softcap: float,
+    q_descale,
+    k_descale: Optional[torch.Tensor],
+    v_descale: Optional[torch.Tensor],
+    alibi_slopes: Optional[torch.Tensor] = None,
+    avg_seqlen_q=None,  # tuning inputs of the reference's autotuner; unused here
+    avg_seqlen_k=None,
+    force_selection: Optional[int] = None,  # None, 2 (2D kernel), 3 (3D kernel) as in the reference; 1 = SIMT net
+    workspace: Optional[torch.Tensor] = None,
+    **_ignored,
+) -> None:
+    if not causal:
+        raise AssertionError("Only causal attention is supported")  # reference :861
+    if q_descale is not None:
+        raise AssertionError("Q scales not supported")  # reference :862
+    _require_cuda(q, k, v, out, cu_seqlens_q, seqused_k, block_table)
+    if q.element_size() < 2:
+        # the reference's fp8-Q branch ignores k/v scales; not offered
+        raise ValueError("fp8 queries are not supported; keep Q in bf16/fp16")
+
+    max_seqlen_q = int(max_seqlen_q)
+    # reference dispatch (:884): any batch with a multi-token query runs the 2D kernel
+    if force_selection == 1:
+        path = _cabi.PATH_GENERIC
+    elif force_selection == 4:
+        path = _cabi.PATH_PREFILL_TC
+    elif max_seqlen_q > 1:
+        path = _cabi.PATH_AUTO if force_selection != 22 else _cabi.PATH_PREFILL
+    elif force_selection == 2:
+        path = _cabi.PATH_PREFILL
+    else:
+        path = _cabi.PATH_AUTO
+
+    if workspace is None and max_seqlen_q <= 1 and path in (_cabi.PATH_AUTO, _cabi.PATH_DECODE):
+        need = workspace_bytes(q.shape[0], seqused_k.shape[0], q.shape[1], k.shape[2], q.shape[2])
+        workspace = get_workspace(q.device, need)
+    p = build_attention_params(
+        q, k, v, out, cu_seqlens_q, max_seqlen_q, seqused_k, max_seqlen_k, softmax_scale, window_size, block_table,
+        softcap, k_descale, v_descale, alibi_slopes, path, workspace,
+    )
+    _cabi.check(_cabi.load_library().b200attn_unified_attention(ctypes.byref(p), _stream_ptr(q)))
