@@ -70,7 +70,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(self.gpu_index)],
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "50", "-i", str(self.gpu_index)],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except Exception:
             self.proc = None
@@ -172,6 +172,27 @@ def make_device_workload(w, hq, hkv, device, seed):
     return dict(kv=kv, block_table=block_table, seq_lens=seq_lens, cu=cu, slot_mapping=last, q=q, k_new=k_new, v_new=v_new)
 
 
+
+def measure_prefill(device, world):
+    """Tensor-bound half of the metric: prefill attention TFLOP/s on one full 8k causal
+    prompt and on the C3 chunked-prefill mixed batch (Llama-3.1-8B shape), through
+    ops.unified_attention.  CUDA events around >= 50 ms of launches after warm-up."""
+    import types
+
+    sys.path.insert(0, os.path.join(ROOT, "scripts"))
+    import kbench
+
+    out = {}
+    for shape in ("full8k", "mixed"):
+        a = types.SimpleNamespace(shape=shape, hq=0, hkv=0, bs=0, fp8=False, layout="planes", force=None)
+        fn, flops, cfg = kbench.prefill_case(a, device)
+        ms, n = kbench.time_fn(fn, min_ms=50.0)
+        out[shape] = dict(ms=ms, tflops=flops / ms / 1e9, tokens=cfg["T"], iters=n)
+        del fn
+        torch.cuda.empty_cache()
+    return out
+
+
 class _Layer:
     """The attributes of vLLM's Attention layer the impl reads."""
 
@@ -211,7 +232,7 @@ def run_ours(args):
     layer = _Layer(device, 0.5 if fp8 else 1.0, 0.5 if fp8 else 1.0)
     impl = B200AttentionImpl(num_heads=hq, head_size=D, scale=scale, num_kv_heads=hkv, alibi_slopes=None,
                              sliding_window=None, kv_cache_dtype="fp8" if fp8 else "auto")
-    workspace = torch.empty(ops.workspace_bytes(B, B, hq, hkv, D), dtype=torch.uint8, device=device)
+    workspace = torch.zeros(ops.workspace_bytes(B, B, hq, hkv, D), dtype=torch.uint8, device=device)
     meta = B200AttentionMetadata(num_actual_tokens=B, max_query_len=1, query_start_loc=st["cu"], max_seq_len=w["ctx"],
                                  seq_lens=st["seq_lens"], block_table=st["block_table"], slot_mapping=st["slot_mapping"],
                                  workspace=workspace)
@@ -296,6 +317,12 @@ def run_ours(args):
     e2e_s = time.perf_counter() - t0
     clocks = sampler.stop(t_begin, t_end)
 
+    pre = None
+    if not args.no_prefill:
+        del st["kv"]
+        torch.cuda.empty_cache()
+        pre = measure_prefill(device, world)
+
     # ---- reduce over ranks --------------------------------------------------------
     stats = torch.tensor([total_ms, e2e_s * 1e3, statistics.mean(att_ms)], dtype=torch.float64, device=device)
     if world > 1:
@@ -322,7 +349,7 @@ def run_ours(args):
             "data": "synthetic",
             "config": {"workload": w["desc"], "batch": B, "ctx": w["ctx"], "q_heads_per_gpu": hq, "kv_heads_per_gpu": hkv,
                        "head_dim": D, "block_size": w["bs"], "kv_cache_dtype": w["kv"],
-                       "step": "reshape_and_cache_flash(64 new tokens) + decode attention (split-KV + reduce)",
+                       "step": "reshape_and_cache_flash(64 new tokens) + decode attention (split-KV, fused merge)",
                        "l2": f"KV working set {dec_bytes / 1e9:.2f} GB per GPU >> 126 MB L2; no flush needed",
                        "parallelism": f"kv-head shard x{world} (no collective)"},
             "clocks": clocks,
@@ -332,12 +359,24 @@ def run_ours(args):
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": round(achieved, 2), "peak": peaks["hbm_gbs"], "unit": "GB/s",
                          "frac": round(achieved / peaks["hbm_gbs"], 4), "traffic": args.ncu_traffic,
-                         "kernel": "attn_decode_kernel (+decode_reduce_kernel, same C call)", "peak_source": peaks["source"],
+                         "kernel": "attn_decode_kernel (split-KV, merge of partials fused in)", "peak_source": peaks["source"],
                          "frac_of_nominal_8TBs": round(achieved / 8000.0, 4), "algorithmic_bytes_per_launch": dec_bytes,
                          "avg_launch_ms": round(att_mean_ms, 5)},
             "extras": {"decode_tokens_per_s": round(world * B / (ms_per_step * 1e-3), 1),
                        "e2e_tokens_per_s": round(world * B / (e2e_ms / K * 1e-3), 1), "last_kernel": dominant},
         }
+        if pre is not None:
+            # per-rank numbers of rank 0 (every rank runs the same shapes); whole-job = x world
+            line["prefill"] = {
+                "bound": "tensor", "unit": "TFLOP/s", "peak": peaks["bf16_tflops"], "peak_source": peaks["source"],
+                "full_8k_prompt": {"tflops_per_gpu": round(pre["full8k"]["tflops"], 1), "ms": round(pre["full8k"]["ms"], 4),
+                                   "frac": round(pre["full8k"]["tflops"] / peaks["bf16_tflops"], 4),
+                                   "tokens_per_s": round(world * pre["full8k"]["tokens"] / pre["full8k"]["ms"] * 1e3, 1)},
+                "c3_chunked_prefill_mixed": {"tflops_per_gpu": round(pre["mixed"]["tflops"], 1), "ms": round(pre["mixed"]["ms"], 4),
+                                             "frac": round(pre["mixed"]["tflops"] / peaks["bf16_tflops"], 4),
+                                             "tokens_per_s": round(world * pre["mixed"]["tokens"] / pre["mixed"]["ms"] * 1e3, 1)},
+                "kernel": "attn_prefill_tc_kernel (tcgen05/TMEM) + short/decode rows via attn_prefill_kernel / attn_decode_kernel",
+            }
         if cpu_baseline is not None:
             line["cpu_baseline"] = cpu_baseline
         print(json.dumps(line), flush=True)
@@ -445,6 +484,7 @@ def main():
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-prefill", action="store_true", help="skip the prefill TFLOP/s section")
     ap.add_argument("--ncu-traffic", type=float, default=None,
                     help="dram bytes per launch of the decode kernel from the committed ncu capture (profiles/)")
     args = ap.parse_args()

@@ -124,7 +124,9 @@ typedef struct b200attn_attention_params {
   int64_t bt_stride0;
   int64_t kc_block_stride, kc_slot_stride, kc_head_stride;
   int64_t vc_block_stride, vc_slot_stride, vc_head_stride;
-  void* workspace;             /* split-KV partials; caller-owned                  */
+  void* workspace;             /* split-KV partials + ticket counters; caller-owned,
+                                  zero-filled ONCE when allocated (the kernels leave
+                                  the counters at zero after every call)           */
   uint64_t workspace_bytes;
 } b200attn_attention_params;
 

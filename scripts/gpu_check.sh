@@ -11,7 +11,8 @@ run() { # name, pytest args...
 }
 run cache tests/test_gpu_cache_write.py
 run generic tests/test_gpu_attention.py -k "generic or odd_head or argument_checks"
-run prefill tests/test_gpu_attention.py -k "prefill and not through_prefill"
+run prefill tests/test_gpu_attention.py -k "prefill and not through_prefill and not prefill_tc"
+run tc tests/test_gpu_attention.py -k "prefill_tc or mixed_batch or workspace_counters"
 run decode tests/test_gpu_attention.py -k "decode"
 run golden_tc tests/test_gpu_attention.py -k "golden_tensor_core"
 run surface tests/test_backend_surface.py

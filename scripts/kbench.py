@@ -1,0 +1,303 @@
+#!/usr/bin/env python
+"""Kernel micro-benchmarks for tuning (not the driver's bench.py contract).
+
+    python scripts/kbench.py decode  [--workload c2|c4|c2var] [--hpc H] [--stages S] [--split X] [--hkv N --hq N]
+    python scripts/kbench.py prefill [--shape full8k|chunk|mixed|full2k] [--force 2|4]
+    python scripts/kbench.py cache   [--tokens T] [--fp8]
+    python scripts/kbench.py sweep   (decode knob sweep on c2 and c4)
+
+Every line printed is JSON: time per call (CUDA events around >= 50 ms of
+back-to-back launches after warm-up; working sets are >> L2 for decode, and an
+L2 flush variant is available with --flush), algorithmic GB/s or TFLOP/s and the
+fraction of the measured peak (MEASURED_PEAKS.json).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+from vllm_triton_backend_b200 import _cabi, ops  # noqa: E402
+from vllm_triton_backend_b200.roofline import attention_flops, cache_write_bytes, decode_bytes  # noqa: E402
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), float(d["bf16_tflops"])
+    return 6650.0, 1590.0
+
+
+def time_fn(fn, min_ms=60.0, warmup=5, flush=None):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    # calibrate
+    e0.record()
+    fn()
+    e1.record()
+    torch.cuda.synchronize()
+    one = max(e0.elapsed_time(e1), 1e-3)
+    n = max(5, min(2000, int(min_ms / one)))
+    if flush is None:
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / n, n
+    tot = 0.0
+    n = min(n, 50)
+    for _ in range(n):
+        flush.zero_()
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        tot += e0.elapsed_time(e1)
+    return tot / n, n
+
+
+def make_kv(NB, bs, hkv, D, fp8, device, g, layout="planes"):
+    shape = (2, NB, bs, hkv, D) if layout == "planes" else (NB, 2, bs, hkv, D)
+    dt = torch.uint8 if fp8 else torch.bfloat16
+    kv = torch.empty(shape, dtype=dt, device=device)
+    flat = kv.view(-1)
+    chunk = 1 << 26
+    for o in range(0, flat.numel(), chunk):
+        n = min(chunk, flat.numel() - o)
+        x = torch.rand(n, device=device, generator=g) * 2 - 1
+        if fp8:
+            flat[o:o + n] = (x / 0.5).to(torch.float8_e4m3fn).view(torch.uint8)
+        else:
+            flat[o:o + n] = x.to(torch.bfloat16)
+    if fp8:
+        kv = kv.view(torch.float8_e4m3fn)
+    return kv.unbind(0) if layout == "planes" else kv.unbind(1)
+
+
+def decode_case(args, device):
+    g = torch.Generator(device=device).manual_seed(0)
+    if args.workload == "c4":
+        B, ctx, hq, hkv, D, bs, fp8 = 64, 32768, 64, 8, 128, 16, True
+    else:
+        B, ctx, hq, hkv, D, bs, fp8 = 64, 4096, 32, 8, 128, 16, False
+    if args.hq:
+        hq = args.hq
+    if args.hkv:
+        hkv = args.hkv
+    if args.batch:
+        B = args.batch
+    if args.ctx:
+        ctx = args.ctx
+    if args.bs:
+        bs = args.bs
+    if args.fp8:
+        fp8 = True
+    if args.workload == "c2var":
+        pat = [0.1, 0.4, 0.5, 1.0, 0.2]  # reference scripts/benchmark.py:115
+        lens = [max(1, int(ctx * pat[i % len(pat)])) for i in range(B)]
+    else:
+        lens = [ctx] * B
+    pages = [(n + bs - 1) // bs for n in lens]
+    NB = sum(pages) + 1024
+    kc, vc = make_kv(NB, bs, hkv, D, fp8, device, g, args.layout)
+    perm = torch.randperm(NB, device=device, generator=g).to(torch.int32)
+    bt = torch.zeros(B, max(pages), dtype=torch.int32, device=device)
+    o = 0
+    for i, n in enumerate(pages):
+        bt[i, :n] = perm[o:o + n]
+        o += n
+    sl = torch.tensor(lens, dtype=torch.int32, device=device)
+    cu = torch.arange(B + 1, dtype=torch.int32, device=device)
+    q = (torch.rand(B, hq, D, device=device, generator=g) * 2 - 1).to(torch.bfloat16)
+    out = torch.empty_like(q)
+    ws = torch.zeros(ops.workspace_bytes(B, B, hq, hkv, D), dtype=torch.uint8, device=device)
+    sc = torch.tensor([0.5], dtype=torch.float32, device=device) if fp8 else None
+    nbytes = decode_bytes(lens, hq, hkv, D, bs, 1 if fp8 else 2)
+
+    def fn():
+        ops.unified_attention(q=q, k=kc, v=vc, out=out, cu_seqlens_q=cu, max_seqlen_q=1, seqused_k=sl,
+                              max_seqlen_k=max(lens), softmax_scale=D ** -0.5, causal=True, window_size=(-1, -1),
+                              block_table=bt, softcap=0, q_descale=None, k_descale=sc, v_descale=sc, workspace=ws,
+                              force_selection=args.force)
+    return fn, nbytes, dict(B=B, ctx=ctx, hq=hq, hkv=hkv, D=D, bs=bs, fp8=fp8, workload=args.workload, layout=args.layout)
+
+
+def run_decode(args, device):
+    hbm, _ = peaks()
+    fn, nbytes, cfg = decode_case(args, device)
+    _cabi.set_tuning(args.hpc, args.ctas, args.stages, args.split)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=device) if args.flush else None
+    ms, n = time_fn(fn, flush=flush)
+    gbs = nbytes / ms / 1e6
+    print(json.dumps(dict(kind="decode", **cfg, hpc=args.hpc, stages=args.stages, split=args.split, ctas=args.ctas,
+                          ms=round(ms, 5), gbs=round(gbs, 1), frac_measured=round(gbs / hbm, 4),
+                          frac_8tbs=round(gbs / 8000, 4), iters=n, kernel=_cabi.last_kernel(), flush=bool(args.flush))),
+          flush=True)
+    _cabi.set_tuning(0, 0, 0, 0)
+
+
+PREFILL_SHAPES = {
+    # list of (q_len, kv_len)
+    "full8k": [(8192, 8192)],
+    "full2k": [(2048, 2048)] * 4,
+    "full1k": [(1024, 1024)] * 8,
+    "chunk": [(2048, 6144), (2048, 8192)],
+    # C3: 32 decode rows + fresh prompt + 2 chunked continuations + 4 prefix hits
+    "mixed": None,
+}
+
+
+def mixed_c3(seed=0):
+    import random
+
+    rnd = random.Random(seed)
+    dec = [(1, rnd.randint(128, 8192)) for _ in range(32)]
+    big = [(2048, 2048), (2048, 6144), (1024, 7168)]
+    hits = [(rnd.randint(128, 1024), 0) for _ in range(4)]
+    hits = [(q, q + (1024 if i % 2 == 0 else 2048)) for i, (q, _) in enumerate(hits)]
+    seqs = []
+    rest = big + hits
+    # alternate decode / prefill as the reference harness does (scripts/benchmark.py:1101-1112)
+    while dec or rest:
+        if rest:
+            seqs.append(rest.pop(0))
+        if dec:
+            seqs.append(dec.pop(0))
+    return seqs
+
+
+def prefill_case(args, device):
+    g = torch.Generator(device=device).manual_seed(0)
+    hq, hkv, D, bs = args.hq or 32, args.hkv or 8, 128, args.bs or 16
+    lens = PREFILL_SHAPES[args.shape] or mixed_c3()
+    q_lens = [a for a, _ in lens]
+    kv_lens = [b for _, b in lens]
+    pages = [(n + bs - 1) // bs for n in kv_lens]
+    NB = sum(pages) + 64
+    kc, vc = make_kv(NB, bs, hkv, D, args.fp8, device, g, args.layout)
+    perm = torch.randperm(NB, device=device, generator=g).to(torch.int32)
+    bt = torch.zeros(len(lens), max(pages), dtype=torch.int32, device=device)
+    o = 0
+    for i, n in enumerate(pages):
+        bt[i, :n] = perm[o:o + n]
+        o += n
+    T = sum(q_lens)
+    q = (torch.rand(T, hq, D, device=device, generator=g) * 2 - 1).to(torch.bfloat16)
+    out = torch.empty_like(q)
+    cu = torch.tensor([0] + list(torch.tensor(q_lens).cumsum(0)), dtype=torch.int32, device=device)
+    sl = torch.tensor(kv_lens, dtype=torch.int32, device=device)
+    sc = torch.tensor([0.5], dtype=torch.float32, device=device) if args.fp8 else None
+    ws = torch.zeros(ops.workspace_bytes(T, len(lens), hq, hkv, D), dtype=torch.uint8, device=device)
+    flops = attention_flops(q_lens, kv_lens, hq, D)
+
+    def fn():
+        ops.unified_attention(q=q, k=kc, v=vc, out=out, cu_seqlens_q=cu, max_seqlen_q=max(q_lens), seqused_k=sl,
+                              max_seqlen_k=max(kv_lens), softmax_scale=D ** -0.5, causal=True, window_size=(-1, -1),
+                              block_table=bt, softcap=0, q_descale=None, k_descale=sc, v_descale=sc, workspace=ws,
+                              force_selection=args.force)
+    return fn, flops, dict(shape=args.shape, T=T, seqs=len(lens), hq=hq, hkv=hkv, D=D, bs=bs, fp8=bool(args.fp8))
+
+
+def run_prefill(args, device):
+    _, tf = peaks()
+    fn, flops, cfg = prefill_case(args, device)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=device) if args.flush else None
+    ms, n = time_fn(fn, flush=flush)
+    tfs = flops / ms / 1e9
+    print(json.dumps(dict(kind="prefill", **cfg, force=args.force, ms=round(ms, 5), tflops=round(tfs, 1),
+                          frac_measured=round(tfs / tf, 4), tokens_per_s=round(cfg["T"] / ms * 1e3, 1), iters=n,
+                          kernel=_cabi.last_kernel(), launches_per_call=None)), flush=True)
+
+
+def run_cache(args, device):
+    hbm, _ = peaks()
+    g = torch.Generator(device=device).manual_seed(0)
+    T, hkv, D, bs = args.tokens, args.hkv or 8, 128, args.bs or 16
+    NB = (T + bs - 1) // bs + 64
+    kc, vc = make_kv(NB, bs, hkv, D, args.fp8, device, g, args.layout)
+    key = (torch.rand(T, hkv, D, device=device, generator=g) * 2 - 1).to(torch.bfloat16)
+    val = (torch.rand(T, hkv, D, device=device, generator=g) * 2 - 1).to(torch.bfloat16)
+    slots = torch.randperm(NB * bs, device=device, generator=g)[:T].to(torch.int64)
+    sc = torch.tensor([0.5], dtype=torch.float32, device=device)
+    nbytes = cache_write_bytes(T, hkv, D, 2, 1 if args.fp8 else 2)
+
+    def fn():
+        ops.reshape_and_cache_flash(key, val, kc, vc, slots, "fp8" if args.fp8 else "auto", sc, sc)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=device) if args.flush else None
+    ms, n = time_fn(fn, flush=flush)
+    gbs = nbytes / ms / 1e6
+    print(json.dumps(dict(kind="cache_write", tokens=T, hkv=hkv, D=D, bs=bs, fp8=bool(args.fp8), ms=round(ms, 5),
+                          gbs=round(gbs, 1), frac_measured=round(gbs / hbm, 4), iters=n, kernel=_cabi.last_kernel(),
+                          flush=bool(args.flush))), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("kind", choices=["decode", "prefill", "cache", "sweep"])
+    ap.add_argument("--workload", default="c2")
+    ap.add_argument("--shape", default="full8k", choices=sorted(PREFILL_SHAPES))
+    ap.add_argument("--hpc", type=int, default=0)
+    ap.add_argument("--ctas", type=int, default=0)
+    ap.add_argument("--stages", type=int, default=0)
+    ap.add_argument("--split", type=int, default=0)
+    ap.add_argument("--hq", type=int, default=0)
+    ap.add_argument("--hkv", type=int, default=0)
+    ap.add_argument("--batch", type=int, default=0)
+    ap.add_argument("--ctx", type=int, default=0)
+    ap.add_argument("--bs", type=int, default=0)
+    ap.add_argument("--tokens", type=int, default=8192)
+    ap.add_argument("--fp8", action="store_true")
+    ap.add_argument("--flush", action="store_true")
+    ap.add_argument("--layout", default="planes", choices=["planes", "interleaved"])
+    ap.add_argument("--force", type=int, default=None)
+    args = ap.parse_args()
+    device = torch.device("cuda", 0)
+    torch.cuda.set_device(0)
+    if args.kind == "decode":
+        run_decode(args, device)
+    elif args.kind == "prefill":
+        run_prefill(args, device)
+    elif args.kind == "cache":
+        run_cache(args, device)
+    else:
+        hbm, _ = peaks()
+        variants = [("c2", {}), ("c2var", {}), ("c4", {}), ("c4", dict(hq=32, hkv=4)), ("c4", dict(hq=16, hkv=2)),
+                    ("c4", dict(hq=8, hkv=1)), ("c2", dict(batch=8)), ("c2", dict(batch=1, ctx=32768)),
+                    ("c2", dict(batch=256, ctx=1024)), ("c2", dict(bs=128))]
+        for wl, over in variants:
+            args.workload = wl
+            args.hq = args.hkv = args.batch = args.ctx = args.bs = 0
+            for k, v in over.items():
+                setattr(args, k, v)
+            fn, nbytes, cfg = decode_case(args, device)
+            for hpc in (0, 1, 2, 4, 8):
+                if hpc > cfg["hkv"]:
+                    continue
+                for stages in (0, 4):
+                    try:
+                        _cabi.set_tuning(hpc, 0, stages, 0)
+                        ms, n = time_fn(fn, min_ms=30.0)
+                        gbs = nbytes / ms / 1e6
+                        print(json.dumps(dict(kind="decode", workload=wl, **over, hpc=hpc, stages=stages,
+                                              ms=round(ms, 5), gbs=round(gbs, 1), frac_measured=round(gbs / hbm, 4))),
+                              flush=True)
+                    except Exception as e:  # keep sweeping
+                        print(json.dumps(dict(kind="decode", workload=wl, **over, hpc=hpc, stages=stages,
+                                              error=str(e)[:200])), flush=True)
+            _cabi.set_tuning(0, 0, 0, 0)
+            del fn
+            torch.cuda.empty_cache()
+
+
+if __name__ == "__main__":
+    main()

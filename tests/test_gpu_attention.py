@@ -10,7 +10,7 @@ from oracle.paged_attention import unified_attention_ref
 
 pytestmark = pytest.mark.gpu
 
-GENERIC, PREFILL, DECODE_OR_AUTO = 1, 2, None
+GENERIC, PREFILL, DECODE_OR_AUTO, PREFILL_TC = 1, 2, None, 4
 
 
 def _run(inp, scale, path, window=0, softcap=0.0, alibi=None, k_scale=None, v_scale=None, dtype=None):
@@ -72,7 +72,7 @@ def test_golden_tensor_core_kernels(path, dtype):
     c = load_golden_attn(path)
     out, kern = _run(c, c["scale"], DECODE_OR_AUTO, window=c["window"], softcap=c["softcap"], alibi=c["alibi_slopes"],
                      dtype=dtype)
-    assert kern in ("decode_reduce", "attn_prefill_mma", "attn_prefill_tc"), kern
+    assert kern in ("attn_decode_split_kv", "attn_prefill_mma", "attn_prefill_tc"), kern
     # golden inputs live on the fp16 grid; bf16 casts them, so compare with the oracle on the cast inputs too
     assert_close(out, _oracle(c, c["scale"], c["window"], c["softcap"], c["alibi_slopes"], dtype=dtype),
                  atol=BF16_ATOL, rtol=BF16_RTOL, what=c["name"] + " vs oracle")
@@ -103,7 +103,7 @@ def test_decode_matches_oracle(lens, Hq, Hkv, D, bs, dtype, interleaved):
     inp = make_paged_inputs([(1, n) for n in lens], Hq, Hkv, D, bs, dtype=dtype, seed=len(lens) + D, interleaved=interleaved)
     scale = D ** -0.5
     out, kern = _run(inp, scale, DECODE_OR_AUTO)
-    assert kern == "decode_reduce", kern
+    assert kern == "attn_decode_split_kv", kern
     assert_close(out, _oracle(inp, scale), atol=BF16_ATOL, rtol=BF16_RTOL, what="decode")
     assert not torch.isnan(out).any()
 
@@ -136,7 +136,7 @@ def test_decode_features(feature, D):
     alibi = torch.tensor([2.0 ** (-(i + 1)) for i in range(Hq)]) if feature in ("alibi", "all") else None
     scale = D ** -0.5
     out, kern = _run(inp, scale, DECODE_OR_AUTO, window=window, softcap=softcap, alibi=alibi)
-    assert kern == "decode_reduce"
+    assert kern == "attn_decode_split_kv"
     assert_close(out, _oracle(inp, scale, window, softcap, alibi), atol=BF16_ATOL, rtol=BF16_RTOL, what=feature)
 
 
@@ -149,7 +149,7 @@ def test_decode_fp8_kv(scales, Hq, Hkv, dtype):
                             kv_dtype=torch.float8_e4m3fn, k_scale=scales[0], v_scale=scales[1])
     scale = 128 ** -0.5
     out, kern = _run(inp, scale, DECODE_OR_AUTO, k_scale=scales[0], v_scale=scales[1])
-    assert kern == "decode_reduce"
+    assert kern == "attn_decode_split_kv"
     assert_close(out, _oracle(inp, scale, k_scale=scales[0], v_scale=scales[1]), atol=FP8_ATOL, rtol=BF16_RTOL, what="fp8 decode")
 
 
@@ -230,8 +230,113 @@ def test_decode_batch_through_prefill_kernel_matches_decode_kernel():
     inp = make_paged_inputs([(1, n) for n in lens], 32, 8, 128, 16, dtype=torch.bfloat16, seed=8)
     a, ka = _run(inp, 0.088, DECODE_OR_AUTO)
     b, kb = _run(inp, 0.088, PREFILL)
-    assert ka == "decode_reduce" and kb == "attn_prefill_mma"
+    assert ka == "attn_decode_split_kv" and kb == "attn_prefill_mma"
     assert_close(a, b, atol=1e-2, rtol=1e-2, what="2D vs 3D")
+
+
+# ---------------------------------------------------------------------------------
+# tcgen05 / TMEM prefill kernel (D=128, bf16/f16 KV)
+# ---------------------------------------------------------------------------------
+TC_CASES = [
+    # (q, kv) lens, Hq, Hkv, block_size
+    ([(128, 128)], 4, 1, 16),                                      # one full tile pair, group 4
+    ([(64, 64)], 4, 1, 16),                                        # second subtile empty
+    ([(1, 1328), (5, 18), (129, 463)], 4, 4, 16),                  # upstream shapes, MHA
+    ([(1, 1328), (5, 18), (129, 463)], 8, 2, 16),
+    ([(200, 200), (64, 64), (1, 1), (77, 300)], 32, 8, 16),        # fresh prompts + prefix hit
+    ([(512, 1536), (33, 33), (1, 700), (1, 9)], 32, 8, 32),        # chunked continuation + decodes
+    ([(300, 1000), (257, 257)], 16, 2, 64),                        # group 8, block 64
+    ([(130, 900)], 8, 8, 128),                                     # block == tile
+    ([(100, 700), (31, 31)], 16, 1, 256),                          # MQA 16, block > tile
+    ([(1000, 1000)], 64, 8, 16),
+]
+
+
+@pytest.mark.parametrize("lens,Hq,Hkv,bs", TC_CASES)
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("interleaved", [False, True])
+def test_prefill_tc_matches_oracle(lens, Hq, Hkv, bs, dtype, interleaved):
+    """Every sequence forced through the tcgen05 kernel (force_selection=4)."""
+    inp = make_paged_inputs(lens, Hq, Hkv, 128, bs, dtype=dtype, seed=Hq + bs, interleaved=interleaved)
+    scale = 128 ** -0.5
+    out, kern = _run(inp, scale, PREFILL_TC)
+    assert kern == "attn_prefill_tc", kern
+    assert_close(out, _oracle(inp, scale), atol=BF16_ATOL, rtol=BF16_RTOL, what="prefill_tc")
+    assert not torch.isnan(out).any()
+
+
+@pytest.mark.parametrize("window", [64, 128, 300])
+def test_prefill_tc_sliding_window(window):
+    lens = [(1, 1328), (129, 463), (300, 300), (700, 1500)]
+    inp = make_paged_inputs(lens, 8, 2, 128, 16, dtype=torch.bfloat16, seed=23)
+    scale = 128 ** -0.5
+    out, kern = _run(inp, scale, PREFILL_TC, window=window)
+    assert kern == "attn_prefill_tc"
+    assert_close(out, _oracle(inp, scale, window), atol=BF16_ATOL, rtol=BF16_RTOL, what=f"window {window}")
+
+
+def test_prefill_tc_large_logits_exercise_the_lazy_rescale():
+    """Row maxima that keep growing along the KV axis force O to be rescaled."""
+    lens = [(256, 1024)]
+    inp = make_paged_inputs(lens, 4, 1, 128, 16, dtype=torch.bfloat16, seed=31)
+    # keys grow with position so later tiles dominate: max logit climbs by >> 2^8 per tile
+    bt = inp["block_table"][0]
+    for pos in range(1024):
+        inp["k_cache"][int(bt[pos // 16]), pos % 16] *= (1.0 + pos / 64.0)
+    q = inp["q"]
+    inp["q"] = (q.float().abs() * 2).to(q.dtype)
+    kc = inp["k_cache"]
+    inp["k_cache"] = kc.float().abs().to(kc.dtype)
+    scale = 1.0
+    out, kern = _run(inp, scale, PREFILL_TC)
+    assert kern == "attn_prefill_tc"
+    assert_close(out, _oracle(inp, scale), atol=BF16_ATOL, rtol=BF16_RTOL, what="lazy rescale")
+
+
+def test_prefill_tc_ignores_garbage_beyond_seq_len():
+    lens = [(100, 117), (40, 40), (200, 700), (64, 905)]
+    inp = make_paged_inputs(lens, 8, 2, 128, 16, dtype=torch.bfloat16, seed=9)
+    ref = _oracle(inp, 0.1)
+    bt = inp["block_table"]
+    for b, (_, n) in enumerate(lens):
+        if n % 16:
+            page = int(bt[b, (n - 1) // 16])
+            inp["k_cache"][page, n % 16:] = float("nan")
+            inp["v_cache"][page, n % 16:] = float("inf")
+    out, _ = _run(inp, 0.1, PREFILL_TC)
+    assert_close(out, ref, atol=BF16_ATOL, rtol=BF16_RTOL, what="garbage tail")
+
+
+def test_mixed_batch_is_routed_across_three_kernels():
+    """AUTO on a mixed batch: tcgen05 for long queries, mma.sync for short extends,
+    split-KV decode for single-token rows; together they must cover every row."""
+    from vllm_triton_backend_b200 import _cabi
+
+    lens = [(1, 1328), (300, 300), (5, 18), (1, 77), (129, 463), (12, 900), (1, 1)]
+    inp = make_paged_inputs(lens, 32, 8, 128, 16, dtype=torch.bfloat16, seed=41)
+    scale = 128 ** -0.5
+    _cabi.reset_launch_count()
+    out, kern = _run(inp, scale, DECODE_OR_AUTO)
+    assert _cabi.launch_count() == 3 and kern == "attn_decode_split_kv"
+    assert not torch.isnan(out).any()
+    assert_close(out, _oracle(inp, scale), atol=BF16_ATOL, rtol=BF16_RTOL, what="mixed routing")
+
+
+def test_workspace_counters_are_left_clean():
+    """The split-KV ticket counters must be zero again after a call (self-cleaning)."""
+    from vllm_triton_backend_b200 import ops
+
+    lens = [4096, 100, 1777, 16, 3000]
+    inp = make_paged_inputs([(1, n) for n in lens], 32, 8, 128, 16, dtype=torch.bfloat16, seed=3, device="cuda")
+    ws = torch.zeros(ops.workspace_bytes(5, 5, 32, 8, 128), dtype=torch.uint8, device="cuda")
+    out = torch.empty_like(inp["q"])
+    for _ in range(3):
+        ops.unified_attention(q=inp["q"], k=inp["k_cache"], v=inp["v_cache"], out=out, cu_seqlens_q=inp["cu_seqlens_q"],
+                              max_seqlen_q=1, seqused_k=inp["seq_lens"], max_seqlen_k=4096, softmax_scale=0.088,
+                              causal=True, window_size=(-1, -1), block_table=inp["block_table"], softcap=0,
+                              q_descale=None, k_descale=None, v_descale=None, workspace=ws)
+    torch.cuda.synchronize()
+    assert int(ws[: 5 * 8 * 4].view(torch.int32).abs().sum()) == 0
 
 
 # ---------------------------------------------------------------------------------

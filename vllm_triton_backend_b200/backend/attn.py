@@ -72,7 +72,8 @@ class B200AttentionMetadataBuilder(AttentionMetadataBuilder[B200AttentionMetadat
         self.headdim = model_config.get_head_size()
         max_num_seqs = vllm_config.scheduler_config.max_num_seqs
         nbytes = ops.workspace_bytes(max_num_seqs, max_num_seqs, self.num_heads_q, self.num_heads_kv, self.headdim)
-        self.workspace = torch.empty(nbytes, dtype=torch.uint8, device=device)
+        # zeroed once: holds the decode kernel's self-cleaning ticket counters
+        self.workspace = torch.zeros(nbytes, dtype=torch.uint8, device=device)
 
     def build_for_cudagraph_capture(self, common_attn_metadata: CommonAttentionMetadata) -> B200AttentionMetadata:
         attn_metadata = self.build(0, common_attn_metadata)

@@ -22,8 +22,12 @@
 //  * Split-KV without host sync: the flattened (sequence, head-group, KV-step)
 //    space is cut into equal contiguous ranges, one per CTA (grid = #SMs), from
 //    the device-side seq_lens; a CTA that covers a whole item writes the output
-//    directly, otherwise it writes an un-normalised partial that
-//    `decode_reduce_kernel` merges (slot = item + cta is collision free).
+//    directly, otherwise it writes an un-normalised partial (slot = item + cta is
+//    collision free) and takes a ticket on the item's counter; the CTA that
+//    takes the last ticket merges the item's partials and writes the output
+//    (the reference's separate `reduce_segments` launch, :757-836, folded in).
+//    Counters are self-cleaning: the merging CTA resets its item's counter, so
+//    the workspace only has to be zeroed once, when it is allocated.
 #include "common.cuh"
 
 namespace b200attn {
@@ -41,10 +45,10 @@ struct DecodeParams {
   int stages;
   int tma_split;   // 0: one TMA op per (page box); 1: one per (page box, head, d-chunk)
   int group;       // query heads per kv head
+  int only_q1;     // mixed batch: only sequences with exactly one query token are this kernel's
   float* ws_acc;   // [slots][hpc*group][D]
   float* ws_ml;    // [slots][hpc*group][2]  (max in log2 units, exp-sum)
-  int* ws_lo;      // [items] first cta of an item that needs reducing
-  int* ws_hi;      // [items] last cta, or -1 when the output was written directly
+  int* ws_cnt;     // [items] tickets taken on an item split across CTAs (0 between calls)
 };
 
 __device__ __forceinline__ float ex2(float x) {
@@ -63,7 +67,7 @@ struct ItemCursor {
 __device__ __forceinline__ void seq_steps(const DecodeParams& P, int b, int& seq_len, int& first, int& n) {
   seq_len = P.a.seq_lens[b];
   int q_len = P.a.cu_seqlens_q ? (P.a.cu_seqlens_q[b + 1] - P.a.cu_seqlens_q[b]) : 1;
-  if (seq_len <= 0 || q_len <= 0) {
+  if (seq_len <= 0 || q_len <= 0 || (P.only_q1 && q_len != 1)) {
     first = 0, n = 0;
     return;
   }
@@ -112,7 +116,7 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
   float* ml_buf = mbuf + NW * 8 * D;                                                      // [NW][8][2]
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(ml_buf + NW * 8 * 2);
   uint64_t* empty_bar = full_bar + kMaxStages;
-  int* s_part = reinterpret_cast<int*>(empty_bar + kMaxStages);  // [0]=begin [1]=end [2]=b [3]=hg [4]=step
+  int* s_part = reinterpret_cast<int*>(empty_bar + kMaxStages);  // [0]=begin [1]=end [2]=b [3]=hg [4]=step [5]=per [6]=ticket flag
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int gid = lane >> 2, t4 = lane & 3;
@@ -170,6 +174,7 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
       s_part[0] = (int)begin;
       s_part[1] = (fb < 0) ? (int)begin : (int)end;
       s_part[2] = fb, s_part[3] = fhg, s_part[4] = fstep;
+      s_part[5] = (int)(per > 0 ? per : 1);
     }
   } else if (warp == 1 && lane == 0) {
     for (int s = 0; s < P.stages; ++s) {
@@ -179,7 +184,20 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
     fence_barrier_init();
   }
   __syncthreads();
+  // sequences with no visible key get zeros (reference reduce_segments :828); nobody visits them below
+  for (int b = blockIdx.x; b < P.a.num_seqs; b += gridDim.x) {
+    const int sl = P.a.seq_lens[b];
+    const int ql = P.a.cu_seqlens_q ? (P.a.cu_seqlens_q[b + 1] - P.a.cu_seqlens_q[b]) : 1;
+    if (sl <= 0 && ql == 1) {
+      const int tq = P.a.cu_seqlens_q ? P.a.cu_seqlens_q[b] : b;
+      for (int e = threadIdx.x; e < P.a.num_q_heads * D; e += blockDim.x) {
+        char* orow = static_cast<char*>(P.a.out) + ((int64_t)tq * P.a.out_stride0 + (int64_t)(e / D) * P.a.out_stride1) * 2;
+        reinterpret_cast<uint16_t*>(orow)[e % D] = 0;
+      }
+    }
+  }
   const int my_begin = s_part[0], my_end = s_part[1];
+  const int per_cta = s_part[5];
   if (my_begin >= my_end) return;
 
   ItemCursor cur;
@@ -190,42 +208,86 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
 
   if (warp == NW) {
     // ======================= producer warp ====================================
+    // The whole warp issues: lane i looks up the page of box i and launches its
+    // K and V copies, so page-table latency and TMA issue overlap across boxes.
     if (lane == 0) {
       tma_prefetch_desc(&k_map);
       tma_prefetch_desc(&v_map);
-      const uint64_t pol = policy_evict_first();
-      int stage = 0;
-      uint32_t phase = 0;
-      while (true) {
-        mbar_wait(&empty_bar[stage], phase ^ 1);
-        const int tok0 = cur.step * P.tps;
-        const int ntok = min(P.tps, cur.seq_len - tok0);
-        const int nbox = (ntok + P.box_slots - 1) / P.box_slots;
-        const int head0 = cur.hg * P.hpc;
-        const int32_t* bt = P.a.block_tables + (int64_t)cur.b * P.a.bt_stride0;
-        uint8_t* kdst = stage_base + (size_t)stage * 2 * KV_STAGE_BYTES;
-        uint8_t* vdst = kdst + KV_STAGE_BYTES;
-        mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)(2 * nbox * boxb));
-        for (int i = 0; i < nbox; ++i) {
-          const int tok = tok0 + i * P.box_slots;
-          const int page = bt[tok / P.a.block_size];
+    }
+    const uint64_t pol = policy_evict_first();
+    int stage = 0;
+    uint32_t phase = 0;
+    // Page ids are read through a 128-page window held in registers (lane l keeps
+    // pages base + 32 r + l) with the next window already in flight, so the copy
+    // loop never waits on a block-table load (one DRAM round trip per item, not per step).
+    int win_b = -1, win_base = -1;
+    int ids[4] = {0, 0, 0, 0}, nxt[4] = {0, 0, 0, 0};
+    auto load_ids = [&](int (&dst)[4], const int32_t* bt, int base, int npages) {
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const int pg = base + r * 32 + lane;
+        dst[r] = pg < npages ? bt[pg] : 0;
+      }
+    };
+    while (true) {
+      const int tok0 = cur.step * P.tps;
+      const int ntok = min(P.tps, cur.seq_len - tok0);
+      const int nbox = (ntok + P.box_slots - 1) / P.box_slots;
+      const int head0 = cur.hg * P.hpc;
+      const int32_t* bt = P.a.block_tables + (int64_t)cur.b * P.a.bt_stride0;
+      const int npages = (cur.seq_len + P.a.block_size - 1) / P.a.block_size;
+      const int p_first = tok0 / P.a.block_size;
+      const int base = p_first & ~127;
+      if (cur.b != win_b || base != win_base) {
+        if (cur.b == win_b && base == win_base + 128) {
+#pragma unroll
+          for (int r = 0; r < 4; ++r) ids[r] = nxt[r];
+        } else {
+          load_ids(ids, bt, base, npages);
+        }
+        load_ids(nxt, bt, base + 128, npages);
+        win_b = cur.b, win_base = base;
+      }
+      auto page_of = [&](int pg) {  // warp-collective: every lane asks for one page id
+        const int src = pg & 31, r = (pg >> 5) & 3;
+        const int v0 = __shfl_sync(0xffffffffu, ids[0], src), v1 = __shfl_sync(0xffffffffu, ids[1], src);
+        const int v2 = __shfl_sync(0xffffffffu, ids[2], src), v3 = __shfl_sync(0xffffffffu, ids[3], src);
+        return r == 0 ? v0 : (r == 1 ? v1 : (r == 2 ? v2 : v3));
+      };
+      mbar_wait(&empty_bar[stage], phase ^ 1);
+      uint8_t* kdst = stage_base + (size_t)stage * 2 * KV_STAGE_BYTES;
+      uint8_t* vdst = kdst + KV_STAGE_BYTES;
+      if (lane == 0) mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)(2 * nbox * boxb));
+      __syncwarp();
+      if (P.tma_split == 0) {
+        // nbox <= 8: one lane per box
+        const int i = lane;
+        const int tok = tok0 + i * P.box_slots;
+        const int page = page_of(tok / P.a.block_size);  // lanes past nbox read a don't-care id
+        if (i < nbox) {
           const int slot0 = tok % P.a.block_size;
-          if (P.tma_split == 0) {
-            tma_load_5d(kdst + (size_t)i * boxb, &k_map, &full_bar[stage], 0, slot0, 0, head0, page, pol);
-            tma_load_5d(vdst + (size_t)i * boxb, &v_map, &full_bar[stage], 0, slot0, 0, head0, page, pol);
-          } else {
-            for (int h = 0; h < P.hpc; ++h)
-              for (int dc = 0; dc < NDC; ++dc) {
-                const size_t off = (size_t)i * boxb + (size_t)(h * NDC + dc) * P.box_slots * 128;
-                tma_load_5d(kdst + off, &k_map, &full_bar[stage], 0, slot0, dc, head0 + h, page, pol);
-                tma_load_5d(vdst + off, &v_map, &full_bar[stage], 0, slot0, dc, head0 + h, page, pol);
-              }
+          tma_load_5d(kdst + (size_t)i * boxb, &k_map, &full_bar[stage], 0, slot0, 0, head0, page, pol);
+          tma_load_5d(vdst + (size_t)i * boxb, &v_map, &full_bar[stage], 0, slot0, 0, head0, page, pol);
+        }
+      } else {
+        const int per_box = P.hpc * NDC;
+        const int units = nbox * per_box;
+        for (int u0 = 0; u0 < units; u0 += 32) {
+          const int u = u0 + lane;
+          const int i = min(u / per_box, nbox - 1), r = u % per_box, h = r / NDC, dc = r % NDC;
+          const int tok = tok0 + i * P.box_slots;
+          const int page = page_of(tok / P.a.block_size);
+          if (u < units) {
+            const int slot0 = tok % P.a.block_size;
+            const size_t off = (size_t)i * boxb + (size_t)(h * NDC + dc) * P.box_slots * 128;
+            tma_load_5d(kdst + off, &k_map, &full_bar[stage], 0, slot0, dc, head0 + h, page, pol);
+            tma_load_5d(vdst + off, &v_map, &full_bar[stage], 0, slot0, dc, head0 + h, page, pol);
           }
         }
-        if (++stage == P.stages) stage = 0, phase ^= 1;
-        if (cur.flat + 1 >= my_end) break;
-        cursor_next(P, cur);
       }
+      if (++stage == P.stages) stage = 0, phase ^= 1;
+      if (cur.flat + 1 >= my_end) break;
+      cursor_next(P, cur);
     }
     return;
   }
@@ -496,7 +558,6 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
       const int item = cur.b * P.head_groups + cur.hg;
       const int item_flat0 = cur.flat - (cur.step - cur.first);
       const bool direct = item_flat0 >= my_begin && item_flat0 + cur.n <= my_end;
-      const bool has_first = item_flat0 >= my_begin;
       const int tq = P.a.cu_seqlens_q ? P.a.cu_seqlens_q[cur.b] : cur.b;
       const int wph = NW / P.hpc;  // warps per kv head
 #pragma unroll
@@ -556,11 +617,41 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
           }
         }
       }
-      if (threadIdx.x == 0) {
-        if (direct) P.ws_hi[item] = -1;
-        else {
-          if (has_first) P.ws_lo[item] = blockIdx.x;
-          if (item_end) P.ws_hi[item] = blockIdx.x;
+      if (!direct) {
+        // ---- ticket: the CTA that completes the item merges its partials ------
+        const int first_cta = item_flat0 / per_cta;
+        const int last_cta = (item_flat0 + cur.n - 1) / per_cta;
+        __threadfence();  // partials visible device-wide before the ticket
+        asm volatile("bar.sync 1, %0;" ::"r"(NW * 32));
+        if (threadIdx.x == 0) {
+          const int ticket = atomicAdd(&P.ws_cnt[item], 1);
+          s_part[6] = (ticket == last_cta - first_cta) ? 1 : 0;
+        }
+        asm volatile("bar.sync 1, %0;" ::"r"(NW * 32));
+        if (s_part[6]) {
+          __threadfence();
+          const int rec_heads = P.hpc * P.group;
+          for (int e = threadIdx.x; e < rec_heads * D; e += NW * 32) {
+            const int hq_in = e / D, d = e % D;
+            float M = -INFINITY;
+            for (int c = first_cta; c <= last_cta; ++c)
+              M = fmaxf(M, __ldcg(&P.ws_ml[(((int64_t)item + c) * rec_heads + hq_in) * 2]));
+            float val = 0.f, L = 0.f;
+#pragma unroll 4
+            for (int c = first_cta; c <= last_cta; ++c) {
+              const int64_t rec = ((int64_t)item + c) * rec_heads + hq_in;
+              const float mw = __ldcg(&P.ws_ml[rec * 2]);
+              const float sc = (mw == -INFINITY) ? 0.f : ex2(mw - M);
+              val += __ldcg(&P.ws_acc[rec * D + d]) * sc;
+              L += __ldcg(&P.ws_ml[rec * 2 + 1]) * sc;
+            }
+            const float o = (L > 0.f) ? val * v_scale / L : 0.f;  // 0 when nothing is visible (reference :828)
+            const int hq = cur.hg * rec_heads + hq_in;
+            char* orow = static_cast<char*>(P.a.out) + ((int64_t)tq * P.a.out_stride0 + (int64_t)hq * P.a.out_stride1) * 2;
+            if constexpr (Q_BF16) reinterpret_cast<__nv_bfloat16*>(orow)[d] = __float2bfloat16_rn(o);
+            else reinterpret_cast<__half*>(orow)[d] = __float2half_rn(o);
+          }
+          if (threadIdx.x == 0) P.ws_cnt[item] = 0;  // self-cleaning: ready for the next call
         }
       }
       if (last) break;
@@ -574,101 +665,7 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
   }
 }
 
-// K2b: merge the partials of every item that was split across CTAs.
-template <bool Q_BF16>
-__global__ void __launch_bounds__(128) decode_reduce_kernel(const DecodeParams P) {
-  const int item = blockIdx.x;
-  const int b = item / P.head_groups, hg = item % P.head_groups;
-  int seq_len, first, n;
-  seq_steps(P, b, seq_len, first, n);
-  const int D = P.a.head_size;
-  const int q_len = P.a.cu_seqlens_q ? (P.a.cu_seqlens_q[b + 1] - P.a.cu_seqlens_q[b]) : 1;
-  if (q_len <= 0) return;
-  const int tq = P.a.cu_seqlens_q ? P.a.cu_seqlens_q[b] : b;
-  const int rec_heads = P.hpc * P.group;
-  const float v_scale = (P.a.kv_dtype == B200ATTN_FP8_E4M3 && P.a.v_scale) ? *P.a.v_scale : 1.0f;
-  int lo = 0, hi = -1;
-  const bool empty = (n == 0);
-  if (!empty) {
-    hi = P.ws_hi[item];
-    if (hi < 0) return;  // written directly by the decode kernel
-    lo = P.ws_lo[item];
-  }
-  for (int e = threadIdx.x; e < rec_heads * D; e += blockDim.x) {
-    const int hq_in = e / D, d = e % D;
-    float o = 0.f;
-    if (!empty) {
-      float M = -INFINITY;
-      for (int c = lo; c <= hi; ++c) M = fmaxf(M, P.ws_ml[(((int64_t)item + c) * rec_heads + hq_in) * 2]);
-      float val = 0.f, L = 0.f;
-      for (int c = lo; c <= hi; ++c) {
-        const int64_t rec = ((int64_t)item + c) * rec_heads + hq_in;
-        const float mw = P.ws_ml[rec * 2];
-        const float sc = (mw == -INFINITY) ? 0.f : ex2(mw - M);
-        val += P.ws_acc[rec * D + d] * sc;
-        L += P.ws_ml[rec * 2 + 1] * sc;
-      }
-      o = (L > 0.f) ? val * v_scale / L : 0.f;  // 0 when nothing is visible (reference :828)
-    }
-    const int hq = hg * rec_heads + hq_in;
-    char* orow = static_cast<char*>(P.a.out) + ((int64_t)tq * P.a.out_stride0 + (int64_t)hq * P.a.out_stride1) * 2;
-    if constexpr (Q_BF16) reinterpret_cast<__nv_bfloat16*>(orow)[d] = __float2bfloat16_rn(o);
-    else reinterpret_cast<__half*>(orow)[d] = __float2half_rn(o);
-  }
-}
-
 // ---- host side ------------------------------------------------------------------
-struct MapKey {
-  const void* base;
-  int64_t s_block, s_slot, s_head, nb;
-  int bs, hkv, d, esz, box_slots, box_heads, box_dc;
-  bool operator==(const MapKey& o) const {
-    return base == o.base && s_block == o.s_block && s_slot == o.s_slot && s_head == o.s_head && nb == o.nb &&
-           bs == o.bs && hkv == o.hkv && d == o.d && esz == o.esz && box_slots == o.box_slots &&
-           box_heads == o.box_heads && box_dc == o.box_dc;
-  }
-};
-struct MapEntry {
-  MapKey key;
-  CUtensorMap map;
-  bool used = false;
-};
-thread_local MapEntry g_map_cache[16];
-thread_local int g_map_next = 0;
-
-// 5-D view of a paged cache: (128-byte chunk elems, slot, chunk, head, block)
-int make_kv_map(CUtensorMap* out, const void* base, int esz, int D, int bs, int hkv, int64_t nb, int64_t s_block,
-                int64_t s_slot, int64_t s_head, int box_slots, int box_heads, int box_dc) {
-  MapKey key{base, s_block, s_slot, s_head, nb, bs, hkv, D, esz, box_slots, box_heads, box_dc};
-  for (auto& e : g_map_cache)
-    if (e.used && e.key == key) {
-      *out = e.map;
-      return B200ATTN_OK;
-    }
-  EncodeTiledFn fn = encode_tiled_fn();
-  if (!fn) {
-    set_error("decode: cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
-    return B200ATTN_E_CUDA;
-  }
-  const int epc = 128 / esz;
-  cuuint64_t dims[5] = {(cuuint64_t)epc, (cuuint64_t)bs, (cuuint64_t)(D * esz / 128), (cuuint64_t)hkv, (cuuint64_t)nb};
-  cuuint64_t strides[4] = {(cuuint64_t)(s_slot * esz), 128, (cuuint64_t)(s_head * esz), (cuuint64_t)(s_block * esz)};
-  cuuint32_t box[5] = {(cuuint32_t)epc, (cuuint32_t)box_slots, (cuuint32_t)box_dc, (cuuint32_t)box_heads, 1};
-  cuuint32_t estr[5] = {1, 1, 1, 1, 1};
-  CUtensorMapDataType dt = esz == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_UINT16;
-  CUresult r = fn(out, dt, 5, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) {
-    set_error("decode: cuTensorMapEncodeTiled failed (%d) strides=(%lld,128,%lld,%lld)B box=(%d,%d,%d,%d,1)", (int)r,
-              (long long)strides[0], (long long)strides[2], (long long)strides[3], epc, box_slots, box_dc, box_heads);
-    return B200ATTN_E_CUDA;
-  }
-  MapEntry& e = g_map_cache[g_map_next];
-  g_map_next = (g_map_next + 1) % 16;
-  e.key = key, e.map = *out, e.used = true;
-  return B200ATTN_OK;
-}
-
 struct DecodeConfig {
   int nw, nt, hpc, stages, smem_bytes, grid;
 };
@@ -690,7 +687,23 @@ int launch_variant(const b200attn_attention_params& a, DecodeParams& P, cudaStre
   constexpr int KV_STAGE_BYTES = NW * 16 * D * ESZ;
   const DeviceInfo& dev = device_info();
   const Tuning& tn = tuning();
-  P.hpc = pick_hpc(a.num_kv_heads, NW, tn.decode_heads_per_cta > 0 ? tn.decode_heads_per_cta : NW);
+  if (tn.decode_heads_per_cta > 0) {
+    P.hpc = pick_hpc(a.num_kv_heads, NW, tn.decode_heads_per_cta);
+  } else {
+    // Fewest kv heads per CTA whose TMA box is still big enough: more
+    // (sequence, head group) items means more outputs written directly and
+    // parallel merges, but the copy engine pays per box (measured on B200,
+    // profiles/r01_decode_sweep_v2.jsonl: bf16 KV is best at 4 KB boxes, fp8 at 8 KB).
+    const int min_box = KV_FP8 ? 8192 : 4096;
+    int hpc = 1;
+    while (hpc < NW && a.num_kv_heads % (hpc * 2) == 0) {
+      const int tps = NW * 16 / hpc;
+      const int slots = a.block_size < tps ? a.block_size : tps;
+      if (hpc * NDC * slots * 128 >= min_box) break;
+      hpc *= 2;
+    }
+    P.hpc = hpc;
+  }
   P.head_groups = a.num_kv_heads / P.hpc;
   P.tps = NW * 16 / P.hpc;
   P.box_slots = a.block_size < P.tps ? a.block_size : P.tps;
@@ -735,11 +748,7 @@ int launch_variant(const b200attn_attention_params& a, DecodeParams& P, cudaStre
   }
   kern<<<(unsigned)grid, (NW + 1) * 32, smem, stream>>>(P, kmap, vmap);
   note_launch("attn_decode_split_kv");
-  rc = check_launch("attn_decode");
-  if (rc) return rc;
-  decode_reduce_kernel<Q_BF16><<<(unsigned)(a.num_seqs * P.head_groups), 128, 0, stream>>>(P);
-  note_launch("decode_reduce");
-  return check_launch("decode_reduce");
+  return check_launch("attn_decode");
 }
 
 template <int D, int NT, int NW>
@@ -764,7 +773,7 @@ inline bool pow2(int x) { return x > 0 && (x & (x - 1)) == 0; }
 
 uint64_t decode_workspace_bytes(int num_seqs, int num_q_heads, int num_kv_heads, int head_size) {
   // slots <= items + ctas; records of (hpc*group) heads: bounded by
-  // (B*Hq + ctas*8*group) head-rows of (D + 2) floats, plus lo/hi per item.
+  // (B*Hq + ctas*8*group) head-rows of (D + 2) floats, plus one ticket counter per item.
   const uint64_t group = (uint64_t)(num_q_heads / (num_kv_heads > 0 ? num_kv_heads : 1));
   const uint64_t ctas = 160;  // >= SM count of any B200 SKU
   const uint64_t rows = (uint64_t)num_seqs * num_q_heads + ctas * 8 * (group > 0 ? group : 1);
@@ -772,9 +781,9 @@ uint64_t decode_workspace_bytes(int num_seqs, int num_q_heads, int num_kv_heads,
   return rows * (uint64_t)(head_size + 2) * 4 + items * 8 + 1024;
 }
 
-bool decode_supported(const b200attn_attention_params& p, const char** why) {
+bool decode_supported(const b200attn_attention_params& p, const char** why, bool mixed_batch) {
   auto no = [&](const char* w) { if (why) *why = w; return false; };
-  if (p.max_seqlen_q != 1) return no("max_seqlen_q != 1");
+  if (p.max_seqlen_q != 1 && !mixed_batch) return no("max_seqlen_q != 1");
   if (p.q_dtype != B200ATTN_BF16 && p.q_dtype != B200ATTN_F16) return no("query dtype must be bf16/f16");
   if (p.kv_dtype != p.q_dtype && p.kv_dtype != B200ATTN_FP8_E4M3) return no("kv dtype");
   if (p.head_size != 64 && p.head_size != 128 && p.head_size != 256) return no("head_size not in {64,128,256}");
@@ -794,9 +803,9 @@ bool decode_supported(const b200attn_attention_params& p, const char** why) {
   return true;
 }
 
-int launch_attn_decode(const b200attn_attention_params& a, cudaStream_t stream) {
+int launch_attn_decode(const b200attn_attention_params& a, cudaStream_t stream, bool only_single_token_seqs) {
   const char* why = nullptr;
-  if (!decode_supported(a, &why)) {
+  if (!decode_supported(a, &why, only_single_token_seqs)) {
     set_error("decode: unsupported configuration (%s)", why);
     return B200ATTN_E_UNSUPPORTED;
   }
@@ -809,11 +818,11 @@ int launch_attn_decode(const b200attn_attention_params& a, cudaStream_t stream) 
   DecodeParams P;
   P.a = a;
   P.group = a.num_q_heads / a.num_kv_heads;
-  // carve the workspace: lo/hi first (items <= B*Hkv), then ml, then acc
+  P.only_q1 = only_single_token_seqs ? 1 : 0;
+  // carve the workspace: ticket counters first (items <= B*Hkv; zero between calls), then ml, then acc
   const uint64_t items_max = (uint64_t)a.num_seqs * a.num_kv_heads;
   char* w = static_cast<char*>(a.workspace);
-  P.ws_lo = reinterpret_cast<int*>(w);
-  P.ws_hi = P.ws_lo + items_max;
+  P.ws_cnt = reinterpret_cast<int*>(w);
   uint64_t off = ((items_max * 8 + 255) / 256) * 256;
   const uint64_t group = (uint64_t)P.group;
   const uint64_t rows = (uint64_t)a.num_seqs * a.num_q_heads + 160ull * 8 * group;

@@ -172,9 +172,34 @@ int b200attn_unified_attention(const b200attn_attention_params* pp, b200attn_str
     if (prefill_supported(p, &why)) return launch_attn_prefill(p, stream);
     return launch_attn_generic(p, stream);
   }
-  if (prefill_tc_supported(p, &why)) return launch_attn_prefill_tc(p, stream);
-  if (prefill_supported(p, &why)) return launch_attn_prefill(p, stream);
-  return launch_attn_generic(p, stream);
+  // A batch with multi-token queries.  Long queries go to the tcgen05 kernel;
+  // what it leaves (short extends, decode rows of a mixed batch) goes to the
+  // mma.sync kernel and, for single-token rows, to the split-KV decode kernel.
+  // Which sequences are which is device data, so every launch carries a
+  // query-length range and skips the others' sequences.
+  if (!prefill_supported(p, &why)) return launch_attn_generic(p, stream);
+  const bool ws_ok = p.workspace && p.workspace_bytes >= decode_workspace_bytes(p.num_seqs, p.num_q_heads, p.num_kv_heads, p.head_size);
+  const bool dec_ok = ws_ok && decode_supported(p, &why, /*mixed_batch=*/true);
+  // every sequence has exactly max_seqlen_q tokens <=> T == B * max_seqlen_q
+  const bool uniform = (int64_t)p.num_tokens == (int64_t)p.num_seqs * p.max_seqlen_q;
+  int short_max = 0x7fffffff;  // longest query the mma.sync launch takes
+  if (prefill_tc_supported(p, &why) && p.max_seqlen_q >= prefill_tc_min_q_len(p)) {
+    QLenRange r;
+    r.min_q_len = prefill_tc_min_q_len(p);
+    rc = launch_attn_prefill_tc(p, stream, r);
+    if (rc || uniform) return rc;
+    short_max = r.min_q_len - 1;
+  }
+  if (uniform) return launch_attn_prefill(p, stream);
+  QLenRange r;
+  r.min_q_len = dec_ok ? 2 : 0;
+  r.max_q_len = short_max;
+  if (short_max >= r.min_q_len) {
+    rc = launch_attn_prefill(p, stream, r);
+    if (rc) return rc;
+  }
+  if (dec_ok) return launch_attn_decode(p, stream, /*only_single_token_seqs=*/true);
+  return B200ATTN_OK;
 }
 
 }  // extern "C"

@@ -38,6 +38,21 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 EncodeTiledFn encode_tiled_fn();
+// TMA descriptors (tma_maps.cu); small per-thread cache keyed by pointer + strides
+int make_kv_map(CUtensorMap* out, const void* base, int esz, int D, int bs, int hkv, int64_t nb, int64_t s_block,
+                int64_t s_slot, int64_t s_head, int box_slots, int box_heads, int box_dc);
+int make_thd_map(CUtensorMap* out, const void* base, int D, int heads, int64_t tokens, int64_t s_token, int64_t s_head,
+                 int box_heads, int box_tokens);
+
+// Which sequences of a batch a launch is responsible for: those with
+// min_q_len <= query_len <= max_q_len.  A mixed batch is covered by up to three
+// launches (decode rows -> split-KV kernel, short extends -> mma.sync kernel,
+// long prefills -> tcgen05 kernel); every grid is a host-int upper bound and
+// CTAs whose sequence belongs to another launch exit at once.
+struct QLenRange {
+  int min_q_len = 0;
+  int max_q_len = 0x7fffffff;
+};
 
 // kernel launchers (one per .cu file)
 int launch_cache_write(const void* key, const void* value, void* k_cache, void* v_cache, const int64_t* slot_mapping,
@@ -48,13 +63,14 @@ int launch_cache_write(const void* key, const void* value, void* k_cache, void* 
 int launch_scaled_fp8_quant(void* out, const void* in, int64_t rows, int64_t row_elems, int64_t in_row_stride,
                             int src_dtype, const float* scale, cudaStream_t stream);
 int launch_attn_generic(const b200attn_attention_params& p, cudaStream_t stream);
-int launch_attn_decode(const b200attn_attention_params& p, cudaStream_t stream);
-bool decode_supported(const b200attn_attention_params& p, const char** why);
+int launch_attn_decode(const b200attn_attention_params& p, cudaStream_t stream, bool only_single_token_seqs = false);
+bool decode_supported(const b200attn_attention_params& p, const char** why, bool mixed_batch = false);
 uint64_t decode_workspace_bytes(int num_seqs, int num_q_heads, int num_kv_heads, int head_size);
-int launch_attn_prefill(const b200attn_attention_params& p, cudaStream_t stream);
+int launch_attn_prefill(const b200attn_attention_params& p, cudaStream_t stream, QLenRange range = QLenRange());
 bool prefill_supported(const b200attn_attention_params& p, const char** why);
-int launch_attn_prefill_tc(const b200attn_attention_params& p, cudaStream_t stream);
+int launch_attn_prefill_tc(const b200attn_attention_params& p, cudaStream_t stream, QLenRange range = QLenRange());
 bool prefill_tc_supported(const b200attn_attention_params& p, const char** why);
+int prefill_tc_min_q_len(const b200attn_attention_params& p);  // shortest query the tcgen05 tile is worth using for
 
 static inline int dtype_bytes(int dt) {
   switch (dt) {

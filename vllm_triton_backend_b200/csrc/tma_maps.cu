@@ -1,0 +1,103 @@
+// Host-side TMA descriptor builders shared by the decode and prefill kernels.
+//
+// The paged cache is handed to us as a strided [NB, bs, Hkv, D] view whose block
+// stride is arbitrary (K/V planes or K/V interleaved per block),
+// so the descriptors are built over the strides, not over a dense shape.  A
+// 128-byte row chunk is the innermost TMA dimension so the hardware 128-byte
+// swizzle lands every (token, 128-byte chunk) where ldmatrix / UMMA expect it.
+#include "common.cuh"
+
+namespace b200attn {
+namespace {
+
+struct MapKey {
+  const void* base;
+  int64_t s0, s1, s2, n0;
+  int a, b, c, d, e, f, g;
+  int kind;
+  bool operator==(const MapKey& o) const {
+    return base == o.base && s0 == o.s0 && s1 == o.s1 && s2 == o.s2 && n0 == o.n0 && a == o.a && b == o.b &&
+           c == o.c && d == o.d && e == o.e && f == o.f && g == o.g && kind == o.kind;
+  }
+};
+struct MapEntry {
+  MapKey key;
+  CUtensorMap map;
+  bool used = false;
+};
+constexpr int kCacheSize = 32;
+thread_local MapEntry g_map_cache[kCacheSize];
+thread_local int g_map_next = 0;
+
+bool lookup(const MapKey& key, CUtensorMap* out) {
+  for (auto& e : g_map_cache)
+    if (e.used && e.key == key) {
+      *out = e.map;
+      return true;
+    }
+  return false;
+}
+void remember(const MapKey& key, const CUtensorMap& map) {
+  MapEntry& e = g_map_cache[g_map_next];
+  g_map_next = (g_map_next + 1) % kCacheSize;
+  e.key = key, e.map = map, e.used = true;
+}
+
+}  // namespace
+
+// 5-D view of a paged cache: (128-byte chunk elems, slot, chunk, head, block)
+int make_kv_map(CUtensorMap* out, const void* base, int esz, int D, int bs, int hkv, int64_t nb, int64_t s_block,
+                int64_t s_slot, int64_t s_head, int box_slots, int box_heads, int box_dc) {
+  MapKey key{base, s_block, s_slot, s_head, nb, bs, hkv, D, esz, box_slots, box_heads, box_dc, 0};
+  if (lookup(key, out)) return B200ATTN_OK;
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn) {
+    set_error("cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
+    return B200ATTN_E_CUDA;
+  }
+  const int epc = 128 / esz;
+  cuuint64_t dims[5] = {(cuuint64_t)epc, (cuuint64_t)bs, (cuuint64_t)(D * esz / 128), (cuuint64_t)hkv, (cuuint64_t)nb};
+  cuuint64_t strides[4] = {(cuuint64_t)(s_slot * esz), 128, (cuuint64_t)(s_head * esz), (cuuint64_t)(s_block * esz)};
+  cuuint32_t box[5] = {(cuuint32_t)epc, (cuuint32_t)box_slots, (cuuint32_t)box_dc, (cuuint32_t)box_heads, 1};
+  cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+  CUtensorMapDataType dt = esz == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_UINT16;
+  CUresult r = fn(out, dt, 5, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("kv map: cuTensorMapEncodeTiled failed (%d) strides=(%lld,128,%lld,%lld)B box=(%d,%d,%d,%d,1)", (int)r,
+              (long long)strides[0], (long long)strides[2], (long long)strides[3], epc, box_slots, box_dc, box_heads);
+    return B200ATTN_E_CUDA;
+  }
+  remember(key, *out);
+  return B200ATTN_OK;
+}
+
+// 4-D view of a [T, H, D] 2-byte tensor (queries): (64 elems, chunk, head, token);
+// a box is (64, 1, box_heads, box_tokens), i.e. rows ordered token-major then
+// head — the row order of the reference's Q tile (triton_unified_attention.py:343-346).
+int make_thd_map(CUtensorMap* out, const void* base, int D, int heads, int64_t tokens, int64_t s_token, int64_t s_head,
+                 int box_heads, int box_tokens) {
+  MapKey key{base, s_token, s_head, 0, tokens, D, heads, box_heads, box_tokens, 0, 0, 0, 1};
+  if (lookup(key, out)) return B200ATTN_OK;
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn) {
+    set_error("cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
+    return B200ATTN_E_CUDA;
+  }
+  cuuint64_t dims[4] = {64, (cuuint64_t)(D / 64), (cuuint64_t)heads, (cuuint64_t)tokens};
+  cuuint64_t strides[3] = {128, (cuuint64_t)(s_head * 2), (cuuint64_t)(s_token * 2)};
+  cuuint32_t box[4] = {64, 1, (cuuint32_t)box_heads, (cuuint32_t)box_tokens};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_UINT16, 4, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("thd map: cuTensorMapEncodeTiled failed (%d) strides=(128,%lld,%lld)B box=(64,1,%d,%d)", (int)r,
+              (long long)strides[1], (long long)strides[2], box_heads, box_tokens);
+    return B200ATTN_E_CUDA;
+  }
+  remember(key, *out);
+  return B200ATTN_OK;
+}
+
+}  // namespace b200attn

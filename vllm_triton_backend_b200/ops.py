@@ -65,13 +65,14 @@ def workspace_bytes(num_tokens: int, num_seqs: int, num_q_heads: int, num_kv_hea
 
 def get_workspace(device, nbytes: int) -> torch.Tensor:
     """Grow-only per-device split-KV workspace (replaces the reference's per-call
-    torch.empty of segm_output/segm_max/segm_expsum, triton_unified_attention.py:950-971)."""
+    torch.empty of segm_output/segm_max/segm_expsum, triton_unified_attention.py:950-971).
+    Zero-filled once: it starts with the kernels' self-cleaning ticket counters."""
     key = str(device)
     ws = _workspaces.get(key)
     if ws is None or ws.numel() < nbytes:
         if torch.cuda.is_current_stream_capturing():
             raise RuntimeError("b200attn workspace must be allocated before CUDA-graph capture (pass workspace=...)")
-        ws = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+        ws = torch.zeros(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
         _workspaces[key] = ws
     return ws
 
@@ -232,7 +233,8 @@ def unified_attention(
     else:
         path = _cabi.PATH_AUTO
 
-    if workspace is None and max_seqlen_q <= 1 and path in (_cabi.PATH_AUTO, _cabi.PATH_DECODE):
+    if workspace is None and path in (_cabi.PATH_AUTO, _cabi.PATH_DECODE):
+        # decode batches, and the single-token rows of a mixed batch, use the split-KV kernel
         need = workspace_bytes(q.shape[0], seqused_k.shape[0], q.shape[1], k.shape[2], q.shape[2])
         workspace = get_workspace(q.device, need)
     p = build_attention_params(
