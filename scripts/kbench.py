@@ -35,6 +35,20 @@ def peaks():
     return 6650.0, 1590.0
 
 
+LAST_CLOCK = None
+
+
+def sample_clock():
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(0)
+        return dict(sm_mhz=pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM),
+                    power_w=round(pynvml.nvmlDeviceGetPowerUsage(h) / 1000.0, 1))
+    except Exception:
+        return None
+
+
 def time_fn(fn, min_ms=60.0, warmup=5, flush=None):
     for _ in range(warmup):
         fn()
@@ -52,6 +66,8 @@ def time_fn(fn, min_ms=60.0, warmup=5, flush=None):
         for _ in range(n):
             fn()
         e1.record()
+        global LAST_CLOCK
+        LAST_CLOCK = sample_clock()  # launches are still running: the clock under load
         torch.cuda.synchronize()
         return e0.elapsed_time(e1) / n, n
     tot = 0.0
@@ -211,12 +227,14 @@ def prefill_case(args, device):
 def run_prefill(args, device):
     _, tf = peaks()
     fn, flops, cfg = prefill_case(args, device)
+    _cabi.set_tuning(0, 0, 0, args.tune)
+    cfg["tune"] = args.tune
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=device) if args.flush else None
     ms, n = time_fn(fn, flush=flush)
     tfs = flops / ms / 1e9
     print(json.dumps(dict(kind="prefill", **cfg, force=args.force, ms=round(ms, 5), tflops=round(tfs, 1),
                           frac_measured=round(tfs / tf, 4), tokens_per_s=round(cfg["T"] / ms * 1e3, 1), iters=n,
-                          kernel=_cabi.last_kernel(), launches_per_call=None)), flush=True)
+                          kernel=_cabi.last_kernel(), clock=LAST_CLOCK)), flush=True)
 
 
 def run_cache(args, device):
@@ -260,6 +278,7 @@ def main():
     ap.add_argument("--flush", action="store_true")
     ap.add_argument("--layout", default="planes", choices=["planes", "interleaved"])
     ap.add_argument("--force", type=int, default=None)
+    ap.add_argument("--tune", type=int, default=0, help="raw b200attn_set_tuning `reserved` word (kernel variant bits)")
     args = ap.parse_args()
     device = torch.device("cuda", 0)
     torch.cuda.set_device(0)

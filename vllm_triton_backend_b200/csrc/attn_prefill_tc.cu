@@ -36,7 +36,8 @@ namespace {
 
 constexpr int kD = 128;
 constexpr int kBN = 128;                        // kv tokens per tile
-constexpr int kStages = 2;
+constexpr int kKStages = 3;                     // K is needed right after PV of the previous tile: prefetch deeper
+constexpr int kVStages = 2;
 constexpr int kSubtileBytes = 128 * 128;        // [128 rows][128 B]: one 64-element chunk of 128 rows
 constexpr int kTileBytes = 2 * kSubtileBytes;   // 128 rows x 128 dims x 2 B
 constexpr int kThreads = 384;
@@ -45,10 +46,32 @@ __host__ __device__ constexpr uint32_t col_s(int w) { return 128u * (uint32_t)w;
 __host__ __device__ constexpr uint32_t col_o(int w) { return 256u + 128u * (uint32_t)w; }
 constexpr int kSmemQ = 0;
 constexpr int kSmemK = 2 * kTileBytes;
-constexpr int kSmemV = kSmemK + kStages * kTileBytes;
-constexpr int kSmemBar = kSmemV + kStages * kTileBytes;
+constexpr int kSmemV = kSmemK + kKStages * kTileBytes;
+constexpr int kSmemBar = kSmemV + kVStages * kTileBytes;
 constexpr int kSmemBytes = kSmemBar + 256 + 1024;  // barriers + tmem ptr + alignment slack
 constexpr float kRescaleThreshold = 8.0f;          // log2 units
+
+#ifdef B200ATTN_TC_TRACE
+// debug build only (scripts/ubench/tc_trace.cu): clock64 stamps of CTA (0, 0)'s pipeline events
+__device__ long long g_tc_trace[65 * 32];
+__device__ long long g_tc_cta[4096 * 4];  // per CTA: smid, start ns, end ns, tiles
+__device__ __forceinline__ long long tc_globaltimer() {
+  long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+#define TC_TRACE(j, ev)                                                            \
+  do {                                                                             \
+    if (blockIdx.x == 1 && blockIdx.y == 0 && (j) < 64) g_tc_trace[(j) * 32 + (ev)] = clock64(); \
+  } while (0)
+#define TC_MARK(k)                                                                \
+  do {                                                                             \
+    if (blockIdx.x == 1 && blockIdx.y == 0) g_tc_trace[64 * 32 + (k)] = clock64(); \
+  } while (0)
+#else
+#define TC_MARK(k) do { } while (0)
+#define TC_TRACE(j, ev) do { } while (0)
+#endif
 
 struct TcParams {
   b200attn_attention_params a;
@@ -58,7 +81,8 @@ struct TcParams {
   int box_slots;  // tokens per TMA box = min(block_size, 128)
 };
 
-enum Bar { Q_FULL = 0, K_FULL = 1, V_FULL = 3, K_EMPTY = 5, V_EMPTY = 7, S_FULL = 9, P_FULL = 11, O_DONE = 13, V_FIX = 15, NUM_BARS = 16 };
+// P_FULL: first half of P (keys 0..63 of the tile) stored; P_FULLB: second half
+enum Bar { Q_FULL = 0, K_FULL = 1, K_EMPTY = 4, V_FULL = 7, V_EMPTY = 9, S_FULL = 11, P_FULL = 13, P_FULLB = 15, O_DONE = 17, V_FIX = 19, NUM_BARS = 20 };
 
 // ---- tcgen05 wrappers -----------------------------------------------------------------
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -110,6 +134,17 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32
       "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
       : "memory");
 }
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&r)[8]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr)
+               : "memory");
+}
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&r)[8]) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+               ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+               : "memory");
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
@@ -147,13 +182,80 @@ __host__ __device__ constexpr uint32_t umma_idesc(bool bf16, bool b_mn_major, in
          ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ float ex2_approx(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
 
-template <bool kBf16>
+
+// ---- packed fp32 pairs (FFMA2 / FADD2 on sm_100) and 3-input max (FMNMX3) ---------------
+__device__ __forceinline__ uint64_t f2_pack(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void f2_unpack(uint64_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t f2_fma(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ uint64_t f2_add(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ uint64_t f2_sub(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ uint64_t f2_add_rm(uint64_t a, uint64_t b) {  // round toward -inf
+  uint64_t r;
+  asm("add.rm.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ float fmax3(float a, float b, float c) {
+  float r;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+  return r;
+}
+// 2^x for a pair without the MUFU: x = floor(x) + f, 2^f by a degree-3 polynomial on the
+// FMA pipe (max rel. error 9e-5, far below P's bf16/f16 rounding), floor(x) added into the
+// exponent field.  The MUFU does 16 ex2/clk/SM, which for a 128x128 tile is exactly the time
+// of the two MMAs; moving a fraction of the exponentials here takes it off the critical path.
+__device__ __forceinline__ uint64_t ex2_poly2(float x0, float x1) {
+  const float kMagic = 12582912.f;  // 2^23 + 2^22: ulp 1, so add.rm leaves floor(x) in the low mantissa bits
+  const uint64_t x = f2_pack(fmaxf(x0, -127.f), fmaxf(x1, -127.f));
+  const uint64_t xr = f2_add_rm(x, f2_pack(kMagic, kMagic));
+  const uint64_t fl = f2_sub(xr, f2_pack(kMagic, kMagic));
+  const uint64_t f = f2_sub(x, fl);
+  uint64_t r = f2_fma(f, f2_pack(0.077119089663028717f, 0.077119089663028717f), f2_pack(0.227564394474029541f, 0.227564394474029541f));
+  r = f2_fma(r, f, f2_pack(0.695146143436431885f, 0.695146143436431885f));
+  r = f2_fma(r, f, f2_pack(1.f, 1.f));
+  float r0, r1, i0, i1;
+  f2_unpack(r, r0, r1);
+  f2_unpack(xr, i0, i1);
+  const float p0 = __int_as_float(__float_as_int(r0) + (__float_as_int(i0) << 23));
+  const float p1 = __int_as_float(__float_as_int(r1) + (__float_as_int(i1) << 23));
+  return f2_pack(p0, p1);
+}
+
+// kEmuNum of every kEmuDen exponential pairs are computed by ex2_poly2, the rest on the MUFU.
+// kMode bit 0: exponentials of the first half start against the previous reference max while
+//              the tile max is still being found (redo if it jumps);
+//       bit 1: the two softmax warpgroups take turns on the MUFU (named-barrier ping-pong), so
+//              one subtile's exponentials run under the other subtile's MMAs instead of both
+//              drifting into the same phase and halving each other's rate.
+template <bool kBf16, int kEmuNum, int kEmuDen, int kMode>
 __global__ void __launch_bounds__(kThreads, 1)
 attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CUtensorMap k_map,
                        const __grid_constant__ CUtensorMap v_map) {
@@ -169,6 +271,10 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = P.group;
   const int BQ = 2 * P.block_q;  // query tokens per CTA
+#ifdef B200ATTN_TC_TRACE
+  const long long tc_t0 = tc_globaltimer();
+  if (threadIdx.x == 0) TC_MARK(0);
+#endif
 
   // ---- q-tile -> sequence; heaviest (latest) tiles are scheduled first ---------------
   const int q_tile_global = (int)gridDim.x - 1 - (int)blockIdx.x;
@@ -213,13 +319,16 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
   // ---- one-time setup ------------------------------------------------------------------
   if (warp == 8 && lane == 0) {
     mbar_init(&bars[Q_FULL], 1);
-    for (int s = 0; s < 2; ++s) {
+    for (int s = 0; s < kKStages; ++s) {
       mbar_init(&bars[K_FULL + s], 1);
-      mbar_init(&bars[V_FULL + s], 1);
       mbar_init(&bars[K_EMPTY + s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&bars[V_FULL + s], 1);
       mbar_init(&bars[V_EMPTY + s], 1);
       mbar_init(&bars[S_FULL + s], 1);
       mbar_init(&bars[P_FULL + s], 128);
+      mbar_init(&bars[P_FULLB + s], 128);
       mbar_init(&bars[O_DONE + s], 1);
     }
     mbar_init(&bars[V_FIX], 1);
@@ -230,10 +339,16 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  if (threadIdx.x == 0) TC_MARK(1);
 
   const int last_tile = n_tiles - 1;
   const int last_valid = kv_limit - (tile0 + last_tile) * kBN;  // rows of the last tile that hold visible keys
   const bool need_fix = last_valid < kBN;
+
+  // Register budget follows the roles: the softmax warpgroups hold a 128-column row of S
+  // each, the MMA / TMA warpgroup needs almost nothing (2 x 208 + 80 <= 512 per lane slot).
+  if (warp < 8) asm volatile("setmaxnreg.inc.sync.aligned.u32 208;");
+  else asm volatile("setmaxnreg.dec.sync.aligned.u32 80;");
 
   if (warp < 8) {
     // ============================ softmax warpgroups ====================================
@@ -249,14 +364,23 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
     const uint32_t o_tmem = tmem_base + lane_base + col_o(w);
     const float scale_log2 = a.softmax_scale * kLog2e;
     float m_used = -INFINITY, l_sum = 0.f;
+    // ping-pong: warpgroup 0 goes first (warpgroup 1 hands it the first turn)
+    if constexpr ((kMode & 2) != 0) {
+      if (w == 1) asm volatile("bar.arrive 2, 256;" ::: "memory");
+    }
 
     for (int j = 0; j < n_tiles; ++j) {
       mbar_wait(&bars[S_FULL + w], (uint32_t)(j & 1));
       tc_fence_after();
+      if (row == 0) TC_TRACE(j, w * 5 + 0);
+      if (row == 0 && w == 0 && j == 0) TC_MARK(2);
+      if (row == 0 && w == 0 && j == 1) TC_MARK(3);
+      if (row == 0 && w == 0 && j == last_tile) TC_MARK(4);
       uint32_t s[4][32];
 #pragma unroll
       for (int c = 0; c < 4; ++c) tmem_ld32(s_tmem + c * 32, s[c]);
       tmem_ld_wait();
+      if (row == 0) TC_TRACE(j, w * 5 + 1);
       const int n0 = (tile0 + j) * kBN;
       if (n0 + kBN > limit || n0 < lo) {
 #pragma unroll
@@ -267,55 +391,110 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
             if (pos >= limit || pos < lo) s[c][i] = 0xff800000u;  // -inf
           }
       }
-      float mx = -INFINITY;
+      // P = 2^(S*scale - m) in two halves of 64 keys; each half replaces S in place (bf16
+      // pairs: columns [32h, 32h+32) of the S region) and is announced on its own barrier,
+      // so the first four k-steps of PV run while the second half is still being computed.
+      const uint64_t sc2 = f2_pack(scale_log2, scale_log2);
+      uint32_t pk[32];
+      auto exp_half = [&](int h, float m_eff, uint64_t& sum_out) {
+        const uint64_t nm2 = f2_pack(-m_eff, -m_eff);
+        uint64_t sum2[2] = {0ull, 0ull};
+#pragma unroll
+        for (int cc = 0; cc < 2; ++cc) {
+          const int c = 2 * h + cc;
+#pragma unroll
+          for (int i = 0; i < 32; i += 2) {
+            const int k = cc * 16 + (i >> 1);
+            const uint64_t x2 = f2_fma(f2_pack(__uint_as_float(s[c][i]), __uint_as_float(s[c][i + 1])), sc2, nm2);
+            float x0, x1, p0, p1;
+            f2_unpack(x2, x0, x1);
+            uint64_t p2;
+            if ((k % kEmuDen) < kEmuNum) {
+              p2 = ex2_poly2(x0, x1);
+              f2_unpack(p2, p0, p1);
+            } else {
+              p0 = ex2_approx(x0), p1 = ex2_approx(x1);
+              p2 = f2_pack(p0, p1);
+            }
+            sum2[k & 1] = f2_add(sum2[k & 1], p2);
+            pk[k] = pack2<kBf16>(p0, p1);
+          }
+        }
+        sum_out = f2_add(sum2[0], sum2[1]);
+      };
+      // The row max is NOT a prerequisite of the exponentials: the reference point m_used only
+      // has to be within 2^kRescaleThreshold of the true running max, so the first half is
+      // computed against the m_used of the previous tiles while the max of this tile (FMNMX3, on
+      // the otherwise idle ALU pipe) is found under the MUFU's shadow.  Only if the tile max
+      // jumps past the threshold (always on a row's first visible tile) is the half redone.
+      constexpr bool kOptMax = (kMode & 1) != 0, kPingPong = (kMode & 2) != 0;
+      auto turn_wait = [&]() {  // my turn on the MUFU: the other warpgroup has released barrier 2 + w
+        if constexpr (kPingPong) asm volatile("bar.sync %0, 256;" ::"r"(2 + w) : "memory");
+      };
+      uint64_t sum_a, sum_b;
+      if constexpr (kOptMax) {
+        turn_wait();
+        exp_half(0, (m_used == -INFINITY) ? 0.f : m_used, sum_a);
+      }
+      float mxc[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
       for (int c = 0; c < 4; ++c)
 #pragma unroll
-        for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(s[c][i]));
+        for (int i = 0; i < 32; i += 2) mxc[c] = fmax3(mxc[c], __uint_as_float(s[c][i]), __uint_as_float(s[c][i + 1]));
+      const float mx = fmax3(fmaxf(mxc[0], mxc[1]), mxc[2], mxc[3]);
       const float m_tile = mx * scale_log2;  // softmax_scale > 0 (checked on the host)
       float alpha = 1.f;
-      if (m_tile > m_used + kRescaleThreshold) {  // also the first finite max (m_used = -inf)
-        alpha = ex2_approx(m_used - m_tile);       // 0 when m_used = -inf
-        m_used = m_tile;
+      if (row == 0) TC_TRACE(j, w * 5 + 2);
+      const bool grew = __any_sync(0xffffffffu, m_tile > m_used + kRescaleThreshold);
+      if (grew) {
+        if (m_tile > m_used + kRescaleThreshold) {  // also the first finite max (m_used = -inf)
+          alpha = ex2_approx(m_used - m_tile);       // 0 when m_used = -inf
+          m_used = m_tile;
+        }
+        if (j > 0) {
+          // rescale the running output before PV(j) accumulates into it
+          mbar_wait(&bars[O_DONE + w], (uint32_t)((j - 1) & 1));
+          tc_fence_after();
+          // (8 columns at a time: all 128 S values are live here)
+#pragma unroll 1
+          for (int c = 0; c < 16; ++c) {
+            uint32_t t[8];
+            tmem_ld8(o_tmem + c * 8, t);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 8; ++i) t[i] = __float_as_uint(__uint_as_float(t[i]) * alpha);
+            tmem_st8(o_tmem + c * 8, t);
+          }
+        }
       }
+      if constexpr (!kOptMax) turn_wait();
+      if (!kOptMax || grew) exp_half(0, (m_used == -INFINITY) ? 0.f : m_used, sum_a);
       const float m_eff = (m_used == -INFINITY) ? 0.f : m_used;
-      float sum = 0.f;
-      uint32_t pk[2][32];
-#pragma unroll
-      for (int c = 0; c < 4; ++c)
-#pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          const float p0 = ex2_approx(fmaf(__uint_as_float(s[c][i]), scale_log2, -m_eff));
-          const float p1 = ex2_approx(fmaf(__uint_as_float(s[c][i + 1]), scale_log2, -m_eff));
-          sum += p0 + p1;
-          pk[c >> 1][(c & 1) * 16 + (i >> 1)] = pack2<kBf16>(p0, p1);
-        }
-      l_sum = l_sum * alpha + sum;
-      // P replaces S in place: columns [0, 64) of the S region, two K elements per column
-      tmem_st32(s_tmem, pk[0]);
-      tmem_st32(s_tmem + 32, pk[1]);
-      if (j > 0 && __any_sync(0xffffffffu, alpha != 1.f)) {
-        // rare: rescale the running output before PV(j) accumulates into it
-        mbar_wait(&bars[O_DONE + w], (uint32_t)((j - 1) & 1));
-        tc_fence_after();
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          uint32_t t[32];
-          tmem_ld32(o_tmem + c * 32, t);
-          tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 32; ++i) t[i] = __float_as_uint(__uint_as_float(t[i]) * alpha);
-          tmem_st32(o_tmem + c * 32, t);
-        }
-      }
+      tmem_st32(s_tmem, pk);
       tmem_st_wait();
       tc_fence_before();
       mbar_arrive(&bars[P_FULL + w]);
+      if (row == 0) TC_TRACE(j, w * 5 + 3);
+      exp_half(1, m_eff, sum_b);
+      tmem_st32(s_tmem + 32, pk);
+      tmem_st_wait();
+      tc_fence_before();
+      mbar_arrive(&bars[P_FULLB + w]);
+      if constexpr (kPingPong) asm volatile("bar.arrive %0, 256;" ::"r"(2 + (w ^ 1)) : "memory");
+      if (row == 0) TC_TRACE(j, w * 5 + 4);
+      float sa, sb;
+      f2_unpack(f2_add(sum_a, sum_b), sa, sb);
+      l_sum = l_sum * alpha + (sa + sb);
     }
 
+    if constexpr ((kMode & 2) != 0) {
+      if (w == 0) asm volatile("bar.sync 2, 256;" ::: "memory");  // absorb warpgroup 1's last hand-over
+    }
     // ---- epilogue: O / L -> global -----------------------------------------------------
+    if (row == 0 && w == 1) TC_MARK(5);
     mbar_wait(&bars[O_DONE + w], (uint32_t)(last_tile & 1));
     tc_fence_after();
+    if (row == 0 && w == 1) TC_MARK(6);
     const float inv = (l_sum > 0.f) ? 1.f / l_sum : 0.f;
     char* orow = static_cast<char*>(a.out) +
                  ((int64_t)(q_start + (row_valid ? qpos : 0)) * a.out_stride0 + (int64_t)(kvh * g + head) * a.out_stride1) * 2;
@@ -338,73 +517,105 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
     }
   } else if (warp == 8) {
     // ============================ MMA issue warp =========================================
-    if (lane == 0) {
-      constexpr uint32_t idesc_qk = umma_idesc(kBf16, false, 128, 128);
-      constexpr uint32_t idesc_pv = umma_idesc(kBf16, true, 128, 128);
-      const uint32_t q_base = smem_u32(sQ), k_base = smem_u32(sK), v_base = smem_u32(sV);
-      auto issue_qk = [&](int w, int st) {
-        const uint32_t ab = q_base + w * kTileBytes, bb = k_base + st * kTileBytes;
+    // The whole warp walks the (warp-uniform) control flow and one elected lane issues, so
+    // descriptors live in uniform registers; every descriptor is a precomputed base plus a
+    // compile-time offset in the 14-bit address field.  (A `lane == 0` version cost ~130
+    // cycles per MMA in scalar address arithmetic and R2UR loops - twice the MMA itself.)
+    constexpr uint32_t idesc_qk = umma_idesc(kBf16, false, 128, 128);
+    constexpr uint32_t idesc_pv = umma_idesc(kBf16, true, 128, 128);
+    const uint32_t tm = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint64_t q_desc0 = umma_desc(__shfl_sync(0xffffffffu, smem_u32(sQ), 0), 16, 1024);
+    const uint64_t k_desc0 = umma_desc(__shfl_sync(0xffffffffu, smem_u32(sK), 0), 16, 1024);
+    const uint64_t v_desc0 = umma_desc(__shfl_sync(0xffffffffu, smem_u32(sV), 0), kSubtileBytes, 1024);
+    const bool leader = elect_one();
+    auto issue_qk = [&](int w, int st) {
+      const uint64_t ad = q_desc0 + (uint64_t)((w * kTileBytes) >> 4), bd = k_desc0 + (uint64_t)((st * kTileBytes) >> 4);
+      if (leader) {
 #pragma unroll
         for (int kk = 0; kk < kD / 16; ++kk) {
-          const uint32_t off = (kk >> 2) * kSubtileBytes + (kk & 3) * 32;
-          umma_ss(tmem_base + col_s(w), umma_desc(ab + off, 16, 1024), umma_desc(bb + off, 16, 1024), idesc_qk, kk > 0 ? 1u : 0u);
+          const uint64_t off = (uint64_t)(((kk >> 2) * kSubtileBytes + (kk & 3) * 32) >> 4);
+          umma_ss(tm + col_s(w), ad + off, bd + off, idesc_qk, kk > 0 ? 1u : 0u);
         }
-      };
-      auto issue_pv = [&](int w, int st, bool acc) {
-        const uint32_t bb = v_base + st * kTileBytes;
+      }
+    };
+    // PV for subtile w, tile j: k-steps 0..3 as soon as the first half of P is in TMEM, 4..7 after the second
+    auto issue_pv = [&](int w, int st, bool acc, int j) {
+      const uint64_t bd = v_desc0 + (uint64_t)((st * kTileBytes) >> 4);
 #pragma unroll
-        for (int kk = 0; kk < kBN / 16; ++kk)
-          umma_ts(tmem_base + col_o(w), tmem_base + col_s(w) + kk * 8, umma_desc(bb + kk * 2048, kSubtileBytes, 1024), idesc_pv,
-                  (acc || kk > 0) ? 1u : 0u);
-      };
-      mbar_wait(&bars[Q_FULL], 0);
-      mbar_wait(&bars[K_FULL + 0], 0);
-      tc_fence_after();
-      issue_qk(0, 0);
-      umma_commit(&bars[S_FULL + 0]);
-      issue_qk(1, 0);
+      for (int h = 0; h < 2; ++h) {
+        mbar_wait(&bars[(h ? P_FULLB : P_FULL) + w], (uint32_t)(j & 1));
+        tc_fence_after();
+        if (leader) {
+          TC_TRACE(j, 10 + w * 3 + h);
+#pragma unroll
+          for (int kk = 4 * h; kk < 4 * h + 4; ++kk)
+            umma_ts(tm + col_o(w), tm + col_s(w) + kk * 8, bd + (uint64_t)((kk * 2048) >> 4), idesc_pv, (acc || kk > 0) ? 1u : 0u);
+        }
+      }
+    };
+    mbar_wait(&bars[Q_FULL], 0);
+    mbar_wait(&bars[K_FULL + 0], 0);
+    tc_fence_after();
+    issue_qk(0, 0);
+    if (leader) umma_commit(&bars[S_FULL + 0]);
+    issue_qk(1, 0);
+    if (leader) {
       umma_commit(&bars[S_FULL + 1]);
       umma_commit(&bars[K_EMPTY + 0]);
-      for (int j = 0; j < n_tiles; ++j) {
-        const int st = j & 1;
-        const uint32_t ph = (uint32_t)((j >> 1) & 1);
-        const bool more = j + 1 < n_tiles;
-        const int st1 = (j + 1) & 1;
-        mbar_wait(&bars[V_FULL + st], ph);
-        if (j == last_tile && need_fix) mbar_wait(&bars[V_FIX], 0);
-        mbar_wait(&bars[P_FULL + 0], (uint32_t)(j & 1));
-        tc_fence_after();
-        issue_pv(0, st, j > 0);
-        umma_commit(&bars[O_DONE + 0]);
-        if (more) {
-          mbar_wait(&bars[K_FULL + st1], (uint32_t)(((j + 1) >> 1) & 1));
-          tc_fence_after();
-          issue_qk(0, st1);
+    }
+    int ks1 = 1 % kKStages;      // K stage / phase of tile j + 1
+    uint32_t kph1 = 0;
+    for (int j = 0; j < n_tiles; ++j) {
+      const int st = j & 1;
+      const uint32_t ph = (uint32_t)((j >> 1) & 1);
+      const bool more = j + 1 < n_tiles;
+      // operand tiles first: they arrive long before P does, so these waits are off the
+      // critical path P(j) -> PV(j), QK(j+1) -> S(j+1)
+      mbar_wait(&bars[V_FULL + st], ph);
+      if (j == last_tile && need_fix) mbar_wait(&bars[V_FIX], 0);
+      if (more) mbar_wait(&bars[K_FULL + ks1], kph1);
+      if (leader) TC_TRACE(j, 18);
+      issue_pv(0, st, j > 0, j);
+      if (leader) umma_commit(&bars[O_DONE + 0]);
+      if (more) {
+        issue_qk(0, ks1);
+        if (leader) {
           umma_commit(&bars[S_FULL + 0]);
+          TC_TRACE(j, 12);
         }
-        mbar_wait(&bars[P_FULL + 1], (uint32_t)(j & 1));
-        tc_fence_after();
-        issue_pv(1, st, j > 0);
+      }
+      issue_pv(1, st, j > 0, j);
+      if (leader) {
         umma_commit(&bars[O_DONE + 1]);
         umma_commit(&bars[V_EMPTY + st]);
-        if (more) {
-          issue_qk(1, st1);
+      }
+      if (more) {
+        issue_qk(1, ks1);
+        if (leader) {
           umma_commit(&bars[S_FULL + 1]);
-          umma_commit(&bars[K_EMPTY + st1]);
+          umma_commit(&bars[K_EMPTY + ks1]);
+          TC_TRACE(j, 15);
         }
+      }
+      if (++ks1 == kKStages) ks1 = 0, kph1 ^= 1;
+    }
+    __syncwarp();
+  } else if (warp == 9 || warp == 10) {
+    // ============================ TMA warps: 9 = Q and K, 10 = V =========================
+    // Separate warps so a full V ring never holds back the K prefetch (K of tile j+1 is on the
+    // critical path right after PV(j); a K tile takes ~2000 cycles from request to arrival).
+    const bool is_k = warp == 9;
+    if (lane == 0) {
+      if (is_k) {
+        tma_prefetch_desc(&q_map);
+        tma_prefetch_desc(&k_map);
+        mbar_arrive_expect_tx(&bars[Q_FULL], 2 * kTileBytes);
+      } else {
+        tma_prefetch_desc(&v_map);
       }
     }
     __syncwarp();
-  } else if (warp == 9) {
-    // ============================ TMA warp ===============================================
-    if (lane == 0) {
-      tma_prefetch_desc(&q_map);
-      tma_prefetch_desc(&k_map);
-      tma_prefetch_desc(&v_map);
-      mbar_arrive_expect_tx(&bars[Q_FULL], 2 * kTileBytes);
-    }
-    __syncwarp();
-    if (lane < 4) {
+    if (is_k && lane < 4) {
       const int w = lane >> 1, dc = lane & 1;
       tma_load_4d(sQ + w * kTileBytes + dc * kSubtileBytes, &q_map, &bars[Q_FULL], 0, dc, kvh * g, q_start + qpos0 + w * P.block_q);
     }
@@ -418,10 +629,14 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
       const int tok = (tile0 + j) * kBN + my_box * P.box_slots;
       return (j < n_tiles && my_box < boxes_per_tile && tok < kv_limit) ? bt[tok / bs] : 0;
     };
+    const int nst = is_k ? kKStages : kVStages;
+    const int full0 = is_k ? K_FULL : V_FULL, empty0 = is_k ? K_EMPTY : V_EMPTY;
+    uint8_t* ring = is_k ? sK : sV;
+    const CUtensorMap* map = is_k ? &k_map : &v_map;
     int page_next = lookup(0);
+    int st = 0;
+    uint32_t ph = 0;
     for (int j = 0; j < n_tiles; ++j) {
-      const int st = j & 1;
-      const uint32_t ph = (uint32_t)((j >> 1) & 1);
       const int n0 = (tile0 + j) * kBN;
       const int nbox = min(boxes_per_tile, (kv_limit - n0 + P.box_slots - 1) / P.box_slots);
       const bool active = my_box < nbox;
@@ -429,23 +644,21 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
       page_next = lookup(j + 1);
       const int slot0 = (n0 + my_box * P.box_slots) % bs;
       const uint32_t dst_off = (uint32_t)(st * kTileBytes + my_dc * kSubtileBytes) + (uint32_t)my_box * box_bytes;
-      mbar_wait(&bars[K_EMPTY + st], ph ^ 1);
-      if (lane == 0) mbar_arrive_expect_tx(&bars[K_FULL + st], (uint32_t)nbox * 2 * box_bytes);
+      mbar_wait(&bars[empty0 + st], ph ^ 1);
+      if (lane == 0) TC_TRACE(j, is_k ? 19 : 20);
+      if (lane == 0) mbar_arrive_expect_tx(&bars[full0 + st], (uint32_t)nbox * 2 * box_bytes);
       __syncwarp();
-      if (active) tma_load_5d_nohint(sK + dst_off, &k_map, &bars[K_FULL + st], 0, slot0, my_dc, kvh, page);
-      mbar_wait(&bars[V_EMPTY + st], ph ^ 1);
-      if (lane == 0) mbar_arrive_expect_tx(&bars[V_FULL + st], (uint32_t)nbox * 2 * box_bytes);
-      __syncwarp();
-      if (active) tma_load_5d_nohint(sV + dst_off, &v_map, &bars[V_FULL + st], 0, slot0, my_dc, kvh, page);
+      if (active) tma_load_5d_nohint(ring + dst_off, map, &bars[full0 + st], 0, slot0, my_dc, kvh, page);
+      if (++st == nst) st = 0, ph ^= 1;
     }
     // ---- V tail fix-up -------------------------------------------------------------------
     // Rows of the last tile beyond the visible keys are either unwritten cache slots or
     // shared memory no copy touched; P is 0 there, but 0 x NaN would poison O.  The last
     // tile's copy was issued just above, so its V_FULL phase is the one in flight.
-    if (need_fix) {
-      const int st = last_tile & 1;
-      mbar_wait(&bars[V_FULL + st], (uint32_t)((last_tile >> 1) & 1));
-      uint8_t* vt = sV + st * kTileBytes;
+    if (!is_k && need_fix) {
+      const int vst = last_tile % kVStages;
+      mbar_wait(&bars[V_FULL + vst], (uint32_t)((last_tile / kVStages) & 1));
+      uint8_t* vt = sV + vst * kTileBytes;
       const int n16 = (kBN - last_valid) * 16;  // 16-byte pieces: 2 chunks x 8 per row
       for (int idx = lane; idx < n16; idx += 32) {
         const int r = last_valid + (idx >> 4), dc = (idx >> 3) & 1, c = idx & 7;
@@ -460,6 +673,17 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
   // ---- teardown ---------------------------------------------------------------------------
   tc_fence_before();
   __syncthreads();
+#ifdef B200ATTN_TC_TRACE
+  if (threadIdx.x == 0) TC_MARK(7);
+  if (threadIdx.x == 0) {
+    const int cta = blockIdx.y * gridDim.x + blockIdx.x;
+    if (cta < 4096) {
+      unsigned smid;
+      asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
+      g_tc_cta[cta * 4 + 0] = smid, g_tc_cta[cta * 4 + 1] = tc_t0, g_tc_cta[cta * 4 + 2] = tc_globaltimer(), g_tc_cta[cta * 4 + 3] = n_tiles;
+    }
+  }
+#endif
   if (warp == 11) {
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
@@ -520,15 +744,25 @@ int launch_attn_prefill_tc(const b200attn_attention_params& a, cudaStream_t stre
                    a.vc_head_stride, P.box_slots, 1, 1);
   if (rc) return rc;
   const bool bf16 = a.q_dtype == B200ATTN_BF16;
-  auto kern = bf16 ? attn_prefill_tc_kernel<true> : attn_prefill_tc_kernel<false>;
-  static thread_local bool attr_set[2] = {false, false};
-  if (!attr_set[bf16 ? 1 : 0]) {
+  // fraction of the exponentials taken off the MUFU (tuning().reserved bits 4..7; 0 = default)
+  using Kern = void (*)(const TcParams, const CUtensorMap, const CUtensorMap, const CUtensorMap);
+#define TCV(B) {attn_prefill_tc_kernel<B, 0, 1, 0>, attn_prefill_tc_kernel<B, 0, 1, 0>, attn_prefill_tc_kernel<B, 0, 1, 2>, \
+                attn_prefill_tc_kernel<B, 0, 1, 3>, attn_prefill_tc_kernel<B, 1, 4, 2>, attn_prefill_tc_kernel<B, 1, 4, 3>, \
+                attn_prefill_tc_kernel<B, 1, 3, 2>, attn_prefill_tc_kernel<B, 1, 2, 2>, attn_prefill_tc_kernel<B, 1, 3, 3>}
+  constexpr int kNumVariants = 9;
+  static const Kern kVariants[2][kNumVariants] = {TCV(false), TCV(true)};
+#undef TCV
+  int variant = (tuning().reserved >> 4) & 15;
+  if (variant >= kNumVariants) variant = 0;
+  Kern kern = kVariants[bf16 ? 1 : 0][variant];
+  static thread_local bool attr_set[2][kNumVariants] = {};
+  if (!attr_set[bf16 ? 1 : 0][variant]) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
     if (e != cudaSuccess) {
       set_error("prefill_tc: cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
       return B200ATTN_E_CUDA;
     }
-    attr_set[bf16 ? 1 : 0] = true;
+    attr_set[bf16 ? 1 : 0][variant] = true;
   }
   const int BQ = 2 * P.block_q;
   const dim3 grid((unsigned)(a.num_tokens / BQ + a.num_seqs), (unsigned)a.num_kv_heads);
