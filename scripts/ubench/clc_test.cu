@@ -2,6 +2,7 @@
 #include <cstdio>
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __global__ void k(int* out, int* count) {
+  extern __shared__ char big[];
   __shared__ __align__(16) uint4 resp;
   __shared__ uint64_t bar;
   if (threadIdx.x == 0) {
@@ -18,7 +19,8 @@ __global__ void k(int* out, int* count) {
       asm volatile("clusterlaunchcontrol.try_cancel.async.shared::cta.mbarrier::complete_tx::bytes.b128 [%0], [%1];" ::"r"(smem_u32(&resp)), "r"(smem_u32(&bar)) : "memory");
     }
     // work
-    if (threadIdx.x == 0) { atomicAdd(&out[by * gridDim.x + bx], 1); }
+    if (threadIdx.x == 0) { atomicAdd(&out[by * gridDim.x + bx], 1); big[bx] = 1; }
+    { long long t0 = clock64(); while (clock64() - t0 < 20000) {} }
     n++;
     uint32_t ok = 0;
     while (!ok) asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(smem_u32(&bar)), "r"(phase) : "memory");
@@ -33,7 +35,8 @@ __global__ void k(int* out, int* count) {
 }
 int main() {
   int *out, *cnt; cudaMalloc(&out, 129 * 8 * 4); cudaMalloc(&cnt, 4); cudaMemset(out, 0, 129 * 8 * 4); cudaMemset(cnt, 0, 4);
-  k<<<dim3(129, 8), 128>>>(out, cnt);
+  cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  k<<<dim3(129, 8), 128, 200 * 1024>>>(out, cnt);
   cudaError_t e = cudaDeviceSynchronize();
   int h[129 * 8], c; cudaMemcpy(h, out, sizeof(h), cudaMemcpyDeviceToHost); cudaMemcpy(&c, cnt, 4, cudaMemcpyDeviceToHost);
   int bad = 0; for (int i = 0; i < 129 * 8; ++i) bad += h[i] != 1;

@@ -39,7 +39,7 @@ int main(int argc, char** argv) {
     cudaMemcpyFromSymbol(ct, g_tc_cta, sizeof(ct));
     long long tmin = 1LL << 62, tmax = 0; double busy[160] = {0}; long long tiles[160] = {0}; int ncta[160] = {0};
     double per_tile_sum = 0; int nw = 0; double ovh = 0;
-    for (int c = 0; c < 129 * 8; ++c) {
+    for (int c = 0; c < 4096; ++c) {
       if (ct[c * 4 + 3] <= 0 || ct[c * 4 + 1] == 0) continue;
       int sm = (int)ct[c * 4]; long long a0 = ct[c * 4 + 1], a1 = ct[c * 4 + 2];
       if (a0 < tmin) tmin = a0; if (a1 > tmax) tmax = a1;
@@ -52,7 +52,7 @@ int main(int argc, char** argv) {
            kms * 1e3, (tmax - tmin) * 1e-3, nw, tsum, bsum / 148 * 1e-3, bmin * 1e-3, bmax * 1e-3, bsum / tsum);
     // fit busy = a + b * tiles over CTAs
     double sx = 0, sy = 0, sxx = 0, sxy = 0; int n = 0;
-    for (int c = 0; c < 129 * 8; ++c) { if (ct[c * 4 + 3] <= 0 || ct[c * 4 + 1] == 0) continue; double x = (double)ct[c * 4 + 3], y = (double)(ct[c * 4 + 2] - ct[c * 4 + 1]); sx += x; sy += y; sxx += x * x; sxy += x * y; n++; }
+    for (int c = 0; c < 4096; ++c) { if (ct[c * 4 + 3] <= 0 || ct[c * 4 + 1] == 0) continue; double x = (double)ct[c * 4 + 3], y = (double)(ct[c * 4 + 2] - ct[c * 4 + 1]); sx += x; sy += y; sxx += x * x; sxy += x * y; n++; }
     double bb = (n * sxy - sx * sy) / (n * sxx - sx * sx), aa = (sy - bb * sx) / n;
     printf("per-CTA time ~= %.0f ns + %.1f ns x tiles  (n=%d)\n", aa, bb, n);
   }

@@ -47,8 +47,6 @@ __host__ __device__ constexpr uint32_t col_o(int w) { return 256u + 128u * (uint
 constexpr int kSmemQ = 0;
 constexpr int kSmemK = 2 * kTileBytes;
 constexpr int kSmemV = kSmemK + kKStages * kTileBytes;
-constexpr int kSmemBar = kSmemV + kVStages * kTileBytes;
-constexpr int kSmemBytes = kSmemBar + 256 + 1024;  // barriers + tmem ptr + alignment slack
 constexpr float kRescaleThreshold = 8.0f;          // log2 units
 
 #ifdef B200ATTN_TC_TRACE
@@ -62,7 +60,7 @@ __device__ __forceinline__ long long tc_globaltimer() {
 }
 #define TC_TRACE(j, ev)                                                            \
   do {                                                                             \
-    if (blockIdx.x == 1 && blockIdx.y == 0 && (j) < 64) g_tc_trace[(j) * 32 + (ev)] = clock64(); \
+    if (blockIdx.x == 0 && blockIdx.y == 1 && (j) < 64) g_tc_trace[(j) * 32 + (ev)] = clock64(); \
   } while (0)
 #define TC_MARK(k)                                                                \
   do {                                                                             \
@@ -81,8 +79,6 @@ struct TcParams {
   int box_slots;  // tokens per TMA box = min(block_size, 128)
 };
 
-// P_FULL: first half of P (keys 0..63 of the tile) stored; P_FULLB: second half
-enum Bar { Q_FULL = 0, K_FULL = 1, K_EMPTY = 4, V_FULL = 7, V_EMPTY = 9, S_FULL = 11, P_FULL = 13, P_FULLB = 15, O_DONE = 17, V_FIX = 19, NUM_BARS = 20 };
 
 // ---- tcgen05 wrappers -----------------------------------------------------------------
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -249,13 +245,41 @@ __device__ __forceinline__ uint64_t ex2_poly2(float x0, float x1) {
   return f2_pack(p0, p1);
 }
 
+// ---- persistent work loop -------------------------------------------------------------
+// The grid is still the reference's host-int upper bound (one CTA per (q tile, kv head)), but a
+// CTA does not exit after its tile: a scheduler warp cancels CTAs that have not been launched
+// yet (cluster launch control, `clusterlaunchcontrol.try_cancel`) and runs their tiles here, so
+// barrier init, the TMEM allocation and - more important - the pipeline fill and drain of a
+// tile overlap with its neighbours' (a 64-tile CTA used to pay ~14k idle tensor cycles).
+// Work items travel from the scheduler warp to the other roles through a 2-slot mailbox.
+struct Item {
+  int valid;     // 0 = no more work
+  int b;         // sequence
+  int kvh;       // kv head
+  int q_start;   // first token of the sequence in q / out
+  int q_len;
+  int qpos0;     // first query position of this CTA tile within the sequence
+  int ctx;       // seq_len - q_len
+  int kv_limit;  // keys [tile0 * kBN, kv_limit) can be visible
+  int tile0;
+  int n_tiles;
+  int pad[6];
+};
+static_assert(sizeof(Item) == 64, "mailbox slot");
+
+enum Bar {
+  Q_FULL = 0, Q_EMPTY = 1, K_FULL = 2, K_EMPTY = 5, V_FULL = 8, V_EMPTY = 10, S_FULL = 12, P_FULL = 14, P_FULLB = 16,
+  O_DONE = 18, V_FIX = 20, ITEM_FULL = 21, ITEM_EMPTY = 23, CLC_DONE = 25, NUM_BARS = 26
+};
+constexpr int kSmemBar = kSmemV + kVStages * kTileBytes;
+constexpr int kBarBytes = 256;                       // NUM_BARS * 8 = 208, tmem pointer behind them
+constexpr int kSmemItems = kSmemBar + kBarBytes;     // 2 x Item
+constexpr int kSmemClc = kSmemItems + 2 * 64;        // 16-byte try_cancel response
+constexpr int kSmemBytes = kSmemClc + 64 + 1024;     // + alignment slack
+constexpr int kConsumerWarps = 11;                   // warps 0..10 read every item
+
 // kEmuNum of every kEmuDen exponential pairs are computed by ex2_poly2, the rest on the MUFU.
-// kMode bit 0: exponentials of the first half start against the previous reference max while
-//              the tile max is still being found (redo if it jumps);
-//       bit 1: the two softmax warpgroups take turns on the MUFU (named-barrier ping-pong), so
-//              one subtile's exponentials run under the other subtile's MMAs instead of both
-//              drifting into the same phase and halving each other's rate.
-template <bool kBf16, int kEmuNum, int kEmuDen, int kMode>
+template <bool kBf16, int kEmuNum, int kEmuDen>
 __global__ void __launch_bounds__(kThreads, 1)
 attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CUtensorMap k_map,
                        const __grid_constant__ CUtensorMap v_map) {
@@ -266,59 +290,23 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
   uint8_t* sV = smem + kSmemV;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kSmemBar);
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + NUM_BARS);
+  Item* items = reinterpret_cast<Item*>(smem + kSmemItems);
+  uint4* clc_resp = reinterpret_cast<uint4*>(smem + kSmemClc);
 
   const b200attn_attention_params& a = P.a;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = P.group;
-  const int BQ = 2 * P.block_q;  // query tokens per CTA
+  const int BQ = 2 * P.block_q;  // query tokens per CTA tile
+  const int window = a.sliding_window;
 #ifdef B200ATTN_TC_TRACE
   const long long tc_t0 = tc_globaltimer();
-  if (threadIdx.x == 0) TC_MARK(0);
+  int tc_tiles = 0;
 #endif
-
-  // ---- q-tile -> sequence; heaviest (latest) tiles are scheduled first ---------------
-  const int q_tile_global = (int)gridDim.x - 1 - (int)blockIdx.x;
-  const int kvh = blockIdx.y;
-  int left = 0, right = a.num_seqs;
-  while (left < right) {
-    const int mid = (left + right) >> 1;
-    const int mid_val = a.cu_seqlens_q[mid] / BQ + mid;
-    if (mid_val <= q_tile_global) left = mid + 1; else right = mid;
-  }
-  const int b = left - 1;
-  if (b < 0) return;
-  const int q_start = a.cu_seqlens_q[b];
-  const int q_len = a.cu_seqlens_q[b + 1] - q_start;
-  const int q_tile_local = q_tile_global - (q_start / BQ + b);
-  if (q_tile_local * BQ >= q_len) return;
-  if (q_len < P.min_q_len || q_len > P.max_q_len) return;  // another launch covers this sequence
-  const int seq_len = a.seq_lens[b];
-  const int ctx = seq_len - q_len;
-  const int qpos0 = q_tile_local * BQ;
-  const int qpos_last = min(qpos0 + BQ, q_len) - 1;
-  const int kv_limit = min(ctx + qpos_last + 1, seq_len);  // keys [kv_first, kv_limit) can be visible
-  const int window = a.sliding_window;
-  const int kv_first = window > 0 ? max(0, ctx + qpos0 - window + 1) : 0;
-  const int tile0 = kv_first / kBN;
-  const int n_tiles = (kv_limit + kBN - 1) / kBN - tile0;
-
-  if (n_tiles <= 0) {
-    // nothing visible (seq_len <= 0): rows get zeros like the reference's reduce (:828)
-    if (threadIdx.x < 256) {
-      const int r = threadIdx.x, qpos = qpos0 + r / g;
-      if (qpos < q_len) {
-        int4* orow = reinterpret_cast<int4*>(static_cast<char*>(a.out) +
-                                             ((int64_t)(q_start + qpos) * a.out_stride0 + (int64_t)(kvh * g + r % g) * a.out_stride1) * 2);
-#pragma unroll
-        for (int i = 0; i < kD * 2 / 16; ++i) orow[i] = make_int4(0, 0, 0, 0);
-      }
-    }
-    return;
-  }
 
   // ---- one-time setup ------------------------------------------------------------------
   if (warp == 8 && lane == 0) {
     mbar_init(&bars[Q_FULL], 1);
+    mbar_init(&bars[Q_EMPTY], 1);
     for (int s = 0; s < kKStages; ++s) {
       mbar_init(&bars[K_FULL + s], 1);
       mbar_init(&bars[K_EMPTY + s], 1);
@@ -330,130 +318,113 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
       mbar_init(&bars[P_FULL + s], 128);
       mbar_init(&bars[P_FULLB + s], 128);
       mbar_init(&bars[O_DONE + s], 1);
+      mbar_init(&bars[ITEM_FULL + s], 1);
+      mbar_init(&bars[ITEM_EMPTY + s], kConsumerWarps);
     }
     mbar_init(&bars[V_FIX], 1);
+    mbar_init(&bars[CLC_DONE], 1);
     fence_barrier_init();
   }
   if (warp == 11) tmem_alloc(tmem_ptr_smem, 512);
+  if (warp == 9 && lane == 0) {
+    tma_prefetch_desc(&q_map);
+    tma_prefetch_desc(&k_map);
+  }
+  if (warp == 10 && lane == 0) tma_prefetch_desc(&v_map);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
-  if (threadIdx.x == 0) TC_MARK(1);
 
-  const int last_tile = n_tiles - 1;
-  const int last_valid = kv_limit - (tile0 + last_tile) * kBN;  // rows of the last tile that hold visible keys
-  const bool need_fix = last_valid < kBN;
+  // ---- state shared by the roles that consume the work queue -------------------------------
+  uint32_t n_items = 0;   // items taken so far (mailbox slot / phase)
+  uint32_t t_run = 0;     // KV tiles processed so far: parity source of the per-tile barriers
+  const float scale_log2 = a.softmax_scale * kLog2e;
+  int k_st = 0, v_st = 0;           // ring positions (TMA warps: next to fill; MMA warp: next to use)
+  uint32_t k_ph = 0, v_ph = 0;
+  uint32_t n_fix = 0;               // V tail fix-ups so far (V_FIX parity)
+  const bool leader = elect_one();  // MMA warp: the issuing lane
+  const uint32_t tm = __shfl_sync(0xffffffffu, tmem_base, 0);
+  const uint64_t q_desc0 = umma_desc(__shfl_sync(0xffffffffu, smem_u32(sQ), 0), 16, 1024);
+  const uint64_t k_desc0 = umma_desc(__shfl_sync(0xffffffffu, smem_u32(sK), 0), 16, 1024);
+  const uint64_t v_desc0 = umma_desc(__shfl_sync(0xffffffffu, smem_u32(sV), 0), kSubtileBytes, 1024);
+  // next work item from the mailbox; false = no more work
+  auto next_item = [&](Item& it) -> bool {
+    const uint32_t slot = n_items & 1;
+    mbar_wait(&bars[ITEM_FULL + slot], (n_items >> 1) & 1);
+    it = items[slot];
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&bars[ITEM_EMPTY + slot]);  // the copy is in registers: the slot is free
+    return it.valid != 0;
+  };
+#define B200ATTN_ITEM_VARS                                                                              \
+  const int n_tiles = it.n_tiles, tile0 = it.tile0, kvh = it.kvh;                                       \
+  const int last_tile = n_tiles - 1;                                                                    \
+  const int last_valid = it.kv_limit - (tile0 + last_tile) * kBN; /* visible rows of the last tile */ \
+  const bool need_fix = last_valid < kBN;                                                               \
+  (void)kvh, (void)need_fix, (void)last_valid;
 
-  // Register budget follows the roles: the softmax warpgroups hold a 128-column row of S
-  // each, the MMA / TMA warpgroup needs almost nothing (2 x 208 + 80 <= 512 per lane slot).
-  if (warp < 8) asm volatile("setmaxnreg.inc.sync.aligned.u32 208;");
-  else asm volatile("setmaxnreg.dec.sync.aligned.u32 80;");
-
+  // Register budget follows the roles (each role has its own loop after its setmaxnreg): the
+  // softmax warpgroups hold a 128-column row of S each, the MMA / TMA / scheduler warpgroup
+  // needs almost nothing (2 x 208 + 80 <= 512 per lane slot).
   if (warp < 8) {
-    // ============================ softmax warpgroups ====================================
-    const int w = warp >> 2;                  // Q subtile
-    const int row = (warp & 3) * 32 + lane;   // row of the subtile == TMEM lane
-    const int qpos = qpos0 + (w * 128 + row) / g;
-    const int head = row % g;                 // 128 % g == 0
-    const bool row_valid = qpos < q_len;
-    const int limit = row_valid ? ctx + qpos + 1 : 0;                        // visible keys: [lo, limit)
-    const int lo = (window > 0 && row_valid) ? max(0, ctx + qpos - window + 1) : 0;
-    const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
-    const uint32_t s_tmem = tmem_base + lane_base + col_s(w);
-    const uint32_t o_tmem = tmem_base + lane_base + col_o(w);
-    const float scale_log2 = a.softmax_scale * kLog2e;
-    float m_used = -INFINITY, l_sum = 0.f;
-    // ping-pong: warpgroup 0 goes first (warpgroup 1 hands it the first turn)
-    if constexpr ((kMode & 2) != 0) {
-      if (w == 1) asm volatile("bar.arrive 2, 256;" ::: "memory");
-    }
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 208;");
+    Item it;
+    while (next_item(it)) {
+      B200ATTN_ITEM_VARS
+#ifdef B200ATTN_TC_TRACE
+      tc_tiles += n_tiles;
+#endif
+      // ============================ softmax warpgroups ====================================
+      const int w = warp >> 2;                  // Q subtile
+      const int row = (warp & 3) * 32 + lane;   // row of the subtile == TMEM lane
+      const int qpos = it.qpos0 + (w * 128 + row) / g;
+      const int head = row % g;                 // 128 % g == 0
+      const bool row_valid = qpos < it.q_len;
+      const int limit = row_valid ? it.ctx + qpos + 1 : 0;                        // visible keys: [lo, limit)
+      const int lo = (window > 0 && row_valid) ? max(0, it.ctx + qpos - window + 1) : 0;
+      const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
+      const uint32_t s_tmem = tmem_base + lane_base + col_s(w);
+      const uint32_t o_tmem = tmem_base + lane_base + col_o(w);
+      float m_used = -INFINITY, l_sum = 0.f;
 
-    for (int j = 0; j < n_tiles; ++j) {
-      mbar_wait(&bars[S_FULL + w], (uint32_t)(j & 1));
-      tc_fence_after();
-      if (row == 0) TC_TRACE(j, w * 5 + 0);
-      if (row == 0 && w == 0 && j == 0) TC_MARK(2);
-      if (row == 0 && w == 0 && j == 1) TC_MARK(3);
-      if (row == 0 && w == 0 && j == last_tile) TC_MARK(4);
-      uint32_t s[4][32];
+      for (int j = 0; j < n_tiles; ++j) {
+        const uint32_t par = (t_run + (uint32_t)j) & 1;
+        mbar_wait(&bars[S_FULL + w], par);
+        tc_fence_after();
+        if (row == 0) TC_TRACE(t_run + j, w * 5 + 0);
+        uint32_t s[4][32];
 #pragma unroll
-      for (int c = 0; c < 4; ++c) tmem_ld32(s_tmem + c * 32, s[c]);
-      tmem_ld_wait();
-      if (row == 0) TC_TRACE(j, w * 5 + 1);
-      const int n0 = (tile0 + j) * kBN;
-      if (n0 + kBN > limit || n0 < lo) {
+        for (int c = 0; c < 4; ++c) tmem_ld32(s_tmem + c * 32, s[c]);
+        tmem_ld_wait();
+        if (row == 0) TC_TRACE(t_run + j, w * 5 + 1);
+        const int n0 = (tile0 + j) * kBN;
+        if (n0 + kBN > limit || n0 < lo) {
+#pragma unroll
+          for (int c = 0; c < 4; ++c)
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              const int pos = n0 + c * 32 + i;
+              if (pos >= limit || pos < lo) s[c][i] = 0xff800000u;  // -inf
+            }
+        }
+        // row max: four FMNMX3 chains (two new values per instruction)
+        float mxc[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
         for (int c = 0; c < 4; ++c)
 #pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            const int pos = n0 + c * 32 + i;
-            if (pos >= limit || pos < lo) s[c][i] = 0xff800000u;  // -inf
-          }
-      }
-      // P = 2^(S*scale - m) in two halves of 64 keys; each half replaces S in place (bf16
-      // pairs: columns [32h, 32h+32) of the S region) and is announced on its own barrier,
-      // so the first four k-steps of PV run while the second half is still being computed.
-      const uint64_t sc2 = f2_pack(scale_log2, scale_log2);
-      uint32_t pk[32];
-      auto exp_half = [&](int h, float m_eff, uint64_t& sum_out) {
-        const uint64_t nm2 = f2_pack(-m_eff, -m_eff);
-        uint64_t sum2[2] = {0ull, 0ull};
-#pragma unroll
-        for (int cc = 0; cc < 2; ++cc) {
-          const int c = 2 * h + cc;
-#pragma unroll
-          for (int i = 0; i < 32; i += 2) {
-            const int k = cc * 16 + (i >> 1);
-            const uint64_t x2 = f2_fma(f2_pack(__uint_as_float(s[c][i]), __uint_as_float(s[c][i + 1])), sc2, nm2);
-            float x0, x1, p0, p1;
-            f2_unpack(x2, x0, x1);
-            uint64_t p2;
-            if ((k % kEmuDen) < kEmuNum) {
-              p2 = ex2_poly2(x0, x1);
-              f2_unpack(p2, p0, p1);
-            } else {
-              p0 = ex2_approx(x0), p1 = ex2_approx(x1);
-              p2 = f2_pack(p0, p1);
-            }
-            sum2[k & 1] = f2_add(sum2[k & 1], p2);
-            pk[k] = pack2<kBf16>(p0, p1);
-          }
-        }
-        sum_out = f2_add(sum2[0], sum2[1]);
-      };
-      // The row max is NOT a prerequisite of the exponentials: the reference point m_used only
-      // has to be within 2^kRescaleThreshold of the true running max, so the first half is
-      // computed against the m_used of the previous tiles while the max of this tile (FMNMX3, on
-      // the otherwise idle ALU pipe) is found under the MUFU's shadow.  Only if the tile max
-      // jumps past the threshold (always on a row's first visible tile) is the half redone.
-      constexpr bool kOptMax = (kMode & 1) != 0, kPingPong = (kMode & 2) != 0;
-      auto turn_wait = [&]() {  // my turn on the MUFU: the other warpgroup has released barrier 2 + w
-        if constexpr (kPingPong) asm volatile("bar.sync %0, 256;" ::"r"(2 + w) : "memory");
-      };
-      uint64_t sum_a, sum_b;
-      if constexpr (kOptMax) {
-        turn_wait();
-        exp_half(0, (m_used == -INFINITY) ? 0.f : m_used, sum_a);
-      }
-      float mxc[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-#pragma unroll
-      for (int c = 0; c < 4; ++c)
-#pragma unroll
-        for (int i = 0; i < 32; i += 2) mxc[c] = fmax3(mxc[c], __uint_as_float(s[c][i]), __uint_as_float(s[c][i + 1]));
-      const float mx = fmax3(fmaxf(mxc[0], mxc[1]), mxc[2], mxc[3]);
-      const float m_tile = mx * scale_log2;  // softmax_scale > 0 (checked on the host)
-      float alpha = 1.f;
-      if (row == 0) TC_TRACE(j, w * 5 + 2);
-      const bool grew = __any_sync(0xffffffffu, m_tile > m_used + kRescaleThreshold);
-      if (grew) {
+          for (int i = 0; i < 32; i += 2) mxc[c] = fmax3(mxc[c], __uint_as_float(s[c][i]), __uint_as_float(s[c][i + 1]));
+        const float mx = fmax3(fmaxf(mxc[0], mxc[1]), mxc[2], mxc[3]);
+        const float m_tile = mx * scale_log2;  // softmax_scale > 0 (checked on the host)
+        float alpha = 1.f;
         if (m_tile > m_used + kRescaleThreshold) {  // also the first finite max (m_used = -inf)
           alpha = ex2_approx(m_used - m_tile);       // 0 when m_used = -inf
           m_used = m_tile;
         }
-        if (j > 0) {
-          // rescale the running output before PV(j) accumulates into it
-          mbar_wait(&bars[O_DONE + w], (uint32_t)((j - 1) & 1));
+        const float m_eff = (m_used == -INFINITY) ? 0.f : m_used;
+        if (j > 0 && __any_sync(0xffffffffu, alpha != 1.f)) {
+          // rare: rescale the running output before PV(j) accumulates into it
+          mbar_wait(&bars[O_DONE + w], par ^ 1);
           tc_fence_after();
           // (8 columns at a time: all 128 S values are live here)
 #pragma unroll 1
@@ -466,221 +437,343 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
             tmem_st8(o_tmem + c * 8, t);
           }
         }
+        if (row == 0) TC_TRACE(t_run + j, w * 5 + 2);
+        // P = 2^(S*scale - m) in two halves of 64 keys; each half replaces S in place (bf16
+        // pairs: columns [32h, 32h+32) of the S region) and is announced on its own barrier,
+        // so the first four k-steps of PV run while the second half is still being computed.
+        const uint64_t sc2 = f2_pack(scale_log2, scale_log2), nm2 = f2_pack(-m_eff, -m_eff);
+        uint64_t sum2[2] = {0ull, 0ull};
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          uint32_t pk[32];
+#pragma unroll
+          for (int cc = 0; cc < 2; ++cc) {
+            const int c = 2 * h + cc;
+#pragma unroll
+            for (int i = 0; i < 32; i += 2) {
+              const int k = cc * 16 + (i >> 1);
+              const uint64_t x2 = f2_fma(f2_pack(__uint_as_float(s[c][i]), __uint_as_float(s[c][i + 1])), sc2, nm2);
+              float x0, x1, p0, p1;
+              f2_unpack(x2, x0, x1);
+              uint64_t p2;
+              if ((k % kEmuDen) < kEmuNum) {
+                p2 = ex2_poly2(x0, x1);
+                f2_unpack(p2, p0, p1);
+              } else {
+                p0 = ex2_approx(x0), p1 = ex2_approx(x1);
+                p2 = f2_pack(p0, p1);
+              }
+              sum2[k & 1] = f2_add(sum2[k & 1], p2);
+              pk[k] = pack2<kBf16>(p0, p1);
+            }
+          }
+          tmem_st32(s_tmem + 32 * h, pk);
+          tmem_st_wait();
+          tc_fence_before();
+          mbar_arrive(&bars[(h ? P_FULLB : P_FULL) + w]);
+          if (row == 0) TC_TRACE(t_run + j, w * 5 + 3 + h);
+        }
+        float sa, sb;
+        f2_unpack(f2_add(sum2[0], sum2[1]), sa, sb);
+        l_sum = l_sum * alpha + (sa + sb);
       }
-      if constexpr (!kOptMax) turn_wait();
-      if (!kOptMax || grew) exp_half(0, (m_used == -INFINITY) ? 0.f : m_used, sum_a);
-      const float m_eff = (m_used == -INFINITY) ? 0.f : m_used;
-      tmem_st32(s_tmem, pk);
-      tmem_st_wait();
-      tc_fence_before();
-      mbar_arrive(&bars[P_FULL + w]);
-      if (row == 0) TC_TRACE(j, w * 5 + 3);
-      exp_half(1, m_eff, sum_b);
-      tmem_st32(s_tmem + 32, pk);
-      tmem_st_wait();
-      tc_fence_before();
-      mbar_arrive(&bars[P_FULLB + w]);
-      if constexpr (kPingPong) asm volatile("bar.arrive %0, 256;" ::"r"(2 + (w ^ 1)) : "memory");
-      if (row == 0) TC_TRACE(j, w * 5 + 4);
-      float sa, sb;
-      f2_unpack(f2_add(sum_a, sum_b), sa, sb);
-      l_sum = l_sum * alpha + (sa + sb);
-    }
 
-    if constexpr ((kMode & 2) != 0) {
-      if (w == 0) asm volatile("bar.sync 2, 256;" ::: "memory");  // absorb warpgroup 1's last hand-over
-    }
-    // ---- epilogue: O / L -> global -----------------------------------------------------
-    if (row == 0 && w == 1) TC_MARK(5);
-    mbar_wait(&bars[O_DONE + w], (uint32_t)(last_tile & 1));
-    tc_fence_after();
-    if (row == 0 && w == 1) TC_MARK(6);
-    const float inv = (l_sum > 0.f) ? 1.f / l_sum : 0.f;
-    char* orow = static_cast<char*>(a.out) +
-                 ((int64_t)(q_start + (row_valid ? qpos : 0)) * a.out_stride0 + (int64_t)(kvh * g + head) * a.out_stride1) * 2;
+      // ---- epilogue: O / L -> global -----------------------------------------------------
+      // The next item's first PV overwrites O, but it waits for this warpgroup's next P, which
+      // is only produced after the loads below have completed: no extra barrier is needed.
+      mbar_wait(&bars[O_DONE + w], (t_run + (uint32_t)last_tile) & 1);
+      tc_fence_after();
+      const float inv = (l_sum > 0.f) ? 1.f / l_sum : 0.f;
+      char* orow = static_cast<char*>(a.out) +
+                   ((int64_t)(it.q_start + (row_valid ? qpos : 0)) * a.out_stride0 + (int64_t)(kvh * g + head) * a.out_stride1) * 2;
 #pragma unroll
-    for (int c = 0; c < 4; ++c) {
-      uint32_t t[32];
-      tmem_ld32(o_tmem + c * 32, t);
-      tmem_ld_wait();
-      if (row_valid) {
+      for (int c = 0; c < 4; ++c) {
+        uint32_t t[32];
+        tmem_ld32(o_tmem + c * 32, t);
+        tmem_ld_wait();
+        if (row_valid) {
 #pragma unroll
-        for (int i = 0; i < 32; i += 8) {
-          int4 v;
-          v.x = (int)pack2<kBf16>(__uint_as_float(t[i]) * inv, __uint_as_float(t[i + 1]) * inv);
-          v.y = (int)pack2<kBf16>(__uint_as_float(t[i + 2]) * inv, __uint_as_float(t[i + 3]) * inv);
-          v.z = (int)pack2<kBf16>(__uint_as_float(t[i + 4]) * inv, __uint_as_float(t[i + 5]) * inv);
-          v.w = (int)pack2<kBf16>(__uint_as_float(t[i + 6]) * inv, __uint_as_float(t[i + 7]) * inv);
-          *reinterpret_cast<int4*>(orow + (c * 32 + i) * 2) = v;
+          for (int i = 0; i < 32; i += 8) {
+            int4 v;
+            v.x = (int)pack2<kBf16>(__uint_as_float(t[i]) * inv, __uint_as_float(t[i + 1]) * inv);
+            v.y = (int)pack2<kBf16>(__uint_as_float(t[i + 2]) * inv, __uint_as_float(t[i + 3]) * inv);
+            v.z = (int)pack2<kBf16>(__uint_as_float(t[i + 4]) * inv, __uint_as_float(t[i + 5]) * inv);
+            v.w = (int)pack2<kBf16>(__uint_as_float(t[i + 6]) * inv, __uint_as_float(t[i + 7]) * inv);
+            *reinterpret_cast<int4*>(orow + (c * 32 + i) * 2) = v;
+          }
         }
       }
+      tc_fence_before();
+      t_run += (uint32_t)n_tiles;
+      ++n_items;
     }
-  } else if (warp == 8) {
-    // ============================ MMA issue warp =========================================
-    // The whole warp walks the (warp-uniform) control flow and one elected lane issues, so
-    // descriptors live in uniform registers; every descriptor is a precomputed base plus a
-    // compile-time offset in the 14-bit address field.  (A `lane == 0` version cost ~130
-    // cycles per MMA in scalar address arithmetic and R2UR loops - twice the MMA itself.)
-    constexpr uint32_t idesc_qk = umma_idesc(kBf16, false, 128, 128);
-    constexpr uint32_t idesc_pv = umma_idesc(kBf16, true, 128, 128);
-    const uint32_t tm = __shfl_sync(0xffffffffu, tmem_base, 0);
-    const uint64_t q_desc0 = umma_desc(__shfl_sync(0xffffffffu, smem_u32(sQ), 0), 16, 1024);
-    const uint64_t k_desc0 = umma_desc(__shfl_sync(0xffffffffu, smem_u32(sK), 0), 16, 1024);
-    const uint64_t v_desc0 = umma_desc(__shfl_sync(0xffffffffu, smem_u32(sV), 0), kSubtileBytes, 1024);
-    const bool leader = elect_one();
-    auto issue_qk = [&](int w, int st) {
-      const uint64_t ad = q_desc0 + (uint64_t)((w * kTileBytes) >> 4), bd = k_desc0 + (uint64_t)((st * kTileBytes) >> 4);
-      if (leader) {
-#pragma unroll
-        for (int kk = 0; kk < kD / 16; ++kk) {
-          const uint64_t off = (uint64_t)(((kk >> 2) * kSubtileBytes + (kk & 3) * 32) >> 4);
-          umma_ss(tm + col_s(w), ad + off, bd + off, idesc_qk, kk > 0 ? 1u : 0u);
+  } else {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 80;");
+    if (warp == 11) {
+      // ============================ scheduler warp ==========================================
+      // Decodes a grid coordinate into a work item exactly as a one-tile CTA used to (the
+      // reference's q-block -> sequence binary search, triton_unified_attention.py:32-52),
+      // publishes it, and asks the hardware for the next not-yet-launched CTA.
+      // grid = (kv heads, q tiles): CTAs are launched x-fastest, so all heads of the heaviest
+      // (latest) q tile go first and the lightest tiles form the tail
+      int bx = (int)blockIdx.x, by = (int)blockIdx.y;
+      uint32_t n_pub = 0, clc_phase = 0;
+      while (true) {
+        const int q_tile_global = (int)gridDim.y - 1 - by;
+        int left = 0, right = a.num_seqs;
+        while (left < right) {
+          const int mid = (left + right) >> 1;
+          const int mid_val = a.cu_seqlens_q[mid] / BQ + mid;
+          if (mid_val <= q_tile_global) left = mid + 1; else right = mid;
         }
-      }
-    };
-    // PV for subtile w, tile j: k-steps 0..3 as soon as the first half of P is in TMEM, 4..7 after the second
-    auto issue_pv = [&](int w, int st, bool acc, int j) {
-      const uint64_t bd = v_desc0 + (uint64_t)((st * kTileBytes) >> 4);
+        Item it;
+        it.valid = 1, it.b = left - 1, it.kvh = bx, it.n_tiles = 0;
+        bool zero_rows = false;
+        if (it.b >= 0) {
+          it.q_start = a.cu_seqlens_q[it.b];
+          it.q_len = a.cu_seqlens_q[it.b + 1] - it.q_start;
+          const int q_tile_local = q_tile_global - (it.q_start / BQ + it.b);
+          it.qpos0 = q_tile_local * BQ;
+          // sequences outside [min_q_len, max_q_len] belong to another launch of a mixed batch
+          if (it.qpos0 < it.q_len && it.q_len >= P.min_q_len && it.q_len <= P.max_q_len) {
+            const int seq_len = a.seq_lens[it.b];
+            it.ctx = seq_len - it.q_len;
+            const int qpos_last = min(it.qpos0 + BQ, it.q_len) - 1;
+            it.kv_limit = min(it.ctx + qpos_last + 1, seq_len);
+            const int kv_first = window > 0 ? max(0, it.ctx + it.qpos0 - window + 1) : 0;
+            it.tile0 = kv_first / kBN;
+            it.n_tiles = (it.kv_limit + kBN - 1) / kBN - it.tile0;
+            zero_rows = it.n_tiles <= 0;
+          }
+        }
+        if (zero_rows) {
+          // nothing visible (seq_len <= 0): rows get zeros like the reference's reduce (:828)
+          for (int r = lane; r < 256; r += 32) {
+            const int qpos = it.qpos0 + r / g;
+            if (qpos < it.q_len) {
+              int4* orow = reinterpret_cast<int4*>(static_cast<char*>(a.out) +
+                                                   ((int64_t)(it.q_start + qpos) * a.out_stride0 + (int64_t)(it.kvh * g + r % g) * a.out_stride1) * 2);
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        mbar_wait(&bars[(h ? P_FULLB : P_FULL) + w], (uint32_t)(j & 1));
+              for (int i = 0; i < kD * 2 / 16; ++i) orow[i] = make_int4(0, 0, 0, 0);
+            }
+          }
+        } else if (it.n_tiles > 0) {
+          const uint32_t slot = n_pub & 1;
+          mbar_wait(&bars[ITEM_EMPTY + slot], ((n_pub >> 1) & 1) ^ 1);
+          if (lane == 0) items[slot] = it;
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&bars[ITEM_FULL + slot]);
+          // Do not reserve more work until every role has started on this item: a CTA then
+          // holds its current tile plus at most one queued tile (whose pipeline fill overlaps
+          // the current one's drain), which keeps the tail of the grid balanced.
+          mbar_wait(&bars[ITEM_EMPTY + slot], (n_pub >> 1) & 1);
+          ++n_pub;
+        }
+        if (lane == 0) {
+          mbar_arrive_expect_tx(&bars[CLC_DONE], 16);
+          asm volatile("clusterlaunchcontrol.try_cancel.async.shared::cta.mbarrier::complete_tx::bytes.b128 [%0], [%1];"
+                       ::"r"(smem_u32(clc_resp)), "r"(smem_u32(&bars[CLC_DONE])) : "memory");
+        }
+        mbar_wait(&bars[CLC_DONE], clc_phase);
+        clc_phase ^= 1;
+        uint32_t got, nx, ny;
+        asm volatile(
+            "{\n\t.reg .b128 r;\n\t.reg .pred p;\n\t"
+            "ld.shared.b128 r, [%3];\n\t"
+            "clusterlaunchcontrol.query_cancel.is_canceled.pred.b128 p, r;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t"
+            "@p clusterlaunchcontrol.query_cancel.get_first_ctaid.v4.b32.b128 {%1, %2, _, _}, r;\n\t}"
+            : "=r"(got), "=r"(nx), "=r"(ny)
+            : "r"(smem_u32(clc_resp))
+            : "memory");
+        if (!got) break;
+        bx = (int)nx, by = (int)ny;
+      }
+      {  // tell the other roles to stop
+        const uint32_t slot = n_pub & 1;
+        mbar_wait(&bars[ITEM_EMPTY + slot], ((n_pub >> 1) & 1) ^ 1);
+        if (lane == 0) items[slot].valid = 0;
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bars[ITEM_FULL + slot]);
+      }
+    } else if (warp == 8) {
+      Item it;
+      while (next_item(it)) {
+        B200ATTN_ITEM_VARS
+        // ============================ MMA issue warp =========================================
+        // The whole warp walks the (warp-uniform) control flow and one elected lane issues, so
+        // descriptors live in uniform registers; every descriptor is a precomputed base plus a
+        // compile-time offset in the 14-bit address field.  (A `lane == 0` version cost ~130
+        // cycles per MMA in scalar address arithmetic and R2UR loops - twice the MMA itself.)
+        constexpr uint32_t idesc_qk = umma_idesc(kBf16, false, 128, 128);
+        constexpr uint32_t idesc_pv = umma_idesc(kBf16, true, 128, 128);
+        auto issue_qk = [&](int w, int st) {
+          const uint64_t ad = q_desc0 + (uint64_t)((w * kTileBytes) >> 4), bd = k_desc0 + (uint64_t)((st * kTileBytes) >> 4);
+          if (leader) {
+#pragma unroll
+            for (int kk = 0; kk < kD / 16; ++kk) {
+              const uint64_t off = (uint64_t)(((kk >> 2) * kSubtileBytes + (kk & 3) * 32) >> 4);
+              umma_ss(tm + col_s(w), ad + off, bd + off, idesc_qk, kk > 0 ? 1u : 0u);
+            }
+          }
+        };
+        // PV for subtile w: k-steps 0..3 as soon as the first half of P is in TMEM, 4..7 after the second
+        auto issue_pv = [&](int w, int st, bool acc, uint32_t par, uint32_t t) {
+          const uint64_t bd = v_desc0 + (uint64_t)((st * kTileBytes) >> 4);
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            mbar_wait(&bars[(h ? P_FULLB : P_FULL) + w], par);
+            tc_fence_after();
+            if (leader) {
+              TC_TRACE(t, 10 + w * 3 + h);
+#pragma unroll
+              for (int kk = 4 * h; kk < 4 * h + 4; ++kk)
+                umma_ts(tm + col_o(w), tm + col_s(w) + kk * 8, bd + (uint64_t)((kk * 2048) >> 4), idesc_pv, (acc || kk > 0) ? 1u : 0u);
+            }
+          }
+        };
+        // S(0) of this item: needs Q and the first K tile; S is free (its last reader, the
+        // previous item's final PV, is ahead of these MMAs on the in-order tensor pipe)
+        mbar_wait(&bars[Q_FULL], (n_items & 1));
+        mbar_wait(&bars[K_FULL + k_st], k_ph);
         tc_fence_after();
-        if (leader) {
-          TC_TRACE(j, 10 + w * 3 + h);
-#pragma unroll
-          for (int kk = 4 * h; kk < 4 * h + 4; ++kk)
-            umma_ts(tm + col_o(w), tm + col_s(w) + kk * 8, bd + (uint64_t)((kk * 2048) >> 4), idesc_pv, (acc || kk > 0) ? 1u : 0u);
-        }
-      }
-    };
-    mbar_wait(&bars[Q_FULL], 0);
-    mbar_wait(&bars[K_FULL + 0], 0);
-    tc_fence_after();
-    issue_qk(0, 0);
-    if (leader) umma_commit(&bars[S_FULL + 0]);
-    issue_qk(1, 0);
-    if (leader) {
-      umma_commit(&bars[S_FULL + 1]);
-      umma_commit(&bars[K_EMPTY + 0]);
-    }
-    int ks1 = 1 % kKStages;      // K stage / phase of tile j + 1
-    uint32_t kph1 = 0;
-    for (int j = 0; j < n_tiles; ++j) {
-      const int st = j & 1;
-      const uint32_t ph = (uint32_t)((j >> 1) & 1);
-      const bool more = j + 1 < n_tiles;
-      // operand tiles first: they arrive long before P does, so these waits are off the
-      // critical path P(j) -> PV(j), QK(j+1) -> S(j+1)
-      mbar_wait(&bars[V_FULL + st], ph);
-      if (j == last_tile && need_fix) mbar_wait(&bars[V_FIX], 0);
-      if (more) mbar_wait(&bars[K_FULL + ks1], kph1);
-      if (leader) TC_TRACE(j, 18);
-      issue_pv(0, st, j > 0, j);
-      if (leader) umma_commit(&bars[O_DONE + 0]);
-      if (more) {
-        issue_qk(0, ks1);
-        if (leader) {
-          umma_commit(&bars[S_FULL + 0]);
-          TC_TRACE(j, 12);
-        }
-      }
-      issue_pv(1, st, j > 0, j);
-      if (leader) {
-        umma_commit(&bars[O_DONE + 1]);
-        umma_commit(&bars[V_EMPTY + st]);
-      }
-      if (more) {
-        issue_qk(1, ks1);
+        issue_qk(0, k_st);
+        if (leader) umma_commit(&bars[S_FULL + 0]);
+        issue_qk(1, k_st);
         if (leader) {
           umma_commit(&bars[S_FULL + 1]);
-          umma_commit(&bars[K_EMPTY + ks1]);
-          TC_TRACE(j, 15);
+          umma_commit(&bars[K_EMPTY + k_st]);
+          if (n_tiles == 1) umma_commit(&bars[Q_EMPTY]);
         }
+        if (++k_st == kKStages) k_st = 0, k_ph ^= 1;
+        for (int j = 0; j < n_tiles; ++j) {
+          const uint32_t t = t_run + (uint32_t)j, par = t & 1;
+          const bool more = j + 1 < n_tiles;
+          // operand tiles first: they arrive long before P does, so these waits are off the
+          // critical path P(j) -> PV(j), QK(j+1) -> S(j+1)
+          mbar_wait(&bars[V_FULL + v_st], v_ph);
+          if (j == last_tile && need_fix) {
+            mbar_wait(&bars[V_FIX], n_fix & 1);
+            ++n_fix;
+          }
+          if (more) mbar_wait(&bars[K_FULL + k_st], k_ph);
+          issue_pv(0, v_st, j > 0, par, t);
+          if (leader) umma_commit(&bars[O_DONE + 0]);
+          if (more) {
+            issue_qk(0, k_st);
+            if (leader) {
+              umma_commit(&bars[S_FULL + 0]);
+              TC_TRACE(t, 12);
+            }
+          }
+          issue_pv(1, v_st, j > 0, par, t);
+          if (leader) {
+            umma_commit(&bars[O_DONE + 1]);
+            umma_commit(&bars[V_EMPTY + v_st]);
+          }
+          if (more) {
+            issue_qk(1, k_st);
+            if (leader) {
+              umma_commit(&bars[S_FULL + 1]);
+              umma_commit(&bars[K_EMPTY + k_st]);
+              if (j + 2 == n_tiles) umma_commit(&bars[Q_EMPTY]);  // last QK of the item: Q may be replaced
+              TC_TRACE(t, 15);
+            }
+            if (++k_st == kKStages) k_st = 0, k_ph ^= 1;
+          }
+          if (++v_st == kVStages) v_st = 0, v_ph ^= 1;
+        }
+        __syncwarp();
+        t_run += (uint32_t)n_tiles;
+        ++n_items;
       }
-      if (++ks1 == kKStages) ks1 = 0, kph1 ^= 1;
-    }
-    __syncwarp();
-  } else if (warp == 9 || warp == 10) {
-    // ============================ TMA warps: 9 = Q and K, 10 = V =========================
-    // Separate warps so a full V ring never holds back the K prefetch (K of tile j+1 is on the
-    // critical path right after PV(j); a K tile takes ~2000 cycles from request to arrival).
-    const bool is_k = warp == 9;
-    if (lane == 0) {
-      if (is_k) {
-        tma_prefetch_desc(&q_map);
-        tma_prefetch_desc(&k_map);
-        mbar_arrive_expect_tx(&bars[Q_FULL], 2 * kTileBytes);
-      } else {
-        tma_prefetch_desc(&v_map);
+    } else {
+      Item it;
+      while (next_item(it)) {
+        B200ATTN_ITEM_VARS
+        // ============================ TMA warps: 9 = Q and K, 10 = V =========================
+        // Separate warps so a full V ring never holds back the K prefetch (K of tile j+1 is on the
+        // critical path right after PV(j); a K tile takes ~2000 cycles from request to arrival).
+        const bool is_k = warp == 9;
+        if (is_k) {
+          // Q: the previous item's QK MMAs must be done with the buffer
+          mbar_wait(&bars[Q_EMPTY], (n_items & 1) ^ 1);
+          if (lane == 0) mbar_arrive_expect_tx(&bars[Q_FULL], 2 * kTileBytes);
+          __syncwarp();
+          if (lane < 4) {
+            const int w = lane >> 1, dc = lane & 1;
+            tma_load_4d(sQ + w * kTileBytes + dc * kSubtileBytes, &q_map, &bars[Q_FULL], 0, dc, kvh * g,
+                        it.q_start + it.qpos0 + w * P.block_q);
+          }
+        }
+        const int bs = a.block_size;
+        const int boxes_per_tile = kBN / P.box_slots;
+        const uint32_t box_bytes = (uint32_t)P.box_slots * 128;
+        const int32_t* bt = a.block_tables + (int64_t)it.b * a.bt_stride0;
+        const int my_box = lane >> 1, my_dc = lane & 1;
+        // page id of this lane's box, fetched one tile ahead of its use
+        auto lookup = [&](int j) {
+          const int tok = (tile0 + j) * kBN + my_box * P.box_slots;
+          return (j < n_tiles && my_box < boxes_per_tile && tok < it.kv_limit) ? bt[tok / bs] : 0;
+        };
+        const int nst = is_k ? kKStages : kVStages;
+        const int full0 = is_k ? K_FULL : V_FULL, empty0 = is_k ? K_EMPTY : V_EMPTY;
+        uint8_t* ring = is_k ? sK : sV;
+        const CUtensorMap* map = is_k ? &k_map : &v_map;
+        int& st = is_k ? k_st : v_st;
+        uint32_t& ph = is_k ? k_ph : v_ph;
+        int page_next = lookup(0);
+        int last_st = 0;
+        uint32_t last_ph = 0;
+        for (int j = 0; j < n_tiles; ++j) {
+          const int n0 = (tile0 + j) * kBN;
+          const int nbox = min(boxes_per_tile, (it.kv_limit - n0 + P.box_slots - 1) / P.box_slots);
+          const bool active = my_box < nbox;
+          const int page = page_next;
+          page_next = lookup(j + 1);
+          const int slot0 = (n0 + my_box * P.box_slots) % bs;
+          const uint32_t dst_off = (uint32_t)(st * kTileBytes + my_dc * kSubtileBytes) + (uint32_t)my_box * box_bytes;
+          mbar_wait(&bars[empty0 + st], ph ^ 1);
+          if (lane == 0) TC_TRACE(t_run + j, is_k ? 19 : 20);
+          if (lane == 0) mbar_arrive_expect_tx(&bars[full0 + st], (uint32_t)nbox * 2 * box_bytes);
+          __syncwarp();
+          if (active) tma_load_5d_nohint(ring + dst_off, map, &bars[full0 + st], 0, slot0, my_dc, kvh, page);
+          last_st = st, last_ph = ph;
+          if (++st == nst) st = 0, ph ^= 1;
+        }
+        // ---- V tail fix-up -------------------------------------------------------------------
+        // Rows of the last tile beyond the visible keys are either unwritten cache slots or
+        // shared memory no copy touched; P is 0 there, but 0 x NaN would poison O.  The last
+        // tile's copy was issued just above, so its V_FULL phase is the one in flight.
+        if (!is_k && need_fix) {
+          mbar_wait(&bars[V_FULL + last_st], last_ph);
+          uint8_t* vt = sV + last_st * kTileBytes;
+          const int n16 = (kBN - last_valid) * 16;  // 16-byte pieces: 2 chunks x 8 per row
+          for (int idx = lane; idx < n16; idx += 32) {
+            const int r = last_valid + (idx >> 4), dc = (idx >> 3) & 1, c = idx & 7;
+            *reinterpret_cast<int4*>(vt + dc * kSubtileBytes + r * 128 + c * 16) = make_int4(0, 0, 0, 0);
+          }
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&bars[V_FIX]);
+        }
+        t_run += (uint32_t)n_tiles;
+        ++n_items;
       }
-    }
-    __syncwarp();
-    if (is_k && lane < 4) {
-      const int w = lane >> 1, dc = lane & 1;
-      tma_load_4d(sQ + w * kTileBytes + dc * kSubtileBytes, &q_map, &bars[Q_FULL], 0, dc, kvh * g, q_start + qpos0 + w * P.block_q);
-    }
-    const int bs = a.block_size;
-    const int boxes_per_tile = kBN / P.box_slots;
-    const uint32_t box_bytes = (uint32_t)P.box_slots * 128;
-    const int32_t* bt = a.block_tables + (int64_t)b * a.bt_stride0;
-    const int my_box = lane >> 1, my_dc = lane & 1;
-    // page id of this lane's box, fetched one tile ahead of its use
-    auto lookup = [&](int j) {
-      const int tok = (tile0 + j) * kBN + my_box * P.box_slots;
-      return (j < n_tiles && my_box < boxes_per_tile && tok < kv_limit) ? bt[tok / bs] : 0;
-    };
-    const int nst = is_k ? kKStages : kVStages;
-    const int full0 = is_k ? K_FULL : V_FULL, empty0 = is_k ? K_EMPTY : V_EMPTY;
-    uint8_t* ring = is_k ? sK : sV;
-    const CUtensorMap* map = is_k ? &k_map : &v_map;
-    int page_next = lookup(0);
-    int st = 0;
-    uint32_t ph = 0;
-    for (int j = 0; j < n_tiles; ++j) {
-      const int n0 = (tile0 + j) * kBN;
-      const int nbox = min(boxes_per_tile, (kv_limit - n0 + P.box_slots - 1) / P.box_slots);
-      const bool active = my_box < nbox;
-      const int page = page_next;
-      page_next = lookup(j + 1);
-      const int slot0 = (n0 + my_box * P.box_slots) % bs;
-      const uint32_t dst_off = (uint32_t)(st * kTileBytes + my_dc * kSubtileBytes) + (uint32_t)my_box * box_bytes;
-      mbar_wait(&bars[empty0 + st], ph ^ 1);
-      if (lane == 0) TC_TRACE(j, is_k ? 19 : 20);
-      if (lane == 0) mbar_arrive_expect_tx(&bars[full0 + st], (uint32_t)nbox * 2 * box_bytes);
-      __syncwarp();
-      if (active) tma_load_5d_nohint(ring + dst_off, map, &bars[full0 + st], 0, slot0, my_dc, kvh, page);
-      if (++st == nst) st = 0, ph ^= 1;
-    }
-    // ---- V tail fix-up -------------------------------------------------------------------
-    // Rows of the last tile beyond the visible keys are either unwritten cache slots or
-    // shared memory no copy touched; P is 0 there, but 0 x NaN would poison O.  The last
-    // tile's copy was issued just above, so its V_FULL phase is the one in flight.
-    if (!is_k && need_fix) {
-      const int vst = last_tile % kVStages;
-      mbar_wait(&bars[V_FULL + vst], (uint32_t)((last_tile / kVStages) & 1));
-      uint8_t* vt = sV + vst * kTileBytes;
-      const int n16 = (kBN - last_valid) * 16;  // 16-byte pieces: 2 chunks x 8 per row
-      for (int idx = lane; idx < n16; idx += 32) {
-        const int r = last_valid + (idx >> 4), dc = (idx >> 3) & 1, c = idx & 7;
-        *reinterpret_cast<int4*>(vt + dc * kSubtileBytes + r * 128 + c * 16) = make_int4(0, 0, 0, 0);
-      }
-      fence_proxy_async();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&bars[V_FIX]);
     }
   }
+#undef B200ATTN_ITEM_VARS
 
   // ---- teardown ---------------------------------------------------------------------------
   tc_fence_before();
   __syncthreads();
 #ifdef B200ATTN_TC_TRACE
-  if (threadIdx.x == 0) TC_MARK(7);
   if (threadIdx.x == 0) {
     const int cta = blockIdx.y * gridDim.x + blockIdx.x;
     if (cta < 4096) {
       unsigned smid;
       asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
-      g_tc_cta[cta * 4 + 0] = smid, g_tc_cta[cta * 4 + 1] = tc_t0, g_tc_cta[cta * 4 + 2] = tc_globaltimer(), g_tc_cta[cta * 4 + 3] = n_tiles;
+      g_tc_cta[cta * 4 + 0] = smid, g_tc_cta[cta * 4 + 1] = tc_t0, g_tc_cta[cta * 4 + 2] = tc_globaltimer(), g_tc_cta[cta * 4 + 3] = tc_tiles;
     }
   }
 #endif
@@ -746,10 +839,9 @@ int launch_attn_prefill_tc(const b200attn_attention_params& a, cudaStream_t stre
   const bool bf16 = a.q_dtype == B200ATTN_BF16;
   // fraction of the exponentials taken off the MUFU (tuning().reserved bits 4..7; 0 = default)
   using Kern = void (*)(const TcParams, const CUtensorMap, const CUtensorMap, const CUtensorMap);
-#define TCV(B) {attn_prefill_tc_kernel<B, 0, 1, 0>, attn_prefill_tc_kernel<B, 0, 1, 0>, attn_prefill_tc_kernel<B, 0, 1, 2>, \
-                attn_prefill_tc_kernel<B, 0, 1, 3>, attn_prefill_tc_kernel<B, 1, 4, 2>, attn_prefill_tc_kernel<B, 1, 4, 3>, \
-                attn_prefill_tc_kernel<B, 1, 3, 2>, attn_prefill_tc_kernel<B, 1, 2, 2>, attn_prefill_tc_kernel<B, 1, 3, 3>}
-  constexpr int kNumVariants = 9;
+#define TCV(B) {attn_prefill_tc_kernel<B, 0, 1>, attn_prefill_tc_kernel<B, 0, 1>, attn_prefill_tc_kernel<B, 1, 4>, \
+                attn_prefill_tc_kernel<B, 1, 3>, attn_prefill_tc_kernel<B, 1, 2>}
+  constexpr int kNumVariants = 5;
   static const Kern kVariants[2][kNumVariants] = {TCV(false), TCV(true)};
 #undef TCV
   int variant = (tuning().reserved >> 4) & 15;
@@ -765,7 +857,7 @@ int launch_attn_prefill_tc(const b200attn_attention_params& a, cudaStream_t stre
     attr_set[bf16 ? 1 : 0][variant] = true;
   }
   const int BQ = 2 * P.block_q;
-  const dim3 grid((unsigned)(a.num_tokens / BQ + a.num_seqs), (unsigned)a.num_kv_heads);
+  const dim3 grid((unsigned)a.num_kv_heads, (unsigned)(a.num_tokens / BQ + a.num_seqs));
   kern<<<grid, kThreads, kSmemBytes, stream>>>(P, qmap, kmap, vmap);
   note_launch("attn_prefill_tc");
   return check_launch("attn_prefill_tc");
