@@ -358,7 +358,7 @@ def run_ours(args):
                     "api": "B200AttentionImpl.do_kv_cache_update + .forward (pinned host q/k/v/metadata in, output out)"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": round(achieved, 2), "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                         "frac": round(achieved / peaks["hbm_gbs"], 4), "traffic": args.ncu_traffic,
+                         "frac": round(achieved / peaks["hbm_gbs"], 4), "traffic": args.ncu_traffic if args.ncu_traffic is not None else (committed_ncu_traffic() if args.workload == "c2" else None),
                          "kernel": "attn_decode_kernel (split-KV, merge of partials fused in)", "peak_source": peaks["source"],
                          "frac_of_nominal_8TBs": round(achieved / 8000.0, 4), "algorithmic_bytes_per_launch": dec_bytes,
                          "avg_launch_ms": round(att_mean_ms, 5)},
@@ -473,6 +473,16 @@ def run_reference_arm(args):
         "e2e": {"value": round(v, 4), "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
+
+
+def committed_ncu_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the decode kernel on
+    this workload, from the committed `ncu --set full` capture (profiles/ncu_traffic.json)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            return int(json.load(f)["attn_decode_kernel_c2"]["dram_bytes_per_launch"])
+    except (OSError, KeyError, ValueError):
+        return None
 
 
 def main():

@@ -1,0 +1,61 @@
+"""The reference Triton kernels, compiled natively on the GPU box (test/bench checker only).
+
+`/root/reference` does not exist on the GPU box, but the vLLM installed in the
+image ships the upstream copy of the same kernel the reference plugin carries
+(`vllm/v1/attention/ops/triton_unified_attention.py` — the reference file
+ibm-triton-lib/ibm_triton_lib/kernels/triton_unified_attention.py:275-836 was
+upstreamed from it; the 2D/3D split, tile loop, softcap/ALiBi/window handling and
+`reduce_segments` are the same code).  BASELINE.json asks for bf16/FP8 parity
+"with the reference Triton kernels": this is them, run on the same tensors.
+
+Never imported by the product; `scripts/kbench.py --impl triton` uses it to time
+the reference kernels beside ours.
+"""
+from __future__ import annotations
+
+import torch
+
+
+def available() -> str | None:
+    """None if the Triton reference can run here, else the reason."""
+    if not torch.cuda.is_available():
+        return "no GPU"
+    try:
+        from vllm.v1.attention.ops.triton_unified_attention import unified_attention  # noqa: F401
+    except Exception as e:  # pragma: no cover - depends on the image
+        return f"vllm triton_unified_attention not importable: {type(e).__name__}: {e}"
+    return None
+
+
+class TritonReference:
+    """Holds the 3D-path scratch tensors the way vLLM's builder allocates them
+    (site-packages/vllm/v1/attention/backends/triton_attn.py:168-201)."""
+
+    NUM_SEGMENTS = 16
+
+    def __init__(self, max_seqs: int, num_q_heads: int, head_size: int, device="cuda"):
+        pad = 1 << (head_size - 1).bit_length()
+        self.max_seqs = max_seqs
+        self.segm_output = torch.empty(max_seqs, num_q_heads, self.NUM_SEGMENTS, pad, dtype=torch.float32, device=device)
+        self.segm_max = torch.empty(max_seqs, num_q_heads, self.NUM_SEGMENTS, dtype=torch.float32, device=device)
+        self.segm_expsum = torch.empty_like(self.segm_max)
+
+    def __call__(self, q, k_cache, v_cache, out, cu_seqlens_q, max_seqlen_q, seq_lens, max_seqlen_k, scale,
+                 block_table, window=0, softcap=0.0, alibi_slopes=None, k_scale=None, v_scale=None, use_3d=True):
+        from vllm.v1.attention.ops.triton_unified_attention import unified_attention
+
+        dev = q.device
+        one = torch.ones(1, dtype=torch.float32, device=dev)
+        kw = {}
+        if use_3d and max_seqlen_q == 1 and seq_lens.shape[0] <= self.max_seqs:
+            kw = dict(seq_threshold_3D=self.max_seqs, num_par_softmax_segments=self.NUM_SEGMENTS,
+                      softmax_segm_output=self.segm_output, softmax_segm_max=self.segm_max,
+                      softmax_segm_expsum=self.segm_expsum)
+        unified_attention(
+            q=q, k=k_cache, v=v_cache, out=out, cu_seqlens_q=cu_seqlens_q, max_seqlen_q=max_seqlen_q,
+            seqused_k=seq_lens, max_seqlen_k=max_seqlen_k, softmax_scale=scale, causal=True,
+            window_size=(window - 1, 0) if window > 0 else (-1, -1), block_table=block_table, softcap=softcap,
+            q_descale=None, k_descale=one if k_scale is None else k_scale, v_descale=one if v_scale is None else v_scale,
+            alibi_slopes=alibi_slopes, **kw,
+        )
+        return out
