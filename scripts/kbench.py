@@ -82,6 +82,21 @@ def time_fn(fn, min_ms=60.0, warmup=5, flush=None):
     return tot / n, n
 
 
+def triton_reference():
+    """tests/triton_reference.py: the reference Triton kernels as shipped by the installed vLLM."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import triton_reference as tr
+
+    why = tr.available()
+    if why:
+        raise SystemExit(f"--impl triton unavailable: {why}")
+    return tr
+
+
+def kernel_name(args):
+    return "triton kernel_unified_attention (vLLM %s)" % __import__("vllm").__version__ if args.impl == "triton" else _cabi.last_kernel()
+
+
 def make_kv(NB, bs, hkv, D, fp8, device, g, layout="planes"):
     shape = (2, NB, bs, hkv, D) if layout == "planes" else (NB, 2, bs, hkv, D)
     dt = torch.uint8 if fp8 else torch.bfloat16
@@ -145,6 +160,11 @@ def decode_case(args, device):
                               max_seqlen_k=max(lens), softmax_scale=D ** -0.5, causal=True, window_size=(-1, -1),
                               block_table=bt, softcap=0, q_descale=None, k_descale=sc, v_descale=sc, workspace=ws,
                               force_selection=args.force)
+    if args.impl == "triton":
+        tri = triton_reference().TritonReference(B, hq, D, device)
+
+        def fn():  # noqa: F811 - the reference kernels on the same tensors
+            tri(q, kc, vc, out, cu, 1, sl, max(lens), D ** -0.5, bt, k_scale=sc, v_scale=sc, use_3d=args.force != 2)
     return fn, nbytes, dict(B=B, ctx=ctx, hq=hq, hkv=hkv, D=D, bs=bs, fp8=fp8, workload=args.workload, layout=args.layout)
 
 
@@ -157,7 +177,8 @@ def run_decode(args, device):
     gbs = nbytes / ms / 1e6
     print(json.dumps(dict(kind="decode", **cfg, hpc=args.hpc, stages=args.stages, split=args.split, ctas=args.ctas,
                           ms=round(ms, 5), gbs=round(gbs, 1), frac_measured=round(gbs / hbm, 4),
-                          frac_8tbs=round(gbs / 8000, 4), iters=n, kernel=_cabi.last_kernel(), flush=bool(args.flush))),
+                          frac_8tbs=round(gbs / 8000, 4), iters=n, kernel=kernel_name(args), flush=bool(args.flush),
+                          impl=args.impl)),
           flush=True)
     _cabi.set_tuning(0, 0, 0, 0)
 
@@ -221,6 +242,11 @@ def prefill_case(args, device):
                               max_seqlen_k=max(kv_lens), softmax_scale=D ** -0.5, causal=True, window_size=(-1, -1),
                               block_table=bt, softcap=0, q_descale=None, k_descale=sc, v_descale=sc, workspace=ws,
                               force_selection=args.force)
+    if args.impl == "triton":
+        tri = triton_reference().TritonReference(len(lens), hq, D, device)
+
+        def fn():  # noqa: F811
+            tri(q, kc, vc, out, cu, max(q_lens), sl, max(kv_lens), D ** -0.5, bt, k_scale=sc, v_scale=sc)
     return fn, flops, dict(shape=args.shape, T=T, seqs=len(lens), hq=hq, hkv=hkv, D=D, bs=bs, fp8=bool(args.fp8))
 
 
@@ -234,7 +260,7 @@ def run_prefill(args, device):
     tfs = flops / ms / 1e9
     print(json.dumps(dict(kind="prefill", **cfg, force=args.force, ms=round(ms, 5), tflops=round(tfs, 1),
                           frac_measured=round(tfs / tf, 4), tokens_per_s=round(cfg["T"] / ms * 1e3, 1), iters=n,
-                          kernel=_cabi.last_kernel(), clock=LAST_CLOCK)), flush=True)
+                          kernel=kernel_name(args), clock=LAST_CLOCK, impl=args.impl)), flush=True)
 
 
 def run_cache(args, device):
@@ -278,6 +304,8 @@ def main():
     ap.add_argument("--flush", action="store_true")
     ap.add_argument("--layout", default="planes", choices=["planes", "interleaved"])
     ap.add_argument("--force", type=int, default=None)
+    ap.add_argument("--impl", default="ours", choices=["ours", "triton"],
+                    help="triton = time the reference Triton kernels (vLLM's copy) on the same tensors")
     ap.add_argument("--tune", type=int, default=0, help="raw b200attn_set_tuning `reserved` word (kernel variant bits)")
     args = ap.parse_args()
     device = torch.device("cuda", 0)

@@ -25,6 +25,8 @@ def test_entry_points_resolve():
 
     assert AttentionBackendEnum.CUSTOM.get_path() == BACKEND_PATH
     assert AttentionBackendEnum.CUSTOM.get_class() is B200AttentionBackend
+    # Attention.__init__ maps the backend back to its enum member by name (attention.py:386)
+    assert AttentionBackendEnum[B200AttentionBackend.get_name()] is AttentionBackendEnum.CUSTOM
 
 
 def test_backend_class_surface():

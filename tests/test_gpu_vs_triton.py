@@ -60,7 +60,7 @@ DECODE = [
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
 def test_decode_matches_triton_3d_kernel(lens, Hq, Hkv, D, bs, dtype):
     ours, ref, kern = _both([(1, n) for n in lens], Hq, Hkv, D, bs, dtype=dtype, seed=3)
-    assert kern == "attn_decode_split_kv"
+    assert kern.startswith("attn_decode_split_kv")
     assert_close(ours, ref, atol=BF16_ATOL, rtol=BF16_RTOL, what="decode vs triton 3D")
 
 
@@ -68,7 +68,7 @@ def test_decode_matches_triton_3d_kernel(lens, Hq, Hkv, D, bs, dtype):
 def test_fp8_kv_decode_matches_triton(k_scale, v_scale):
     ours, ref, kern = _both([(1, n) for n in [300, 4096, 129, 2048]], 64, 8, 128, 16, fp8=True, k_scale=k_scale,
                             v_scale=v_scale, seed=5)
-    assert kern == "attn_decode_split_kv"
+    assert kern.startswith("attn_decode_split_kv")
     assert_close(ours, ref, atol=FP8_ATOL, rtol=BF16_RTOL, what="fp8 decode vs triton")
 
 

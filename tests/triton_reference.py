@@ -44,7 +44,12 @@ class TritonReference:
                  block_table, window=0, softcap=0.0, alibi_slopes=None, k_scale=None, v_scale=None, use_3d=True):
         from vllm.v1.attention.ops.triton_unified_attention import unified_attention
 
+        from vllm.v1.kv_cache_interface import KVQuantMode
+
         dev = q.device
+        # fp8 caches: per-tensor dequant `fp8 -> f32 * scale -> q dtype` (upstream _cast_kv_tile; the
+        # reference file does the same at triton_unified_attention.py:434-455 when Q is not fp8)
+        mode = KVQuantMode.FP8_PER_TENSOR if k_cache.dtype == torch.float8_e4m3fn else KVQuantMode.NONE
         one = torch.ones(1, dtype=torch.float32, device=dev)
         kw = {}
         if use_3d and max_seqlen_q == 1 and seq_lens.shape[0] <= self.max_seqs:
@@ -56,6 +61,6 @@ class TritonReference:
             seqused_k=seq_lens, max_seqlen_k=max_seqlen_k, softmax_scale=scale, causal=True,
             window_size=(window - 1, 0) if window > 0 else (-1, -1), block_table=block_table, softcap=softcap,
             q_descale=None, k_descale=one if k_scale is None else k_scale, v_descale=one if v_scale is None else v_scale,
-            alibi_slopes=alibi_slopes, **kw,
+            alibi_slopes=alibi_slopes, kv_quant_mode=mode, **kw,
         )
         return out

@@ -34,7 +34,10 @@ from vllm.v1.attention.backend import (
 
 from .. import ops
 
-BACKEND_NAME = "B200_ATTN"
+# vLLM resolves `AttentionBackendEnum[backend.get_name()]` when it builds each Attention layer
+# (site-packages/vllm/model_executor/layers/attention/attention.py:386), so an out-of-tree
+# backend has to carry the name of the enum member it is registered under.
+BACKEND_NAME = "CUSTOM"
 BACKEND_PATH = "vllm_triton_backend_b200.backend.attn.B200AttentionBackend"
 
 

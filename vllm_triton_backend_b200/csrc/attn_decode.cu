@@ -12,7 +12,11 @@
 //    tiled map over the strided [NB, bs, Hkv, D] cache view, 128-byte swizzle)
 //    into a multi-stage shared-memory ring; one producer warp issues the copies
 //    from the block table, 8 (4 for D=256) consumer warps each own a 16-token x
-//    one-kv-head tile of every stage.
+//    one-kv-head tile of every stage.  When a page holds less than 4 KB per copy
+//    (one kv head per GPU under tensor parallelism, FP8 or D=64) the copy
+//    engine's fixed cost per box shows, so four producer warps fill the same
+//    swizzled ring with 16-byte cp.async instead (completion through
+//    cp.async.mbarrier.arrive on the same full/empty barriers).
 //  * Tokens sit on the MMA M axis, the GQA group's query heads on N (=8), so a
 //    group of 4..8 heads costs one m16n8k16 per 16 tokens x 16 dims, K is read by
 //    plain ldmatrix and V by ldmatrix.trans; P^T is produced from the S^T
@@ -34,6 +38,7 @@ namespace b200attn {
 namespace {
 
 constexpr int kMaxStages = 8;
+constexpr int kCpWarps = 4;  // producer warps of the cp.async copy mode
 
 struct DecodeParams {
   b200attn_attention_params a;
@@ -43,7 +48,7 @@ struct DecodeParams {
   int box_slots;   // min(block_size, tps)
   int boxes;       // tps / box_slots
   int stages;
-  int tma_split;   // 0: one TMA op per (page box); 1: one per (page box, head, d-chunk)
+  int tma_split;   // 0: one TMA op per (page box); 1: one per (page box, head, d-chunk); 2: cp.async producers
   int group;       // query heads per kv head
   int only_q1;     // mixed batch: only sequences with exactly one query token are this kernel's
   float* ws_acc;   // [slots][hpc*group][D]
@@ -97,7 +102,7 @@ __device__ __forceinline__ bool cursor_next(const DecodeParams& P, ItemCursor& c
 }
 
 template <int D, bool KV_FP8, bool MMA_BF16, bool Q_BF16, int NT, int NW>
-__global__ void __launch_bounds__((NW + 1) * 32, 1)
+__global__ void __launch_bounds__((NW + kCpWarps) * 32, 1)
 attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_map,
                    const __grid_constant__ CUtensorMap v_map) {
   constexpr int ESZ = KV_FP8 ? 1 : 2;
@@ -178,7 +183,7 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
     }
   } else if (warp == 1 && lane == 0) {
     for (int s = 0; s < P.stages; ++s) {
-      mbar_init(&full_bar[s], 1);
+      mbar_init(&full_bar[s], P.tma_split == 2 ? kCpWarps * 32 : 1);
       mbar_init(&empty_bar[s], NW);
     }
     fence_barrier_init();
@@ -206,6 +211,86 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
 
   const int boxb = P.hpc * NDC * P.box_slots * 128;  // bytes of one TMA box (all heads, all chunks)
 
+  if (warp >= NW && P.tma_split == 2) {
+    // ======================= cp.async producer warps ==========================
+    // 128 threads move one stage (K and V, NW*16 (token, head) rows of NDC 128-byte
+    // chunks each) as 16-byte copies into the layout a 128B-swizzled TMA box would
+    // have: unit u = 16-byte chunk index in box order [box][head][d-chunk][slot][c]
+    // lands at (u >> 3) * 128 + ((c ^ (slot & 7)) << 4).  A box never straddles a
+    // page and holds a multiple of 128 units, so the page of copy `it` is uniform
+    // over the producer threads.
+    constexpr int ITER = NW * NDC;  // copies per thread, per tensor, per full stage
+    const int ptid = threadIdx.x - NW * 32;
+    const uint64_t pol = policy_evict_first();
+    const int upb = P.hpc * NDC * P.box_slots * 8;  // 16-byte units per box (>= 128, power of two)
+    const int ipb_shift = 31 - __clz(upb >> 7);  // log2(copies per thread per box)
+    const int ipb_mask = (upb >> 7) - 1;
+    int goff[ITER];  // byte offset of copy `it` inside its box's page, without the page / first-slot part
+#pragma unroll
+    for (int it = 0; it < ITER; ++it) {
+      const int r = (it * 128 + ptid) & (upb - 1);
+      const int c = r & 7, slot = (r >> 3) % P.box_slots, hd = (r >> 3) / P.box_slots;
+      const int dc = hd % NDC, h = hd / NDC;
+      goff[it] = (int)(((int64_t)slot * P.a.kc_slot_stride + (int64_t)h * P.a.kc_head_stride) * ESZ) + dc * 128 + c * 16;
+    }
+    const uint32_t sm_thread = (uint32_t)((ptid >> 3) * 128 + (((ptid & 7) ^ ((ptid >> 3) & 7)) << 4));
+    const char* kbase = static_cast<const char*>(P.a.k_cache);
+    const char* vbase = static_cast<const char*>(P.a.v_cache);
+    const int pages_shift = 31 - __clz(P.a.block_size);
+    auto load_pages = [&](const ItemCursor& c, int (&pg)[8]) {
+      const int tok0 = c.step * P.tps;
+      const int32_t* bt = P.a.block_tables + (int64_t)c.b * P.a.bt_stride0;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int tok = tok0 + i * P.box_slots;
+        pg[i] = (i < P.boxes && tok < c.seq_len) ? __ldg(bt + (tok >> pages_shift)) : 0;
+      }
+    };
+    int pg[8], pg_n[8];
+    load_pages(cur, pg);
+    int stage = 0;
+    uint32_t phase = 0;
+    while (true) {
+      const int tok0 = cur.step * P.tps;
+      const int ntok = min(P.tps, cur.seq_len - tok0);
+      const int nbox = (ntok + P.box_slots - 1) / P.box_slots;
+      const int head0 = cur.hg * P.hpc;
+      const bool last = cur.flat + 1 >= my_end;
+      ItemCursor nxt = cur;
+      if (!last) {
+        cursor_next(P, nxt);
+        load_pages(nxt, pg_n);  // in flight while this step's copies are issued
+      }
+      mbar_wait(&empty_bar[stage], phase ^ 1);
+      const uint32_t kdst = smem_u32(stage_base + (size_t)stage * 2 * KV_STAGE_BYTES) + sm_thread;
+      const uint32_t vdst = kdst + KV_STAGE_BYTES;
+      const int64_t head_off = (int64_t)head0 * P.a.kc_head_stride * ESZ;
+      int64_t box_off = 0;
+#pragma unroll
+      for (int it = 0; it < ITER; ++it) {
+        const int i = it >> ipb_shift;
+        if (i >= nbox) break;
+        if ((it & ipb_mask) == 0) {
+          const int tok = tok0 + i * P.box_slots;
+          const int page = pg[0];
+#pragma unroll
+          for (int j = 0; j < 7; ++j) pg[j] = pg[j + 1];  // consume the page ids in box order
+          box_off = ((int64_t)page * P.a.kc_block_stride + (int64_t)(tok & (P.a.block_size - 1)) * P.a.kc_slot_stride) * ESZ + head_off;
+        }
+        const int64_t off = box_off + goff[it];
+        asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(kdst + it * 2048), "l"(kbase + off), "l"(pol) : "memory");
+        asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(vdst + it * 2048), "l"(vbase + off), "l"(pol) : "memory");
+      }
+      asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(&full_bar[stage])) : "memory");
+      if (++stage == P.stages) stage = 0, phase ^= 1;
+      if (last) break;
+      cur = nxt;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) pg[j] = pg_n[j];
+    }
+    return;
+  }
+  if (warp > NW) return;
   if (warp == NW) {
     // ======================= producer warp ====================================
     // The whole warp issues: lane i looks up the page of box i and launches its
@@ -709,6 +794,15 @@ int launch_variant(const b200attn_attention_params& a, DecodeParams& P, cudaStre
   P.box_slots = a.block_size < P.tps ? a.block_size : P.tps;
   P.boxes = P.tps / P.box_slots;
   P.tma_split = tn.reserved & 1;
+  {
+    // cp.async producers when a box is too small for the copy engine (see the header comment);
+    // needs K and V to share strides.  tuning().reserved bit 1 forces it, bit 2 forbids it.
+    const bool same = a.kc_block_stride == a.vc_block_stride && a.kc_slot_stride == a.vc_slot_stride &&
+                      a.kc_head_stride == a.vc_head_stride;
+    const int box_bytes = P.hpc * NDC * P.box_slots * 128;
+    const bool want = (tn.reserved & 2) || (box_bytes < 4096 && !(tn.reserved & 4));
+    if (same && want && P.boxes <= 8) P.tma_split = 2;
+  }
   const int fixed = NW * 8 * D * 4 + NW * 8 * 2 * 4 + 2 * kMaxStages * 8 + 64 + 1024 /*alignment slack*/;
   int stages = (dev.max_smem_optin - fixed) / (2 * KV_STAGE_BYTES);
   if (stages > kMaxStages) stages = kMaxStages;
@@ -746,8 +840,8 @@ int launch_variant(const b200attn_attention_params& a, DecodeParams& P, cudaStre
     }
     attr_set = true;
   }
-  kern<<<(unsigned)grid, (NW + 1) * 32, smem, stream>>>(P, kmap, vmap);
-  note_launch("attn_decode_split_kv");
+  kern<<<(unsigned)grid, (NW + (P.tma_split == 2 ? kCpWarps : 1)) * 32, smem, stream>>>(P, kmap, vmap);
+  note_launch(P.tma_split == 2 ? "attn_decode_split_kv_cpasync" : "attn_decode_split_kv");
   return check_launch("attn_decode");
 }
 
