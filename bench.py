@@ -278,32 +278,26 @@ def run_ours(args):
     att_ms = [a.elapsed_time(b) for a, b in att_ev]
 
     # ---- end to end through the plugin with HOST buffers (e2e) --------------------
-    h_q = st["q"].cpu().pin_memory()
-    h_k = st["k_new"].cpu().pin_memory()
-    h_v = st["v_new"].cpu().pin_memory()
-    h_slots = st["slot_mapping"].cpu().pin_memory()
-    h_bt = st["block_table"].cpu().pin_memory()
-    h_sl = st["seq_lens"].cpu().pin_memory()
-    h_cu = st["cu"].cpu().pin_memory()
+    # The step's host inputs live in one pinned arena (vllm_triton_backend_b200.staging) and go
+    # to the device with a single copy; the output comes back with one copy.
+    from vllm_triton_backend_b200.staging import StepStaging
+
+    names = {"q": st["q"], "k": st["k_new"], "v": st["v_new"], "slots": st["slot_mapping"], "bt": st["block_table"],
+             "sl": st["seq_lens"], "cu": st["cu"]}
+    stg = StepStaging([(n, tuple(t.shape), t.dtype) for n, t in names.items()], device)
+    for n, t in names.items():
+        stg.host[n].copy_(t.cpu())
     h_out = torch.empty(B, hq, D, dtype=torch.bfloat16).pin_memory()
-    d_q, d_k, d_v = torch.empty_like(st["q"]), torch.empty_like(st["k_new"]), torch.empty_like(st["v_new"])
-    d_slots, d_bt = torch.empty_like(st["slot_mapping"]), torch.empty_like(st["block_table"])
-    d_sl, d_cu = torch.empty_like(st["seq_lens"]), torch.empty_like(st["cu"])
-    h2d = sum(t.numel() * t.element_size() for t in (h_q, h_k, h_v, h_slots, h_bt, h_sl, h_cu))
+    h2d = stg.payload_bytes
     d2h = h_out.numel() * h_out.element_size()
+    d = stg.dev
 
     def e2e_step():
-        d_q.copy_(h_q, non_blocking=True)
-        d_k.copy_(h_k, non_blocking=True)
-        d_v.copy_(h_v, non_blocking=True)
-        d_slots.copy_(h_slots, non_blocking=True)
-        d_bt.copy_(h_bt, non_blocking=True)
-        d_sl.copy_(h_sl, non_blocking=True)
-        d_cu.copy_(h_cu, non_blocking=True)
-        m = B200AttentionMetadata(num_actual_tokens=B, max_query_len=1, query_start_loc=d_cu, max_seq_len=w["ctx"],
-                                  seq_lens=d_sl, block_table=d_bt, slot_mapping=d_slots, workspace=workspace)
-        impl.do_kv_cache_update(layer, d_k, d_v, st["kv"], d_slots)
-        impl.forward(layer, d_q, d_k, d_v, st["kv"], m, output=out)
+        stg.upload()
+        m = B200AttentionMetadata(num_actual_tokens=B, max_query_len=1, query_start_loc=d["cu"], max_seq_len=w["ctx"],
+                                  seq_lens=d["sl"], block_table=d["bt"], slot_mapping=d["slots"], workspace=workspace)
+        impl.do_kv_cache_update(layer, d["k"], d["v"], st["kv"], d["slots"])
+        impl.forward(layer, d["q"], d["k"], d["v"], st["kv"], m, output=out)
         h_out.copy_(out, non_blocking=True)
         stream.synchronize()  # the caller reads the result of every step
 
@@ -355,7 +349,7 @@ def run_ours(args):
             "clocks": clocks,
             "e2e": {"value": round(e2e_gbs, 2), "unit": "GB/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": round(e2e_ms / K, 5),
-                    "api": "B200AttentionImpl.do_kv_cache_update + .forward (pinned host q/k/v/metadata in, output out)"},
+                    "api": "StepStaging.upload (one pinned arena: q/k/v/metadata) + B200AttentionImpl.do_kv_cache_update + .forward + output D2H, sync every step"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": round(achieved, 2), "peak": peaks["hbm_gbs"], "unit": "GB/s",
                          "frac": round(achieved / peaks["hbm_gbs"], 4), "traffic": args.ncu_traffic if args.ncu_traffic is not None else (committed_ncu_traffic() if args.workload == "c2" else None),

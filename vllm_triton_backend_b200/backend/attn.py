@@ -223,6 +223,7 @@ class B200AttentionImpl(AttentionImpl):
             )
         self.attn_type = attn_type
         self.supports_quant_query_input = False
+        self._plans: dict = {}
         if kv_cache_dtype.startswith("fp8") and kv_cache_dtype not in ("fp8", "fp8_e4m3"):
             raise NotImplementedError(f"kv_cache_dtype {kv_cache_dtype!r}: only fp8_e4m3 is implemented")
 
@@ -233,15 +234,34 @@ class B200AttentionImpl(AttentionImpl):
             value_cache = value_cache.view(torch.float8_e4m3fn)
         return key_cache, value_cache
 
+    def _plans_for(self, layer, kv_cache: torch.Tensor, q_dtype: torch.dtype):
+        """(cache-write plan, attention plan) of this layer's cache tensor: the argument
+        lists of the two C calls with everything that does not change from step to step
+        filled in once (ops.AttentionPlan / ops.CacheWritePlan)."""
+        key = (kv_cache.data_ptr(), q_dtype)
+        plans = self._plans.get(key)
+        if plans is None:
+            key_cache, value_cache = self._views(kv_cache)
+            if self._alibi_slopes_host is not None and self.alibi_slopes is None:
+                self.alibi_slopes = self._alibi_slopes_host.to(kv_cache.device)
+            fp8 = self.kv_cache_dtype.startswith("fp8")
+            plans = (
+                ops.CacheWritePlan(key_cache, value_cache, self.kv_cache_dtype, q_dtype, layer._k_scale, layer._v_scale),
+                ops.AttentionPlan(key_cache, value_cache, q_dtype, self.num_heads, self.head_size, self.scale,
+                                  self.sliding_window, self.logits_soft_cap, self.alibi_slopes,
+                                  layer._k_scale if fp8 else None, layer._v_scale if fp8 else None),  # element 0 is read (:438)
+            )
+            if len(self._plans) > 8:  # a layer has one cache tensor; bound the dict if a caller keeps reallocating
+                self._plans.clear()
+            self._plans[key] = plans
+        return plans
+
     def do_kv_cache_update(self, layer, key, value, kv_cache, slot_mapping) -> None:
         """Cache write, split out of forward by vLLM >= 0.11 (reference did it
         inside forward, triton_attn.py:393-405)."""
         if self.kv_sharing_target_layer_name is not None:
             return
-        key_cache, value_cache = self._views(kv_cache)
-        ops.reshape_and_cache_flash(
-            key, value, key_cache, value_cache, slot_mapping, self.kv_cache_dtype, layer._k_scale, layer._v_scale
-        )
+        self._plans_for(layer, kv_cache, key.dtype)[0](key, value, slot_mapping)
 
     def forward(
         self,
@@ -265,19 +285,12 @@ class B200AttentionImpl(AttentionImpl):
         assert attn_metadata.use_cascade is False
 
         n = attn_metadata.num_actual_tokens
-        key_cache, value_cache = self._views(kv_cache)
-        if self._alibi_slopes_host is not None and self.alibi_slopes is None:
-            self.alibi_slopes = self._alibi_slopes_host.to(query.device)
         q = query[:n].view(-1, self.num_heads, self.head_size)
         out = output[:n].view(-1, self.num_heads, self.head_size)
-        ops.unified_attention(
-            q=q, k=key_cache, v=value_cache, out=out,
-            cu_seqlens_q=attn_metadata.query_start_loc, max_seqlen_q=attn_metadata.max_query_len,
-            seqused_k=attn_metadata.seq_lens, max_seqlen_k=attn_metadata.max_seq_len,
-            softmax_scale=self.scale, causal=True, alibi_slopes=self.alibi_slopes,
-            window_size=self.sliding_window, block_table=attn_metadata.block_table,
-            softcap=self.logits_soft_cap, q_descale=None,  # not supported (reference :465)
-            k_descale=layer._k_scale, v_descale=layer._v_scale,  # element 0 is what the kernels read (:438)
-            workspace=attn_metadata.workspace,
+        # reference launcher arguments (triton_attn.py:446-468): causal, q_descale=None (:465),
+        # window/softcap/alibi/scales are fixed per layer and live in the plan
+        self._plans_for(layer, kv_cache, query.dtype)[1](
+            q, out, attn_metadata.query_start_loc, attn_metadata.max_query_len, attn_metadata.seq_lens,
+            attn_metadata.max_seq_len, attn_metadata.block_table, attn_metadata.workspace,
         )
         return output

@@ -242,3 +242,115 @@ def unified_attention(
         softcap, k_descale, v_descale, alibi_slopes, path, workspace,
     )
     _cabi.check(_cabi.load_library().b200attn_unified_attention(ctypes.byref(p), _stream_ptr(q)))
+
+
+# ---------------------------------------------------------------------------------
+# Per-layer plans: the argument marshalling above costs ~20 us of Python per call
+# (every .stride()/.data_ptr() is a C++ round trip).  Inside vLLM the same layer
+# calls with the same cache tensor and head geometry on every step, and in
+# piecewise-CUDA-graph mode the attention op runs eagerly once per layer per step,
+# so the backend keeps the invariant part filled in and only writes the step's
+# pointers and sizes.  Same C entry points, same checks (done once, at plan time).
+# ---------------------------------------------------------------------------------
+class AttentionPlan:
+    """`b200attn_attention_params` pre-filled for one (cache, head geometry, features)."""
+
+    __slots__ = ("p", "_ref", "_fn", "_keep", "_ws_ptr", "num_q_heads", "head_size", "q_dtype")
+
+    def __init__(self, k, v, q_dtype, num_q_heads, head_size, softmax_scale, window_size, softcap, alibi_slopes,
+                 k_descale, v_descale):
+        _require_cuda(k, v, alibi_slopes, k_descale, v_descale)
+        if k.dim() != 4 or v.dim() != 4 or k.stride(3) != 1 or v.stride(3) != 1:
+            raise ValueError("k, v must be [NB, bs, Hkv, D] views with a contiguous innermost dimension")
+        q_dt, kv_dt = _DTYPE.get(q_dtype), _DTYPE.get(k.dtype)
+        if q_dt is None or q_dt == _cabi.FP8_E4M3:
+            raise ValueError(f"unsupported query dtype {q_dtype}")
+        if kv_dt is None or v.dtype != k.dtype:
+            raise ValueError(f"unsupported kv cache dtypes {k.dtype}/{v.dtype}")
+        p = AttentionParams()
+        p.k_cache, p.v_cache = k.data_ptr(), v.data_ptr()
+        p.alibi_slopes = alibi_slopes.data_ptr() if alibi_slopes is not None else None
+        p.k_scale = k_descale.data_ptr() if k_descale is not None else None
+        p.v_scale = v_descale.data_ptr() if v_descale is not None else None
+        p.sinks = None
+        p.softmax_scale = float(softmax_scale)
+        p.softcap = float(softcap or 0.0)
+        p.sliding_window = int(1 + window_size[0]) if window_size is not None else 0
+        p.num_q_heads, p.num_kv_heads, p.head_size, p.block_size = num_q_heads, k.shape[2], head_size, v.shape[1]
+        p.q_dtype, p.kv_dtype, p.path = q_dt, kv_dt, _cabi.PATH_AUTO
+        p.num_blocks = k.shape[0]
+        p.kc_block_stride, p.kc_slot_stride, p.kc_head_stride = k.stride(0), k.stride(1), k.stride(2)
+        p.vc_block_stride, p.vc_slot_stride, p.vc_head_stride = v.stride(0), v.stride(1), v.stride(2)
+        self.p, self._ref = p, ctypes.byref(p)
+        self._fn = _cabi.load_library().b200attn_unified_attention
+        self._keep = (k, v, alibi_slopes, k_descale, v_descale)  # the struct holds raw pointers into these
+        self._ws_ptr = None
+        self.num_q_heads, self.head_size, self.q_dtype = num_q_heads, head_size, q_dtype
+
+    def __call__(self, q, out, cu_seqlens_q, max_seqlen_q, seqused_k, max_seqlen_k, block_table, workspace) -> None:
+        """q/out: [T, Hq, D] views (innermost contiguous); metadata tensors int32 on the device."""
+        if q.dtype != self.q_dtype or out.dtype != self.q_dtype or not q.is_cuda:
+            raise ValueError("query/output dtype or device differs from the plan")
+        p = self.p
+        p.q, p.out = q.data_ptr(), out.data_ptr()
+        qs, os_ = q.stride(), out.stride()
+        if qs[2] != 1 or os_[2] != 1:
+            raise ValueError("innermost dimension of q/out must be contiguous")
+        p.q_stride0, p.q_stride1, p.out_stride0, p.out_stride1 = qs[0], qs[1], os_[0], os_[1]
+        p.num_tokens, p.num_seqs = q.shape[0], seqused_k.shape[0]
+        p.block_tables, p.seq_lens, p.cu_seqlens_q = block_table.data_ptr(), seqused_k.data_ptr(), cu_seqlens_q.data_ptr()
+        p.bt_stride0 = block_table.stride(0)
+        p.max_seqlen_q, p.max_seqlen_k = max_seqlen_q, max_seqlen_k
+        wp = workspace.data_ptr()
+        if wp != self._ws_ptr:
+            p.workspace, p.workspace_bytes, self._ws_ptr = wp, workspace.numel() * workspace.element_size(), wp
+        rc = self._fn(self._ref, torch.cuda.current_stream(q.device).cuda_stream)
+        if rc:
+            _cabi.check(rc)
+
+
+class CacheWritePlan:
+    """`b200attn_reshape_and_cache_flash` with the cache side of the argument list fixed."""
+
+    __slots__ = ("_fn", "_tail", "_head", "_keep", "_src_dtype", "_src_dt")
+
+    def __init__(self, key_cache, value_cache, kv_cache_dtype: str, src_dtype, k_scale, v_scale):
+        _require_cuda(key_cache, value_cache)
+        if key_cache.dim() != 4 or key_cache.stride(3) != 1 or value_cache.stride(3) != 1:
+            raise ValueError("caches must be [NB, bs, Hkv, D] views with a contiguous head_dim")
+        src_dt = _DTYPE.get(src_dtype)
+        if src_dt is None or src_dt == _cabi.FP8_E4M3:
+            raise ValueError(f"unsupported key dtype {src_dtype}")
+        if kv_cache_dtype.startswith("fp8"):
+            if kv_cache_dtype not in ("fp8", "fp8_e4m3"):
+                raise ValueError(f"unsupported kv_cache_dtype {kv_cache_dtype!r} (fp8_e4m3 only)")
+            if key_cache.element_size() != 1:
+                raise ValueError("fp8 kv cache must be a 1-byte tensor")
+            kv_dt = _cabi.FP8_E4M3
+            ks, vs = _scalar_tensor(k_scale, key_cache.device), _scalar_tensor(v_scale, key_cache.device)
+            ks_ptr, vs_ptr = ks.data_ptr(), vs.data_ptr()
+        else:
+            if key_cache.dtype != src_dtype:
+                raise ValueError(f"kv cache dtype {key_cache.dtype} != key dtype {src_dtype} with kv_cache_dtype={kv_cache_dtype!r}")
+            kv_dt, ks, vs, ks_ptr, vs_ptr = src_dt, None, None, None, None
+        _, bs, hkv, d = key_cache.shape
+        self._fn = _cabi.load_library().b200attn_reshape_and_cache_flash
+        self._head = (key_cache.data_ptr(), value_cache.data_ptr())
+        self._tail = (hkv, d, bs)
+        self._keep = (key_cache, value_cache, ks, vs,
+                      (key_cache.stride(0), key_cache.stride(1), key_cache.stride(2),
+                       value_cache.stride(0), value_cache.stride(1), value_cache.stride(2), src_dt, kv_dt, ks_ptr, vs_ptr))
+        self._src_dtype, self._src_dt = src_dtype, src_dt
+
+    def __call__(self, key, value, slot_mapping) -> None:
+        if key.dtype != self._src_dtype or not key.is_cuda or slot_mapping.dtype != torch.int64:
+            raise ValueError("key dtype/device differs from the plan, or slot_mapping is not int64")
+        ks, vs = key.stride(), value.stride()
+        hkv, d, bs = self._tail
+        if ks[2] != 1 or ks[1] != d or vs[2] != 1 or vs[1] != d:
+            raise ValueError("key/value rows must be contiguous in (head, dim)")
+        rc = self._fn(key.data_ptr(), value.data_ptr(), self._head[0], self._head[1], slot_mapping.data_ptr(),
+                      slot_mapping.shape[0], hkv, d, bs, ks[0], vs[0], *self._keep[4],
+                      torch.cuda.current_stream(key.device).cuda_stream)
+        if rc:
+            _cabi.check(rc)

@@ -1,0 +1,54 @@
+"""One pinned host arena + one device arena for a step's inputs, moved with ONE copy.
+
+A caller that holds the step's inputs on the host (q/k/v of the new tokens, block
+table, seq_lens, query_start_loc, slot_mapping) would otherwise issue one
+host-to-device copy per tensor; at decode sizes each copy is a few hundred KB at
+most and the per-copy launch + DMA latency (about 8 us each) costs more than the
+bytes.  `StepStaging` lays all of them out in a single pinned buffer with the same
+layout on the device: fill the host views, call `upload()`, pass the device views
+to `do_kv_cache_update` / `forward`.  This mirrors how vLLM's model runner keeps
+its per-step metadata in persistent pinned buffers
+(site-packages/vllm/v1/worker/gpu_model_runner.py, `_make_buffer`).
+
+Plain PyTorch memory plumbing; no arithmetic happens here.
+"""
+from __future__ import annotations
+
+from typing import Dict, Iterable, Tuple
+
+import torch
+
+_ALIGN = 256  # keeps every view 16-byte aligned for the kernels' vector loads (and TMA-friendly)
+
+
+class StepStaging:
+    def __init__(self, spec: Iterable[Tuple[str, Tuple[int, ...], torch.dtype]], device) -> None:
+        """spec: (name, shape, dtype) of every tensor of a step, in any order."""
+        self.device = torch.device(device)
+        self._layout = []
+        off = 0
+        for name, shape, dtype in spec:
+            n = 1
+            for s in shape:
+                n *= int(s)
+            nbytes = n * torch.empty((), dtype=dtype).element_size()
+            self._layout.append((name, tuple(int(s) for s in shape), dtype, off, nbytes))
+            off = (off + nbytes + _ALIGN - 1) // _ALIGN * _ALIGN
+        self.nbytes = max(off, _ALIGN)
+        pin = self.device.type == "cuda"
+        self._host = torch.empty(self.nbytes, dtype=torch.uint8, pin_memory=pin)
+        self._dev = torch.empty(self.nbytes, dtype=torch.uint8, device=self.device)
+        self.host: Dict[str, torch.Tensor] = {}
+        self.dev: Dict[str, torch.Tensor] = {}
+        for name, shape, dtype, o, nb in self._layout:
+            self.host[name] = self._host[o:o + nb].view(dtype).view(shape)
+            self.dev[name] = self._dev[o:o + nb].view(dtype).view(shape)
+
+    @property
+    def payload_bytes(self) -> int:
+        """Bytes of tensors (without alignment padding)."""
+        return sum(nb for *_, nb in self._layout)
+
+    def upload(self) -> None:
+        """One asynchronous host-to-device copy of the whole arena on the current stream."""
+        self._dev.copy_(self._host, non_blocking=True)
