@@ -280,33 +280,41 @@ def run_ours(args):
     # ---- end to end through the plugin with HOST buffers (e2e) --------------------
     # The step's host inputs live in one pinned arena (vllm_triton_backend_b200.staging) and go
     # to the device with a single copy; the output comes back with one copy.
-    from vllm_triton_backend_b200.staging import StepStaging
+    from vllm_triton_backend_b200.staging import StepPipeline
 
     names = {"q": st["q"], "k": st["k_new"], "v": st["v_new"], "slots": st["slot_mapping"], "bt": st["block_table"],
              "sl": st["seq_lens"], "cu": st["cu"]}
-    stg = StepStaging([(n, tuple(t.shape), t.dtype) for n, t in names.items()], device)
-    for n, t in names.items():
-        stg.host[n].copy_(t.cpu())
-    h_out = torch.empty(B, hq, D, dtype=torch.bfloat16).pin_memory()
-    h2d = stg.payload_bytes
-    d2h = h_out.numel() * h_out.element_size()
-    d = stg.dev
+    depth = 1 if args.e2e_serial else 2
+    pipe = StepPipeline([(n, tuple(t.shape), t.dtype) for n, t in names.items()], (B, hq, D), torch.bfloat16, device,
+                        depth=depth)
+    for slot in pipe.slots:
+        for n, t in names.items():
+            slot.staging.host[n].copy_(t.cpu())
+    h2d = pipe.slots[0].staging.payload_bytes
+    d2h = B * hq * D * 2
 
-    def e2e_step():
-        stg.upload()
+    def compute(d, o):
         m = B200AttentionMetadata(num_actual_tokens=B, max_query_len=1, query_start_loc=d["cu"], max_seq_len=w["ctx"],
                                   seq_lens=d["sl"], block_table=d["bt"], slot_mapping=d["slots"], workspace=workspace)
         impl.do_kv_cache_update(layer, d["k"], d["v"], st["kv"], d["slots"])
-        impl.forward(layer, d["q"], d["k"], d["v"], st["kv"], m, output=out)
-        h_out.copy_(out, non_blocking=True)
-        stream.synchronize()  # the caller reads the result of every step
+        impl.forward(layer, d["q"], d["k"], d["v"], st["kv"], m, output=o)
+
+    checksum = 0.0
+
+    def e2e_step():
+        nonlocal checksum
+        slot = pipe.acquire()  # blocks until the result of the step that last used this slot is on the host
+        checksum += float(slot.host_out[0, 0, 0])  # the caller reads every step's result
+        pipe.run(slot, compute)
 
     for _ in range(max(args.warmup, 3)):
         e2e_step()
+    pipe.drain()
     barrier()
     t0 = time.perf_counter()
     for _ in range(K):
         e2e_step()
+    pipe.drain()
     barrier()
     e2e_s = time.perf_counter() - t0
     clocks = sampler.stop(t_begin, t_end)
@@ -349,7 +357,7 @@ def run_ours(args):
             "clocks": clocks,
             "e2e": {"value": round(e2e_gbs, 2), "unit": "GB/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": round(e2e_ms / K, 5),
-                    "api": "StepStaging.upload (one pinned arena: q/k/v/metadata) + B200AttentionImpl.do_kv_cache_update + .forward + output D2H, sync every step"},
+                    "api": "StepPipeline(depth=%d): one pinned arena per step (q/k/v/metadata) uploaded on a copy stream, B200AttentionImpl.do_kv_cache_update + .forward, result read back on a second copy stream; the host reads every step's result when it reuses the slot" % depth},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": round(achieved, 2), "peak": peaks["hbm_gbs"], "unit": "GB/s",
                          "frac": round(achieved / peaks["hbm_gbs"], 4), "traffic": args.ncu_traffic if args.ncu_traffic is not None else (committed_ncu_traffic() if args.workload == "c2" else None),
@@ -488,6 +496,7 @@ def main():
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e-serial", action="store_true", help="e2e without overlap: upload, compute, read back, sync, every step")
     ap.add_argument("--no-prefill", action="store_true", help="skip the prefill TFLOP/s section")
     ap.add_argument("--ncu-traffic", type=float, default=None,
                     help="dram bytes per launch of the decode kernel from the committed ncu capture (profiles/)")

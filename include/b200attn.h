@@ -164,6 +164,12 @@ B200ATTN_API const char* b200attn_last_kernel(void);
 B200ATTN_API void b200attn_set_tuning(int32_t decode_heads_per_cta, int32_t decode_ctas_per_sm,
                          int32_t decode_stages, int32_t reserved);
 
+/* Debug: when `device_buffer` is not NULL the split-KV decode kernel writes 8 uint64
+ * per CTA (globaltimer at entry, then %clock64 at: entry, partition done, first KV
+ * stage landed, last stage consumed, exit; globaltimer at exit; items finalised).
+ * Process-wide; NULL switches it off.  Used by scripts/kbench.py decode --trace. */
+B200ATTN_API void b200attn_debug_set_decode_trace(void* device_buffer);
+
 #ifdef __cplusplus
 }
 #endif

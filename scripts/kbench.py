@@ -168,10 +168,39 @@ def decode_case(args, device):
     return fn, nbytes, dict(B=B, ctx=ctx, hq=hq, hkv=hkv, D=D, bs=bs, fp8=fp8, workload=args.workload, layout=args.layout)
 
 
+def decode_trace(fn, device):
+    """Per-CTA phase times of one decode launch (b200attn_debug_set_decode_trace)."""
+    lib = _cabi.load_library()
+    nsm = torch.cuda.get_device_properties(device).multi_processor_count
+    buf = torch.zeros(nsm * 8, dtype=torch.int64, device=device)
+    for _ in range(5):
+        fn()
+    torch.cuda.synchronize()
+    lib.b200attn_debug_set_decode_trace(buf.data_ptr())
+    fn()
+    torch.cuda.synchronize()
+    lib.b200attn_debug_set_decode_trace(None)
+    t = buf.cpu().view(nsm, 8).double()
+    t = t[t[:, 0] > 0]
+    span_ns = float(t[:, 6].max() - t[:, 0].min())
+    ghz = float(((t[:, 5] - t[:, 1]) / (t[:, 6] - t[:, 0]).clamp(min=1)).median())  # cycles per ns
+    us = lambda cyc: cyc / ghz / 1e3
+
+    def stat(x):
+        return dict(mean=round(float(x.mean()), 2), min=round(float(x.min()), 2), max=round(float(x.max()), 2))
+    return dict(kind="decode_trace", ctas=int(t.shape[0]), kernel_span_us=round(span_ns / 1e3, 2), sm_ghz=round(ghz, 3),
+                start_skew_us=stat((t[:, 0] - t[:, 0].min()) / 1e3), partition_us=stat(us(t[:, 2] - t[:, 1])),
+                first_data_us=stat(us(t[:, 3] - t[:, 2])), streaming_us=stat(us(t[:, 4] - t[:, 3])),
+                tail_us=stat(us(t[:, 5] - t[:, 4])), cta_total_us=stat((t[:, 6] - t[:, 0]) / 1e3),
+                end_skew_us=stat((t[:, 6].max() - t[:, 6]) / 1e3), items_per_cta=stat(t[:, 7]))
+
+
 def run_decode(args, device):
     hbm, _ = peaks()
     fn, nbytes, cfg = decode_case(args, device)
     _cabi.set_tuning(args.hpc, args.ctas, args.stages, args.split)
+    if args.trace:
+        print(json.dumps(dict(**decode_trace(fn, device), **cfg)), flush=True)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=device) if args.flush else None
     ms, n = time_fn(fn, flush=flush)
     gbs = nbytes / ms / 1e6
@@ -304,6 +333,7 @@ def main():
     ap.add_argument("--flush", action="store_true")
     ap.add_argument("--layout", default="planes", choices=["planes", "interleaved"])
     ap.add_argument("--force", type=int, default=None)
+    ap.add_argument("--trace", action="store_true", help="decode: print per-CTA phase times of one launch first")
     ap.add_argument("--impl", default="ours", choices=["ours", "triton"],
                     help="triton = time the reference Triton kernels (vLLM's copy) on the same tensors")
     ap.add_argument("--tune", type=int, default=0, help="raw b200attn_set_tuning `reserved` word (kernel variant bits)")

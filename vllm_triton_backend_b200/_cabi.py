@@ -33,6 +33,7 @@ EXPORTED_SYMBOLS = [
     "b200attn_reset_launch_count",
     "b200attn_last_kernel",
     "b200attn_set_tuning",
+    "b200attn_debug_set_decode_trace",
 ]
 
 
@@ -92,6 +93,8 @@ def load_library() -> ctypes.CDLL:
     lib.b200attn_last_kernel.restype = c_char_p
     lib.b200attn_set_tuning.restype = None
     lib.b200attn_set_tuning.argtypes = [c_int32] * 4
+    lib.b200attn_debug_set_decode_trace.restype = None
+    lib.b200attn_debug_set_decode_trace.argtypes = [c_void_p]
     _lib = lib
     return lib
 

@@ -12,11 +12,8 @@
 //    tiled map over the strided [NB, bs, Hkv, D] cache view, 128-byte swizzle)
 //    into a multi-stage shared-memory ring; one producer warp issues the copies
 //    from the block table, 8 (4 for D=256) consumer warps each own a 16-token x
-//    one-kv-head tile of every stage.  When a page holds less than 4 KB per copy
-//    (one kv head per GPU under tensor parallelism, FP8 or D=64) the copy
-//    engine's fixed cost per box shows, so four producer warps fill the same
-//    swizzled ring with 16-byte cp.async instead (completion through
-//    cp.async.mbarrier.arrive on the same full/empty barriers).
+//    one-kv-head tile of every stage.  (A cp.async producer variant for pages under
+//    4 KB was measured and dropped: profiles/r01_kbench_cpasync_and_ctx_fit.jsonl.)
 //  * Tokens sit on the MMA M axis, the GQA group's query heads on N (=8), so a
 //    group of 4..8 heads costs one m16n8k16 per 16 tokens x 16 dims, K is read by
 //    plain ldmatrix and V by ldmatrix.trans; P^T is produced from the S^T
@@ -38,23 +35,29 @@ namespace b200attn {
 namespace {
 
 constexpr int kMaxStages = 8;
-constexpr int kCpWarps = 4;  // producer warps of the cp.async copy mode
 
 struct DecodeParams {
   b200attn_attention_params a;
   int hpc;         // kv heads per CTA (divides num_kv_heads and NW)
   int head_groups; // num_kv_heads / hpc
-  int tps;         // tokens per stage-step = NW*16/hpc
+  int tps;         // tokens per stage-step = NW*TT/hpc (TT = tokens of a warp's tile)
   int box_slots;   // min(block_size, tps)
   int boxes;       // tps / box_slots
   int stages;
-  int tma_split;   // 0: one TMA op per (page box); 1: one per (page box, head, d-chunk); 2: cp.async producers
+  int tma_split;   // 0: one TMA op per (page box); 1: one per (page box, head, d-chunk)
   int group;       // query heads per kv head
   int only_q1;     // mixed batch: only sequences with exactly one query token are this kernel's
   float* ws_acc;   // [slots][hpc*group][D]
   float* ws_ml;    // [slots][hpc*group][2]  (max in log2 units, exp-sum)
   int* ws_cnt;     // [items] tickets taken on an item split across CTAs (0 between calls)
+  unsigned long long* trace;  // debug time stamps, 8 per CTA (b200attn_debug_set_decode_trace) or nullptr
 };
+
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 
 __device__ __forceinline__ float ex2(float x) {
   float y;
@@ -101,16 +104,18 @@ __device__ __forceinline__ bool cursor_next(const DecodeParams& P, ItemCursor& c
   return false;
 }
 
-template <int D, bool KV_FP8, bool MMA_BF16, bool Q_BF16, int NT, int NW>
-__global__ void __launch_bounds__((NW + kCpWarps) * 32, 1)
+template <int D, bool KV_FP8, bool MMA_BF16, bool Q_BF16, int NT, int NW, int TT>
+__global__ void __launch_bounds__((NW + 1) * 32, 1)
 attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_map,
                    const __grid_constant__ CUtensorMap v_map) {
   constexpr int ESZ = KV_FP8 ? 1 : 2;
   constexpr int NDC = D * ESZ / 128;      // 128-byte chunks per row
   constexpr int KSTEPS = D / 16;          // k16 steps of S = K Q^T
   constexpr int MTILES = D / 16;          // m16 tiles of O^T = V^T P^T
-  constexpr int TILE_BYTES = 16 * D * ESZ;
+  constexpr int SUB = TT / 16;             // 16-token MMA sub-tiles of a warp's TT-token tile
+  constexpr int TILE_BYTES = TT * D * ESZ;
   constexpr int KV_STAGE_BYTES = NW * TILE_BYTES;  // K (or V) bytes per stage
+  static_assert(TT == 16 || TT == 32, "warp tile is one or two 16-token MMA tiles");
   static_assert(NDC >= 1, "row must be at least 128 bytes");
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -126,17 +131,52 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int gid = lane >> 2, t4 = lane & 3;
 
-  // ---- work partition (warp 0) and barrier init (warp 1) ----------------------
-  if (warp == 0) {
-    // total steps over all sequences
+  unsigned long long* trace = P.trace ? P.trace + (size_t)blockIdx.x * 8 : nullptr;
+  if (trace && threadIdx.x == 0) trace[0] = global_ns(), trace[1] = clock64(), trace[7] = 0;
+
+  // ---- work partition and barrier init ----------------------------------------
+  if (warp == NW && lane == 0) {  // descriptor fetch overlaps the partition
+    tma_prefetch_desc(&k_map);
+    tma_prefetch_desc(&v_map);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < P.stages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], NW);
+    }
+    fence_barrier_init();
+  }
+  int my_begin, my_end, per_cta;
+  ItemCursor cur;
+  int tq_first = 0;  // first query-token index of cur.b
+  constexpr int kFastSeqs = 256;
+  if (P.a.num_seqs <= kFastSeqs) {
+    // Every warp derives the partition on its own from one round of independent
+    // loads (lane l holds sequences l, l+32, ...): no shared-memory hand-off and a
+    // single global-memory latency before the first page can be requested.
+    constexpr int R = kFastSeqs / 32;
+    int n_r[R], first_r[R], sl_r[R], tq_r[R];
     int total = 0;
-    for (int b0 = 0; b0 < P.a.num_seqs; b0 += 32) {
-      int b = b0 + lane, n = 0;
+    unsigned zero_rows = 0;  // bit r: sequence lane+32r has no visible key and one query token
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const int b = r * 32 + lane;
+      n_r[r] = 0, first_r[r] = 0, sl_r[r] = 0, tq_r[r] = 0;
       if (b < P.a.num_seqs) {
-        int sl, first;
-        seq_steps(P, b, sl, first, n);
+        const int sl = P.a.seq_lens[b];
+        int c0 = b, c1 = b + 1;
+        if (P.a.cu_seqlens_q) c0 = P.a.cu_seqlens_q[b], c1 = P.a.cu_seqlens_q[b + 1];
+        const int ql = c1 - c0;
+        sl_r[r] = sl, tq_r[r] = c0;
+        if (sl > 0 && ql > 0 && !(P.only_q1 && ql != 1)) {
+          int lo_tok = 0;
+          if (P.a.sliding_window > 0) lo_tok = max(0, sl - P.a.sliding_window);
+          first_r[r] = lo_tok / P.tps;
+          n_r[r] = (sl + P.tps - 1) / P.tps - first_r[r];
+        }
+        if (sl <= 0 && ql == 1 && b % gridDim.x == blockIdx.x) zero_rows |= 1u << r;
+        total += n_r[r];
       }
-      total += n;
     }
     total = __reduce_add_sync(0xffffffffu, total);
     const long long total_flat = (long long)total * P.head_groups;
@@ -145,160 +185,147 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
     long long end = begin + per;
     if (begin > total_flat) begin = total_flat;
     if (end > total_flat) end = total_flat;
-    // locate `begin`: largest b with HG * prefix(b) <= begin and n_b > 0 covering it
-    int fb = -1, fhg = 0, fstep = 0;
+    int fb = -1, fhg = 0, fstep = 0, fsl = 0, ffirst = 0, fn = 0;
     if (begin < end) {
-      long long run = 0;  // HG * sum of n over sequences before the chunk
-      for (int b0 = 0; b0 < P.a.num_seqs && fb < 0; b0 += 32) {
-        int b = b0 + lane, n = 0, first = 0, sl;
-        if (b < P.a.num_seqs) seq_steps(P, b, sl, first, n);
-        int incl = n;
+      long long run = 0;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-          int v = __shfl_up_sync(0xffffffffu, incl, o);
-          if (lane >= o) incl += v;
+      for (int r = 0; r < R; ++r) {
+        if (r * 32 < P.a.num_seqs && fb < 0) {  // warp-uniform
+          int incl = n_r[r];
+#pragma unroll
+          for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+          }
+          const long long lo = run + (long long)(incl - n_r[r]) * P.head_groups;
+          const long long hi = run + (long long)incl * P.head_groups;
+          const unsigned hit = __ballot_sync(0xffffffffu, n_r[r] > 0 && begin >= lo && begin < hi);
+          if (hit) {
+            const int src = __ffs(hit) - 1;
+            const long long lo_s = __shfl_sync(0xffffffffu, lo, src);
+            fn = __shfl_sync(0xffffffffu, n_r[r], src);
+            ffirst = __shfl_sync(0xffffffffu, first_r[r], src);
+            fsl = __shfl_sync(0xffffffffu, sl_r[r], src);
+            tq_first = __shfl_sync(0xffffffffu, tq_r[r], src);
+            fb = r * 32 + src;
+            const long long rem = begin - lo_s;
+            fhg = (int)(rem / fn);
+            fstep = ffirst + (int)(rem % fn);
+          }
+          run += (long long)__shfl_sync(0xffffffffu, incl, 31) * P.head_groups;
         }
-        const long long lo = run + (long long)(incl - n) * P.head_groups;
-        const long long hi = run + (long long)incl * P.head_groups;
-        const bool mine = n > 0 && begin >= lo && begin < hi;
-        const unsigned hit = __ballot_sync(0xffffffffu, mine);
-        if (hit) {
-          const int src = __ffs(hit) - 1;
-          const long long lo_s = __shfl_sync(0xffffffffu, lo, src);
-          const int n_s = __shfl_sync(0xffffffffu, n, src);
-          const int first_s = __shfl_sync(0xffffffffu, first, src);
-          fb = b0 + src;
-          const long long rem = begin - lo_s;
-          fhg = (int)(rem / n_s);
-          fstep = first_s + (int)(rem % n_s);
-        }
-        run += (long long)__shfl_sync(0xffffffffu, incl, 31) * P.head_groups;
       }
     }
-    if (lane == 0) {
-      s_part[0] = (int)begin;
-      s_part[1] = (fb < 0) ? (int)begin : (int)end;
-      s_part[2] = fb, s_part[3] = fhg, s_part[4] = fstep;
-      s_part[5] = (int)(per > 0 ? per : 1);
-    }
-  } else if (warp == 1 && lane == 0) {
-    for (int s = 0; s < P.stages; ++s) {
-      mbar_init(&full_bar[s], P.tma_split == 2 ? kCpWarps * 32 : 1);
-      mbar_init(&empty_bar[s], NW);
-    }
-    fence_barrier_init();
-  }
-  __syncthreads();
-  // sequences with no visible key get zeros (reference reduce_segments :828); nobody visits them below
-  for (int b = blockIdx.x; b < P.a.num_seqs; b += gridDim.x) {
-    const int sl = P.a.seq_lens[b];
-    const int ql = P.a.cu_seqlens_q ? (P.a.cu_seqlens_q[b + 1] - P.a.cu_seqlens_q[b]) : 1;
-    if (sl <= 0 && ql == 1) {
-      const int tq = P.a.cu_seqlens_q ? P.a.cu_seqlens_q[b] : b;
-      for (int e = threadIdx.x; e < P.a.num_q_heads * D; e += blockDim.x) {
-        char* orow = static_cast<char*>(P.a.out) + ((int64_t)tq * P.a.out_stride0 + (int64_t)(e / D) * P.a.out_stride1) * 2;
-        reinterpret_cast<uint16_t*>(orow)[e % D] = 0;
+    my_begin = (int)begin, my_end = (fb < 0) ? (int)begin : (int)end;
+    per_cta = (int)(per > 0 ? per : 1);
+    cur.b = fb, cur.hg = fhg, cur.step = fstep, cur.flat = my_begin;
+    cur.seq_len = fsl, cur.first = ffirst, cur.n = fn;
+    // sequences with no visible key get zeros (reference reduce_segments :828); nobody visits them below
+    if (warp == 0 && __any_sync(0xffffffffu, zero_rows != 0)) {
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        unsigned m = __ballot_sync(0xffffffffu, (zero_rows >> r) & 1u);
+        while (m) {
+          const int src = __ffs(m) - 1;
+          m &= m - 1;
+          const int tq = __shfl_sync(0xffffffffu, tq_r[r], src);
+          for (int e = lane; e < P.a.num_q_heads * D; e += 32) {
+            char* orow = static_cast<char*>(P.a.out) + ((int64_t)tq * P.a.out_stride0 + (int64_t)(e / D) * P.a.out_stride1) * 2;
+            reinterpret_cast<uint16_t*>(orow)[e % D] = 0;
+          }
+        }
       }
     }
+    __syncthreads();  // mbarrier init visible to every warp
+  } else {
+    if (warp == 0) {
+      // total steps over all sequences
+      int total = 0;
+      for (int b0 = 0; b0 < P.a.num_seqs; b0 += 32) {
+        int b = b0 + lane, n = 0;
+        if (b < P.a.num_seqs) {
+          int sl, first;
+          seq_steps(P, b, sl, first, n);
+        }
+        total += n;
+      }
+      total = __reduce_add_sync(0xffffffffu, total);
+      const long long total_flat = (long long)total * P.head_groups;
+      const long long per = (total_flat + gridDim.x - 1) / gridDim.x;
+      long long begin = per * blockIdx.x;
+      long long end = begin + per;
+      if (begin > total_flat) begin = total_flat;
+      if (end > total_flat) end = total_flat;
+      // locate `begin`: largest b with HG * prefix(b) <= begin and n_b > 0 covering it
+      int fb = -1, fhg = 0, fstep = 0;
+      if (begin < end) {
+        long long run = 0;  // HG * sum of n over sequences before the chunk
+        for (int b0 = 0; b0 < P.a.num_seqs && fb < 0; b0 += 32) {
+          int b = b0 + lane, n = 0, first = 0, sl;
+          if (b < P.a.num_seqs) seq_steps(P, b, sl, first, n);
+          int incl = n;
+#pragma unroll
+          for (int o = 1; o < 32; o <<= 1) {
+            int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+          }
+          const long long lo = run + (long long)(incl - n) * P.head_groups;
+          const long long hi = run + (long long)incl * P.head_groups;
+          const bool mine = n > 0 && begin >= lo && begin < hi;
+          const unsigned hit = __ballot_sync(0xffffffffu, mine);
+          if (hit) {
+            const int src = __ffs(hit) - 1;
+            const long long lo_s = __shfl_sync(0xffffffffu, lo, src);
+            const int n_s = __shfl_sync(0xffffffffu, n, src);
+            const int first_s = __shfl_sync(0xffffffffu, first, src);
+            fb = b0 + src;
+            const long long rem = begin - lo_s;
+            fhg = (int)(rem / n_s);
+            fstep = first_s + (int)(rem % n_s);
+          }
+          run += (long long)__shfl_sync(0xffffffffu, incl, 31) * P.head_groups;
+        }
+      }
+      if (lane == 0) {
+        s_part[0] = (int)begin;
+        s_part[1] = (fb < 0) ? (int)begin : (int)end;
+        s_part[2] = fb, s_part[3] = fhg, s_part[4] = fstep;
+        s_part[5] = (int)(per > 0 ? per : 1);
+      }
+    }
+    __syncthreads();
+    for (int b = blockIdx.x; b < P.a.num_seqs; b += gridDim.x) {
+      const int sl = P.a.seq_lens[b];
+      const int ql = P.a.cu_seqlens_q ? (P.a.cu_seqlens_q[b + 1] - P.a.cu_seqlens_q[b]) : 1;
+      if (sl <= 0 && ql == 1) {
+        const int tq = P.a.cu_seqlens_q ? P.a.cu_seqlens_q[b] : b;
+        for (int e = threadIdx.x; e < P.a.num_q_heads * D; e += blockDim.x) {
+          char* orow = static_cast<char*>(P.a.out) + ((int64_t)tq * P.a.out_stride0 + (int64_t)(e / D) * P.a.out_stride1) * 2;
+          reinterpret_cast<uint16_t*>(orow)[e % D] = 0;
+        }
+      }
+    }
+    my_begin = s_part[0], my_end = s_part[1];
+    per_cta = s_part[5];
+    cur.b = s_part[2], cur.hg = s_part[3], cur.step = s_part[4], cur.flat = my_begin;
+    cur.seq_len = 0, cur.first = 0, cur.n = 0;
+    if (my_begin < my_end) {
+      seq_steps(P, cur.b, cur.seq_len, cur.first, cur.n);
+      tq_first = P.a.cu_seqlens_q ? P.a.cu_seqlens_q[cur.b] : cur.b;
+    }
   }
-  const int my_begin = s_part[0], my_end = s_part[1];
-  const int per_cta = s_part[5];
-  if (my_begin >= my_end) return;
-
-  ItemCursor cur;
-  cur.b = s_part[2], cur.hg = s_part[3], cur.step = s_part[4], cur.flat = my_begin;
-  seq_steps(P, cur.b, cur.seq_len, cur.first, cur.n);
+  if (trace && threadIdx.x == 0) trace[2] = clock64();
+  if (my_begin >= my_end) {
+    if (trace && threadIdx.x == 0) trace[3] = trace[4] = trace[5] = clock64(), trace[6] = global_ns();
+    return;
+  }
 
   const int boxb = P.hpc * NDC * P.box_slots * 128;  // bytes of one TMA box (all heads, all chunks)
 
-  if (warp >= NW && P.tma_split == 2) {
-    // ======================= cp.async producer warps ==========================
-    // 128 threads move one stage (K and V, NW*16 (token, head) rows of NDC 128-byte
-    // chunks each) as 16-byte copies into the layout a 128B-swizzled TMA box would
-    // have: unit u = 16-byte chunk index in box order [box][head][d-chunk][slot][c]
-    // lands at (u >> 3) * 128 + ((c ^ (slot & 7)) << 4).  A box never straddles a
-    // page and holds a multiple of 128 units, so the page of copy `it` is uniform
-    // over the producer threads.
-    constexpr int ITER = NW * NDC;  // copies per thread, per tensor, per full stage
-    const int ptid = threadIdx.x - NW * 32;
-    const uint64_t pol = policy_evict_first();
-    const int upb = P.hpc * NDC * P.box_slots * 8;  // 16-byte units per box (>= 128, power of two)
-    const int ipb_shift = 31 - __clz(upb >> 7);  // log2(copies per thread per box)
-    const int ipb_mask = (upb >> 7) - 1;
-    int goff[ITER];  // byte offset of copy `it` inside its box's page, without the page / first-slot part
-#pragma unroll
-    for (int it = 0; it < ITER; ++it) {
-      const int r = (it * 128 + ptid) & (upb - 1);
-      const int c = r & 7, slot = (r >> 3) % P.box_slots, hd = (r >> 3) / P.box_slots;
-      const int dc = hd % NDC, h = hd / NDC;
-      goff[it] = (int)(((int64_t)slot * P.a.kc_slot_stride + (int64_t)h * P.a.kc_head_stride) * ESZ) + dc * 128 + c * 16;
-    }
-    const uint32_t sm_thread = (uint32_t)((ptid >> 3) * 128 + (((ptid & 7) ^ ((ptid >> 3) & 7)) << 4));
-    const char* kbase = static_cast<const char*>(P.a.k_cache);
-    const char* vbase = static_cast<const char*>(P.a.v_cache);
-    const int pages_shift = 31 - __clz(P.a.block_size);
-    auto load_pages = [&](const ItemCursor& c, int (&pg)[8]) {
-      const int tok0 = c.step * P.tps;
-      const int32_t* bt = P.a.block_tables + (int64_t)c.b * P.a.bt_stride0;
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const int tok = tok0 + i * P.box_slots;
-        pg[i] = (i < P.boxes && tok < c.seq_len) ? __ldg(bt + (tok >> pages_shift)) : 0;
-      }
-    };
-    int pg[8], pg_n[8];
-    load_pages(cur, pg);
-    int stage = 0;
-    uint32_t phase = 0;
-    while (true) {
-      const int tok0 = cur.step * P.tps;
-      const int ntok = min(P.tps, cur.seq_len - tok0);
-      const int nbox = (ntok + P.box_slots - 1) / P.box_slots;
-      const int head0 = cur.hg * P.hpc;
-      const bool last = cur.flat + 1 >= my_end;
-      ItemCursor nxt = cur;
-      if (!last) {
-        cursor_next(P, nxt);
-        load_pages(nxt, pg_n);  // in flight while this step's copies are issued
-      }
-      mbar_wait(&empty_bar[stage], phase ^ 1);
-      const uint32_t kdst = smem_u32(stage_base + (size_t)stage * 2 * KV_STAGE_BYTES) + sm_thread;
-      const uint32_t vdst = kdst + KV_STAGE_BYTES;
-      const int64_t head_off = (int64_t)head0 * P.a.kc_head_stride * ESZ;
-      int64_t box_off = 0;
-#pragma unroll
-      for (int it = 0; it < ITER; ++it) {
-        const int i = it >> ipb_shift;
-        if (i >= nbox) break;
-        if ((it & ipb_mask) == 0) {
-          const int tok = tok0 + i * P.box_slots;
-          const int page = pg[0];
-#pragma unroll
-          for (int j = 0; j < 7; ++j) pg[j] = pg[j + 1];  // consume the page ids in box order
-          box_off = ((int64_t)page * P.a.kc_block_stride + (int64_t)(tok & (P.a.block_size - 1)) * P.a.kc_slot_stride) * ESZ + head_off;
-        }
-        const int64_t off = box_off + goff[it];
-        asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(kdst + it * 2048), "l"(kbase + off), "l"(pol) : "memory");
-        asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(vdst + it * 2048), "l"(vbase + off), "l"(pol) : "memory");
-      }
-      asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(&full_bar[stage])) : "memory");
-      if (++stage == P.stages) stage = 0, phase ^= 1;
-      if (last) break;
-      cur = nxt;
-#pragma unroll
-      for (int j = 0; j < 8; ++j) pg[j] = pg_n[j];
-    }
-    return;
-  }
-  if (warp > NW) return;
   if (warp == NW) {
     // ======================= producer warp ====================================
     // The whole warp issues: lane i looks up the page of box i and launches its
     // K and V copies, so page-table latency and TMA issue overlap across boxes.
-    if (lane == 0) {
-      tma_prefetch_desc(&k_map);
-      tma_prefetch_desc(&v_map);
-    }
     const uint64_t pol = policy_evict_first();
     int stage = 0;
     uint32_t phase = 0;
@@ -379,12 +406,14 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
 
   // ========================= consumer warps ====================================
   const int h_local = warp % P.hpc;           // kv head within the CTA's head group
-  const int jtile = warp / P.hpc;             // 16-token group within the stage-step
-  const int tok_off = jtile * 16;
-  const int box_i = tok_off / P.box_slots;
-  const int slot_in_box = tok_off % P.box_slots;
-  const uint32_t tile_off =
-      (uint32_t)(box_i * boxb + h_local * NDC * P.box_slots * 128 + slot_in_box * 128);  // + dc*box_slots*128
+  const int jtile = warp / P.hpc;             // TT-token group within the stage-step
+  const int tok_off = jtile * TT;
+  uint32_t tile_off[SUB];                     // byte offset of each 16-token sub-tile inside a stage (+ dc*dc_stride)
+#pragma unroll
+  for (int sb = 0; sb < SUB; ++sb) {
+    const int to = tok_off + 16 * sb;
+    tile_off[sb] = (uint32_t)((to / P.box_slots) * boxb + h_local * NDC * P.box_slots * 128 + (to % P.box_slots) * 128);
+  }
   const uint32_t dc_stride = (uint32_t)P.box_slots * 128;
 
   const float k_scale = (KV_FP8 && P.a.k_scale) ? *P.a.k_scale : 1.0f;
@@ -430,9 +459,8 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
     for (int nt = 0; nt < NT; ++nt) m_run[nt][0] = m_run[nt][1] = -INFINITY, l_run[nt][0] = l_run[nt][1] = 0.f;
   };
 
-  auto load_q = [&]() {
+  auto load_q = [&](int tq) {
     const int kvh = cur.hg * P.hpc + h_local;
-    const int tq = P.a.cu_seqlens_q ? P.a.cu_seqlens_q[cur.b] : cur.b;
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt) {
       const int hq_local = nt * 8 + gid;
@@ -474,85 +502,109 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
   };
 
   reset_state();
-  load_q();
+  load_q(tq_first);
+  int tq_cur = tq_first;
+  bool first_stage = true;
 
   int stage = 0;
   uint32_t phase = 0;
   while (true) {
     const int tok0 = cur.step * P.tps + tok_off;  // first token of this warp's tile
     mbar_wait(&full_bar[stage], phase);
+    if (trace && first_stage && threadIdx.x == 0) trace[3] = clock64();
+    first_stage = false;
     if (tok0 < cur.seq_len) {
-      const uint32_t ktile = smem_u32(stage_base + (size_t)stage * 2 * KV_STAGE_BYTES) + tile_off;
-      const uint32_t vtile = ktile + KV_STAGE_BYTES;
-      const int valid = cur.seq_len - tok0;  // > 0; tokens >= valid are out of range
+      const uint32_t kbase_s = smem_u32(stage_base + (size_t)stage * 2 * KV_STAGE_BYTES);
+      const uint32_t vbase_s = kbase_s + KV_STAGE_BYTES;
+      const int valid = cur.seq_len - tok0;  // > 0; tile tokens >= valid are out of range
       int win_lo = 0;                        // tokens < win_lo (tile-relative) are outside the sliding window
       if (P.a.sliding_window > 0) win_lo = (cur.seq_len - P.a.sliding_window) - tok0;
-      const bool partial = valid < 16 || win_lo > 0;
+      const bool partial = valid < TT || win_lo > 0;
 
-      // ---- S^T[16 tok][8 heads] = K Q^T ------------------------------------
-      float sacc[NT][4];
+      // ---- S^T[16 tok][8 heads] = K Q^T per sub-tile; even/odd k-steps accumulate in
+      // separate chains (a 16-deep dependent HMMA chain is what bounds a warp otherwise)
+      float sacc[SUB][NT][4];
 #pragma unroll
-      for (int nt = 0; nt < NT; ++nt) sacc[nt][0] = sacc[nt][1] = sacc[nt][2] = sacc[nt][3] = 0.f;
-      if constexpr (!KV_FP8) {
+      for (int sb = 0; sb < SUB; ++sb) {
+        float sodd[NT][4];
 #pragma unroll
-        for (int dc = 0; dc < NDC; ++dc) {
+        for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
-          for (int k4 = 0; k4 < 4; ++k4) {
-            uint32_t a[4];
-            const uint32_t chunk = (uint32_t)(2 * k4 + k_chunk_sel);
-            ldmatrix_x4(a, ktile + dc * dc_stride + k_lane_off + ((chunk ^ swz) << 4));
+          for (int i = 0; i < 4; ++i) sacc[sb][nt][i] = 0.f, sodd[nt][i] = 0.f;
+        if (sb == 0 || 16 * sb < valid) {  // warp-uniform; a sub-tile past the end is masked below
+          const uint32_t ktile = kbase_s + tile_off[sb];
+          if constexpr (!KV_FP8) {
 #pragma unroll
-            for (int nt = 0; nt < NT; ++nt)
-              mma_16816<MMA_BF16>(sacc[nt], a, qf[dc * 4 + k4][nt][0], qf[dc * 4 + k4][nt][1]);
-          }
-        }
-      } else {
+            for (int dc = 0; dc < NDC; ++dc) {
 #pragma unroll
-        for (int dc = 0; dc < NDC; ++dc) {
+              for (int k4 = 0; k4 < 4; ++k4) {
+                uint32_t a[4];
+                const uint32_t chunk = (uint32_t)(2 * k4 + k_chunk_sel);
+                ldmatrix_x4(a, ktile + dc * dc_stride + k_lane_off + ((chunk ^ swz) << 4));
 #pragma unroll
-          for (int c2 = 0; c2 < 4; ++c2) {  // pairs of 16-byte chunks = pairs of k16 steps
-            uint32_t r[4];
-            const uint32_t chunk = (uint32_t)(2 * c2 + k_chunk_sel);
-            ldmatrix_x4(r, ktile + dc * dc_stride + k_lane_off + ((chunk ^ swz) << 4));
+                for (int nt = 0; nt < NT; ++nt)
+                  mma_16816<MMA_BF16>((k4 & 1) ? sodd[nt] : sacc[sb][nt], a, qf[dc * 4 + k4][nt][0], qf[dc * 4 + k4][nt][1]);
+              }
+            }
+          } else {
 #pragma unroll
-            for (int half = 0; half < 2; ++half) {
-              uint32_t a[4];
-              a[0] = e4m3x2_to_f16x2((uint16_t)(r[2 * half] & 0xffffu));
-              a[1] = e4m3x2_to_f16x2((uint16_t)(r[2 * half + 1] & 0xffffu));
-              a[2] = e4m3x2_to_f16x2((uint16_t)(r[2 * half] >> 16));
-              a[3] = e4m3x2_to_f16x2((uint16_t)(r[2 * half + 1] >> 16));
-              const int ks = dc * 8 + c2 * 2 + half;
+            for (int dc = 0; dc < NDC; ++dc) {
 #pragma unroll
-              for (int nt = 0; nt < NT; ++nt) mma_16816<false>(sacc[nt], a, qf[ks][nt][0], qf[ks][nt][1]);
+              for (int c2 = 0; c2 < 4; ++c2) {  // pairs of 16-byte chunks = pairs of k16 steps
+                uint32_t r[4];
+                const uint32_t chunk = (uint32_t)(2 * c2 + k_chunk_sel);
+                ldmatrix_x4(r, ktile + dc * dc_stride + k_lane_off + ((chunk ^ swz) << 4));
+#pragma unroll
+                for (int half = 0; half < 2; ++half) {
+                  uint32_t a[4];
+                  a[0] = e4m3x2_to_f16x2((uint16_t)(r[2 * half] & 0xffffu));
+                  a[1] = e4m3x2_to_f16x2((uint16_t)(r[2 * half + 1] & 0xffffu));
+                  a[2] = e4m3x2_to_f16x2((uint16_t)(r[2 * half] >> 16));
+                  a[3] = e4m3x2_to_f16x2((uint16_t)(r[2 * half + 1] >> 16));
+                  const int ks = dc * 8 + c2 * 2 + half;
+#pragma unroll
+                  for (int nt = 0; nt < NT; ++nt)
+                    mma_16816<false>(half ? sodd[nt] : sacc[sb][nt], a, qf[ks][nt][0], qf[ks][nt][1]);
+                }
+              }
             }
           }
+#pragma unroll
+          for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) sacc[sb][nt][i] += sodd[nt][i];
         }
       }
 
-      // ---- online softmax (log2 domain) --------------------------------------
-      uint32_t pb[NT][2];
+      // ---- online softmax (log2 domain), one running-max update for the whole tile ----
+      uint32_t pb[SUB][NT][2];
       float alpha[NT][2];
 #pragma unroll
       for (int nt = 0; nt < NT; ++nt) {
-        float s[4];
+        float sv[SUB][4];
+        float mx0 = -INFINITY, mx1 = -INFINITY;
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          float x = sacc[nt][i] * qk_scale;
-          if (has_cap) x = softcap_fn(x, P.a.softcap, inv_cap);
-          s[i] = x * kLog2e;
+        for (int sb = 0; sb < SUB; ++sb) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            float x = sacc[sb][nt][i] * qk_scale;
+            if (has_cap) x = softcap_fn(x, P.a.softcap, inv_cap);
+            sv[sb][i] = x * kLog2e;
+          }
+          const int tr = 16 * sb + gid;  // tile-relative token of rows gid (and gid + 8)
+          if (has_alibi) {
+            // bias slope * (pos - ctx), ctx = seq_len - 1 for a decode token
+            const float p0 = (float)(tok0 + tr - (cur.seq_len - 1)), p1 = p0 + 8.f;
+            sv[sb][0] += slope[nt][0] * p0 * kLog2e, sv[sb][1] += slope[nt][1] * p0 * kLog2e;
+            sv[sb][2] += slope[nt][0] * p1 * kLog2e, sv[sb][3] += slope[nt][1] * p1 * kLog2e;
+          }
+          if (partial) {
+            const bool ok0 = tr < valid && tr >= win_lo, ok1 = tr + 8 < valid && tr + 8 >= win_lo;
+            if (!ok0) sv[sb][0] = sv[sb][1] = -INFINITY;
+            if (!ok1) sv[sb][2] = sv[sb][3] = -INFINITY;
+          }
+          mx0 = fmaxf(mx0, fmaxf(sv[sb][0], sv[sb][2])), mx1 = fmaxf(mx1, fmaxf(sv[sb][1], sv[sb][3]));
         }
-        if (has_alibi) {
-          // bias slope * (pos - ctx), ctx = seq_len - 1 for a decode token
-          const float p0 = (float)(tok0 + gid - (cur.seq_len - 1)), p1 = p0 + 8.f;
-          s[0] += slope[nt][0] * p0 * kLog2e, s[1] += slope[nt][1] * p0 * kLog2e;
-          s[2] += slope[nt][0] * p1 * kLog2e, s[3] += slope[nt][1] * p1 * kLog2e;
-        }
-        if (partial) {
-          const bool ok0 = gid < valid && gid >= win_lo, ok1 = gid + 8 < valid && gid + 8 >= win_lo;
-          if (!ok0) s[0] = s[1] = -INFINITY;
-          if (!ok1) s[2] = s[3] = -INFINITY;
-        }
-        float mx0 = fmaxf(s[0], s[2]), mx1 = fmaxf(s[1], s[3]);
 #pragma unroll
         for (int o = 4; o < 32; o <<= 1) {
           mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, o));
@@ -562,12 +614,17 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
         const float mu0 = (mn0 == -INFINITY) ? 0.f : mn0, mu1 = (mn1 == -INFINITY) ? 0.f : mn1;
         alpha[nt][0] = ex2(m_run[nt][0] - mu0), alpha[nt][1] = ex2(m_run[nt][1] - mu1);
         m_run[nt][0] = mn0, m_run[nt][1] = mn1;
-        const float p0 = ex2(s[0] - mu0), p1 = ex2(s[1] - mu1), p2 = ex2(s[2] - mu0), p3 = ex2(s[3] - mu1);
-        l_run[nt][0] = l_run[nt][0] * alpha[nt][0] + p0 + p2;
-        l_run[nt][1] = l_run[nt][1] * alpha[nt][1] + p1 + p3;
-        // P^T fragments: transpose the two 8x8 (token x head) blocks
-        pb[nt][0] = movmatrix_trans(pack2<MMA_BF16>(p0, p1));
-        pb[nt][1] = movmatrix_trans(pack2<MMA_BF16>(p2, p3));
+        float ls0 = 0.f, ls1 = 0.f;
+#pragma unroll
+        for (int sb = 0; sb < SUB; ++sb) {
+          const float p0 = ex2(sv[sb][0] - mu0), p1 = ex2(sv[sb][1] - mu1), p2 = ex2(sv[sb][2] - mu0), p3 = ex2(sv[sb][3] - mu1);
+          ls0 += p0 + p2, ls1 += p1 + p3;
+          // P^T fragments: transpose the two 8x8 (token x head) blocks
+          pb[sb][nt][0] = movmatrix_trans(pack2<MMA_BF16>(p0, p1));
+          pb[sb][nt][1] = movmatrix_trans(pack2<MMA_BF16>(p2, p3));
+        }
+        l_run[nt][0] = l_run[nt][0] * alpha[nt][0] + ls0;
+        l_run[nt][1] = l_run[nt][1] * alpha[nt][1] + ls1;
       }
       // rescale the accumulators (columns = heads 2t, 2t+1)
 #pragma unroll
@@ -581,52 +638,57 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
         }
       }
 
-      // ---- O^T[D][8 heads] += V^T P^T -----------------------------------------
-      // token masks for the V fragments of a partial tile (garbage x 0 must not make NaN)
-      uint32_t vm_lo = 0xffffffffu, vm_hi = 0xffffffffu;
-      if (partial) {
-        const int ta = 2 * t4, tb = 2 * t4 + 8;
-        auto okt = [&](int tk) { return tk < valid && tk >= win_lo; };
-        vm_lo = (okt(ta) ? 0x0000ffffu : 0u) | (okt(ta + 1) ? 0xffff0000u : 0u);
-        vm_hi = (okt(tb) ? 0x0000ffffu : 0u) | (okt(tb + 1) ? 0xffff0000u : 0u);
-      }
-      if constexpr (!KV_FP8) {
+      // ---- O^T[D][8 heads] += V^T P^T ------------------------------------------
 #pragma unroll
-        for (int dc = 0; dc < NDC; ++dc) {
-#pragma unroll
-          for (int m4 = 0; m4 < 4; ++m4) {
-            uint32_t a[4];
-            const uint32_t chunk = (uint32_t)(2 * m4 + v_chunk_sel);
-            ldmatrix_x4_trans(a, vtile + dc * dc_stride + v_lane_off + ((chunk ^ swz) << 4));
-            // a0:(d gid; tok 2t,2t+1) a1:(d gid+8; same) a2:(d gid; tok 2t+8,+9) a3:(d gid+8; ...)
-            if (partial) a[0] &= vm_lo, a[1] &= vm_lo, a[2] &= vm_hi, a[3] &= vm_hi;
-#pragma unroll
-            for (int nt = 0; nt < NT; ++nt) mma_16816<MMA_BF16>(oacc[dc * 4 + m4][nt], a, pb[nt][0], pb[nt][1]);
-          }
+      for (int sb = 0; sb < SUB; ++sb) {
+        if (sb > 0 && 16 * sb >= valid) continue;  // warp-uniform: nothing of this sub-tile is visible
+        const uint32_t vtile = vbase_s + tile_off[sb];
+        // token masks for the V fragments of a partial tile (garbage x 0 must not make NaN)
+        uint32_t vm_lo = 0xffffffffu, vm_hi = 0xffffffffu;
+        if (partial) {
+          const int ta = 16 * sb + 2 * t4, tb = ta + 8;
+          auto okt = [&](int tk) { return tk < valid && tk >= win_lo; };
+          vm_lo = (okt(ta) ? 0x0000ffffu : 0u) | (okt(ta + 1) ? 0xffff0000u : 0u);
+          vm_hi = (okt(tb) ? 0x0000ffffu : 0u) | (okt(tb + 1) ? 0xffff0000u : 0u);
         }
-      } else {
+        if constexpr (!KV_FP8) {
 #pragma unroll
-        for (int dc = 0; dc < NDC; ++dc) {
+          for (int dc = 0; dc < NDC; ++dc) {
 #pragma unroll
-          for (int c2 = 0; c2 < 4; ++c2) {
-            uint32_t r[4];
-            const uint32_t chunk = (uint32_t)(2 * c2 + v_chunk_sel);
-            ldmatrix_x4_trans(r, vtile + dc * dc_stride + v_lane_off + ((chunk ^ swz) << 4));
-            // r0: tokens 0-7 chunk c | r1: tokens 8-15 chunk c | r2, r3: chunk c+1
-            // each: [tok 2t: d0 d1 | tok 2t+1: d0 d1] with d0 = 16c + 2gid
-#pragma unroll
-            for (int half = 0; half < 2; ++half) {
-              const uint32_t x0 = __byte_perm(r[2 * half], 0, 0x3120);      // [t d0, t+1 d0 | t d1, t+1 d1]
-              const uint32_t x1 = __byte_perm(r[2 * half + 1], 0, 0x3120);
+            for (int m4 = 0; m4 < 4; ++m4) {
               uint32_t a[4];
-              a[0] = e4m3x2_to_f16x2((uint16_t)(x0 & 0xffffu));  // row gid   <-> d0, tokens 2t,2t+1
-              a[1] = e4m3x2_to_f16x2((uint16_t)(x0 >> 16));      // row gid+8 <-> d1
-              a[2] = e4m3x2_to_f16x2((uint16_t)(x1 & 0xffffu));  // tokens 2t+8, 2t+9
-              a[3] = e4m3x2_to_f16x2((uint16_t)(x1 >> 16));
+              const uint32_t chunk = (uint32_t)(2 * m4 + v_chunk_sel);
+              ldmatrix_x4_trans(a, vtile + dc * dc_stride + v_lane_off + ((chunk ^ swz) << 4));
+              // a0:(d gid; tok 2t,2t+1) a1:(d gid+8; same) a2:(d gid; tok 2t+8,+9) a3:(d gid+8; ...)
               if (partial) a[0] &= vm_lo, a[1] &= vm_lo, a[2] &= vm_hi, a[3] &= vm_hi;
-              const int mt = dc * 8 + c2 * 2 + half;
 #pragma unroll
-              for (int nt = 0; nt < NT; ++nt) mma_16816<false>(oacc[mt][nt], a, pb[nt][0], pb[nt][1]);
+              for (int nt = 0; nt < NT; ++nt) mma_16816<MMA_BF16>(oacc[dc * 4 + m4][nt], a, pb[sb][nt][0], pb[sb][nt][1]);
+            }
+          }
+        } else {
+#pragma unroll
+          for (int dc = 0; dc < NDC; ++dc) {
+#pragma unroll
+            for (int c2 = 0; c2 < 4; ++c2) {
+              uint32_t r[4];
+              const uint32_t chunk = (uint32_t)(2 * c2 + v_chunk_sel);
+              ldmatrix_x4_trans(r, vtile + dc * dc_stride + v_lane_off + ((chunk ^ swz) << 4));
+              // r0: tokens 0-7 chunk c | r1: tokens 8-15 chunk c | r2, r3: chunk c+1
+              // each: [tok 2t: d0 d1 | tok 2t+1: d0 d1] with d0 = 16c + 2gid
+#pragma unroll
+              for (int half = 0; half < 2; ++half) {
+                const uint32_t x0 = __byte_perm(r[2 * half], 0, 0x3120);      // [t d0, t+1 d0 | t d1, t+1 d1]
+                const uint32_t x1 = __byte_perm(r[2 * half + 1], 0, 0x3120);
+                uint32_t a[4];
+                a[0] = e4m3x2_to_f16x2((uint16_t)(x0 & 0xffffu));  // row gid   <-> d0, tokens 2t,2t+1
+                a[1] = e4m3x2_to_f16x2((uint16_t)(x0 >> 16));      // row gid+8 <-> d1
+                a[2] = e4m3x2_to_f16x2((uint16_t)(x1 & 0xffffu));  // tokens 2t+8, 2t+9
+                a[3] = e4m3x2_to_f16x2((uint16_t)(x1 >> 16));
+                if (partial) a[0] &= vm_lo, a[1] &= vm_lo, a[2] &= vm_hi, a[3] &= vm_hi;
+                const int mt = dc * 8 + c2 * 2 + half;
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt) mma_16816<false>(oacc[mt][nt], a, pb[sb][nt][0], pb[sb][nt][1]);
+              }
             }
           }
         }
@@ -643,7 +705,11 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
       const int item = cur.b * P.head_groups + cur.hg;
       const int item_flat0 = cur.flat - (cur.step - cur.first);
       const bool direct = item_flat0 >= my_begin && item_flat0 + cur.n <= my_end;
-      const int tq = P.a.cu_seqlens_q ? P.a.cu_seqlens_q[cur.b] : cur.b;
+      const int tq = tq_cur;
+      if (trace && threadIdx.x == 0) {
+        if (last) trace[4] = clock64();
+        trace[7] += 1;
+      }
       const int wph = NW / P.hpc;  // warps per kv head
 #pragma unroll
       for (int nt = 0; nt < NT; ++nt) {
@@ -715,26 +781,60 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
         asm volatile("bar.sync 1, %0;" ::"r"(NW * 32));
         if (s_part[6]) {
           __threadfence();
+          // Every thread owns (query head, 4 dims) chunks; the (max, exp-sum) pair and the
+          // float4 of every part are requested before any of them is used, so a chunk costs
+          // one L2 round trip (a loop that first reduces the maxima costs two per element,
+          // which was 20 us of tail at 4 kv heads per CTA).
           const int rec_heads = P.hpc * P.group;
-          for (int e = threadIdx.x; e < rec_heads * D; e += NW * 32) {
-            const int hq_in = e / D, d = e % D;
-            float M = -INFINITY;
-            for (int c = first_cta; c <= last_cta; ++c)
-              M = fmaxf(M, __ldcg(&P.ws_ml[(((int64_t)item + c) * rec_heads + hq_in) * 2]));
-            float val = 0.f, L = 0.f;
+          const int nparts = last_cta - first_cta + 1;
+          constexpr int D4 = D / 4;
+          for (int e = threadIdx.x; e < rec_heads * D4; e += NW * 32) {
+            const int hq_in = e / D4, d4 = (e % D4) * 4;
+            const int64_t rec0 = ((int64_t)item + first_cta) * rec_heads + hq_in;
+            float M = -INFINITY, L = 0.f;
+            float4 val = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (nparts <= 4) {
+              float2 ml[4];
+              float4 av[4];
+#pragma unroll
+              for (int c = 0; c < 4; ++c) {
+                if (c < nparts) {
+                  const int64_t rec = rec0 + (int64_t)c * rec_heads;
+                  ml[c] = __ldcg(reinterpret_cast<const float2*>(&P.ws_ml[rec * 2]));
+                  av[c] = __ldcg(reinterpret_cast<const float4*>(&P.ws_acc[rec * D + d4]));
+                } else {
+                  ml[c] = make_float2(-INFINITY, 0.f), av[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+              }
+#pragma unroll
+              for (int c = 0; c < 4; ++c) M = fmaxf(M, ml[c].x);
+#pragma unroll
+              for (int c = 0; c < 4; ++c) {
+                const float sc = (ml[c].x == -INFINITY) ? 0.f : ex2(ml[c].x - M);
+                val.x += av[c].x * sc, val.y += av[c].y * sc, val.z += av[c].z * sc, val.w += av[c].w * sc;
+                L += ml[c].y * sc;
+              }
+            } else {
+              for (int c = 0; c < nparts; ++c) M = fmaxf(M, __ldcg(&P.ws_ml[(rec0 + (int64_t)c * rec_heads) * 2]));
 #pragma unroll 4
-            for (int c = first_cta; c <= last_cta; ++c) {
-              const int64_t rec = ((int64_t)item + c) * rec_heads + hq_in;
-              const float mw = __ldcg(&P.ws_ml[rec * 2]);
-              const float sc = (mw == -INFINITY) ? 0.f : ex2(mw - M);
-              val += __ldcg(&P.ws_acc[rec * D + d]) * sc;
-              L += __ldcg(&P.ws_ml[rec * 2 + 1]) * sc;
+              for (int c = 0; c < nparts; ++c) {
+                const int64_t rec = rec0 + (int64_t)c * rec_heads;
+                const float2 ml = __ldcg(reinterpret_cast<const float2*>(&P.ws_ml[rec * 2]));
+                const float4 av = __ldcg(reinterpret_cast<const float4*>(&P.ws_acc[rec * D + d4]));
+                const float sc = (ml.x == -INFINITY) ? 0.f : ex2(ml.x - M);
+                val.x += av.x * sc, val.y += av.y * sc, val.z += av.z * sc, val.w += av.w * sc;
+                L += ml.y * sc;
+              }
             }
-            const float o = (L > 0.f) ? val * v_scale / L : 0.f;  // 0 when nothing is visible (reference :828)
+            const float inv = (L > 0.f) ? v_scale / L : 0.f;  // 0 when nothing is visible (reference :828)
             const int hq = cur.hg * rec_heads + hq_in;
             char* orow = static_cast<char*>(P.a.out) + ((int64_t)tq * P.a.out_stride0 + (int64_t)hq * P.a.out_stride1) * 2;
-            if constexpr (Q_BF16) reinterpret_cast<__nv_bfloat16*>(orow)[d] = __float2bfloat16_rn(o);
-            else reinterpret_cast<__half*>(orow)[d] = __float2half_rn(o);
+            const float o4[4] = {val.x * inv, val.y * inv, val.z * inv, val.w * inv};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              if constexpr (Q_BF16) reinterpret_cast<__nv_bfloat16*>(orow)[d4 + j] = __float2bfloat16_rn(o4[j]);
+              else reinterpret_cast<__half*>(orow)[d4 + j] = __float2half_rn(o4[j]);
+            }
           }
           if (threadIdx.x == 0) P.ws_cnt[item] = 0;  // self-cleaning: ready for the next call
         }
@@ -743,11 +843,13 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
       asm volatile("bar.sync 1, %0;" ::"r"(NW * 32));  // merge buffers are reused by the next item
       cursor_next(P, cur);
       reset_state();
-      load_q();
+      tq_cur = P.a.cu_seqlens_q ? P.a.cu_seqlens_q[cur.b] : cur.b;
+      load_q(tq_cur);
     } else {
       cursor_next(P, cur);
     }
   }
+  if (trace && threadIdx.x == 0) trace[5] = clock64(), trace[6] = global_ns();
 }
 
 // ---- host side ------------------------------------------------------------------
@@ -765,11 +867,11 @@ inline int pick_hpc(int hkv, int nw, int want) {
   return hpc;
 }
 
-template <int D, bool KV_FP8, bool MMA_BF16, bool Q_BF16, int NT, int NW>
+template <int D, bool KV_FP8, bool MMA_BF16, bool Q_BF16, int NT, int NW, int TT>
 int launch_variant(const b200attn_attention_params& a, DecodeParams& P, cudaStream_t stream) {
   constexpr int ESZ = KV_FP8 ? 1 : 2;
   constexpr int NDC = D * ESZ / 128;
-  constexpr int KV_STAGE_BYTES = NW * 16 * D * ESZ;
+  constexpr int KV_STAGE_BYTES = NW * TT * D * ESZ;
   const DeviceInfo& dev = device_info();
   const Tuning& tn = tuning();
   if (tn.decode_heads_per_cta > 0) {
@@ -782,7 +884,7 @@ int launch_variant(const b200attn_attention_params& a, DecodeParams& P, cudaStre
     const int min_box = KV_FP8 ? 8192 : 4096;
     int hpc = 1;
     while (hpc < NW && a.num_kv_heads % (hpc * 2) == 0) {
-      const int tps = NW * 16 / hpc;
+      const int tps = NW * TT / hpc;
       const int slots = a.block_size < tps ? a.block_size : tps;
       if (hpc * NDC * slots * 128 >= min_box) break;
       hpc *= 2;
@@ -790,19 +892,10 @@ int launch_variant(const b200attn_attention_params& a, DecodeParams& P, cudaStre
     P.hpc = hpc;
   }
   P.head_groups = a.num_kv_heads / P.hpc;
-  P.tps = NW * 16 / P.hpc;
+  P.tps = NW * TT / P.hpc;
   P.box_slots = a.block_size < P.tps ? a.block_size : P.tps;
   P.boxes = P.tps / P.box_slots;
   P.tma_split = tn.reserved & 1;
-  {
-    // cp.async producers when a box is too small for the copy engine (see the header comment);
-    // needs K and V to share strides.  tuning().reserved bit 1 forces it, bit 2 forbids it.
-    const bool same = a.kc_block_stride == a.vc_block_stride && a.kc_slot_stride == a.vc_slot_stride &&
-                      a.kc_head_stride == a.vc_head_stride;
-    const int box_bytes = P.hpc * NDC * P.box_slots * 128;
-    const bool want = (tn.reserved & 2) || (box_bytes < 4096 && !(tn.reserved & 4));
-    if (same && want && P.boxes <= 8) P.tma_split = 2;
-  }
   const int fixed = NW * 8 * D * 4 + NW * 8 * 2 * 4 + 2 * kMaxStages * 8 + 64 + 1024 /*alignment slack*/;
   int stages = (dev.max_smem_optin - fixed) / (2 * KV_STAGE_BYTES);
   if (stages > kMaxStages) stages = kMaxStages;
@@ -830,7 +923,7 @@ int launch_variant(const b200attn_attention_params& a, DecodeParams& P, cudaStre
   if (grid > max_steps) grid = max_steps;
   if (grid < 1) grid = 1;
 
-  auto kern = attn_decode_kernel<D, KV_FP8, MMA_BF16, Q_BF16, NT, NW>;
+  auto kern = attn_decode_kernel<D, KV_FP8, MMA_BF16, Q_BF16, NT, NW, TT>;
   static thread_local bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, dev.max_smem_optin);
@@ -840,8 +933,8 @@ int launch_variant(const b200attn_attention_params& a, DecodeParams& P, cudaStre
     }
     attr_set = true;
   }
-  kern<<<(unsigned)grid, (NW + (P.tma_split == 2 ? kCpWarps : 1)) * 32, smem, stream>>>(P, kmap, vmap);
-  note_launch(P.tma_split == 2 ? "attn_decode_split_kv_cpasync" : "attn_decode_split_kv");
+  kern<<<(unsigned)grid, (NW + 1) * 32, smem, stream>>>(P, kmap, vmap);
+  note_launch("attn_decode_split_kv");
   return check_launch("attn_decode");
 }
 
@@ -850,15 +943,18 @@ int dispatch_types(const b200attn_attention_params& a, DecodeParams& P, cudaStre
   const bool qbf = a.q_dtype == B200ATTN_BF16;
   if (a.kv_dtype == B200ATTN_FP8_E4M3) {
     if constexpr (D >= 128) {
-      return qbf ? launch_variant<D, true, false, true, NT, NW>(a, P, stream)
-                 : launch_variant<D, true, false, false, NT, NW>(a, P, stream);
+      // fp8: two 16-token sub-tiles per warp and step (a stage of 8 x 32 tokens is the size a bf16
+      // stage of 8 x 16 has); the tile's latency chain, not HBM, bounds this variant otherwise
+      constexpr int TT = (D == 128 && NT == 1) ? 32 : 16;  // (NT = 2 would spill)
+      return qbf ? launch_variant<D, true, false, true, NT, NW, TT>(a, P, stream)
+                 : launch_variant<D, true, false, false, NT, NW, TT>(a, P, stream);
     } else {
       set_error("decode: fp8 KV needs head_size >= 128");
       return B200ATTN_E_UNSUPPORTED;
     }
   }
-  return qbf ? launch_variant<D, false, true, true, NT, NW>(a, P, stream)
-             : launch_variant<D, false, false, false, NT, NW>(a, P, stream);
+  return qbf ? launch_variant<D, false, true, true, NT, NW, 16>(a, P, stream)
+             : launch_variant<D, false, false, false, NT, NW, 16>(a, P, stream);
 }
 
 inline bool pow2(int x) { return x > 0 && (x & (x - 1)) == 0; }
@@ -913,6 +1009,7 @@ int launch_attn_decode(const b200attn_attention_params& a, cudaStream_t stream, 
   P.a = a;
   P.group = a.num_q_heads / a.num_kv_heads;
   P.only_q1 = only_single_token_seqs ? 1 : 0;
+  P.trace = decode_trace_buffer();
   // carve the workspace: ticket counters first (items <= B*Hkv; zero between calls), then ml, then acc
   const uint64_t items_max = (uint64_t)a.num_seqs * a.num_kv_heads;
   char* w = static_cast<char*>(a.workspace);

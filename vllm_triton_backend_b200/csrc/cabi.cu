@@ -13,7 +13,10 @@ thread_local char g_error[512] = "";
 thread_local uint64_t g_launches = 0;
 thread_local const char* g_last_kernel = "";
 Tuning g_tuning;
+unsigned long long* g_decode_trace = nullptr;
 }  // namespace
+
+unsigned long long* decode_trace_buffer() { return g_decode_trace; }
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -113,6 +116,10 @@ void b200attn_set_tuning(int32_t decode_heads_per_cta, int32_t decode_ctas_per_s
   g_tuning.decode_ctas_per_sm = decode_ctas_per_sm;
   g_tuning.decode_stages = decode_stages;
   g_tuning.reserved = reserved;
+}
+
+void b200attn_debug_set_decode_trace(void* device_buffer) {
+  g_decode_trace = static_cast<unsigned long long*>(device_buffer);
 }
 
 int b200attn_reshape_and_cache_flash(const void* key, const void* value, void* k_cache, void* v_cache,

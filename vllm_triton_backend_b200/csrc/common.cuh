@@ -24,6 +24,7 @@ struct Tuning {
   int reserved = 0;
 };
 Tuning& tuning();
+unsigned long long* decode_trace_buffer();  // debug (b200attn_debug_set_decode_trace)
 
 struct DeviceInfo {
   int num_sms = 0;

@@ -52,3 +52,67 @@ class StepStaging:
     def upload(self) -> None:
         """One asynchronous host-to-device copy of the whole arena on the current stream."""
         self._dev.copy_(self._host, non_blocking=True)
+
+
+class _Slot:
+    __slots__ = ("staging", "dev_out", "host_out", "uploaded", "computed", "downloaded", "busy")
+
+
+class StepPipeline:
+    """`depth` StepStaging arenas + output buffers cycled through three streams: the upload of
+    step i+1 (copy stream) and the read-back of step i-1 (second copy stream) overlap the
+    kernels of step i (the caller's current stream).  Every step still moves all of its inputs
+    host->device and its result device->host; the host blocks only when it needs a slot back,
+    at which point that slot's result is complete and readable in `slot.host_out`.
+
+        pipe = StepPipeline(spec, out_shape, out_dtype, device)
+        for step in steps:
+            slot = pipe.acquire()            # host_out of the step that used this slot is valid now
+            ... fill slot.staging.host[...] ...
+            pipe.run(slot, lambda dev, out: impl.forward(..., dev["q"], ..., output=out))
+        pipe.drain()
+    """
+
+    def __init__(self, spec, out_shape, out_dtype, device, depth: int = 2) -> None:
+        self.device = torch.device(device)
+        spec = list(spec)
+        self.h2d = torch.cuda.Stream(self.device)
+        self.d2h = torch.cuda.Stream(self.device)
+        self.slots = []
+        for _ in range(depth):
+            s = _Slot()
+            s.staging = StepStaging(spec, self.device)
+            s.dev_out = torch.empty(out_shape, dtype=out_dtype, device=self.device)
+            s.host_out = torch.empty(out_shape, dtype=out_dtype, pin_memory=True)
+            s.uploaded, s.computed, s.downloaded = (torch.cuda.Event() for _ in range(3))
+            s.busy = False
+            self.slots.append(s)
+        self._next = 0
+
+    def acquire(self) -> _Slot:
+        s = self.slots[self._next]
+        self._next = (self._next + 1) % len(self.slots)
+        if s.busy:
+            s.downloaded.synchronize()  # result of the step that last used this slot is on the host
+            s.busy = False
+        return s
+
+    def run(self, slot: _Slot, compute) -> None:
+        main = torch.cuda.current_stream(self.device)
+        with torch.cuda.stream(self.h2d):
+            slot.staging.upload()  # the slot's previous kernels finished: acquire() waited for its read-back
+            slot.uploaded.record(self.h2d)
+        main.wait_event(slot.uploaded)
+        compute(slot.staging.dev, slot.dev_out)
+        slot.computed.record(main)
+        self.d2h.wait_event(slot.computed)
+        with torch.cuda.stream(self.d2h):
+            slot.host_out.copy_(slot.dev_out, non_blocking=True)
+            slot.downloaded.record(self.d2h)
+        slot.busy = True
+
+    def drain(self) -> None:
+        for s in self.slots:
+            if s.busy:
+                s.downloaded.synchronize()
+                s.busy = False
