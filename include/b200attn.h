@@ -102,7 +102,10 @@ typedef struct b200attn_attention_params {
   const float* alibi_slopes;   /* [Hq] or NULL                                     */
   const float* k_scale;        /* device scalar ("k_descale" element 0) or NULL=1  */
   const float* v_scale;
-  const float* sinks;          /* reserved (NULL)                                  */
+  const float* sinks;          /* [Hq] fp32 attention-sink logits or NULL: one extra
+                                  key per head that only joins the softmax denominator
+                                  (upstream addition to the same kernel, `init_softmax_M`
+                                  in vllm/v1/attention/ops/triton_attention_helpers.py) */
   float softmax_scale;
   float softcap;               /* 0 = off                                          */
   int32_t sliding_window;      /* 0 = off; = 1 + window_size[0] (:915)             */

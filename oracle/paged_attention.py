@@ -62,7 +62,12 @@ def unified_attention_ref(
     v_scale: float = 1.0,
     round_p_to: Optional[torch.dtype] = None,  # kernel casts P to V's dtype before PV (:508)
     out_dtype: Optional[torch.dtype] = None,
+    sinks: Optional[torch.Tensor] = None,  # [Hq]: per-head logit that only joins the softmax denominator
 ) -> torch.Tensor:
+    """`sinks` is an upstream addition to the same kernel (vLLM's
+    vllm/v1/attention/ops/triton_attention_helpers.py `init_softmax_M`: the running max starts at
+    the head's sink value and the running sum at 1, i.e. one extra key with logit `sink`, unscaled,
+    and a zero value row)."""
     T, Hq, D = q.shape
     Hkv = k_cache.shape[2]
     g = Hq // Hkv
@@ -93,9 +98,13 @@ def unified_attention_ref(
         if alibi_slopes is not None:
             s = s + alibi_slopes.to(torch.float32).view(Hq, 1, 1) * (kpos - ctx)  # :481-482
         m = s.max(dim=-1, keepdim=True).values
+        if sinks is not None:
+            m = torch.maximum(m, sinks.to(torch.float32).view(Hq, 1, 1))
         m = torch.where(m > float("-inf"), m, torch.zeros_like(m))  # :489
         p = torch.exp(s - m)
         l = p.sum(dim=-1, keepdim=True)
+        if sinks is not None:
+            l = l + torch.exp(sinks.to(torch.float32).view(Hq, 1, 1) - m)
         if round_p_to is not None:
             p = p.to(round_p_to).to(torch.float32)
         o = torch.einsum("hqk,khd->qhd", p, v) / l.permute(1, 0, 2)  # :508-511

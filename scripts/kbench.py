@@ -97,6 +97,18 @@ def kernel_name(args):
     return "triton kernel_unified_attention (vLLM %s)" % __import__("vllm").__version__ if args.impl == "triton" else _cabi.last_kernel()
 
 
+def graphed(fn, inner=20):
+    """`inner` back-to-back calls captured in one CUDA graph (the do_bench_cudagraph-style variant of
+    SURVEY.md §8d): returns a callable replaying the graph and the number of calls per replay."""
+    fn()
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for _ in range(inner):
+            fn()
+    return g.replay, inner
+
+
 def make_kv(NB, bs, hkv, D, fp8, device, g, layout="planes"):
     shape = (2, NB, bs, hkv, D) if layout == "planes" else (NB, 2, bs, hkv, D)
     dt = torch.uint8 if fp8 else torch.bfloat16
@@ -202,7 +214,12 @@ def run_decode(args, device):
     if args.trace:
         print(json.dumps(dict(**decode_trace(fn, device), **cfg)), flush=True)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=device) if args.flush else None
+    inner = 1
+    if args.graph:
+        fn, inner = graphed(fn)
     ms, n = time_fn(fn, flush=flush)
+    ms /= inner
+    cfg["cuda_graph"] = bool(args.graph)
     gbs = nbytes / ms / 1e6
     print(json.dumps(dict(kind="decode", **cfg, hpc=args.hpc, stages=args.stages, split=args.split, ctas=args.ctas,
                           ms=round(ms, 5), gbs=round(gbs, 1), frac_measured=round(gbs / hbm, 4),
@@ -333,6 +350,7 @@ def main():
     ap.add_argument("--flush", action="store_true")
     ap.add_argument("--layout", default="planes", choices=["planes", "interleaved"])
     ap.add_argument("--force", type=int, default=None)
+    ap.add_argument("--graph", action="store_true", help="decode: time 20 calls captured in one CUDA graph")
     ap.add_argument("--trace", action="store_true", help="decode: print per-CTA phase times of one launch first")
     ap.add_argument("--impl", default="ours", choices=["ours", "triton"],
                     help="triton = time the reference Triton kernels (vLLM's copy) on the same tensors")

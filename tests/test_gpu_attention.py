@@ -13,7 +13,7 @@ pytestmark = pytest.mark.gpu
 GENERIC, PREFILL, DECODE_OR_AUTO, PREFILL_TC = 1, 2, None, 4
 
 
-def _run(inp, scale, path, window=0, softcap=0.0, alibi=None, k_scale=None, v_scale=None, dtype=None):
+def _run(inp, scale, path, window=0, softcap=0.0, alibi=None, k_scale=None, v_scale=None, dtype=None, sinks=None):
     from vllm_triton_backend_b200 import _cabi, ops
 
     dev = "cuda"
@@ -36,19 +36,20 @@ def _run(inp, scale, path, window=0, softcap=0.0, alibi=None, k_scale=None, v_sc
         k_descale=None if k_scale is None else torch.tensor([k_scale], dtype=torch.float32, device=dev),
         v_descale=None if v_scale is None else torch.tensor([v_scale], dtype=torch.float32, device=dev),
         alibi_slopes=None if alibi is None else alibi.to(dev), force_selection=force,
+        sinks=None if sinks is None else sinks.to(dev),
     )
     torch.cuda.synchronize()
     return out.cpu(), _cabi.last_kernel()
 
 
-def _oracle(inp, scale, window=0, softcap=0.0, alibi=None, k_scale=1.0, v_scale=1.0, dtype=None):
+def _oracle(inp, scale, window=0, softcap=0.0, alibi=None, k_scale=1.0, v_scale=1.0, dtype=None, sinks=None):
     q = inp["q"] if dtype is None else inp["q"].to(dtype)
     kc, vc = inp["k_cache"], inp["v_cache"]
     if dtype is not None and kc.dtype != torch.float8_e4m3fn:
         kc, vc = kc.to(dtype), vc.to(dtype)
     return unified_attention_ref(
         q, kc, vc, inp["cu_seqlens_q"], inp["seq_lens"], inp["block_table"], scale, sliding_window=window,
-        softcap=softcap, alibi_slopes=alibi, k_scale=k_scale, v_scale=v_scale, out_dtype=torch.float32,
+        softcap=softcap, alibi_slopes=alibi, k_scale=k_scale, v_scale=v_scale, out_dtype=torch.float32, sinks=sinks,
     )
 
 
@@ -363,3 +364,24 @@ def test_reference_argument_checks():
         ops.unified_attention(causal=False, q_descale=None, **kw)
     with pytest.raises(AssertionError, match="Q scales"):
         ops.unified_attention(causal=True, q_descale=torch.ones(1, device="cuda"), **kw)
+
+
+# ---------------------------------------------------------------------------------
+# attention sinks
+# ---------------------------------------------------------------------------------
+@pytest.mark.parametrize("path", [GENERIC, PREFILL, DECODE_OR_AUTO])
+@pytest.mark.parametrize("fp8", [False, True])
+def test_attention_sinks_match_oracle(path, fp8):
+    Hq, Hkv, D, bs = 16, 2, 128, 16
+    lens = [(1, 700), (1, 33), (1, 4096), (1, 1)] if path is DECODE_OR_AUTO else [(1, 300), (70, 470), (129, 129), (1, 5)]
+    ks, vs = (0.37, 0.61) if fp8 else (1.0, 1.0)
+    inp = make_paged_inputs(lens, Hq, Hkv, D, bs, seed=23, kv_dtype=torch.float8_e4m3fn if fp8 else None, k_scale=ks,
+                            v_scale=vs)
+    sinks = torch.linspace(-3.0, 4.0, Hq, dtype=torch.float32)
+    scale = D ** -0.5
+    out, kern = _run(inp, scale, path, k_scale=ks if fp8 else None, v_scale=vs if fp8 else None, sinks=sinks, window=256)
+    ref = _oracle(inp, scale, window=256, k_scale=ks, v_scale=vs, sinks=sinks)
+    assert_close(out, ref, atol=FP8_ATOL if fp8 else BF16_ATOL, rtol=BF16_RTOL, what=f"sinks ({kern})")
+    # a sink can only shrink the output: compare norms with the sink-free run
+    out0, _ = _run(inp, scale, path, k_scale=ks if fp8 else None, v_scale=vs if fp8 else None, window=256)
+    assert (out.float().norm(dim=-1) <= out0.float().norm(dim=-1) + 1e-2).all()

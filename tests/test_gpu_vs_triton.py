@@ -14,7 +14,7 @@ pytestmark = pytest.mark.gpu
 
 
 def _both(lens, Hq, Hkv, D, bs, dtype=torch.bfloat16, fp8=False, k_scale=1.0, v_scale=1.0, window=0, softcap=0.0,
-          alibi=False, seed=0):
+          alibi=False, seed=0, sinks=False):
     why = triton_reference.available()
     if why:
         pytest.skip(why)
@@ -30,18 +30,21 @@ def _both(lens, Hq, Hkv, D, bs, dtype=torch.bfloat16, fp8=False, k_scale=1.0, v_
     slopes = None
     if alibi:
         slopes = torch.tensor([2.0 ** (-(i + 1) * 8.0 / Hq) for i in range(Hq)], dtype=torch.float32, device=dev)
+    sink_t = None
+    if sinks:
+        sink_t = torch.linspace(-2.0, 3.0, Hq, dtype=torch.float32, device=dev)
     ours = torch.full_like(inp["q"], float("nan"))
     ops.unified_attention(
         q=inp["q"], k=inp["k_cache"], v=inp["v_cache"], out=ours, cu_seqlens_q=inp["cu_seqlens_q"], max_seqlen_q=max_q,
         seqused_k=inp["seq_lens"], max_seqlen_k=max_k, softmax_scale=scale, causal=True,
         window_size=(window - 1, 0) if window > 0 else (-1, -1), block_table=inp["block_table"], softcap=softcap,
-        q_descale=None, k_descale=ks, v_descale=vs, alibi_slopes=slopes,
+        q_descale=None, k_descale=ks, v_descale=vs, alibi_slopes=slopes, sinks=sink_t,
     )
     kern = _cabi.last_kernel()
     ref = torch.full_like(inp["q"], float("nan"))
     triton_reference.TritonReference(max(len(lens), 1), Hq, D, dev)(
         inp["q"], inp["k_cache"], inp["v_cache"], ref, inp["cu_seqlens_q"], max_q, inp["seq_lens"], max_k, scale,
-        inp["block_table"], window=window, softcap=softcap, alibi_slopes=slopes, k_scale=ks, v_scale=vs,
+        inp["block_table"], window=window, softcap=softcap, alibi_slopes=slopes, k_scale=ks, v_scale=vs, sinks=sink_t,
     )
     torch.cuda.synchronize()
     return ours.cpu(), ref.cpu(), kern
@@ -100,3 +103,15 @@ def test_fp8_kv_prefill_matches_triton():
     ours, ref, kern = _both([(300, 300), (64, 1064), (1, 555)], 32, 8, 128, 16, fp8=True, k_scale=0.37, v_scale=0.61,
                             seed=13)
     assert_close(ours, ref, atol=FP8_ATOL, rtol=BF16_RTOL, what=f"fp8 prefill vs triton ({kern})")
+
+
+@pytest.mark.parametrize("lens,D,window", [
+    ([(1, 900), (1, 40), (1, 3000), (1, 1)], 64, 128),       # gpt-oss-like decode: D=64, sliding window + sinks
+    ([(1, 900), (1, 40), (1, 3000)], 128, 0),
+    ([(1, 700), (200, 700), (1, 40), (333, 333)], 64, 128),  # mixed batch
+    ([(512, 512), (64, 1064)], 128, 0),                       # D=128 prefill with sinks: mma.sync kernel, not tcgen05
+])
+def test_attention_sinks_match_triton(lens, D, window):
+    ours, ref, kern = _both(lens, 16, 2, D, 16, window=window, sinks=True, seed=17)
+    assert kern != "attn_prefill_tc"
+    assert_close(ours, ref, atol=BF16_ATOL, rtol=BF16_RTOL, what=f"sinks vs triton ({kern})")

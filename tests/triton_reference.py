@@ -41,7 +41,7 @@ class TritonReference:
         self.segm_expsum = torch.empty_like(self.segm_max)
 
     def __call__(self, q, k_cache, v_cache, out, cu_seqlens_q, max_seqlen_q, seq_lens, max_seqlen_k, scale,
-                 block_table, window=0, softcap=0.0, alibi_slopes=None, k_scale=None, v_scale=None, use_3d=True):
+                 block_table, window=0, softcap=0.0, alibi_slopes=None, k_scale=None, v_scale=None, use_3d=True, sinks=None):
         from vllm.v1.attention.ops.triton_unified_attention import unified_attention
 
         from vllm.v1.kv_cache_interface import KVQuantMode
@@ -61,6 +61,6 @@ class TritonReference:
             seqused_k=seq_lens, max_seqlen_k=max_seqlen_k, softmax_scale=scale, causal=True,
             window_size=(window - 1, 0) if window > 0 else (-1, -1), block_table=block_table, softcap=softcap,
             q_descale=None, k_descale=one if k_scale is None else k_scale, v_descale=one if v_scale is None else v_scale,
-            alibi_slopes=alibi_slopes, kv_quant_mode=mode, **kw,
+            alibi_slopes=alibi_slopes, kv_quant_mode=mode, sinks=sinks, **kw,
         )
         return out

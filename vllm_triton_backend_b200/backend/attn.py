@@ -170,7 +170,7 @@ class B200AttentionBackend(AttentionBackend):
 
     @classmethod
     def supports_sink(cls) -> bool:
-        return False
+        return True  # decode, mma.sync prefill and SIMT kernels; sequences with sinks skip the tcgen05 kernel
 
 
 def split_kv_cache(kv_cache: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor]:
@@ -203,8 +203,12 @@ class B200AttentionImpl(AttentionImpl):
     ) -> None:
         if blocksparse_params is not None:
             raise ValueError("B200Attention does not support block-sparse attention.")  # reference :305-306
-        if sinks is not None:
-            raise NotImplementedError("attention sinks are not implemented for B200AttentionImpl")
+        if sinks is not None and sinks.shape[0] != num_heads:
+            raise ValueError(  # same check as upstream's launcher (triton_unified_attention.py: "Sinks must be ...")
+                f"Sinks must have the same number of heads as the number of heads in the layer. "
+                f"Expected {num_heads}, but got {sinks.shape[0]}."
+            )
+        self.sinks = sinks  # converted to fp32 when the plan is made (weights are loaded by then)
         self.num_heads = num_heads
         self.head_size = head_size
         self.scale = float(scale)
@@ -249,7 +253,8 @@ class B200AttentionImpl(AttentionImpl):
                 ops.CacheWritePlan(key_cache, value_cache, self.kv_cache_dtype, q_dtype, layer._k_scale, layer._v_scale),
                 ops.AttentionPlan(key_cache, value_cache, q_dtype, self.num_heads, self.head_size, self.scale,
                                   self.sliding_window, self.logits_soft_cap, self.alibi_slopes,
-                                  layer._k_scale if fp8 else None, layer._v_scale if fp8 else None),  # element 0 is read (:438)
+                                  layer._k_scale if fp8 else None, layer._v_scale if fp8 else None,  # element 0 is read (:438)
+                                  sinks=self.sinks),
             )
             if len(self._plans) > 8:  # a layer has one cache tensor; bound the dict if a caller keeps reallocating
                 self._plans.clear()

@@ -45,6 +45,7 @@ struct DecodeParams {
   int boxes;       // tps / box_slots
   int stages;
   int tma_split;   // 0: one TMA op per (page box); 1: one per (page box, head, d-chunk)
+  int paired;      // 1: one TMA box carries the K and the V rows of a page ([head][k|v][slot][128 B]); fp8 D=128
   int group;       // query heads per kv head
   int only_q1;     // mixed batch: only sequences with exactly one query token are this kernel's
   float* ws_acc;   // [slots][hpc*group][D]
@@ -371,7 +372,14 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
       uint8_t* vdst = kdst + KV_STAGE_BYTES;
       if (lane == 0) mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)(2 * nbox * boxb));
       __syncwarp();
-      if (P.tma_split == 0) {
+      if (P.paired) {
+        // k_map's third coordinate selects K (0) or V (1); the box takes both
+        const int i = lane;
+        const int tok = tok0 + i * P.box_slots;
+        const int page = page_of(tok / P.a.block_size);
+        if (i < nbox)
+          tma_load_5d(kdst + (size_t)i * 2 * boxb, &k_map, &full_bar[stage], 0, tok % P.a.block_size, 0, head0, page, pol);
+      } else if (P.tma_split == 0) {
         // nbox <= 8: one lane per box
         const int i = lane;
         const int tok = tok0 + i * P.box_slots;
@@ -412,9 +420,12 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
 #pragma unroll
   for (int sb = 0; sb < SUB; ++sb) {
     const int to = tok_off + 16 * sb;
-    tile_off[sb] = (uint32_t)((to / P.box_slots) * boxb + h_local * NDC * P.box_slots * 128 + (to % P.box_slots) * 128);
+    tile_off[sb] = (uint32_t)(((to / P.box_slots) * boxb + h_local * NDC * P.box_slots * 128) * (P.paired ? 2 : 1) +
+                              (to % P.box_slots) * 128);
   }
   const uint32_t dc_stride = (uint32_t)P.box_slots * 128;
+  // V tile relative to the K tile of the same tokens: next plane of the paired box, or the stage's V half
+  const uint32_t v_from_k = P.paired ? dc_stride : (uint32_t)KV_STAGE_BYTES;
 
   const float k_scale = (KV_FP8 && P.a.k_scale) ? *P.a.k_scale : 1.0f;
   const float v_scale = (KV_FP8 && P.a.v_scale) ? *P.a.v_scale : 1.0f;
@@ -515,7 +526,7 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
     first_stage = false;
     if (tok0 < cur.seq_len) {
       const uint32_t kbase_s = smem_u32(stage_base + (size_t)stage * 2 * KV_STAGE_BYTES);
-      const uint32_t vbase_s = kbase_s + KV_STAGE_BYTES;
+      const uint32_t vbase_s = kbase_s + v_from_k;
       const int valid = cur.seq_len - tok0;  // > 0; tile tokens >= valid are out of range
       int win_lo = 0;                        // tokens < win_lo (tile-relative) are outside the sliding window
       if (P.a.sliding_window > 0) win_lo = (cur.seq_len - P.a.sliding_window) - tok0;
@@ -756,6 +767,7 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
           const int hq_in_cta = hl * P.group + nt * 8 + col;  // query head within the CTA's head group
           if (direct) {
             const int hq = cur.hg * P.hpc * P.group + hq_in_cta;
+            if (P.a.sinks) val *= sink_rescale<true>(P.a.sinks[hq], M, L);
             const float o = (L > 0.f) ? val * v_scale / L : 0.f;
             char* orow = static_cast<char*>(P.a.out) + ((int64_t)tq * P.a.out_stride0 + (int64_t)hq * P.a.out_stride1) * 2;
             if constexpr (Q_BF16) reinterpret_cast<__nv_bfloat16*>(orow)[d] = __float2bfloat16_rn(o);
@@ -826,8 +838,10 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
                 L += ml.y * sc;
               }
             }
-            const float inv = (L > 0.f) ? v_scale / L : 0.f;  // 0 when nothing is visible (reference :828)
             const int hq = cur.hg * rec_heads + hq_in;
+            float fs = 1.f;
+            if (P.a.sinks) fs = sink_rescale<true>(P.a.sinks[hq], M, L);  // once per item, here (upstream: segment 0 only)
+            const float inv = (L > 0.f) ? fs * v_scale / L : 0.f;  // 0 when nothing is visible (reference :828)
             char* orow = static_cast<char*>(P.a.out) + ((int64_t)tq * P.a.out_stride0 + (int64_t)hq * P.a.out_stride1) * 2;
             const float o4[4] = {val.x * inv, val.y * inv, val.z * inv, val.w * inv};
 #pragma unroll
@@ -874,6 +888,13 @@ int launch_variant(const b200attn_attention_params& a, DecodeParams& P, cudaStre
   constexpr int KV_STAGE_BYTES = NW * TT * D * ESZ;
   const DeviceInfo& dev = device_info();
   const Tuning& tn = tuning();
+  // K and V of a page in ONE box when they are two equally strided views of one allocation
+  // (both vLLM layouts) and a row is a single 128-byte chunk (fp8, D=128): halves the box count,
+  // which is what bounds small pages (1-2 kv heads per GPU).  tuning().reserved bit 3 forbids it.
+  const int64_t kv_delta = (static_cast<const char*>(a.v_cache) - static_cast<const char*>(a.k_cache));
+  const bool can_pair = KV_FP8 && NDC == 1 && !(tn.reserved & 8) && !(tn.reserved & 1) && kv_delta > 0 &&
+                        kv_delta % 16 == 0 && kv_delta < (1ll << 40) && a.kc_block_stride == a.vc_block_stride &&
+                        a.kc_slot_stride == a.vc_slot_stride && a.kc_head_stride == a.vc_head_stride;
   if (tn.decode_heads_per_cta > 0) {
     P.hpc = pick_hpc(a.num_kv_heads, NW, tn.decode_heads_per_cta);
   } else {
@@ -886,7 +907,7 @@ int launch_variant(const b200attn_attention_params& a, DecodeParams& P, cudaStre
     while (hpc < NW && a.num_kv_heads % (hpc * 2) == 0) {
       const int tps = NW * TT / hpc;
       const int slots = a.block_size < tps ? a.block_size : tps;
-      if (hpc * NDC * slots * 128 >= min_box) break;
+      if (hpc * NDC * slots * 128 * (can_pair ? 2 : 1) >= min_box) break;
       hpc *= 2;
     }
     P.hpc = hpc;
@@ -896,6 +917,7 @@ int launch_variant(const b200attn_attention_params& a, DecodeParams& P, cudaStre
   P.box_slots = a.block_size < P.tps ? a.block_size : P.tps;
   P.boxes = P.tps / P.box_slots;
   P.tma_split = tn.reserved & 1;
+  P.paired = 0;
   const int fixed = NW * 8 * D * 4 + NW * 8 * 2 * 4 + 2 * kMaxStages * 8 + 64 + 1024 /*alignment slack*/;
   int stages = (dev.max_smem_optin - fixed) / (2 * KV_STAGE_BYTES);
   if (stages > kMaxStages) stages = kMaxStages;
@@ -909,8 +931,9 @@ int launch_variant(const b200attn_attention_params& a, DecodeParams& P, cudaStre
 
   CUtensorMap kmap, vmap;
   const int box_heads = P.tma_split ? 1 : P.hpc, box_dc = P.tma_split ? 1 : NDC;
+  P.paired = (can_pair && P.hpc * NDC * P.box_slots * 128 < 16384) ? 1 : 0;
   int rc = make_kv_map(&kmap, a.k_cache, ESZ, D, a.block_size, a.num_kv_heads, a.num_blocks, a.kc_block_stride,
-                       a.kc_slot_stride, a.kc_head_stride, P.box_slots, box_heads, box_dc);
+                       a.kc_slot_stride, a.kc_head_stride, P.box_slots, box_heads, box_dc, P.paired ? kv_delta : 0);
   if (rc) return rc;
   rc = make_kv_map(&vmap, a.v_cache, ESZ, D, a.block_size, a.num_kv_heads, a.num_blocks, a.vc_block_stride,
                    a.vc_slot_stride, a.vc_head_stride, P.box_slots, box_heads, box_dc);
@@ -989,7 +1012,6 @@ bool decode_supported(const b200attn_attention_params& p, const char** why, bool
     return no("cache strides not 16-byte multiples");
   if ((reinterpret_cast<uintptr_t>(p.k_cache) & 15) || (reinterpret_cast<uintptr_t>(p.v_cache) & 15)) return no("cache base alignment");
   if ((reinterpret_cast<uintptr_t>(p.q) & 7) || (p.q_stride0 % 4) || (p.q_stride1 % 4)) return no("query alignment");
-  if (p.sinks) return no("sinks");
   return true;
 }
 

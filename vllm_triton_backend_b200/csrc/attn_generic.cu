@@ -112,7 +112,9 @@ __global__ void __launch_bounds__(128) attn_generic_kernel(b200attn_attention_pa
   }
   QT* orow = static_cast<QT*>(p.out) + (int64_t)t * p.out_stride0 + (int64_t)h * p.out_stride1;
   // L == 0 happens only when no key is visible; the reference's reduce returns 0 there (:828)
-  const float inv_l = l > 0.f ? 1.0f / l : 0.f;
+  float f = 1.f;
+  if (p.sinks) f = sink_rescale<false>(p.sinks[h], m, l);
+  const float inv_l = l > 0.f ? f / l : 0.f;
 #pragma unroll
   for (int i = 0; i < kMaxDPerLane; ++i) {
     const int d = lane + 32 * i;

@@ -303,7 +303,9 @@ attn_prefill_kernel(const b200attn_attention_params p, const int block_q, const 
     if (!row_ok[ri]) continue;
     const int r = warp * 16 + gid + 8 * ri;
     const int hq = kvh * group + r % group;
-    const float inv = (l > 0.f) ? v_scale / l : 0.f;
+    float f = 1.f;
+    if (p.sinks) f = sink_rescale<true>(p.sinks[hq], m_run[ri], l);
+    const float inv = (l > 0.f) ? f * v_scale / l : 0.f;
     char* orow = static_cast<char*>(p.out) + ((int64_t)(q_start + row_qpos[ri]) * p.out_stride0 + (int64_t)hq * p.out_stride1) * 2;
 #pragma unroll
     for (int dt = 0; dt < DT; ++dt) {
@@ -359,7 +361,6 @@ bool prefill_supported(const b200attn_attention_params& p, const char** why) {
   if ((reinterpret_cast<uintptr_t>(p.k_cache) & 15) || (reinterpret_cast<uintptr_t>(p.v_cache) & 15)) return no("cache base alignment");
   if ((reinterpret_cast<uintptr_t>(p.q) & 15) || (p.q_stride0 % 8) || (p.q_stride1 % 8)) return no("query alignment");
   if ((reinterpret_cast<uintptr_t>(p.out) & 3) || (p.out_stride0 % 2) || (p.out_stride1 % 2)) return no("output alignment");
-  if (p.sinks) return no("sinks");
   return true;
 }
 

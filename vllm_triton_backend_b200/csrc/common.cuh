@@ -41,7 +41,7 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
 EncodeTiledFn encode_tiled_fn();
 // TMA descriptors (tma_maps.cu); small per-thread cache keyed by pointer + strides
 int make_kv_map(CUtensorMap* out, const void* base, int esz, int D, int bs, int hkv, int64_t nb, int64_t s_block,
-                int64_t s_slot, int64_t s_head, int box_slots, int box_heads, int box_dc);
+                int64_t s_slot, int64_t s_head, int box_slots, int box_heads, int box_dc, int64_t pair_bytes = 0);
 int make_thd_map(CUtensorMap* out, const void* base, int D, int heads, int64_t tokens, int64_t s_token, int64_t s_head,
                  int box_heads, int box_tokens);
 
@@ -119,6 +119,22 @@ __device__ __forceinline__ float softcap_fn(float x, float cap, float inv_cap) {
   float e = __expf(2.0f * x * inv_cap);
   // tanh(y) = 1 - 2/(e^{2y}+1); e=inf -> 1, e=0 -> -1
   return cap * (1.0f - __fdividef(2.0f, e + 1.0f));
+}
+
+// Attention sink (upstream `init_softmax_M`, vllm/v1/attention/ops/triton_attention_helpers.py):
+// one extra key per head with logit `sink` (natural units, not scaled) and a zero value row.
+// Applied once, after the last KV tile: `m` is the final running max (`m_is_log2`: in log2
+// units) and `l` the running sum; returns the factor for the un-normalised accumulator.
+template <bool m_is_log2> __device__ __forceinline__ float sink_rescale(float sink, float m, float& l) {
+  const float s = m_is_log2 ? sink * kLog2e : sink;
+  const float mx = fmaxf(m, s);
+  if (mx == -INFINITY) {
+    l = 0.f;
+    return 0.f;
+  }
+  const float f = (m == -INFINITY) ? 0.f : (m_is_log2 ? exp2f(m - mx) : __expf(m - mx));
+  l = l * f + (m_is_log2 ? exp2f(s - mx) : __expf(s - mx));
+  return f;
 }
 
 // ---- mbarrier / TMA / ldmatrix / mma wrappers --------------------------------

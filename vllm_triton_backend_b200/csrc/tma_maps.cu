@@ -45,10 +45,13 @@ void remember(const MapKey& key, const CUtensorMap& map) {
 
 }  // namespace
 
-// 5-D view of a paged cache: (128-byte chunk elems, slot, chunk, head, block)
+// 5-D view of a paged cache: (128-byte chunk elems, slot, chunk, head, block).
+// `pair_bytes` > 0 (rows of one 128-byte chunk only): the third dimension is not the chunk index
+// but the K/V selector — extent 2, stride = distance from the K view to the V view — and a box
+// takes both, so one copy brings the K and the V rows of a page: [head][k|v][slot][128 B].
 int make_kv_map(CUtensorMap* out, const void* base, int esz, int D, int bs, int hkv, int64_t nb, int64_t s_block,
-                int64_t s_slot, int64_t s_head, int box_slots, int box_heads, int box_dc) {
-  MapKey key{base, s_block, s_slot, s_head, nb, bs, hkv, D, esz, box_slots, box_heads, box_dc, 0};
+                int64_t s_slot, int64_t s_head, int box_slots, int box_heads, int box_dc, int64_t pair_bytes) {
+  MapKey key{base, s_block, s_slot, s_head, nb + (pair_bytes << 20), bs, hkv, D, esz, box_slots, box_heads, box_dc, 0};
   if (lookup(key, out)) return B200ATTN_OK;
   EncodeTiledFn fn = encode_tiled_fn();
   if (!fn) {
@@ -59,6 +62,13 @@ int make_kv_map(CUtensorMap* out, const void* base, int esz, int D, int bs, int 
   cuuint64_t dims[5] = {(cuuint64_t)epc, (cuuint64_t)bs, (cuuint64_t)(D * esz / 128), (cuuint64_t)hkv, (cuuint64_t)nb};
   cuuint64_t strides[4] = {(cuuint64_t)(s_slot * esz), 128, (cuuint64_t)(s_head * esz), (cuuint64_t)(s_block * esz)};
   cuuint32_t box[5] = {(cuuint32_t)epc, (cuuint32_t)box_slots, (cuuint32_t)box_dc, (cuuint32_t)box_heads, 1};
+  if (pair_bytes > 0) {
+    if (D * esz != 128) {
+      set_error("kv map: K/V pairing needs 128-byte rows");
+      return B200ATTN_E_UNSUPPORTED;
+    }
+    dims[2] = 2, strides[1] = (cuuint64_t)pair_bytes, box[2] = 2;
+  }
   cuuint32_t estr[5] = {1, 1, 1, 1, 1};
   CUtensorMapDataType dt = esz == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_UINT16;
   CUresult r = fn(out, dt, 5, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,

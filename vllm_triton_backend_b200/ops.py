@@ -144,7 +144,7 @@ def scaled_fp8_quant(x: torch.Tensor, scale: torch.Tensor) -> Tuple[torch.Tensor
 
 def build_attention_params(
     q, k, v, out, cu_seqlens_q, max_seqlen_q, seqused_k, max_seqlen_k, softmax_scale, window_size, block_table,
-    softcap, k_descale, v_descale, alibi_slopes, path, workspace,
+    softcap, k_descale, v_descale, alibi_slopes, path, workspace, sinks=None,
 ) -> AttentionParams:
     if q.dim() != 3 or k.dim() != 4 or v.dim() != 4:
         raise ValueError("q must be [T, Hq, D]; k, v must be [NB, bs, Hkv, D]")
@@ -165,7 +165,9 @@ def build_attention_params(
     p.alibi_slopes = alibi_slopes.data_ptr() if alibi_slopes is not None else None
     p.k_scale = k_descale.data_ptr() if k_descale is not None else None
     p.v_scale = v_descale.data_ptr() if v_descale is not None else None
-    p.sinks = None
+    if sinks is not None and (sinks.dtype != torch.float32 or sinks.shape[0] != q.shape[1] or not sinks.is_contiguous()):
+        raise ValueError("sinks must be a contiguous float32 tensor with one entry per query head")
+    p.sinks = sinks.data_ptr() if sinks is not None else None
     p.softmax_scale = float(softmax_scale)
     p.softcap = float(softcap or 0.0)
     p.sliding_window = int(1 + window_size[0]) if window_size is not None else 0  # reference :915
@@ -209,13 +211,14 @@ def unified_attention(
     avg_seqlen_k=None,
     force_selection: Optional[int] = None,  # None, 2 (2D kernel), 3 (3D kernel) as in the reference; 1 = SIMT net
     workspace: Optional[torch.Tensor] = None,
+    sinks: Optional[torch.Tensor] = None,  # [Hq] float32 (upstream keyword)
     **_ignored,
 ) -> None:
     if not causal:
         raise AssertionError("Only causal attention is supported")  # reference :861
     if q_descale is not None:
         raise AssertionError("Q scales not supported")  # reference :862
-    _require_cuda(q, k, v, out, cu_seqlens_q, seqused_k, block_table)
+    _require_cuda(q, k, v, out, cu_seqlens_q, seqused_k, block_table, sinks)
     if q.element_size() < 2:
         # the reference's fp8-Q branch ignores k/v scales; not offered
         raise ValueError("fp8 queries are not supported; keep Q in bf16/fp16")
@@ -239,7 +242,7 @@ def unified_attention(
         workspace = get_workspace(q.device, need)
     p = build_attention_params(
         q, k, v, out, cu_seqlens_q, max_seqlen_q, seqused_k, max_seqlen_k, softmax_scale, window_size, block_table,
-        softcap, k_descale, v_descale, alibi_slopes, path, workspace,
+        softcap, k_descale, v_descale, alibi_slopes, path, workspace, sinks,
     )
     _cabi.check(_cabi.load_library().b200attn_unified_attention(ctypes.byref(p), _stream_ptr(q)))
 
@@ -258,8 +261,12 @@ class AttentionPlan:
     __slots__ = ("p", "_ref", "_fn", "_keep", "_ws_ptr", "num_q_heads", "head_size", "q_dtype")
 
     def __init__(self, k, v, q_dtype, num_q_heads, head_size, softmax_scale, window_size, softcap, alibi_slopes,
-                 k_descale, v_descale):
-        _require_cuda(k, v, alibi_slopes, k_descale, v_descale)
+                 k_descale, v_descale, sinks=None):
+        _require_cuda(k, v, alibi_slopes, k_descale, v_descale, sinks)
+        if sinks is not None:
+            if sinks.shape[0] != num_q_heads:
+                raise ValueError("sinks must have one entry per query head")
+            sinks = sinks.detach().to(torch.float32).contiguous()
         if k.dim() != 4 or v.dim() != 4 or k.stride(3) != 1 or v.stride(3) != 1:
             raise ValueError("k, v must be [NB, bs, Hkv, D] views with a contiguous innermost dimension")
         q_dt, kv_dt = _DTYPE.get(q_dtype), _DTYPE.get(k.dtype)
@@ -272,7 +279,7 @@ class AttentionPlan:
         p.alibi_slopes = alibi_slopes.data_ptr() if alibi_slopes is not None else None
         p.k_scale = k_descale.data_ptr() if k_descale is not None else None
         p.v_scale = v_descale.data_ptr() if v_descale is not None else None
-        p.sinks = None
+        p.sinks = sinks.data_ptr() if sinks is not None else None
         p.softmax_scale = float(softmax_scale)
         p.softcap = float(softcap or 0.0)
         p.sliding_window = int(1 + window_size[0]) if window_size is not None else 0
@@ -283,7 +290,7 @@ class AttentionPlan:
         p.vc_block_stride, p.vc_slot_stride, p.vc_head_stride = v.stride(0), v.stride(1), v.stride(2)
         self.p, self._ref = p, ctypes.byref(p)
         self._fn = _cabi.load_library().b200attn_unified_attention
-        self._keep = (k, v, alibi_slopes, k_descale, v_descale)  # the struct holds raw pointers into these
+        self._keep = (k, v, alibi_slopes, k_descale, v_descale, sinks)  # the struct holds raw pointers into these
         self._ws_ptr = None
         self.num_q_heads, self.head_size, self.q_dtype = num_q_heads, head_size, q_dtype
 
