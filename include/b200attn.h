@@ -153,6 +153,41 @@ B200ATTN_API int b200attn_scaled_fp8_quant(void* out_fp8, const void* in, int64_
                               int32_t src_dtype, const float* scale,
                               b200attn_stream_t stream);
 
+/* ---- K5: rotary embedding of q and k (in place) + KV-cache write, one launch ----
+ * Replaces the two launches vLLM issues before attention:
+ * rotary_embedding (vllm/csrc/pos_encoding_kernels.cu) and reshape_and_cache_flash
+ * (vllm/csrc/cache_kernels.cu:286-358), behind
+ * AttentionImpl.do_rope_and_kv_cache_update (vLLM 0.22, vllm/v1/attention/backend.py:823-841).
+ *   for t < rope_tokens, every q and k head, pair (x, y) of the first rot_dim dims
+ *   (neox: (j, j + rot_dim/2); else (2j, 2j+1)), c = cos_sin_cache[positions[t]][j],
+ *   s = cos_sin_cache[positions[t]][rot_dim/2 + j]:
+ *       x' = R(R(x c) - R(y s)),  y' = R(R(y c) + R(x s))     R = round to the 16-bit type
+ *   for t < cache_tokens with slot_mapping[t] >= 0: the rotated k row and the v row go to
+ *   the cache exactly as b200attn_reshape_and_cache_flash writes them.
+ * Strides in elements; rows must be 16-byte aligned (B200ATTN_E_ALIGNMENT otherwise). */
+typedef struct b200attn_rope_cache_params {
+  void* q;                      /* [T, Hq, D]  rotated in place                     */
+  void* k;                      /* [T, Hkv, D] rotated in place                     */
+  const void* v;                /* [T, Hkv, D]                                      */
+  const int64_t* positions;     /* [rope_tokens]                                    */
+  const void* cos_sin_cache;    /* [max_position, rot_dim], dtype of q              */
+  void* k_cache;                /* [NB, bs, Hkv, D] views                           */
+  void* v_cache;
+  const int64_t* slot_mapping;  /* [cache_tokens], -1 = padding                     */
+  const float* k_scale;         /* device scalars, fp8 cache only                   */
+  const float* v_scale;
+  int64_t rope_tokens, cache_tokens;
+  int64_t q_stride0, q_stride1, k_stride0, k_stride1, v_stride0, v_stride1;
+  int64_t kc_block_stride, kc_slot_stride, kc_head_stride;
+  int64_t vc_block_stride, vc_slot_stride, vc_head_stride;
+  int32_t num_q_heads, num_kv_heads, head_size, rot_dim, block_size;
+  int32_t is_neox;              /* 1: GPT-NeoX halves, 0: GPT-J interleaved pairs   */
+  int32_t src_dtype;            /* BF16 / F16                                       */
+  int32_t kv_dtype;             /* == src_dtype or FP8_E4M3                         */
+} b200attn_rope_cache_params;
+
+B200ATTN_API int b200attn_rope_and_cache_flash(const b200attn_rope_cache_params* p, b200attn_stream_t stream);
+
 /* ---- introspection ---------------------------------------------------------*/
 B200ATTN_API int b200attn_abi_version(void);
 B200ATTN_API const char* b200attn_last_error(void);

@@ -27,6 +27,7 @@ EXPORTED_SYMBOLS = [
     "b200attn_workspace_bytes",
     "b200attn_unified_attention",
     "b200attn_scaled_fp8_quant",
+    "b200attn_rope_and_cache_flash",
     "b200attn_abi_version",
     "b200attn_last_error",
     "b200attn_launch_count",
@@ -53,6 +54,22 @@ class AttentionParams(Structure):
         ("kc_block_stride", c_int64), ("kc_slot_stride", c_int64), ("kc_head_stride", c_int64),
         ("vc_block_stride", c_int64), ("vc_slot_stride", c_int64), ("vc_head_stride", c_int64),
         ("workspace", c_void_p), ("workspace_bytes", c_uint64),
+    ]
+
+
+class RopeCacheParams(Structure):
+    """Mirror of `b200attn_rope_cache_params` (include/b200attn.h)."""
+
+    _fields_ = [
+        ("q", c_void_p), ("k", c_void_p), ("v", c_void_p), ("positions", c_void_p), ("cos_sin_cache", c_void_p),
+        ("k_cache", c_void_p), ("v_cache", c_void_p), ("slot_mapping", c_void_p), ("k_scale", c_void_p),
+        ("v_scale", c_void_p), ("rope_tokens", c_int64), ("cache_tokens", c_int64),
+        ("q_stride0", c_int64), ("q_stride1", c_int64), ("k_stride0", c_int64), ("k_stride1", c_int64),
+        ("v_stride0", c_int64), ("v_stride1", c_int64),
+        ("kc_block_stride", c_int64), ("kc_slot_stride", c_int64), ("kc_head_stride", c_int64),
+        ("vc_block_stride", c_int64), ("vc_slot_stride", c_int64), ("vc_head_stride", c_int64),
+        ("num_q_heads", c_int32), ("num_kv_heads", c_int32), ("head_size", c_int32), ("rot_dim", c_int32),
+        ("block_size", c_int32), ("is_neox", c_int32), ("src_dtype", c_int32), ("kv_dtype", c_int32),
     ]
 
 
@@ -84,6 +101,8 @@ def load_library() -> ctypes.CDLL:
     lib.b200attn_workspace_bytes.argtypes = [c_int32] * 5
     lib.b200attn_unified_attention.restype = c_int32
     lib.b200attn_unified_attention.argtypes = [POINTER(AttentionParams), c_void_p]
+    lib.b200attn_rope_and_cache_flash.restype = c_int32
+    lib.b200attn_rope_and_cache_flash.argtypes = [POINTER(RopeCacheParams), c_void_p]
     lib.b200attn_scaled_fp8_quant.restype = c_int32
     lib.b200attn_scaled_fp8_quant.argtypes = [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int32, c_void_p, c_void_p]
     lib.b200attn_abi_version.restype = c_int32

@@ -268,6 +268,17 @@ class B200AttentionImpl(AttentionImpl):
             return
         self._plans_for(layer, kv_cache, key.dtype)[0](key, value, slot_mapping)
 
+    def fused_rope_kvcache_supported(self) -> bool:
+        """RoPE + cache write in one launch (ops.rope_and_cache_flash); vLLM's
+        RopeKVCacheFusionPass asks before rewriting the graph."""
+        return self.kv_sharing_target_layer_name is None and self.head_size % 8 == 0
+
+    def do_rope_and_kv_cache_update(self, layer, query, key, value, positions, cos_sin_cache, is_neox, kv_cache,
+                                    layer_slot_mapping) -> None:
+        key_cache, value_cache = self._views(kv_cache)
+        ops.rope_and_cache_flash(query, key, value, positions, cos_sin_cache, is_neox, key_cache, value_cache,
+                                 layer_slot_mapping, self.kv_cache_dtype, layer._k_scale, layer._v_scale)
+
     def forward(
         self,
         layer,

@@ -907,7 +907,7 @@ int launch_variant(const b200attn_attention_params& a, DecodeParams& P, cudaStre
     while (hpc < NW && a.num_kv_heads % (hpc * 2) == 0) {
       const int tps = NW * TT / hpc;
       const int slots = a.block_size < tps ? a.block_size : tps;
-      if (hpc * NDC * slots * 128 * (can_pair ? 2 : 1) >= min_box) break;
+      if (hpc * NDC * slots * 128 >= min_box) break;
       hpc *= 2;
     }
     P.hpc = hpc;
@@ -931,7 +931,7 @@ int launch_variant(const b200attn_attention_params& a, DecodeParams& P, cudaStre
 
   CUtensorMap kmap, vmap;
   const int box_heads = P.tma_split ? 1 : P.hpc, box_dc = P.tma_split ? 1 : NDC;
-  P.paired = (can_pair && P.hpc * NDC * P.box_slots * 128 < 16384) ? 1 : 0;
+  P.paired = (can_pair && P.hpc * NDC * P.box_slots * 128 <= 16384) ? 1 : 0;  // measured: profiles/r01_kbench_paired.jsonl
   int rc = make_kv_map(&kmap, a.k_cache, ESZ, D, a.block_size, a.num_kv_heads, a.num_blocks, a.kc_block_stride,
                        a.kc_slot_stride, a.kc_head_stride, P.box_slots, box_heads, box_dc, P.paired ? kv_delta : 0);
   if (rc) return rc;

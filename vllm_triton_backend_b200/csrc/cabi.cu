@@ -135,6 +135,14 @@ int b200attn_reshape_and_cache_flash(const void* key, const void* value, void* k
                             reinterpret_cast<cudaStream_t>(stream));
 }
 
+int b200attn_rope_and_cache_flash(const b200attn_rope_cache_params* p, b200attn_stream_t stream) {
+  if (!p) {
+    set_error("rope_and_cache_flash: null params");
+    return B200ATTN_E_NULL;
+  }
+  return launch_rope_cache(*p, reinterpret_cast<cudaStream_t>(stream));
+}
+
 int b200attn_scaled_fp8_quant(void* out_fp8, const void* in, int64_t num_rows, int64_t row_elems,
                               int64_t in_row_stride, int32_t src_dtype, const float* scale,
                               b200attn_stream_t stream) {

@@ -63,6 +63,7 @@ int launch_cache_write(const void* key, const void* value, void* k_cache, void* 
                        int kv_dtype, const float* k_scale, const float* v_scale, cudaStream_t stream);
 int launch_scaled_fp8_quant(void* out, const void* in, int64_t rows, int64_t row_elems, int64_t in_row_stride,
                             int src_dtype, const float* scale, cudaStream_t stream);
+int launch_rope_cache(const b200attn_rope_cache_params& p, cudaStream_t stream);
 int launch_attn_generic(const b200attn_attention_params& p, cudaStream_t stream);
 int launch_attn_decode(const b200attn_attention_params& p, cudaStream_t stream, bool only_single_token_seqs = false);
 bool decode_supported(const b200attn_attention_params& p, const char** why, bool mixed_batch = false);

@@ -361,3 +361,58 @@ class CacheWritePlan:
                       torch.cuda.current_stream(key.device).cuda_stream)
         if rc:
             _cabi.check(rc)
+
+
+def rope_and_cache_flash(
+    query: torch.Tensor,  # [T, Hq, D] (any token stride: usually a view into the fused qkv projection)
+    key: torch.Tensor,  # [T, Hkv, D]
+    value: torch.Tensor,  # [T, Hkv, D]
+    positions: torch.Tensor,  # int64 [T]
+    cos_sin_cache: torch.Tensor,  # [max_position, rot_dim], query dtype
+    is_neox: bool,
+    key_cache: torch.Tensor,  # [NB, bs, Hkv, D] view
+    value_cache: torch.Tensor,
+    slot_mapping: torch.Tensor,  # int64 [<=T]
+    kv_cache_dtype: str,
+    k_scale,
+    v_scale,
+) -> None:
+    """Rotary embedding of `query`/`key` in place and the KV-cache write, in one launch
+    (`AttentionImpl.do_rope_and_kv_cache_update`, vLLM 0.22 vllm/v1/attention/backend.py:823-841;
+    unfused pair: `ops.rotary_embedding` + `reshape_and_cache_flash`, reference triton_attn.py:396-405)."""
+    _require_cuda(query, key, value, positions, cos_sin_cache, key_cache, value_cache, slot_mapping)
+    if query.dim() != 3 or key.dim() != 3 or value.dim() != 3 or key_cache.dim() != 4:
+        raise ValueError("query/key/value must be [T, H, D] and the caches [NB, bs, Hkv, D]")
+    if query.stride(2) != 1 or key.stride(2) != 1 or value.stride(2) != 1 or key_cache.stride(3) != 1 or value_cache.stride(3) != 1:
+        raise ValueError("innermost dimension must be contiguous")
+    if positions.dtype != torch.int64 or slot_mapping.dtype != torch.int64:
+        raise ValueError("positions and slot_mapping must be int64")
+    if positions.dim() != 1:
+        raise ValueError("positions must be 1-D (mrope is not supported)")
+    if cos_sin_cache.dtype != query.dtype or key.dtype != query.dtype or value.dtype != query.dtype:
+        raise ValueError("query, key, value and cos_sin_cache must share one 16-bit dtype")
+    src_dt = _DTYPE.get(query.dtype)
+    if src_dt not in (_cabi.BF16, _cabi.F16):
+        raise ValueError(f"unsupported dtype {query.dtype}")
+    p = _cabi.RopeCacheParams()
+    if kv_cache_dtype.startswith("fp8"):
+        if kv_cache_dtype not in ("fp8", "fp8_e4m3") or key_cache.element_size() != 1:
+            raise ValueError(f"unsupported kv_cache_dtype {kv_cache_dtype!r} / cache element size")
+        ks, vs = _scalar_tensor(k_scale, query.device), _scalar_tensor(v_scale, query.device)
+        p.kv_dtype, p.k_scale, p.v_scale = _cabi.FP8_E4M3, ks.data_ptr(), vs.data_ptr()
+    else:
+        if key_cache.dtype != query.dtype:
+            raise ValueError(f"kv cache dtype {key_cache.dtype} != {query.dtype} with kv_cache_dtype={kv_cache_dtype!r}")
+        p.kv_dtype, p.k_scale, p.v_scale = src_dt, None, None
+    p.q, p.k, p.v = query.data_ptr(), key.data_ptr(), value.data_ptr()
+    p.positions, p.cos_sin_cache = positions.data_ptr(), cos_sin_cache.data_ptr()
+    p.k_cache, p.v_cache, p.slot_mapping = key_cache.data_ptr(), value_cache.data_ptr(), slot_mapping.data_ptr()
+    p.rope_tokens, p.cache_tokens = min(positions.shape[0], query.shape[0]), min(slot_mapping.shape[0], key.shape[0])
+    p.q_stride0, p.q_stride1 = query.stride(0), query.stride(1)
+    p.k_stride0, p.k_stride1 = key.stride(0), key.stride(1)
+    p.v_stride0, p.v_stride1 = value.stride(0), value.stride(1)
+    p.kc_block_stride, p.kc_slot_stride, p.kc_head_stride = key_cache.stride(0), key_cache.stride(1), key_cache.stride(2)
+    p.vc_block_stride, p.vc_slot_stride, p.vc_head_stride = value_cache.stride(0), value_cache.stride(1), value_cache.stride(2)
+    p.num_q_heads, p.num_kv_heads, p.head_size = query.shape[1], key.shape[1], query.shape[2]
+    p.rot_dim, p.block_size, p.is_neox, p.src_dtype = cos_sin_cache.shape[1], key_cache.shape[1], int(bool(is_neox)), src_dt
+    _cabi.check(_cabi.load_library().b200attn_rope_and_cache_flash(ctypes.byref(p), _stream_ptr(query)))
