@@ -161,7 +161,8 @@ B200ATTN_API int b200attn_scaled_fp8_quant(void* out_fp8, const void* in, int64_
  *   for t < rope_tokens, every q and k head, pair (x, y) of the first rot_dim dims
  *   (neox: (j, j + rot_dim/2); else (2j, 2j+1)), c = cos_sin_cache[positions[t]][j],
  *   s = cos_sin_cache[positions[t]][rot_dim/2 + j]:
- *       x' = R(R(x c) - R(y s)),  y' = R(R(y c) + R(x s))     R = round to the 16-bit type
+ *       x' = R(x c - y s),  y' = R(y c + x s)    fp32 arithmetic, R = one rounding to the 16-bit type
+ *       (what vLLM 0.22's compiled rotary_embedding produces, bit for bit)
  *   for t < cache_tokens with slot_mapping[t] >= 0: the rotated k row and the v row go to
  *   the cache exactly as b200attn_reshape_and_cache_flash writes them.
  * Strides in elements; rows must be 16-byte aligned (B200ATTN_E_ALIGNMENT otherwise). */

@@ -36,11 +36,11 @@ def test_rotation_matches_float64_and_preserves_norm(is_neox, rot, D):
     assert torch.equal(q2[0], q[0]) and torch.equal(k2[0], k[0])  # position 0 is the identity
 
 
-def test_bf16_rounds_after_every_operation():
+def test_bf16_is_fp32_arithmetic_rounded_once():
     x = torch.tensor([[[0.3379, 0.7773]]], dtype=torch.bfloat16)
     cs = torch.tensor([[math.cos(1.0), math.sin(1.0)]], dtype=torch.bfloat16)
     out, _ = rotary_embedding_ref(torch.tensor([0]), x, x.clone(), cs, True)
-    r = lambda v: torch.tensor(v, dtype=torch.float32).bfloat16().float().item()
     a, b, c, s = (float(v) for v in (x[0, 0, 0], x[0, 0, 1], cs[0, 0], cs[0, 1]))
-    assert float(out[0, 0, 0]) == r(r(a * c) - r(b * s))
-    assert float(out[0, 0, 1]) == r(r(b * c) + r(a * s))
+    r = lambda v: torch.tensor(v, dtype=torch.float64).float().bfloat16().float().item()
+    assert float(out[0, 0, 0]) == r(a * c - b * s)  # products of bf16 values are exact in fp32/fp64
+    assert float(out[0, 0, 1]) == r(b * c + a * s)

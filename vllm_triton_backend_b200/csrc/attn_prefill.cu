@@ -37,7 +37,7 @@ template <int ROWB> __device__ __forceinline__ uint32_t swz_off(int r, int c) {
 template <int D, bool MMA_BF16, bool Q_BF16, bool KV_FP8>
 __global__ void __launch_bounds__(NWARPS * 32, (D <= 128) ? 2 : 1)
 attn_prefill_kernel(const b200attn_attention_params p, const int block_q, const int group, const int min_q_len,
-                    const int max_q_len) {
+                    const int max_q_len, const int qb_per_seq) {
   constexpr int ROWB = D * 2;           // smem row bytes (operands are 2-byte in smem)
   constexpr int CPR = ROWB / 16;        // 16-byte chunks per row
   constexpr int KSTEPS = D / 16;
@@ -52,17 +52,25 @@ attn_prefill_kernel(const b200attn_attention_params p, const int block_q, const 
   const int gid = lane >> 2, t4 = lane & 3;
   const int q_block_global = blockIdx.x, kvh = blockIdx.y;
 
-  // ---- q-block -> sequence (binary search over cu_seqlens_q // BLOCK_Q + idx) --
-  int left = 0, right = p.num_seqs;
-  while (left < right) {
-    const int mid = (left + right) >> 1;
-    const int mid_val = p.cu_seqlens_q[mid] / block_q + mid;
-    if (mid_val <= q_block_global) left = mid + 1; else right = mid;
+  // ---- q-block -> sequence ------------------------------------------------------
+  int b, q_block_local;
+  if (qb_per_seq > 0) {
+    // launch restricted to short queries: a fixed number of q-blocks per sequence, no search
+    // (most CTAs of a mixed batch exit here, so the exit has to be cheap)
+    b = q_block_global / qb_per_seq, q_block_local = q_block_global % qb_per_seq;
+  } else {
+    // binary search over cu_seqlens_q // BLOCK_Q + idx (reference :32-52)
+    int left = 0, right = p.num_seqs;
+    while (left < right) {
+      const int mid = (left + right) >> 1;
+      const int mid_val = p.cu_seqlens_q[mid] / block_q + mid;
+      if (mid_val <= q_block_global) left = mid + 1; else right = mid;
+    }
+    b = left - 1;
+    q_block_local = q_block_global - (p.cu_seqlens_q[b] / block_q + b);
   }
-  const int b = left - 1;
   const int q_start = p.cu_seqlens_q[b];
   const int q_len = p.cu_seqlens_q[b + 1] - q_start;
-  const int q_block_local = q_block_global - (q_start / block_q + b);
   if (q_block_local * block_q >= q_len) return;
   if (q_len < min_q_len || q_len > max_q_len) return;  // another launch covers this sequence
   const int seq_len = p.seq_lens[b];
@@ -330,8 +338,15 @@ int launch_variant(const b200attn_attention_params& a, cudaStream_t stream, QLen
     }
     attr_set = true;
   }
-  const dim3 grid((unsigned)(a.num_tokens / block_q + a.num_seqs), (unsigned)a.num_kv_heads);
-  kern<<<grid, NWARPS * 32, smem, stream>>>(a, block_q, group, range.min_q_len, range.max_q_len);
+  // host-int upper bounds on the q-blocks: the reference's (T // BLOCK_Q + B, :886-889), or, when the launch
+  // only takes queries up to max_q_len, B * ceil(max_q_len / BLOCK_Q) with a direct block -> sequence map
+  long long nblocks = (long long)a.num_tokens / block_q + a.num_seqs;
+  int qb_per_seq = 0;
+  const int longest = range.max_q_len < a.max_seqlen_q ? range.max_q_len : a.max_seqlen_q;
+  const long long per_seq = ((long long)longest + block_q - 1) / block_q;
+  if (per_seq >= 1 && per_seq * a.num_seqs < nblocks) qb_per_seq = (int)per_seq, nblocks = per_seq * a.num_seqs;
+  const dim3 grid((unsigned)nblocks, (unsigned)a.num_kv_heads);
+  kern<<<grid, NWARPS * 32, smem, stream>>>(a, block_q, group, range.min_q_len, range.max_q_len, qb_per_seq);
   note_launch("attn_prefill_mma");
   return check_launch("attn_prefill");
 }
