@@ -93,3 +93,25 @@ def test_platform_selects_our_backend_unconditionally():
     from vllm_triton_backend_b200.backend.platform import B200Platform
 
     assert B200Platform.get_attn_backend_cls(None, None, 32) == BACKEND_PATH
+
+
+def test_kv_cache_stride_order_follows_the_configured_layout():
+    from vllm.v1.attention.backends import utils as vutils
+
+    try:
+        vutils.set_kv_cache_layout("NHD")
+        assert B200AttentionBackend.get_kv_cache_stride_order() == (0, 1, 2, 3, 4)
+        vutils.set_kv_cache_layout("HND")
+        order = B200AttentionBackend.get_kv_cache_stride_order()
+        assert order == (0, 1, 3, 2, 4)
+        assert B200AttentionBackend.get_kv_cache_stride_order(include_num_layers_dimension=True) == (2, 4, 0, 1, 3, 5)
+    finally:
+        vutils.set_kv_cache_layout(None)
+    # what the model runner does with it (gpu_model_runner.py:6935-6984): allocate permuted, view back
+    shape = B200AttentionBackend.get_kv_cache_shape(6, 16, 4, 64)
+    phys = torch.zeros(tuple(shape[i] for i in order))
+    inv = [order.index(i) for i in range(len(order))]
+    kv = phys.permute(*inv)
+    assert tuple(kv.shape) == shape
+    k, v = split_kv_cache(kv)
+    assert k.shape == (6, 16, 4, 64) and k.stride(3) == 1 and k.stride(1) == 64 and k.stride(2) == 16 * 64

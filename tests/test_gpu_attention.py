@@ -385,3 +385,49 @@ def test_attention_sinks_match_oracle(path, fp8):
     # a sink can only shrink the output: compare norms with the sink-free run
     out0, _ = _run(inp, scale, path, k_scale=ks if fp8 else None, v_scale=vs if fp8 else None, window=256)
     assert (out.float().norm(dim=-1) <= out0.float().norm(dim=-1) + 1e-2).all()
+
+
+# ---------------------------------------------------------------------------------
+# HND cache layout (SURVEY.md §8f-3): same [NB, bs, Hkv, D] views, memory ordered [NB, Hkv, bs, D]
+# ---------------------------------------------------------------------------------
+def _as_hnd(t):
+    """[NB, bs, H, D] view over memory laid out [NB, H, bs, D] (vLLM's VLLM_KV_CACHE_LAYOUT=HND)."""
+    return t.permute(0, 2, 1, 3).contiguous().permute(0, 2, 1, 3)
+
+
+@pytest.mark.parametrize("lens,fp8", [
+    ([(1, 700), (1, 33), (1, 4096), (1, 1)], False),            # decode (TMA boxes over HND strides)
+    ([(1, 700), (1, 33), (1, 4096), (1, 1)], True),
+    ([(300, 300), (64, 1064), (1, 555), (5, 40)], False),        # mixed: tcgen05 + mma.sync + decode
+    ([(300, 300), (64, 1064), (1, 555)], True),
+])
+def test_hnd_cache_layout(lens, fp8):
+    from vllm_triton_backend_b200 import ops
+
+    Hq, Hkv, D, bs = 32, 8, 128, 16
+    ks, vs = (0.37, 0.61) if fp8 else (1.0, 1.0)
+    inp = make_paged_inputs(lens, Hq, Hkv, D, bs, seed=31, kv_dtype=torch.float8_e4m3fn if fp8 else None, k_scale=ks, v_scale=vs)
+    scale = D ** -0.5
+    ref = _oracle(inp, scale, k_scale=ks, v_scale=vs)
+    hnd = dict(inp)
+    kc8, vc8 = (inp["k_cache"].view(torch.uint8), inp["v_cache"].view(torch.uint8)) if fp8 else (inp["k_cache"], inp["v_cache"])
+    kh, vh = _as_hnd(kc8).to("cuda"), _as_hnd(vc8).to("cuda")
+    assert kh.stride(1) == D and kh.stride(2) == bs * D  # really HND in device memory
+    if fp8:
+        kh, vh = kh.view(torch.float8_e4m3fn), vh.view(torch.float8_e4m3fn)
+    hnd["k_cache"], hnd["v_cache"] = kh, vh
+    out, kern = _run(hnd, scale, DECODE_OR_AUTO, k_scale=ks if fp8 else None, v_scale=vs if fp8 else None)
+    assert_close(out, ref, atol=FP8_ATOL if fp8 else BF16_ATOL, rtol=BF16_RTOL, what=f"HND ({kern})")
+    # cache write into an HND cache: same bytes as into an NHD one
+    T = 9
+    g = torch.Generator().manual_seed(1)
+    key = (torch.rand(T, Hkv, D, generator=g) * 2 - 1).bfloat16().cuda()
+    val = (torch.rand(T, Hkv, D, generator=g) * 2 - 1).bfloat16().cuda()
+    slots = torch.randperm(kh.shape[0] * bs, generator=g)[:T].to(torch.int64).cuda()
+    nhd_k, nhd_v = kh.contiguous().clone(), vh.contiguous().clone()
+    kvd = "fp8" if fp8 else "auto"
+    ops.reshape_and_cache_flash(key, val, nhd_k, nhd_v, slots, kvd, ks, vs)
+    ops.reshape_and_cache_flash(key, val, kh, vh, slots, kvd, ks, vs)
+    torch.cuda.synchronize()
+    as_b = lambda t: t.view(torch.uint8) if fp8 else t
+    assert torch.equal(as_b(kh), as_b(nhd_k)) and torch.equal(as_b(vh), as_b(nhd_v))

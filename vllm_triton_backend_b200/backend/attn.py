@@ -157,6 +157,21 @@ class B200AttentionBackend(AttentionBackend):
         return (2, num_blocks, block_size, num_kv_heads, head_size)
 
     @staticmethod
+    def get_kv_cache_stride_order(include_num_layers_dimension: bool = False) -> tuple[int, ...]:
+        """Permutation from `get_kv_cache_shape` to the memory order (vLLM's VLLM_KV_CACHE_LAYOUT /
+        KV-connector preference; same contract as flash_attn.py:152-170).  The kernels take the cache as
+        strided [NB, bs, Hkv, D] views, so NHD and HND are both just strides."""
+        from vllm.v1.attention.backends.utils import get_kv_cache_layout
+
+        layout = get_kv_cache_layout()
+        if layout not in ("NHD", "HND"):
+            raise ValueError(f"Unknown cache layout format {layout}.")
+        if include_num_layers_dimension:
+            # physical (num_blocks, [num_kv_heads,] num_layers, 2, block_size, [num_kv_heads,] head_size)
+            return (2, 0, 1, 3, 4, 5) if layout == "NHD" else (2, 4, 0, 1, 3, 5)
+        return (0, 1, 2, 3, 4) if layout == "NHD" else (0, 1, 3, 2, 4)
+
+    @staticmethod
     def use_cascade_attention(*args, **kwargs) -> bool:
         return False
 
