@@ -94,7 +94,7 @@ def triton_reference():
 
 
 def kernel_name(args):
-    return "triton kernel_unified_attention (vLLM %s)" % __import__("vllm").__version__ if args.impl == "triton" else _cabi.last_kernel()
+    return "triton kernel_unified_attention (vLLM %s)" % __import__("vllm").__version__ if getattr(args, "impl", "ours") == "triton" else _cabi.last_kernel()
 
 
 def graphed(fn, inner=20):
@@ -172,7 +172,7 @@ def decode_case(args, device):
                               max_seqlen_k=max(lens), softmax_scale=D ** -0.5, causal=True, window_size=(-1, -1),
                               block_table=bt, softcap=0, q_descale=None, k_descale=sc, v_descale=sc, workspace=ws,
                               force_selection=args.force)
-    if args.impl == "triton":
+    if getattr(args, "impl", "ours") == "triton":
         tri = triton_reference().TritonReference(B, hq, D, device)
 
         def fn():  # noqa: F811 - the reference kernels on the same tensors
@@ -280,7 +280,10 @@ def prefill_case(args, device):
     cu = torch.tensor([0] + list(torch.tensor(q_lens).cumsum(0)), dtype=torch.int32, device=device)
     sl = torch.tensor(kv_lens, dtype=torch.int32, device=device)
     sc = torch.tensor([0.5], dtype=torch.float32, device=device) if args.fp8 else None
-    ws = torch.zeros(ops.workspace_bytes(T, len(lens), hq, hkv, D), dtype=torch.uint8, device=device)
+    ws_bytes = ops.workspace_bytes(T, len(lens), hq, hkv, D)
+    if args.fp8 and not getattr(args, "no_staging", False):  # room to stage the prefill sequences (csrc/kv_stage.cu)
+        ws_bytes += ops.fp8_staging_bytes(len(lens), sum(kv for q, kv in lens if q > 16), bs, hkv, D)
+    ws = torch.zeros(ws_bytes, dtype=torch.uint8, device=device)
     flops = attention_flops(q_lens, kv_lens, hq, D)
 
     def fn():
@@ -288,7 +291,7 @@ def prefill_case(args, device):
                               max_seqlen_k=max(kv_lens), softmax_scale=D ** -0.5, causal=True, window_size=(-1, -1),
                               block_table=bt, softcap=0, q_descale=None, k_descale=sc, v_descale=sc, workspace=ws,
                               force_selection=args.force)
-    if args.impl == "triton":
+    if getattr(args, "impl", "ours") == "triton":
         tri = triton_reference().TritonReference(len(lens), hq, D, device)
 
         def fn():  # noqa: F811
@@ -350,6 +353,7 @@ def main():
     ap.add_argument("--flush", action="store_true")
     ap.add_argument("--layout", default="planes", choices=["planes", "interleaved"])
     ap.add_argument("--force", type=int, default=None)
+    ap.add_argument("--no-staging", action="store_true", help="fp8 prefill: no staging pool (mma.sync kernel only)")
     ap.add_argument("--graph", action="store_true", help="decode: time 20 calls captured in one CUDA graph")
     ap.add_argument("--trace", action="store_true", help="decode: print per-CTA phase times of one launch first")
     ap.add_argument("--impl", default="ours", choices=["ours", "triton"],

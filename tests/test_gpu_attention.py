@@ -431,3 +431,84 @@ def test_hnd_cache_layout(lens, fp8):
     torch.cuda.synchronize()
     as_b = lambda t: t.view(torch.uint8) if fp8 else t
     assert torch.equal(as_b(kh), as_b(nhd_k)) and torch.equal(as_b(vh), as_b(nhd_v))
+
+
+# ---------------------------------------------------------------------------------
+# FP8 prefill through the staging pool + tcgen05 kernel (csrc/kv_stage.cu)
+# ---------------------------------------------------------------------------------
+def _fp8_prefill(lens, ws_tokens, scales=(0.37, 0.61), Hq=32, Hkv=8, tune=0):
+    from vllm_triton_backend_b200 import _cabi, ops
+
+    D, bs = 128, 16
+    inp = make_paged_inputs(lens, Hq, Hkv, D, bs, seed=41, kv_dtype=torch.float8_e4m3fn, k_scale=scales[0], v_scale=scales[1])
+    dev = "cuda"
+    q = inp["q"].to(dev)
+    out = torch.full_like(q, float("nan"))
+    T, B = q.shape[0], len(lens)
+    nbytes = ops.workspace_bytes(T, B, Hq, Hkv, D) + (ops.fp8_staging_bytes(B, ws_tokens, bs, Hkv, D) if ws_tokens else 0)
+    ws = torch.zeros(nbytes, dtype=torch.uint8, device=dev)
+    sc = [torch.tensor([s], dtype=torch.float32, device=dev) for s in scales]
+    _cabi.set_tuning(0, 0, 0, tune)
+    _cabi.reset_launch_count()
+    try:
+        ops.unified_attention(
+            q=q, k=inp["k_cache"].to(dev), v=inp["v_cache"].to(dev), out=out, cu_seqlens_q=inp["cu_seqlens_q"].to(dev),
+            max_seqlen_q=max(a for a, _ in lens), seqused_k=inp["seq_lens"].to(dev), max_seqlen_k=max(b for _, b in lens),
+            softmax_scale=D ** -0.5, causal=True, window_size=(-1, -1), block_table=inp["block_table"].to(dev), softcap=0,
+            q_descale=None, k_descale=sc[0], v_descale=sc[1], workspace=ws)
+        torch.cuda.synchronize()
+    finally:
+        _cabi.set_tuning(0, 0, 0, 0)
+    ref = _oracle(inp, D ** -0.5, k_scale=scales[0], v_scale=scales[1])
+    return out.cpu(), ref, _cabi.launch_count()
+
+
+def test_fp8_prefill_is_staged_for_the_tcgen05_kernel():
+    lens = [(300, 300), (1, 555), (64, 1064), (5, 40), (513, 2049)]
+    out, ref, launches = _fp8_prefill(lens, ws_tokens=4096)
+    assert launches == 5  # plan, dequant, tcgen05, mma.sync (short extend), decode row
+    assert_close(out, ref, atol=FP8_ATOL, rtol=BF16_RTOL, what="fp8 prefill, staged")
+    # the staged values are exactly what the reference forms on the fly, so bf16-level agreement holds too
+    assert_close(out, ref, atol=BF16_ATOL, rtol=BF16_RTOL, what="fp8 prefill, staged (bf16 tolerance)")
+
+
+def test_fp8_prefill_partial_staging_falls_back_per_sequence():
+    lens = [(300, 300), (64, 1064), (513, 2049), (200, 900)]
+    full, ref, _ = _fp8_prefill(lens, ws_tokens=8192)
+    part, _, launches = _fp8_prefill(lens, ws_tokens=1500)   # room for the first two sequences only
+    none, _, n0 = _fp8_prefill(lens, ws_tokens=0)             # no pool: mma.sync kernel for all
+    off, _, n1 = _fp8_prefill(lens, ws_tokens=8192, tune=256)  # switched off by the tuning word
+    assert launches == 5 and n0 == n1 == 2  # plan, dequant, tcgen05, mma.sync, decode  |  mma.sync, decode
+    for name, o in (("full", full), ("partial", part), ("no pool", none), ("off", off)):
+        assert_close(o, ref, atol=FP8_ATOL, rtol=BF16_RTOL, what=f"fp8 prefill ({name})")
+        assert not torch.isnan(o).any()
+
+
+def test_fp8_prefill_staging_in_a_cuda_graph():
+    from vllm_triton_backend_b200 import ops
+
+    Hq, Hkv, D, bs = 32, 8, 128, 16
+    lens = [(256, 256), (128, 1152)]
+    inp = make_paged_inputs(lens, Hq, Hkv, D, bs, seed=43, kv_dtype=torch.float8_e4m3fn, k_scale=0.5, v_scale=0.25)
+    dev = "cuda"
+    q, out = inp["q"].to(dev), torch.zeros_like(inp["q"]).to(dev)
+    kc, vc = inp["k_cache"].to(dev), inp["v_cache"].to(dev)
+    cu, bt = inp["cu_seqlens_q"].to(dev), inp["block_table"].to(dev)
+    sl = torch.tensor([256, 128], dtype=torch.int32, device=dev)  # capture with context-free lengths
+    ws = torch.zeros(ops.workspace_bytes(384, 2, Hq, Hkv, D) + ops.fp8_staging_bytes(2, 2048, bs, Hkv, D), dtype=torch.uint8, device=dev)
+    sc = torch.tensor([0.5], device=dev), torch.tensor([0.25], device=dev)
+
+    def call():
+        ops.unified_attention(q=q, k=kc, v=vc, out=out, cu_seqlens_q=cu, max_seqlen_q=256, seqused_k=sl, max_seqlen_k=1152,
+                              softmax_scale=D ** -0.5, causal=True, window_size=(-1, -1), block_table=bt, softcap=0,
+                              q_descale=None, k_descale=sc[0], v_descale=sc[1], workspace=ws)
+    call()
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        call()
+    sl.copy_(inp["seq_lens"].to(dev))
+    out.fill_(float("nan"))
+    g.replay()
+    torch.cuda.synchronize()
+    assert_close(out.cpu(), _oracle(inp, D ** -0.5, k_scale=0.5, v_scale=0.25), atol=FP8_ATOL, rtol=BF16_RTOL, what="staged, graph")

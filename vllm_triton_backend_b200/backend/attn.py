@@ -75,6 +75,14 @@ class B200AttentionMetadataBuilder(AttentionMetadataBuilder[B200AttentionMetadat
         self.headdim = model_config.get_head_size()
         max_num_seqs = vllm_config.scheduler_config.max_num_seqs
         nbytes = ops.workspace_bytes(max_num_seqs, max_num_seqs, self.num_heads_q, self.num_heads_kv, self.headdim)
+        cache_dtype = str(getattr(vllm_config.cache_config, "cache_dtype", "auto"))
+        if cache_dtype.startswith("fp8"):
+            # FP8 cache: staging pool that lets long prefills run the tcgen05 kernel (csrc/kv_stage.cu).  Sized for
+            # two sequences of max_model_len (or B200ATTN_FP8_STAGING_TOKENS); what does not fit runs mma.sync.
+            import os
+
+            tokens = int(os.environ.get("B200ATTN_FP8_STAGING_TOKENS", 2 * int(model_config.max_model_len)))
+            nbytes += ops.fp8_staging_bytes(max_num_seqs, tokens, self.block_size, self.num_heads_kv, self.headdim)
         # zeroed once: holds the decode kernel's self-cleaning ticket counters
         self.workspace = torch.zeros(nbytes, dtype=torch.uint8, device=device)
 

@@ -19,7 +19,7 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
 BUILD_DIR = os.path.join(PKG_DIR, "_build")
 LIB_PATH = os.path.join(PKG_DIR, "libb200attn.so")
-SOURCES = ["cabi.cu", "tma_maps.cu", "cache_write.cu", "rope_cache_write.cu", "attn_generic.cu", "attn_decode.cu", "attn_prefill.cu",
+SOURCES = ["cabi.cu", "tma_maps.cu", "cache_write.cu", "rope_cache_write.cu", "kv_stage.cu", "attn_generic.cu", "attn_decode.cu", "attn_prefill.cu",
            "attn_prefill_tc.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [

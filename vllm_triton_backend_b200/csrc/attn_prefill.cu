@@ -37,7 +37,7 @@ template <int ROWB> __device__ __forceinline__ uint32_t swz_off(int r, int c) {
 template <int D, bool MMA_BF16, bool Q_BF16, bool KV_FP8>
 __global__ void __launch_bounds__(NWARPS * 32, (D <= 128) ? 2 : 1)
 attn_prefill_kernel(const b200attn_attention_params p, const int block_q, const int group, const int min_q_len,
-                    const int max_q_len, const int qb_per_seq) {
+                    const int max_q_len, const int qb_per_seq, const int32_t* skip_staged) {
   constexpr int ROWB = D * 2;           // smem row bytes (operands are 2-byte in smem)
   constexpr int CPR = ROWB / 16;        // 16-byte chunks per row
   constexpr int KSTEPS = D / 16;
@@ -73,6 +73,7 @@ attn_prefill_kernel(const b200attn_attention_params p, const int block_q, const 
   const int q_len = p.cu_seqlens_q[b + 1] - q_start;
   if (q_block_local * block_q >= q_len) return;
   if (q_len < min_q_len || q_len > max_q_len) return;  // another launch covers this sequence
+  if (skip_staged && skip_staged[b] >= 0) return;      // staged for the tcgen05 kernel (kv_stage.cu)
   const int seq_len = p.seq_lens[b];
   const int ctx = seq_len - q_len;
   const int qpos0 = q_block_local * block_q;                   // first query position of this block
@@ -324,7 +325,7 @@ attn_prefill_kernel(const b200attn_attention_params p, const int block_q, const 
 }
 
 template <int D, bool MMA_BF16, bool Q_BF16, bool KV_FP8>
-int launch_variant(const b200attn_attention_params& a, cudaStream_t stream, QLenRange range) {
+int launch_variant(const b200attn_attention_params& a, cudaStream_t stream, QLenRange range, const int32_t* skip_staged) {
   const int group = a.num_q_heads / a.num_kv_heads;
   const int block_q = BM / group;
   const int smem = BM * D * 2 + 4 * BN * D * 2;
@@ -346,17 +347,17 @@ int launch_variant(const b200attn_attention_params& a, cudaStream_t stream, QLen
   const long long per_seq = ((long long)longest + block_q - 1) / block_q;
   if (per_seq >= 1 && per_seq * a.num_seqs < nblocks) qb_per_seq = (int)per_seq, nblocks = per_seq * a.num_seqs;
   const dim3 grid((unsigned)nblocks, (unsigned)a.num_kv_heads);
-  kern<<<grid, NWARPS * 32, smem, stream>>>(a, block_q, group, range.min_q_len, range.max_q_len, qb_per_seq);
+  kern<<<grid, NWARPS * 32, smem, stream>>>(a, block_q, group, range.min_q_len, range.max_q_len, qb_per_seq, skip_staged);
   note_launch("attn_prefill_mma");
   return check_launch("attn_prefill");
 }
 
 template <int D>
-int dispatch_types(const b200attn_attention_params& a, cudaStream_t stream, QLenRange range) {
+int dispatch_types(const b200attn_attention_params& a, cudaStream_t stream, QLenRange range, const int32_t* skip) {
   const bool qbf = a.q_dtype == B200ATTN_BF16;
   if (a.kv_dtype == B200ATTN_FP8_E4M3)
-    return qbf ? launch_variant<D, false, true, true>(a, stream, range) : launch_variant<D, false, false, true>(a, stream, range);
-  return qbf ? launch_variant<D, true, true, false>(a, stream, range) : launch_variant<D, false, false, false>(a, stream, range);
+    return qbf ? launch_variant<D, false, true, true>(a, stream, range, skip) : launch_variant<D, false, false, true>(a, stream, range, skip);
+  return qbf ? launch_variant<D, true, true, false>(a, stream, range, skip) : launch_variant<D, false, false, false>(a, stream, range, skip);
 }
 
 }  // namespace
@@ -379,16 +380,17 @@ bool prefill_supported(const b200attn_attention_params& p, const char** why) {
   return true;
 }
 
-int launch_attn_prefill(const b200attn_attention_params& a, cudaStream_t stream, QLenRange range) {
+int launch_attn_prefill(const b200attn_attention_params& a, cudaStream_t stream, QLenRange range,
+                        const int32_t* skip_staged) {
   const char* why = nullptr;
   if (!prefill_supported(a, &why)) {
     set_error("prefill: unsupported configuration (%s)", why);
     return B200ATTN_E_UNSUPPORTED;
   }
   switch (a.head_size) {
-    case 64: return dispatch_types<64>(a, stream, range);
-    case 128: return dispatch_types<128>(a, stream, range);
-    case 256: return dispatch_types<256>(a, stream, range);
+    case 64: return dispatch_types<64>(a, stream, range, skip_staged);
+    case 128: return dispatch_types<128>(a, stream, range, skip_staged);
+    case 256: return dispatch_types<256>(a, stream, range, skip_staged);
   }
   return B200ATTN_E_UNSUPPORTED;
 }

@@ -77,6 +77,8 @@ struct TcParams {
   int block_q;    // tokens per 128-row subtile
   int min_q_len, max_q_len;
   int box_slots;  // tokens per TMA box = min(block_size, 128)
+  const int32_t* staged_base;  // FP8 staging (kv_stage.cu): page p of sequence b is staged_base[b] + p of the
+                               // cache handed in; sequences with a negative entry are not this launch's.  Or nullptr.
 };
 
 
@@ -535,7 +537,8 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
           const int q_tile_local = q_tile_global - (it.q_start / BQ + it.b);
           it.qpos0 = q_tile_local * BQ;
           // sequences outside [min_q_len, max_q_len] belong to another launch of a mixed batch
-          if (it.qpos0 < it.q_len && it.q_len >= P.min_q_len && it.q_len <= P.max_q_len) {
+          if (it.qpos0 < it.q_len && it.q_len >= P.min_q_len && it.q_len <= P.max_q_len &&
+              (!P.staged_base || P.staged_base[it.b] >= 0)) {
             const int seq_len = a.seq_lens[it.b];
             it.ctx = seq_len - it.q_len;
             const int qpos_last = min(it.qpos0 + BQ, it.q_len) - 1;
@@ -710,11 +713,13 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
         const int boxes_per_tile = kBN / P.box_slots;
         const uint32_t box_bytes = (uint32_t)P.box_slots * 128;
         const int32_t* bt = a.block_tables + (int64_t)it.b * a.bt_stride0;
+        const int staged0 = (P.staged_base && n_tiles > 0) ? P.staged_base[it.b] : -1;
         const int my_box = lane >> 1, my_dc = lane & 1;
         // page id of this lane's box, fetched one tile ahead of its use
         auto lookup = [&](int j) {
           const int tok = (tile0 + j) * kBN + my_box * P.box_slots;
-          return (j < n_tiles && my_box < boxes_per_tile && tok < it.kv_limit) ? bt[tok / bs] : 0;
+          if (!(j < n_tiles && my_box < boxes_per_tile && tok < it.kv_limit)) return 0;
+          return staged0 >= 0 ? staged0 + tok / bs : bt[tok / bs];
         };
         const int nst = is_k ? kKStages : kVStages;
         const int full0 = is_k ? K_FULL : V_FULL, empty0 = is_k ? K_EMPTY : V_EMPTY;
@@ -815,7 +820,8 @@ bool prefill_tc_supported(const b200attn_attention_params& p, const char** why) 
   return true;
 }
 
-int launch_attn_prefill_tc(const b200attn_attention_params& a, cudaStream_t stream, QLenRange range) {
+int launch_attn_prefill_tc(const b200attn_attention_params& a, cudaStream_t stream, QLenRange range,
+                           const int32_t* staged_base) {
   const char* why = nullptr;
   if (!prefill_tc_supported(a, &why)) {
     set_error("prefill_tc: unsupported configuration (%s)", why);
@@ -826,6 +832,7 @@ int launch_attn_prefill_tc(const b200attn_attention_params& a, cudaStream_t stre
   P.group = a.num_q_heads / a.num_kv_heads;
   P.block_q = 128 / P.group;
   P.min_q_len = range.min_q_len, P.max_q_len = range.max_q_len;
+  P.staged_base = staged_base;
   P.box_slots = a.block_size < kBN ? a.block_size : kBN;
   CUtensorMap qmap, kmap, vmap;
   int rc = make_thd_map(&qmap, a.q, kD, a.num_q_heads, a.num_tokens, a.q_stride0, a.q_stride1, P.group, P.block_q);

@@ -197,6 +197,29 @@ int b200attn_unified_attention(const b200attn_attention_params* pp, b200attn_str
   const bool dec_ok = ws_ok && decode_supported(p, &why, /*mixed_batch=*/true);
   // every sequence has exactly max_seqlen_q tokens <=> T == B * max_seqlen_q
   const bool uniform = (int64_t)p.num_tokens == (int64_t)p.num_seqs * p.max_seqlen_q;
+  if (p.kv_dtype == B200ATTN_FP8_E4M3 && !(g_tuning.reserved & 256)) {
+    // FP8 cache: the sequences with long queries are dequantised once into the staging pool (the part of
+    // the workspace past the decode region) and run the tcgen05 kernel on it; what does not fit the pool,
+    // short extends and decode rows keep reading the FP8 cache.  (tuning().reserved bit 8 switches it off.)
+    KvStage st;
+    if (plan_kv_stage(p, &st)) {
+      const b200attn_attention_params s16 = staged_params(p, st);
+      if (prefill_tc_supported(s16, &why) && p.max_seqlen_q >= prefill_tc_min_q_len(s16)) {
+        QLenRange r;
+        r.min_q_len = prefill_tc_min_q_len(s16);
+        rc = launch_kv_stage(p, st, r, stream);
+        if (rc) return rc;
+        rc = launch_attn_prefill_tc(s16, stream, r, st.staged_base);
+        if (rc) return rc;
+        QLenRange rest;  // every multi-token query that was not staged
+        rest.min_q_len = dec_ok ? 2 : 0;
+        rc = launch_attn_prefill(p, stream, rest, st.staged_base);
+        if (rc) return rc;
+        if (dec_ok && !uniform) return launch_attn_decode(p, stream, /*only_single_token_seqs=*/true);
+        return B200ATTN_OK;
+      }
+    }
+  }
   int short_max = 0x7fffffff;  // longest query the mma.sync launch takes
   if (prefill_tc_supported(p, &why) && p.max_seqlen_q >= prefill_tc_min_q_len(p)) {
     QLenRange r;

@@ -55,6 +55,19 @@ struct QLenRange {
   int max_q_len = 0x7fffffff;
 };
 
+// FP8 prefill staging (kv_stage.cu): a 16-bit copy of the pages of the sequences the tcgen05 kernel
+// takes, carved out of the workspace past the decode kernel's region.
+struct KvStage {
+  int32_t* staged_base = nullptr;  // [num_seqs]: first staging page of a sequence, or -1
+  void* k_stage = nullptr;
+  void* v_stage = nullptr;
+  int cap_pages = 0;
+};
+bool plan_kv_stage(const b200attn_attention_params& p, KvStage* st);
+b200attn_attention_params staged_params(const b200attn_attention_params& p, const KvStage& st);
+int launch_kv_stage(const b200attn_attention_params& p, const KvStage& st, QLenRange range, cudaStream_t stream);
+uint64_t stage_bytes_for_pages(int num_seqs, int64_t pages, int block_size, int num_kv_heads, int head_size);
+
 // kernel launchers (one per .cu file)
 int launch_cache_write(const void* key, const void* value, void* k_cache, void* v_cache, const int64_t* slot_mapping,
                        int64_t num_tokens, int num_kv_heads, int head_size, int block_size, int64_t key_stride0,
@@ -68,9 +81,11 @@ int launch_attn_generic(const b200attn_attention_params& p, cudaStream_t stream)
 int launch_attn_decode(const b200attn_attention_params& p, cudaStream_t stream, bool only_single_token_seqs = false);
 bool decode_supported(const b200attn_attention_params& p, const char** why, bool mixed_batch = false);
 uint64_t decode_workspace_bytes(int num_seqs, int num_q_heads, int num_kv_heads, int head_size);
-int launch_attn_prefill(const b200attn_attention_params& p, cudaStream_t stream, QLenRange range = QLenRange());
+int launch_attn_prefill(const b200attn_attention_params& p, cudaStream_t stream, QLenRange range = QLenRange(),
+                        const int32_t* skip_staged = nullptr);
 bool prefill_supported(const b200attn_attention_params& p, const char** why);
-int launch_attn_prefill_tc(const b200attn_attention_params& p, cudaStream_t stream, QLenRange range = QLenRange());
+int launch_attn_prefill_tc(const b200attn_attention_params& p, cudaStream_t stream, QLenRange range = QLenRange(),
+                           const int32_t* staged_base = nullptr);
 bool prefill_tc_supported(const b200attn_attention_params& p, const char** why);
 int prefill_tc_min_q_len(const b200attn_attention_params& p);  // shortest query the tcgen05 tile is worth using for
 

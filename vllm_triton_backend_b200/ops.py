@@ -63,6 +63,17 @@ def workspace_bytes(num_tokens: int, num_seqs: int, num_q_heads: int, num_kv_hea
     return int(_cabi.load_library().b200attn_workspace_bytes(num_tokens, num_seqs, num_q_heads, num_kv_heads, head_size))
 
 
+def fp8_staging_bytes(num_seqs: int, tokens: int, block_size: int, num_kv_heads: int, head_size: int) -> int:
+    """Extra workspace (past `workspace_bytes(...)`) that lets FP8-KV prefill run the tcgen05 kernel:
+    a 16-bit staging pool for `tokens` cached tokens (csrc/kv_stage.cu).  Sequences that do not fit
+    stay on the mma.sync kernel, so any size is valid; 0 disables staging."""
+    if tokens <= 0:
+        return 0
+    pages = (tokens + block_size - 1) // block_size + num_seqs
+    index = (num_seqs * 4 + 255) // 256 * 256
+    return 256 + index + 2 * pages * block_size * num_kv_heads * head_size * 2 + 512
+
+
 def get_workspace(device, nbytes: int) -> torch.Tensor:
     """Grow-only per-device split-KV workspace (replaces the reference's per-call
     torch.empty of segm_output/segm_max/segm_expsum, triton_unified_attention.py:950-971).
@@ -239,6 +250,10 @@ def unified_attention(
     if workspace is None and path in (_cabi.PATH_AUTO, _cabi.PATH_DECODE):
         # decode batches, and the single-token rows of a mixed batch, use the split-KV kernel
         need = workspace_bytes(q.shape[0], seqused_k.shape[0], q.shape[1], k.shape[2], q.shape[2])
+        if k.element_size() == 1 and max_seqlen_q > 1:
+            # FP8 prefill: room to stage every sequence at full length (bounded; what does not fit runs mma.sync)
+            tokens = min(seqused_k.shape[0] * int(max_seqlen_k), 1 << 20)
+            need += fp8_staging_bytes(seqused_k.shape[0], tokens, v.shape[1], k.shape[2], q.shape[2])
         workspace = get_workspace(q.device, need)
     p = build_attention_params(
         q, k, v, out, cu_seqlens_q, max_seqlen_q, seqused_k, max_seqlen_k, softmax_scale, window_size, block_table,
