@@ -213,8 +213,13 @@ int b200attn_unified_attention(const b200attn_attention_params* pp, b200attn_str
         if (rc) return rc;
         QLenRange rest;  // every multi-token query that was not staged
         rest.min_q_len = dec_ok ? 2 : 0;
-        rc = launch_attn_prefill(p, stream, rest, st.staged_base);
-        if (rc) return rc;
+        // a pool that holds every sequence at full length cannot overflow: only short queries are left
+        const int64_t every = (int64_t)p.num_seqs * ((p.max_seqlen_k + p.block_size - 1) / p.block_size);
+        if (st.cap_pages >= every) rest.max_q_len = r.min_q_len - 1;
+        if (rest.max_q_len >= rest.min_q_len && !(uniform && st.cap_pages >= every)) {
+          rc = launch_attn_prefill(p, stream, rest, st.staged_base);
+          if (rc) return rc;
+        }
         if (dec_ok && !uniform) return launch_attn_decode(p, stream, /*only_single_token_seqs=*/true);
         return B200ATTN_OK;
       }
