@@ -364,7 +364,8 @@ def run_ours(args):
                          "kernel": "attn_decode_kernel (split-KV, merge of partials fused in)", "peak_source": peaks["source"],
                          "frac_of_nominal_8TBs": round(achieved / 8000.0, 4), "algorithmic_bytes_per_launch": dec_bytes,
                          "avg_launch_ms": round(att_mean_ms, 5)},
-            "extras": {"decode_tokens_per_s": round(world * B / (ms_per_step * 1e-3), 1),
+            "extras": {"decode_launch_ms_p20_p50_p80": [round(x, 5) for x in _percentiles(att_ms, (20, 50, 80))],
+                       "decode_tokens_per_s": round(world * B / (ms_per_step * 1e-3), 1),
                        "e2e_tokens_per_s": round(world * B / (e2e_ms / K * 1e-3), 1), "last_kernel": dominant},
         }
         if pre is not None:
@@ -475,6 +476,11 @@ def run_reference_arm(args):
         "e2e": {"value": round(v, 4), "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
+
+
+def _percentiles(xs, ps):
+    ys = sorted(xs)
+    return [ys[min(len(ys) - 1, max(0, int(round(p / 100.0 * (len(ys) - 1)))))] for p in ps]
 
 
 def committed_ncu_traffic():

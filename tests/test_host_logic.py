@@ -57,3 +57,35 @@ def test_shard_heads(world, hq, hkv, expect):
 def test_shard_heads_rejects_uneven_splits():
     with pytest.raises(ValueError):
         shard_heads(0, 3, 32, 8)
+
+
+def test_bench_helpers_and_kbench_namespace_contract():
+    """bench.py's prefill section drives scripts/kbench.py with a SimpleNamespace: every attribute
+    kbench.prefill_case reads without a default must be in it (a missing one broke the default bench run once)."""
+    import ast
+    import importlib.util
+    import os
+    import re
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(root, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    assert bench._percentiles([5, 1, 3, 2, 4], (0, 50, 100)) == [1, 3, 5]
+    t = bench.committed_ncu_traffic()
+    assert t is None or 1.0e9 < t < 1.2e9  # C2 decode kernel: ~1.075 GB algorithmic
+    src = open(os.path.join(root, "bench.py")).read()
+    ns = re.search(r"types\.SimpleNamespace\(([^)]*)\)", src).group(1)
+    provided = set(re.findall(r"(\w+)=", ns))
+    ksrc = open(os.path.join(root, "scripts", "kbench.py")).read()
+    fn = next(n for n in ast.parse(ksrc).body if isinstance(n, ast.FunctionDef) and n.name == "prefill_case")
+    needed = {n.attr for n in ast.walk(fn) if isinstance(n, ast.Attribute) and isinstance(n.value, ast.Name) and n.value.id == "args"}
+    assert needed <= provided, f"bench.py's namespace lacks {needed - provided}"
+
+
+def test_fp8_staging_bytes_covers_what_the_library_carves():
+    # csrc/kv_stage.cu plan_kv_stage: index (256-aligned) + 2 planes of pages; any size is valid, 0 disables
+    assert ops.fp8_staging_bytes(4, 0, 16, 8, 128) == 0
+    n = ops.fp8_staging_bytes(4, 4096, 16, 8, 128)
+    pages = 4096 // 16 + 4
+    assert n >= 256 + 2 * pages * 16 * 8 * 128 * 2
