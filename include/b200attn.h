@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 1
+#define B200ATTN_ABI_VERSION 2
 
 #if defined(__GNUC__)
 #define B200ATTN_API __attribute__((visibility("default")))
@@ -92,7 +92,7 @@ B200ATTN_API int b200attn_reshape_and_cache_flash(
  * (:757-836).  Field meanings follow the reference launcher's arguments.
  */
 typedef struct b200attn_attention_params {
-  void* out;                   /* [T, Hq, D]  q_dtype                              */
+  void* out;                   /* [T, Hq, D]  q_dtype (FP8-e4m3 when out_scale != NULL) */
   const void* q;               /* [T, Hq, D]  innermost contiguous                 */
   const void* k_cache;         /* [NB, bs, Hkv, D] view, innermost contiguous      */
   const void* v_cache;
@@ -131,6 +131,13 @@ typedef struct b200attn_attention_params {
                                   zero-filled ONCE when allocated (the kernels leave
                                   the counters at zero after every call)           */
   uint64_t workspace_bytes;
+  const float* out_scale;      /* NULL: `out` has q_dtype.  Else a device scalar ("output_scale" of
+                                  AttentionImpl.forward when fused_output_quant_supported, vLLM 0.22
+                                  vllm/v1/attention/backends/triton_attn.py:453-454,663; upstream kernel
+                                  `acc * (1/output_scale)`, clamp +-448, store e4m3): `out` is then
+                                  FP8-e4m3 [T, Hq, D], out_stride* in 1-byte elements, rows 8-byte
+                                  aligned, and every kernel of the path quantises in its epilogue:
+                                  out = e4m3_rn_satfinite(o_fp32 * (1.0f / *out_scale))               */
 } b200attn_attention_params;
 
 /* Bytes of workspace b200attn_unified_attention may need for this shape
@@ -191,6 +198,9 @@ B200ATTN_API int b200attn_rope_and_cache_flash(const b200attn_rope_cache_params*
 
 /* ---- introspection ---------------------------------------------------------*/
 B200ATTN_API int b200attn_abi_version(void);
+/* sizeof the parameter blocks as this library was compiled (0: b200attn_attention_params,
+ * 1: b200attn_rope_cache_params; else 0): a binding checks its own struct layout against it. */
+B200ATTN_API uint64_t b200attn_params_size(int32_t which);
 B200ATTN_API const char* b200attn_last_error(void);
 /* Number of kernels this library launched on the calling thread since the last
  * reset (bench.py reports it as `gpu_launches`). */

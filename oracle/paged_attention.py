@@ -63,8 +63,17 @@ def unified_attention_ref(
     round_p_to: Optional[torch.dtype] = None,  # kernel casts P to V's dtype before PV (:508)
     out_dtype: Optional[torch.dtype] = None,
     sinks: Optional[torch.Tensor] = None,  # [Hq]: per-head logit that only joins the softmax denominator
+    output_scale: Optional[float] = None,  # static per-tensor FP8 output quantisation; result is float8_e4m3fn
+    local_chunk: int = 0,  # chunked local attention: a query only sees keys of its own chunk of positions
 ) -> torch.Tensor:
-    """`sinks` is an upstream addition to the same kernel (vLLM's
+    """`local_chunk` states chunked local attention (iRoPE / Llama-4) directly as a mask: position p
+    attends to keys in [floor(p / chunk) * chunk, p].  The reference gets the same result by cutting
+    the batch into virtual sequences (`make_local_attention_virtual_batches`, used at
+    ibm-triton-lib/ibm_triton_lib/backend/triton_attn.py:155-190, 423-444) and running the unchanged kernel.
+    `output_scale` follows the upstream kernel epilogue (installed vLLM
+    vllm/v1/attention/ops/triton_unified_attention.py:608-610, 722-724, 986): the fp32 result times
+    the fp32 reciprocal of the scale, clamped to +-448, stored as e4m3 (round to nearest even).
+    `sinks` is an upstream addition to the same kernel (vLLM's
     vllm/v1/attention/ops/triton_attention_helpers.py `init_softmax_M`: the running max starts at
     the head's sink value and the running sum at 1, i.e. one extra key with logit `sink`, unscaled,
     and a zero value row)."""
@@ -94,6 +103,8 @@ def unified_attention_ref(
         visible = kpos < ctx + qpos + 1  # :460
         if sliding_window > 0:
             visible = visible & ((ctx + qpos - kpos) < sliding_window)  # :474-479
+        if local_chunk > 0:
+            visible = visible & (kpos >= ((ctx + qpos) // local_chunk) * local_chunk)
         s = torch.where(visible, s, torch.full_like(s, float("-inf")))
         if alibi_slopes is not None:
             s = s + alibi_slopes.to(torch.float32).view(Hq, 1, 1) * (kpos - ctx)  # :481-482
@@ -109,6 +120,9 @@ def unified_attention_ref(
             p = p.to(round_p_to).to(torch.float32)
         o = torch.einsum("hqk,khd->qhd", p, v) / l.permute(1, 0, 2)  # :508-511
         out[q0:q1] = o
+    if output_scale is not None:
+        inv = 1.0 / torch.tensor(float(output_scale), dtype=torch.float32)  # fp32 reciprocal, as `1 / output_scale`
+        return (out * inv).clamp(-448.0, 448.0).to(torch.float8_e4m3fn)
     return out.to(out_dtype or q.dtype)
 
 

@@ -73,8 +73,12 @@ def test_profiling_run_and_fused_output_quant():
     impl = B200AttentionImpl(4, 64, 1.0, 4, None, None, "auto")
     out = torch.ones(3, 4 * 64)
     assert impl.forward(None, None, None, None, None, None, output=out).abs().sum() == 0  # attn_metadata is None
-    with pytest.raises(NotImplementedError, match="fused output quantization"):
-        impl.forward(None, None, None, None, None, object(), output=out, output_scale=torch.ones(1))
+    with pytest.raises(NotImplementedError, match="block_scale output quantization"):
+        impl.forward(None, None, None, None, None, object(), output=out, output_block_scale=torch.ones(1))
+    # static per-tensor FP8 of the output is fused into the kernels (vLLM 0.22 triton_attn.py:453-454)
+    from vllm.model_executor.layers.quantization.utils.quant_utils import kFp8DynamicTokenSym, kFp8StaticTensorSym
+    assert impl.fused_output_quant_supported(kFp8StaticTensorSym)
+    assert not impl.fused_output_quant_supported(kFp8DynamicTokenSym)
     with pytest.raises(AssertionError, match="Output tensor"):
         impl.forward(None, None, None, None, None, object(), output=None)
 

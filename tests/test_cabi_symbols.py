@@ -1,5 +1,6 @@
 """The C-ABI library loads without a GPU/driver and exports every symbol that
 include/b200attn.h declares (no compute calls here)."""
+import ctypes
 import os
 import re
 
@@ -36,7 +37,7 @@ def test_every_declared_symbol_is_exported(lib):
 
 
 def test_abi_version_and_host_only_calls(lib):
-    assert lib.b200attn_abi_version() == 1
+    assert lib.b200attn_abi_version() == 2
     # workspace size is a function of host ints only
     a = lib.b200attn_workspace_bytes(64, 64, 32, 8, 128)
     b = lib.b200attn_workspace_bytes(128, 128, 32, 8, 128)
@@ -74,3 +75,12 @@ def test_missing_library_fails_loudly(monkeypatch, tmp_path):
     monkeypatch.setattr(_cabi, "LIB_PATH", str(tmp_path / "nope.so"))
     with pytest.raises(ImportError, match="no CPU/PyTorch fallback"):
         _cabi.load_library()
+
+
+def test_struct_sizes_agree_with_the_compiled_library(lib):
+    """load_library() refuses a stale .so; the same check spelled out."""
+    from vllm_triton_backend_b200._cabi import AttentionParams, RopeCacheParams
+
+    assert lib.b200attn_params_size(0) == ctypes.sizeof(AttentionParams)
+    assert lib.b200attn_params_size(1) == ctypes.sizeof(RopeCacheParams)
+    assert lib.b200attn_params_size(7) == 0

@@ -81,3 +81,17 @@ def test_cache_write_skips_negative_slots_and_uses_slot_mapping_length():
     untouched = torch.ones(4, 16, dtype=torch.bool)
     untouched[0, 3] = untouched[1, 4] = untouched[3, 15] = False
     assert (kc[untouched] == 7.0).all() and (vc[untouched] == 7.0).all()
+
+
+def test_output_scale_quantises_the_fp32_result():
+    """`output_scale` (upstream epilogue: acc * (1/scale), clamp +-448, e4m3 store) applied to a golden case."""
+    c = load_golden_attn(f"{GOLDEN_DIR}/attn_decode3d_f32.npz")
+    args = (c["q"], c["k_cache"], c["v_cache"], c["cu_seqlens_q"], c["seq_lens"], c["block_table"], c["scale"])
+    dense = unified_attention_ref(*args, out_dtype=torch.float32)
+    q8 = unified_attention_ref(*args, output_scale=0.01)
+    assert q8.dtype == torch.float8_e4m3fn and q8.shape == dense.shape
+    x = dense / 0.01
+    step = torch.exp2(torch.floor(torch.log2(x.abs().clamp_min(2.0 ** -6))) - 3)
+    assert ((q8.float() - x).abs() <= 0.5 * step * (1 + 1e-5)).all(), "not the nearest e4m3 code"
+    sat = unified_attention_ref(*args, output_scale=1e-12).view(torch.uint8)
+    assert set(sat.unique().tolist()) <= {0x7E, 0xFE}, "saturates to +-448, never NaN"

@@ -22,6 +22,8 @@ STATUS_NAMES = {
     6: "E_CUDA", 7: "E_NULL",
 }
 
+ABI_VERSION = 2  # include/b200attn.h B200ATTN_ABI_VERSION
+
 EXPORTED_SYMBOLS = [
     "b200attn_reshape_and_cache_flash",
     "b200attn_workspace_bytes",
@@ -29,6 +31,7 @@ EXPORTED_SYMBOLS = [
     "b200attn_scaled_fp8_quant",
     "b200attn_rope_and_cache_flash",
     "b200attn_abi_version",
+    "b200attn_params_size",
     "b200attn_last_error",
     "b200attn_launch_count",
     "b200attn_reset_launch_count",
@@ -54,6 +57,7 @@ class AttentionParams(Structure):
         ("kc_block_stride", c_int64), ("kc_slot_stride", c_int64), ("kc_head_stride", c_int64),
         ("vc_block_stride", c_int64), ("vc_slot_stride", c_int64), ("vc_head_stride", c_int64),
         ("workspace", c_void_p), ("workspace_bytes", c_uint64),
+        ("out_scale", c_void_p),
     ]
 
 
@@ -106,6 +110,15 @@ def load_library() -> ctypes.CDLL:
     lib.b200attn_scaled_fp8_quant.restype = c_int32
     lib.b200attn_scaled_fp8_quant.argtypes = [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int32, c_void_p, c_void_p]
     lib.b200attn_abi_version.restype = c_int32
+    lib.b200attn_params_size.restype = c_uint64
+    lib.b200attn_params_size.argtypes = [c_int32]
+    if lib.b200attn_abi_version() != ABI_VERSION or lib.b200attn_params_size(0) != ctypes.sizeof(AttentionParams) \
+            or lib.b200attn_params_size(1) != ctypes.sizeof(RopeCacheParams):
+        raise ImportError(
+            f"{LIB_PATH} was built from other sources (ABI {lib.b200attn_abi_version()} vs {ABI_VERSION}, params "
+            f"{lib.b200attn_params_size(0)}/{lib.b200attn_params_size(1)} bytes vs {ctypes.sizeof(AttentionParams)}/"
+            f"{ctypes.sizeof(RopeCacheParams)}): rebuild with `python -m vllm_triton_backend_b200.build`"
+        )
     lib.b200attn_last_error.restype = c_char_p
     lib.b200attn_launch_count.restype = c_uint64
     lib.b200attn_reset_launch_count.restype = None

@@ -74,6 +74,7 @@ class B200AttentionMetadataBuilder(AttentionMetadataBuilder[B200AttentionMetadat
         self.num_heads_kv = model_config.get_num_kv_heads(parallel_config)
         self.headdim = model_config.get_head_size()
         max_num_seqs = vllm_config.scheduler_config.max_num_seqs
+        self._ws_seqs = max_num_seqs
         nbytes = ops.workspace_bytes(max_num_seqs, max_num_seqs, self.num_heads_q, self.num_heads_kv, self.headdim)
         cache_dtype = str(getattr(vllm_config.cache_config, "cache_dtype", "auto"))
         if cache_dtype.startswith("fp8"):
@@ -85,6 +86,19 @@ class B200AttentionMetadataBuilder(AttentionMetadataBuilder[B200AttentionMetadat
             nbytes += ops.fp8_staging_bytes(max_num_seqs, tokens, self.block_size, self.num_heads_kv, self.headdim)
         # zeroed once: holds the decode kernel's self-cleaning ticket counters
         self.workspace = torch.zeros(nbytes, dtype=torch.uint8, device=device)
+        self._ws_extra = nbytes - ops.workspace_bytes(max_num_seqs, max_num_seqs, self.num_heads_q, self.num_heads_kv,
+                                                      self.headdim)
+
+    def _fit_workspace(self, num_seqs: int) -> None:
+        """Chunked local attention (vLLM wraps this builder and hands it virtual batches,
+        `make_local_attention_virtual_batches`) can present more sequences than max_num_seqs; the split-KV
+        records are sized per sequence, so grow once (eager steps only: captured sizes never exceed
+        max_num_seqs)."""
+        if num_seqs <= self._ws_seqs:
+            return
+        self._ws_seqs = max(num_seqs, 2 * self._ws_seqs)
+        nbytes = ops.workspace_bytes(self._ws_seqs, self._ws_seqs, self.num_heads_q, self.num_heads_kv, self.headdim)
+        self.workspace = torch.zeros(nbytes + self._ws_extra, dtype=torch.uint8, device=self.workspace.device)
 
     def build_for_cudagraph_capture(self, common_attn_metadata: CommonAttentionMetadata) -> B200AttentionMetadata:
         attn_metadata = self.build(0, common_attn_metadata)
@@ -96,6 +110,7 @@ class B200AttentionMetadataBuilder(AttentionMetadataBuilder[B200AttentionMetadat
     def build(self, common_prefix_len: int, common_attn_metadata: CommonAttentionMetadata,
               fast_build: bool = False) -> B200AttentionMetadata:
         m = common_attn_metadata
+        self._fit_workspace(m.seq_lens.shape[0])
         return B200AttentionMetadata(
             num_actual_tokens=m.num_actual_tokens,
             max_query_len=m.max_query_len,
@@ -291,6 +306,15 @@ class B200AttentionImpl(AttentionImpl):
             return
         self._plans_for(layer, kv_cache, key.dtype)[0](key, value, slot_mapping)
 
+    def fused_output_quant_supported(self, quant_key) -> bool:
+        """Static per-tensor symmetric FP8 of the output, done in every kernel's epilogue
+        (vLLM 0.22 vllm/v1/attention/backends/triton_attn.py:453-454)."""
+        try:
+            from vllm.model_executor.layers.quantization.utils.quant_utils import kFp8StaticTensorSym
+        except Exception:  # pragma: no cover - depends on the installed vLLM
+            return False
+        return quant_key == kFp8StaticTensorSym
+
     def fused_rope_kvcache_supported(self) -> bool:
         """RoPE + cache write in one launch (ops.rope_and_cache_flash); vLLM's
         RopeKVCacheFusionPass asks before rewriting the graph."""
@@ -315,9 +339,9 @@ class B200AttentionImpl(AttentionImpl):
         output_block_scale: Optional[torch.Tensor] = None,
     ) -> torch.Tensor:
         assert output is not None, "Output tensor must be provided."  # reference :366
-        if output_scale is not None or output_block_scale is not None:
-            raise NotImplementedError(  # reference :368-372
-                "fused output quantization is not yet supported for B200AttentionImpl"
+        if output_block_scale is not None:
+            raise NotImplementedError(  # vLLM 0.22 triton_attn.py:557-561 (reference :368-372 rejected both)
+                "fused block_scale output quantization is not yet supported for B200AttentionImpl"
             )
         if attn_metadata is None:
             return output.fill_(0)  # profiling run (reference :374-376)
@@ -330,6 +354,6 @@ class B200AttentionImpl(AttentionImpl):
         # window/softcap/alibi/scales are fixed per layer and live in the plan
         self._plans_for(layer, kv_cache, query.dtype)[1](
             q, out, attn_metadata.query_start_loc, attn_metadata.max_query_len, attn_metadata.seq_lens,
-            attn_metadata.max_seq_len, attn_metadata.block_table, attn_metadata.workspace,
+            attn_metadata.max_seq_len, attn_metadata.block_table, attn_metadata.workspace, output_scale,
         )
         return output

@@ -231,8 +231,10 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
           m &= m - 1;
           const int tq = __shfl_sync(0xffffffffu, tq_r[r], src);
           for (int e = lane; e < P.a.num_q_heads * D; e += 32) {
-            char* orow = static_cast<char*>(P.a.out) + ((int64_t)tq * P.a.out_stride0 + (int64_t)(e / D) * P.a.out_stride1) * 2;
-            reinterpret_cast<uint16_t*>(orow)[e % D] = 0;
+            const int osz = P.a.out_scale ? 1 : 2;  // fp8 output: one byte per element, 0x00 == +0
+            char* orow = static_cast<char*>(P.a.out) + ((int64_t)tq * P.a.out_stride0 + (int64_t)(e / D) * P.a.out_stride1) * osz;
+            if (osz == 1) orow[e % D] = 0;
+            else reinterpret_cast<uint16_t*>(orow)[e % D] = 0;
           }
         }
       }
@@ -301,8 +303,10 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
       if (sl <= 0 && ql == 1) {
         const int tq = P.a.cu_seqlens_q ? P.a.cu_seqlens_q[b] : b;
         for (int e = threadIdx.x; e < P.a.num_q_heads * D; e += blockDim.x) {
-          char* orow = static_cast<char*>(P.a.out) + ((int64_t)tq * P.a.out_stride0 + (int64_t)(e / D) * P.a.out_stride1) * 2;
-          reinterpret_cast<uint16_t*>(orow)[e % D] = 0;
+          const int osz = P.a.out_scale ? 1 : 2;
+          char* orow = static_cast<char*>(P.a.out) + ((int64_t)tq * P.a.out_stride0 + (int64_t)(e / D) * P.a.out_stride1) * osz;
+          if (osz == 1) orow[e % D] = 0;
+          else reinterpret_cast<uint16_t*>(orow)[e % D] = 0;
         }
       }
     }
@@ -769,9 +773,14 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
             const int hq = cur.hg * P.hpc * P.group + hq_in_cta;
             if (P.a.sinks) val *= sink_rescale<true>(P.a.sinks[hq], M, L);
             const float o = (L > 0.f) ? val * v_scale / L : 0.f;
-            char* orow = static_cast<char*>(P.a.out) + ((int64_t)tq * P.a.out_stride0 + (int64_t)hq * P.a.out_stride1) * 2;
-            if constexpr (Q_BF16) reinterpret_cast<__nv_bfloat16*>(orow)[d] = __float2bfloat16_rn(o);
-            else reinterpret_cast<__half*>(orow)[d] = __float2half_rn(o);
+            const int64_t oel = (int64_t)tq * P.a.out_stride0 + (int64_t)hq * P.a.out_stride1;
+            if (P.a.out_scale) {  // fused e4m3 output quantisation (b200attn.h: out_scale)
+              static_cast<uint8_t*>(P.a.out)[oel + d] = fp8_out(o * out_quant_factor(P.a.out_scale));
+            } else {
+              char* orow = static_cast<char*>(P.a.out) + oel * 2;
+              if constexpr (Q_BF16) reinterpret_cast<__nv_bfloat16*>(orow)[d] = __float2bfloat16_rn(o);
+              else reinterpret_cast<__half*>(orow)[d] = __float2half_rn(o);
+            }
           } else {
             const int64_t slot = (int64_t)item + blockIdx.x;
             const int64_t rec = slot * (P.hpc * P.group) + hq_in_cta;
@@ -842,12 +851,18 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
             float fs = 1.f;
             if (P.a.sinks) fs = sink_rescale<true>(P.a.sinks[hq], M, L);  // once per item, here (upstream: segment 0 only)
             const float inv = (L > 0.f) ? fs * v_scale / L : 0.f;  // 0 when nothing is visible (reference :828)
-            char* orow = static_cast<char*>(P.a.out) + ((int64_t)tq * P.a.out_stride0 + (int64_t)hq * P.a.out_stride1) * 2;
+            const int64_t oel = (int64_t)tq * P.a.out_stride0 + (int64_t)hq * P.a.out_stride1;
             const float o4[4] = {val.x * inv, val.y * inv, val.z * inv, val.w * inv};
+            if (P.a.out_scale) {
+              const float oq = out_quant_factor(P.a.out_scale);
+              *reinterpret_cast<uint32_t*>(static_cast<char*>(P.a.out) + oel + d4) = fp8x4_out(o4[0] * oq, o4[1] * oq, o4[2] * oq, o4[3] * oq);
+            } else {
+              char* orow = static_cast<char*>(P.a.out) + oel * 2;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              if constexpr (Q_BF16) reinterpret_cast<__nv_bfloat16*>(orow)[d4 + j] = __float2bfloat16_rn(o4[j]);
-              else reinterpret_cast<__half*>(orow)[d4 + j] = __float2half_rn(o4[j]);
+              for (int j = 0; j < 4; ++j) {
+                if constexpr (Q_BF16) reinterpret_cast<__nv_bfloat16*>(orow)[d4 + j] = __float2bfloat16_rn(o4[j]);
+                else reinterpret_cast<__half*>(orow)[d4 + j] = __float2half_rn(o4[j]);
+              }
             }
           }
           if (threadIdx.x == 0) P.ws_cnt[item] = 0;  // self-cleaning: ready for the next call

@@ -315,7 +315,16 @@ attn_prefill_kernel(const b200attn_attention_params p, const int block_q, const 
     float f = 1.f;
     if (p.sinks) f = sink_rescale<true>(p.sinks[hq], m_run[ri], l);
     const float inv = (l > 0.f) ? f * v_scale / l : 0.f;
-    char* orow = static_cast<char*>(p.out) + ((int64_t)(q_start + row_qpos[ri]) * p.out_stride0 + (int64_t)hq * p.out_stride1) * 2;
+    const int64_t oel = (int64_t)(q_start + row_qpos[ri]) * p.out_stride0 + (int64_t)hq * p.out_stride1;
+    if (p.out_scale) {  // fused e4m3 output quantisation (b200attn.h: out_scale)
+      const float oq = inv * out_quant_factor(p.out_scale);
+      char* orow = static_cast<char*>(p.out) + oel;
+#pragma unroll
+      for (int dt = 0; dt < DT; ++dt)
+        *reinterpret_cast<uint16_t*>(orow + dt * 8 + 2 * t4) = (uint16_t)fp8x2_out(oacc[dt][2 * ri] * oq, oacc[dt][2 * ri + 1] * oq);
+      continue;
+    }
+    char* orow = static_cast<char*>(p.out) + oel * 2;
 #pragma unroll
     for (int dt = 0; dt < DT; ++dt) {
       const float a = oacc[dt][2 * ri] * inv, c = oacc[dt][2 * ri + 1] * inv;

@@ -486,14 +486,24 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
       mbar_wait(&bars[O_DONE + w], (t_run + (uint32_t)last_tile) & 1);
       tc_fence_after();
       const float inv = (l_sum > 0.f) ? 1.f / l_sum : 0.f;
+      const bool out_fp8 = a.out_scale != nullptr;  // fused e4m3 output quantisation (b200attn.h: out_scale)
+      const float oq = inv * out_quant_factor(a.out_scale);
       char* orow = static_cast<char*>(a.out) +
-                   ((int64_t)(it.q_start + (row_valid ? qpos : 0)) * a.out_stride0 + (int64_t)(kvh * g + head) * a.out_stride1) * 2;
+                   ((int64_t)(it.q_start + (row_valid ? qpos : 0)) * a.out_stride0 + (int64_t)(kvh * g + head) * a.out_stride1) * (out_fp8 ? 1 : 2);
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
         uint32_t t[32];
         tmem_ld32(o_tmem + c * 32, t);
         tmem_ld_wait();
-        if (row_valid) {
+        if (row_valid && out_fp8) {
+#pragma unroll
+          for (int i = 0; i < 32; i += 8) {
+            int2 v;
+            v.x = (int)fp8x4_out(__uint_as_float(t[i]) * oq, __uint_as_float(t[i + 1]) * oq, __uint_as_float(t[i + 2]) * oq, __uint_as_float(t[i + 3]) * oq);
+            v.y = (int)fp8x4_out(__uint_as_float(t[i + 4]) * oq, __uint_as_float(t[i + 5]) * oq, __uint_as_float(t[i + 6]) * oq, __uint_as_float(t[i + 7]) * oq);
+            *reinterpret_cast<int2*>(orow + c * 32 + i) = v;
+          }
+        } else if (row_valid) {
 #pragma unroll
           for (int i = 0; i < 32; i += 8) {
             int4 v;
@@ -554,10 +564,10 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
           for (int r = lane; r < 256; r += 32) {
             const int qpos = it.qpos0 + r / g;
             if (qpos < it.q_len) {
-              int4* orow = reinterpret_cast<int4*>(static_cast<char*>(a.out) +
-                                                   ((int64_t)(it.q_start + qpos) * a.out_stride0 + (int64_t)(it.kvh * g + r % g) * a.out_stride1) * 2);
-#pragma unroll
-              for (int i = 0; i < kD * 2 / 16; ++i) orow[i] = make_int4(0, 0, 0, 0);
+              const int osz = a.out_scale ? 1 : 2;
+              int2* orow = reinterpret_cast<int2*>(static_cast<char*>(a.out) +
+                                                   ((int64_t)(it.q_start + qpos) * a.out_stride0 + (int64_t)(it.kvh * g + r % g) * a.out_stride1) * osz);
+              for (int i = 0; i < kD * osz / 8; ++i) orow[i] = make_int2(0, 0);
             }
           }
         } else if (it.n_tiles > 0) {

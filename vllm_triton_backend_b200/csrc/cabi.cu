@@ -94,6 +94,11 @@ int validate_attention(const b200attn_attention_params& p) {
     set_error("unified_attention: head_size %d > 256", p.head_size);
     return B200ATTN_E_BAD_SHAPE;
   }
+  if (p.out_scale && ((reinterpret_cast<uintptr_t>(p.out) & 7) || p.out_stride0 % 8 || p.out_stride1 % 8 || p.head_size % 8)) {
+    set_error("unified_attention: fp8 output rows must be 8-byte aligned (out=%p strides %lld,%lld)", p.out,
+              (long long)p.out_stride0, (long long)p.out_stride1);
+    return B200ATTN_E_ALIGNMENT;
+  }
   return B200ATTN_OK;
 }
 
@@ -105,6 +110,9 @@ using namespace b200attn;
 extern "C" {
 
 int b200attn_abi_version(void) { return B200ATTN_ABI_VERSION; }
+uint64_t b200attn_params_size(int32_t which) {
+  return which == 0 ? sizeof(b200attn_attention_params) : which == 1 ? sizeof(b200attn_rope_cache_params) : 0;
+}
 const char* b200attn_last_error(void) { return g_error; }
 uint64_t b200attn_launch_count(void) { return g_launches; }
 void b200attn_reset_launch_count(void) { g_launches = 0; }

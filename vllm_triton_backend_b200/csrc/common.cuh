@@ -153,6 +153,17 @@ template <bool m_is_log2> __device__ __forceinline__ float sink_rescale(float si
   return f;
 }
 
+// ---- fused FP8 output quantisation (b200attn_attention_params::out_scale) -----
+// Upstream: `acc = acc * tl.load(out_scale)` with out_scale = 1/output_scale, clamp to the e4m3
+// range, store as e4m3 (vllm/v1/attention/ops/triton_unified_attention.py:608-610, 722-724).
+// Saturating round-to-nearest-even conversion == clamp + rn.
+__device__ __forceinline__ float out_quant_factor(const float* out_scale) { return out_scale ? 1.0f / __ldg(out_scale) : 0.f; }
+__device__ __forceinline__ uint32_t fp8x2_out(float lo, float hi) {
+  return (uint32_t)__nv_cvt_float2_to_fp8x2(make_float2(lo, hi), __NV_SATFINITE, __NV_E4M3);
+}
+__device__ __forceinline__ uint32_t fp8x4_out(float a, float b, float c, float d) { return fp8x2_out(a, b) | (fp8x2_out(c, d) << 16); }
+__device__ __forceinline__ uint8_t fp8_out(float x) { return (uint8_t)__nv_cvt_float_to_fp8(x, __NV_SATFINITE, __NV_E4M3); }
+
 // ---- mbarrier / TMA / ldmatrix / mma wrappers --------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));

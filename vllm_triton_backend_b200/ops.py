@@ -153,9 +153,22 @@ def scaled_fp8_quant(x: torch.Tensor, scale: torch.Tensor) -> Tuple[torch.Tensor
     return out, scale
 
 
+def _check_out(out, q_dtype, output_scale) -> None:
+    """`output_scale` (upstream keyword: fused static per-tensor FP8 quantisation of the output,
+    vllm/v1/attention/ops/triton_unified_attention.py:786,986) switches `out` to float8_e4m3fn."""
+    if output_scale is None:
+        if out.dtype != q_dtype:
+            raise ValueError("out dtype must equal q dtype")
+        return
+    if out.dtype not in (torch.float8_e4m3fn, torch.uint8):
+        raise ValueError("with output_scale the output must be float8_e4m3fn")
+    if output_scale.dtype != torch.float32 or output_scale.numel() != 1 or not output_scale.is_cuda:
+        raise ValueError("output_scale must be a one-element float32 CUDA tensor")
+
+
 def build_attention_params(
     q, k, v, out, cu_seqlens_q, max_seqlen_q, seqused_k, max_seqlen_k, softmax_scale, window_size, block_table,
-    softcap, k_descale, v_descale, alibi_slopes, path, workspace, sinks=None,
+    softcap, k_descale, v_descale, alibi_slopes, path, workspace, sinks=None, output_scale=None,
 ) -> AttentionParams:
     if q.dim() != 3 or k.dim() != 4 or v.dim() != 4:
         raise ValueError("q must be [T, Hq, D]; k, v must be [NB, bs, Hkv, D]")
@@ -163,8 +176,7 @@ def build_attention_params(
         raise ValueError("innermost dimension of q/out/k/v must be contiguous")
     if block_table.dtype != torch.int32 or seqused_k.dtype != torch.int32 or cu_seqlens_q.dtype != torch.int32:
         raise ValueError("block_table, seqused_k and cu_seqlens_q must be int32")
-    if out.dtype != q.dtype:
-        raise ValueError("out dtype must equal q dtype")
+    _check_out(out, q.dtype, output_scale)
     q_dt, kv_dt = _DTYPE.get(q.dtype), _DTYPE.get(k.dtype)
     if q_dt is None or q_dt == _cabi.FP8_E4M3:
         raise ValueError(f"unsupported query dtype {q.dtype}")
@@ -179,6 +191,7 @@ def build_attention_params(
     if sinks is not None and (sinks.dtype != torch.float32 or sinks.shape[0] != q.shape[1] or not sinks.is_contiguous()):
         raise ValueError("sinks must be a contiguous float32 tensor with one entry per query head")
     p.sinks = sinks.data_ptr() if sinks is not None else None
+    p.out_scale = output_scale.data_ptr() if output_scale is not None else None
     p.softmax_scale = float(softmax_scale)
     p.softcap = float(softcap or 0.0)
     p.sliding_window = int(1 + window_size[0]) if window_size is not None else 0  # reference :915
@@ -223,6 +236,7 @@ def unified_attention(
     force_selection: Optional[int] = None,  # None, 2 (2D kernel), 3 (3D kernel) as in the reference; 1 = SIMT net
     workspace: Optional[torch.Tensor] = None,
     sinks: Optional[torch.Tensor] = None,  # [Hq] float32 (upstream keyword)
+    output_scale: Optional[torch.Tensor] = None,  # upstream keyword: `out` is e4m3, out = quant(o / output_scale)
     **_ignored,
 ) -> None:
     if not causal:
@@ -257,7 +271,7 @@ def unified_attention(
         workspace = get_workspace(q.device, need)
     p = build_attention_params(
         q, k, v, out, cu_seqlens_q, max_seqlen_q, seqused_k, max_seqlen_k, softmax_scale, window_size, block_table,
-        softcap, k_descale, v_descale, alibi_slopes, path, workspace, sinks,
+        softcap, k_descale, v_descale, alibi_slopes, path, workspace, sinks, output_scale,
     )
     _cabi.check(_cabi.load_library().b200attn_unified_attention(ctypes.byref(p), _stream_ptr(q)))
 
@@ -309,12 +323,16 @@ class AttentionPlan:
         self._ws_ptr = None
         self.num_q_heads, self.head_size, self.q_dtype = num_q_heads, head_size, q_dtype
 
-    def __call__(self, q, out, cu_seqlens_q, max_seqlen_q, seqused_k, max_seqlen_k, block_table, workspace) -> None:
-        """q/out: [T, Hq, D] views (innermost contiguous); metadata tensors int32 on the device."""
-        if q.dtype != self.q_dtype or out.dtype != self.q_dtype or not q.is_cuda:
-            raise ValueError("query/output dtype or device differs from the plan")
+    def __call__(self, q, out, cu_seqlens_q, max_seqlen_q, seqused_k, max_seqlen_k, block_table, workspace,
+                 output_scale=None) -> None:
+        """q/out: [T, Hq, D] views (innermost contiguous); metadata tensors int32 on the device.
+        `output_scale`: one-element fp32 device tensor => `out` is float8_e4m3fn (fused output quant)."""
+        if q.dtype != self.q_dtype or not q.is_cuda:
+            raise ValueError("query dtype or device differs from the plan")
+        _check_out(out, self.q_dtype, output_scale)
         p = self.p
         p.q, p.out = q.data_ptr(), out.data_ptr()
+        p.out_scale = output_scale.data_ptr() if output_scale is not None else None
         qs, os_ = q.stride(), out.stride()
         if qs[2] != 1 or os_[2] != 1:
             raise ValueError("innermost dimension of q/out must be contiguous")
