@@ -285,18 +285,20 @@ def prefill_case(args, device):
         ws_bytes += ops.fp8_staging_bytes(len(lens), sum(kv for q, kv in lens if q > 16), bs, hkv, D)
     ws = torch.zeros(ws_bytes, dtype=torch.uint8, device=device)
     flops = attention_flops(q_lens, kv_lens, hq, D)
+    softcap = float(getattr(args, "softcap", 0.0) or 0.0)
 
     def fn():
         ops.unified_attention(q=q, k=kc, v=vc, out=out, cu_seqlens_q=cu, max_seqlen_q=max(q_lens), seqused_k=sl,
                               max_seqlen_k=max(kv_lens), softmax_scale=D ** -0.5, causal=True, window_size=(-1, -1),
-                              block_table=bt, softcap=0, q_descale=None, k_descale=sc, v_descale=sc, workspace=ws,
+                              block_table=bt, softcap=softcap, q_descale=None, k_descale=sc, v_descale=sc, workspace=ws,
                               force_selection=args.force)
     if getattr(args, "impl", "ours") == "triton":
         tri = triton_reference().TritonReference(len(lens), hq, D, device)
 
         def fn():  # noqa: F811
-            tri(q, kc, vc, out, cu, max(q_lens), sl, max(kv_lens), D ** -0.5, bt, k_scale=sc, v_scale=sc)
-    return fn, flops, dict(shape=args.shape, T=T, seqs=len(lens), hq=hq, hkv=hkv, D=D, bs=bs, fp8=bool(args.fp8))
+            tri(q, kc, vc, out, cu, max(q_lens), sl, max(kv_lens), D ** -0.5, bt, k_scale=sc, v_scale=sc, softcap=softcap)
+    return fn, flops, dict(shape=args.shape, T=T, seqs=len(lens), hq=hq, hkv=hkv, D=D, bs=bs, fp8=bool(args.fp8),
+                           softcap=softcap)
 
 
 def run_prefill(args, device):
@@ -353,6 +355,7 @@ def main():
     ap.add_argument("--flush", action="store_true")
     ap.add_argument("--layout", default="planes", choices=["planes", "interleaved"])
     ap.add_argument("--force", type=int, default=None)
+    ap.add_argument("--softcap", type=float, default=0.0, help="prefill: logit soft cap (0 = off)")
     ap.add_argument("--no-staging", action="store_true", help="fp8 prefill: no staging pool (mma.sync kernel only)")
     ap.add_argument("--graph", action="store_true", help="decode: time 20 calls captured in one CUDA graph")
     ap.add_argument("--trace", action="store_true", help="decode: print per-CTA phase times of one launch first")

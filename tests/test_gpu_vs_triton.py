@@ -99,6 +99,14 @@ def test_features_match_triton(window, softcap, alibi):
     assert_close(ours, ref, atol=BF16_ATOL, rtol=BF16_RTOL, what=f"features vs triton ({kern})")
 
 
+@pytest.mark.parametrize("softcap,window", [(30.0, 0), (50.0, 256)])
+def test_long_prompt_softcap_matches_triton(softcap, window):
+    # Gemma-2-27B-like: D=128, softcap on the logits, optional sliding window; runs the tcgen05 kernel
+    # (tests/test_gpu_attention.py::test_prefill_tc_softcap_and_sinks pins the routing)
+    ours, ref, kern = _both([(2048, 2048), (700, 1500)], 32, 16, 128, 16, softcap=softcap, window=window, seed=19)
+    assert_close(ours, ref, atol=BF16_ATOL, rtol=BF16_RTOL, what=f"softcap {softcap} vs triton ({kern})")
+
+
 def test_fp8_kv_prefill_matches_triton():
     ours, ref, kern = _both([(300, 300), (64, 1064), (1, 555)], 32, 8, 128, 16, fp8=True, k_scale=0.37, v_scale=0.61,
                             seed=13)
@@ -109,9 +117,8 @@ def test_fp8_kv_prefill_matches_triton():
     ([(1, 900), (1, 40), (1, 3000), (1, 1)], 64, 128),       # gpt-oss-like decode: D=64, sliding window + sinks
     ([(1, 900), (1, 40), (1, 3000)], 128, 0),
     ([(1, 700), (200, 700), (1, 40), (333, 333)], 64, 128),  # mixed batch
-    ([(512, 512), (64, 1064)], 128, 0),                       # D=128 prefill with sinks: mma.sync kernel, not tcgen05
+    ([(512, 512), (64, 1064)], 128, 0),                       # D=128 prefill with sinks: tcgen05 kernel epilogue
 ])
 def test_attention_sinks_match_triton(lens, D, window):
     ours, ref, kern = _both(lens, 16, 2, D, 16, window=window, sinks=True, seed=17)
-    assert kern != "attn_prefill_tc"
     assert_close(ours, ref, atol=BF16_ATOL, rtol=BF16_RTOL, what=f"sinks vs triton ({kern})")

@@ -185,6 +185,11 @@ __device__ __forceinline__ bool elect_one() {
   asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
   return pred != 0;
 }
+__device__ __forceinline__ float tanh_approx(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 __device__ __forceinline__ float ex2_approx(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -281,7 +286,10 @@ constexpr int kSmemBytes = kSmemClc + 64 + 1024;     // + alignment slack
 constexpr int kConsumerWarps = 11;                   // warps 0..10 read every item
 
 // kEmuNum of every kEmuDen exponential pairs are computed by ex2_poly2, the rest on the MUFU.
-template <bool kBf16, int kEmuNum, int kEmuDen>
+// kSoftcap: logits are cap * tanh(s * scale / cap) (reference apply_softcap, triton_unified_attention.py:24-29,
+// 467-468): S is replaced by tanh(S * scale / cap) right after it leaves TMEM (one MUFU op per element, before
+// masking, as the reference caps before it masks) and `cap` takes the place of the softmax scale.
+template <bool kBf16, int kEmuNum, int kEmuDen, bool kSoftcap = false>
 __global__ void __launch_bounds__(kThreads, 1)
 attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CUtensorMap k_map,
                        const __grid_constant__ CUtensorMap v_map) {
@@ -341,7 +349,7 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
   // ---- state shared by the roles that consume the work queue -------------------------------
   uint32_t n_items = 0;   // items taken so far (mailbox slot / phase)
   uint32_t t_run = 0;     // KV tiles processed so far: parity source of the per-tile barriers
-  const float scale_log2 = a.softmax_scale * kLog2e;
+  const float scale_log2 = (kSoftcap ? a.softcap : a.softmax_scale) * kLog2e;
   int k_st = 0, v_st = 0;           // ring positions (TMA warps: next to fill; MMA warp: next to use)
   uint32_t k_ph = 0, v_ph = 0;
   uint32_t n_fix = 0;               // V tail fix-ups so far (V_FIX parity)
@@ -400,6 +408,13 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
         for (int c = 0; c < 4; ++c) tmem_ld32(s_tmem + c * 32, s[c]);
         tmem_ld_wait();
         if (row == 0) TC_TRACE(t_run + j, w * 5 + 1);
+        if constexpr (kSoftcap) {
+          const float pre = a.softmax_scale / a.softcap;
+#pragma unroll
+          for (int c = 0; c < 4; ++c)
+#pragma unroll
+            for (int i = 0; i < 32; ++i) s[c][i] = __float_as_uint(tanh_approx(__uint_as_float(s[c][i]) * pre));
+        }
         const int n0 = (tile0 + j) * kBN;
         if (n0 + kBN > limit || n0 < lo) {
 #pragma unroll
@@ -485,7 +500,9 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
       // is only produced after the loads below have completed: no extra barrier is needed.
       mbar_wait(&bars[O_DONE + w], (t_run + (uint32_t)last_tile) & 1);
       tc_fence_after();
-      const float inv = (l_sum > 0.f) ? 1.f / l_sum : 0.f;
+      float fs = 1.f;
+      if (a.sinks && row_valid) fs = sink_rescale<true>(a.sinks[kvh * g + head], m_used, l_sum);  // once per row, after the last tile
+      const float inv = (l_sum > 0.f) ? fs / l_sum : 0.f;
       const bool out_fp8 = a.out_scale != nullptr;  // fused e4m3 output quantisation (b200attn.h: out_scale)
       const float oq = inv * out_quant_factor(a.out_scale);
       char* orow = static_cast<char*>(a.out) +
@@ -818,7 +835,8 @@ bool prefill_tc_supported(const b200attn_attention_params& p, const char** why) 
   const int g = p.num_q_heads / p.num_kv_heads;
   if (!pow2(g) || g > 128) return no("GQA group not a power of two <= 128");
   if (!pow2(p.block_size) || p.block_size < 16) return no("block_size not a power of two >= 16");
-  if (p.softcap != 0.f || p.alibi_slopes || p.sinks) return no("softcap / ALiBi / sinks");
+  if (p.alibi_slopes) return no("ALiBi");
+  if (p.softcap < 0.f) return no("softcap < 0");
   if (!(p.softmax_scale > 0.f)) return no("softmax_scale <= 0");
   auto m8 = [&](int64_t s) { return s % 8 == 0; };
   if (!m8(p.kc_block_stride) || !m8(p.kc_slot_stride) || !m8(p.kc_head_stride) || !m8(p.vc_block_stride) ||
@@ -857,12 +875,16 @@ int launch_attn_prefill_tc(const b200attn_attention_params& a, cudaStream_t stre
   // fraction of the exponentials taken off the MUFU (tuning().reserved bits 4..7; 0 = default)
   using Kern = void (*)(const TcParams, const CUtensorMap, const CUtensorMap, const CUtensorMap);
 #define TCV(B) {attn_prefill_tc_kernel<B, 0, 1>, attn_prefill_tc_kernel<B, 0, 1>, attn_prefill_tc_kernel<B, 1, 4>, \
-                attn_prefill_tc_kernel<B, 1, 3>, attn_prefill_tc_kernel<B, 1, 2>}
-  constexpr int kNumVariants = 5;
+                attn_prefill_tc_kernel<B, 1, 3>, attn_prefill_tc_kernel<B, 1, 2>, attn_prefill_tc_kernel<B, 0, 1, true>, \
+                attn_prefill_tc_kernel<B, 1, 2, true>}
+  // softcap (variants 5, 6): the tanh doubles the MUFU work; moving half the exps to the FMA pipe (6) measured
+  // slower than leaving them (5): 8k prompt 0.705 ms vs 0.671 ms (profiles/r01_kbench_softcap_tc.jsonl)
+  constexpr int kNumVariants = 7, kSoftcapVariant = 5;
   static const Kern kVariants[2][kNumVariants] = {TCV(false), TCV(true)};
 #undef TCV
   int variant = (tuning().reserved >> 4) & 15;
-  if (variant >= kNumVariants) variant = 0;
+  if (variant >= kSoftcapVariant) variant = 0;
+  if (a.softcap > 0.f) variant = (((tuning().reserved >> 4) & 15) == 6) ? 6 : kSoftcapVariant;
   Kern kern = kVariants[bf16 ? 1 : 0][variant];
   static thread_local bool attr_set[2][kNumVariants] = {};
   if (!attr_set[bf16 ? 1 : 0][variant]) {
