@@ -147,6 +147,9 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
     }
     fence_barrier_init();
   }
+  // Everything above touched only shared memory and kernel parameters.  From here on the kernel reads what
+  // earlier kernels on the stream wrote (metadata, q, the cache): wait for them (no-op without PDL).
+  pdl_wait();
   int my_begin, my_end, per_cta;
   ItemCursor cur;
   int tq_first = 0;  // first query-token index of cur.b
@@ -971,7 +974,15 @@ int launch_variant(const b200attn_attention_params& a, DecodeParams& P, cudaStre
     }
     attr_set = true;
   }
-  kern<<<(unsigned)grid, (NW + 1) * 32, smem, stream>>>(P, kmap, vmap);
+  // Programmatic dependent launch: lets this grid's launch and prologue overlap the cache write in front of it
+  // (common.cuh).  tuning().reserved bit 9 turns it off.
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid), cfg.blockDim = dim3((NW + 1) * 32), cfg.dynamicSmemBytes = (size_t)smem, cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr, cfg.numAttrs = (tn.reserved & 512) ? 0 : 1;
+  cudaLaunchKernelEx(&cfg, kern, P, kmap, vmap);
   note_launch("attn_decode_split_kv");
   return check_launch("attn_decode");
 }

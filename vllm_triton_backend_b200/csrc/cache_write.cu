@@ -66,6 +66,7 @@ struct CacheWriteArgs {
 // Copy path: 16-byte vectors of kElemBytes-sized elements.
 template <int kElemBytes>
 __global__ void __launch_bounds__(256) cache_copy_vec_kernel(CacheWriteArgs a) {
+  pdl_launch_dependents();  // the attention launch behind us may start its prologue now (common.cuh)
   constexpr int kVec = 16 / kElemBytes;
   const int64_t token = blockIdx.x;
   const int which = blockIdx.y;
@@ -86,6 +87,7 @@ __global__ void __launch_bounds__(256) cache_copy_vec_kernel(CacheWriteArgs a) {
 // FP8 path, 16 elements per thread: two 16-byte loads, one 16-byte store.
 template <typename SrcT>
 __global__ void __launch_bounds__(256) cache_quant_vec16_kernel(CacheWriteArgs a) {
+  pdl_launch_dependents();  // the attention launch behind us may start its prologue now (common.cuh)
   const int64_t token = blockIdx.x;
   const int which = blockIdx.y;
   const int64_t slot = a.slot_mapping[token];
@@ -115,6 +117,7 @@ __global__ void __launch_bounds__(256) cache_quant_vec16_kernel(CacheWriteArgs a
 // Element-wise net for shapes/alignments the vector kernels do not take.
 template <typename SrcT, bool kQuant>
 __global__ void __launch_bounds__(256) cache_scalar_kernel(CacheWriteArgs a) {
+  pdl_launch_dependents();  // the attention launch behind us may start its prologue now (common.cuh)
   const int64_t token = blockIdx.x;
   const int which = blockIdx.y;
   const int64_t slot = a.slot_mapping[token];

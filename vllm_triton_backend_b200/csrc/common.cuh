@@ -164,6 +164,15 @@ __device__ __forceinline__ uint32_t fp8x2_out(float lo, float hi) {
 __device__ __forceinline__ uint32_t fp8x4_out(float a, float b, float c, float d) { return fp8x2_out(a, b) | (fp8x2_out(c, d) << 16); }
 __device__ __forceinline__ uint8_t fp8_out(float x) { return (uint8_t)__nv_cvt_float_to_fp8(x, __NV_SATFINITE, __NV_E4M3); }
 
+// ---- programmatic dependent launch (griddepcontrol) ---------------------------
+// The cache write (K1 / K5) is always followed on the stream by the attention launch of the same layer.  The
+// writers release their dependents as soon as they start; the decode kernel is launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization and sets up shared memory, barriers and descriptors while
+// the writer is still running, then waits (full completion + memory flush of everything before it) in front
+// of its first global-memory read.  After any other kernel (which never triggers) the launch behaves as usual.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ---- mbarrier / TMA / ldmatrix / mma wrappers --------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));

@@ -82,6 +82,7 @@ __device__ __forceinline__ void to_cache(void* cache_row, int d, const Vec8<T>& 
 
 template <typename T, bool kNeox, bool kQuant>
 __global__ void __launch_bounds__(256) rope_cache_kernel(const RopeArgs a) {
+  pdl_launch_dependents();  // the attention launch behind us may start its prologue now (common.cuh)
   const int64_t t = blockIdx.x;
   const bool do_rope = t < a.rope_tokens;
   int64_t slot = -1;
