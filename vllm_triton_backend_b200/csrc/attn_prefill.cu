@@ -34,10 +34,13 @@ template <int ROWB> __device__ __forceinline__ uint32_t swz_off(int r, int c) {
   return (uint32_t)(r * ROWB + ((c ^ (r & 7)) << 4));
 }
 
-template <int D, bool MMA_BF16, bool Q_BF16, bool KV_FP8>
+// kPlain: no softcap, no ALiBi and a positive scale -- the scale then folds into the exp2 argument
+// (one FFMA per logit) and the row max is taken over the raw dot products.
+// bs_shift: log2(block_size) when it is a power of two (page = pos >> bs_shift), else -1 (division).
+template <int D, bool MMA_BF16, bool Q_BF16, bool KV_FP8, bool kPlain>
 __global__ void __launch_bounds__(NWARPS * 32, (D <= 128) ? 2 : 1)
 attn_prefill_kernel(const b200attn_attention_params p, const int block_q, const int group, const int min_q_len,
-                    const int max_q_len, const int qb_per_seq, const int32_t* skip_staged) {
+                    const int max_q_len, const int qb_per_seq, const int32_t* skip_staged, const int bs_shift) {
   constexpr int ROWB = D * 2;           // smem row bytes (operands are 2-byte in smem)
   constexpr int CPR = ROWB / 16;        // 16-byte chunks per row
   constexpr int KSTEPS = D / 16;
@@ -90,6 +93,7 @@ attn_prefill_kernel(const b200attn_attention_params p, const int block_q, const 
   const bool has_cap = p.softcap > 0.f;
   const float inv_cap = has_cap ? 1.f / p.softcap : 0.f;
   const float qk_scale = p.softmax_scale * k_scale;
+  const float scale_log2 = qk_scale * kLog2e;
 
   // ---- load the Q tile: row r = (token r / group, head r % group) --------------
   const int rows_used = block_q * group;
@@ -114,39 +118,44 @@ attn_prefill_kernel(const b200attn_attention_params p, const int block_q, const 
   }
 
   // ---- KV tile loader -----------------------------------------------------------
+  // Thread `tid` always copies the same 16-byte column of rows ld_r0, ld_r0 + RSTEP, ...: the column, the
+  // head offset and the swizzle are hoisted out of the tile loop; per row there is one block-table load and
+  // one 32x32->64-bit multiply-add per cache (strides < 2^31 elements, checked on the host).
+  constexpr int ESZ = KV_FP8 ? 1 : 2;
+  constexpr int CPT = KV_FP8 ? D / 16 : CPR;       // 16-byte global chunks per cache row
+  constexpr int RSTEP = NWARPS * 32 / CPT;         // rows between two chunks of one thread
+  const int ld_c = tid % CPT, ld_r0 = tid / CPT;
+  const char* k_col = static_cast<const char*>(p.k_cache) + ((int64_t)kvh * p.kc_head_stride) * ESZ + ld_c * 16;
+  const char* v_col = static_cast<const char*>(p.v_cache) + ((int64_t)kvh * p.vc_head_stride) * ESZ + ld_c * 16;
+  const int kc_bs = (int)p.kc_block_stride * ESZ, kc_ss = (int)p.kc_slot_stride * ESZ;
+  const int vc_bs = (int)p.vc_block_stride * ESZ, vc_ss = (int)p.vc_slot_stride * ESZ;
+  const int bs_mask = p.block_size - 1;
   auto load_tile = [&](int tile, int buf) {
     const int n0 = tile * BN;
     uint8_t* dK = sK + buf * TILE_B;
     uint8_t* dV = sV + buf * TILE_B;
-    if constexpr (!KV_FP8) {
-      for (int idx = tid; idx < BN * CPR; idx += NWARPS * 32) {
-        const int r = idx / CPR, c = idx % CPR;
-        const int pos = n0 + r;
-        const bool ok = pos < kv_limit;
-        const int64_t page = ok ? bt[pos / p.block_size] : 0;
-        const int slot = pos % p.block_size;
-        const char* ksrc = static_cast<const char*>(p.k_cache) +
-                           (page * p.kc_block_stride + (int64_t)slot * p.kc_slot_stride + (int64_t)kvh * p.kc_head_stride) * 2 + c * 16;
-        const char* vsrc = static_cast<const char*>(p.v_cache) +
-                           (page * p.vc_block_stride + (int64_t)slot * p.vc_slot_stride + (int64_t)kvh * p.vc_head_stride) * 2 + c * 16;
-        cp_async_16(smem_u32(dK + swz_off<ROWB>(r, c)), ksrc, ok);
-        cp_async_16(smem_u32(dV + swz_off<ROWB>(r, c)), vsrc, ok);
+#pragma unroll
+    for (int k = 0; k < BN / RSTEP; ++k) {
+      const int r = ld_r0 + k * RSTEP;
+      const int pos = n0 + r;
+      const bool ok = pos < kv_limit;
+      int page = 0, slot = 0;
+      if (ok) {
+        if (bs_shift >= 0) page = bt[pos >> bs_shift], slot = pos & bs_mask;
+        else page = bt[pos / p.block_size], slot = pos % p.block_size;
       }
-    } else {
-      // 16 fp8 -> 16 f16 = two 16-byte smem chunks
-      constexpr int CPR8 = D / 16;
-      for (int idx = tid; idx < BN * CPR8; idx += NWARPS * 32) {
-        const int r = idx / CPR8, c8 = idx % CPR8;
-        const int pos = n0 + r;
-        const bool ok = pos < kv_limit;
+      const char* ksrc = k_col + ((int64_t)page * kc_bs + (int64_t)slot * kc_ss);
+      const char* vsrc = v_col + ((int64_t)page * vc_bs + (int64_t)slot * vc_ss);
+      if constexpr (!KV_FP8) {
+        const uint32_t off = swz_off<ROWB>(r, ld_c);
+        cp_async_16(smem_u32(dK + off), ksrc, ok);
+        cp_async_16(smem_u32(dV + off), vsrc, ok);
+      } else {
+        // 16 fp8 -> 16 f16 = two 16-byte smem chunks
         int4 kraw = make_int4(0, 0, 0, 0), vraw = kraw;
         if (ok) {
-          const int64_t page = bt[pos / p.block_size];
-          const int slot = pos % p.block_size;
-          kraw = *reinterpret_cast<const int4*>(static_cast<const char*>(p.k_cache) + page * p.kc_block_stride +
-                                                (int64_t)slot * p.kc_slot_stride + (int64_t)kvh * p.kc_head_stride + c8 * 16);
-          vraw = *reinterpret_cast<const int4*>(static_cast<const char*>(p.v_cache) + page * p.vc_block_stride +
-                                                (int64_t)slot * p.vc_slot_stride + (int64_t)kvh * p.vc_head_stride + c8 * 16);
+          kraw = *reinterpret_cast<const int4*>(ksrc);
+          vraw = *reinterpret_cast<const int4*>(vsrc);
         }
         const uint32_t* kw = reinterpret_cast<const uint32_t*>(&kraw);
         const uint32_t* vw = reinterpret_cast<const uint32_t*>(&vraw);
@@ -157,8 +166,8 @@ attn_prefill_kernel(const b200attn_attention_params p, const int block_q, const 
           ko.z = e4m3x2_to_f16x2((uint16_t)(kw[2 * h + 1] & 0xffff)), ko.w = e4m3x2_to_f16x2((uint16_t)(kw[2 * h + 1] >> 16));
           vo.x = e4m3x2_to_f16x2((uint16_t)(vw[2 * h] & 0xffff)), vo.y = e4m3x2_to_f16x2((uint16_t)(vw[2 * h] >> 16));
           vo.z = e4m3x2_to_f16x2((uint16_t)(vw[2 * h + 1] & 0xffff)), vo.w = e4m3x2_to_f16x2((uint16_t)(vw[2 * h + 1] >> 16));
-          *reinterpret_cast<int4*>(dK + swz_off<ROWB>(r, 2 * c8 + h)) = ko;
-          *reinterpret_cast<int4*>(dV + swz_off<ROWB>(r, 2 * c8 + h)) = vo;
+          *reinterpret_cast<int4*>(dK + swz_off<ROWB>(r, 2 * ld_c + h)) = ko;
+          *reinterpret_cast<int4*>(dV + swz_off<ROWB>(r, 2 * ld_c + h)) = vo;
         }
       }
     }
@@ -237,23 +246,42 @@ attn_prefill_kernel(const b200attn_attention_params p, const int block_q, const 
                         (p.sliding_window <= 0 || (ctx + wq_max - n0) < p.sliding_window) && (warp * 16 + 16 <= rows_used) &&
                         (qpos0 + (warp * 16 + 15) / group < q_len);
       float mx[2] = {-INFINITY, -INFINITY};
+      if constexpr (kPlain) {
+        // max over the raw dot products (scale > 0), masking only on boundary tiles
 #pragma unroll
-      for (int nt = 0; nt < BN / 8; ++nt) {
+        for (int nt = 0; nt < BN / 8; ++nt) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int ri = i >> 1;
-          const int pos = n0 + nt * 8 + 2 * t4 + (i & 1);
-          float x = sacc[nt][i] * qk_scale;
-          if (has_cap) x = softcap_fn(x, p.softcap, inv_cap);
-          if (!full) {
-            bool vis = row_ok[ri] && pos < ctx + row_qpos[ri] + 1 && pos < seq_len;
-            if (p.sliding_window > 0) vis = vis && (ctx + row_qpos[ri] - pos) < p.sliding_window;
-            if (!vis) x = -INFINITY;
+          for (int i = 0; i < 4; ++i) {
+            const int ri = i >> 1;
+            if (!full) {
+              const int pos = n0 + nt * 8 + 2 * t4 + (i & 1);
+              bool vis = row_ok[ri] && pos < ctx + row_qpos[ri] + 1 && pos < seq_len;
+              if (p.sliding_window > 0) vis = vis && (ctx + row_qpos[ri] - pos) < p.sliding_window;
+              if (!vis) sacc[nt][i] = -INFINITY;
+            }
+            mx[ri] = fmaxf(mx[ri], sacc[nt][i]);
           }
-          if (p.alibi_slopes) x += row_slope[ri] * (float)(pos - ctx);
-          x *= kLog2e;
-          sacc[nt][i] = x;
-          mx[ri] = fmaxf(mx[ri], x);
+        }
+        mx[0] *= scale_log2, mx[1] *= scale_log2;
+      } else {
+#pragma unroll
+        for (int nt = 0; nt < BN / 8; ++nt) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int ri = i >> 1;
+            const int pos = n0 + nt * 8 + 2 * t4 + (i & 1);
+            float x = sacc[nt][i] * qk_scale;
+            if (has_cap) x = softcap_fn(x, p.softcap, inv_cap);
+            if (!full) {
+              bool vis = row_ok[ri] && pos < ctx + row_qpos[ri] + 1 && pos < seq_len;
+              if (p.sliding_window > 0) vis = vis && (ctx + row_qpos[ri] - pos) < p.sliding_window;
+              if (!vis) x = -INFINITY;
+            }
+            if (p.alibi_slopes) x += row_slope[ri] * (float)(pos - ctx);
+            x *= kLog2e;
+            sacc[nt][i] = x;
+            mx[ri] = fmaxf(mx[ri], x);
+          }
         }
       }
       float alpha[2], mu[2];
@@ -270,8 +298,14 @@ attn_prefill_kernel(const b200attn_attention_params p, const int block_q, const 
       uint32_t pa[BN / 16][4];
 #pragma unroll
       for (int nt = 0; nt < BN / 8; ++nt) {
-        const float p0 = ex2f(sacc[nt][0] - mu[0]), p1 = ex2f(sacc[nt][1] - mu[0]);
-        const float p2 = ex2f(sacc[nt][2] - mu[1]), p3 = ex2f(sacc[nt][3] - mu[1]);
+        float p0, p1, p2, p3;
+        if constexpr (kPlain) {  // exp2(s * scale_log2 - m): the scale rides in the FFMA
+          p0 = ex2f(fmaf(sacc[nt][0], scale_log2, -mu[0])), p1 = ex2f(fmaf(sacc[nt][1], scale_log2, -mu[0]));
+          p2 = ex2f(fmaf(sacc[nt][2], scale_log2, -mu[1])), p3 = ex2f(fmaf(sacc[nt][3], scale_log2, -mu[1]));
+        } else {
+          p0 = ex2f(sacc[nt][0] - mu[0]), p1 = ex2f(sacc[nt][1] - mu[0]);
+          p2 = ex2f(sacc[nt][2] - mu[1]), p3 = ex2f(sacc[nt][3] - mu[1]);
+        }
         ls[0] += p0 + p1, ls[1] += p2 + p3;
         // C fragments of n-tiles (2j, 2j+1) are the A fragment of k16 step j
         pa[nt >> 1][(nt & 1) * 2 + 0] = pack2<MMA_BF16>(p0, p1);
@@ -279,10 +313,13 @@ attn_prefill_kernel(const b200attn_attention_params p, const int block_q, const 
       }
       l_run[0] = l_run[0] * alpha[0] + ls[0];
       l_run[1] = l_run[1] * alpha[1] + ls[1];
+      // the running output only needs rescaling when some row of the warp saw a new maximum
+      if (__any_sync(0xffffffffu, alpha[0] != 1.f || alpha[1] != 1.f)) {
 #pragma unroll
-      for (int dt = 0; dt < DT; ++dt) {
-        oacc[dt][0] *= alpha[0], oacc[dt][1] *= alpha[0];
-        oacc[dt][2] *= alpha[1], oacc[dt][3] *= alpha[1];
+        for (int dt = 0; dt < DT; ++dt) {
+          oacc[dt][0] *= alpha[0], oacc[dt][1] *= alpha[0];
+          oacc[dt][2] *= alpha[1], oacc[dt][3] *= alpha[1];
+        }
       }
       // ---- O += P V ----------------------------------------------------------------
 #pragma unroll
@@ -333,12 +370,15 @@ attn_prefill_kernel(const b200attn_attention_params p, const int block_q, const 
   }
 }
 
-template <int D, bool MMA_BF16, bool Q_BF16, bool KV_FP8>
+template <int D, bool MMA_BF16, bool Q_BF16, bool KV_FP8, bool kPlain>
 int launch_variant(const b200attn_attention_params& a, cudaStream_t stream, QLenRange range, const int32_t* skip_staged) {
   const int group = a.num_q_heads / a.num_kv_heads;
   const int block_q = BM / group;
   const int smem = BM * D * 2 + 4 * BN * D * 2;
-  auto kern = attn_prefill_kernel<D, MMA_BF16, Q_BF16, KV_FP8>;
+  auto kern = attn_prefill_kernel<D, MMA_BF16, Q_BF16, KV_FP8, kPlain>;
+  int bs_shift = -1;
+  if ((a.block_size & (a.block_size - 1)) == 0)
+    for (bs_shift = 0; (1 << bs_shift) < a.block_size; ++bs_shift) {}
   static thread_local bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
@@ -356,17 +396,19 @@ int launch_variant(const b200attn_attention_params& a, cudaStream_t stream, QLen
   const long long per_seq = ((long long)longest + block_q - 1) / block_q;
   if (per_seq >= 1 && per_seq * a.num_seqs < nblocks) qb_per_seq = (int)per_seq, nblocks = per_seq * a.num_seqs;
   const dim3 grid((unsigned)nblocks, (unsigned)a.num_kv_heads);
-  kern<<<grid, NWARPS * 32, smem, stream>>>(a, block_q, group, range.min_q_len, range.max_q_len, qb_per_seq, skip_staged);
+  kern<<<grid, NWARPS * 32, smem, stream>>>(a, block_q, group, range.min_q_len, range.max_q_len, qb_per_seq, skip_staged, bs_shift);
   note_launch("attn_prefill_mma");
   return check_launch("attn_prefill");
 }
 
-template <int D>
+template <int D, bool kPlain>
 int dispatch_types(const b200attn_attention_params& a, cudaStream_t stream, QLenRange range, const int32_t* skip) {
   const bool qbf = a.q_dtype == B200ATTN_BF16;
   if (a.kv_dtype == B200ATTN_FP8_E4M3)
-    return qbf ? launch_variant<D, false, true, true>(a, stream, range, skip) : launch_variant<D, false, false, true>(a, stream, range, skip);
-  return qbf ? launch_variant<D, true, true, false>(a, stream, range, skip) : launch_variant<D, false, false, false>(a, stream, range, skip);
+    return qbf ? launch_variant<D, false, true, true, kPlain>(a, stream, range, skip)
+               : launch_variant<D, false, false, true, kPlain>(a, stream, range, skip);
+  return qbf ? launch_variant<D, true, true, false, kPlain>(a, stream, range, skip)
+             : launch_variant<D, false, false, false, kPlain>(a, stream, range, skip);
 }
 
 }  // namespace
@@ -383,6 +425,9 @@ bool prefill_supported(const b200attn_attention_params& p, const char** why) {
   if (!m16(p.kc_block_stride) || !m16(p.kc_slot_stride) || !m16(p.kc_head_stride) || !m16(p.vc_block_stride) ||
       !m16(p.vc_slot_stride) || !m16(p.vc_head_stride))
     return no("cache strides not 16-byte multiples");
+  auto fits = [&](int64_t s) { return s >= 0 && s * esz < (int64_t(1) << 31); };  // the loader multiplies in 32 x 32 -> 64 bits
+  if (!fits(p.kc_block_stride) || !fits(p.kc_slot_stride) || !fits(p.vc_block_stride) || !fits(p.vc_slot_stride))
+    return no("cache block/slot stride >= 2 GiB");
   if ((reinterpret_cast<uintptr_t>(p.k_cache) & 15) || (reinterpret_cast<uintptr_t>(p.v_cache) & 15)) return no("cache base alignment");
   if ((reinterpret_cast<uintptr_t>(p.q) & 15) || (p.q_stride0 % 8) || (p.q_stride1 % 8)) return no("query alignment");
   if ((reinterpret_cast<uintptr_t>(p.out) & 3) || (p.out_stride0 % 2) || (p.out_stride1 % 2)) return no("output alignment");
@@ -396,10 +441,12 @@ int launch_attn_prefill(const b200attn_attention_params& a, cudaStream_t stream,
     set_error("prefill: unsupported configuration (%s)", why);
     return B200ATTN_E_UNSUPPORTED;
   }
+  // the scale of an FP8 cache is a device scalar: it is taken as positive (a quantisation scale always is)
+  const bool plain = a.softcap == 0.f && !a.alibi_slopes && a.softmax_scale > 0.f;
   switch (a.head_size) {
-    case 64: return dispatch_types<64>(a, stream, range, skip_staged);
-    case 128: return dispatch_types<128>(a, stream, range, skip_staged);
-    case 256: return dispatch_types<256>(a, stream, range, skip_staged);
+    case 64: return plain ? dispatch_types<64, true>(a, stream, range, skip_staged) : dispatch_types<64, false>(a, stream, range, skip_staged);
+    case 128: return plain ? dispatch_types<128, true>(a, stream, range, skip_staged) : dispatch_types<128, false>(a, stream, range, skip_staged);
+    case 256: return plain ? dispatch_types<256, true>(a, stream, range, skip_staged) : dispatch_types<256, false>(a, stream, range, skip_staged);
   }
   return B200ATTN_E_UNSUPPORTED;
 }
