@@ -247,41 +247,63 @@ attn_prefill_kernel(const b200attn_attention_params p, const int block_q, const 
                         (qpos0 + (warp * 16 + 15) / group < q_len);
       float mx[2] = {-INFINITY, -INFINITY};
       if constexpr (kPlain) {
-        // max over the raw dot products (scale > 0), masking only on boundary tiles
+        // max over the raw dot products (scale > 0); only boundary tiles run the masking code
+        if (!full) {
+          // visible keys of row ri: [lo, hi)
+          int lo[2], hi[2];
+#pragma unroll
+          for (int ri = 0; ri < 2; ++ri) {
+            hi[ri] = row_ok[ri] ? min(ctx + row_qpos[ri] + 1, seq_len) : 0;
+            lo[ri] = p.sliding_window > 0 ? ctx + row_qpos[ri] - p.sliding_window + 1 : 0;
+          }
+#pragma unroll
+          for (int nt = 0; nt < BN / 8; ++nt) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const int ri = i >> 1;
+              const int pos = n0 + nt * 8 + 2 * t4 + (i & 1);
+              if (pos >= hi[ri] || pos < lo[ri]) sacc[nt][i] = -INFINITY;
+            }
+          }
+        }
 #pragma unroll
         for (int nt = 0; nt < BN / 8; ++nt) {
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const int ri = i >> 1;
-            if (!full) {
-              const int pos = n0 + nt * 8 + 2 * t4 + (i & 1);
-              bool vis = row_ok[ri] && pos < ctx + row_qpos[ri] + 1 && pos < seq_len;
-              if (p.sliding_window > 0) vis = vis && (ctx + row_qpos[ri] - pos) < p.sliding_window;
-              if (!vis) sacc[nt][i] = -INFINITY;
-            }
-            mx[ri] = fmaxf(mx[ri], sacc[nt][i]);
-          }
+          mx[0] = fmaxf(mx[0], fmaxf(sacc[nt][0], sacc[nt][1]));
+          mx[1] = fmaxf(mx[1], fmaxf(sacc[nt][2], sacc[nt][3]));
         }
         mx[0] *= scale_log2, mx[1] *= scale_log2;
       } else {
+        // general path: scale, softcap (before masking, reference :467-468), ALiBi, then the mask
+        const float cap_log2 = p.softcap * kLog2e, pre = qk_scale * inv_cap;
 #pragma unroll
         for (int nt = 0; nt < BN / 8; ++nt) {
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
-            const int ri = i >> 1;
-            const int pos = n0 + nt * 8 + 2 * t4 + (i & 1);
-            float x = sacc[nt][i] * qk_scale;
-            if (has_cap) x = softcap_fn(x, p.softcap, inv_cap);
-            if (!full) {
-              bool vis = row_ok[ri] && pos < ctx + row_qpos[ri] + 1 && pos < seq_len;
-              if (p.sliding_window > 0) vis = vis && (ctx + row_qpos[ri] - pos) < p.sliding_window;
-              if (!vis) x = -INFINITY;
-            }
-            if (p.alibi_slopes) x += row_slope[ri] * (float)(pos - ctx);
-            x *= kLog2e;
+            float x = has_cap ? cap_log2 * tanh_approx(sacc[nt][i] * pre) : sacc[nt][i] * scale_log2;
+            if (p.alibi_slopes) x = fmaf(row_slope[i >> 1] * kLog2e, (float)(n0 + nt * 8 + 2 * t4 + (i & 1) - ctx), x);
             sacc[nt][i] = x;
-            mx[ri] = fmaxf(mx[ri], x);
           }
+        }
+        if (!full) {
+          int lo[2], hi[2];
+#pragma unroll
+          for (int ri = 0; ri < 2; ++ri) {
+            hi[ri] = row_ok[ri] ? min(ctx + row_qpos[ri] + 1, seq_len) : 0;
+            lo[ri] = p.sliding_window > 0 ? ctx + row_qpos[ri] - p.sliding_window + 1 : 0;
+          }
+#pragma unroll
+          for (int nt = 0; nt < BN / 8; ++nt) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const int pos = n0 + nt * 8 + 2 * t4 + (i & 1);
+              if (pos >= hi[i >> 1] || pos < lo[i >> 1]) sacc[nt][i] = -INFINITY;
+            }
+          }
+        }
+#pragma unroll
+        for (int nt = 0; nt < BN / 8; ++nt) {
+          mx[0] = fmaxf(mx[0], fmaxf(sacc[nt][0], sacc[nt][1]));
+          mx[1] = fmaxf(mx[1], fmaxf(sacc[nt][2], sacc[nt][3]));
         }
       }
       float alpha[2], mu[2];

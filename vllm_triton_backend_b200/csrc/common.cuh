@@ -137,6 +137,13 @@ __device__ __forceinline__ float softcap_fn(float x, float cap, float inv_cap) {
   return cap * (1.0f - __fdividef(2.0f, e + 1.0f));
 }
 
+// one MUFU op (relative error 2^-11): the prefill kernels' softcap, cap * tanh_approx(x / cap)
+__device__ __forceinline__ float tanh_approx(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 // Attention sink (upstream `init_softmax_M`, vllm/v1/attention/ops/triton_attention_helpers.py):
 // one extra key per head with logit `sink` (natural units, not scaled) and a zero value row.
 // Applied once, after the last KV tile: `m` is the final running max (`m_is_log2`: in log2
