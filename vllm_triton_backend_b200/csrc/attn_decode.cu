@@ -722,8 +722,17 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
       // ---------------- finalise this (sequence, head group) ------------------
       const int item = cur.b * P.head_groups + cur.hg;
       const int item_flat0 = cur.flat - (cur.step - cur.first);
-      const bool direct = item_flat0 >= my_begin && item_flat0 + cur.n <= my_end;
+      const int hg_done = cur.hg, n_done = cur.n;
+      const bool direct = item_flat0 >= my_begin && item_flat0 + n_done <= my_end;
       const int tq = tq_cur;
+      // Move on to the next item first: its dependent global loads (seq_lens / cu_seqlens_q, then the query
+      // rows) are in flight while this item is merged and stored.  The query fragments are dead after the
+      // item's last tile; the accumulators are reset only after the merge has read them.
+      if (!last) {
+        cursor_next(P, cur);
+        tq_cur = P.a.cu_seqlens_q ? P.a.cu_seqlens_q[cur.b] : cur.b;
+        load_q(tq_cur);
+      }
       if (trace && threadIdx.x == 0) {
         if (last) trace[4] = clock64();
         trace[7] += 1;
@@ -773,7 +782,7 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
           }
           const int hq_in_cta = hl * P.group + nt * 8 + col;  // query head within the CTA's head group
           if (direct) {
-            const int hq = cur.hg * P.hpc * P.group + hq_in_cta;
+            const int hq = hg_done * P.hpc * P.group + hq_in_cta;
             if (P.a.sinks) val *= sink_rescale<true>(P.a.sinks[hq], M, L);
             const float o = (L > 0.f) ? val * v_scale / L : 0.f;
             const int64_t oel = (int64_t)tq * P.a.out_stride0 + (int64_t)hq * P.a.out_stride1;
@@ -795,7 +804,7 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
       if (!direct) {
         // ---- ticket: the CTA that completes the item merges its partials ------
         const int first_cta = item_flat0 / per_cta;
-        const int last_cta = (item_flat0 + cur.n - 1) / per_cta;
+        const int last_cta = (item_flat0 + n_done - 1) / per_cta;
         __threadfence();  // partials visible device-wide before the ticket
         asm volatile("bar.sync 1, %0;" ::"r"(NW * 32));
         if (threadIdx.x == 0) {
@@ -850,7 +859,7 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
                 L += ml.y * sc;
               }
             }
-            const int hq = cur.hg * rec_heads + hq_in;
+            const int hq = hg_done * rec_heads + hq_in;
             float fs = 1.f;
             if (P.a.sinks) fs = sink_rescale<true>(P.a.sinks[hq], M, L);  // once per item, here (upstream: segment 0 only)
             const float inv = (L > 0.f) ? fs * v_scale / L : 0.f;  // 0 when nothing is visible (reference :828)
@@ -873,10 +882,7 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
       }
       if (last) break;
       asm volatile("bar.sync 1, %0;" ::"r"(NW * 32));  // merge buffers are reused by the next item
-      cursor_next(P, cur);
       reset_state();
-      tq_cur = P.a.cu_seqlens_q ? P.a.cu_seqlens_q[cur.b] : cur.b;
-      load_q(tq_cur);
     } else {
       cursor_next(P, cur);
     }
