@@ -276,21 +276,25 @@ def test_prefill_tc_sliding_window(window):
     assert_close(out, _oracle(inp, scale, window), atol=BF16_ATOL, rtol=BF16_RTOL, what=f"window {window}")
 
 
-@pytest.mark.parametrize("softcap,sinks,window", [(30.0, False, 0), (50.0, False, 128), (0.0, True, 0), (20.0, True, 300)])
+@pytest.mark.parametrize("softcap,sinks,window,alibi", [
+    (30.0, False, 0, False), (50.0, False, 128, False), (0.0, True, 0, False), (20.0, True, 300, False),
+    (0.0, False, 0, True), (30.0, False, 200, True),
+])
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
-def test_prefill_tc_softcap_and_sinks(softcap, sinks, window, dtype):
-    """Softcap (tanh of S before masking, cap as the softmax scale) and attention sinks (epilogue only)
-    inside the tcgen05 kernel; large logits so that the cap actually bends them."""
+def test_prefill_tc_softcap_alibi_and_sinks(softcap, sinks, window, alibi, dtype):
+    """Softcap (tanh of S before masking), ALiBi (slope * (key position - context length)) and attention
+    sinks (epilogue only) inside the tcgen05 kernel; large logits so that the cap actually bends them."""
     lens = [(1, 1328), (129, 463), (300, 300), (700, 1500), (5, 40)]
     Hq = 8
     inp = make_paged_inputs(lens, Hq, 2, 128, 16, dtype=dtype, seed=37)
     inp["q"] = inp["q"] * 3
     sink_t = torch.linspace(-2.0, 6.0, Hq, dtype=torch.float32) if sinks else None
+    slopes = torch.tensor([2.0 ** (-(i + 1) * 8.0 / Hq) for i in range(Hq)], dtype=torch.float32) if alibi else None
     scale = 0.4
-    out, kern = _run(inp, scale, PREFILL_TC, window=window, softcap=softcap, sinks=sink_t)
+    out, kern = _run(inp, scale, PREFILL_TC, window=window, softcap=softcap, sinks=sink_t, alibi=slopes)
     assert kern == "attn_prefill_tc"
-    ref = _oracle(inp, scale, window=window, softcap=softcap, sinks=sink_t)
-    assert_close(out, ref, atol=BF16_ATOL, rtol=BF16_RTOL, what=f"prefill_tc softcap={softcap} sinks={sinks}")
+    ref = _oracle(inp, scale, window=window, softcap=softcap, sinks=sink_t, alibi=slopes)
+    assert_close(out, ref, atol=BF16_ATOL, rtol=BF16_RTOL, what=f"prefill_tc softcap={softcap} sinks={sinks} alibi={alibi}")
 
 
 def test_prefill_tc_large_logits_exercise_the_lazy_rescale():

@@ -281,9 +281,11 @@ constexpr int kSmemBytes = kSmemClc + 64 + 1024;     // + alignment slack
 constexpr int kConsumerWarps = 11;                   // warps 0..10 read every item
 
 // kEmuNum of every kEmuDen exponential pairs are computed by ex2_poly2, the rest on the MUFU.
-// kSoftcap: logits are cap * tanh(s * scale / cap) (reference apply_softcap, triton_unified_attention.py:24-29,
-// 467-468): S is replaced by tanh(S * scale / cap) right after it leaves TMEM (one MUFU op per element, before
-// masking, as the reference caps before it masks) and `cap` takes the place of the softmax scale.
+// kSoftcap ("general logits" variant): softcap and / or ALiBi.  S is replaced, right after it leaves TMEM and
+// before masking (the reference caps before it masks, triton_unified_attention.py:24-29, 467-468), by the final
+// logit in log2 units: cap * tanh(S * scale / cap) (one MUFU op per element) or S * scale, plus
+// slope * (key position - context length) for ALiBi (:481-482); the max / exp2 code below then runs with a scale of 1
+// (softcap alone: tanh() stays in S and `cap` is the scale).
 template <bool kBf16, int kEmuNum, int kEmuDen, bool kSoftcap = false>
 __global__ void __launch_bounds__(kThreads, 1)
 attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CUtensorMap k_map,
@@ -344,7 +346,9 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
   // ---- state shared by the roles that consume the work queue -------------------------------
   uint32_t n_items = 0;   // items taken so far (mailbox slot / phase)
   uint32_t t_run = 0;     // KV tiles processed so far: parity source of the per-tile barriers
-  const float scale_log2 = (kSoftcap ? a.softcap : a.softmax_scale) * kLog2e;
+  // softcap without ALiBi keeps tanh() in S and lets `cap` ride in the exp2 FFMA (one multiply per logit less)
+  const bool cap_folded = kSoftcap && a.softcap > 0.f && !a.alibi_slopes;
+  const float scale_log2 = !kSoftcap ? a.softmax_scale * kLog2e : (cap_folded ? a.softcap * kLog2e : 1.0f);
   int k_st = 0, v_st = 0;           // ring positions (TMA warps: next to fill; MMA warp: next to use)
   uint32_t k_ph = 0, v_ph = 0;
   uint32_t n_fix = 0;               // V tail fix-ups so far (V_FIX parity)
@@ -403,14 +407,37 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
         for (int c = 0; c < 4; ++c) tmem_ld32(s_tmem + c * 32, s[c]);
         tmem_ld_wait();
         if (row == 0) TC_TRACE(t_run + j, w * 5 + 1);
-        if constexpr (kSoftcap) {
-          const float pre = a.softmax_scale / a.softcap;
-#pragma unroll
-          for (int c = 0; c < 4; ++c)
-#pragma unroll
-            for (int i = 0; i < 32; ++i) s[c][i] = __float_as_uint(tanh_approx(__uint_as_float(s[c][i]) * pre));
-        }
         const int n0 = (tile0 + j) * kBN;
+        if constexpr (kSoftcap) {
+          if (a.softcap > 0.f) {
+            const float pre = a.softmax_scale / a.softcap, cap_log2 = cap_folded ? 1.0f : a.softcap * kLog2e;
+            if (cap_folded) {
+#pragma unroll
+              for (int c = 0; c < 4; ++c)
+#pragma unroll
+                for (int i = 0; i < 32; ++i) s[c][i] = __float_as_uint(tanh_approx(__uint_as_float(s[c][i]) * pre));
+            } else {
+#pragma unroll
+              for (int c = 0; c < 4; ++c)
+#pragma unroll
+                for (int i = 0; i < 32; ++i) s[c][i] = __float_as_uint(cap_log2 * tanh_approx(__uint_as_float(s[c][i]) * pre));
+            }
+          } else {
+            const float sl2 = a.softmax_scale * kLog2e;
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+#pragma unroll
+              for (int i = 0; i < 32; ++i) s[c][i] = __float_as_uint(__uint_as_float(s[c][i]) * sl2);
+          }
+          if (a.alibi_slopes) {
+            const float slope = a.alibi_slopes[kvh * g + head] * kLog2e;
+            const float b0 = slope * (float)(n0 - it.ctx);
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+#pragma unroll
+              for (int i = 0; i < 32; ++i) s[c][i] = __float_as_uint(fmaf(slope, (float)(c * 32 + i), __uint_as_float(s[c][i]) + b0));
+          }
+        }
         if (n0 + kBN > limit || n0 < lo) {
 #pragma unroll
           for (int c = 0; c < 4; ++c)
@@ -830,7 +857,6 @@ bool prefill_tc_supported(const b200attn_attention_params& p, const char** why) 
   const int g = p.num_q_heads / p.num_kv_heads;
   if (!pow2(g) || g > 128) return no("GQA group not a power of two <= 128");
   if (!pow2(p.block_size) || p.block_size < 16) return no("block_size not a power of two >= 16");
-  if (p.alibi_slopes) return no("ALiBi");
   if (p.softcap < 0.f) return no("softcap < 0");
   if (!(p.softmax_scale > 0.f)) return no("softmax_scale <= 0");
   auto m8 = [&](int64_t s) { return s % 8 == 0; };
@@ -879,7 +905,7 @@ int launch_attn_prefill_tc(const b200attn_attention_params& a, cudaStream_t stre
 #undef TCV
   int variant = (tuning().reserved >> 4) & 15;
   if (variant >= kSoftcapVariant) variant = 0;
-  if (a.softcap > 0.f) variant = (((tuning().reserved >> 4) & 15) == 6) ? 6 : kSoftcapVariant;
+  if (a.softcap > 0.f || a.alibi_slopes) variant = (((tuning().reserved >> 4) & 15) == 6) ? 6 : kSoftcapVariant;
   Kern kern = kVariants[bf16 ? 1 : 0][variant];
   static thread_local bool attr_set[2][kNumVariants] = {};
   if (!attr_set[bf16 ? 1 : 0][variant]) {
