@@ -173,6 +173,18 @@ def make_device_workload(w, hq, hkv, device, seed):
 
 
 
+def _mixed_bounds(m, peaks):
+    """A mixed batch has a tensor-bound share (the prompts' FLOPs) and an HBM-bound share (the KV the
+    single-token rows stream).  Lower bounds on its time from the two measured peaks: the larger of the two
+    if they overlapped perfectly, their sum when they run one after the other (as here: the tcgen05
+    kernel fills every SM's shared memory, so the decode rows follow it)."""
+    t_flop = m["flops"] / (peaks["bf16_tflops"] * 1e12) * 1e3
+    t_byte = m["decode_row_kv_bytes"] / (peaks["hbm_gbs"] * 1e9) * 1e3
+    return {"decode_rows": m["decode_rows"], "decode_row_kv_gb": round(m["decode_row_kv_bytes"] / 1e9, 4),
+            "bound_ms_overlapped": round(max(t_flop, t_byte), 4), "bound_ms_serial": round(t_flop + t_byte, 4),
+            "frac_of_serial_bound": round((t_flop + t_byte) / m["ms"], 4)}
+
+
 def measure_prefill(device, world):
     """Tensor-bound half of the metric: prefill attention TFLOP/s on one full 8k causal
     prompt and on the C3 chunked-prefill mixed batch (Llama-3.1-8B shape), through
@@ -187,7 +199,8 @@ def measure_prefill(device, world):
         a = types.SimpleNamespace(shape=shape, hq=0, hkv=0, bs=0, fp8=False, layout="planes", force=None)
         fn, flops, cfg = kbench.prefill_case(a, device)
         ms, n = kbench.time_fn(fn, min_ms=50.0)
-        out[shape] = dict(ms=ms, tflops=flops / ms / 1e9, tokens=cfg["T"], iters=n)
+        out[shape] = dict(ms=ms, tflops=flops / ms / 1e9, tokens=cfg["T"], iters=n, flops=flops,
+                          decode_rows=cfg["decode_rows"], decode_row_kv_bytes=cfg["decode_row_kv_bytes"])
         del fn
         torch.cuda.empty_cache()
     return out
@@ -386,7 +399,8 @@ def run_ours(args):
                                    "tokens_per_s": round(world * pre["full8k"]["tokens"] / pre["full8k"]["ms"] * 1e3, 1)},
                 "c3_chunked_prefill_mixed": {"tflops_per_gpu": round(pre["mixed"]["tflops"], 1), "ms": round(pre["mixed"]["ms"], 4),
                                              "frac": round(pre["mixed"]["tflops"] / peaks["bf16_tflops"], 4),
-                                             "tokens_per_s": round(world * pre["mixed"]["tokens"] / pre["mixed"]["ms"] * 1e3, 1)},
+                                             "tokens_per_s": round(world * pre["mixed"]["tokens"] / pre["mixed"]["ms"] * 1e3, 1),
+                                             **_mixed_bounds(pre["mixed"], peaks)},
                 "kernel": "attn_prefill_tc_kernel (tcgen05/TMEM) + short/decode rows via attn_prefill_kernel / attn_decode_kernel",
             }
         if cpu_baseline is not None:

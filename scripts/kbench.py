@@ -297,8 +297,10 @@ def prefill_case(args, device):
 
         def fn():  # noqa: F811
             tri(q, kc, vc, out, cu, max(q_lens), sl, max(kv_lens), D ** -0.5, bt, k_scale=sc, v_scale=sc, softcap=softcap)
+    # bytes of the KV the single-token (decode) rows stream: the HBM-bound share of a mixed batch
+    dec_bytes = sum(kv for ql, kv in lens if ql == 1) * hkv * D * 2 * (1 if args.fp8 else 2)
     return fn, flops, dict(shape=args.shape, T=T, seqs=len(lens), hq=hq, hkv=hkv, D=D, bs=bs, fp8=bool(args.fp8),
-                           softcap=softcap)
+                           softcap=softcap, decode_rows=sum(1 for ql, _ in lens if ql == 1), decode_row_kv_bytes=dec_bytes)
 
 
 def run_prefill(args, device):

@@ -72,6 +72,9 @@ def test_bench_helpers_and_kbench_namespace_contract():
     bench = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(bench)
     assert bench._percentiles([5, 1, 3, 2, 4], (0, 50, 100)) == [1, 3, 5]
+    # mixed batch: 1e12 FLOP at 1000 TFLOP/s = 1 ms, 1e9 B at 1000 GB/s = 1 ms; measured 4 ms
+    mb = bench._mixed_bounds(dict(flops=1e12, decode_row_kv_bytes=1e9, ms=4.0, decode_rows=3), dict(bf16_tflops=1000.0, hbm_gbs=1000.0))
+    assert mb["bound_ms_overlapped"] == 1.0 and mb["bound_ms_serial"] == 2.0 and mb["frac_of_serial_bound"] == 0.5
     t = bench.committed_ncu_traffic()
     assert t is None or 1.0e9 < t < 1.2e9  # C2 decode kernel: ~1.075 GB algorithmic
     src = open(os.path.join(root, "bench.py")).read()
