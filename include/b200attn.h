@@ -128,8 +128,11 @@ typedef struct b200attn_attention_params {
   int64_t kc_block_stride, kc_slot_stride, kc_head_stride;
   int64_t vc_block_stride, vc_slot_stride, vc_head_stride;
   void* workspace;             /* split-KV partials + ticket counters; caller-owned,
-                                  zero-filled ONCE when allocated (the kernels leave
-                                  the counters at zero after every call)           */
+                                  zero-filled ONCE when allocated.  The first 1 MiB
+                                  holds the counters (the kernels leave them at zero
+                                  after every call) whatever the shape of the call, so
+                                  one buffer serves batches of every size; everything
+                                  behind it is scratch that is rewritten before use. */
   uint64_t workspace_bytes;
   const float* out_scale;      /* NULL: `out` has q_dtype.  Else a device scalar ("output_scale" of
                                   AttentionImpl.forward when fused_output_quant_supported, vLLM 0.22

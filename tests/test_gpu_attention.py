@@ -359,6 +359,31 @@ def test_workspace_counters_are_left_clean():
                               q_descale=None, k_descale=None, v_descale=None, workspace=ws)
     torch.cuda.synchronize()
     assert int(ws[: 5 * 8 * 4].view(torch.int32).abs().sum()) == 0
+    assert int(ws[: 1 << 20].view(torch.int32).abs().sum()) == 0  # the whole counter region (include/b200attn.h)
+
+
+def test_one_workspace_serves_batches_of_changing_size():
+    """Continuous batching: the same workspace sees a small batch, then a larger one, then a small one again.
+    The ticket counters of the larger batch must not land where the smaller one left partial results
+    (they did once: the counter region was sized by the call's own batch)."""
+    from vllm_triton_backend_b200 import ops
+
+    Hq, Hkv, D, bs = 32, 8, 128, 16
+    big = ops.workspace_bytes(256, 256, Hq, Hkv, D)
+    ws = torch.zeros(big, dtype=torch.uint8, device="cuda")
+    scale = D ** -0.5
+    for step, B in enumerate([2, 96, 3, 256, 17]):
+        lens = [(1, 3000 + 37 * i if i % 3 == 0 else 40 + 11 * i) for i in range(B)]  # long (split over CTAs) and short
+        inp = make_paged_inputs(lens, Hq, Hkv, D, bs, dtype=torch.bfloat16, seed=50 + step)
+        out = torch.full_like(inp["q"], float("nan")).cuda()
+        ops.unified_attention(q=inp["q"].cuda(), k=inp["k_cache"].cuda(), v=inp["v_cache"].cuda(), out=out,
+                              cu_seqlens_q=inp["cu_seqlens_q"].cuda(), max_seqlen_q=1, seqused_k=inp["seq_lens"].cuda(),
+                              max_seqlen_k=max(b for _, b in lens), softmax_scale=scale, causal=True, window_size=(-1, -1),
+                              block_table=inp["block_table"].cuda(), softcap=0, q_descale=None, k_descale=None,
+                              v_descale=None, workspace=ws)
+        torch.cuda.synchronize()
+        assert_close(out.cpu(), _oracle(inp, scale), atol=BF16_ATOL, rtol=BF16_RTOL, what=f"step {step}, batch {B}")
+        assert int(ws[: 1 << 20].view(torch.int32).abs().sum()) == 0
 
 
 # ---------------------------------------------------------------------------------

@@ -40,7 +40,9 @@ struct DecodeParams {
   b200attn_attention_params a;
   int hpc;         // kv heads per CTA (divides num_kv_heads and NW)
   int head_groups; // num_kv_heads / hpc
-  int tps;         // tokens per stage-step = NW*TT/hpc (TT = tokens of a warp's tile)
+  int tps;         // tokens per stage-step = NW*TT/hpc (TT = tokens of a warp's tile); a power of two
+  int tps_shift;   // log2(tps)
+  int bs_shift;    // log2(block_size) (decode_supported() requires a power of two)
   int box_slots;   // min(block_size, tps)
   int boxes;       // tps / box_slots
   int stages;
@@ -82,8 +84,8 @@ __device__ __forceinline__ void seq_steps(const DecodeParams& P, int b, int& seq
   }
   int lo_tok = 0;
   if (P.a.sliding_window > 0) lo_tok = max(0, seq_len - P.a.sliding_window);
-  first = lo_tok / P.tps;
-  n = (seq_len + P.tps - 1) / P.tps - first;
+  first = lo_tok >> P.tps_shift;
+  n = ((seq_len + P.tps - 1) >> P.tps_shift) - first;
 }
 
 // advance to the next step in (b, hg, step) order; returns false past the end
@@ -175,8 +177,8 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
         if (sl > 0 && ql > 0 && !(P.only_q1 && ql != 1)) {
           int lo_tok = 0;
           if (P.a.sliding_window > 0) lo_tok = max(0, sl - P.a.sliding_window);
-          first_r[r] = lo_tok / P.tps;
-          n_r[r] = (sl + P.tps - 1) / P.tps - first_r[r];
+          first_r[r] = lo_tok >> P.tps_shift;
+          n_r[r] = ((sl + P.tps - 1) >> P.tps_shift) - first_r[r];
         }
         if (sl <= 0 && ql == 1 && b % gridDim.x == blockIdx.x) zero_rows |= 1u << r;
         total += n_r[r];
@@ -184,7 +186,10 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
     }
     total = __reduce_add_sync(0xffffffffu, total);
     const long long total_flat = (long long)total * P.head_groups;
-    const long long per = (total_flat + gridDim.x - 1) / gridDim.x;
+    // 64-bit division is a long dependent sequence; the totals fit 32 bits unless the batch holds > 2^31 steps
+    const bool small = total_flat < (1ll << 31);
+    const long long per = small ? (long long)(((unsigned)total_flat + gridDim.x - 1) / gridDim.x)
+                                : (total_flat + gridDim.x - 1) / gridDim.x;
     long long begin = per * blockIdx.x;
     long long end = begin + per;
     if (begin > total_flat) begin = total_flat;
@@ -212,9 +217,13 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
             fsl = __shfl_sync(0xffffffffu, sl_r[r], src);
             tq_first = __shfl_sync(0xffffffffu, tq_r[r], src);
             fb = r * 32 + src;
-            const long long rem = begin - lo_s;
-            fhg = (int)(rem / fn);
-            fstep = ffirst + (int)(rem % fn);
+            const long long rem = begin - lo_s;  // < fn * head_groups
+            if (small) {
+              const unsigned qd = (unsigned)rem / (unsigned)fn;
+              fhg = (int)qd, fstep = ffirst + (int)((unsigned)rem - qd * (unsigned)fn);
+            } else {
+              fhg = (int)(rem / fn), fstep = ffirst + (int)(rem % fn);
+            }
           }
           run += (long long)__shfl_sync(0xffffffffu, incl, 31) * P.head_groups;
         }
@@ -355,8 +364,8 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
       const int nbox = (ntok + P.box_slots - 1) / P.box_slots;
       const int head0 = cur.hg * P.hpc;
       const int32_t* bt = P.a.block_tables + (int64_t)cur.b * P.a.bt_stride0;
-      const int npages = (cur.seq_len + P.a.block_size - 1) / P.a.block_size;
-      const int p_first = tok0 / P.a.block_size;
+      const int npages = (cur.seq_len + P.a.block_size - 1) >> P.bs_shift;
+      const int p_first = tok0 >> P.bs_shift;
       const int base = p_first & ~127;
       if (cur.b != win_b || base != win_base) {
         if (cur.b == win_b && base == win_base + 128) {
@@ -383,16 +392,16 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
         // k_map's third coordinate selects K (0) or V (1); the box takes both
         const int i = lane;
         const int tok = tok0 + i * P.box_slots;
-        const int page = page_of(tok / P.a.block_size);
+        const int page = page_of(tok >> P.bs_shift);
         if (i < nbox)
-          tma_load_5d(kdst + (size_t)i * 2 * boxb, &k_map, &full_bar[stage], 0, tok % P.a.block_size, 0, head0, page, pol);
+          tma_load_5d(kdst + (size_t)i * 2 * boxb, &k_map, &full_bar[stage], 0, tok & (P.a.block_size - 1), 0, head0, page, pol);
       } else if (P.tma_split == 0) {
         // nbox <= 8: one lane per box
         const int i = lane;
         const int tok = tok0 + i * P.box_slots;
-        const int page = page_of(tok / P.a.block_size);  // lanes past nbox read a don't-care id
+        const int page = page_of(tok >> P.bs_shift);  // lanes past nbox read a don't-care id
         if (i < nbox) {
-          const int slot0 = tok % P.a.block_size;
+          const int slot0 = tok & (P.a.block_size - 1);
           tma_load_5d(kdst + (size_t)i * boxb, &k_map, &full_bar[stage], 0, slot0, 0, head0, page, pol);
           tma_load_5d(vdst + (size_t)i * boxb, &v_map, &full_bar[stage], 0, slot0, 0, head0, page, pol);
         }
@@ -403,9 +412,9 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
           const int u = u0 + lane;
           const int i = min(u / per_box, nbox - 1), r = u % per_box, h = r / NDC, dc = r % NDC;
           const int tok = tok0 + i * P.box_slots;
-          const int page = page_of(tok / P.a.block_size);
+          const int page = page_of(tok >> P.bs_shift);
           if (u < units) {
-            const int slot0 = tok % P.a.block_size;
+            const int slot0 = tok & (P.a.block_size - 1);
             const size_t off = (size_t)i * boxb + (size_t)(h * NDC + dc) * P.box_slots * 128;
             tma_load_5d(kdst + off, &k_map, &full_bar[stage], 0, slot0, dc, head0 + h, page, pol);
             tma_load_5d(vdst + off, &v_map, &full_bar[stage], 0, slot0, dc, head0 + h, page, pol);
@@ -938,6 +947,12 @@ int launch_variant(const b200attn_attention_params& a, DecodeParams& P, cudaStre
   }
   P.head_groups = a.num_kv_heads / P.hpc;
   P.tps = NW * TT / P.hpc;
+  for (P.tps_shift = 0; (1 << P.tps_shift) < P.tps; ++P.tps_shift) {}
+  for (P.bs_shift = 0; (1 << P.bs_shift) < a.block_size; ++P.bs_shift) {}
+  if ((1 << P.tps_shift) != P.tps || (1 << P.bs_shift) != a.block_size) {
+    set_error("decode: tokens per step (%d) and block_size (%d) must be powers of two", P.tps, a.block_size);
+    return B200ATTN_E_UNSUPPORTED;
+  }
   P.box_slots = a.block_size < P.tps ? a.block_size : P.tps;
   P.boxes = P.tps / P.box_slots;
   P.tma_split = tn.reserved & 1;
@@ -1016,14 +1031,18 @@ inline bool pow2(int x) { return x > 0 && (x & (x - 1)) == 0; }
 
 }  // namespace
 
+// The ticket counters live in a region of FIXED size at the start of the workspace: they are the only bytes
+// that must be zero between calls, and the same buffer serves calls of every shape (a batch grows and shrinks
+// from step to step), so their region may never be another shape's partial-result region.
+constexpr uint64_t kCounterBytes = 1ull << 20;  // one int per (sequence, head group): 262144 items
+
 uint64_t decode_workspace_bytes(int num_seqs, int num_q_heads, int num_kv_heads, int head_size) {
   // slots <= items + ctas; records of (hpc*group) heads: bounded by
-  // (B*Hq + ctas*8*group) head-rows of (D + 2) floats, plus one ticket counter per item.
+  // (B*Hq + ctas*8*group) head-rows of (D + 2) floats, after the counter region.
   const uint64_t group = (uint64_t)(num_q_heads / (num_kv_heads > 0 ? num_kv_heads : 1));
   const uint64_t ctas = 160;  // >= SM count of any B200 SKU
   const uint64_t rows = (uint64_t)num_seqs * num_q_heads + ctas * 8 * (group > 0 ? group : 1);
-  const uint64_t items = (uint64_t)num_seqs * num_kv_heads;
-  return rows * (uint64_t)(head_size + 2) * 4 + items * 8 + 1024;
+  return kCounterBytes + rows * (uint64_t)(head_size + 2) * 4 + 1024;
 }
 
 bool decode_supported(const b200attn_attention_params& p, const char** why, bool mixed_batch) {
@@ -1064,11 +1083,16 @@ int launch_attn_decode(const b200attn_attention_params& a, cudaStream_t stream, 
   P.group = a.num_q_heads / a.num_kv_heads;
   P.only_q1 = only_single_token_seqs ? 1 : 0;
   P.trace = decode_trace_buffer();
-  // carve the workspace: ticket counters first (items <= B*Hkv; zero between calls), then ml, then acc
+  // carve the workspace: ticket counters first (fixed region, zero between calls), then ml, then acc
   const uint64_t items_max = (uint64_t)a.num_seqs * a.num_kv_heads;
+  if (items_max * sizeof(int) > kCounterBytes) {
+    set_error("decode: %llu (sequence, kv head) items exceed the %llu ticket counters of the workspace",
+              (unsigned long long)items_max, (unsigned long long)(kCounterBytes / sizeof(int)));
+    return B200ATTN_E_WORKSPACE;
+  }
   char* w = static_cast<char*>(a.workspace);
   P.ws_cnt = reinterpret_cast<int*>(w);
-  uint64_t off = ((items_max * 8 + 255) / 256) * 256;
+  uint64_t off = kCounterBytes;
   const uint64_t group = (uint64_t)P.group;
   const uint64_t rows = (uint64_t)a.num_seqs * a.num_q_heads + 160ull * 8 * group;
   P.ws_ml = reinterpret_cast<float*>(w + off);

@@ -83,7 +83,7 @@ def get_workspace(device, nbytes: int) -> torch.Tensor:
     if ws is None or ws.numel() < nbytes:
         if torch.cuda.is_current_stream_capturing():
             raise RuntimeError("b200attn workspace must be allocated before CUDA-graph capture (pass workspace=...)")
-        ws = torch.zeros(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+        ws = torch.zeros(max(nbytes, 4 << 20), dtype=torch.uint8, device=device)
         _workspaces[key] = ws
     return ws
 
