@@ -132,7 +132,8 @@ typedef struct b200attn_attention_params {
                                   holds the counters (the kernels leave them at zero
                                   after every call) whatever the shape of the call, so
                                   one buffer serves batches of every size; everything
-                                  behind it is scratch that is rewritten before use. */
+                                  behind it is scratch that is rewritten before use.
+                                  One workspace per stream with calls in flight.    */
   uint64_t workspace_bytes;
   const float* out_scale;      /* NULL: `out` has q_dtype.  Else a device scalar ("output_scale" of
                                   AttentionImpl.forward when fused_output_quant_supported, vLLM 0.22

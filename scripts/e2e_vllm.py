@@ -81,7 +81,7 @@ def run(args) -> dict:
     model_dir = write_model_dir(args.layers)
     kw = dict(model=model_dir, skip_tokenizer_init=True, load_format="dummy", dtype="bfloat16", seed=0,
               max_model_len=args.max_model_len, gpu_memory_utilization=args.gpu_mem, enable_prefix_caching=args.prefix_caching,
-              max_num_seqs=args.num_prompts, max_num_batched_tokens=args.max_batched_tokens, enforce_eager=args.eager,
+              max_num_seqs=args.max_num_seqs or args.num_prompts, max_num_batched_tokens=args.max_batched_tokens, enforce_eager=args.eager,
               kv_cache_dtype=args.kv_cache_dtype, generation_config="vllm")
     if backend is not None:
         kw["attention_backend"] = backend
@@ -95,6 +95,12 @@ def run(args) -> dict:
     prompts = [{"prompt_token_ids": shared + [rnd.randrange(10, vocab) for _ in range(args.input_len - len(shared))]}
                for _ in range(args.num_prompts)]
     sp = SamplingParams(max_tokens=args.output_len, ignore_eos=True, temperature=0.0, detokenize=False)
+    if args.ragged:
+        # continuous batching: prompts and generations of different lengths, more requests than batch slots, so
+        # the decode batch grows and shrinks from step to step and prefill chunks share steps with decode rows
+        prompts = [{"prompt_token_ids": p["prompt_token_ids"][: rnd.randint(32, args.input_len)]} for p in prompts]
+        sp = [SamplingParams(max_tokens=rnd.randint(8, args.output_len), ignore_eos=True, temperature=0.0, detokenize=False)
+              for _ in prompts]
     # warm-up on the full batch (same prefill/decode batch shapes as the timed run), so that JIT
     # compilation and autotuning of either backend stay out of the timed region
     warm = SamplingParams(max_tokens=16, ignore_eos=True, temperature=0.0, detokenize=False)
@@ -183,6 +189,8 @@ def main():
     ap.add_argument("--kv-cache-dtype", default="auto")
     ap.add_argument("--prefix-caching", action="store_true")
     ap.add_argument("--eager", action="store_true")
+    ap.add_argument("--ragged", action="store_true", help="random prompt / generation lengths (batch size changes every few steps)")
+    ap.add_argument("--max-num-seqs", type=int, default=0, help="batch slots (default: --num-prompts)")
     ap.add_argument("--mp", action="store_true", help="engine core in a subprocess (vLLM default); plugin via entry point")
     ap.add_argument("--repeats", type=int, default=3, help="timed generate() calls; the median is reported")
     ap.add_argument("--save", default=None)
