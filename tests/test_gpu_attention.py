@@ -362,6 +362,31 @@ def test_workspace_counters_are_left_clean():
     assert int(ws[: 1 << 20].view(torch.int32).abs().sum()) == 0  # the whole counter region (include/b200attn.h)
 
 
+@pytest.mark.parametrize("B,fp8,mixed", [(257, False, False), (300, True, False), (1000, False, False), (300, False, True)])
+def test_more_than_256_sequences_take_the_shared_memory_partition(B, fp8, mixed):
+    """Up to 256 sequences every warp derives the work partition in registers; beyond that warp 0 does and
+    hands it over through shared memory.  Ragged lengths, empty sequences, and (mixed) prompts in between."""
+    import random
+
+    r = random.Random(B)
+    lens = [(1, r.choice([0, 1, 16, 17, r.randint(1, 900), r.randint(1, 3000)])) for _ in range(B)]
+    if mixed:
+        for i in range(0, B, 37):
+            q = r.randint(2, 200)
+            lens[i] = (q, q + r.randint(0, 500))
+    alloc = [(a, max(b, 1)) for a, b in lens]
+    ks, vs = (0.37, 0.61) if fp8 else (1.0, 1.0)
+    inp = make_paged_inputs(alloc, 16, 4, 128, 16, dtype=torch.bfloat16, seed=B, kv_dtype=torch.float8_e4m3fn if fp8 else None,
+                            k_scale=ks, v_scale=vs)
+    inp["seq_lens"] = torch.tensor([b for _, b in lens], dtype=torch.int32)
+    scale = 128 ** -0.5
+    out, kern = _run(inp, scale, DECODE_OR_AUTO, k_scale=ks, v_scale=vs)
+    assert kern.startswith("attn_decode_split_kv")
+    assert not torch.isnan(out).any()
+    assert_close(out, _oracle(inp, scale, k_scale=ks, v_scale=vs), atol=FP8_ATOL if fp8 else BF16_ATOL, rtol=BF16_RTOL,
+                 what=f"{B} sequences")
+
+
 def test_one_workspace_serves_batches_of_changing_size():
     """Continuous batching: the same workspace sees a small batch, then a larger one, then a small one again.
     The ticket counters of the larger batch must not land where the smaller one left partial results
