@@ -98,6 +98,8 @@ class B200AttentionMetadataBuilder(AttentionMetadataBuilder[B200AttentionMetadat
             return
         self._ws_seqs = max(num_seqs, 2 * self._ws_seqs)
         nbytes = ops.workspace_bytes(self._ws_seqs, self._ws_seqs, self.num_heads_q, self.num_heads_kv, self.headdim)
+        # captured CUDA graphs hold the old buffer's address: keep it alive
+        self._retired_workspaces = getattr(self, "_retired_workspaces", []) + [self.workspace]
         self.workspace = torch.zeros(nbytes + self._ws_extra, dtype=torch.uint8, device=self.workspace.device)
 
     def build_for_cudagraph_capture(self, common_attn_metadata: CommonAttentionMetadata) -> B200AttentionMetadata:
