@@ -30,6 +30,7 @@ _DTYPE = {
 }
 
 _workspaces: dict = {}
+_retired_workspaces: list = []
 _scalar_cache: dict = {}
 
 
@@ -83,6 +84,8 @@ def get_workspace(device, nbytes: int) -> torch.Tensor:
     if ws is None or ws.numel() < nbytes:
         if torch.cuda.is_current_stream_capturing():
             raise RuntimeError("b200attn workspace must be allocated before CUDA-graph capture (pass workspace=...)")
+        if ws is not None:
+            _retired_workspaces.append(ws)  # a CUDA graph captured earlier may still hold its address
         ws = torch.zeros(max(nbytes, 4 << 20), dtype=torch.uint8, device=device)
         _workspaces[key] = ws
     return ws
