@@ -281,12 +281,13 @@ constexpr int kSmemBytes = kSmemClc + 64 + 1024;     // + alignment slack
 constexpr int kConsumerWarps = 11;                   // warps 0..10 read every item
 
 // kEmuNum of every kEmuDen exponential pairs are computed by ex2_poly2, the rest on the MUFU.
-// kSoftcap ("general logits" variant): softcap and / or ALiBi.  S is replaced, right after it leaves TMEM and
-// before masking (the reference caps before it masks, triton_unified_attention.py:24-29, 467-468), by the final
-// logit in log2 units: cap * tanh(S * scale / cap) (one MUFU op per element) or S * scale, plus
-// slope * (key position - context length) for ALiBi (:481-482); the max / exp2 code below then runs with a scale of 1
-// (softcap alone: tanh() stays in S and `cap` is the scale).
-template <bool kBf16, int kEmuNum, int kEmuDen, bool kSoftcap = false>
+// kLogits selects how a logit is formed from the dot product S (always right after S leaves TMEM and before
+// masking: the reference caps before it masks, triton_unified_attention.py:24-29, 467-468):
+//   0  S * scale                                      (the scale rides in the exp2 FFMA)
+//   1  cap * tanh(S * scale / cap)                    (tanh() replaces S, one MUFU op; `cap` rides in the FFMA)
+//   2  either of the above + slope * (key position - context length) for ALiBi (:481-482), formed in place in
+//      log2 units; the max / exp2 code then runs with a scale of 1.
+template <bool kBf16, int kEmuNum, int kEmuDen, int kLogits = 0>
 __global__ void __launch_bounds__(kThreads, 1)
 attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CUtensorMap k_map,
                        const __grid_constant__ CUtensorMap v_map) {
@@ -346,9 +347,7 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
   // ---- state shared by the roles that consume the work queue -------------------------------
   uint32_t n_items = 0;   // items taken so far (mailbox slot / phase)
   uint32_t t_run = 0;     // KV tiles processed so far: parity source of the per-tile barriers
-  // softcap without ALiBi keeps tanh() in S and lets `cap` ride in the exp2 FFMA (one multiply per logit less)
-  const bool cap_folded = kSoftcap && a.softcap > 0.f && !a.alibi_slopes;
-  const float scale_log2 = !kSoftcap ? a.softmax_scale * kLog2e : (cap_folded ? a.softcap * kLog2e : 1.0f);
+  const float scale_log2 = kLogits == 0 ? a.softmax_scale * kLog2e : (kLogits == 1 ? a.softcap * kLog2e : 1.0f);
   int k_st = 0, v_st = 0;           // ring positions (TMA warps: next to fill; MMA warp: next to use)
   uint32_t k_ph = 0, v_ph = 0;
   uint32_t n_fix = 0;               // V tail fix-ups so far (V_FIX parity)
@@ -408,20 +407,19 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
         tmem_ld_wait();
         if (row == 0) TC_TRACE(t_run + j, w * 5 + 1);
         const int n0 = (tile0 + j) * kBN;
-        if constexpr (kSoftcap) {
+        if constexpr (kLogits == 1) {
+          const float pre = a.softmax_scale / a.softcap;
+#pragma unroll
+          for (int c = 0; c < 4; ++c)
+#pragma unroll
+            for (int i = 0; i < 32; ++i) s[c][i] = __float_as_uint(tanh_approx(__uint_as_float(s[c][i]) * pre));
+        } else if constexpr (kLogits == 2) {
           if (a.softcap > 0.f) {
-            const float pre = a.softmax_scale / a.softcap, cap_log2 = cap_folded ? 1.0f : a.softcap * kLog2e;
-            if (cap_folded) {
+            const float pre = a.softmax_scale / a.softcap, cap_log2 = a.softcap * kLog2e;
 #pragma unroll
-              for (int c = 0; c < 4; ++c)
+            for (int c = 0; c < 4; ++c)
 #pragma unroll
-                for (int i = 0; i < 32; ++i) s[c][i] = __float_as_uint(tanh_approx(__uint_as_float(s[c][i]) * pre));
-            } else {
-#pragma unroll
-              for (int c = 0; c < 4; ++c)
-#pragma unroll
-                for (int i = 0; i < 32; ++i) s[c][i] = __float_as_uint(cap_log2 * tanh_approx(__uint_as_float(s[c][i]) * pre));
-            }
+              for (int i = 0; i < 32; ++i) s[c][i] = __float_as_uint(cap_log2 * tanh_approx(__uint_as_float(s[c][i]) * pre));
           } else {
             const float sl2 = a.softmax_scale * kLog2e;
 #pragma unroll
@@ -896,16 +894,18 @@ int launch_attn_prefill_tc(const b200attn_attention_params& a, cudaStream_t stre
   // fraction of the exponentials taken off the MUFU (tuning().reserved bits 4..7; 0 = default)
   using Kern = void (*)(const TcParams, const CUtensorMap, const CUtensorMap, const CUtensorMap);
 #define TCV(B) {attn_prefill_tc_kernel<B, 0, 1>, attn_prefill_tc_kernel<B, 0, 1>, attn_prefill_tc_kernel<B, 1, 4>, \
-                attn_prefill_tc_kernel<B, 1, 3>, attn_prefill_tc_kernel<B, 1, 2>, attn_prefill_tc_kernel<B, 0, 1, true>, \
-                attn_prefill_tc_kernel<B, 1, 2, true>}
-  // softcap (variants 5, 6): the tanh doubles the MUFU work; moving half the exps to the FMA pipe (6) measured
-  // slower than leaving them (5): 8k prompt 0.705 ms vs 0.671 ms (profiles/r01_kbench_softcap_tc.jsonl)
-  constexpr int kNumVariants = 7, kSoftcapVariant = 5;
+                attn_prefill_tc_kernel<B, 1, 3>, attn_prefill_tc_kernel<B, 1, 2>, attn_prefill_tc_kernel<B, 0, 1, 1>, \
+                attn_prefill_tc_kernel<B, 1, 2, 1>, attn_prefill_tc_kernel<B, 0, 1, 2>}
+  // softcap alone (variants 5, 6): the tanh doubles the MUFU work; moving half the exps to the FMA pipe (6) measured
+  // slower than leaving them (5): 8k prompt 0.705 ms vs 0.671 ms (profiles/r01_kbench_softcap_tc.jsonl).
+  // ALiBi, with or without softcap: variant 7.
+  constexpr int kNumVariants = 8, kSoftcapVariant = 5, kGeneralVariant = 7;
   static const Kern kVariants[2][kNumVariants] = {TCV(false), TCV(true)};
 #undef TCV
   int variant = (tuning().reserved >> 4) & 15;
   if (variant >= kSoftcapVariant) variant = 0;
-  if (a.softcap > 0.f || a.alibi_slopes) variant = (((tuning().reserved >> 4) & 15) == 6) ? 6 : kSoftcapVariant;
+  if (a.alibi_slopes) variant = kGeneralVariant;
+  else if (a.softcap > 0.f) variant = (((tuning().reserved >> 4) & 15) == 6) ? 6 : kSoftcapVariant;
   Kern kern = kVariants[bf16 ? 1 : 0][variant];
   static thread_local bool attr_set[2][kNumVariants] = {};
   if (!attr_set[bf16 ? 1 : 0][variant]) {
