@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 2
+#define B200ATTN_ABI_VERSION 3
 
 #if defined(__GNUC__)
 #define B200ATTN_API __attribute__((visibility("default")))
@@ -142,6 +142,12 @@ typedef struct b200attn_attention_params {
                                   FP8-e4m3 [T, Hq, D], out_stride* in 1-byte elements, rows 8-byte
                                   aligned, and every kernel of the path quantises in its epilogue:
                                   out = e4m3_rn_satfinite(o_fp32 * (1.0f / *out_scale))               */
+  const float* qq_bias;        /* NULL, or a [q_len_max, qq_bias_stride0] fp32 matrix (upstream `qq_bias`, tree /
+                                  speculative-decoding masks; vllm/v1/attention/ops/triton_unified_attention.py:376,
+                                  526-528, triton_attention_helpers.py:344-357): after masking and ALiBi,
+                                  S[query i of a sequence][key j] += qq_bias[i][j - context_len] for
+                                  0 <= j - context_len < qq_bias_stride0.  Served by the SIMT kernel only.   */
+  int64_t qq_bias_stride0;
 } b200attn_attention_params;
 
 /* Bytes of workspace b200attn_unified_attention may need for this shape

@@ -65,8 +65,12 @@ def unified_attention_ref(
     sinks: Optional[torch.Tensor] = None,  # [Hq]: per-head logit that only joins the softmax denominator
     output_scale: Optional[float] = None,  # static per-tensor FP8 output quantisation; result is float8_e4m3fn
     local_chunk: int = 0,  # chunked local attention: a query only sees keys of its own chunk of positions
+    qq_bias: Optional[torch.Tensor] = None,  # [q, n] fp32: bias between the query tokens of a step
 ) -> torch.Tensor:
-    """`local_chunk` states chunked local attention (iRoPE / Llama-4) directly as a mask: position p
+    """`qq_bias` (upstream, vllm/v1/attention/ops/triton_unified_attention.py:526-528 with
+    triton_attention_helpers.py:344-357): after masking and ALiBi, S[query i][key j] += qq_bias[i][j - ctx] for
+    0 <= j - ctx < qq_bias.stride(0), the same matrix for every sequence and head.
+    `local_chunk` states chunked local attention (iRoPE / Llama-4) directly as a mask: position p
     attends to keys in [floor(p / chunk) * chunk, p].  The reference gets the same result by cutting
     the batch into virtual sequences (`make_local_attention_virtual_batches`, used at
     ibm-triton-lib/ibm_triton_lib/backend/triton_attn.py:155-190, 423-444) and running the unchanged kernel.
@@ -108,6 +112,11 @@ def unified_attention_ref(
         s = torch.where(visible, s, torch.full_like(s, float("-inf")))
         if alibi_slopes is not None:
             s = s + alibi_slopes.to(torch.float32).view(Hq, 1, 1) * (kpos - ctx)  # :481-482
+        if qq_bias is not None:
+            n_rel = min(qq_bias.stride(0), q_len, qq_bias.shape[1])
+            bias = torch.zeros(q_len, kv_len, dtype=torch.float32)
+            bias[:, ctx:ctx + n_rel] = qq_bias[:q_len, :n_rel].to(torch.float32)
+            s = s + bias.view(1, q_len, kv_len)
         m = s.max(dim=-1, keepdim=True).values
         if sinks is not None:
             m = torch.maximum(m, sinks.to(torch.float32).view(Hq, 1, 1))

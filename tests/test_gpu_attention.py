@@ -583,3 +583,38 @@ def test_fp8_prefill_staging_in_a_cuda_graph():
     g.replay()
     torch.cuda.synchronize()
     assert_close(out.cpu(), _oracle(inp, D ** -0.5, k_scale=0.5, v_scale=0.25), atol=FP8_ATOL, rtol=BF16_RTOL, what="staged, graph")
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("D", [64, 128])
+def test_qq_bias_between_the_query_tokens_of_a_step(dtype, D):
+    """Upstream `qq_bias` (tree / speculative-decoding masks): a [q, q] bias on the logits between a step's own
+    query tokens, the same for every sequence and head; -inf entries cut a query off from a sibling branch."""
+    from vllm_triton_backend_b200 import _cabi, ops
+
+    lens = [(8, 700), (8, 8), (8, 33), (5, 1200), (1, 90)]
+    Hq, Hkv, bs = 8, 2, 16
+    inp = make_paged_inputs(lens, Hq, Hkv, D, bs, dtype=dtype, seed=61)
+    g = torch.Generator().manual_seed(7)
+    bias = torch.randn(8, 8, generator=g)
+    bias[torch.rand(8, 8, generator=g) < 0.3] = float("-inf")
+    bias.fill_diagonal_(0.0)  # a token always sees itself
+    scale = D ** -0.5
+    dev = "cuda"
+    out = torch.full_like(inp["q"], float("nan")).to(dev)
+    ops.unified_attention(
+        q=inp["q"].to(dev), k=inp["k_cache"].to(dev), v=inp["v_cache"].to(dev), out=out, cu_seqlens_q=inp["cu_seqlens_q"].to(dev),
+        max_seqlen_q=8, seqused_k=inp["seq_lens"].to(dev), max_seqlen_k=1200, softmax_scale=scale, causal=True,
+        window_size=(-1, -1), block_table=inp["block_table"].to(dev), softcap=0, q_descale=None, k_descale=None,
+        v_descale=None, qq_bias=bias.to(dev))
+    torch.cuda.synchronize()
+    assert _cabi.last_kernel() == "attn_generic"
+    ref = unified_attention_ref(inp["q"], inp["k_cache"], inp["v_cache"], inp["cu_seqlens_q"], inp["seq_lens"],
+                                inp["block_table"], scale, out_dtype=torch.float32, qq_bias=bias)
+    assert_close(out.cpu(), ref, atol=BF16_ATOL, rtol=BF16_RTOL, what="qq_bias")
+    with pytest.raises(_cabi.B200AttnError, match="generic kernel only"):
+        ops.unified_attention(
+            q=inp["q"].to(dev), k=inp["k_cache"].to(dev), v=inp["v_cache"].to(dev), out=out,
+            cu_seqlens_q=inp["cu_seqlens_q"].to(dev), max_seqlen_q=8, seqused_k=inp["seq_lens"].to(dev), max_seqlen_k=1200,
+            softmax_scale=scale, causal=True, window_size=(-1, -1), block_table=inp["block_table"].to(dev), softcap=0,
+            q_descale=None, k_descale=None, v_descale=None, qq_bias=bias.to(dev), force_selection=22)

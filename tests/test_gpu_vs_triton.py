@@ -122,3 +122,31 @@ def test_fp8_kv_prefill_matches_triton():
 def test_attention_sinks_match_triton(lens, D, window):
     ours, ref, kern = _both(lens, 16, 2, D, 16, window=window, sinks=True, seed=17)
     assert_close(ours, ref, atol=BF16_ATOL, rtol=BF16_RTOL, what=f"sinks vs triton ({kern})")
+
+
+def test_qq_bias_matches_triton():
+    why = triton_reference.available()
+    if why:
+        pytest.skip(why)
+    from vllm.v1.attention.ops.triton_unified_attention import unified_attention as triton_unified_attention
+    from vllm_triton_backend_b200 import ops
+
+    dev = "cuda"
+    lens = [(6, 500), (6, 6), (6, 77), (3, 900)]
+    Hq, Hkv, D, bs = 16, 4, 128, 16
+    inp = make_paged_inputs(lens, Hq, Hkv, D, bs, seed=63, device=dev)
+    g = torch.Generator().manual_seed(9)
+    bias = torch.randn(6, 6, generator=g)
+    bias[torch.rand(6, 6, generator=g) < 0.3] = float("-inf")
+    bias.fill_diagonal_(0.0)
+    bias = bias.to(dev)
+    kw = dict(q=inp["q"], k=inp["k_cache"], v=inp["v_cache"], cu_seqlens_q=inp["cu_seqlens_q"], max_seqlen_q=6,
+              seqused_k=inp["seq_lens"], max_seqlen_k=900, softmax_scale=D ** -0.5, causal=True, window_size=(-1, -1),
+              block_table=inp["block_table"], softcap=0.0, q_descale=None, k_descale=None, v_descale=None, qq_bias=bias)
+    ours, ref = torch.full_like(inp["q"], float("nan")), torch.full_like(inp["q"], float("nan"))
+    ops.unified_attention(out=ours, **kw)
+    one = torch.ones(1, dtype=torch.float32, device=dev)
+    kw.update(k_descale=one, v_descale=one)
+    triton_unified_attention(out=ref, **kw)
+    torch.cuda.synchronize()
+    assert_close(ours.cpu(), ref.cpu(), atol=BF16_ATOL, rtol=BF16_RTOL, what="qq_bias vs triton")

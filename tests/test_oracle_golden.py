@@ -95,3 +95,22 @@ def test_output_scale_quantises_the_fp32_result():
     assert ((q8.float() - x).abs() <= 0.5 * step * (1 + 1e-5)).all(), "not the nearest e4m3 code"
     sat = unified_attention_ref(*args, output_scale=1e-12).view(torch.uint8)
     assert set(sat.unique().tolist()) <= {0x7E, 0xFE}, "saturates to +-448, never NaN"
+
+
+def test_qq_bias_is_an_additive_bias_on_the_query_query_block():
+    """Zero bias changes nothing; -inf between query i and an earlier query j of the same step equals dropping key ctx+j."""
+    c = load_golden_attn(f"{GOLDEN_DIR}/attn_mixed2d_f32.npz")
+    args = (c["q"], c["k_cache"], c["v_cache"], c["cu_seqlens_q"], c["seq_lens"], c["block_table"], c["scale"])
+    q_max = int((c["cu_seqlens_q"][1:] - c["cu_seqlens_q"][:-1]).max())
+    base = unified_attention_ref(*args, out_dtype=torch.float32)
+    same = unified_attention_ref(*args, out_dtype=torch.float32, qq_bias=torch.zeros(q_max, q_max))
+    assert torch.equal(base, same)
+    if q_max >= 2:
+        bias = torch.zeros(q_max, q_max)
+        bias[1:, 0] = float("-inf")  # nobody but the first query token sees the first query token's key
+        cut = unified_attention_ref(*args, out_dtype=torch.float32, qq_bias=bias)
+        cu = c["cu_seqlens_q"].tolist()
+        first_rows = torch.tensor([cu[b] for b in range(len(cu) - 1) if cu[b + 1] > cu[b]])
+        assert torch.allclose(cut[first_rows], base[first_rows], atol=1e-6)  # row 0 of every sequence is unaffected
+        multi = [b for b in range(len(cu) - 1) if cu[b + 1] - cu[b] >= 2]
+        assert multi and any(not torch.allclose(cut[cu[b] + 1], base[cu[b] + 1], atol=1e-6) for b in multi)

@@ -22,7 +22,7 @@ STATUS_NAMES = {
     6: "E_CUDA", 7: "E_NULL",
 }
 
-ABI_VERSION = 2  # include/b200attn.h B200ATTN_ABI_VERSION
+ABI_VERSION = 3  # include/b200attn.h B200ATTN_ABI_VERSION
 
 EXPORTED_SYMBOLS = [
     "b200attn_reshape_and_cache_flash",
@@ -58,6 +58,7 @@ class AttentionParams(Structure):
         ("vc_block_stride", c_int64), ("vc_slot_stride", c_int64), ("vc_head_stride", c_int64),
         ("workspace", c_void_p), ("workspace_bytes", c_uint64),
         ("out_scale", c_void_p),
+        ("qq_bias", c_void_p), ("qq_bias_stride0", c_int64),
     ]
 
 

@@ -83,6 +83,10 @@ __global__ void __launch_bounds__(128) attn_generic_kernel(b200attn_attention_pa
       s = dot * p.softmax_scale;
       if (p.softcap > 0.f) s = softcap_fn(s, p.softcap, inv_cap);
       if (p.alibi_slopes) s += slope * (float)(pos - ctx);
+      if (p.qq_bias) {  // bias between this step's query tokens (upstream load_qq_bias_tile)
+        const int rel = pos - ctx;
+        if (rel >= 0 && rel < p.qq_bias_stride0) s += p.qq_bias[(int64_t)qpos * p.qq_bias_stride0 + rel];
+      }
     }
     float m_new = fmaxf(m, warp_max(s));
     const float m_use = (m_new == -INFINITY) ? 0.f : m_new;

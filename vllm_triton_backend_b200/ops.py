@@ -171,7 +171,7 @@ def _check_out(out, q_dtype, output_scale) -> None:
 
 def build_attention_params(
     q, k, v, out, cu_seqlens_q, max_seqlen_q, seqused_k, max_seqlen_k, softmax_scale, window_size, block_table,
-    softcap, k_descale, v_descale, alibi_slopes, path, workspace, sinks=None, output_scale=None,
+    softcap, k_descale, v_descale, alibi_slopes, path, workspace, sinks=None, output_scale=None, qq_bias=None,
 ) -> AttentionParams:
     if q.dim() != 3 or k.dim() != 4 or v.dim() != 4:
         raise ValueError("q must be [T, Hq, D]; k, v must be [NB, bs, Hkv, D]")
@@ -195,6 +195,12 @@ def build_attention_params(
         raise ValueError("sinks must be a contiguous float32 tensor with one entry per query head")
     p.sinks = sinks.data_ptr() if sinks is not None else None
     p.out_scale = output_scale.data_ptr() if output_scale is not None else None
+    if qq_bias is not None:
+        if qq_bias.dtype != torch.float32 or qq_bias.dim() != 2 or qq_bias.stride(1) != 1 or not qq_bias.is_cuda:
+            raise ValueError("qq_bias must be a 2-D float32 CUDA tensor with a contiguous last dimension")
+        if qq_bias.shape[0] < int(max_seqlen_q):
+            raise ValueError("qq_bias needs one row per query position of the longest sequence")
+        p.qq_bias, p.qq_bias_stride0 = qq_bias.data_ptr(), qq_bias.stride(0)
     p.softmax_scale = float(softmax_scale)
     p.softcap = float(softcap or 0.0)
     p.sliding_window = int(1 + window_size[0]) if window_size is not None else 0  # reference :915
@@ -240,6 +246,7 @@ def unified_attention(
     workspace: Optional[torch.Tensor] = None,
     sinks: Optional[torch.Tensor] = None,  # [Hq] float32 (upstream keyword)
     output_scale: Optional[torch.Tensor] = None,  # upstream keyword: `out` is e4m3, out = quant(o / output_scale)
+    qq_bias: Optional[torch.Tensor] = None,  # upstream keyword: [q, q] fp32 bias between a step's query tokens (SIMT kernel)
     **_ignored,
 ) -> None:
     if not causal:
@@ -274,7 +281,7 @@ def unified_attention(
         workspace = get_workspace(q.device, need)
     p = build_attention_params(
         q, k, v, out, cu_seqlens_q, max_seqlen_q, seqused_k, max_seqlen_k, softmax_scale, window_size, block_table,
-        softcap, k_descale, v_descale, alibi_slopes, path, workspace, sinks, output_scale,
+        softcap, k_descale, v_descale, alibi_slopes, path, workspace, sinks, output_scale, qq_bias,
     )
     _cabi.check(_cabi.load_library().b200attn_unified_attention(ctypes.byref(p), _stream_ptr(q)))
 
