@@ -78,12 +78,21 @@ class B200AttentionMetadataBuilder(AttentionMetadataBuilder[B200AttentionMetadat
         nbytes = ops.workspace_bytes(max_num_seqs, max_num_seqs, self.num_heads_q, self.num_heads_kv, self.headdim)
         cache_dtype = str(getattr(vllm_config.cache_config, "cache_dtype", "auto"))
         if cache_dtype.startswith("fp8"):
-            # FP8 cache: staging pool that lets long prefills run the tcgen05 kernel (csrc/kv_stage.cu).  Sized for
-            # two sequences of max_model_len (or B200ATTN_FP8_STAGING_TOKENS); what does not fit runs mma.sync.
+            # FP8 cache: staging pool that lets long prefills run the tcgen05 kernel (csrc/kv_stage.cu).  It sits
+            # outside vLLM's KV-cache budget (gpu_memory_utilization does not see it), so it is bounded: one
+            # sequence of max_model_len, at most B200ATTN_FP8_STAGING_MIB (default 256) MiB; what does not fit
+            # runs the mma.sync kernel.  B200ATTN_FP8_STAGING_TOKENS overrides the token count (0 = no staging).
             import os
 
-            tokens = int(os.environ.get("B200ATTN_FP8_STAGING_TOKENS", 2 * int(model_config.max_model_len)))
-            nbytes += ops.fp8_staging_bytes(max_num_seqs, tokens, self.block_size, self.num_heads_kv, self.headdim)
+            per_token = 2 * self.num_heads_kv * self.headdim * 2  # K + V, 16-bit
+            cap_tokens = (int(os.environ.get("B200ATTN_FP8_STAGING_MIB", 256)) << 20) // per_token
+            tokens = int(os.environ.get("B200ATTN_FP8_STAGING_TOKENS", min(int(model_config.max_model_len), cap_tokens)))
+            stage = ops.fp8_staging_bytes(max_num_seqs, tokens, self.block_size, self.num_heads_kv, self.headdim)
+            nbytes += stage
+            import logging
+
+            logging.getLogger("vllm_triton_backend_b200").info(
+                "b200attn: FP8 prefill staging pool %.1f MiB (%d tokens), outside the KV-cache budget", stage / 2**20, tokens)
         # zeroed once: holds the decode kernel's self-cleaning ticket counters
         self.workspace = torch.zeros(nbytes, dtype=torch.uint8, device=device)
         self._ws_extra = nbytes - ops.workspace_bytes(max_num_seqs, max_num_seqs, self.num_heads_q, self.num_heads_kv,
@@ -206,18 +215,20 @@ class B200AttentionBackend(AttentionBackend):
 
     @classmethod
     def supports_compute_capability(cls, capability) -> bool:
-        return capability.major >= 10  # sm_100a kernels only
+        return capability.major == 10  # sm_100a cubins only (they do not load on sm_12x)
 
     @classmethod
     def supports_sink(cls) -> bool:
-        return True  # decode, mma.sync prefill and SIMT kernels; sequences with sinks skip the tcgen05 kernel
+        return True  # every kernel applies the sink in its epilogue (decode: direct epilogue or the merge)
 
 
 def split_kv_cache(kv_cache: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor]:
     """K/V views [NB, bs, Hkv, D] of either allocation vLLM may hand us:
     (2, NB, bs, Hkv, D) — ours / the reference plugin's — or (NB, 2, bs, Hkv, D)
     (stock vLLM >= 0.11, block stride 2*bs*Hkv*D)."""
-    if kv_cache.shape[0] == 2 and kv_cache.dim() == 5 and kv_cache.shape[1] != 2:
+    if kv_cache.dim() == 5 and kv_cache.shape[0] == 2 and kv_cache.shape[1] == 2:
+        # NB == 2 makes the two allocations look alike; this backend declares (2, NB, ...) (get_kv_cache_shape),
+        # so that is what a cache vLLM allocated for it is
         return kv_cache.unbind(0)
     if kv_cache.dim() == 5 and kv_cache.shape[1] == 2:
         return kv_cache.unbind(1)
@@ -239,8 +250,17 @@ class B200AttentionImpl(AttentionImpl):
         kv_sharing_target_layer_name: Optional[str] = None,
         blocksparse_params=None,
         sinks: Optional[torch.Tensor] = None,
+        use_alibi_sqrt: bool = False,  # vLLM 0.22 impl arguments that change the result and are not built here:
+        chunk_lookback: int = -1,      # a non-default value raises (upstream triton_attn.py TritonAttentionImpl.__init__)
         **extra_impl_args,
     ) -> None:
+        if use_alibi_sqrt:
+            raise NotImplementedError("B200AttentionImpl: use_alibi_sqrt is not implemented")
+        if chunk_lookback is not None and int(chunk_lookback) >= 0:
+            raise NotImplementedError("B200AttentionImpl: chunk_lookback is not implemented")
+        if extra_impl_args:
+            # an argument this backend does not know may change what the layer computes: refuse, never ignore
+            raise NotImplementedError(f"B200AttentionImpl: unsupported impl arguments {sorted(extra_impl_args)}")
         if blocksparse_params is not None:
             raise ValueError("B200Attention does not support block-sparse attention.")  # reference :305-306
         if sinks is not None and sinks.shape[0] != num_heads:

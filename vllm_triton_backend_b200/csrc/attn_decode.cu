@@ -981,20 +981,12 @@ int launch_variant(const b200attn_attention_params& a, DecodeParams& P, cudaStre
   // grid: one CTA per SM, never more CTAs than the upper bound on steps
   const long long max_steps =
       (long long)a.num_seqs * P.head_groups * ((a.max_seqlen_k + P.tps - 1) / P.tps > 0 ? (a.max_seqlen_k + P.tps - 1) / P.tps : 1);
-  long long grid = dev.num_sms;
-  if (grid > max_steps) grid = max_steps;
+  long long grid = dev.num_sms < kMaxDecodeCtas ? dev.num_sms : kMaxDecodeCtas;
+  if (grid > max_steps && !launch_is_captured()) grid = max_steps;
   if (grid < 1) grid = 1;
 
   auto kern = attn_decode_kernel<D, KV_FP8, MMA_BF16, Q_BF16, NT, NW, TT>;
-  static thread_local bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, dev.max_smem_optin);
-    if (e != cudaSuccess) {
-      set_error("decode: cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
-      return B200ATTN_E_CUDA;
-    }
-    attr_set = true;
-  }
+  if (int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(kern), dev.max_smem_optin, "decode")) return rc;
   // Programmatic dependent launch: lets this grid's launch and prologue overlap the cache write in front of it
   // (common.cuh).  tuning().reserved bit 9 turns it off.
   cudaLaunchConfig_t cfg = {};
@@ -1040,7 +1032,7 @@ uint64_t decode_workspace_bytes(int num_seqs, int num_q_heads, int num_kv_heads,
   // slots <= items + ctas; records of (hpc*group) heads: bounded by
   // (B*Hq + ctas*8*group) head-rows of (D + 2) floats, after the counter region.
   const uint64_t group = (uint64_t)(num_q_heads / (num_kv_heads > 0 ? num_kv_heads : 1));
-  const uint64_t ctas = 160;  // >= SM count of any B200 SKU
+  const uint64_t ctas = kMaxDecodeCtas;  // the grid is min(#SMs, kMaxDecodeCtas)
   const uint64_t rows = (uint64_t)num_seqs * num_q_heads + ctas * 8 * (group > 0 ? group : 1);
   return kCounterBytes + rows * (uint64_t)(head_size + 2) * 4 + 1024;
 }
@@ -1094,7 +1086,7 @@ int launch_attn_decode(const b200attn_attention_params& a, cudaStream_t stream, 
   P.ws_cnt = reinterpret_cast<int*>(w);
   uint64_t off = kCounterBytes;
   const uint64_t group = (uint64_t)P.group;
-  const uint64_t rows = (uint64_t)a.num_seqs * a.num_q_heads + 160ull * 8 * group;
+  const uint64_t rows = (uint64_t)a.num_seqs * a.num_q_heads + (uint64_t)kMaxDecodeCtas * 8 * group;
   P.ws_ml = reinterpret_cast<float*>(w + off);
   off += ((rows * 8 + 255) / 256) * 256;
   P.ws_acc = reinterpret_cast<float*>(w + off);

@@ -401,20 +401,14 @@ int launch_variant(const b200attn_attention_params& a, cudaStream_t stream, QLen
   int bs_shift = -1;
   if ((a.block_size & (a.block_size - 1)) == 0)
     for (bs_shift = 0; (1 << bs_shift) < a.block_size; ++bs_shift) {}
-  static thread_local bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) {
-      set_error("prefill: cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
-      return B200ATTN_E_CUDA;
-    }
-    attr_set = true;
-  }
+  if (int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(kern), smem, "prefill")) return rc;
   // host-int upper bounds on the q-blocks: the reference's (T // BLOCK_Q + B, :886-889), or, when the launch
   // only takes queries up to max_q_len, B * ceil(max_q_len / BLOCK_Q) with a direct block -> sequence map
   long long nblocks = (long long)a.num_tokens / block_q + a.num_seqs;
   int qb_per_seq = 0;
-  const int longest = range.max_q_len < a.max_seqlen_q ? range.max_q_len : a.max_seqlen_q;
+  // (max_seqlen_q describes the batch in hand; a captured launch is replayed with others, so it only trusts the range)
+  const bool captured = launch_is_captured();
+  const int longest = (captured || range.max_q_len < a.max_seqlen_q) ? range.max_q_len : a.max_seqlen_q;
   const long long per_seq = ((long long)longest + block_q - 1) / block_q;
   if (per_seq >= 1 && per_seq * a.num_seqs < nblocks) qb_per_seq = (int)per_seq, nblocks = per_seq * a.num_seqs;
   const dim3 grid((unsigned)nblocks, (unsigned)a.num_kv_heads);

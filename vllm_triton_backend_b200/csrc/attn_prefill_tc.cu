@@ -907,15 +907,7 @@ int launch_attn_prefill_tc(const b200attn_attention_params& a, cudaStream_t stre
   if (a.alibi_slopes) variant = kGeneralVariant;
   else if (a.softcap > 0.f) variant = (((tuning().reserved >> 4) & 15) == 6) ? 6 : kSoftcapVariant;
   Kern kern = kVariants[bf16 ? 1 : 0][variant];
-  static thread_local bool attr_set[2][kNumVariants] = {};
-  if (!attr_set[bf16 ? 1 : 0][variant]) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
-    if (e != cudaSuccess) {
-      set_error("prefill_tc: cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
-      return B200ATTN_E_CUDA;
-    }
-    attr_set[bf16 ? 1 : 0][variant] = true;
-  }
+  if (int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(kern), kSmemBytes, "prefill_tc")) return rc;
   const int BQ = 2 * P.block_q;
   const dim3 grid((unsigned)a.num_kv_heads, (unsigned)(a.num_tokens / BQ + a.num_seqs));
   kern<<<grid, kThreads, kSmemBytes, stream>>>(P, qmap, kmap, vmap);

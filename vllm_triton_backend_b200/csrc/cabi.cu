@@ -3,6 +3,7 @@
 #include <cstdio>
 #include <cstring>
 #include <mutex>
+#include <unordered_map>
 
 #include "common.cuh"
 
@@ -12,7 +13,8 @@ namespace {
 thread_local char g_error[512] = "";
 thread_local uint64_t g_launches = 0;
 thread_local const char* g_last_kernel = "";
-Tuning g_tuning;
+Tuning g_tuning;  // benchmark A/B switches; set before launching, not while other threads launch
+thread_local bool g_capturing = false;
 unsigned long long* g_decode_trace = nullptr;
 }  // namespace
 
@@ -40,19 +42,45 @@ int check_launch(const char* what) {
 }
 
 Tuning& tuning() { return g_tuning; }
+bool launch_is_captured() { return g_capturing; }
+
+// Per-device attributes and per-(device, kernel) launch attributes: a process may drive several GPUs from one
+// thread (cudaSetDevice between calls), so nothing here is cached "for the first device seen".
+constexpr int kMaxDevices = 64;
 
 const DeviceInfo& device_info() {
-  static DeviceInfo info;
-  static std::once_flag once;
-  std::call_once(once, [] {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess) return;
-    cudaDeviceGetAttribute(&info.num_sms, cudaDevAttrMultiProcessorCount, dev);
-    cudaDeviceGetAttribute(&info.max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
-    cudaDeviceGetAttribute(&info.cc_major, cudaDevAttrComputeCapabilityMajor, dev);
-    cudaDeviceGetAttribute(&info.cc_minor, cudaDevAttrComputeCapabilityMinor, dev);
+  static DeviceInfo info[kMaxDevices];
+  static std::once_flag once[kMaxDevices];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) dev = 0;
+  std::call_once(once[dev], [dev] {
+    DeviceInfo& d = info[dev];
+    cudaDeviceGetAttribute(&d.num_sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaDeviceGetAttribute(&d.max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+    cudaDeviceGetAttribute(&d.cc_major, cudaDevAttrComputeCapabilityMajor, dev);
+    cudaDeviceGetAttribute(&d.cc_minor, cudaDevAttrComputeCapabilityMinor, dev);
+    d.device = dev;
   });
-  return info;
+  return info[dev];
+}
+
+int ensure_dynamic_smem(const void* kernel, int bytes, const char* what) {
+  static std::mutex mu;
+  static std::unordered_map<uint64_t, int> done;  // (kernel, device) -> bytes granted
+  const uint64_t key = reinterpret_cast<uint64_t>(kernel) * 64u + (uint64_t)device_info().device;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = done.find(key);
+    if (it != done.end() && it->second >= bytes) return B200ATTN_OK;
+  }
+  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e != cudaSuccess) {
+    set_error("%s: cudaFuncSetAttribute(%d bytes of shared memory) failed: %s", what, bytes, cudaGetErrorString(e));
+    return B200ATTN_E_CUDA;
+  }
+  std::lock_guard<std::mutex> lock(mu);
+  done[key] = bytes;
+  return B200ATTN_OK;
 }
 
 EncodeTiledFn encode_tiled_fn() {
@@ -194,6 +222,16 @@ int b200attn_unified_attention(const b200attn_attention_params* pp, b200attn_str
   // AUTO: reference dispatch (max_seqlen_q > 1 -> 2D else 3D,
   // triton_unified_attention.py:884); shapes a tensor-core kernel does not take
   // run the SIMT kernel (still CUDA; there is no CPU path).
+  //
+  // A launch that is being captured into a CUDA graph is replayed with other batch CONTENTS (and, in vLLM's mixed
+  // FULL graphs, other query lengths) behind the same host ints, so under capture the set of launches depends on
+  // capability and shape class only - the reference's two kernels each take any batch, and so must the set
+  // recorded here: no shortcut that assumes every sequence looks like the captured ones, and grids are sized
+  // from T and B alone (launch_is_captured() in the launchers).
+  cudaStreamCaptureStatus cap_status = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(stream, &cap_status) != cudaSuccess) cap_status = cudaStreamCaptureStatusNone, (void)cudaGetLastError();
+  g_capturing = cap_status != cudaStreamCaptureStatusNone;
+  const bool captured = g_capturing;
   const char* why = nullptr;
   if (p.max_seqlen_q <= 1) {
     if (decode_supported(p, &why) && p.workspace &&
@@ -210,8 +248,9 @@ int b200attn_unified_attention(const b200attn_attention_params* pp, b200attn_str
   if (!prefill_supported(p, &why)) return launch_attn_generic(p, stream);
   const bool ws_ok = p.workspace && p.workspace_bytes >= decode_workspace_bytes(p.num_seqs, p.num_q_heads, p.num_kv_heads, p.head_size);
   const bool dec_ok = ws_ok && decode_supported(p, &why, /*mixed_batch=*/true);
-  // every sequence has exactly max_seqlen_q tokens <=> T == B * max_seqlen_q
-  const bool uniform = (int64_t)p.num_tokens == (int64_t)p.num_seqs * p.max_seqlen_q;
+  // every sequence has exactly max_seqlen_q tokens <=> T == B * max_seqlen_q (true of THIS batch only: not used
+  // when the launches are being captured)
+  const bool uniform = !captured && (int64_t)p.num_tokens == (int64_t)p.num_seqs * p.max_seqlen_q;
   if (p.kv_dtype == B200ATTN_FP8_E4M3 && !(g_tuning.reserved & 256)) {
     // FP8 cache: the sequences with long queries are dequantised once into the staging pool (the part of
     // the workspace past the decode region) and run the tcgen05 kernel on it; what does not fit the pool,
@@ -219,7 +258,7 @@ int b200attn_unified_attention(const b200attn_attention_params* pp, b200attn_str
     KvStage st;
     if (plan_kv_stage(p, &st)) {
       const b200attn_attention_params s16 = staged_params(p, st);
-      if (prefill_tc_supported(s16, &why) && p.max_seqlen_q >= prefill_tc_min_q_len(s16)) {
+      if (prefill_tc_supported(s16, &why) && (captured || p.max_seqlen_q >= prefill_tc_min_q_len(s16))) {
         QLenRange r;
         r.min_q_len = prefill_tc_min_q_len(s16);
         rc = launch_kv_stage(p, st, r, stream);
@@ -230,8 +269,9 @@ int b200attn_unified_attention(const b200attn_attention_params* pp, b200attn_str
         rest.min_q_len = dec_ok ? 2 : 0;
         // a pool that holds every sequence at full length cannot overflow: only short queries are left
         const int64_t every = (int64_t)p.num_seqs * ((p.max_seqlen_k + p.block_size - 1) / p.block_size);
-        if (st.cap_pages >= every) rest.max_q_len = r.min_q_len - 1;
-        if (rest.max_q_len >= rest.min_q_len && !(uniform && st.cap_pages >= every)) {
+        const bool fits = !captured && st.cap_pages >= every;
+        if (fits) rest.max_q_len = r.min_q_len - 1;
+        if (rest.max_q_len >= rest.min_q_len && !(uniform && fits)) {
           rc = launch_attn_prefill(p, stream, rest, st.staged_base);
           if (rc) return rc;
         }
@@ -241,7 +281,7 @@ int b200attn_unified_attention(const b200attn_attention_params* pp, b200attn_str
     }
   }
   int short_max = 0x7fffffff;  // longest query the mma.sync launch takes
-  if (prefill_tc_supported(p, &why) && p.max_seqlen_q >= prefill_tc_min_q_len(p)) {
+  if (prefill_tc_supported(p, &why) && (captured || p.max_seqlen_q >= prefill_tc_min_q_len(p))) {
     QLenRange r;
     r.min_q_len = prefill_tc_min_q_len(p);
     rc = launch_attn_prefill_tc(p, stream, r);

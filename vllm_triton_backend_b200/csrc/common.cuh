@@ -24,14 +24,21 @@ struct Tuning {
   int reserved = 0;
 };
 Tuning& tuning();
+// true while the current b200attn_unified_attention call is being captured into a CUDA graph: launchers then size
+// grids from T and B only (max_seqlen_q / max_seqlen_k describe the captured batch, not the replayed ones)
+bool launch_is_captured();
 unsigned long long* decode_trace_buffer();  // debug (b200attn_debug_set_decode_trace)
 
 struct DeviceInfo {
   int num_sms = 0;
   int max_smem_optin = 0;
   int cc_major = 0, cc_minor = 0;
+  int device = 0;
 };
-const DeviceInfo& device_info();
+const DeviceInfo& device_info();  // of the calling thread's current device
+// cudaFuncAttributeMaxDynamicSharedMemorySize, set once per (device, kernel)
+int ensure_dynamic_smem(const void* kernel, int bytes, const char* what);
+constexpr int kMaxDecodeCtas = 160;  // decode grid = min(#SMs, this); the split-KV workspace is sized for it
 
 // cuTensorMapEncodeTiled resolved through cudaGetDriverEntryPoint (no -lcuda, so
 // the library also loads on machines without a driver).

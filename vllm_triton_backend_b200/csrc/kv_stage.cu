@@ -64,14 +64,17 @@ template <> __device__ __forceinline__ uint32_t pack_t<__half>(float a, float b)
 
 template <typename T>
 __global__ void __launch_bounds__(256) stage_dequant_kernel(const StageArgs a) {
-  const int b = blockIdx.y, p = blockIdx.x;
+  const int b = blockIdx.y;
   const int base = a.staged_base[b];
   if (base < 0) return;
-  if (p * a.block_size >= a.seq_lens[b]) return;
-  const int64_t page = a.block_tables[(int64_t)b * a.bt_stride0 + p];
   const int D = a.head_size, H = a.num_kv_heads, bs = a.block_size;
   const int d16 = D / 16, per_slot = H * d16, units = bs * per_slot;
   const float ks = a.k_scale ? *a.k_scale : 1.f, vs = a.v_scale ? *a.v_scale : 1.f;
+  const int seq_len = a.seq_lens[b];
+  // pages are strided over the grid's x dimension: the grid is an upper bound from host ints, the
+  // length is device data (a captured graph replays with longer sequences than it was captured with)
+  for (int p = blockIdx.x; p * bs < seq_len; p += gridDim.x) {
+  const int64_t page = a.block_tables[(int64_t)b * a.bt_stride0 + p];
   const int64_t dst_page = (int64_t)(base + p) * bs * H * D;  // elements
   for (int u = threadIdx.x; u < 2 * units; u += blockDim.x) {
     const bool is_v = u >= units;
@@ -96,6 +99,7 @@ __global__ void __launch_bounds__(256) stage_dequant_kernel(const StageArgs a) {
     reinterpret_cast<int4*>(dst)[0] = make_int4(o[0], o[1], o[2], o[3]);
     reinterpret_cast<int4*>(dst)[1] = make_int4(o[4], o[5], o[6], o[7]);
   }
+  }
 }
 
 }  // namespace
@@ -116,7 +120,7 @@ bool plan_kv_stage(const b200attn_attention_params& p, KvStage* st) {
   const uint64_t page_bytes = (uint64_t)p.block_size * p.num_kv_heads * p.head_size * 2;
   uint64_t cap = (p.workspace_bytes - dec - index - 256) / (2 * page_bytes);
   const uint64_t useful = (uint64_t)p.num_seqs * ((p.max_seqlen_k + p.block_size - 1) / p.block_size);
-  if (cap > useful) cap = useful;  // never needs more than every sequence at full length
+  if (cap > useful && !launch_is_captured()) cap = useful;  // never needs more than every sequence at full length
   if (cap < 8 || cap > 0x7fffffffull) return false;
   char* w = static_cast<char*>(p.workspace) + dec;
   st->staged_base = reinterpret_cast<int32_t*>(w);
@@ -157,7 +161,8 @@ int launch_kv_stage(const b200attn_attention_params& p, const KvStage& st, QLenR
   note_launch("kv_stage_plan");
   int rc = check_launch("kv_stage_plan");
   if (rc) return rc;
-  const int max_pages = (p.max_seqlen_k + p.block_size - 1) / p.block_size;
+  int max_pages = (p.max_seqlen_k + p.block_size - 1) / p.block_size;
+  if (max_pages > 1024 || launch_is_captured()) max_pages = 1024;  // the kernel strides over a sequence's pages
   const dim3 grid((unsigned)(max_pages > 0 ? max_pages : 1), (unsigned)p.num_seqs);
   if (p.q_dtype == B200ATTN_BF16) stage_dequant_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(a);
   else stage_dequant_kernel<__half><<<grid, 256, 0, stream>>>(a);

@@ -5,6 +5,8 @@
 // so the descriptors are built over the strides, not over a dense shape.  A
 // 128-byte row chunk is the innermost TMA dimension so the hardware 128-byte
 // swizzle lands every (token, 128-byte chunk) where ldmatrix / UMMA expect it.
+#include <unordered_map>
+
 #include "common.cuh"
 
 namespace b200attn {
@@ -12,35 +14,46 @@ namespace {
 
 struct MapKey {
   const void* base;
-  int64_t s0, s1, s2, n0;
+  int64_t s0, s1, s2, n0, pair;
   int a, b, c, d, e, f, g;
-  int kind;
+  int kind, device;
   bool operator==(const MapKey& o) const {
-    return base == o.base && s0 == o.s0 && s1 == o.s1 && s2 == o.s2 && n0 == o.n0 && a == o.a && b == o.b &&
-           c == o.c && d == o.d && e == o.e && f == o.f && g == o.g && kind == o.kind;
+    return base == o.base && s0 == o.s0 && s1 == o.s1 && s2 == o.s2 && n0 == o.n0 && pair == o.pair && a == o.a &&
+           b == o.b && c == o.c && d == o.d && e == o.e && f == o.f && g == o.g && kind == o.kind && device == o.device;
   }
 };
-struct MapEntry {
-  MapKey key;
-  CUtensorMap map;
-  bool used = false;
+struct MapKeyHash {
+  size_t operator()(const MapKey& k) const {
+    uint64_t h = 0x9e3779b97f4a7c15ull;
+    auto mix = [&](uint64_t v) { h ^= v + 0x9e3779b97f4a7c15ull + (h << 6) + (h >> 2); };
+    mix(reinterpret_cast<uint64_t>(k.base)), mix((uint64_t)k.s0), mix((uint64_t)k.s1), mix((uint64_t)k.s2);
+    mix((uint64_t)k.n0), mix((uint64_t)k.pair), mix(((uint64_t)(uint32_t)k.a << 32) | (uint32_t)k.b);
+    mix(((uint64_t)(uint32_t)k.c << 32) | (uint32_t)k.d), mix(((uint64_t)(uint32_t)k.e << 32) | (uint32_t)k.f);
+    mix(((uint64_t)(uint32_t)k.g << 32) | (uint32_t)(k.kind * 64 + k.device));
+    return (size_t)h;
+  }
 };
-constexpr int kCacheSize = 32;
-thread_local MapEntry g_map_cache[kCacheSize];
-thread_local int g_map_next = 0;
+// Per-thread descriptor cache.  A model has two cache maps per layer (K and V) for each kernel family plus a query
+// map per step on the tcgen05 path, so the table holds a few thousand entries (a 32-slot ring thrashed from 16 layers
+// up); it is emptied when full (query maps of long-gone activations are the only entries that go stale).
+constexpr size_t kCacheMax = 4096;
+thread_local std::unordered_map<MapKey, CUtensorMap, MapKeyHash> g_map_cache;
+
+int current_device_or0() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) dev = 0;
+  return dev;
+}
 
 bool lookup(const MapKey& key, CUtensorMap* out) {
-  for (auto& e : g_map_cache)
-    if (e.used && e.key == key) {
-      *out = e.map;
-      return true;
-    }
-  return false;
+  auto it = g_map_cache.find(key);
+  if (it == g_map_cache.end()) return false;
+  *out = it->second;
+  return true;
 }
 void remember(const MapKey& key, const CUtensorMap& map) {
-  MapEntry& e = g_map_cache[g_map_next];
-  g_map_next = (g_map_next + 1) % kCacheSize;
-  e.key = key, e.map = map, e.used = true;
+  if (g_map_cache.size() >= kCacheMax) g_map_cache.clear();
+  g_map_cache.emplace(key, map);
 }
 
 }  // namespace
@@ -51,7 +64,7 @@ void remember(const MapKey& key, const CUtensorMap& map) {
 // takes both, so one copy brings the K and the V rows of a page: [head][k|v][slot][128 B].
 int make_kv_map(CUtensorMap* out, const void* base, int esz, int D, int bs, int hkv, int64_t nb, int64_t s_block,
                 int64_t s_slot, int64_t s_head, int box_slots, int box_heads, int box_dc, int64_t pair_bytes) {
-  MapKey key{base, s_block, s_slot, s_head, nb + (pair_bytes << 20), bs, hkv, D, esz, box_slots, box_heads, box_dc, 0};
+  MapKey key{base, s_block, s_slot, s_head, nb, pair_bytes, bs, hkv, D, esz, box_slots, box_heads, box_dc, 0, current_device_or0()};
   if (lookup(key, out)) return B200ATTN_OK;
   EncodeTiledFn fn = encode_tiled_fn();
   if (!fn) {
@@ -87,7 +100,7 @@ int make_kv_map(CUtensorMap* out, const void* base, int esz, int D, int bs, int 
 // head — the row order of the reference's Q tile (triton_unified_attention.py:343-346).
 int make_thd_map(CUtensorMap* out, const void* base, int D, int heads, int64_t tokens, int64_t s_token, int64_t s_head,
                  int box_heads, int box_tokens) {
-  MapKey key{base, s_token, s_head, 0, tokens, D, heads, box_heads, box_tokens, 0, 0, 0, 1};
+  MapKey key{base, s_token, s_head, 0, tokens, 0, D, heads, box_heads, box_tokens, 0, 0, 0, 1, current_device_or0()};
   if (lookup(key, out)) return B200ATTN_OK;
   EncodeTiledFn fn = encode_tiled_fn();
   if (!fn) {

@@ -29,6 +29,10 @@ _DTYPE = {
     torch.uint8: _cabi.FP8_E4M3,  # vLLM allocates fp8 caches as uint8
 }
 
+# upstream KVQuantMode values whose scales are the per-tensor k_descale / v_descale this library takes
+# (vllm/v1/kv_cache_interface.py: NONE = 0, FP8_PER_TENSOR = 1)
+_PER_TENSOR_KV_MODES = (0, 1)
+
 _workspaces: dict = {}
 _retired_workspaces: list = []
 _scalar_cache: dict = {}
@@ -85,7 +89,10 @@ def get_workspace(device, nbytes: int) -> torch.Tensor:
         if torch.cuda.is_current_stream_capturing():
             raise RuntimeError("b200attn workspace must be allocated before CUDA-graph capture (pass workspace=...)")
         if ws is not None:
-            _retired_workspaces.append(ws)  # a CUDA graph captured earlier may still hold its address
+            # a CUDA graph captured earlier may still hold its address; the buffer at least doubles, so the
+            # retired ones add up to less than the live one
+            _retired_workspaces.append(ws)
+            nbytes = max(nbytes, 2 * ws.numel())
         ws = torch.zeros(max(nbytes, 4 << 20), dtype=torch.uint8, device=device)
         _workspaces[key] = ws
     return ws
@@ -191,8 +198,12 @@ def build_attention_params(
     p.alibi_slopes = alibi_slopes.data_ptr() if alibi_slopes is not None else None
     p.k_scale = k_descale.data_ptr() if k_descale is not None else None
     p.v_scale = v_descale.data_ptr() if v_descale is not None else None
-    if sinks is not None and (sinks.dtype != torch.float32 or sinks.shape[0] != q.shape[1] or not sinks.is_contiguous()):
-        raise ValueError("sinks must be a contiguous float32 tensor with one entry per query head")
+    if sinks is not None:
+        if sinks.shape[0] != q.shape[1]:
+            raise ValueError("Sinks must be num_query_heads size")  # upstream's assertion
+        if sinks.dtype != torch.float32 or not sinks.is_contiguous():
+            sinks = sinks.detach().to(torch.float32).contiguous()  # upstream takes the model dtype; the kernels read fp32
+        p._keep_sinks = sinks  # the struct holds a raw pointer
     p.sinks = sinks.data_ptr() if sinks is not None else None
     p.out_scale = output_scale.data_ptr() if output_scale is not None else None
     if qq_bias is not None:
@@ -247,8 +258,35 @@ def unified_attention(
     sinks: Optional[torch.Tensor] = None,  # [Hq] float32 (upstream keyword)
     output_scale: Optional[torch.Tensor] = None,  # upstream keyword: `out` is e4m3, out = quant(o / output_scale)
     qq_bias: Optional[torch.Tensor] = None,  # upstream keyword: [q, q] fp32 bias between a step's query tokens (SIMT kernel)
-    **_ignored,
+    # Pure tuning inputs of upstream's launcher (vLLM 0.22 vllm/v1/attention/ops/triton_unified_attention.py):
+    # where its split-KV partials live and when it splits.  They do not change the result; this library sizes
+    # and owns its workspace itself, so they are accepted and unused.
+    seq_threshold_3D=None,
+    num_par_softmax_segments=None,
+    softmax_segm_output=None,
+    softmax_segm_max=None,
+    softmax_segm_expsum=None,
+    use_td: bool = False,
+    # Result-changing upstream keywords that are not built here: a non-default value raises instead of
+    # silently computing plain causal attention.
+    mm_prefix_range=None,
+    use_alibi_sqrt: bool = False,
+    kv_quant_mode=None,
+    k_scale_cache=None,
+    v_scale_cache=None,
+    chunk_lookback: int = -1,
 ) -> None:
+    if mm_prefix_range is not None:
+        raise NotImplementedError("b200attn: mm_prefix_range (PrefixLM bidirectional ranges) is not implemented")
+    if use_alibi_sqrt:
+        raise NotImplementedError("b200attn: use_alibi_sqrt is not implemented")
+    if chunk_lookback is not None and int(chunk_lookback) >= 0:
+        raise NotImplementedError("b200attn: chunk_lookback (chunked attention with lookback) is not implemented; "
+                                  "chunked local attention runs through vLLM's virtual batches")
+    if kv_quant_mode is not None and int(getattr(kv_quant_mode, "value", kv_quant_mode)) not in _PER_TENSOR_KV_MODES:
+        raise NotImplementedError(f"b200attn: kv_quant_mode={kv_quant_mode!r} (per-token-head scale caches) is not implemented")
+    if k_scale_cache is not None or v_scale_cache is not None:
+        raise NotImplementedError("b200attn: k_scale_cache / v_scale_cache (per-token-head KV scales) are not implemented")
     if not causal:
         raise AssertionError("Only causal attention is supported")  # reference :861
     if q_descale is not None:
@@ -275,8 +313,9 @@ def unified_attention(
         # decode batches, and the single-token rows of a mixed batch, use the split-KV kernel
         need = workspace_bytes(q.shape[0], seqused_k.shape[0], q.shape[1], k.shape[2], q.shape[2])
         if k.element_size() == 1 and max_seqlen_q > 1:
-            # FP8 prefill: room to stage every sequence at full length (bounded; what does not fit runs mma.sync)
-            tokens = min(seqused_k.shape[0] * int(max_seqlen_k), 1 << 20)
+            # FP8 prefill: room to stage the batch (bounded at 128k tokens - 512 MiB at 8 kv heads, D=128; what does
+            # not fit runs mma.sync).  Callers that care pass their own workspace.
+            tokens = min(seqused_k.shape[0] * int(max_seqlen_k), 1 << 17)
             need += fp8_staging_bytes(seqused_k.shape[0], tokens, v.shape[1], k.shape[2], q.shape[2])
         workspace = get_workspace(q.device, need)
     p = build_attention_params(
