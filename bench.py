@@ -10,10 +10,12 @@ followed by split-KV decode attention (K2 + segment reduce).  The metric is deco
 KV GB/s = algorithmic bytes / device time.
 
 N>1 (torchrun, one rank per GPU): the path shards by KV head with no collective
-(vLLM tensor parallelism); every rank runs one C2-shaped head
-shard ("weak": per-GPU work fixed), `value` is the sum over ranks / max time.
-`--workload c4` runs the 70B-shaped FP8 decode with its 8 KV heads split over the
-ranks instead (strong scaling; used for the profiles/ tables, not by the driver).
+(vLLM tensor parallelism).  The workload is then BASELINE.json's
+multi-GPU configuration, C4: Llama-3.1-70B-shaped decode, 64q/8kv heads, FP8-e4m3
+KV, batch 64, ctx 32k, its 8 KV heads split over the ranks ("strong": total work
+fixed), `value` = total algorithmic bytes / max time over ranks.  One C2-shaped
+replica per rank ("weak", round 1's line) is reported under extras; `--workload`
+overrides either default.
 
 `--impl reference` times the CPU restatement of the reference path (oracle/, the
 reference being Python+Triton has no CPU binary to run on the GPU box) on the
@@ -176,12 +178,12 @@ def make_device_workload(w, hq, hkv, device, seed):
 def _mixed_bounds(m, peaks):
     """A mixed batch has a tensor-bound share (the prompts' FLOPs) and an HBM-bound share (the KV the
     single-token rows stream).  Lower bounds on its time from the two measured peaks: the larger of the two
-    if they overlapped perfectly, their sum when they run one after the other (as here: the tcgen05
-    kernel fills every SM's shared memory, so the decode rows follow it)."""
+    if they overlap perfectly, their sum when they run one after the other."""
     t_flop = m["flops"] / (peaks["bf16_tflops"] * 1e12) * 1e3
     t_byte = m["decode_row_kv_bytes"] / (peaks["hbm_gbs"] * 1e9) * 1e3
     return {"decode_rows": m["decode_rows"], "decode_row_kv_gb": round(m["decode_row_kv_bytes"] / 1e9, 4),
             "bound_ms_overlapped": round(max(t_flop, t_byte), 4), "bound_ms_serial": round(t_flop + t_byte, 4),
+            "frac_of_overlapped_bound": round(max(t_flop, t_byte) / m["ms"], 4),
             "frac_of_serial_bound": round((t_flop + t_byte) / m["ms"], 4)}
 
 
@@ -215,9 +217,169 @@ class _Layer:
         self._q_scale = torch.tensor(1.0, dtype=torch.float32, device=device)
 
 
+class HotPath:
+    """One workload resident in HBM and the calls a step makes through the plugin surface:
+    `B200AttentionImpl.do_kv_cache_update` (K1) then `.forward` (K2), with the step's metadata - including the
+    split-KV work plan the metadata builder computes once per step - in a `B200AttentionMetadata`."""
+
+    def __init__(self, w, hq, hkv, device, seed):
+        from vllm_triton_backend_b200 import ops
+        from vllm_triton_backend_b200.backend.attn import B200AttentionImpl, B200AttentionMetadata
+
+        self.w, self.hq, self.hkv, self.device = w, hq, hkv, device
+        self.fp8 = w["kv"] == "fp8"
+        self.st = st = make_device_workload(w, hq, hkv, device, seed)
+        B, D = w["batch"], w["d"]
+        self.layer = _Layer(device, 0.5 if self.fp8 else 1.0, 0.5 if self.fp8 else 1.0)
+        self.impl = B200AttentionImpl(num_heads=hq, head_size=D, scale=D ** -0.5, num_kv_heads=hkv, alibi_slopes=None,
+                                      sliding_window=None, kv_cache_dtype="fp8" if self.fp8 else "auto")
+        self.workspace = torch.zeros(ops.workspace_bytes(B, B, hq, hkv, D), dtype=torch.uint8, device=device)
+        kv_dtype = torch.float8_e4m3fn if self.fp8 else torch.bfloat16
+        self.new_plan = lambda: ops.DecodePlan(device, B, hq, hkv, D, w["bs"], torch.bfloat16, kv_dtype)
+        self.plan = self.new_plan()
+        self.plan.build(st["cu"], st["seq_lens"], 1)  # what B200AttentionMetadataBuilder.build does every step
+        self.Meta = B200AttentionMetadata
+        self.meta = self.metadata(st["cu"], st["seq_lens"], st["block_table"], st["slot_mapping"], self.plan)
+        self.out = torch.empty(B, hq, D, dtype=torch.bfloat16, device=device)
+        kvb = 1 if self.fp8 else 2
+        self.dec_bytes, self.cw_bytes = algorithmic_bytes(w, hq, hkv, kvb)
+        self.step_bytes = self.dec_bytes + self.cw_bytes
+
+    def metadata(self, cu, seq_lens, block_table, slots, plan):
+        return self.Meta(num_actual_tokens=self.w["batch"], max_query_len=1, query_start_loc=cu, max_seq_len=self.w["ctx"],
+                         seq_lens=seq_lens, block_table=block_table, slot_mapping=slots, workspace=self.workspace,
+                         decode_plan=plan)
+
+    def cache_write(self):
+        st = self.st
+        self.impl.do_kv_cache_update(self.layer, st["k_new"], st["v_new"], st["kv"], st["slot_mapping"])
+
+    def attention(self):
+        st = self.st
+        self.impl.forward(self.layer, st["q"], st["k_new"], st["v_new"], st["kv"], self.meta, output=self.out)
+
+    def step(self):
+        self.cache_write()
+        self.attention()
+
+    def free(self):
+        self.st.clear()
+        self.meta = self.out = self.workspace = None
+        torch.cuda.empty_cache()
+
+
+def time_steps(hp, K, warmup, barrier, stream):
+    """W untimed steps, then exactly K steps between two events on the launching stream; ms total."""
+    for _ in range(warmup):
+        hp.step()
+    barrier()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    ev[0].record(stream)
+    for _ in range(K):
+        hp.step()
+    ev[1].record(stream)
+    barrier()
+    return ev[0].elapsed_time(ev[1])
+
+
+def roofline_pass(hp, launches, stream):
+    """Per-launch duration of the dominant kernel: `launches` attention launches, each bracketed by its own pair of
+    events on the launching stream, in a pass of its own (an event record between two launches serialises them, so
+    doing this inside the timed loop would change what `value` measures)."""
+    for _ in range(5):
+        hp.attention()
+    torch.cuda.synchronize(hp.device)
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(launches)]
+    for a, b in evs:
+        a.record(stream)
+        hp.attention()
+        b.record(stream)
+    torch.cuda.synchronize(hp.device)
+    return [a.elapsed_time(b) for a, b in evs]
+
+
+def e2e_pass(hp, K, warmup, barrier, serial):
+    """The same step through the plugin with HOST buffers: the step's inputs live in one pinned arena
+    (vllm_triton_backend_b200.staging), go to the device with one copy, the split-KV plan is rebuilt from the
+    uploaded metadata (as the builder does each step), and the output comes back with one copy."""
+    from vllm_triton_backend_b200.staging import StepPipeline
+
+    st, w = hp.st, hp.w
+    B, D = w["batch"], w["d"]
+    names = {"q": st["q"], "k": st["k_new"], "v": st["v_new"], "slots": st["slot_mapping"], "bt": st["block_table"],
+             "sl": st["seq_lens"], "cu": st["cu"]}
+    depth = 1 if serial else 2
+    pipe = StepPipeline([(n, tuple(t.shape), t.dtype) for n, t in names.items()], (B, hp.hq, D), torch.bfloat16, hp.device,
+                        depth=depth)
+    plans = {}
+    for slot in pipe.slots:
+        for n, t in names.items():
+            slot.staging.host[n].copy_(t.cpu())
+        plans[id(slot.staging.dev)] = hp.new_plan()
+    h2d = pipe.slots[0].staging.payload_bytes
+    d2h = B * hp.hq * D * 2
+
+    def compute(d, o):
+        plan = plans[id(d)]
+        plan.build(d["cu"], d["sl"], 1)
+        m = hp.metadata(d["cu"], d["sl"], d["bt"], d["slots"], plan)
+        hp.impl.do_kv_cache_update(hp.layer, d["k"], d["v"], st["kv"], d["slots"])
+        hp.impl.forward(hp.layer, d["q"], d["k"], d["v"], st["kv"], m, output=o)
+
+    checksum = 0.0
+
+    def e2e_step():
+        nonlocal checksum
+        slot = pipe.acquire()  # blocks until the result of the step that last used this slot is on the host
+        checksum += float(slot.host_out[0, 0, 0])  # the caller reads every step's result
+        pipe.run(slot, compute)
+
+    for _ in range(warmup):
+        e2e_step()
+    pipe.drain()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(K):
+        e2e_step()
+    pipe.drain()
+    barrier()
+    return (time.perf_counter() - t0) * 1e3, h2d, d2h, depth
+
+
+def same_gpu_comparators(hp, budget_ms=60.0):
+    """The reference's own kernels on the same tensors of the same GPU (tests/triton_reference.py: the reference
+    file from baseline/_ref when build() put it there, else the copy the installed vLLM ships)."""
+    out = {}
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "scripts"))
+        import kbench
+        import triton_reference as tr
+
+        why = tr.available()
+        if why:
+            return {"triton_unified_attention": {"unavailable": why}}
+        st, w = hp.st, hp.w
+        B, D = w["batch"], w["d"]
+        kc, vc = hp.impl._views(st["kv"])
+        sc = hp.layer._k_scale.view(1) if hp.fp8 else None
+        tri = tr.TritonReference(B, hp.hq, D, hp.device)
+        o = torch.empty_like(hp.out)
+
+        def fn():
+            tri(st["q"], kc, vc, o, st["cu"], 1, st["seq_lens"], w["ctx"], D ** -0.5, st["block_table"], k_scale=sc, v_scale=sc)
+        ms, n = kbench.time_fn(fn, min_ms=budget_ms)
+        hp.attention()
+        torch.cuda.synchronize(hp.device)
+        err = float((o.float() - hp.out.float()).abs().max())
+        out["triton_unified_attention"] = {"ms": round(ms, 5), "gbs": round(hp.dec_bytes / ms / 1e6, 1), "iters": n,
+                                           "source": tr.SOURCE, "max_abs_diff_vs_ours": round(err, 5),
+                                           "what": "kernel_unified_attention_3d + reduce_segments, the reference launcher's 16 segments"}
+    except Exception as e:  # a comparator must never take the bench line down
+        out["triton_unified_attention"] = {"unavailable": f"{type(e).__name__}: {str(e)[:160]}"}
+    return out
+
 def run_ours(args):
-    from vllm_triton_backend_b200 import _cabi, ops
-    from vllm_triton_backend_b200.backend.attn import B200AttentionImpl, B200AttentionMetadata
+    from vllm_triton_backend_b200 import _cabi
 
     rank, world, local = dist_env()
     if world != args.gpus:
@@ -229,32 +391,19 @@ def run_ours(args):
         import torch.distributed as dist
 
         dist.init_process_group("nccl", device_id=device)
-    w = WORKLOADS[args.workload]
-    if args.workload == "c4":
+    # N = 1: C2, the configuration BASELINE.json's metric is quoted on.  N > 1: C4, the north_star's multi-GPU
+    # configuration - its 8 KV heads split over the ranks the way vLLM tensor parallelism splits them
+    # (vllm/config/model.py:1348-1363), total work fixed ("strong").  --workload overrides.
+    name = args.workload or ("c2" if world == 1 else "c4")
+    w = WORKLOADS[name]
+    if name == "c4":
         assert w["hkv"] % world == 0
         hq, hkv, scaling = w["hq"] // world, w["hkv"] // world, "strong"
     else:
         hq, hkv, scaling = w["hq"], w["hkv"], "weak"
     fp8 = w["kv"] == "fp8"
-    kv_bytes = 1 if fp8 else 2
-    dec_bytes, cw_bytes = algorithmic_bytes(w, hq, hkv, kv_bytes)
-    step_bytes = dec_bytes + cw_bytes
-    st = make_device_workload(w, hq, hkv, device, seed=rank)
     B, D = w["batch"], w["d"]
-    scale = D ** -0.5
-    layer = _Layer(device, 0.5 if fp8 else 1.0, 0.5 if fp8 else 1.0)
-    impl = B200AttentionImpl(num_heads=hq, head_size=D, scale=scale, num_kv_heads=hkv, alibi_slopes=None,
-                             sliding_window=None, kv_cache_dtype="fp8" if fp8 else "auto")
-    workspace = torch.zeros(ops.workspace_bytes(B, B, hq, hkv, D), dtype=torch.uint8, device=device)
-    meta = B200AttentionMetadata(num_actual_tokens=B, max_query_len=1, query_start_loc=st["cu"], max_seq_len=w["ctx"],
-                                 seq_lens=st["seq_lens"], block_table=st["block_table"], slot_mapping=st["slot_mapping"],
-                                 workspace=workspace)
-    out = torch.empty(B, hq, D, dtype=torch.bfloat16, device=device)
     stream = torch.cuda.current_stream(device)
-
-    def step():
-        impl.do_kv_cache_update(layer, st["k_new"], st["v_new"], st["kv"], st["slot_mapping"])
-        impl.forward(layer, st["q"], st["k_new"], st["v_new"], st["kv"], meta, output=out)
 
     def barrier():
         if world > 1:
@@ -263,133 +412,120 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize(device)
 
-    # ---- device-resident timing (value) -----------------------------------------
-    for _ in range(max(args.warmup, 3)):
-        step()
+    hp = HotPath(w, hq, hkv, device, seed=rank)
+    W = max(args.warmup, 3)
+    K = args.steps
+
+    # ---- device-resident timing (value): nothing but the step's launches between the two events -----------
+    for _ in range(W):
+        hp.step()
     barrier()
     sampler = ClockSampler(local)
     sampler.start()
     time.sleep(0.25)
-    K = args.steps
-    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
-    # per-launch duration of the dominant kernel (decode + its reduce), inside the timed region, on every
-    # EVENT_EVERY-th step: an event record between the cache write and the attention launch serialises the
-    # two (it defeats the programmatic dependent launch that otherwise overlaps the decode kernel's launch
-    # and prologue with the cache write), so bracketing every step would change what `value` measures.
-    EVENT_EVERY = 4
-    att_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
-              for _ in range((K + EVENT_EVERY - 1) // EVENT_EVERY)]
     _cabi.reset_launch_count()
     t_begin = sampler.mark()
-    ev[0].record(stream)
-    for i in range(K):
-        impl.do_kv_cache_update(layer, st["k_new"], st["v_new"], st["kv"], st["slot_mapping"])
-        if i % EVENT_EVERY:
-            impl.forward(layer, st["q"], st["k_new"], st["v_new"], st["kv"], meta, output=out)
-            continue
-        att_ev[i // EVENT_EVERY][0].record(stream)
-        impl.forward(layer, st["q"], st["k_new"], st["v_new"], st["kv"], meta, output=out)
-        att_ev[i // EVENT_EVERY][1].record(stream)
-    ev[1].record(stream)
-    barrier()
+    total_ms = time_steps(hp, K, 0, barrier, stream)
     t_end = sampler.mark()
     launches = _cabi.launch_count()
     dominant = _cabi.last_kernel()
-    total_ms = ev[0].elapsed_time(ev[1])
-    att_ms = [a.elapsed_time(b) for a, b in att_ev]
 
-    # ---- end to end through the plugin with HOST buffers (e2e) --------------------
-    # The step's host inputs live in one pinned arena (vllm_triton_backend_b200.staging) and go
-    # to the device with a single copy; the output comes back with one copy.
-    from vllm_triton_backend_b200.staging import StepPipeline
+    # ---- roofline of the dominant kernel: its own pass, every launch bracketed -----------------------------
+    att_ms = roofline_pass(hp, max(32, args.roofline_launches), stream)
 
-    names = {"q": st["q"], "k": st["k_new"], "v": st["v_new"], "slots": st["slot_mapping"], "bt": st["block_table"],
-             "sl": st["seq_lens"], "cu": st["cu"]}
-    depth = 1 if args.e2e_serial else 2
-    pipe = StepPipeline([(n, tuple(t.shape), t.dtype) for n, t in names.items()], (B, hq, D), torch.bfloat16, device,
-                        depth=depth)
-    for slot in pipe.slots:
-        for n, t in names.items():
-            slot.staging.host[n].copy_(t.cpu())
-    h2d = pipe.slots[0].staging.payload_bytes
-    d2h = B * hq * D * 2
-
-    def compute(d, o):
-        m = B200AttentionMetadata(num_actual_tokens=B, max_query_len=1, query_start_loc=d["cu"], max_seq_len=w["ctx"],
-                                  seq_lens=d["sl"], block_table=d["bt"], slot_mapping=d["slots"], workspace=workspace)
-        impl.do_kv_cache_update(layer, d["k"], d["v"], st["kv"], d["slots"])
-        impl.forward(layer, d["q"], d["k"], d["v"], st["kv"], m, output=o)
-
-    checksum = 0.0
-
-    def e2e_step():
-        nonlocal checksum
-        slot = pipe.acquire()  # blocks until the result of the step that last used this slot is on the host
-        checksum += float(slot.host_out[0, 0, 0])  # the caller reads every step's result
-        pipe.run(slot, compute)
-
-    for _ in range(max(args.warmup, 3)):
-        e2e_step()
-    pipe.drain()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(K):
-        e2e_step()
-    pipe.drain()
-    barrier()
-    e2e_s = time.perf_counter() - t0
+    # ---- end to end through the plugin with HOST buffers (e2e) ---------------------------------------------
+    e2e_ms, h2d, d2h, depth = e2e_pass(hp, K, W, barrier, args.e2e_serial)
     clocks = sampler.stop(t_begin, t_end)
+
+    # ---- context (rank 0): the reference's kernels on the same tensors; the other decode configuration -------
+    comparators = None
+    if rank == 0 and not args.no_comparators:
+        comparators = same_gpu_comparators(hp)
+    dec_bytes, step_bytes = hp.dec_bytes, hp.step_bytes
+    hp.free()
+    del hp
+    other = {}
+    if not args.no_extras:
+        # N = 1: the C4 decode on this one GPU (all 8 KV heads) and its 8-GPU shard shape (1 KV head) - the strong-
+        # scaling reference points.  N > 1: one C2-shaped replica per rank (round 1's "weak" number).
+        todo = [("c4", WORKLOADS["c4"]["hq"], WORKLOADS["c4"]["hkv"]), ("c4", 8, 1)] if world == 1 and name == "c2" else \
+               ([("c2", WORKLOADS["c2"]["hq"], WORKLOADS["c2"]["hkv"])] if name == "c4" else [])
+        for wl, ohq, ohkv in todo:
+            o = HotPath(WORKLOADS[wl], ohq, ohkv, device, seed=rank)
+            k2 = max(20, min(K, 200))
+            ms = time_steps(o, k2, W, barrier, stream) / k2
+            t = torch.tensor([ms], dtype=torch.float64, device=device)
+            if world > 1:
+                import torch.distributed as dist
+
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.cpu())
+            mult = world if wl == "c2" else 1
+            other[f"{wl}_{ohq}q{ohkv}kv_per_gpu"] = {
+                "ms_per_step": round(ms, 5), "gbs": round(mult * o.step_bytes / ms / 1e6, 1), "n_gpus": world,
+                "what": ("one replica per rank, sum over ranks" if wl == "c2" else
+                         ("every KV head on one GPU" if ohkv == 8 else "the shard one of 8 GPUs holds (1 KV head)"))}
+            o.free()
+            del o
 
     pre = None
     if not args.no_prefill:
-        del st["kv"]
         torch.cuda.empty_cache()
         pre = measure_prefill(device, world)
 
-    # ---- reduce over ranks --------------------------------------------------------
-    stats = torch.tensor([total_ms, e2e_s * 1e3, statistics.mean(att_ms)], dtype=torch.float64, device=device)
+    # ---- reduce over ranks ------------------------------------------------------------------------------------
+    att_sorted = sorted(att_ms)
+    att_med = att_sorted[len(att_sorted) // 2]
+    stats = torch.tensor([total_ms, e2e_ms, att_med], dtype=torch.float64, device=device)
     if world > 1:
         import torch.distributed as dist
 
         dist.all_reduce(stats, op=dist.ReduceOp.MAX)
-    total_ms, e2e_ms, att_mean_ms = (float(x) for x in stats.cpu())
+    total_ms, e2e_ms, att_med = (float(x) for x in stats.cpu())
 
-    # ---- CPU baseline (rank 0, N=1 only) --------------------------------------------
+    # ---- CPU baseline (rank 0, N=1 only) ------------------------------------------------------------------------
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cpu_baseline = run_cpu_reference(w, hq, hkv, budget_s=args.cpu_seconds, seed=0, state=st)
+        cpu_baseline = run_cpu_reference(w, hq, hkv, budget_s=args.cpu_seconds, seed=0)
 
     if rank == 0:
         peaks = measured_peaks()
         ms_per_step = total_ms / K
         gbs = world * step_bytes / (ms_per_step * 1e-3) / 1e9
         e2e_gbs = world * step_bytes / (e2e_ms / K * 1e-3) / 1e9
-        achieved = dec_bytes / (att_mean_ms * 1e-3) / 1e9
+        achieved = dec_bytes / (att_med * 1e-3) / 1e9
+        p20, p50, p80 = _percentiles(att_ms, (20, 50, 80))
         line = {
             "metric": "decode_kv_gbps", "value": round(gbs, 2), "unit": "GB/s", "n_gpus": world, "steps": K,
-            "warmup": max(args.warmup, 3), "ms_per_step": round(ms_per_step, 5), "higher_is_better": True,
+            "warmup": W, "ms_per_step": round(ms_per_step, 5), "higher_is_better": True,
             "scaling": scaling, "vs_baseline": None, "dtype": "bf16" if not fp8 else "bf16 (fp8-e4m3 KV)",
             "data": "synthetic",
             "config": {"workload": w["desc"], "batch": B, "ctx": w["ctx"], "q_heads_per_gpu": hq, "kv_heads_per_gpu": hkv,
                        "head_dim": D, "block_size": w["bs"], "kv_cache_dtype": w["kv"],
-                       "step": "reshape_and_cache_flash(64 new tokens) + decode attention (split-KV, fused merge)",
+                       "step": "reshape_and_cache_flash(64 new tokens) + decode attention (split-KV, fused merge); the split-KV "
+                               "work plan is built once per step's metadata, as the metadata builder does for all layers",
                        "l2": f"KV working set {dec_bytes / 1e9:.2f} GB per GPU >> 126 MB L2; no flush needed",
                        "parallelism": f"kv-head shard x{world} (no collective)"},
             "clocks": clocks,
             "e2e": {"value": round(e2e_gbs, 2), "unit": "GB/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": round(e2e_ms / K, 5),
-                    "api": "StepPipeline(depth=%d): one pinned arena per step (q/k/v/metadata) uploaded on a copy stream, B200AttentionImpl.do_kv_cache_update + .forward, result read back on a second copy stream; the host reads every step's result when it reuses the slot" % depth},
+                    "api": "StepPipeline(depth=%d): one pinned arena per step (q/k/v/metadata) uploaded on a copy stream, ops.DecodePlan.build + B200AttentionImpl.do_kv_cache_update + .forward, result read back on a second copy stream; the host reads every step's result when it reuses the slot" % depth},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": round(achieved, 2), "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                         "frac": round(achieved / peaks["hbm_gbs"], 4), "traffic": args.ncu_traffic if args.ncu_traffic is not None else (committed_ncu_traffic() if args.workload == "c2" else None),
+                         "frac": round(achieved / peaks["hbm_gbs"], 4),
+                         "traffic": args.ncu_traffic if args.ncu_traffic is not None else (committed_ncu_traffic() if name == "c2" else None),
                          "kernel": "attn_decode_kernel (split-KV, merge of partials fused in)", "peak_source": peaks["source"],
                          "frac_of_nominal_8TBs": round(achieved / 8000.0, 4), "algorithmic_bytes_per_launch": dec_bytes,
-                         "avg_launch_ms": round(att_mean_ms, 5), "launches_timed": len(att_ms),
-                         "timing": "CUDA events on the launching stream around every 4th attention launch of the timed region"},
-            "extras": {"decode_launch_ms_p20_p50_p80": [round(x, 5) for x in _percentiles(att_ms, (20, 50, 80))],
-                       "decode_tokens_per_s": round(world * B / (ms_per_step * 1e-3), 1),
-                       "e2e_tokens_per_s": round(world * B / (e2e_ms / K * 1e-3), 1), "last_kernel": dominant},
+                         "avg_launch_ms": round(att_med, 5), "launch_ms_p20_p50_p80": [round(p20, 5), round(p50, 5), round(p80, 5)],
+                         "launch_ms_mean": round(statistics.mean(att_ms), 5), "launches_timed": len(att_ms),
+                         "timing": "median of CUDA-event pairs on the launching stream around every attention launch of a "
+                                   "separate pass (max over ranks); the timed region of `value` carries no events"},
+            "extras": {"decode_tokens_per_s": round(world * B / (ms_per_step * 1e-3), 1),
+                       "e2e_tokens_per_s": round(world * B / (e2e_ms / K * 1e-3), 1), "last_kernel": dominant,
+                       "other_decode_configs": other},
         }
+        if comparators is not None:
+            line["same_gpu_comparators"] = comparators
         if pre is not None:
             # per-rank numbers of rank 0 (every rank runs the same shapes); whole-job = x world
             line["prefill"] = {
@@ -401,6 +537,11 @@ def run_ours(args):
                                              "frac": round(pre["mixed"]["tflops"] / peaks["bf16_tflops"], 4),
                                              "tokens_per_s": round(world * pre["mixed"]["tokens"] / pre["mixed"]["ms"] * 1e3, 1),
                                              **_mixed_bounds(pre["mixed"], peaks)},
+                "roofline": {"bound": "tensor", "achieved": round(pre["full8k"]["tflops"], 1), "peak": peaks["bf16_tflops"],
+                             "unit": "TFLOP/s", "frac": round(pre["full8k"]["tflops"] / peaks["bf16_tflops"], 4),
+                             "kernel": "attn_prefill_tc_kernel", "algorithmic_flops_per_launch": pre["full8k"]["flops"],
+                             "avg_launch_ms": round(pre["full8k"]["ms"], 5), "traffic": None,
+                             "ncu": "profiles/: sm__pipe_tensor* of the committed --set full capture of this kernel"},
                 "kernel": "attn_prefill_tc_kernel (tcgen05/TMEM) + short/decode rows via attn_prefill_kernel / attn_decode_kernel",
             }
         if cpu_baseline is not None:
@@ -420,9 +561,11 @@ def run_cpu_reference(w, hq, hkv, budget_s, seed, state=None):
     from oracle.paged_attention import unified_attention_ref
     from vllm_triton_backend_b200.roofline import decode_bytes
 
+    # torchrun exports OMP_NUM_THREADS=1 to its workers: a CPU arm timed that way is a 1-thread arm
+    torch.set_num_threads(max(1, os.cpu_count() or 1))
     B, ctx, D, bs = w["batch"], w["ctx"], w["d"], w["bs"]
     fp8 = w["kv"] == "fp8"
-    sample_b = min(B, 8)  # sequences per CPU pass
+    sample_b = min(B, 8 if ctx <= 8192 else 2)  # sequences per CPU pass
     pages = ctx // bs
     g = torch.Generator().manual_seed(seed)
     NB = sample_b * pages + 8
@@ -462,10 +605,41 @@ def run_cpu_reference(w, hq, hkv, budget_s, seed, state=None):
             "tokens_per_s": round(n * sample_b / el, 2)}
 
 
+def run_triton_interpret_c1(timeout_s=150):
+    """SURVEY.md 8(d)'s other CPU row: the reference's own Triton kernels under TRITON_INTERPRET=1 on C1 (batch 4,
+    32q/8kv, D=128, ctx 512, block 16, fp32), one call, in a subprocess (the interpreter is chosen when triton is
+    imported).  Needs the reference kernel file: /root/reference here, baseline/_ref (put there by build()) on
+    the GPU box."""
+    code = (
+        "import os,sys,time,json,torch\n"
+        "sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+        "from oracle import reference_runner as rr\n"
+        "from helpers import make_paged_inputs\n"
+        "if not rr.reference_available(): print(json.dumps({'unavailable': 'reference kernel file not present'})); sys.exit(0)\n"
+        "mod = rr.load_reference_kernels(16, 32)\n"
+        "inp = make_paged_inputs([(1,512)]*4, 32, 8, 128, 16, dtype=torch.float32, seed=0)\n"
+        "out = torch.empty_like(inp['q'])\n"
+        "one = torch.ones(1)\n"
+        "t0 = time.perf_counter()\n"
+        "mod.unified_attention(q=inp['q'], k=inp['k_cache'], v=inp['v_cache'], out=out, cu_seqlens_q=inp['cu_seqlens_q'], max_seqlen_q=1, seqused_k=inp['seq_lens'], max_seqlen_k=512, avg_seqlen_q=1, avg_seqlen_k=512, softmax_scale=128**-0.5, causal=True, window_size=(-1,-1), block_table=inp['block_table'], softcap=0, q_descale=None, k_descale=one, v_descale=one)\n"
+        "el = time.perf_counter() - t0\n"
+        "print(json.dumps({'seconds_per_call': round(el, 3), 'decode_tokens_per_s': round(4 / el, 4), 'cores': os.cpu_count(), 'config': 'C1: batch 4, 32q/8kv, D=128, ctx 512, block 16, fp32', 'kernels': 'kernel_unified_attention_3d + reduce_segments of the reference file, Triton CPU interpreter'}))\n"
+    ) % (ROOT, os.path.join(ROOT, "tests"))
+    env = dict(os.environ, TRITON_INTERPRET="1", CUDA_VISIBLE_DEVICES="")
+    env.pop("OMP_NUM_THREADS", None)
+    try:
+        r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=timeout_s, cwd="/tmp")
+        lines = [l for l in r.stdout.splitlines() if l.startswith("{")]
+        return json.loads(lines[-1]) if lines else {"unavailable": (r.stderr or "no output")[-200:]}
+    except Exception as e:
+        return {"unavailable": f"{type(e).__name__}: {str(e)[:160]}"}
+
+
 def run_reference_arm(args):
     rank, world, local = dist_env()
     if rank != 0:
         return
+    args.workload = args.workload or ("c2" if world <= 1 else "c4")
     w = WORKLOADS[args.workload]
     hq, hkv = w["hq"], w["hkv"]
     if args.workload == "c4":
@@ -498,6 +672,8 @@ def run_reference_arm(args):
         "cpu_baseline": cb,
         "e2e": {"value": round(v, 4), "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
+    if not args.no_extras:
+        line["cpu_baseline"]["triton_interpret_c1"] = run_triton_interpret_c1()
     print(json.dumps(line), flush=True)
 
 
@@ -522,7 +698,11 @@ def main():
     ap.add_argument("--steps", type=int, default=1000)
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS),
+                    help="default: c2 at --gpus 1, c4 (KV heads sharded over the ranks, strong scaling) at --gpus > 1")
+    ap.add_argument("--roofline-launches", type=int, default=64, help="bracketed attention launches of the roofline pass (>= 32)")
+    ap.add_argument("--no-comparators", action="store_true", help="skip the same-GPU Triton reference timing")
+    ap.add_argument("--no-extras", action="store_true", help="skip the other decode configuration (C4 at N=1, C2 replicas at N>1)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-serial", action="store_true", help="e2e without overlap: upload, compute, read back, sync, every step")

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 3
+#define B200ATTN_ABI_VERSION 4
 
 #if defined(__GNUC__)
 #define B200ATTN_API __attribute__((visibility("default")))
@@ -148,6 +148,11 @@ typedef struct b200attn_attention_params {
                                   S[query i of a sequence][key j] += qq_bias[i][j - context_len] for
                                   0 <= j - context_len < qq_bias_stride0.  Served by the SIMT kernel only.   */
   int64_t qq_bias_stride0;
+  const void* decode_plan;     /* NULL, or a plan written by b200attn_decode_plan for THIS step's seq_lens /
+                                  cu_seqlens_q (all layers of a step share it; the metadata builder makes it once).
+                                  Without one the split-KV launch plans for itself (one more small launch).   */
+  uint64_t decode_plan_key;    /* the key b200attn_decode_plan returned; a plan whose key does not match the
+                                  launch's own geometry (other head counts, window, ...) is ignored            */
 } b200attn_attention_params;
 
 /* Bytes of workspace b200attn_unified_attention may need for this shape
@@ -159,6 +164,20 @@ B200ATTN_API uint64_t b200attn_workspace_bytes(int32_t num_tokens, int32_t num_s
 
 B200ATTN_API int b200attn_unified_attention(const b200attn_attention_params* p,
                                b200attn_stream_t stream);
+
+/* Work plan of the split-KV decode launches of one step.  The reference cuts every sequence into 16 fixed
+ * segments on the host side of the launch (triton_unified_attention.py:931-948); here the (sequence, kv-head
+ * group, KV step) space is cut on the device from seq_lens: one static range per CTA plus a pool of chunks
+ * the CTAs share (csrc/attn_decode.cu).  That cut depends on seq_lens / cu_seqlens_q only, not on the layer,
+ * so the metadata builder computes it once per step (replaces nothing in the reference: its builder computes
+ * nothing of the kind, triton_attn.py:130-227) and passes it in `decode_plan`.
+ *   p:          the step's parameters (seq_lens, cu_seqlens_q, num_seqs, head counts, head_size, block_size,
+ *               dtypes, sliding_window, max_seqlen_q; data pointers other than the two metadata arrays unused)
+ *   plan:       device buffer of b200attn_decode_plan_bytes(num_seqs) bytes, 16-byte aligned, caller-owned
+ *   key_out:    host: the key to put in decode_plan_key; 0 = this shape does not use the split-KV kernel */
+B200ATTN_API uint64_t b200attn_decode_plan_bytes(int32_t num_seqs);
+B200ATTN_API int b200attn_decode_plan(const b200attn_attention_params* p, void* plan, uint64_t plan_bytes,
+                                      uint64_t* key_out_host, b200attn_stream_t stream);
 
 /* ---- K4 (optional): static per-tensor FP8 quantisation of Q ----------------
  * Replaces ops.scaled_fp8_quant(query, layer._q_scale) at triton_attn.py:417
@@ -220,11 +239,11 @@ B200ATTN_API void b200attn_reset_launch_count(void);
 B200ATTN_API const char* b200attn_last_kernel(void);
 /* Tuning knobs (process-wide; 0 = library default).  Used by the benchmark
  * sweeps; not needed for correctness. */
-B200ATTN_API void b200attn_set_tuning(int32_t decode_heads_per_cta, int32_t decode_ctas_per_sm,
+B200ATTN_API void b200attn_set_tuning(int32_t decode_heads_per_cta, int32_t decode_pool_sixteenths,
                          int32_t decode_stages, int32_t reserved);
 
 /* Debug: when `device_buffer` is not NULL the split-KV decode kernel writes 8 uint64
- * per CTA (globaltimer at entry, then %clock64 at: entry, partition done, first KV
+ * per CTA (globaltimer at entry, then %clock64 at: entry, first run known, first KV
  * stage landed, last stage consumed, exit; globaltimer at exit; items finalised).
  * Process-wide; NULL switches it off.  Used by scripts/kbench.py decode --trace. */
 B200ATTN_API void b200attn_debug_set_decode_trace(void* device_buffer);

@@ -39,6 +39,19 @@ def quantize_e4m3_torch(x: torch.Tensor, scale: float) -> torch.Tensor:
     return torch.where(nan, torch.full_like(bits, 0x7F), bits)
 
 
+def scaled_fp8_quant_ref(x: torch.Tensor, scale: float) -> torch.Tensor:
+    """Static per-tensor quantisation of the query (`ops.scaled_fp8_quant(query, layer._q_scale)`, reference
+    ibm-triton-lib/ibm_triton_lib/backend/triton_attn.py:417): vllm/csrc/quantization/w8a8/fp8/common.cu:11-29 calls
+    `scaled_fp8_conversion<true>(val, 1 / *scale)` (common.cuh:40-60) - a MULTIPLICATION by the fp32 reciprocal (not the
+    division of the cache write), `fmaxf(-448, fminf(x, 448))` (so NaN becomes +448: fminf returns the number), then
+    the round-to-nearest-even e4m3 conversion.  Returns uint8 bit patterns."""
+    inv = torch.tensor(1.0, dtype=torch.float32) / torch.tensor(scale, dtype=torch.float32)
+    y = x.to(torch.float32) * inv
+    hi, lo = torch.tensor(448.0), torch.tensor(-448.0)
+    y = torch.fmax(lo, torch.fmin(y, hi))  # fmin/fmax ignore a NaN operand, like fminf/fmaxf
+    return y.to(_FP8).view(torch.uint8)
+
+
 def load_c_lib() -> Optional[ctypes.CDLL]:
     if not os.path.exists(_C_LIB_PATH):
         return None

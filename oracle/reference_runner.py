@@ -19,9 +19,15 @@ import sys
 import types
 
 REFERENCE_ROOT = os.environ.get("B200ATTN_REFERENCE_ROOT", "/root/reference")
+_REPO_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+# The GPU box has no /root/reference.  __graft_entry__.build() puts a copy of this ONE file into the git-ignored
+# baseline/_ref/ (which travels with gpurun), so the reference's own kernels - not a sibling copy - run there too.
+REF_COPY = os.path.join(_REPO_ROOT, "baseline", "_ref", "triton_unified_attention.py")
 _KERNEL_FILE = os.path.join(
     REFERENCE_ROOT, "ibm-triton-lib", "ibm_triton_lib", "kernels", "triton_unified_attention.py"
 )
+if not os.path.isfile(_KERNEL_FILE) and os.path.isfile(REF_COPY):
+    _KERNEL_FILE = REF_COPY
 
 
 def reference_available() -> bool:
@@ -68,12 +74,12 @@ def _install_dejavu_stub(block_m: int, block_n: int) -> None:
 _MOD = None
 
 
-def load_reference_kernels(block_m: int = 16, block_n: int = 32):
-    """Returns the reference module (with `.unified_attention`)."""
+def load_reference_kernels(block_m: int = 16, block_n: int = 32, interpret: bool = True):
+    """Returns the reference module (with `.unified_attention`).  `interpret=False`: compiled for the GPU in hand."""
     global _MOD
     if not reference_available():
         raise FileNotFoundError(_KERNEL_FILE)
-    if os.environ.get("TRITON_INTERPRET") != "1":
+    if interpret and os.environ.get("TRITON_INTERPRET") != "1":
         raise RuntimeError("set TRITON_INTERPRET=1 before importing triton (CPU interpreter)")
     _install_dejavu_stub(block_m, block_n)
     if _MOD is None:

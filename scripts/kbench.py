@@ -166,18 +166,25 @@ def decode_case(args, device):
     ws = torch.zeros(ops.workspace_bytes(B, B, hq, hkv, D), dtype=torch.uint8, device=device)
     sc = torch.tensor([0.5], dtype=torch.float32, device=device) if fp8 else None
     nbytes = decode_bytes(lens, hq, hkv, D, bs, 1 if fp8 else 2)
+    plan = None
+    if getattr(args, "plan", False):
+        # what the metadata builder does once per step: the split-KV work plan, shared by every layer's launch
+        _cabi.set_tuning(args.hpc, args.ctas, args.stages, args.split)
+        plan = ops.DecodePlan(device, B, hq, hkv, D, bs, torch.bfloat16, torch.float8_e4m3fn if fp8 else torch.bfloat16)
+        plan.build(cu, sl, 1)
 
     def fn():
         ops.unified_attention(q=q, k=kc, v=vc, out=out, cu_seqlens_q=cu, max_seqlen_q=1, seqused_k=sl,
                               max_seqlen_k=max(lens), softmax_scale=D ** -0.5, causal=True, window_size=(-1, -1),
                               block_table=bt, softcap=0, q_descale=None, k_descale=sc, v_descale=sc, workspace=ws,
-                              force_selection=args.force)
+                              force_selection=args.force, decode_plan=plan)
     if getattr(args, "impl", "ours") == "triton":
         tri = triton_reference().TritonReference(B, hq, D, device)
 
         def fn():  # noqa: F811 - the reference kernels on the same tensors
             tri(q, kc, vc, out, cu, 1, sl, max(lens), D ** -0.5, bt, k_scale=sc, v_scale=sc, use_3d=args.force != 2)
-    return fn, nbytes, dict(B=B, ctx=ctx, hq=hq, hkv=hkv, D=D, bs=bs, fp8=fp8, workload=args.workload, layout=args.layout)
+    return fn, nbytes, dict(B=B, ctx=ctx, hq=hq, hkv=hkv, D=D, bs=bs, fp8=fp8, workload=args.workload, layout=args.layout,
+                            plan=plan is not None)
 
 
 def decode_trace(fn, device):
@@ -201,10 +208,10 @@ def decode_trace(fn, device):
     def stat(x):
         return dict(mean=round(float(x.mean()), 2), min=round(float(x.min()), 2), max=round(float(x.max()), 2))
     return dict(kind="decode_trace", ctas=int(t.shape[0]), kernel_span_us=round(span_ns / 1e3, 2), sm_ghz=round(ghz, 3),
-                start_skew_us=stat((t[:, 0] - t[:, 0].min()) / 1e3), partition_us=stat(us(t[:, 2] - t[:, 1])),
+                start_skew_us=stat((t[:, 0] - t[:, 0].min()) / 1e3), first_run_us=stat(us(t[:, 2] - t[:, 1])),
                 first_data_us=stat(us(t[:, 3] - t[:, 2])), streaming_us=stat(us(t[:, 4] - t[:, 3])),
                 tail_us=stat(us(t[:, 5] - t[:, 4])), cta_total_us=stat((t[:, 6] - t[:, 0]) / 1e3),
-                end_skew_us=stat((t[:, 6].max() - t[:, 6]) / 1e3), items_per_cta=stat(t[:, 7]))
+                end_skew_us=stat((t[:, 6].max() - t[:, 6]) / 1e3), runs_per_cta=stat(t[:, 7]))
 
 
 def run_decode(args, device):
@@ -344,7 +351,9 @@ def main():
     ap.add_argument("--workload", default="c2")
     ap.add_argument("--shape", default="full8k", choices=sorted(PREFILL_SHAPES))
     ap.add_argument("--hpc", type=int, default=0)
-    ap.add_argument("--ctas", type=int, default=0)
+    ap.add_argument("--ctas", "--pool", dest="ctas", type=int, default=0,
+                    help="decode: share of a CTA's steps that goes to the dynamic pool, in 1/16 (0 = default 3, 100 = none)")
+    ap.add_argument("--plan", action="store_true", help="decode: build the split-KV plan once (as the metadata builder does)")
     ap.add_argument("--stages", type=int, default=0)
     ap.add_argument("--split", type=int, default=0)
     ap.add_argument("--hq", type=int, default=0)

@@ -107,3 +107,58 @@ def make_paged_inputs(
         if interleaved:
             out["k_cache"], out["v_cache"] = out["kv"].unbind(1)
     return out
+
+
+def device_attention_reference(q, k_cache, v_cache, cu_seqlens_q, seq_lens, block_table, softmax_scale, k_scale=1.0,
+                               v_scale=1.0, sliding_window=0, softcap=0.0, rows=None):
+    """fp32 torch reference evaluated ON THE DEVICE the tensors live on: the same arithmetic, statement by statement,
+    as oracle/paged_attention.py:unified_attention_ref (reference kernel_unified_attention_2d, triton_unified_attention.py
+    :400-511: fp8 -> fp32 * scale -> query dtype, scale after the dot, softcap before the mask, causal/context + window
+    mask, fp32 softmax, acc / L) - for BASELINE.json's full sizes, where the CPU oracle stays the arbiter on a sample
+    of sequences (tests/test_gpu_full_size_numeric.py checks this function against it there).
+    `rows`: iterable of sequence indices to evaluate (default all); other rows of the result are NaN."""
+    T, Hq, D = q.shape
+    Hkv, bs = k_cache.shape[2], k_cache.shape[1]
+    g = Hq // Hkv
+    cu = [int(x) for x in cu_seqlens_q.tolist()]
+    sl = [int(x) for x in seq_lens.tolist()]
+    out = torch.full((T, Hq, D), float("nan"), dtype=torch.float32, device=q.device)
+    fp8 = k_cache.dtype == torch.float8_e4m3fn
+    torch.backends.cuda.matmul.allow_tf32 = False  # a true fp32 reference
+    torch.set_float32_matmul_precision("highest")
+
+    def rows_of(cache, b, n, scale):
+        idx = block_table[b, : (n + bs - 1) // bs].long()
+        r = cache[idx].reshape(-1, Hkv, D)[:n]
+        if fp8:
+            return (r.to(torch.float32) * scale).to(q.dtype).to(torch.float32)
+        return r.to(torch.float32)
+
+    for b in (range(len(sl)) if rows is None else rows):
+        q0, q1 = cu[b], cu[b + 1]
+        ql, kl = q1 - q0, sl[b]
+        if ql == 0:
+            continue
+        if kl == 0:
+            out[q0:q1] = 0
+            continue
+        ctx = kl - ql
+        k, v = rows_of(k_cache, b, kl, k_scale), rows_of(v_cache, b, kl, v_scale)  # [kv, Hkv, D]
+        qb = q[q0:q1].to(torch.float32).view(ql, Hkv, g, D)
+        s = softmax_scale * torch.einsum("qhgd,khd->hgqk", qb, k)
+        if softcap > 0:
+            s = softcap * torch.tanh(s / softcap)
+        qpos = torch.arange(ql, device=q.device).view(1, 1, ql, 1)
+        kpos = torch.arange(kl, device=q.device).view(1, 1, 1, kl)
+        vis = kpos < ctx + qpos + 1
+        if sliding_window > 0:
+            vis = vis & ((ctx + qpos - kpos) < sliding_window)
+        s = s.masked_fill(~vis, float("-inf"))
+        m = s.max(dim=-1, keepdim=True).values
+        m = torch.where(m > float("-inf"), m, torch.zeros_like(m))
+        p = torch.exp(s - m)
+        l = p.sum(dim=-1, keepdim=True)
+        o = torch.einsum("hgqk,khd->qhgd", p, v) / l.permute(2, 0, 1, 3)
+        out[q0:q1] = o.reshape(ql, Hq, D)
+        del s, p, k, v
+    return out

@@ -339,7 +339,7 @@ def test_mixed_batch_is_routed_across_three_kernels():
     scale = 128 ** -0.5
     _cabi.reset_launch_count()
     out, kern = _run(inp, scale, DECODE_OR_AUTO)
-    assert _cabi.launch_count() == 3 and kern.startswith("attn_decode_split_kv")
+    assert _cabi.launch_count() == 4 and kern.startswith("attn_decode_split_kv")  # tcgen05, mma.sync, split-KV plan, decode
     assert not torch.isnan(out).any()
     assert_close(out, _oracle(inp, scale), atol=BF16_ATOL, rtol=BF16_RTOL, what="mixed routing")
 
@@ -537,7 +537,7 @@ def _fp8_prefill(lens, ws_tokens, scales=(0.37, 0.61), Hq=32, Hkv=8, tune=0):
 def test_fp8_prefill_is_staged_for_the_tcgen05_kernel():
     lens = [(300, 300), (1, 555), (64, 1064), (5, 40), (513, 2049)]
     out, ref, launches = _fp8_prefill(lens, ws_tokens=4096)
-    assert launches == 5  # plan, dequant, tcgen05, mma.sync (short extend), decode row
+    assert launches == 6  # stage plan, dequant, tcgen05, mma.sync (short extend), split-KV plan, decode row
     assert_close(out, ref, atol=FP8_ATOL, rtol=BF16_RTOL, what="fp8 prefill, staged")
     # the staged values are exactly what the reference forms on the fly, so bf16-level agreement holds too
     assert_close(out, ref, atol=BF16_ATOL, rtol=BF16_RTOL, what="fp8 prefill, staged (bf16 tolerance)")
@@ -549,7 +549,7 @@ def test_fp8_prefill_partial_staging_falls_back_per_sequence():
     part, _, launches = _fp8_prefill(lens, ws_tokens=1500)   # room for the first two sequences only
     none, _, n0 = _fp8_prefill(lens, ws_tokens=0)             # no pool: mma.sync kernel for all
     off, _, n1 = _fp8_prefill(lens, ws_tokens=8192, tune=256)  # switched off by the tuning word
-    assert launches == 5 and n0 == n1 == 2  # plan, dequant, tcgen05, mma.sync, decode  |  mma.sync, decode
+    assert launches == 6 and n0 == n1 == 3  # stage plan, dequant, tcgen05, mma.sync, split-KV plan, decode  |  mma.sync, plan, decode
     for name, o in (("full", full), ("partial", part), ("no pool", none), ("off", off)):
         assert_close(o, ref, atol=FP8_ATOL, rtol=BF16_RTOL, what=f"fp8 prefill ({name})")
         assert not torch.isnan(o).any()

@@ -1,9 +1,11 @@
 """bf16 / FP8-KV parity of the CUDA path against the reference Triton kernels compiled
 on the GPU (BASELINE.json: "bf16 outputs must match the reference Triton kernels ...
 within max-abs 2e-2 and rtol 1e-2 (FP8 KV within 6e-2)").  The Triton interpreter on
-the CPU cannot run bf16/FP8, so this is where that clause is checked:
-tests/triton_reference.py runs the upstream copy of the reference kernel that the
-installed vLLM ships, on the same device tensors our kernels read."""
+the CPU cannot run bf16/FP8, so this is where that clause is checked, on the
+same device tensors our kernels read, against BOTH sources of tests/triton_reference.py:
+`reference_file` = the reference's own ibm_triton_lib/kernels/triton_unified_attention.py
+(from /root/reference, or the copy build() leaves in the git-ignored baseline/_ref/), and
+`vllm_copy` = the upstream copy the installed vLLM ships (which also has sinks / qq_bias)."""
 import pytest
 import torch
 
@@ -13,9 +15,12 @@ from helpers import BF16_ATOL, BF16_RTOL, FP8_ATOL, assert_close, make_paged_inp
 pytestmark = pytest.mark.gpu
 
 
+SOURCES = ["reference_file", "vllm_copy"]
+
+
 def _both(lens, Hq, Hkv, D, bs, dtype=torch.bfloat16, fp8=False, k_scale=1.0, v_scale=1.0, window=0, softcap=0.0,
-          alibi=False, seed=0, sinks=False):
-    why = triton_reference.available()
+          alibi=False, seed=0, sinks=False, source="vllm_copy"):
+    why = triton_reference.reference_file_available() if source == "reference_file" else triton_reference.available()
     if why:
         pytest.skip(why)
     from vllm_triton_backend_b200 import _cabi, ops
@@ -42,10 +47,16 @@ def _both(lens, Hq, Hkv, D, bs, dtype=torch.bfloat16, fp8=False, k_scale=1.0, v_
     )
     kern = _cabi.last_kernel()
     ref = torch.full_like(inp["q"], float("nan"))
-    triton_reference.TritonReference(max(len(lens), 1), Hq, D, dev)(
-        inp["q"], inp["k_cache"], inp["v_cache"], ref, inp["cu_seqlens_q"], max_q, inp["seq_lens"], max_k, scale,
-        inp["block_table"], window=window, softcap=softcap, alibi_slopes=slopes, k_scale=ks, v_scale=vs, sinks=sink_t,
-    )
+    if source == "reference_file":
+        assert sink_t is None, "the reference file has no sinks"
+        triton_reference.ReferenceFileKernels(Hq // Hkv, bs)(
+            inp["q"], inp["k_cache"], inp["v_cache"], ref, inp["cu_seqlens_q"], max_q, inp["seq_lens"], max_k, scale,
+            inp["block_table"], window=window, softcap=softcap, alibi_slopes=slopes, k_scale=ks, v_scale=vs)
+    else:
+        triton_reference.TritonReference(max(len(lens), 1), Hq, D, dev)(
+            inp["q"], inp["k_cache"], inp["v_cache"], ref, inp["cu_seqlens_q"], max_q, inp["seq_lens"], max_k, scale,
+            inp["block_table"], window=window, softcap=softcap, alibi_slopes=slopes, k_scale=ks, v_scale=vs, sinks=sink_t,
+        )
     torch.cuda.synchronize()
     return ours.cpu(), ref.cpu(), kern
 
@@ -59,18 +70,20 @@ DECODE = [
 ]
 
 
+@pytest.mark.parametrize("source", SOURCES)
 @pytest.mark.parametrize("lens,Hq,Hkv,D,bs", DECODE)
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
-def test_decode_matches_triton_3d_kernel(lens, Hq, Hkv, D, bs, dtype):
-    ours, ref, kern = _both([(1, n) for n in lens], Hq, Hkv, D, bs, dtype=dtype, seed=3)
+def test_decode_matches_triton_3d_kernel(lens, Hq, Hkv, D, bs, dtype, source):
+    ours, ref, kern = _both([(1, n) for n in lens], Hq, Hkv, D, bs, dtype=dtype, seed=3, source=source)
     assert kern.startswith("attn_decode_split_kv")
     assert_close(ours, ref, atol=BF16_ATOL, rtol=BF16_RTOL, what="decode vs triton 3D")
 
 
+@pytest.mark.parametrize("source", SOURCES)
 @pytest.mark.parametrize("k_scale,v_scale", [(1.0, 1.0), (0.5, 0.5), (0.37, 0.61)])
-def test_fp8_kv_decode_matches_triton(k_scale, v_scale):
+def test_fp8_kv_decode_matches_triton(k_scale, v_scale, source):
     ours, ref, kern = _both([(1, n) for n in [300, 4096, 129, 2048]], 64, 8, 128, 16, fp8=True, k_scale=k_scale,
-                            v_scale=v_scale, seed=5)
+                            v_scale=v_scale, seed=5, source=source)
     assert kern.startswith("attn_decode_split_kv")
     assert_close(ours, ref, atol=FP8_ATOL, rtol=BF16_RTOL, what="fp8 decode vs triton")
 
@@ -87,15 +100,17 @@ MIXED = [
 
 @pytest.mark.parametrize("lens", MIXED, ids=lambda l: "-".join(f"{a}x{b}" for a, b in l)[:40])
 @pytest.mark.parametrize("heads", [(32, 8), (4, 4), (16, 2)])
-def test_mixed_batches_match_triton_2d_kernel(lens, heads):
-    ours, ref, kern = _both(lens, heads[0], heads[1], 128, 16, seed=7)
+@pytest.mark.parametrize("source", SOURCES)
+def test_mixed_batches_match_triton_2d_kernel(lens, heads, source):
+    ours, ref, kern = _both(lens, heads[0], heads[1], 128, 16, seed=7, source=source)
     assert_close(ours, ref, atol=BF16_ATOL, rtol=BF16_RTOL, what=f"mixed vs triton 2D ({kern})")
 
 
+@pytest.mark.parametrize("source", SOURCES)
 @pytest.mark.parametrize("window,softcap,alibi", [(128, 0.0, False), (0, 30.0, False), (0, 0.0, True), (256, 50.0, False)])
-def test_features_match_triton(window, softcap, alibi):
+def test_features_match_triton(window, softcap, alibi, source):
     lens = [(1, 900), (200, 700), (1, 40), (333, 333)]
-    ours, ref, kern = _both(lens, 16, 4, 128, 16, window=window, softcap=softcap, alibi=alibi, seed=11)
+    ours, ref, kern = _both(lens, 16, 4, 128, 16, window=window, softcap=softcap, alibi=alibi, seed=11, source=source)
     assert_close(ours, ref, atol=BF16_ATOL, rtol=BF16_RTOL, what=f"features vs triton ({kern})")
 
 
@@ -107,9 +122,10 @@ def test_long_prompt_softcap_matches_triton(softcap, window):
     assert_close(ours, ref, atol=BF16_ATOL, rtol=BF16_RTOL, what=f"softcap {softcap} vs triton ({kern})")
 
 
-def test_fp8_kv_prefill_matches_triton():
+@pytest.mark.parametrize("source", SOURCES)
+def test_fp8_kv_prefill_matches_triton(source):
     ours, ref, kern = _both([(300, 300), (64, 1064), (1, 555)], 32, 8, 128, 16, fp8=True, k_scale=0.37, v_scale=0.61,
-                            seed=13)
+                            seed=13, source=source)
     assert_close(ours, ref, atol=FP8_ATOL, rtol=BF16_RTOL, what=f"fp8 prefill vs triton ({kern})")
 
 

@@ -23,3 +23,19 @@ def test_e4m3_known_answers():
     got = quantize_e4m3_torch(x, 1.0).tolist()
     #            0     1     -1    448   sat   -sat  min-sub  tie->0 (RNE)  tie->even   nan
     assert got == [0x00, 0x38, 0xB8, 0x7E, 0x7E, 0xFE, 0x01, 0x00, 0x18, 0x7F]
+
+
+@pytest.mark.skipif(load_c_lib() is None, reason="oracle C library not built (make -C oracle)")
+@pytest.mark.parametrize("scale", [1.0, 0.37, 2.5])
+def test_scaled_fp8_quant_oracle_is_reciprocal_multiply_then_the_same_conversion(scale):
+    """K4's oracle (vllm .../fp8/common.cuh:40-60): x * fl(1/scale), fmin/fmax clamp, then the e4m3 conversion that the
+    plain-C restatement pins; NaN goes to +448 (fminf returns the number), unlike the cache write's NaN -> 0x7f."""
+    from oracle.cache_write import scaled_fp8_quant_ref
+
+    x = _all_bf16()
+    inv = (torch.tensor(1.0) / torch.tensor(scale, dtype=torch.float32))
+    y = x * inv
+    finite = ~torch.isnan(y)
+    exp = quantize_e4m3_c(torch.where(finite, y, torch.full_like(y, 448.0)), 1.0)
+    assert torch.equal(scaled_fp8_quant_ref(x, scale), exp)
+    assert scaled_fp8_quant_ref(torch.tensor([float("nan"), float("inf"), float("-inf")]), scale).tolist() == [0x7E, 0x7E, 0xFE]

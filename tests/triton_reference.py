@@ -1,5 +1,16 @@
 """The reference Triton kernels, compiled natively on the GPU box (test/bench checker only).
 
+Two sources, both run on the same device tensors our kernels read:
+
+* `ReferenceFileKernels` - the reference's OWN file, ibm-triton-lib/ibm_triton_lib/kernels/
+  triton_unified_attention.py, loaded by path from /root/reference or from the copy `__graft_entry__.build()`
+  leaves in the git-ignored baseline/_ref/ (which travels to the GPU box), with the
+  `triton_dejavu` autotuner stubbed to fixed tiles (it contributes no arithmetic).  This is the
+  "reference Triton kernels" of BASELINE.json's tolerance clause.
+* `TritonReference` - the upstream copy of the same kernel that the installed vLLM ships, which also carries the
+  later additions (sinks, qq_bias, output_scale) the reference file does not have, and vLLM's own launch heuristics
+  (what `scripts/kbench.py --impl triton` and bench.py's same-GPU comparator time).
+
 `/root/reference` does not exist on the GPU box, but the vLLM installed in the
 image ships the upstream copy of the same kernel the reference plugin carries
 (`vllm/v1/attention/ops/triton_unified_attention.py` — the reference file
@@ -13,7 +24,52 @@ the reference kernels beside ours.
 """
 from __future__ import annotations
 
+import os
+import sys
+
 import torch
+
+_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if _ROOT not in sys.path:
+    sys.path.insert(0, _ROOT)
+SOURCE = "vllm.v1.attention.ops.triton_unified_attention (upstream copy shipped by the installed vLLM)"
+
+
+def reference_file_available() -> str | None:
+    """None if the reference's own kernel file can run here, else the reason."""
+    if not torch.cuda.is_available():
+        return "no GPU"
+    from oracle import reference_runner as rr
+
+    if not rr.reference_available():
+        return "reference kernel file neither under /root/reference nor in baseline/_ref (run __graft_entry__.build())"
+    if os.environ.get("TRITON_INTERPRET") == "1":
+        return "TRITON_INTERPRET=1 is set"
+    return None
+
+
+class ReferenceFileKernels:
+    """`unified_attention` of the reference file (its launcher, :839-1030): 2D kernel for batches with a multi-token
+    query, else the 3D kernel with 16 segments + reduce_segments."""
+
+    def __init__(self, num_queries_per_kv: int, block_size: int):
+        from oracle import reference_runner as rr
+
+        bm = max(16, 1 << (max(num_queries_per_kv, 1) - 1).bit_length())
+        self.mod = rr.load_reference_kernels(bm, max(32, block_size), interpret=False)
+        self.source = "reference file " + rr._KERNEL_FILE
+
+    def __call__(self, q, k_cache, v_cache, out, cu_seqlens_q, max_seqlen_q, seq_lens, max_seqlen_k, scale, block_table,
+                 window=0, softcap=0.0, alibi_slopes=None, k_scale=None, v_scale=None):
+        one = torch.ones(1, dtype=torch.float32, device=q.device)
+        self.mod.unified_attention(
+            q=q, k=k_cache, v=v_cache, out=out, cu_seqlens_q=cu_seqlens_q, max_seqlen_q=max_seqlen_q, seqused_k=seq_lens,
+            max_seqlen_k=max_seqlen_k, avg_seqlen_q=max(1, q.shape[0] // max(1, seq_lens.shape[0])),
+            avg_seqlen_k=max_seqlen_k, softmax_scale=scale, causal=True,
+            window_size=(window - 1, 0) if window > 0 else (-1, -1), block_table=block_table, softcap=softcap,
+            q_descale=None, k_descale=one if k_scale is None else k_scale, v_descale=one if v_scale is None else v_scale,
+            alibi_slopes=alibi_slopes)
+        return out
 
 
 def available() -> str | None:

@@ -22,12 +22,14 @@ STATUS_NAMES = {
     6: "E_CUDA", 7: "E_NULL",
 }
 
-ABI_VERSION = 3  # include/b200attn.h B200ATTN_ABI_VERSION
+ABI_VERSION = 4  # include/b200attn.h B200ATTN_ABI_VERSION
 
 EXPORTED_SYMBOLS = [
     "b200attn_reshape_and_cache_flash",
     "b200attn_workspace_bytes",
     "b200attn_unified_attention",
+    "b200attn_decode_plan_bytes",
+    "b200attn_decode_plan",
     "b200attn_scaled_fp8_quant",
     "b200attn_rope_and_cache_flash",
     "b200attn_abi_version",
@@ -59,6 +61,7 @@ class AttentionParams(Structure):
         ("workspace", c_void_p), ("workspace_bytes", c_uint64),
         ("out_scale", c_void_p),
         ("qq_bias", c_void_p), ("qq_bias_stride0", c_int64),
+        ("decode_plan", c_void_p), ("decode_plan_key", c_uint64),
     ]
 
 
@@ -106,6 +109,10 @@ def load_library() -> ctypes.CDLL:
     lib.b200attn_workspace_bytes.argtypes = [c_int32] * 5
     lib.b200attn_unified_attention.restype = c_int32
     lib.b200attn_unified_attention.argtypes = [POINTER(AttentionParams), c_void_p]
+    lib.b200attn_decode_plan_bytes.restype = c_uint64
+    lib.b200attn_decode_plan_bytes.argtypes = [c_int32]
+    lib.b200attn_decode_plan.restype = c_int32
+    lib.b200attn_decode_plan.argtypes = [POINTER(AttentionParams), c_void_p, c_uint64, POINTER(c_uint64), c_void_p]
     lib.b200attn_rope_and_cache_flash.restype = c_int32
     lib.b200attn_rope_and_cache_flash.argtypes = [POINTER(RopeCacheParams), c_void_p]
     lib.b200attn_scaled_fp8_quant.restype = c_int32
@@ -149,5 +156,5 @@ def last_kernel() -> str:
     return load_library().b200attn_last_kernel().decode()
 
 
-def set_tuning(decode_heads_per_cta: int = 0, decode_ctas_per_sm: int = 0, decode_stages: int = 0, reserved: int = 0):
-    load_library().b200attn_set_tuning(decode_heads_per_cta, decode_ctas_per_sm, decode_stages, reserved)
+def set_tuning(decode_heads_per_cta: int = 0, decode_pool_sixteenths: int = 0, decode_stages: int = 0, reserved: int = 0):
+    load_library().b200attn_set_tuning(decode_heads_per_cta, decode_pool_sixteenths, decode_stages, reserved)

@@ -52,6 +52,7 @@ class B200AttentionMetadata:
     block_table: torch.Tensor  # int32 [B, MB] device
     slot_mapping: torch.Tensor  # int64 [T] device, padding = -1
     workspace: torch.Tensor  # split-KV partials, allocated once by the builder
+    decode_plan: Optional["ops.DecodePlan"] = None  # this step's split-KV work plan, built once for all layers
 
     # cascade attention is never used (reference triton_attn.py:279-281)
     use_cascade: bool = False
@@ -97,6 +98,16 @@ class B200AttentionMetadataBuilder(AttentionMetadataBuilder[B200AttentionMetadat
         self.workspace = torch.zeros(nbytes, dtype=torch.uint8, device=device)
         self._ws_extra = nbytes - ops.workspace_bytes(max_num_seqs, max_num_seqs, self.num_heads_q, self.num_heads_kv,
                                                       self.headdim)
+        # The split-KV work plan depends on seq_lens only, and all layers of a step share them: one plan kernel per
+        # step here instead of a partition inside every layer's launch.  A layer whose geometry differs from what
+        # is assumed here (another sliding window) ignores it and plans for itself (the key does not match).
+        q_dtype = model_config.dtype
+        kv_dtype = torch.float8_e4m3fn if cache_dtype.startswith("fp8") else q_dtype
+        self.decode_plan = None
+        if q_dtype in (torch.bfloat16, torch.float16):
+            self.decode_plan = ops.DecodePlan(device, max_num_seqs, self.num_heads_q, self.num_heads_kv, self.headdim,
+                                              self.block_size, q_dtype, kv_dtype,
+                                              int(getattr(kv_cache_spec, "sliding_window", 0) or 0))
 
     def _fit_workspace(self, num_seqs: int) -> None:
         """Chunked local attention (vLLM wraps this builder and hands it virtual batches,
@@ -116,12 +127,16 @@ class B200AttentionMetadataBuilder(AttentionMetadataBuilder[B200AttentionMetadat
         # capture with seq_lens = 1 so it is fast (reference :120-128); the captured
         # grid does not depend on the lengths.
         attn_metadata.seq_lens.fill_(1)
+        if self.decode_plan is not None:  # the plan follows seq_lens
+            self.decode_plan.build(attn_metadata.query_start_loc, attn_metadata.seq_lens, attn_metadata.max_query_len)
         return attn_metadata
 
     def build(self, common_prefix_len: int, common_attn_metadata: CommonAttentionMetadata,
               fast_build: bool = False) -> B200AttentionMetadata:
         m = common_attn_metadata
         self._fit_workspace(m.seq_lens.shape[0])
+        if self.decode_plan is not None:
+            self.decode_plan.build(m.query_start_loc, m.seq_lens, m.max_query_len)
         return B200AttentionMetadata(
             num_actual_tokens=m.num_actual_tokens,
             max_query_len=m.max_query_len,
@@ -131,6 +146,7 @@ class B200AttentionMetadataBuilder(AttentionMetadataBuilder[B200AttentionMetadat
             block_table=m.block_table_tensor,
             slot_mapping=m.slot_mapping,
             workspace=self.workspace,
+            decode_plan=self.decode_plan,
             use_cascade=False,
             common_prefix_len=common_prefix_len,
         )
@@ -377,5 +393,6 @@ class B200AttentionImpl(AttentionImpl):
         self._plans_for(layer, kv_cache, query.dtype)[1](
             q, out, attn_metadata.query_start_loc, attn_metadata.max_query_len, attn_metadata.seq_lens,
             attn_metadata.max_seq_len, attn_metadata.block_table, attn_metadata.workspace, output_scale,
+            attn_metadata.decode_plan,
         )
         return output

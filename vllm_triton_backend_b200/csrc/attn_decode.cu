@@ -35,6 +35,86 @@ namespace b200attn {
 namespace {
 
 constexpr int kMaxStages = 8;
+constexpr int kDescSlots = 16;                                // run descriptors in flight (> kMaxStages + 1)
+constexpr int kPoolRounds = 3;                                // pool chunks per CTA range, at most
+constexpr int kMaxPoolChunks = kPoolRounds * kMaxDecodeCtas;  // pool chunks of one launch
+constexpr int kMaxParts = (1 + kPoolRounds) * kMaxDecodeCtas; // parts one item can be cut into
+constexpr int kMaxSlots = 2 * (kMaxDecodeCtas + kMaxPoolChunks);
+
+// ---- the plan: where every CTA (and every pool chunk) starts -----------------------------------
+// Built on the device from seq_lens by decode_plan_kernel, once per step (all layers of a model share
+// seq_lens; the metadata builder calls b200attn_decode_plan) or by the launcher itself when the caller
+// brought none.  The flattened (sequence, head group, KV step) space [0, total) is cut into one range of
+// `per` steps per CTA.  The first per_static steps of a range are that CTA's own (static) part; the rest -
+// the range's tail - is cut into n_rounds chunks of halving size that go into a pool: chunk k = r * grid + c
+// is round r of range c, and CTAs take chunks in that order with an atomic counter as they finish.
+// SMs do not stream at the same rate when all of them pull from HBM (the slowest took 13 % longer than the
+// mean on the 1-kv-head C4 shard: profiles/r02_kbench_baseline.jsonl, end_skew 11 us of 97), so an equal
+// static split finishes when the slowest SM does; the pool lets the fast ones take the difference.  The
+// pool is the tails of ALL ranges rather than the end of the step space, so every item is cut into a few
+// more parts instead of a few items into fifty (profiles/r02_kbench_pool_v2_epilogue_warp.jsonl).
+struct PlanHeader {  // 64 bytes
+  int total;          // steps in the flat space
+  int per;            // steps of a CTA's range: range c = [c * per, min((c + 1) * per, total))
+  int per_static;     // its first per_static steps are the static part
+  int n_rounds;       // pool chunks per range
+  int n_chunks;       // n_rounds * grid
+  int grid;
+  int has_zero_rows;  // some sequence has one query token and no visible key (its output rows are zeros)
+  int pad;
+  short size[8];      // chunk of round r: [c * per + per_static + off[r], + size[r]) within range c
+  short off[8];
+};
+struct PlanCursor {  // 32 bytes: a flat position resolved to (sequence, head group, step)
+  int b;             // -1: nothing there
+  int hg, step;      // step is absolute (in units of tps tokens) within the sequence
+  int seq_len, first, n;  // of sequence b: visible steps are [first, first + n)
+  int tq;            // first query token of b
+  int flat;          // the flat position itself
+};
+struct Plan {
+  PlanHeader hdr;
+  PlanCursor cta[kMaxDecodeCtas];
+  PlanCursor chunk[kMaxPoolChunks];
+  // int prefix[num_seqs + 1] follows (scratch of the plan kernel)
+};
+
+// Part j of range c: j = 0 the static part, j >= 1 the pool chunk of round j - 1.  [b, e) may be empty.
+__device__ __forceinline__ void part_range(const PlanHeader& h, int c, int j, int& b, int& e) {
+  const int r0 = c * h.per, r1 = min(r0 + h.per, h.total);
+  if (j == 0) {
+    b = r0, e = min(r0 + h.per_static, r1);
+  } else {
+    b = r0 + h.per_static + h.off[j - 1], e = min(b + h.size[j - 1], r1);
+  }
+}
+// Where the partial of the run that part (c, j) = [b, ..) contributes to the item starting at flat i0 goes.  A part
+// can hold two partial runs - the end of one item at its start, the start of another at its end - and whole items
+// in between (written directly): two slots per part, chosen by whether the item began before the part did.
+__device__ __forceinline__ int part_slot(const PlanHeader& h, int c, int j, int b, int i0) {
+  return (j == 0 ? 2 * c : 2 * h.grid + 2 * ((j - 1) * h.grid + c)) + (b < i0 ? 1 : 0);
+}
+
+// A run: consecutive steps of ONE (sequence, head group) item, produced by the producer warp for the consumers.
+struct RunDesc {  // 48 bytes in shared memory
+  int kind;       // 1 = run, 0 = no more work
+  int hg, step0, nsteps, seq_len, tq, item;
+  int slot;       // where this run's partial goes, or -1: the run is the whole item, write the output directly
+  int nparts;     // parts the item is cut into (ticket count that completes it)
+  int i0, n;      // flat position of the item's first step, its number of steps
+  int pad;
+};
+// A partial run handed to the ticket warp, and (the same fields) an item whose last ticket was taken, handed
+// back to the consumers for merging.
+struct FinDesc {  // 32 bytes in shared memory
+  int kind;       // 1 = a partial was written, 0 = the consumers are done
+  int item, hg, tq, nparts, i0, n;
+  int pad;
+};
+constexpr int kFinSlots = 2;   // partial runs waiting for their ticket
+constexpr int kReqSlots = 4;   // items waiting to be merged
+static_assert(sizeof(FinDesc) == 32, "layout");
+static_assert(sizeof(RunDesc) == 48 && sizeof(PlanCursor) == 32 && sizeof(PlanHeader) == 64, "layout");
 
 struct DecodeParams {
   b200attn_attention_params a;
@@ -50,9 +130,11 @@ struct DecodeParams {
   int paired;      // 1: one TMA box carries the K and the V rows of a page ([head][k|v][slot][128 B]); fp8 D=128
   int group;       // query heads per kv head
   int only_q1;     // mixed batch: only sequences with exactly one query token are this kernel's
+  const Plan* plan;
   float* ws_acc;   // [slots][hpc*group][D]
   float* ws_ml;    // [slots][hpc*group][2]  (max in log2 units, exp-sum)
-  int* ws_cnt;     // [items] tickets taken on an item split across CTAs (0 between calls)
+  int* ws_cnt;     // [items] tickets taken on an item split across parts (0 between calls)
+  int* ws_pool;    // [0] next pool chunk, [1] CTAs that are done taking chunks (both 0 between calls)
   unsigned long long* trace;  // debug time stamps, 8 per CTA (b200attn_debug_set_decode_trace) or nullptr
 };
 
@@ -72,20 +154,26 @@ struct ItemCursor {
   int b, hg, step;       // current sequence, head group, step index (absolute, in units of tps tokens)
   int first, n;          // first step and number of steps of sequence b
   int seq_len;
+  int tq;                // first query token of sequence b
   int flat;              // flat index of the current step
 };
 
-__device__ __forceinline__ void seq_steps(const DecodeParams& P, int b, int& seq_len, int& first, int& n) {
-  seq_len = P.a.seq_lens[b];
-  int q_len = P.a.cu_seqlens_q ? (P.a.cu_seqlens_q[b + 1] - P.a.cu_seqlens_q[b]) : 1;
-  if (seq_len <= 0 || q_len <= 0 || (P.only_q1 && q_len != 1)) {
+// visible steps of sequence b: [first, first + n)
+__device__ __forceinline__ void seq_steps(const int32_t* seq_lens, const int32_t* cu_seqlens_q, int only_q1, int window,
+                                          int tps_shift, int b, int& seq_len, int& first, int& n, int& tq) {
+  seq_len = seq_lens[b];
+  int c0 = b, c1 = b + 1;
+  if (cu_seqlens_q) c0 = cu_seqlens_q[b], c1 = cu_seqlens_q[b + 1];
+  tq = c0;
+  const int q_len = c1 - c0;
+  if (seq_len <= 0 || q_len <= 0 || (only_q1 && q_len != 1)) {
     first = 0, n = 0;
     return;
   }
   int lo_tok = 0;
-  if (P.a.sliding_window > 0) lo_tok = max(0, seq_len - P.a.sliding_window);
-  first = lo_tok >> P.tps_shift;
-  n = ((seq_len + P.tps - 1) >> P.tps_shift) - first;
+  if (window > 0) lo_tok = max(0, seq_len - window);
+  first = lo_tok >> tps_shift;
+  n = ((seq_len + (1 << tps_shift) - 1) >> tps_shift) - first;
 }
 
 // advance to the next step in (b, hg, step) order; returns false past the end
@@ -98,7 +186,7 @@ __device__ __forceinline__ bool cursor_next(const DecodeParams& P, ItemCursor& c
   }
   c.hg = 0;
   while (++c.b < P.a.num_seqs) {
-    seq_steps(P, c.b, c.seq_len, c.first, c.n);
+    seq_steps(P.a.seq_lens, P.a.cu_seqlens_q, P.only_q1, P.a.sliding_window, P.tps_shift, c.b, c.seq_len, c.first, c.n, c.tq);
     if (c.n > 0) {
       c.step = c.first;
       return true;
@@ -107,8 +195,117 @@ __device__ __forceinline__ bool cursor_next(const DecodeParams& P, ItemCursor& c
   return false;
 }
 
+// ---- plan kernel: one CTA ------------------------------------------------------------------------
+struct PlanArgs {
+  const int32_t* seq_lens;
+  const int32_t* cu_seqlens_q;
+  Plan* plan;
+  int num_seqs, only_q1, window, tps_shift, head_groups, grid;
+  int pool_sixteenths;  // share of a CTA's steps that goes to the pool, in 1/16
+  int min_chunk;        // smallest chunk, steps
+};
+
+constexpr int kPlanThreads = 1024;
+
+__global__ void __launch_bounds__(kPlanThreads) decode_plan_kernel(const PlanArgs A) {
+  __shared__ int s_warp[kPlanThreads / 32];
+  __shared__ int s_carry, s_zero;
+  __shared__ PlanHeader s_hdr;
+  pdl_launch_dependents();  // the decode kernel behind this one sets itself up meanwhile (it waits before it reads)
+  pdl_wait();
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  int* prefix = reinterpret_cast<int*>(A.plan + 1);  // [num_seqs + 1], steps (not multiplied by head_groups)
+  if (tid == 0) s_carry = 0, s_zero = 0;
+  __syncthreads();
+  // ---- exclusive scan of the per-sequence step counts, kPlanThreads sequences at a time
+  for (int b0 = 0; b0 < A.num_seqs; b0 += kPlanThreads) {
+    const int b = b0 + tid;
+    int n = 0;
+    if (b < A.num_seqs) {
+      int sl, first, tq;
+      seq_steps(A.seq_lens, A.cu_seqlens_q, A.only_q1, A.window, A.tps_shift, b, sl, first, n, tq);
+      const int ql = A.cu_seqlens_q ? A.cu_seqlens_q[b + 1] - A.cu_seqlens_q[b] : 1;
+      if (sl <= 0 && ql == 1) s_zero = 1;
+    }
+    int incl = n;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+      int w = s_warp[lane];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, w, o);
+        if (lane >= o) w += v;
+      }
+      s_warp[lane] = w;  // inclusive over warps
+    }
+    __syncthreads();
+    const int base = s_carry + (warp > 0 ? s_warp[warp - 1] : 0);
+    if (b < A.num_seqs) prefix[b] = base + incl - n;
+    __syncthreads();
+    if (tid == 0) s_carry += s_warp[kPlanThreads / 32 - 1];
+    __syncthreads();
+  }
+  if (tid == 0) {
+    const int total_seq_steps = s_carry;
+    prefix[A.num_seqs] = total_seq_steps;
+    PlanHeader h = {};
+    const long long tot = (long long)total_seq_steps * A.head_groups;
+    h.total = tot > 0x7fffffffll ? 0x7fffffff : (int)tot;  // (a batch of 2^31 steps does not exist)
+    h.grid = A.grid;
+    h.has_zero_rows = s_zero;
+    h.per = (h.total + A.grid - 1) / A.grid;
+    int pool_per = (h.per * A.pool_sixteenths) >> 4;  // tail of every range that goes to the pool
+    if (pool_per < 2 * A.min_chunk || A.pool_sixteenths <= 0) pool_per = 0;  // too little work to be worth sharing
+    if (pool_per > 32000) pool_per = 32000;  // (sizes are shorts)
+    h.per_static = h.per - pool_per;
+    // chunk sizes halve from round to round down to min_chunk; the last round takes what is left
+    int rem = pool_per, nr = 0;
+    while (rem > 0 && nr < kPoolRounds) {
+      int c = (rem + 1) / 2;
+      if (c < A.min_chunk) c = A.min_chunk;
+      if (nr == kPoolRounds - 1 || rem - c < A.min_chunk) c = rem;
+      h.size[nr] = (short)c, h.off[nr] = (short)(pool_per - rem);
+      rem -= c, ++nr;
+    }
+    h.n_rounds = nr, h.n_chunks = nr * A.grid;
+    s_hdr = h;
+    A.plan->hdr = h;
+  }
+  __syncthreads();
+  const PlanHeader h = s_hdr;
+  // ---- resolve the start of every CTA's static part and of every pool chunk
+  for (int t = tid; t < A.grid + h.n_chunks; t += kPlanThreads) {
+    int f, e;
+    if (t < A.grid) part_range(h, t, 0, f, e);
+    else part_range(h, (t - A.grid) % A.grid, 1 + (t - A.grid) / A.grid, f, e);
+    const bool any = f < e;
+    PlanCursor c;
+    c.b = -1, c.hg = 0, c.step = 0, c.seq_len = 0, c.first = 0, c.n = 0, c.tq = 0, c.flat = f;
+    if (any) {
+      // largest b with prefix[b] * HG <= f; sequences without steps share their successor's prefix and
+      // are skipped by taking the LAST such b... they have n = 0, so take the last b whose range is not empty
+      int lo = 0, hi = A.num_seqs;  // invariant: prefix[lo] * HG <= f < prefix[hi] * HG
+      while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if ((long long)prefix[mid] * A.head_groups <= f) lo = mid; else hi = mid;
+      }
+      int sl, first, n, tq;
+      seq_steps(A.seq_lens, A.cu_seqlens_q, A.only_q1, A.window, A.tps_shift, lo, sl, first, n, tq);
+      const int rem = f - prefix[lo] * A.head_groups;  // < n * HG
+      c.b = lo, c.hg = rem / n, c.step = first + rem % n, c.seq_len = sl, c.first = first, c.n = n, c.tq = tq;
+    }
+    (t < A.grid ? A.plan->cta[t] : A.plan->chunk[t - A.grid]) = c;
+  }
+}
+
 template <int D, bool KV_FP8, bool MMA_BF16, bool Q_BF16, int NT, int NW, int TT>
-__global__ void __launch_bounds__((NW + 1) * 32, 1)
+__global__ void __launch_bounds__((NW + 2) * 32, 1)
 attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_map,
                    const __grid_constant__ CUtensorMap v_map) {
   constexpr int ESZ = KV_FP8 ? 1 : 2;
@@ -121,15 +318,27 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
   static_assert(TT == 16 || TT == 32, "warp tile is one or two 16-token MMA tiles");
   static_assert(NDC >= 1, "row must be at least 128 bytes");
 
+  // The stage ring needs 1024-byte alignment (128-byte swizzle) and the declared alignment of the dynamic array is
+  // honoured; three 64 KB stages + the 32 KB merge buffer leave 3 KB of the 227 KB for everything else, so there
+  // is no slack to re-align with (a misaligned base traps instead of corrupting the swizzle).
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  // [stages][K | V] then merge buffer, then barriers / scalars
+  uint8_t* smem = smem_raw;
+  if (smem_u32(smem_raw) & 1023u) __trap();
+  // [stages][K | V] then merge buffer, then barriers / run descriptors
   uint8_t* stage_base = smem;
   float* mbuf = reinterpret_cast<float*>(smem + (size_t)P.stages * 2 * KV_STAGE_BYTES);  // [NW][8][D]
   float* ml_buf = mbuf + NW * 8 * D;                                                      // [NW][8][2]
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(ml_buf + NW * 8 * 2);
   uint64_t* empty_bar = full_bar + kMaxStages;
-  int* s_part = reinterpret_cast<int*>(empty_bar + kMaxStages);  // [0]=begin [1]=end [2]=b [3]=hg [4]=step [5]=per [6]=ticket flag
+  uint64_t* desc_bar = empty_bar + kMaxStages;                     // [kDescSlots]
+  RunDesc* descs = reinterpret_cast<RunDesc*>(desc_bar + kDescSlots);  // [kDescSlots]
+  uint64_t* fin_full = reinterpret_cast<uint64_t*>(descs + kDescSlots);  // [kFinSlots] consumers -> ticket warp
+  uint64_t* fin_empty = fin_full + kFinSlots;                             // [kFinSlots] ticket warp -> consumers
+  uint64_t* epi_done = fin_empty + kFinSlots;                             // [1] the ticket warp has taken every ticket
+  FinDesc* fins = reinterpret_cast<FinDesc*>(epi_done + 1);               // [kFinSlots]
+  FinDesc* reqs = fins + kFinSlots;                                       // [kReqSlots] items to merge
+  volatile int* req_cnt = reinterpret_cast<volatile int*>(reqs + kReqSlots);  // [0] posted by the ticket warp, [1] merged, [2] scratch
+  short* part_slots = reinterpret_cast<short*>(const_cast<int*>(req_cnt) + 4);  // [kMaxParts] the parts of the item being merged
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int gid = lane >> 2, t4 = lane & 3;
@@ -137,8 +346,8 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
   unsigned long long* trace = P.trace ? P.trace + (size_t)blockIdx.x * 8 : nullptr;
   if (trace && threadIdx.x == 0) trace[0] = global_ns(), trace[1] = clock64(), trace[7] = 0;
 
-  // ---- work partition and barrier init ----------------------------------------
-  if (warp == NW && lane == 0) {  // descriptor fetch overlaps the partition
+  // ---- barrier init ---------------------------------------------------------------------------
+  if (warp == NW && lane == 0) {  // descriptor fetch overlaps the rest of the prologue
     tma_prefetch_desc(&k_map);
     tma_prefetch_desc(&v_map);
   }
@@ -147,205 +356,36 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], NW);
     }
+    for (int s = 0; s < kDescSlots; ++s) mbar_init(&desc_bar[s], 1);
+    for (int s = 0; s < kFinSlots; ++s) {
+      mbar_init(&fin_full[s], NW);
+      mbar_init(&fin_empty[s], 1);
+    }
+    mbar_init(epi_done, 1);
+    req_cnt[0] = 0, req_cnt[1] = 0, req_cnt[2] = 0;
     fence_barrier_init();
   }
+  // Whatever is launched behind this kernel with the programmatic-serialisation attribute (the next layer's
+  // cache write, the next decode launch) may be scheduled as this grid's CTAs retire; it waits for this grid
+  // to complete before it touches memory (common.cuh).
+  pdl_launch_dependents();
+  __syncthreads();  // mbarrier init visible to every warp
   // Everything above touched only shared memory and kernel parameters.  From here on the kernel reads what
-  // earlier kernels on the stream wrote (metadata, q, the cache): wait for them (no-op without PDL).
+  // earlier kernels on the stream wrote (the plan, metadata, q, the cache): wait for them (no-op without PDL).
   pdl_wait();
-  int my_begin, my_end, per_cta;
-  ItemCursor cur;
-  int tq_first = 0;  // first query-token index of cur.b
-  constexpr int kFastSeqs = 256;
-  if (P.a.num_seqs <= kFastSeqs) {
-    // Every warp derives the partition on its own from one round of independent
-    // loads (lane l holds sequences l, l+32, ...): no shared-memory hand-off and a
-    // single global-memory latency before the first page can be requested.
-    constexpr int R = kFastSeqs / 32;
-    int n_r[R], first_r[R], sl_r[R], tq_r[R];
-    int total = 0;
-    unsigned zero_rows = 0;  // bit r: sequence lane+32r has no visible key and one query token
-#pragma unroll
-    for (int r = 0; r < R; ++r) {
-      const int b = r * 32 + lane;
-      n_r[r] = 0, first_r[r] = 0, sl_r[r] = 0, tq_r[r] = 0;
-      if (b < P.a.num_seqs) {
-        const int sl = P.a.seq_lens[b];
-        int c0 = b, c1 = b + 1;
-        if (P.a.cu_seqlens_q) c0 = P.a.cu_seqlens_q[b], c1 = P.a.cu_seqlens_q[b + 1];
-        const int ql = c1 - c0;
-        sl_r[r] = sl, tq_r[r] = c0;
-        if (sl > 0 && ql > 0 && !(P.only_q1 && ql != 1)) {
-          int lo_tok = 0;
-          if (P.a.sliding_window > 0) lo_tok = max(0, sl - P.a.sliding_window);
-          first_r[r] = lo_tok >> P.tps_shift;
-          n_r[r] = ((sl + P.tps - 1) >> P.tps_shift) - first_r[r];
-        }
-        if (sl <= 0 && ql == 1 && b % gridDim.x == blockIdx.x) zero_rows |= 1u << r;
-        total += n_r[r];
-      }
-    }
-    total = __reduce_add_sync(0xffffffffu, total);
-    const long long total_flat = (long long)total * P.head_groups;
-    // 64-bit division is a long dependent sequence; the totals fit 32 bits unless the batch holds > 2^31 steps
-    const bool small = total_flat < (1ll << 31);
-    const long long per = small ? (long long)(((unsigned)total_flat + gridDim.x - 1) / gridDim.x)
-                                : (total_flat + gridDim.x - 1) / gridDim.x;
-    long long begin = per * blockIdx.x;
-    long long end = begin + per;
-    if (begin > total_flat) begin = total_flat;
-    if (end > total_flat) end = total_flat;
-    int fb = -1, fhg = 0, fstep = 0, fsl = 0, ffirst = 0, fn = 0;
-    if (begin < end) {
-      long long run = 0;
-#pragma unroll
-      for (int r = 0; r < R; ++r) {
-        if (r * 32 < P.a.num_seqs && fb < 0) {  // warp-uniform
-          int incl = n_r[r];
-#pragma unroll
-          for (int o = 1; o < 32; o <<= 1) {
-            const int v = __shfl_up_sync(0xffffffffu, incl, o);
-            if (lane >= o) incl += v;
-          }
-          const long long lo = run + (long long)(incl - n_r[r]) * P.head_groups;
-          const long long hi = run + (long long)incl * P.head_groups;
-          const unsigned hit = __ballot_sync(0xffffffffu, n_r[r] > 0 && begin >= lo && begin < hi);
-          if (hit) {
-            const int src = __ffs(hit) - 1;
-            const long long lo_s = __shfl_sync(0xffffffffu, lo, src);
-            fn = __shfl_sync(0xffffffffu, n_r[r], src);
-            ffirst = __shfl_sync(0xffffffffu, first_r[r], src);
-            fsl = __shfl_sync(0xffffffffu, sl_r[r], src);
-            tq_first = __shfl_sync(0xffffffffu, tq_r[r], src);
-            fb = r * 32 + src;
-            const long long rem = begin - lo_s;  // < fn * head_groups
-            if (small) {
-              const unsigned qd = (unsigned)rem / (unsigned)fn;
-              fhg = (int)qd, fstep = ffirst + (int)((unsigned)rem - qd * (unsigned)fn);
-            } else {
-              fhg = (int)(rem / fn), fstep = ffirst + (int)(rem % fn);
-            }
-          }
-          run += (long long)__shfl_sync(0xffffffffu, incl, 31) * P.head_groups;
-        }
-      }
-    }
-    my_begin = (int)begin, my_end = (fb < 0) ? (int)begin : (int)end;
-    per_cta = (int)(per > 0 ? per : 1);
-    cur.b = fb, cur.hg = fhg, cur.step = fstep, cur.flat = my_begin;
-    cur.seq_len = fsl, cur.first = ffirst, cur.n = fn;
-    // sequences with no visible key get zeros (reference reduce_segments :828); nobody visits them below
-    if (warp == 0 && __any_sync(0xffffffffu, zero_rows != 0)) {
-#pragma unroll
-      for (int r = 0; r < R; ++r) {
-        unsigned m = __ballot_sync(0xffffffffu, (zero_rows >> r) & 1u);
-        while (m) {
-          const int src = __ffs(m) - 1;
-          m &= m - 1;
-          const int tq = __shfl_sync(0xffffffffu, tq_r[r], src);
-          for (int e = lane; e < P.a.num_q_heads * D; e += 32) {
-            const int osz = P.a.out_scale ? 1 : 2;  // fp8 output: one byte per element, 0x00 == +0
-            char* orow = static_cast<char*>(P.a.out) + ((int64_t)tq * P.a.out_stride0 + (int64_t)(e / D) * P.a.out_stride1) * osz;
-            if (osz == 1) orow[e % D] = 0;
-            else reinterpret_cast<uint16_t*>(orow)[e % D] = 0;
-          }
-        }
-      }
-    }
-    __syncthreads();  // mbarrier init visible to every warp
-  } else {
-    if (warp == 0) {
-      // total steps over all sequences
-      int total = 0;
-      for (int b0 = 0; b0 < P.a.num_seqs; b0 += 32) {
-        int b = b0 + lane, n = 0;
-        if (b < P.a.num_seqs) {
-          int sl, first;
-          seq_steps(P, b, sl, first, n);
-        }
-        total += n;
-      }
-      total = __reduce_add_sync(0xffffffffu, total);
-      const long long total_flat = (long long)total * P.head_groups;
-      const long long per = (total_flat + gridDim.x - 1) / gridDim.x;
-      long long begin = per * blockIdx.x;
-      long long end = begin + per;
-      if (begin > total_flat) begin = total_flat;
-      if (end > total_flat) end = total_flat;
-      // locate `begin`: largest b with HG * prefix(b) <= begin and n_b > 0 covering it
-      int fb = -1, fhg = 0, fstep = 0;
-      if (begin < end) {
-        long long run = 0;  // HG * sum of n over sequences before the chunk
-        for (int b0 = 0; b0 < P.a.num_seqs && fb < 0; b0 += 32) {
-          int b = b0 + lane, n = 0, first = 0, sl;
-          if (b < P.a.num_seqs) seq_steps(P, b, sl, first, n);
-          int incl = n;
-#pragma unroll
-          for (int o = 1; o < 32; o <<= 1) {
-            int v = __shfl_up_sync(0xffffffffu, incl, o);
-            if (lane >= o) incl += v;
-          }
-          const long long lo = run + (long long)(incl - n) * P.head_groups;
-          const long long hi = run + (long long)incl * P.head_groups;
-          const bool mine = n > 0 && begin >= lo && begin < hi;
-          const unsigned hit = __ballot_sync(0xffffffffu, mine);
-          if (hit) {
-            const int src = __ffs(hit) - 1;
-            const long long lo_s = __shfl_sync(0xffffffffu, lo, src);
-            const int n_s = __shfl_sync(0xffffffffu, n, src);
-            const int first_s = __shfl_sync(0xffffffffu, first, src);
-            fb = b0 + src;
-            const long long rem = begin - lo_s;
-            fhg = (int)(rem / n_s);
-            fstep = first_s + (int)(rem % n_s);
-          }
-          run += (long long)__shfl_sync(0xffffffffu, incl, 31) * P.head_groups;
-        }
-      }
-      if (lane == 0) {
-        s_part[0] = (int)begin;
-        s_part[1] = (fb < 0) ? (int)begin : (int)end;
-        s_part[2] = fb, s_part[3] = fhg, s_part[4] = fstep;
-        s_part[5] = (int)(per > 0 ? per : 1);
-      }
-    }
-    __syncthreads();
-    for (int b = blockIdx.x; b < P.a.num_seqs; b += gridDim.x) {
-      const int sl = P.a.seq_lens[b];
-      const int ql = P.a.cu_seqlens_q ? (P.a.cu_seqlens_q[b + 1] - P.a.cu_seqlens_q[b]) : 1;
-      if (sl <= 0 && ql == 1) {
-        const int tq = P.a.cu_seqlens_q ? P.a.cu_seqlens_q[b] : b;
-        for (int e = threadIdx.x; e < P.a.num_q_heads * D; e += blockDim.x) {
-          const int osz = P.a.out_scale ? 1 : 2;
-          char* orow = static_cast<char*>(P.a.out) + ((int64_t)tq * P.a.out_stride0 + (int64_t)(e / D) * P.a.out_stride1) * osz;
-          if (osz == 1) orow[e % D] = 0;
-          else reinterpret_cast<uint16_t*>(orow)[e % D] = 0;
-        }
-      }
-    }
-    my_begin = s_part[0], my_end = s_part[1];
-    per_cta = s_part[5];
-    cur.b = s_part[2], cur.hg = s_part[3], cur.step = s_part[4], cur.flat = my_begin;
-    cur.seq_len = 0, cur.first = 0, cur.n = 0;
-    if (my_begin < my_end) {
-      seq_steps(P, cur.b, cur.seq_len, cur.first, cur.n);
-      tq_first = P.a.cu_seqlens_q ? P.a.cu_seqlens_q[cur.b] : cur.b;
-    }
-  }
-  if (trace && threadIdx.x == 0) trace[2] = clock64();
-  if (my_begin >= my_end) {
-    if (trace && threadIdx.x == 0) trace[3] = trace[4] = trace[5] = clock64(), trace[6] = global_ns();
-    return;
-  }
 
   const int boxb = P.hpc * NDC * P.box_slots * 128;  // bytes of one TMA box (all heads, all chunks)
 
   if (warp == NW) {
     // ======================= producer warp ====================================
-    // The whole warp issues: lane i looks up the page of box i and launches its
-    // K and V copies, so page-table latency and TMA issue overlap across boxes.
+    // Walks this CTA's work - its static range, then pool chunks - cuts it into runs (consecutive steps of one
+    // item), publishes a descriptor per run and streams every step's pages: lane i looks up the page of box i
+    // and launches its K and V copies, so page-table latency and TMA issue overlap across boxes.
     const uint64_t pol = policy_evict_first();
+    const PlanHeader hdr = P.plan->hdr;
     int stage = 0;
     uint32_t phase = 0;
+    int ndesc = 0;
     // Page ids are read through a 128-page window held in registers (lane l keeps
     // pages base + 32 r + l) with the next window already in flight, so the copy
     // loop never waits on a block-table load (one DRAM round trip per item, not per step).
@@ -358,73 +398,204 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
         dst[r] = pg < npages ? bt[pg] : 0;
       }
     };
+    auto load_cursor = [&](const PlanCursor* pc, ItemCursor& c) {
+      const int4 lo = *reinterpret_cast<const int4*>(pc), hi = *(reinterpret_cast<const int4*>(pc) + 1);
+      c.b = lo.x, c.hg = lo.y, c.step = lo.z, c.seq_len = lo.w, c.first = hi.x, c.n = hi.y, c.tq = hi.z, c.flat = hi.w;
+    };
+    const bool pooled = hdr.n_chunks > 0;
+    const int J = 1 + hdr.n_rounds;  // parts per range
+    // parts the item [i0, i1) is cut into: ranges strictly inside it contribute all of theirs, the (one or two)
+    // ranges at its ends are tested part by part, one lane each
+    auto count_parts = [&](int i0, int i1) {
+      const int ca = i0 / hdr.per, cb = (i1 - 1) / hdr.per;
+      int cnt = cb - ca >= 2 ? (cb - ca - 1) * J : 0;
+      bool hit = false;
+      if (lane < (cb > ca ? 2 : 1) * J) {
+        int pb, pe;
+        part_range(hdr, lane < J ? ca : cb, lane < J ? lane : lane - J, pb, pe);
+        hit = max(pb, i0) < min(pe, i1);
+      }
+      return cnt + __popc(__ballot_sync(0xffffffffu, hit));
+    };
+    ItemCursor cur;
+    int range_c = (int)blockIdx.x, range_j = 0;  // the part being walked: range, part index (0 = static)
+    int range_begin, range_end;                  // its flat extent
+    load_cursor(&P.plan->cta[blockIdx.x], cur);
+    part_range(hdr, range_c, 0, range_begin, range_end);
+    bool have_range = cur.b >= 0 && cur.flat < range_end;
     while (true) {
-      const int tok0 = cur.step * P.tps;
-      const int ntok = min(P.tps, cur.seq_len - tok0);
-      const int nbox = (ntok + P.box_slots - 1) / P.box_slots;
-      const int head0 = cur.hg * P.hpc;
-      const int32_t* bt = P.a.block_tables + (int64_t)cur.b * P.a.bt_stride0;
-      const int npages = (cur.seq_len + P.a.block_size - 1) >> P.bs_shift;
-      const int p_first = tok0 >> P.bs_shift;
-      const int base = p_first & ~127;
-      if (cur.b != win_b || base != win_base) {
-        if (cur.b == win_b && base == win_base + 128) {
-#pragma unroll
-          for (int r = 0; r < 4; ++r) ids[r] = nxt[r];
-        } else {
-          load_ids(ids, bt, base, npages);
-        }
-        load_ids(nxt, bt, base + 128, npages);
-        win_b = cur.b, win_base = base;
-      }
-      auto page_of = [&](int pg) {  // warp-collective: every lane asks for one page id
-        const int src = pg & 31, r = (pg >> 5) & 3;
-        const int v0 = __shfl_sync(0xffffffffu, ids[0], src), v1 = __shfl_sync(0xffffffffu, ids[1], src);
-        const int v2 = __shfl_sync(0xffffffffu, ids[2], src), v3 = __shfl_sync(0xffffffffu, ids[3], src);
-        return r == 0 ? v0 : (r == 1 ? v1 : (r == 2 ? v2 : v3));
-      };
-      mbar_wait(&empty_bar[stage], phase ^ 1);
-      uint8_t* kdst = stage_base + (size_t)stage * 2 * KV_STAGE_BYTES;
-      uint8_t* vdst = kdst + KV_STAGE_BYTES;
-      if (lane == 0) mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)(2 * nbox * boxb));
-      __syncwarp();
-      if (P.paired) {
-        // k_map's third coordinate selects K (0) or V (1); the box takes both
-        const int i = lane;
-        const int tok = tok0 + i * P.box_slots;
-        const int page = page_of(tok >> P.bs_shift);
-        if (i < nbox)
-          tma_load_5d(kdst + (size_t)i * 2 * boxb, &k_map, &full_bar[stage], 0, tok & (P.a.block_size - 1), 0, head0, page, pol);
-      } else if (P.tma_split == 0) {
-        // nbox <= 8: one lane per box
-        const int i = lane;
-        const int tok = tok0 + i * P.box_slots;
-        const int page = page_of(tok >> P.bs_shift);  // lanes past nbox read a don't-care id
-        if (i < nbox) {
-          const int slot0 = tok & (P.a.block_size - 1);
-          tma_load_5d(kdst + (size_t)i * boxb, &k_map, &full_bar[stage], 0, slot0, 0, head0, page, pol);
-          tma_load_5d(vdst + (size_t)i * boxb, &v_map, &full_bar[stage], 0, slot0, 0, head0, page, pol);
-        }
-      } else {
-        const int per_box = P.hpc * NDC;
-        const int units = nbox * per_box;
-        for (int u0 = 0; u0 < units; u0 += 32) {
-          const int u = u0 + lane;
-          const int i = min(u / per_box, nbox - 1), r = u % per_box, h = r / NDC, dc = r % NDC;
-          const int tok = tok0 + i * P.box_slots;
-          const int page = page_of(tok >> P.bs_shift);
-          if (u < units) {
-            const int slot0 = tok & (P.a.block_size - 1);
-            const size_t off = (size_t)i * boxb + (size_t)(h * NDC + dc) * P.box_slots * 128;
-            tma_load_5d(kdst + off, &k_map, &full_bar[stage], 0, slot0, dc, head0 + h, page, pol);
-            tma_load_5d(vdst + off, &v_map, &full_bar[stage], 0, slot0, dc, head0 + h, page, pol);
+      int next_chunk = 0x7fffffff;
+      if (pooled && lane == 0) next_chunk = atomicAdd(&P.ws_pool[0], 1);  // in flight while this range is walked
+      ItemCursor next_cur;
+      next_cur.b = -1;
+      bool next_loaded = false;
+      while (have_range) {
+        // ---- a run: steps of the current item that lie in this range
+        const int item_end = cur.first + cur.n;
+        const int nsteps = min(item_end - cur.step, range_end - cur.flat);
+        RunDesc rd = {};
+        {
+          const int item = cur.b * P.head_groups + cur.hg;
+          const int i0 = cur.flat - (cur.step - cur.first);  // flat position of the item's first step
+          const int i1 = i0 + cur.n;
+          int slot = -1, nparts = 1;
+          if (nsteps != cur.n) {  // (warp-uniform)
+            nparts = count_parts(i0, i1);
+            slot = part_slot(hdr, range_c, range_j, range_begin, i0);
           }
+          rd.kind = 1, rd.hg = cur.hg, rd.step0 = cur.step, rd.nsteps = nsteps, rd.seq_len = cur.seq_len, rd.tq = cur.tq;
+          rd.item = item, rd.slot = slot, rd.nparts = nparts, rd.i0 = i0, rd.n = cur.n;
+        }
+        for (int s = 0; s < nsteps; ++s) {
+          const int tok0 = cur.step * P.tps;
+          const int ntok = min(P.tps, cur.seq_len - tok0);
+          const int nbox = (ntok + P.box_slots - 1) / P.box_slots;
+          const int head0 = cur.hg * P.hpc;
+          const int32_t* bt = P.a.block_tables + (int64_t)cur.b * P.a.bt_stride0;
+          const int npages = (cur.seq_len + P.a.block_size - 1) >> P.bs_shift;
+          const int p_first = tok0 >> P.bs_shift;
+          const int base = p_first & ~127;
+          if (cur.b != win_b || base != win_base) {
+            if (cur.b == win_b && base == win_base + 128) {
+#pragma unroll
+              for (int r = 0; r < 4; ++r) ids[r] = nxt[r];
+            } else {
+              load_ids(ids, bt, base, npages);
+            }
+            load_ids(nxt, bt, base + 128, npages);
+            win_b = cur.b, win_base = base;
+          }
+          auto page_of = [&](int pg) {  // warp-collective: every lane asks for one page id
+            const int src = pg & 31, r = (pg >> 5) & 3;
+            const int v0 = __shfl_sync(0xffffffffu, ids[0], src), v1 = __shfl_sync(0xffffffffu, ids[1], src);
+            const int v2 = __shfl_sync(0xffffffffu, ids[2], src), v3 = __shfl_sync(0xffffffffu, ids[3], src);
+            return r == 0 ? v0 : (r == 1 ? v1 : (r == 2 ? v2 : v3));
+          };
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          if (s == 0) {
+            // Publish the run.  Its slot held descriptor ndesc - kDescSlots; the stage just waited for was last used
+            // by a step of run >= ndesc - stages, and a consumer reads a run's descriptor before it releases any of
+            // the run's stages, so every consumer is done with the old contents (kDescSlots > kMaxStages + 1).
+            const int ds = ndesc & (kDescSlots - 1);
+            if (lane == 0) {
+              descs[ds] = rd;
+              mbar_arrive(&desc_bar[ds]);  // release: the stores above are visible to whoever sees the phase flip
+            }
+            ++ndesc;
+          }
+          uint8_t* kdst = stage_base + (size_t)stage * 2 * KV_STAGE_BYTES;
+          uint8_t* vdst = kdst + KV_STAGE_BYTES;
+          if (lane == 0) mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)(2 * nbox * boxb));
+          __syncwarp();
+          if (P.paired) {
+            // k_map's third coordinate selects K (0) or V (1); the box takes both
+            const int i = lane;
+            const int tok = tok0 + i * P.box_slots;
+            const int page = page_of(tok >> P.bs_shift);
+            if (i < nbox)
+              tma_load_5d(kdst + (size_t)i * 2 * boxb, &k_map, &full_bar[stage], 0, tok & (P.a.block_size - 1), 0, head0, page, pol);
+          } else if (P.tma_split == 0) {
+            // nbox <= 8: one lane per box
+            const int i = lane;
+            const int tok = tok0 + i * P.box_slots;
+            const int page = page_of(tok >> P.bs_shift);  // lanes past nbox read a don't-care id
+            if (i < nbox) {
+              const int slot0 = tok & (P.a.block_size - 1);
+              tma_load_5d(kdst + (size_t)i * boxb, &k_map, &full_bar[stage], 0, slot0, 0, head0, page, pol);
+              tma_load_5d(vdst + (size_t)i * boxb, &v_map, &full_bar[stage], 0, slot0, 0, head0, page, pol);
+            }
+          } else {
+            const int per_box = P.hpc * NDC;
+            const int units = nbox * per_box;
+            for (int u0 = 0; u0 < units; u0 += 32) {
+              const int u = u0 + lane;
+              const int i = min(u / per_box, nbox - 1), r = u % per_box, h = r / NDC, dc = r % NDC;
+              const int tok = tok0 + i * P.box_slots;
+              const int page = page_of(tok >> P.bs_shift);
+              if (u < units) {
+                const int slot0 = tok & (P.a.block_size - 1);
+                const size_t off = (size_t)i * boxb + (size_t)(h * NDC + dc) * P.box_slots * 128;
+                tma_load_5d(kdst + off, &k_map, &full_bar[stage], 0, slot0, dc, head0 + h, page, pol);
+                tma_load_5d(vdst + off, &v_map, &full_bar[stage], 0, slot0, dc, head0 + h, page, pol);
+              }
+            }
+          }
+          if (++stage == P.stages) stage = 0, phase ^= 1;
+          if (pooled && !next_loaded) {
+            // the chunk counter has come back by now: fetch where the next chunk starts while this range streams
+            next_loaded = true;
+            next_chunk = __shfl_sync(0xffffffffu, next_chunk, 0);
+            if (next_chunk < hdr.n_chunks) load_cursor(&P.plan->chunk[next_chunk], next_cur);
+          }
+          // next step (the last step of the range must not run past the end of the batch)
+          if (cur.flat + 1 < range_end) cursor_next(P, cur);
+          else cur.flat++;
+        }
+        have_range = cur.flat < range_end;
+      }
+      if (!pooled) break;
+      if (!next_loaded) {
+        next_chunk = __shfl_sync(0xffffffffu, next_chunk, 0);
+        if (next_chunk < hdr.n_chunks) load_cursor(&P.plan->chunk[next_chunk], next_cur);
+      }
+      if (next_chunk >= hdr.n_chunks) break;
+      range_c = next_chunk % hdr.grid, range_j = 1 + next_chunk / hdr.grid;
+      part_range(hdr, range_c, range_j, range_begin, range_end);
+      cur = next_cur;
+      have_range = cur.b >= 0 && cur.flat < range_end;  // (chunks of a range cut short by the end of the batch are empty)
+    }
+    // no more work
+    {
+      const int ds = ndesc & (kDescSlots - 1);
+      if (lane == 0) {
+        descs[ds].kind = 0;
+        mbar_arrive(&desc_bar[ds]);
+      }
+    }
+    if (pooled && lane == 0) {
+      // the CTA that is last to stop taking chunks rewinds the counters for the next launch
+      __threadfence();
+      if (atomicAdd(&P.ws_pool[1], 1) == (int)gridDim.x - 1) {
+        __threadfence();
+        P.ws_pool[0] = 0;
+        P.ws_pool[1] = 0;
+      }
+    }
+    return;
+  }
+
+  if (warp == NW + 1) {
+    // ======================= ticket warp ====================================
+    // Takes the ticket of every partial the consumers hand over - a fence and an atomic round trip the consumers
+    // would otherwise sit through at every partial run (a bubble of several microseconds in this SM's HBM stream:
+    // profiles/r02_kbench_pool_v1.jsonl).  The part that takes an item's LAST ticket must merge the item: that is
+    // handed back to the eight consumer warps, which do it together at their next run boundary (one warp takes
+    // 10 us for a ten-part item, profiles/r02_kbench_pool_v3_tail_chunks.jsonl).
+    int nreq = 0;
+    for (int nf = 0;; ++nf) {
+      const int fs = nf % kFinSlots;
+      mbar_wait(&fin_full[fs], ((uint32_t)nf / kFinSlots) & 1u);
+      const FinDesc f = fins[fs];
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&fin_empty[fs]);
+      if (f.kind == 0) break;
+      int ticket = 0;
+      if (lane == 0) {
+        __threadfence();  // the consumers' partial stores (ordered before this by the hand-off) before the ticket
+        ticket = atomicAdd(&P.ws_cnt[f.item], 1);
+        if (ticket == f.nparts - 1) {
+          __threadfence();  // every other part's partial is visible from here on
+          while (nreq - req_cnt[1] >= kReqSlots) {}  // (the consumers serve requests at every run boundary)
+          reqs[nreq % kReqSlots] = f;
+          __threadfence_block();
+          req_cnt[0] = nreq + 1;
         }
       }
-      if (++stage == P.stages) stage = 0, phase ^= 1;
-      if (cur.flat + 1 >= my_end) break;
-      cursor_next(P, cur);
+      ticket = __shfl_sync(0xffffffffu, ticket, 0);
+      if (ticket == f.nparts - 1) ++nreq;
     }
+    if (lane == 0) mbar_arrive(epi_done);  // release: every request was posted before this
+    if (trace && lane == 0) trace[5] = clock64(), trace[6] = global_ns();
     return;
   }
 
@@ -486,8 +657,8 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
     for (int nt = 0; nt < NT; ++nt) m_run[nt][0] = m_run[nt][1] = -INFINITY, l_run[nt][0] = l_run[nt][1] = 0.f;
   };
 
-  auto load_q = [&](int tq) {
-    const int kvh = cur.hg * P.hpc + h_local;
+  auto load_q = [&](int tq, int hg) {
+    const int kvh = hg * P.hpc + h_local;
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt) {
       const int hq_local = nt * 8 + gid;
@@ -528,10 +699,156 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
     }
   };
 
+  // sequences with one query token and no visible key get zeros (reference reduce_segments :828); no run visits them
+  if (P.plan->hdr.has_zero_rows) {
+    for (int b = blockIdx.x; b < P.a.num_seqs; b += gridDim.x) {
+      const int sl = P.a.seq_lens[b];
+      const int ql = P.a.cu_seqlens_q ? (P.a.cu_seqlens_q[b + 1] - P.a.cu_seqlens_q[b]) : 1;
+      if (sl <= 0 && ql == 1) {
+        const int tq = P.a.cu_seqlens_q ? P.a.cu_seqlens_q[b] : b;
+        for (int e = threadIdx.x; e < P.a.num_q_heads * D; e += NW * 32) {
+          const int osz = P.a.out_scale ? 1 : 2;  // fp8 output: one byte per element, 0x00 == +0
+          char* orow = static_cast<char*>(P.a.out) + ((int64_t)tq * P.a.out_stride0 + (int64_t)(e / D) * P.a.out_stride1) * osz;
+          if (osz == 1) orow[e % D] = 0;
+          else reinterpret_cast<uint16_t*>(orow)[e % D] = 0;
+        }
+      }
+    }
+  }
+
+  // ---- merging an item whose last ticket this CTA's ticket warp took (the reference's `reduce_segments` launch,
+  // :757-836): all consumer warps together, at a run boundary.  Warp 0 lists the item's parts in flat order - every
+  // (range, part) that overlaps [i0, i1), one candidate per lane - then every thread owns (query head, 4 dims)
+  // chunks and folds the parts in groups of G with all of a group's loads in flight at once.
+  int reqs_done = 0;
+  auto merge_item = [&](const FinDesc f) {
+    __threadfence();
+    const int rec_heads = P.hpc * P.group;
+    if (warp == 0) {
+      const PlanHeader hdr = P.plan->hdr;
+      const int J = 1 + hdr.n_rounds;
+      const int i0 = f.i0, i1 = f.i0 + f.n;
+      const int ca = i0 / hdr.per, ncand = ((i1 - 1) / hdr.per - ca + 1) * J;
+      int np = 0;
+      for (int base = 0; base < ncand; base += 32) {
+        const int idx = base + lane;
+        bool hit = false;
+        int slot = 0;
+        if (idx < ncand) {
+          const int c = ca + idx / J, j = idx % J;
+          int pb, pe;
+          part_range(hdr, c, j, pb, pe);
+          hit = max(pb, i0) < min(pe, i1);
+          slot = part_slot(hdr, c, j, pb, i0);
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, hit);
+        if (hit) part_slots[np + __popc(m & ((1u << lane) - 1u))] = (short)slot;
+        np += __popc(m);
+      }
+      if (lane == 0) req_cnt[3] = np;  // == f.nparts: the producers counted the same candidates
+    }
+    asm volatile("bar.sync 1, %0;" ::"r"(NW * 32));
+    const int nparts = req_cnt[3];
+    constexpr int D4 = D / 4;
+    constexpr int G = 8;
+    for (int e = threadIdx.x; e < rec_heads * D4; e += NW * 32) {
+      const int hq_in = e / D4, d4 = (e % D4) * 4;
+      float M = -INFINITY, L = 0.f;
+      float4 val = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int p0 = 0; p0 < nparts; p0 += G) {
+        float2 ml[G];
+        float4 av[G];
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+          if (p0 + g < nparts) {
+            const int64_t rec = (int64_t)part_slots[p0 + g] * rec_heads + hq_in;
+            ml[g] = __ldcg(reinterpret_cast<const float2*>(&P.ws_ml[rec * 2]));
+            av[g] = __ldcg(reinterpret_cast<const float4*>(&P.ws_acc[rec * D + d4]));
+          } else {
+            ml[g] = make_float2(-INFINITY, 0.f), av[g] = make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+        }
+        float mg = M;
+#pragma unroll
+        for (int g = 0; g < G; ++g) mg = fmaxf(mg, ml[g].x);
+        const float so = (M == -INFINITY) ? 0.f : ex2(M - mg);  // (mg = -inf only if M is)
+        val.x *= so, val.y *= so, val.z *= so, val.w *= so, L *= so;
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+          const float sc = (ml[g].x == -INFINITY) ? 0.f : ex2(ml[g].x - mg);
+          val.x += av[g].x * sc, val.y += av[g].y * sc, val.z += av[g].z * sc, val.w += av[g].w * sc;
+          L += ml[g].y * sc;
+        }
+        M = mg;
+      }
+      const int hq = f.hg * rec_heads + hq_in;
+      float fsink = 1.f;
+      if (P.a.sinks) fsink = sink_rescale<true>(P.a.sinks[hq], M, L);  // once per item, here (upstream: segment 0 only)
+      const float inv = (L > 0.f) ? fsink * v_scale / L : 0.f;  // 0 when nothing is visible (reference :828)
+      const int64_t oel = (int64_t)f.tq * P.a.out_stride0 + (int64_t)hq * P.a.out_stride1;
+      const float o4[4] = {val.x * inv, val.y * inv, val.z * inv, val.w * inv};
+      if (P.a.out_scale) {
+        const float oq = out_quant_factor(P.a.out_scale);
+        *reinterpret_cast<uint32_t*>(static_cast<char*>(P.a.out) + oel + d4) = fp8x4_out(o4[0] * oq, o4[1] * oq, o4[2] * oq, o4[3] * oq);
+      } else {
+        char* orow = static_cast<char*>(P.a.out) + oel * 2;
+        *reinterpret_cast<uint2*>(orow + d4 * 2) = make_uint2(pack2<Q_BF16>(o4[0], o4[1]), pack2<Q_BF16>(o4[2], o4[3]));
+      }
+    }
+    if (threadIdx.x == 0) P.ws_cnt[f.item] = 0;  // self-cleaning: ready for the next call
+    asm volatile("bar.sync 1, %0;" ::"r"(NW * 32));  // part_slots is rewritten by the next merge
+  };
+  // Serves the ticket warp's merge requests; every consumer warp calls it at the same points.  Returns true once
+  // the ticket warp has finished (it posts every request before it says so).
+  auto serve_requests = [&]() {
+    if (threadIdx.x == 0) {
+      const int fin = mbar_try_wait(epi_done, 0) ? 1 : 0;  // first: what is posted before this is counted below
+      req_cnt[2] = req_cnt[0] | (fin << 30);
+    }
+    asm volatile("bar.sync 1, %0;" ::"r"(NW * 32));
+    const int v = req_cnt[2];
+    asm volatile("bar.sync 1, %0;" ::"r"(NW * 32));  // everyone has read it before thread 0 writes the next one
+    const int upto = v & 0x3fffffff;
+    while (reqs_done < upto) {
+      const FinDesc f = reqs[reqs_done % kReqSlots];
+      merge_item(f);
+      ++reqs_done;
+      if (threadIdx.x == 0) req_cnt[1] = reqs_done;
+    }
+    return (v >> 30) != 0;
+  };
+
+  // hand-off to the ticket warp (kFinSlots slots; every consumer warp arrives, warp 0 writes the descriptor)
+  RunDesc run = {};
+  int nfin = 0;
+  auto publish_fin = [&](int kind, int item, int hg, int tq) {
+    const int fs = nfin % kFinSlots;
+    mbar_wait(&fin_empty[fs], (((uint32_t)nfin / kFinSlots) & 1u) ^ 1u);  // the slot's previous hand-off has been taken
+    if (warp == 0 && lane == 0) {
+      FinDesc& f = fins[fs];
+      f.kind = kind, f.item = item, f.hg = hg, f.tq = tq, f.nparts = run.nparts, f.i0 = run.i0, f.n = run.n;
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&fin_full[fs]);  // release: this warp's partial stores (and the descriptor) come first
+    ++nfin;
+  };
+
+  // ---- runs ------------------------------------------------------------------------------------
+  struct { int hg, step, seq_len; } cur;  // the step being consumed
+  int nd = 0;                             // descriptors taken so far
+  mbar_wait(&desc_bar[0], 0);
+  run = descs[0];
+  if (trace && threadIdx.x == 0) trace[2] = clock64();
+  if (run.kind == 0) {
+    if (trace && threadIdx.x == 0) trace[3] = trace[4] = clock64();
+    publish_fin(0, 0, 0, 0);
+    return;
+  }
+  cur.hg = run.hg, cur.step = run.step0, cur.seq_len = run.seq_len;
   reset_state();
-  load_q(tq_first);
-  int tq_cur = tq_first;
+  load_q(run.tq, run.hg);
   bool first_stage = true;
+  int steps_left = run.nsteps;
 
   int stage = 0;
   uint32_t phase = 0;
@@ -725,23 +1042,21 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
     if (lane == 0) mbar_arrive(&empty_bar[stage]);
     if (++stage == P.stages) stage = 0, phase ^= 1;
 
-    const bool item_end = (cur.step + 1 == cur.first + cur.n);
-    const bool last = (cur.flat + 1 >= my_end);
-    if (item_end || last) {
-      // ---------------- finalise this (sequence, head group) ------------------
-      const int item = cur.b * P.head_groups + cur.hg;
-      const int item_flat0 = cur.flat - (cur.step - cur.first);
-      const int hg_done = cur.hg, n_done = cur.n;
-      const bool direct = item_flat0 >= my_begin && item_flat0 + n_done <= my_end;
-      const int tq = tq_cur;
-      // Move on to the next item first: its dependent global loads (seq_lens / cu_seqlens_q, then the query
-      // rows) are in flight while this item is merged and stored.  The query fragments are dead after the
-      // item's last tile; the accumulators are reset only after the merge has read them.
-      if (!last) {
-        cursor_next(P, cur);
-        tq_cur = P.a.cu_seqlens_q ? P.a.cu_seqlens_q[cur.b] : cur.b;
-        load_q(tq_cur);
-      }
+    ++cur.step;
+    if (--steps_left == 0) {
+      // ---------------- finalise this run ------------------
+      const int item = run.item;
+      const int hg_done = run.hg;
+      const bool direct = run.slot < 0;
+      const int tq = run.tq;
+      // Take the next run first: its query rows are in flight while this one is merged and stored.  The query
+      // fragments are dead after the run's last tile; the accumulators are reset only after the merge has
+      // read them.  (The producer publishes a run when it issues its first step, stages ahead of this point.)
+      ++nd;
+      mbar_wait(&desc_bar[nd & (kDescSlots - 1)], (uint32_t)(nd / kDescSlots) & 1u);
+      const RunDesc nx = descs[nd & (kDescSlots - 1)];
+      const bool last = nx.kind == 0;
+      if (!last) load_q(nx.tq, nx.hg);
       if (trace && threadIdx.x == 0) {
         if (last) trace[4] = clock64();
         trace[7] += 1;
@@ -803,106 +1118,35 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
               else reinterpret_cast<__half*>(orow)[d] = __float2half_rn(o);
             }
           } else {
-            const int64_t slot = (int64_t)item + blockIdx.x;
-            const int64_t rec = slot * (P.hpc * P.group) + hq_in_cta;
+            const int64_t rec = (int64_t)run.slot * (P.hpc * P.group) + hq_in_cta;
             P.ws_acc[rec * D + d] = val;
             if (d == 0) P.ws_ml[rec * 2] = M, P.ws_ml[rec * 2 + 1] = L;
           }
         }
       }
-      if (!direct) {
-        // ---- ticket: the CTA that completes the item merges its partials ------
-        const int first_cta = item_flat0 / per_cta;
-        const int last_cta = (item_flat0 + n_done - 1) / per_cta;
-        __threadfence();  // partials visible device-wide before the ticket
-        asm volatile("bar.sync 1, %0;" ::"r"(NW * 32));
-        if (threadIdx.x == 0) {
-          const int ticket = atomicAdd(&P.ws_cnt[item], 1);
-          s_part[6] = (ticket == last_cta - first_cta) ? 1 : 0;
-        }
-        asm volatile("bar.sync 1, %0;" ::"r"(NW * 32));
-        if (s_part[6]) {
-          __threadfence();
-          // Every thread owns (query head, 4 dims) chunks; the (max, exp-sum) pair and the
-          // float4 of every part are requested before any of them is used, so a chunk costs
-          // one L2 round trip (a loop that first reduces the maxima costs two per element,
-          // which was 20 us of tail at 4 kv heads per CTA).
-          const int rec_heads = P.hpc * P.group;
-          const int nparts = last_cta - first_cta + 1;
-          constexpr int D4 = D / 4;
-          for (int e = threadIdx.x; e < rec_heads * D4; e += NW * 32) {
-            const int hq_in = e / D4, d4 = (e % D4) * 4;
-            const int64_t rec0 = ((int64_t)item + first_cta) * rec_heads + hq_in;
-            float M = -INFINITY, L = 0.f;
-            float4 val = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (nparts <= 4) {
-              float2 ml[4];
-              float4 av[4];
-#pragma unroll
-              for (int c = 0; c < 4; ++c) {
-                if (c < nparts) {
-                  const int64_t rec = rec0 + (int64_t)c * rec_heads;
-                  ml[c] = __ldcg(reinterpret_cast<const float2*>(&P.ws_ml[rec * 2]));
-                  av[c] = __ldcg(reinterpret_cast<const float4*>(&P.ws_acc[rec * D + d4]));
-                } else {
-                  ml[c] = make_float2(-INFINITY, 0.f), av[c] = make_float4(0.f, 0.f, 0.f, 0.f);
-                }
-              }
-#pragma unroll
-              for (int c = 0; c < 4; ++c) M = fmaxf(M, ml[c].x);
-#pragma unroll
-              for (int c = 0; c < 4; ++c) {
-                const float sc = (ml[c].x == -INFINITY) ? 0.f : ex2(ml[c].x - M);
-                val.x += av[c].x * sc, val.y += av[c].y * sc, val.z += av[c].z * sc, val.w += av[c].w * sc;
-                L += ml[c].y * sc;
-              }
-            } else {
-              for (int c = 0; c < nparts; ++c) M = fmaxf(M, __ldcg(&P.ws_ml[(rec0 + (int64_t)c * rec_heads) * 2]));
-#pragma unroll 4
-              for (int c = 0; c < nparts; ++c) {
-                const int64_t rec = rec0 + (int64_t)c * rec_heads;
-                const float2 ml = __ldcg(reinterpret_cast<const float2*>(&P.ws_ml[rec * 2]));
-                const float4 av = __ldcg(reinterpret_cast<const float4*>(&P.ws_acc[rec * D + d4]));
-                const float sc = (ml.x == -INFINITY) ? 0.f : ex2(ml.x - M);
-                val.x += av.x * sc, val.y += av.y * sc, val.z += av.z * sc, val.w += av.w * sc;
-                L += ml.y * sc;
-              }
-            }
-            const int hq = hg_done * rec_heads + hq_in;
-            float fs = 1.f;
-            if (P.a.sinks) fs = sink_rescale<true>(P.a.sinks[hq], M, L);  // once per item, here (upstream: segment 0 only)
-            const float inv = (L > 0.f) ? fs * v_scale / L : 0.f;  // 0 when nothing is visible (reference :828)
-            const int64_t oel = (int64_t)tq * P.a.out_stride0 + (int64_t)hq * P.a.out_stride1;
-            const float o4[4] = {val.x * inv, val.y * inv, val.z * inv, val.w * inv};
-            if (P.a.out_scale) {
-              const float oq = out_quant_factor(P.a.out_scale);
-              *reinterpret_cast<uint32_t*>(static_cast<char*>(P.a.out) + oel + d4) = fp8x4_out(o4[0] * oq, o4[1] * oq, o4[2] * oq, o4[3] * oq);
-            } else {
-              char* orow = static_cast<char*>(P.a.out) + oel * 2;
-#pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                if constexpr (Q_BF16) reinterpret_cast<__nv_bfloat16*>(orow)[d4 + j] = __float2bfloat16_rn(o4[j]);
-                else reinterpret_cast<__half*>(orow)[d4 + j] = __float2half_rn(o4[j]);
-              }
-            }
-          }
-          if (threadIdx.x == 0) P.ws_cnt[item] = 0;  // self-cleaning: ready for the next call
-        }
-      }
+      if (!direct) publish_fin(1, item, hg_done, tq);  // the partial is on its way to memory: its ticket is the ticket warp's
+      serve_requests();                                // items this CTA has to merge
       if (last) break;
-      asm volatile("bar.sync 1, %0;" ::"r"(NW * 32));  // merge buffers are reused by the next item
+      asm volatile("bar.sync 1, %0;" ::"r"(NW * 32));  // merge buffers are reused by the next run
       reset_state();
-    } else {
-      cursor_next(P, cur);
+      run = nx;
+      cur.hg = run.hg, cur.step = run.step0, cur.seq_len = run.seq_len;
+      steps_left = run.nsteps;
     }
   }
-  if (trace && threadIdx.x == 0) trace[5] = clock64(), trace[6] = global_ns();
+  publish_fin(0, 0, 0, 0);  // no more partials from this CTA
+  while (!serve_requests()) {}  // merge what the ticket warp still hands back, until it has taken its last ticket
 }
 
 // ---- host side ------------------------------------------------------------------
-struct DecodeConfig {
-  int nw, nt, hpc, stages, smem_bytes, grid;
+// Everything the plan and the launch must agree on, from host ints only.
+struct DecodeGeom {
+  int D, nt, nw, tt, fp8;
+  int hpc, head_groups, tps, tps_shift, bs_shift, box_slots, boxes, grid;
+  int pool_sixteenths, min_chunk;
 };
+
+inline bool pow2(int x) { return x > 0 && (x & (x - 1)) == 0; }
 
 inline int pick_hpc(int hkv, int nw, int want) {
   int hpc = 1;
@@ -914,11 +1158,71 @@ inline int pick_hpc(int hkv, int nw, int want) {
   return hpc;
 }
 
+int decode_geometry(const b200attn_attention_params& a, DecodeGeom* G) {
+  const Tuning& tn = tuning();
+  const DeviceInfo& dev = device_info();
+  const int group = a.num_q_heads / a.num_kv_heads;
+  G->D = a.head_size, G->fp8 = a.kv_dtype == B200ATTN_FP8_E4M3 ? 1 : 0;
+  G->nt = group > 8 ? 2 : 1;
+  G->nw = a.head_size == 256 ? 4 : 8;
+  // fp8: two 16-token sub-tiles per warp and step (a stage of 8 x 32 tokens is the size a bf16
+  // stage of 8 x 16 has); the tile's latency chain, not HBM, bounds this variant otherwise.  (NT = 2 would spill.)
+  G->tt = (G->fp8 && G->D == 128 && G->nt == 1) ? 32 : 16;
+  const int esz = G->fp8 ? 1 : 2, ndc = G->D * esz / 128;
+  if (tn.decode_heads_per_cta > 0) {
+    G->hpc = pick_hpc(a.num_kv_heads, G->nw, tn.decode_heads_per_cta);
+  } else {
+    // Fewest kv heads per CTA whose TMA box is still big enough: more
+    // (sequence, head group) items means more outputs written directly and
+    // parallel merges, but the copy engine pays per box (measured on B200,
+    // profiles/r01_decode_sweep_v2.jsonl: bf16 KV is best at 4 KB boxes, fp8 at 8 KB).
+    const int min_box = G->fp8 ? 8192 : 4096;
+    int hpc = 1;
+    while (hpc < G->nw && a.num_kv_heads % (hpc * 2) == 0) {
+      const int tps = G->nw * G->tt / hpc;
+      const int slots = a.block_size < tps ? a.block_size : tps;
+      if (hpc * ndc * slots * 128 >= min_box) break;
+      hpc *= 2;
+    }
+    G->hpc = hpc;
+  }
+  G->head_groups = a.num_kv_heads / G->hpc;
+  G->tps = G->nw * G->tt / G->hpc;
+  for (G->tps_shift = 0; (1 << G->tps_shift) < G->tps; ++G->tps_shift) {}
+  for (G->bs_shift = 0; (1 << G->bs_shift) < a.block_size; ++G->bs_shift) {}
+  if ((1 << G->tps_shift) != G->tps || (1 << G->bs_shift) != a.block_size) {
+    set_error("decode: tokens per step (%d) and block_size (%d) must be powers of two", G->tps, a.block_size);
+    return B200ATTN_E_UNSUPPORTED;
+  }
+  G->box_slots = a.block_size < G->tps ? a.block_size : G->tps;
+  G->boxes = G->tps / G->box_slots;
+  // One CTA per SM whatever the batch (CTAs the plan gives nothing exit at once): the plan is built for a
+  // grid, and a grid that followed max_seqlen_k would differ between a captured launch and its replays.
+  G->grid = dev.num_sms < kMaxDecodeCtas ? dev.num_sms : kMaxDecodeCtas;
+  if (G->grid < 1) G->grid = 1;
+  // pool share: tuning().decode_ctas_per_sm re-used as "sixteenths of a CTA's steps" (0 = default, >= 100 = none)
+  G->pool_sixteenths = tn.decode_ctas_per_sm <= 0 ? 3 : (tn.decode_ctas_per_sm >= 100 ? 0 : (tn.decode_ctas_per_sm > 12 ? 12 : tn.decode_ctas_per_sm));
+  G->min_chunk = (tn.reserved & 1024) ? 1 : ((tn.reserved & 2048) ? 4 : 2);
+  return B200ATTN_OK;
+}
+
+uint64_t decode_plan_key(const b200attn_attention_params& a, const DecodeGeom& G, bool only_q1) {
+  uint64_t h = 0xcbf29ce484222325ull;
+  auto mix = [&](uint64_t v) { h = (h ^ v) * 0x100000001b3ull; };
+  mix((uint64_t)a.num_seqs), mix((uint64_t)G.tps_shift), mix((uint64_t)G.head_groups), mix((uint64_t)(uint32_t)a.sliding_window);
+  mix(only_q1 ? 1 : 0), mix((uint64_t)G.grid), mix((uint64_t)G.pool_sixteenths), mix((uint64_t)G.min_chunk);
+  return h | 1ull;  // never 0: 0 means "no plan"
+}
+
 template <int D, bool KV_FP8, bool MMA_BF16, bool Q_BF16, int NT, int NW, int TT>
-int launch_variant(const b200attn_attention_params& a, DecodeParams& P, cudaStream_t stream) {
+int launch_variant(const b200attn_attention_params& a, const DecodeGeom& G, DecodeParams& P, cudaStream_t stream) {
   constexpr int ESZ = KV_FP8 ? 1 : 2;
   constexpr int NDC = D * ESZ / 128;
   constexpr int KV_STAGE_BYTES = NW * TT * D * ESZ;
+  if (G.nw != NW || G.tt != TT || G.nt != NT) {
+    set_error("decode: internal geometry mismatch");
+    return B200ATTN_E_UNSUPPORTED;
+  }
   const DeviceInfo& dev = device_info();
   const Tuning& tn = tuning();
   // K and V of a page in ONE box when they are two equally strided views of one allocation
@@ -928,36 +1232,11 @@ int launch_variant(const b200attn_attention_params& a, DecodeParams& P, cudaStre
   const bool can_pair = KV_FP8 && NDC == 1 && !(tn.reserved & 8) && !(tn.reserved & 1) && kv_delta > 0 &&
                         kv_delta % 16 == 0 && kv_delta < (1ll << 40) && a.kc_block_stride == a.vc_block_stride &&
                         a.kc_slot_stride == a.vc_slot_stride && a.kc_head_stride == a.vc_head_stride;
-  if (tn.decode_heads_per_cta > 0) {
-    P.hpc = pick_hpc(a.num_kv_heads, NW, tn.decode_heads_per_cta);
-  } else {
-    // Fewest kv heads per CTA whose TMA box is still big enough: more
-    // (sequence, head group) items means more outputs written directly and
-    // parallel merges, but the copy engine pays per box (measured on B200,
-    // profiles/r01_decode_sweep_v2.jsonl: bf16 KV is best at 4 KB boxes, fp8 at 8 KB).
-    const int min_box = KV_FP8 ? 8192 : 4096;
-    int hpc = 1;
-    while (hpc < NW && a.num_kv_heads % (hpc * 2) == 0) {
-      const int tps = NW * TT / hpc;
-      const int slots = a.block_size < tps ? a.block_size : tps;
-      if (hpc * NDC * slots * 128 >= min_box) break;
-      hpc *= 2;
-    }
-    P.hpc = hpc;
-  }
-  P.head_groups = a.num_kv_heads / P.hpc;
-  P.tps = NW * TT / P.hpc;
-  for (P.tps_shift = 0; (1 << P.tps_shift) < P.tps; ++P.tps_shift) {}
-  for (P.bs_shift = 0; (1 << P.bs_shift) < a.block_size; ++P.bs_shift) {}
-  if ((1 << P.tps_shift) != P.tps || (1 << P.bs_shift) != a.block_size) {
-    set_error("decode: tokens per step (%d) and block_size (%d) must be powers of two", P.tps, a.block_size);
-    return B200ATTN_E_UNSUPPORTED;
-  }
-  P.box_slots = a.block_size < P.tps ? a.block_size : P.tps;
-  P.boxes = P.tps / P.box_slots;
+  P.hpc = G.hpc, P.head_groups = G.head_groups, P.tps = G.tps, P.tps_shift = G.tps_shift, P.bs_shift = G.bs_shift;
+  P.box_slots = G.box_slots, P.boxes = G.boxes;
   P.tma_split = tn.reserved & 1;
-  P.paired = 0;
-  const int fixed = NW * 8 * D * 4 + NW * 8 * 2 * 4 + 2 * kMaxStages * 8 + 64 + 1024 /*alignment slack*/;
+  const int fixed = NW * 8 * D * 4 + NW * 8 * 2 * 4 + (2 * kMaxStages + kDescSlots + 2 * kFinSlots + 1) * 8 +
+                    kDescSlots * (int)sizeof(RunDesc) + (kFinSlots + kReqSlots) * (int)sizeof(FinDesc) + 16 + kMaxParts * 2;
   int stages = (dev.max_smem_optin - fixed) / (2 * KV_STAGE_BYTES);
   if (stages > kMaxStages) stages = kMaxStages;
   if (tn.decode_stages > 0 && tn.decode_stages < stages) stages = tn.decode_stages;
@@ -978,19 +1257,13 @@ int launch_variant(const b200attn_attention_params& a, DecodeParams& P, cudaStre
                    a.vc_slot_stride, a.vc_head_stride, P.box_slots, box_heads, box_dc);
   if (rc) return rc;
 
-  // grid: one CTA per SM, never more CTAs than the upper bound on steps
-  const long long max_steps =
-      (long long)a.num_seqs * P.head_groups * ((a.max_seqlen_k + P.tps - 1) / P.tps > 0 ? (a.max_seqlen_k + P.tps - 1) / P.tps : 1);
-  long long grid = dev.num_sms < kMaxDecodeCtas ? dev.num_sms : kMaxDecodeCtas;
-  if (grid > max_steps && !launch_is_captured()) grid = max_steps;
-  if (grid < 1) grid = 1;
-
   auto kern = attn_decode_kernel<D, KV_FP8, MMA_BF16, Q_BF16, NT, NW, TT>;
-  if (int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(kern), dev.max_smem_optin, "decode")) return rc;
-  // Programmatic dependent launch: lets this grid's launch and prologue overlap the cache write in front of it
-  // (common.cuh).  tuning().reserved bit 9 turns it off.
+  if (int rc2 = ensure_dynamic_smem(reinterpret_cast<const void*>(kern), dev.max_smem_optin, "decode")) return rc2;
+  // Programmatic dependent launch: lets this grid's launch and prologue overlap the kernel in front of it
+  // (the cache write, the plan kernel or the previous decode launch - each releases its dependents early;
+  // common.cuh).  tuning().reserved bit 9 turns it off.
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3((unsigned)grid), cfg.blockDim = dim3((NW + 1) * 32), cfg.dynamicSmemBytes = (size_t)smem, cfg.stream = stream;
+  cfg.gridDim = dim3((unsigned)G.grid), cfg.blockDim = dim3((NW + 2) * 32), cfg.dynamicSmemBytes = (size_t)smem, cfg.stream = stream;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
@@ -1001,40 +1274,58 @@ int launch_variant(const b200attn_attention_params& a, DecodeParams& P, cudaStre
 }
 
 template <int D, int NT, int NW>
-int dispatch_types(const b200attn_attention_params& a, DecodeParams& P, cudaStream_t stream) {
+int dispatch_types(const b200attn_attention_params& a, const DecodeGeom& G, DecodeParams& P, cudaStream_t stream) {
   const bool qbf = a.q_dtype == B200ATTN_BF16;
   if (a.kv_dtype == B200ATTN_FP8_E4M3) {
     if constexpr (D >= 128) {
-      // fp8: two 16-token sub-tiles per warp and step (a stage of 8 x 32 tokens is the size a bf16
-      // stage of 8 x 16 has); the tile's latency chain, not HBM, bounds this variant otherwise
-      constexpr int TT = (D == 128 && NT == 1) ? 32 : 16;  // (NT = 2 would spill)
-      return qbf ? launch_variant<D, true, false, true, NT, NW, TT>(a, P, stream)
-                 : launch_variant<D, true, false, false, NT, NW, TT>(a, P, stream);
+      constexpr int TT = (D == 128 && NT == 1) ? 32 : 16;  // decode_geometry()
+      return qbf ? launch_variant<D, true, false, true, NT, NW, TT>(a, G, P, stream)
+                 : launch_variant<D, true, false, false, NT, NW, TT>(a, G, P, stream);
     } else {
       set_error("decode: fp8 KV needs head_size >= 128");
       return B200ATTN_E_UNSUPPORTED;
     }
   }
-  return qbf ? launch_variant<D, false, true, true, NT, NW, 16>(a, P, stream)
-             : launch_variant<D, false, false, false, NT, NW, 16>(a, P, stream);
+  return qbf ? launch_variant<D, false, true, true, NT, NW, 16>(a, G, P, stream)
+             : launch_variant<D, false, false, false, NT, NW, 16>(a, G, P, stream);
 }
 
-inline bool pow2(int x) { return x > 0 && (x & (x - 1)) == 0; }
+int launch_plan_kernel(const b200attn_attention_params& a, const DecodeGeom& G, bool only_q1, void* plan, cudaStream_t stream) {
+  PlanArgs A;
+  A.seq_lens = a.seq_lens, A.cu_seqlens_q = a.cu_seqlens_q, A.plan = static_cast<Plan*>(plan);
+  A.num_seqs = a.num_seqs, A.only_q1 = only_q1 ? 1 : 0, A.window = a.sliding_window, A.tps_shift = G.tps_shift;
+  A.head_groups = G.head_groups, A.grid = G.grid, A.pool_sixteenths = G.pool_sixteenths, A.min_chunk = G.min_chunk;
+  decode_plan_kernel<<<1, kPlanThreads, 0, stream>>>(A);
+  note_launch("decode_plan");
+  return check_launch("decode_plan");
+}
 
 }  // namespace
 
 // The ticket counters live in a region of FIXED size at the start of the workspace: they are the only bytes
 // that must be zero between calls, and the same buffer serves calls of every shape (a batch grows and shrinks
-// from step to step), so their region may never be another shape's partial-result region.
-constexpr uint64_t kCounterBytes = 1ull << 20;  // one int per (sequence, head group): 262144 items
+// from step to step), so their region may never be another shape's partial-result region.  Its last 64 bytes
+// hold the pool's chunk counter and the count of CTAs that have stopped taking chunks.
+constexpr uint64_t kCounterBytes = 1ull << 20;  // one int per (sequence, head group): 262128 items
+constexpr uint64_t kPoolCounterOffset = kCounterBytes - 64;
+
+uint64_t decode_plan_bytes(int num_seqs) {
+  return ((sizeof(Plan) + 4ull * ((uint64_t)(num_seqs > 0 ? num_seqs : 0) + 1) + 255) / 256) * 256;
+}
+
+static uint64_t decode_rows(int num_seqs, int num_q_heads, int num_kv_heads) {
+  // partial slots: two per part (static part of a range, pool chunk), each a record of hpc * group head rows;
+  // hpc <= 8 and hpc * group <= Hq.  Independent of the batch.
+  (void)num_seqs;
+  const uint64_t group = (uint64_t)(num_q_heads / (num_kv_heads > 0 ? num_kv_heads : 1));
+  uint64_t rec = 8 * (group > 0 ? group : 1);
+  if (rec > (uint64_t)num_q_heads) rec = (uint64_t)num_q_heads;
+  return (uint64_t)kMaxSlots * rec;
+}
 
 uint64_t decode_workspace_bytes(int num_seqs, int num_q_heads, int num_kv_heads, int head_size) {
-  // slots <= items + ctas; records of (hpc*group) heads: bounded by
-  // (B*Hq + ctas*8*group) head-rows of (D + 2) floats, after the counter region.
-  const uint64_t group = (uint64_t)(num_q_heads / (num_kv_heads > 0 ? num_kv_heads : 1));
-  const uint64_t ctas = kMaxDecodeCtas;  // the grid is min(#SMs, kMaxDecodeCtas)
-  const uint64_t rows = (uint64_t)num_seqs * num_q_heads + ctas * 8 * (group > 0 ? group : 1);
-  return kCounterBytes + rows * (uint64_t)(head_size + 2) * 4 + 1024;
+  const uint64_t rows = decode_rows(num_seqs, num_q_heads, num_kv_heads);
+  return kCounterBytes + ((rows * 8 + 255) / 256) * 256 + rows * (uint64_t)head_size * 4 + decode_plan_bytes(num_seqs) + 1024;
 }
 
 bool decode_supported(const b200attn_attention_params& p, const char** why, bool mixed_batch) {
@@ -1058,6 +1349,30 @@ bool decode_supported(const b200attn_attention_params& p, const char** why, bool
   return true;
 }
 
+// b200attn_decode_plan: the plan of the decode launches that will follow with these seq_lens / cu_seqlens_q
+// (one per layer).  *key_out = 0 when the shape does not run the split-KV kernel (nothing to plan).
+int build_decode_plan(const b200attn_attention_params& a, void* plan, uint64_t plan_bytes, uint64_t* key_out,
+                      cudaStream_t stream) {
+  if (key_out) *key_out = 0;
+  const bool only_q1 = a.max_seqlen_q > 1;
+  const char* why = nullptr;
+  if (!decode_supported(a, &why, only_q1)) return B200ATTN_OK;
+  if (!plan || plan_bytes < decode_plan_bytes(a.num_seqs)) {
+    set_error("decode_plan: plan buffer too small (%llu < %llu bytes)", (unsigned long long)plan_bytes,
+              (unsigned long long)decode_plan_bytes(a.num_seqs));
+    return B200ATTN_E_WORKSPACE;
+  }
+  if (reinterpret_cast<uintptr_t>(plan) & 15) {
+    set_error("decode_plan: plan buffer must be 16-byte aligned");
+    return B200ATTN_E_ALIGNMENT;
+  }
+  DecodeGeom G;
+  if (int rc = decode_geometry(a, &G)) return rc;
+  if (int rc = launch_plan_kernel(a, G, only_q1, plan, stream)) return rc;
+  if (key_out) *key_out = decode_plan_key(a, G, only_q1);
+  return B200ATTN_OK;
+}
+
 int launch_attn_decode(const b200attn_attention_params& a, cudaStream_t stream, bool only_single_token_seqs) {
   const char* why = nullptr;
   if (!decode_supported(a, &why, only_single_token_seqs)) {
@@ -1070,35 +1385,47 @@ int launch_attn_decode(const b200attn_attention_params& a, cudaStream_t stream, 
               (unsigned long long)need);
     return B200ATTN_E_WORKSPACE;
   }
+  DecodeGeom G;
+  if (int rc = decode_geometry(a, &G)) return rc;
   DecodeParams P;
   P.a = a;
   P.group = a.num_q_heads / a.num_kv_heads;
   P.only_q1 = only_single_token_seqs ? 1 : 0;
   P.trace = decode_trace_buffer();
-  // carve the workspace: ticket counters first (fixed region, zero between calls), then ml, then acc
+  // carve the workspace: ticket counters first (fixed region, zero between calls), then ml, acc and the
+  // launcher's own plan
   const uint64_t items_max = (uint64_t)a.num_seqs * a.num_kv_heads;
-  if (items_max * sizeof(int) > kCounterBytes) {
+  if (items_max * sizeof(int) > kPoolCounterOffset) {
     set_error("decode: %llu (sequence, kv head) items exceed the %llu ticket counters of the workspace",
-              (unsigned long long)items_max, (unsigned long long)(kCounterBytes / sizeof(int)));
+              (unsigned long long)items_max, (unsigned long long)(kPoolCounterOffset / sizeof(int)));
     return B200ATTN_E_WORKSPACE;
   }
   char* w = static_cast<char*>(a.workspace);
   P.ws_cnt = reinterpret_cast<int*>(w);
+  P.ws_pool = reinterpret_cast<int*>(w + kPoolCounterOffset);
   uint64_t off = kCounterBytes;
-  const uint64_t group = (uint64_t)P.group;
-  const uint64_t rows = (uint64_t)a.num_seqs * a.num_q_heads + (uint64_t)kMaxDecodeCtas * 8 * group;
+  const uint64_t rows = decode_rows(a.num_seqs, a.num_q_heads, a.num_kv_heads);
   P.ws_ml = reinterpret_cast<float*>(w + off);
   off += ((rows * 8 + 255) / 256) * 256;
   P.ws_acc = reinterpret_cast<float*>(w + off);
-  if (off + rows * a.head_size * 4 > a.workspace_bytes) {
+  off += rows * (uint64_t)a.head_size * 4;
+  off = ((off + 255) / 256) * 256;
+  if (off + decode_plan_bytes(a.num_seqs) > a.workspace_bytes) {
     set_error("decode: workspace carve-out exceeds the buffer");
     return B200ATTN_E_WORKSPACE;
   }
-  const int nt = P.group > 8 ? 2 : 1;
+  const uint64_t key = decode_plan_key(a, G, P.only_q1 != 0);
+  if (a.decode_plan && a.decode_plan_key == key) {
+    P.plan = static_cast<const Plan*>(a.decode_plan);  // built once for the step (b200attn_decode_plan)
+  } else {
+    // no plan for this shape from the caller: build one in the workspace in front of the launch
+    if (int rc = launch_plan_kernel(a, G, P.only_q1 != 0, w + off, stream)) return rc;
+    P.plan = reinterpret_cast<const Plan*>(w + off);
+  }
   switch (a.head_size) {
-    case 64: return nt == 1 ? dispatch_types<64, 1, 8>(a, P, stream) : dispatch_types<64, 2, 8>(a, P, stream);
-    case 128: return nt == 1 ? dispatch_types<128, 1, 8>(a, P, stream) : dispatch_types<128, 2, 8>(a, P, stream);
-    case 256: return dispatch_types<256, 1, 4>(a, P, stream);
+    case 64: return G.nt == 1 ? dispatch_types<64, 1, 8>(a, G, P, stream) : dispatch_types<64, 2, 8>(a, G, P, stream);
+    case 128: return G.nt == 1 ? dispatch_types<128, 1, 8>(a, G, P, stream) : dispatch_types<128, 2, 8>(a, G, P, stream);
+    case 256: return dispatch_types<256, 1, 4>(a, G, P, stream);
   }
   return B200ATTN_E_UNSUPPORTED;
 }

@@ -146,10 +146,10 @@ uint64_t b200attn_launch_count(void) { return g_launches; }
 void b200attn_reset_launch_count(void) { g_launches = 0; }
 const char* b200attn_last_kernel(void) { return g_last_kernel; }
 
-void b200attn_set_tuning(int32_t decode_heads_per_cta, int32_t decode_ctas_per_sm, int32_t decode_stages,
+void b200attn_set_tuning(int32_t decode_heads_per_cta, int32_t decode_pool_sixteenths, int32_t decode_stages,
                          int32_t reserved) {
   g_tuning.decode_heads_per_cta = decode_heads_per_cta;
-  g_tuning.decode_ctas_per_sm = decode_ctas_per_sm;
+  g_tuning.decode_ctas_per_sm = decode_pool_sixteenths;
   g_tuning.decode_stages = decode_stages;
   g_tuning.reserved = reserved;
 }
@@ -190,6 +190,19 @@ uint64_t b200attn_workspace_bytes(int32_t num_tokens, int32_t num_seqs, int32_t 
                                   int32_t head_size) {
   (void)num_tokens;
   return decode_workspace_bytes(num_seqs, num_q_heads, num_kv_heads, head_size);
+}
+
+uint64_t b200attn_decode_plan_bytes(int32_t num_seqs) { return decode_plan_bytes(num_seqs); }
+
+int b200attn_decode_plan(const b200attn_attention_params* pp, void* plan, uint64_t plan_bytes, uint64_t* key_out_host,
+                         b200attn_stream_t s) {
+  if (key_out_host) *key_out_host = 0;
+  if (!pp || !pp->seq_lens || !pp->cu_seqlens_q) {
+    set_error("decode_plan: null params / seq_lens / cu_seqlens_q");
+    return B200ATTN_E_NULL;
+  }
+  if (pp->num_seqs <= 0 || pp->num_q_heads <= 0 || pp->num_kv_heads <= 0 || pp->num_q_heads % pp->num_kv_heads) return B200ATTN_OK;
+  return build_decode_plan(*pp, plan, plan_bytes, key_out_host, reinterpret_cast<cudaStream_t>(s));
 }
 
 int b200attn_unified_attention(const b200attn_attention_params* pp, b200attn_stream_t s) {

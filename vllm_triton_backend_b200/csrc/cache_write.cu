@@ -67,6 +67,7 @@ struct CacheWriteArgs {
 template <int kElemBytes>
 __global__ void __launch_bounds__(256) cache_copy_vec_kernel(CacheWriteArgs a) {
   pdl_launch_dependents();  // the attention launch behind us may start its prologue now (common.cuh)
+  pdl_wait();               // ... and this grid may itself have been scheduled early: wait for the kernel in front
   constexpr int kVec = 16 / kElemBytes;
   const int64_t token = blockIdx.x;
   const int which = blockIdx.y;
@@ -88,6 +89,7 @@ __global__ void __launch_bounds__(256) cache_copy_vec_kernel(CacheWriteArgs a) {
 template <typename SrcT>
 __global__ void __launch_bounds__(256) cache_quant_vec16_kernel(CacheWriteArgs a) {
   pdl_launch_dependents();  // the attention launch behind us may start its prologue now (common.cuh)
+  pdl_wait();               // ... and this grid may itself have been scheduled early: wait for the kernel in front
   const int64_t token = blockIdx.x;
   const int which = blockIdx.y;
   const int64_t slot = a.slot_mapping[token];
@@ -118,6 +120,7 @@ __global__ void __launch_bounds__(256) cache_quant_vec16_kernel(CacheWriteArgs a
 template <typename SrcT, bool kQuant>
 __global__ void __launch_bounds__(256) cache_scalar_kernel(CacheWriteArgs a) {
   pdl_launch_dependents();  // the attention launch behind us may start its prologue now (common.cuh)
+  pdl_wait();               // ... and this grid may itself have been scheduled early: wait for the kernel in front
   const int64_t token = blockIdx.x;
   const int which = blockIdx.y;
   const int64_t slot = a.slot_mapping[token];
@@ -210,6 +213,7 @@ int launch_cache_write(const void* key, const void* value, void* k_cache, void* 
   auto mult = [](int64_t x, int64_t m) { return x % m == 0; };
   const dim3 grid((unsigned)num_tokens, 2);
   const int n_elems = num_kv_heads * head_size;
+  const bool pdl = !(tuning().reserved & 512);  // common.cuh: launch_pdl
 
   if (!quant) {
     const int vec = 16 / sb;
@@ -220,16 +224,16 @@ int launch_cache_write(const void* key, const void* value, void* k_cache, void* 
     if (vec_ok) {
       int threads = n_elems / vec;
       threads = threads < 32 ? 32 : (threads > 256 ? 256 : ((threads + 31) / 32) * 32);
-      if (sb == 2) cache_copy_vec_kernel<2><<<grid, threads, 0, stream>>>(a);
-      else if (sb == 4) cache_copy_vec_kernel<4><<<grid, threads, 0, stream>>>(a);
-      else cache_copy_vec_kernel<1><<<grid, threads, 0, stream>>>(a);
+      if (sb == 2) launch_pdl(cache_copy_vec_kernel<2>, grid, threads, 0, stream, pdl, a);
+      else if (sb == 4) launch_pdl(cache_copy_vec_kernel<4>, grid, threads, 0, stream, pdl, a);
+      else launch_pdl(cache_copy_vec_kernel<1>, grid, threads, 0, stream, pdl, a);
       note_launch("cache_copy_vec");
     } else {
       int threads = n_elems > 256 ? 256 : ((n_elems + 31) / 32) * 32;
-      if (src_dtype == B200ATTN_BF16) cache_scalar_kernel<__nv_bfloat16, false><<<grid, threads, 0, stream>>>(a);
-      else if (src_dtype == B200ATTN_F16) cache_scalar_kernel<__half, false><<<grid, threads, 0, stream>>>(a);
-      else if (src_dtype == B200ATTN_F32) cache_scalar_kernel<float, false><<<grid, threads, 0, stream>>>(a);
-      else cache_scalar_kernel<uint8_t, false><<<grid, threads, 0, stream>>>(a);
+      if (src_dtype == B200ATTN_BF16) launch_pdl(cache_scalar_kernel<__nv_bfloat16, false>, grid, threads, 0, stream, pdl, a);
+      else if (src_dtype == B200ATTN_F16) launch_pdl(cache_scalar_kernel<__half, false>, grid, threads, 0, stream, pdl, a);
+      else if (src_dtype == B200ATTN_F32) launch_pdl(cache_scalar_kernel<float, false>, grid, threads, 0, stream, pdl, a);
+      else launch_pdl(cache_scalar_kernel<uint8_t, false>, grid, threads, 0, stream, pdl, a);
       note_launch("cache_copy_scalar");
     }
   } else {
@@ -240,14 +244,14 @@ int launch_cache_write(const void* key, const void* value, void* k_cache, void* 
     if (vec_ok) {
       int threads = n_elems / 16;
       threads = threads < 32 ? 32 : (threads > 256 ? 256 : ((threads + 31) / 32) * 32);
-      if (src_dtype == B200ATTN_BF16) cache_quant_vec16_kernel<__nv_bfloat16><<<grid, threads, 0, stream>>>(a);
-      else cache_quant_vec16_kernel<__half><<<grid, threads, 0, stream>>>(a);
+      if (src_dtype == B200ATTN_BF16) launch_pdl(cache_quant_vec16_kernel<__nv_bfloat16>, grid, threads, 0, stream, pdl, a);
+      else launch_pdl(cache_quant_vec16_kernel<__half>, grid, threads, 0, stream, pdl, a);
       note_launch("cache_quant_vec16");
     } else {
       int threads = n_elems > 256 ? 256 : ((n_elems + 31) / 32) * 32;
-      if (src_dtype == B200ATTN_BF16) cache_scalar_kernel<__nv_bfloat16, true><<<grid, threads, 0, stream>>>(a);
-      else if (src_dtype == B200ATTN_F16) cache_scalar_kernel<__half, true><<<grid, threads, 0, stream>>>(a);
-      else cache_scalar_kernel<float, true><<<grid, threads, 0, stream>>>(a);
+      if (src_dtype == B200ATTN_BF16) launch_pdl(cache_scalar_kernel<__nv_bfloat16, true>, grid, threads, 0, stream, pdl, a);
+      else if (src_dtype == B200ATTN_F16) launch_pdl(cache_scalar_kernel<__half, true>, grid, threads, 0, stream, pdl, a);
+      else launch_pdl(cache_scalar_kernel<float, true>, grid, threads, 0, stream, pdl, a);
       note_launch("cache_quant_scalar");
     }
   }

@@ -88,6 +88,8 @@ int launch_attn_generic(const b200attn_attention_params& p, cudaStream_t stream)
 int launch_attn_decode(const b200attn_attention_params& p, cudaStream_t stream, bool only_single_token_seqs = false);
 bool decode_supported(const b200attn_attention_params& p, const char** why, bool mixed_batch = false);
 uint64_t decode_workspace_bytes(int num_seqs, int num_q_heads, int num_kv_heads, int head_size);
+uint64_t decode_plan_bytes(int num_seqs);
+int build_decode_plan(const b200attn_attention_params& p, void* plan, uint64_t plan_bytes, uint64_t* key_out, cudaStream_t stream);
 int launch_attn_prefill(const b200attn_attention_params& p, cudaStream_t stream, QLenRange range = QLenRange(),
                         const int32_t* skip_staged = nullptr);
 bool prefill_supported(const b200attn_attention_params& p, const char** why);
@@ -95,6 +97,23 @@ int launch_attn_prefill_tc(const b200attn_attention_params& p, cudaStream_t stre
                            const int32_t* staged_base = nullptr);
 bool prefill_tc_supported(const b200attn_attention_params& p, const char** why);
 int prefill_tc_min_q_len(const b200attn_attention_params& p);  // shortest query the tcgen05 tile is worth using for
+
+#ifdef __CUDACC__
+// Launch with (or without) programmatic stream serialisation: the grid may be scheduled while the kernel in front
+// of it on the stream is still running, provided that kernel has released its dependents; the launched kernel
+// must execute pdl_wait() before its first global-memory access AND in every CTA before it exits (a CTA that
+// left without waiting would let the grid complete, and the next dependent start, too early).
+template <typename... KArgs, typename... Args>
+inline void launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, bool pdl, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid, cfg.blockDim = block, cfg.dynamicSmemBytes = smem, cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr, cfg.numAttrs = pdl ? 1 : 0;
+  cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+#endif
 
 static inline int dtype_bytes(int dt) {
   switch (dt) {
@@ -184,6 +203,10 @@ __device__ __forceinline__ uint8_t fp8_out(float x) { return (uint8_t)__nv_cvt_f
 // cudaLaunchAttributeProgrammaticStreamSerialization and sets up shared memory, barriers and descriptors while
 // the writer is still running, then waits (full completion + memory flush of everything before it) in front
 // of its first global-memory read.  After any other kernel (which never triggers) the launch behaves as usual.
+// It works the other way round as well: the decode kernel releases ITS dependents when it starts and the cache
+// writers are launched with the attribute and wait first thing, so in a loop of (cache write, attention) pairs
+// - or behind a previous decode launch - the next launch's latency hides under the running kernel.  Waits are
+// transitive (each kernel of the chain waits for its predecessor's completion before it completes itself).
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 

@@ -83,6 +83,7 @@ __device__ __forceinline__ void to_cache(void* cache_row, int d, const Vec8<T>& 
 template <typename T, bool kNeox, bool kQuant>
 __global__ void __launch_bounds__(256) rope_cache_kernel(const RopeArgs a) {
   pdl_launch_dependents();  // the attention launch behind us may start its prologue now (common.cuh)
+  pdl_wait();               // ... and this grid may itself have been scheduled early: wait for the kernel in front
   const int64_t t = blockIdx.x;
   const bool do_rope = t < a.rope_tokens;
   int64_t slot = -1;
@@ -210,7 +211,7 @@ int launch_rope_cache(const b200attn_rope_cache_params& p, cudaStream_t stream) 
   int threads = units < 64 ? 64 : (units > 256 ? 256 : ((units + 31) / 32) * 32);
   const unsigned grid = (unsigned)tokens;
   const bool bf = p.src_dtype == B200ATTN_BF16;
-#define B200_ROPE_LAUNCH(T, NEOX, QUANT) rope_cache_kernel<T, NEOX, QUANT><<<grid, threads, 0, stream>>>(a)
+#define B200_ROPE_LAUNCH(T, NEOX, QUANT) launch_pdl(rope_cache_kernel<T, NEOX, QUANT>, grid, threads, 0, stream, !(tuning().reserved & 512), a)
   if (bf) {
     if (p.is_neox) { if (quant) B200_ROPE_LAUNCH(__nv_bfloat16, true, true); else B200_ROPE_LAUNCH(__nv_bfloat16, true, false); }
     else { if (quant) B200_ROPE_LAUNCH(__nv_bfloat16, false, true); else B200_ROPE_LAUNCH(__nv_bfloat16, false, false); }

@@ -79,6 +79,54 @@ def fp8_staging_bytes(num_seqs: int, tokens: int, block_size: int, num_kv_heads:
     return 256 + index + 2 * pages * block_size * num_kv_heads * head_size * 2 + 512
 
 
+class DecodePlan:
+    """The split-KV work plan of one step (`b200attn_decode_plan`): where every CTA and every pool chunk of
+    the decode launches starts, computed on the device from `seq_lens` / `cu_seqlens_q`.  All layers of a step
+    share those arrays, so the metadata builder builds it once and every layer's launch reads it; a launch
+    without one plans for itself (one more small kernel per call).
+
+    One buffer, rebuilt in place every step (its address is what a captured CUDA graph holds)."""
+
+    __slots__ = ("buf", "key", "_p", "_key_out", "_fn", "_keep", "max_seqs")
+
+    def __init__(self, device, max_num_seqs: int, num_q_heads: int, num_kv_heads: int, head_size: int, block_size: int,
+                 q_dtype: torch.dtype, kv_dtype: torch.dtype, sliding_window: int = 0):
+        lib = _cabi.load_library()
+        self.max_seqs = int(max_num_seqs)
+        self.buf = torch.zeros(int(lib.b200attn_decode_plan_bytes(self.max_seqs)), dtype=torch.uint8, device=device)
+        p = AttentionParams()
+        p.num_q_heads, p.num_kv_heads, p.head_size, p.block_size = num_q_heads, num_kv_heads, head_size, block_size
+        p.q_dtype, p.kv_dtype = _DTYPE[q_dtype], _DTYPE[kv_dtype]
+        p.sliding_window = int(sliding_window or 0)
+        # alignment / stride fields decode_supported() looks at: dense views
+        p.kc_block_stride = p.vc_block_stride = block_size * num_kv_heads * head_size
+        p.kc_slot_stride = p.vc_slot_stride = num_kv_heads * head_size
+        p.kc_head_stride = p.vc_head_stride = head_size
+        p.q_stride0, p.q_stride1 = num_q_heads * head_size, head_size
+        self._p, self._key_out, self._fn, self.key, self._keep = p, ctypes.c_uint64(0), lib.b200attn_decode_plan, 0, None
+
+    def build(self, cu_seqlens_q: torch.Tensor, seqused_k: torch.Tensor, max_seqlen_q: int) -> int:
+        """Launches the plan kernel on the current stream; returns the key (0: nothing to plan for this shape)."""
+        n = seqused_k.shape[0]
+        if n > self.max_seqs:
+            if torch.cuda.is_current_stream_capturing():
+                self.key = 0
+                return 0
+            self.max_seqs = max(n, 2 * self.max_seqs)
+            self._keep = (self._keep, self.buf)  # a captured graph may hold the old address
+            self.buf = torch.zeros(int(_cabi.load_library().b200attn_decode_plan_bytes(self.max_seqs)), dtype=torch.uint8,
+                                   device=self.buf.device)
+        p = self._p
+        p.seq_lens, p.cu_seqlens_q, p.num_seqs = seqused_k.data_ptr(), cu_seqlens_q.data_ptr(), n
+        p.max_seqlen_q = int(max_seqlen_q)
+        rc = self._fn(ctypes.byref(p), self.buf.data_ptr(), self.buf.numel(), ctypes.byref(self._key_out),
+                      torch.cuda.current_stream(self.buf.device).cuda_stream)
+        if rc:
+            _cabi.check(rc)
+        self.key = int(self._key_out.value)
+        return self.key
+
+
 def get_workspace(device, nbytes: int) -> torch.Tensor:
     """Grow-only per-device split-KV workspace (replaces the reference's per-call
     torch.empty of segm_output/segm_max/segm_expsum, triton_unified_attention.py:950-971).
@@ -258,6 +306,7 @@ def unified_attention(
     sinks: Optional[torch.Tensor] = None,  # [Hq] float32 (upstream keyword)
     output_scale: Optional[torch.Tensor] = None,  # upstream keyword: `out` is e4m3, out = quant(o / output_scale)
     qq_bias: Optional[torch.Tensor] = None,  # upstream keyword: [q, q] fp32 bias between a step's query tokens (SIMT kernel)
+    decode_plan: Optional["DecodePlan"] = None,  # this step's split-KV plan (DecodePlan.build), shared by all layers
     # Pure tuning inputs of upstream's launcher (vLLM 0.22 vllm/v1/attention/ops/triton_unified_attention.py):
     # where its split-KV partials live and when it splits.  They do not change the result; this library sizes
     # and owns its workspace itself, so they are accepted and unused.
@@ -322,6 +371,8 @@ def unified_attention(
         q, k, v, out, cu_seqlens_q, max_seqlen_q, seqused_k, max_seqlen_k, softmax_scale, window_size, block_table,
         softcap, k_descale, v_descale, alibi_slopes, path, workspace, sinks, output_scale, qq_bias,
     )
+    if decode_plan is not None and decode_plan.key:
+        p.decode_plan, p.decode_plan_key = decode_plan.buf.data_ptr(), decode_plan.key
     _cabi.check(_cabi.load_library().b200attn_unified_attention(ctypes.byref(p), _stream_ptr(q)))
 
 
@@ -373,7 +424,7 @@ class AttentionPlan:
         self.num_q_heads, self.head_size, self.q_dtype = num_q_heads, head_size, q_dtype
 
     def __call__(self, q, out, cu_seqlens_q, max_seqlen_q, seqused_k, max_seqlen_k, block_table, workspace,
-                 output_scale=None) -> None:
+                 output_scale=None, decode_plan=None) -> None:
         """q/out: [T, Hq, D] views (innermost contiguous); metadata tensors int32 on the device.
         `output_scale`: one-element fp32 device tensor => `out` is float8_e4m3fn (fused output quant)."""
         if q.dtype != self.q_dtype or not q.is_cuda:
@@ -390,6 +441,10 @@ class AttentionPlan:
         p.block_tables, p.seq_lens, p.cu_seqlens_q = block_table.data_ptr(), seqused_k.data_ptr(), cu_seqlens_q.data_ptr()
         p.bt_stride0 = block_table.stride(0)
         p.max_seqlen_q, p.max_seqlen_k = max_seqlen_q, max_seqlen_k
+        if decode_plan is not None and decode_plan.key:
+            p.decode_plan, p.decode_plan_key = decode_plan.buf.data_ptr(), decode_plan.key
+        else:
+            p.decode_plan, p.decode_plan_key = None, 0
         wp = workspace.data_ptr()
         if wp != self._ws_ptr:
             p.workspace, p.workspace_bytes, self._ws_ptr = wp, workspace.numel() * workspace.element_size(), wp
