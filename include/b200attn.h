@@ -238,13 +238,17 @@ B200ATTN_API void b200attn_reset_launch_count(void);
 /* Name of the kernel variant the last attention call on this thread ran. */
 B200ATTN_API const char* b200attn_last_kernel(void);
 /* Tuning knobs (process-wide; 0 = library default).  Used by the benchmark
- * sweeps; not needed for correctness. */
+ * sweeps; not needed for correctness.  decode_pool_sixteenths: 1..12 lets idle CTAs of the split-KV
+ * decode kernel steal that share (in 1/16) of every other CTA's range (default: off, static split,
+ * bit-reproducible results). */
 B200ATTN_API void b200attn_set_tuning(int32_t decode_heads_per_cta, int32_t decode_pool_sixteenths,
                          int32_t decode_stages, int32_t reserved);
 
-/* Debug: when `device_buffer` is not NULL the split-KV decode kernel writes 8 uint64
+/* Debug: when `device_buffer` is not NULL the split-KV decode kernel writes 16 uint64
  * per CTA (globaltimer at entry, then %clock64 at: entry, first run known, first KV
- * stage landed, last stage consumed, exit; globaltimer at exit; items finalised).
+ * stage landed, last stage consumed, exit; globaltimer at exit; runs finalised; then cycle
+ * sums: consumers in run epilogues, consumers waiting for data, producer waiting for a free
+ * stage, producer between ranges; 4 unused).
  * Process-wide; NULL switches it off.  Used by scripts/kbench.py decode --trace. */
 B200ATTN_API void b200attn_debug_set_decode_trace(void* device_buffer);
 

@@ -191,7 +191,7 @@ def decode_trace(fn, device):
     """Per-CTA phase times of one decode launch (b200attn_debug_set_decode_trace)."""
     lib = _cabi.load_library()
     nsm = torch.cuda.get_device_properties(device).multi_processor_count
-    buf = torch.zeros(nsm * 8, dtype=torch.int64, device=device)
+    buf = torch.zeros(nsm * 16, dtype=torch.int64, device=device)
     for _ in range(5):
         fn()
     torch.cuda.synchronize()
@@ -199,7 +199,7 @@ def decode_trace(fn, device):
     fn()
     torch.cuda.synchronize()
     lib.b200attn_debug_set_decode_trace(None)
-    t = buf.cpu().view(nsm, 8).double()
+    t = buf.cpu().view(nsm, 16).double()
     t = t[t[:, 0] > 0]
     span_ns = float(t[:, 6].max() - t[:, 0].min())
     ghz = float(((t[:, 5] - t[:, 1]) / (t[:, 6] - t[:, 0]).clamp(min=1)).median())  # cycles per ns
@@ -211,7 +211,9 @@ def decode_trace(fn, device):
                 start_skew_us=stat((t[:, 0] - t[:, 0].min()) / 1e3), first_run_us=stat(us(t[:, 2] - t[:, 1])),
                 first_data_us=stat(us(t[:, 3] - t[:, 2])), streaming_us=stat(us(t[:, 4] - t[:, 3])),
                 tail_us=stat(us(t[:, 5] - t[:, 4])), cta_total_us=stat((t[:, 6] - t[:, 0]) / 1e3),
-                end_skew_us=stat((t[:, 6].max() - t[:, 6]) / 1e3), runs_per_cta=stat(t[:, 7]))
+                end_skew_us=stat((t[:, 6].max() - t[:, 6]) / 1e3), runs_per_cta=stat(t[:, 7]),
+                finalize_us=stat(us(t[:, 8])), consumer_wait_full_us=stat(us(t[:, 9])), producer_wait_empty_us=stat(us(t[:, 10])),
+                producer_switch_us=stat(us(t[:, 11])))
 
 
 def run_decode(args, device):

@@ -51,15 +51,31 @@ def test_strided_rows_and_nan():
     assert got[2, 44] == 0x7E and got[5, 0] == 0x7E and got[5, 1] == 0xFE  # NaN and +inf -> +448, -inf -> -448
 
 
-def test_reciprocal_multiply_is_not_the_cache_writes_division():
-    """K4 multiplies by fl(1/scale), the cache write divides: with scale 0.37 some inputs land on different bytes.
-    Both conventions are pinned (this test fails if K4 were to divide)."""
+def _rounding_boundary_inputs(scale):
+    """fp32 inputs within a few ulps of `midpoint * scale` for every midpoint between two adjacent e4m3 values: where
+    x * fl(1/scale) and x / scale fall on different sides of a rounding boundary."""
+    import numpy as np
+
+    vals = torch.arange(0, 127, dtype=torch.uint8).view(torch.float8_e4m3fn).float()  # the positive finite e4m3 values
+    x0 = (((vals[:-1] + vals[1:]) / 2).double() * scale).float().numpy()
+    xs, up, dn = [x0], x0.copy(), x0.copy()
+    for _ in range(4):
+        up, dn = np.nextafter(up, np.float32(np.inf)), np.nextafter(dn, np.float32(-np.inf))
+        xs += [up.copy(), dn.copy()]
+    x = torch.from_numpy(np.concatenate(xs))
+    return torch.cat([x, -x]).view(2, -1)
+
+
+@pytest.mark.parametrize("scale", [0.37, 0.21, 3.3])
+def test_reciprocal_multiply_is_not_the_cache_writes_division(scale):
+    """K4 multiplies by fl(1/scale), the cache write divides: next to a rounding boundary the two land on different
+    bytes.  Both conventions are pinned (this test fails if K4 were to divide)."""
     from vllm_triton_backend_b200 import ops
 
-    x = _inputs(torch.float32, 64, 4096, seed=9, spread=100.0)
-    mul, div = scaled_fp8_quant_ref(x, 0.37), quantize_e4m3_torch(x, 0.37)
-    assert int((mul != div).sum()) > 0
-    s = torch.tensor([0.37], dtype=torch.float32, device="cuda")
+    x = _rounding_boundary_inputs(scale)
+    mul, div = scaled_fp8_quant_ref(x, scale), quantize_e4m3_torch(x, scale)
+    assert int((mul != div).sum()) >= 16
+    s = torch.tensor([scale], dtype=torch.float32, device="cuda")
     out, _ = ops.scaled_fp8_quant(x.cuda(), s)
     assert torch.equal(out.cpu().view(torch.uint8), mul)
 

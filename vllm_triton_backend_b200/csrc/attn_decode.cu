@@ -34,12 +34,13 @@
 namespace b200attn {
 namespace {
 
-constexpr int kMaxStages = 8;
+constexpr int kMaxStages = 6;                                 // (a 32 KB stage, D = 64, gives 5)
 constexpr int kDescSlots = 16;                                // run descriptors in flight (> kMaxStages + 1)
 constexpr int kPoolRounds = 3;                                // pool chunks per CTA range, at most
 constexpr int kMaxPoolChunks = kPoolRounds * kMaxDecodeCtas;  // pool chunks of one launch
 constexpr int kMaxParts = (1 + kPoolRounds) * kMaxDecodeCtas; // parts one item can be cut into
 constexpr int kMaxSlots = 2 * (kMaxDecodeCtas + kMaxPoolChunks);
+constexpr int kDequeWord0 = 16;                                // ws_pool[kDequeWord0 + c]: range c's claim word
 
 // ---- the plan: where every CTA (and every pool chunk) starts -----------------------------------
 // Built on the device from seq_lens by decode_plan_kernel, once per step (all layers of a model share
@@ -98,17 +99,18 @@ __device__ __forceinline__ int part_slot(const PlanHeader& h, int c, int j, int 
 // A run: consecutive steps of ONE (sequence, head group) item, produced by the producer warp for the consumers.
 struct RunDesc {  // 48 bytes in shared memory
   int kind;       // 1 = run, 0 = no more work
-  int hg, step0, nsteps, seq_len, tq, item;
-  int slot;       // where this run's partial goes, or -1: the run is the whole item, write the output directly
-  int nparts;     // parts the item is cut into (ticket count that completes it)
+  int hg, step0, seq_len, tq, item;
+  int slot;       // where this run's partial goes if the run turns out not to be the whole item
   int i0, n;      // flat position of the item's first step, its number of steps
-  int pad;
+  int pad[3];     // (how long a run is shows in step_last[]: its owner may lose its tail chunks to a thief on the way)
 };
 // A partial run handed to the ticket warp, and (the same fields) an item whose last ticket was taken, handed
 // back to the consumers for merging.
 struct FinDesc {  // 32 bytes in shared memory
   int kind;       // 1 = a partial was written, 0 = the consumers are done
-  int item, hg, tq, nparts, i0, n;
+  int item, hg, tq;
+  int steps;      // steps the partial covers: the item's counter adds them up, n of n completes it
+  int i0, n;
   int pad;
 };
 constexpr int kFinSlots = 2;   // partial runs waiting for their ticket
@@ -134,8 +136,8 @@ struct DecodeParams {
   float* ws_acc;   // [slots][hpc*group][D]
   float* ws_ml;    // [slots][hpc*group][2]  (max in log2 units, exp-sum)
   int* ws_cnt;     // [items] tickets taken on an item split across parts (0 between calls)
-  int* ws_pool;    // [0] next pool chunk, [1] CTAs that are done taking chunks (both 0 between calls)
-  unsigned long long* trace;  // debug time stamps, 8 per CTA (b200attn_debug_set_decode_trace) or nullptr
+  int* ws_pool;    // [1] CTAs that are done taking chunks, [kDequeWord0 + c] claim word of range c (all 0 between calls)
+  unsigned long long* trace;  // debug time stamps, 16 per CTA (b200attn_debug_set_decode_trace) or nullptr
 };
 
 __device__ __forceinline__ unsigned long long global_ns() {
@@ -338,13 +340,17 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
   FinDesc* fins = reinterpret_cast<FinDesc*>(epi_done + 1);               // [kFinSlots]
   FinDesc* reqs = fins + kFinSlots;                                       // [kReqSlots] items to merge
   volatile int* req_cnt = reinterpret_cast<volatile int*>(reqs + kReqSlots);  // [0] posted by the ticket warp, [1] merged, [2] scratch
-  short* part_slots = reinterpret_cast<short*>(const_cast<int*>(req_cnt) + 4);  // [kMaxParts] the parts of the item being merged
+  int* step_last = const_cast<int*>(req_cnt) + 4;                         // [kMaxStages] 1: the run ends with this stage
+  short* part_slots = reinterpret_cast<short*>(step_last + kMaxStages);   // [kMaxParts] the parts of the item being merged
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int gid = lane >> 2, t4 = lane & 3;
 
-  unsigned long long* trace = P.trace ? P.trace + (size_t)blockIdx.x * 8 : nullptr;
-  if (trace && threadIdx.x == 0) trace[0] = global_ns(), trace[1] = clock64(), trace[7] = 0;
+  unsigned long long* trace = P.trace ? P.trace + (size_t)blockIdx.x * 16 : nullptr;
+  if (trace && threadIdx.x == 0) {
+    trace[0] = global_ns(), trace[1] = clock64(), trace[7] = 0;
+    for (int i = 8; i < 16; ++i) trace[i] = 0;
+  }
 
   // ---- barrier init ---------------------------------------------------------------------------
   if (warp == NW && lane == 0) {  // descriptor fetch overlaps the rest of the prologue
@@ -378,9 +384,14 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
 
   if (warp == NW) {
     // ======================= producer warp ====================================
-    // Walks this CTA's work - its static range, then pool chunks - cuts it into runs (consecutive steps of one
-    // item), publishes a descriptor per run and streams every step's pages: lane i looks up the page of box i
-    // and launches its K and V copies, so page-table latency and TMA issue overlap across boxes.
+    // Walks this CTA's work, cuts it into runs (consecutive steps of one item), publishes a descriptor per run and
+    // streams every step's pages: lane i looks up the page of box i and launches its K and V copies, so page-table
+    // latency and TMA issue overlap across boxes.
+    //
+    // The work: first this CTA's own range - the static part, then the range's tail chunks for as long as no other
+    // CTA has taken them (claimed one chunk ahead, front to back, so the walk simply continues: no run ends at a
+    // chunk boundary) - and when that is exhausted, chunks stolen from the BACK of the range with the most chunks
+    // left.  Each range has one packed word in the workspace: owner claims | thief claims | mask of stolen chunks.
     const uint64_t pol = policy_evict_first();
     const PlanHeader hdr = P.plan->hdr;
     int stage = 0;
@@ -402,147 +413,206 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
       const int4 lo = *reinterpret_cast<const int4*>(pc), hi = *(reinterpret_cast<const int4*>(pc) + 1);
       c.b = lo.x, c.hg = lo.y, c.step = lo.z, c.seq_len = lo.w, c.first = hi.x, c.n = hi.y, c.tq = hi.z, c.flat = hi.w;
     };
-    const bool pooled = hdr.n_chunks > 0;
-    const int J = 1 + hdr.n_rounds;  // parts per range
-    // parts the item [i0, i1) is cut into: ranges strictly inside it contribute all of theirs, the (one or two)
-    // ranges at its ends are tested part by part, one lane each
-    auto count_parts = [&](int i0, int i1) {
-      const int ca = i0 / hdr.per, cb = (i1 - 1) / hdr.per;
-      int cnt = cb - ca >= 2 ? (cb - ca - 1) * J : 0;
-      bool hit = false;
-      if (lane < (cb > ca ? 2 : 1) * J) {
+    const int T = hdr.n_rounds;
+    const bool pooled = T > 0;
+    int* deque = P.ws_pool + kDequeWord0;
+    // chunks of range c that are not cut off by the end of the batch
+    auto chunks_of = [&](int c) {
+      int n = 0;
+      for (int j = 1; j <= T; ++j) {
         int pb, pe;
-        part_range(hdr, lane < J ? ca : cb, lane < J ? lane : lane - J, pb, pe);
-        hit = max(pb, i0) < min(pe, i1);
+        part_range(hdr, c, j, pb, pe);
+        n += pb < pe ? 1 : 0;
       }
-      return cnt + __popc(__ballot_sync(0xffffffffu, hit));
+      return n;
     };
-    ItemCursor cur;
-    int range_c = (int)blockIdx.x, range_j = 0;  // the part being walked: range, part index (0 = static)
-    int range_begin, range_end;                  // its flat extent
-    load_cursor(&P.plan->cta[blockIdx.x], cur);
-    part_range(hdr, range_c, 0, range_begin, range_end);
-    bool have_range = cur.b >= 0 && cur.flat < range_end;
-    while (true) {
-      int next_chunk = 0x7fffffff;
-      if (pooled && lane == 0) next_chunk = atomicAdd(&P.ws_pool[0], 1);  // in flight while this range is walked
-      ItemCursor next_cur;
-      next_cur.b = -1;
-      bool next_loaded = false;
-      while (have_range) {
-        // ---- a run: steps of the current item that lie in this range
-        const int item_end = cur.first + cur.n;
-        const int nsteps = min(item_end - cur.step, range_end - cur.flat);
-        RunDesc rd = {};
-        {
-          const int item = cur.b * P.head_groups + cur.hg;
-          const int i0 = cur.flat - (cur.step - cur.first);  // flat position of the item's first step
-          const int i1 = i0 + cur.n;
-          int slot = -1, nparts = 1;
-          if (nsteps != cur.n) {  // (warp-uniform)
-            nparts = count_parts(i0, i1);
-            slot = part_slot(hdr, range_c, range_j, range_begin, i0);
-          }
-          rd.kind = 1, rd.hg = cur.hg, rd.step0 = cur.step, rd.nsteps = nsteps, rd.seq_len = cur.seq_len, rd.tq = cur.tq;
-          rd.item = item, rd.slot = slot, rd.nparts = nparts, rd.i0 = i0, rd.n = cur.n;
-        }
-        for (int s = 0; s < nsteps; ++s) {
-          const int tok0 = cur.step * P.tps;
-          const int ntok = min(P.tps, cur.seq_len - tok0);
-          const int nbox = (ntok + P.box_slots - 1) / P.box_slots;
-          const int head0 = cur.hg * P.hpc;
-          const int32_t* bt = P.a.block_tables + (int64_t)cur.b * P.a.bt_stride0;
-          const int npages = (cur.seq_len + P.a.block_size - 1) >> P.bs_shift;
-          const int p_first = tok0 >> P.bs_shift;
-          const int base = p_first & ~127;
-          if (cur.b != win_b || base != win_base) {
-            if (cur.b == win_b && base == win_base + 128) {
+
+    ItemCursor cur = {};
+    bool run_open = false;  // a run has been published and its last step not yet issued
+    int slot_c = 0, slot_j = 0, slot_b = 0;  // the part the current extent belongs to (for the partial's slot)
+    // ---- one step: wait for a free stage, publish the run if this is its first step, issue the copies
+    auto issue_step = [&](bool last) {
+      const int tok0 = cur.step * P.tps;
+      const int ntok = min(P.tps, cur.seq_len - tok0);
+      const int nbox = (ntok + P.box_slots - 1) / P.box_slots;
+      const int head0 = cur.hg * P.hpc;
+      const int32_t* bt = P.a.block_tables + (int64_t)cur.b * P.a.bt_stride0;
+      const int npages = (cur.seq_len + P.a.block_size - 1) >> P.bs_shift;
+      const int p_first = tok0 >> P.bs_shift;
+      const int base = p_first & ~127;
+      if (cur.b != win_b || base != win_base) {
+        if (cur.b == win_b && base == win_base + 128) {
 #pragma unroll
-              for (int r = 0; r < 4; ++r) ids[r] = nxt[r];
-            } else {
-              load_ids(ids, bt, base, npages);
-            }
-            load_ids(nxt, bt, base + 128, npages);
-            win_b = cur.b, win_base = base;
-          }
-          auto page_of = [&](int pg) {  // warp-collective: every lane asks for one page id
-            const int src = pg & 31, r = (pg >> 5) & 3;
-            const int v0 = __shfl_sync(0xffffffffu, ids[0], src), v1 = __shfl_sync(0xffffffffu, ids[1], src);
-            const int v2 = __shfl_sync(0xffffffffu, ids[2], src), v3 = __shfl_sync(0xffffffffu, ids[3], src);
-            return r == 0 ? v0 : (r == 1 ? v1 : (r == 2 ? v2 : v3));
-          };
-          mbar_wait(&empty_bar[stage], phase ^ 1);
-          if (s == 0) {
-            // Publish the run.  Its slot held descriptor ndesc - kDescSlots; the stage just waited for was last used
-            // by a step of run >= ndesc - stages, and a consumer reads a run's descriptor before it releases any of
-            // the run's stages, so every consumer is done with the old contents (kDescSlots > kMaxStages + 1).
-            const int ds = ndesc & (kDescSlots - 1);
-            if (lane == 0) {
-              descs[ds] = rd;
-              mbar_arrive(&desc_bar[ds]);  // release: the stores above are visible to whoever sees the phase flip
-            }
-            ++ndesc;
-          }
-          uint8_t* kdst = stage_base + (size_t)stage * 2 * KV_STAGE_BYTES;
-          uint8_t* vdst = kdst + KV_STAGE_BYTES;
-          if (lane == 0) mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)(2 * nbox * boxb));
-          __syncwarp();
-          if (P.paired) {
-            // k_map's third coordinate selects K (0) or V (1); the box takes both
-            const int i = lane;
-            const int tok = tok0 + i * P.box_slots;
-            const int page = page_of(tok >> P.bs_shift);
-            if (i < nbox)
-              tma_load_5d(kdst + (size_t)i * 2 * boxb, &k_map, &full_bar[stage], 0, tok & (P.a.block_size - 1), 0, head0, page, pol);
-          } else if (P.tma_split == 0) {
-            // nbox <= 8: one lane per box
-            const int i = lane;
-            const int tok = tok0 + i * P.box_slots;
-            const int page = page_of(tok >> P.bs_shift);  // lanes past nbox read a don't-care id
-            if (i < nbox) {
-              const int slot0 = tok & (P.a.block_size - 1);
-              tma_load_5d(kdst + (size_t)i * boxb, &k_map, &full_bar[stage], 0, slot0, 0, head0, page, pol);
-              tma_load_5d(vdst + (size_t)i * boxb, &v_map, &full_bar[stage], 0, slot0, 0, head0, page, pol);
-            }
-          } else {
-            const int per_box = P.hpc * NDC;
-            const int units = nbox * per_box;
-            for (int u0 = 0; u0 < units; u0 += 32) {
-              const int u = u0 + lane;
-              const int i = min(u / per_box, nbox - 1), r = u % per_box, h = r / NDC, dc = r % NDC;
-              const int tok = tok0 + i * P.box_slots;
-              const int page = page_of(tok >> P.bs_shift);
-              if (u < units) {
-                const int slot0 = tok & (P.a.block_size - 1);
-                const size_t off = (size_t)i * boxb + (size_t)(h * NDC + dc) * P.box_slots * 128;
-                tma_load_5d(kdst + off, &k_map, &full_bar[stage], 0, slot0, dc, head0 + h, page, pol);
-                tma_load_5d(vdst + off, &v_map, &full_bar[stage], 0, slot0, dc, head0 + h, page, pol);
-              }
-            }
-          }
-          if (++stage == P.stages) stage = 0, phase ^= 1;
-          if (pooled && !next_loaded) {
-            // the chunk counter has come back by now: fetch where the next chunk starts while this range streams
-            next_loaded = true;
-            next_chunk = __shfl_sync(0xffffffffu, next_chunk, 0);
-            if (next_chunk < hdr.n_chunks) load_cursor(&P.plan->chunk[next_chunk], next_cur);
-          }
-          // next step (the last step of the range must not run past the end of the batch)
-          if (cur.flat + 1 < range_end) cursor_next(P, cur);
-          else cur.flat++;
+          for (int r = 0; r < 4; ++r) ids[r] = nxt[r];
+        } else {
+          load_ids(ids, bt, base, npages);
         }
-        have_range = cur.flat < range_end;
+        load_ids(nxt, bt, base + 128, npages);
+        win_b = cur.b, win_base = base;
       }
-      if (!pooled) break;
-      if (!next_loaded) {
-        next_chunk = __shfl_sync(0xffffffffu, next_chunk, 0);
-        if (next_chunk < hdr.n_chunks) load_cursor(&P.plan->chunk[next_chunk], next_cur);
+      auto page_of = [&](int pg) {  // warp-collective: every lane asks for one page id
+        const int src = pg & 31, r = (pg >> 5) & 3;
+        const int v0 = __shfl_sync(0xffffffffu, ids[0], src), v1 = __shfl_sync(0xffffffffu, ids[1], src);
+        const int v2 = __shfl_sync(0xffffffffu, ids[2], src), v3 = __shfl_sync(0xffffffffu, ids[3], src);
+        return r == 0 ? v0 : (r == 1 ? v1 : (r == 2 ? v2 : v3));
+      };
+      {
+        const long long t0 = trace ? clock64() : 0;
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        if (trace && lane == 0) trace[10] += (unsigned long long)(clock64() - t0);
       }
-      if (next_chunk >= hdr.n_chunks) break;
-      range_c = next_chunk % hdr.grid, range_j = 1 + next_chunk / hdr.grid;
-      part_range(hdr, range_c, range_j, range_begin, range_end);
-      cur = next_cur;
-      have_range = cur.b >= 0 && cur.flat < range_end;  // (chunks of a range cut short by the end of the batch are empty)
+      if (!run_open) {
+        // Publish the run.  Its slot held descriptor ndesc - kDescSlots; the stage just waited for was last used
+        // by a step of run >= ndesc - stages, and a consumer reads a run's descriptor before it releases any of
+        // the run's stages, so every consumer is done with the old contents (kDescSlots > kMaxStages + 1).
+        const int ds = ndesc & (kDescSlots - 1);
+        if (lane == 0) {
+          const int i0 = cur.flat - (cur.step - cur.first);  // flat position of the item's first step
+          RunDesc rd = {};
+          rd.kind = 1, rd.hg = cur.hg, rd.step0 = cur.step, rd.seq_len = cur.seq_len, rd.tq = cur.tq;
+          rd.item = cur.b * P.head_groups + cur.hg, rd.i0 = i0, rd.n = cur.n;
+          rd.slot = part_slot(hdr, slot_c, slot_j, slot_b, i0);  // used if the run turns out not to be the whole item
+          descs[ds] = rd;
+          mbar_arrive(&desc_bar[ds]);  // release: the stores above are visible to whoever sees the phase flip
+        }
+        ++ndesc;
+        run_open = true;
+      }
+      uint8_t* kdst = stage_base + (size_t)stage * 2 * KV_STAGE_BYTES;
+      uint8_t* vdst = kdst + KV_STAGE_BYTES;
+      if (lane == 0) {
+        step_last[stage] = last ? 1 : 0;  // the consumers end the run after this stage
+        mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)(2 * nbox * boxb));
+      }
+      __syncwarp();
+      if (P.paired) {
+        // k_map's third coordinate selects K (0) or V (1); the box takes both
+        const int i = lane;
+        const int tok = tok0 + i * P.box_slots;
+        const int page = page_of(tok >> P.bs_shift);
+        if (i < nbox)
+          tma_load_5d(kdst + (size_t)i * 2 * boxb, &k_map, &full_bar[stage], 0, tok & (P.a.block_size - 1), 0, head0, page, pol);
+      } else if (P.tma_split == 0) {
+        // nbox <= 8: one lane per box
+        const int i = lane;
+        const int tok = tok0 + i * P.box_slots;
+        const int page = page_of(tok >> P.bs_shift);  // lanes past nbox read a don't-care id
+        if (i < nbox) {
+          const int slot0 = tok & (P.a.block_size - 1);
+          tma_load_5d(kdst + (size_t)i * boxb, &k_map, &full_bar[stage], 0, slot0, 0, head0, page, pol);
+          tma_load_5d(vdst + (size_t)i * boxb, &v_map, &full_bar[stage], 0, slot0, 0, head0, page, pol);
+        }
+      } else {
+        const int per_box = P.hpc * NDC;
+        const int units = nbox * per_box;
+        for (int u0 = 0; u0 < units; u0 += 32) {
+          const int u = u0 + lane;
+          const int i = min(u / per_box, nbox - 1), r = u % per_box, h = r / NDC, dc = r % NDC;
+          const int tok = tok0 + i * P.box_slots;
+          const int page = page_of(tok >> P.bs_shift);
+          if (u < units) {
+            const int slot0 = tok & (P.a.block_size - 1);
+            const size_t off = (size_t)i * boxb + (size_t)(h * NDC + dc) * P.box_slots * 128;
+            tma_load_5d(kdst + off, &k_map, &full_bar[stage], 0, slot0, dc, head0 + h, page, pol);
+            tma_load_5d(vdst + off, &v_map, &full_bar[stage], 0, slot0, dc, head0 + h, page, pol);
+          }
+        }
+      }
+      if (++stage == P.stages) stage = 0, phase ^= 1;
+      if (last) run_open = false;
+    };
+
+    // ---- this CTA's own range: the static part, then its tail chunks while nobody else has taken them
+    {
+      const int c = (int)blockIdx.x;
+      int extent_end;
+      load_cursor(&P.plan->cta[c], cur);
+      part_range(hdr, c, 0, slot_b, extent_end);
+      slot_c = c, slot_j = 0;
+      if (cur.b >= 0 && cur.flat < extent_end) {
+        const int tc = pooled ? chunks_of(c) : 0;
+        int own_next = 0;      // next own chunk to claim
+        int claim_old = 0;     // lane 0: the packed word before the claim in flight
+        bool claim_pending = false;
+        auto claim = [&]() {
+          if (own_next < tc) {
+            if (lane == 0) claim_old = atomicAdd(&deque[c], 1);
+            claim_pending = true;
+          }
+        };
+        claim();  // chunk 0: the answer is back long before the static part ends
+        while (true) {
+          if (cur.flat + 1 == extent_end && claim_pending) {
+            // the extent ends with this step unless the next own chunk is still there
+            int ok = 0;
+            if (lane == 0) {
+              ok = ((claim_old & 0xff) + ((claim_old >> 8) & 0xff) < tc) ? 1 : 0;
+              if (!ok) atomicSub(&deque[c], 1);  // (a failed claim is taken back: the counts stay exact)
+            }
+            ok = __shfl_sync(0xffffffffu, ok, 0);
+            claim_pending = false;
+            if (ok) {
+              int pb, pe;
+              part_range(hdr, c, 1 + own_next, pb, pe);  // begins where the extent ends
+              extent_end = pe;
+              ++own_next;
+              claim();
+            }
+          }
+          const bool item_last = cur.step + 1 == cur.first + cur.n;
+          const bool ext_last = cur.flat + 1 == extent_end;
+          issue_step(item_last || ext_last);
+          if (ext_last) break;
+          cursor_next(P, cur);
+        }
+      }
+    }
+    // ---- then chunks stolen from the back of other ranges
+    while (pooled) {
+      const long long t_sw = trace ? clock64() : 0;
+      // the range with the most chunks left (ties: the nearest one after this CTA, so thieves spread out)
+      int best_key = 0;
+      for (int c0 = 0; c0 < hdr.grid; c0 += 32) {
+        const int c = c0 + lane;
+        if (c < hdr.grid) {
+          const int w = __ldcg(&deque[c]);
+          const int rem = chunks_of(c) - (w & 0xff) - ((w >> 8) & 0xff);
+          int dist = c - (int)blockIdx.x - 1;
+          if (dist < 0) dist += hdr.grid;
+          if (rem > 0) best_key = max(best_key, (rem << 20) | ((0x3ff - dist) << 10) | c);
+        }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) best_key = max(best_key, __shfl_xor_sync(0xffffffffu, best_key, o));
+      if (best_key == 0) break;  // nothing left anywhere that is not already being worked on
+      const int v = best_key & 0x3ff;
+      const int tv = chunks_of(v);
+      int j = -1;
+      if (lane == 0) {
+        const int old = atomicAdd(&deque[v], 1 << 8);
+        const int f = old & 0xff, bk = (old >> 8) & 0xff;
+        if (f + bk < tv) {
+          j = tv - 1 - bk;
+          atomicOr(&deque[v], 1 << (16 + j));  // the merge needs to know whose partial covers this chunk
+        } else {
+          atomicSub(&deque[v], 1 << 8);
+        }
+      }
+      j = __shfl_sync(0xffffffffu, j, 0);
+      if (j < 0) continue;  // lost the race: look again
+      int cb, ce;
+      part_range(hdr, v, 1 + j, cb, ce);
+      load_cursor(&P.plan->chunk[j * hdr.grid + v], cur);
+      slot_c = v, slot_j = 1 + j, slot_b = cb;
+      if (trace && lane == 0) trace[11] += (unsigned long long)(clock64() - t_sw);
+      if (cur.b < 0) continue;
+      while (true) {
+        const bool item_last = cur.step + 1 == cur.first + cur.n;
+        const bool ext_last = cur.flat + 1 == ce;
+        issue_step(item_last || ext_last);
+        if (ext_last) break;
+        cursor_next(P, cur);
+      }
     }
     // no more work
     {
@@ -553,11 +623,11 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
       }
     }
     if (pooled && lane == 0) {
-      // the CTA that is last to stop taking chunks rewinds the counters for the next launch
+      // the CTA that is last to stop taking chunks rewinds the range words for the next launch
       __threadfence();
       if (atomicAdd(&P.ws_pool[1], 1) == (int)gridDim.x - 1) {
         __threadfence();
-        P.ws_pool[0] = 0;
+        for (int c = 0; c < hdr.grid; ++c) deque[c] = 0;
         P.ws_pool[1] = 0;
       }
     }
@@ -582,8 +652,8 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
       int ticket = 0;
       if (lane == 0) {
         __threadfence();  // the consumers' partial stores (ordered before this by the hand-off) before the ticket
-        ticket = atomicAdd(&P.ws_cnt[f.item], 1);
-        if (ticket == f.nparts - 1) {
+        ticket = atomicAdd(&P.ws_cnt[f.item], f.steps) + f.steps;  // steps of the item that are done
+        if (ticket == f.n) {
           __threadfence();  // every other part's partial is visible from here on
           while (nreq - req_cnt[1] >= kReqSlots) {}  // (the consumers serve requests at every run boundary)
           reqs[nreq % kReqSlots] = f;
@@ -592,7 +662,7 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
         }
       }
       ticket = __shfl_sync(0xffffffffu, ticket, 0);
-      if (ticket == f.nparts - 1) ++nreq;
+      if (ticket == f.n) ++nreq;
     }
     if (lane == 0) mbar_arrive(epi_done);  // release: every request was posted before this
     if (trace && lane == 0) trace[5] = clock64(), trace[6] = global_ns();
@@ -725,8 +795,13 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
     __threadfence();
     const int rec_heads = P.hpc * P.group;
     if (warp == 0) {
+      // Who holds a partial of this item: in every range the item overlaps, the range's owner (if its static part
+      // or a tail chunk nobody stole overlaps the item) and the thief of every stolen chunk that overlaps it - the
+      // range's claim word says which chunks were stolen.  Every overlapping chunk has been processed by now
+      // (the item's step count is complete), so "not stolen" means the owner did it.
       const PlanHeader hdr = P.plan->hdr;
-      const int J = 1 + hdr.n_rounds;
+      const int T = hdr.n_rounds, J = 1 + T;
+      const int* deque = P.ws_pool + kDequeWord0;
       const int i0 = f.i0, i1 = f.i0 + f.n;
       const int ca = i0 / hdr.per, ncand = ((i1 - 1) / hdr.per - ca + 1) * J;
       int np = 0;
@@ -736,16 +811,26 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
         int slot = 0;
         if (idx < ncand) {
           const int c = ca + idx / J, j = idx % J;
+          const int stolen = T > 0 ? (__ldcg(&deque[c]) >> 16) & 0xff : 0;
           int pb, pe;
           part_range(hdr, c, j, pb, pe);
           hit = max(pb, i0) < min(pe, i1);
+          if (j == 0) {
+            for (int r = 1; r <= T; ++r) {
+              int qb, qe;
+              part_range(hdr, c, r, qb, qe);
+              hit = hit || (!((stolen >> (r - 1)) & 1) && max(qb, i0) < min(qe, i1));
+            }
+          } else {
+            hit = hit && ((stolen >> (j - 1)) & 1);
+          }
           slot = part_slot(hdr, c, j, pb, i0);
         }
         const unsigned m = __ballot_sync(0xffffffffu, hit);
         if (hit) part_slots[np + __popc(m & ((1u << lane) - 1u))] = (short)slot;
         np += __popc(m);
       }
-      if (lane == 0) req_cnt[3] = np;  // == f.nparts: the producers counted the same candidates
+      if (lane == 0) req_cnt[3] = np;
     }
     asm volatile("bar.sync 1, %0;" ::"r"(NW * 32));
     const int nparts = req_cnt[3];
@@ -821,12 +906,12 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
   // hand-off to the ticket warp (kFinSlots slots; every consumer warp arrives, warp 0 writes the descriptor)
   RunDesc run = {};
   int nfin = 0;
-  auto publish_fin = [&](int kind, int item, int hg, int tq) {
+  auto publish_fin = [&](int kind, int item, int hg, int tq, int steps) {
     const int fs = nfin % kFinSlots;
     mbar_wait(&fin_empty[fs], (((uint32_t)nfin / kFinSlots) & 1u) ^ 1u);  // the slot's previous hand-off has been taken
     if (warp == 0 && lane == 0) {
       FinDesc& f = fins[fs];
-      f.kind = kind, f.item = item, f.hg = hg, f.tq = tq, f.nparts = run.nparts, f.i0 = run.i0, f.n = run.n;
+      f.kind = kind, f.item = item, f.hg = hg, f.tq = tq, f.steps = steps, f.i0 = run.i0, f.n = run.n;
     }
     __syncwarp();
     if (lane == 0) mbar_arrive(&fin_full[fs]);  // release: this warp's partial stores (and the descriptor) come first
@@ -841,20 +926,25 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
   if (trace && threadIdx.x == 0) trace[2] = clock64();
   if (run.kind == 0) {
     if (trace && threadIdx.x == 0) trace[3] = trace[4] = clock64();
-    publish_fin(0, 0, 0, 0);
+    publish_fin(0, 0, 0, 0, 0);
     return;
   }
   cur.hg = run.hg, cur.step = run.step0, cur.seq_len = run.seq_len;
   reset_state();
   load_q(run.tq, run.hg);
   bool first_stage = true;
-  int steps_left = run.nsteps;
+  int steps_done = 0;  // of the current run
 
   int stage = 0;
   uint32_t phase = 0;
   while (true) {
     const int tok0 = cur.step * P.tps + tok_off;  // first token of this warp's tile
-    mbar_wait(&full_bar[stage], phase);
+    {
+      const long long t0 = trace ? clock64() : 0;
+      mbar_wait(&full_bar[stage], phase);
+      if (trace && threadIdx.x == 0 && !first_stage) trace[9] += (unsigned long long)(clock64() - t0);
+    }
+    const bool run_ends = step_last[stage] != 0;  // (written before the stage was armed)
     if (trace && first_stage && threadIdx.x == 0) trace[3] = clock64();
     first_stage = false;
     if (tok0 < cur.seq_len) {
@@ -1042,12 +1132,13 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
     if (lane == 0) mbar_arrive(&empty_bar[stage]);
     if (++stage == P.stages) stage = 0, phase ^= 1;
 
-    ++cur.step;
-    if (--steps_left == 0) {
+    ++cur.step, ++steps_done;
+    if (run_ends) {
       // ---------------- finalise this run ------------------
+      const long long t_fin = trace ? clock64() : 0;
       const int item = run.item;
       const int hg_done = run.hg;
-      const bool direct = run.slot < 0;
+      const bool direct = steps_done == run.n;  // the run was the whole item
       const int tq = run.tq;
       // Take the next run first: its query rows are in flight while this one is merged and stored.  The query
       // fragments are dead after the run's last tile; the accumulators are reset only after the merge has
@@ -1124,17 +1215,18 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
           }
         }
       }
-      if (!direct) publish_fin(1, item, hg_done, tq);  // the partial is on its way to memory: its ticket is the ticket warp's
+      if (!direct) publish_fin(1, item, hg_done, tq, steps_done);  // the partial is on its way to memory: its ticket is the ticket warp's
       serve_requests();                                // items this CTA has to merge
+      if (trace && threadIdx.x == 0) trace[8] += (unsigned long long)(clock64() - t_fin);
       if (last) break;
       asm volatile("bar.sync 1, %0;" ::"r"(NW * 32));  // merge buffers are reused by the next run
       reset_state();
       run = nx;
       cur.hg = run.hg, cur.step = run.step0, cur.seq_len = run.seq_len;
-      steps_left = run.nsteps;
+      steps_done = 0;
     }
   }
-  publish_fin(0, 0, 0, 0);  // no more partials from this CTA
+  publish_fin(0, 0, 0, 0, 0);  // no more partials from this CTA
   while (!serve_requests()) {}  // merge what the ticket warp still hands back, until it has taken its last ticket
 }
 
@@ -1200,8 +1292,14 @@ int decode_geometry(const b200attn_attention_params& a, DecodeGeom* G) {
   // grid, and a grid that followed max_seqlen_k would differ between a captured launch and its replays.
   G->grid = dev.num_sms < kMaxDecodeCtas ? dev.num_sms : kMaxDecodeCtas;
   if (G->grid < 1) G->grid = 1;
-  // pool share: tuning().decode_ctas_per_sm re-used as "sixteenths of a CTA's steps" (0 = default, >= 100 = none)
-  G->pool_sixteenths = tn.decode_ctas_per_sm <= 0 ? 3 : (tn.decode_ctas_per_sm >= 100 ? 0 : (tn.decode_ctas_per_sm > 12 ? 12 : tn.decode_ctas_per_sm));
+  // Share of every range that its owner may lose to idle CTAs (work stealing, see the producer warp), in 1/16 of
+  // the range.  OFF by default: measured on B200 it levels the CTAs' finish times (end skew 10 -> 6 us on the
+  // 1-kv-head C4 shard) but what the thieves pay for it - a finalize per stolen chunk at 3.6 us each, on consumers
+  // that are the bottleneck of the fp8 variant - eats the gain: 96.8 vs 95.9 us there, 163.8 vs 162.0 us on C2
+  // (profiles/r02_kbench_pool_v6_stealing.jsonl; the shared-pool variants before it were 10-15 % slower,
+  // profiles/r02_kbench_pool_v1..v5).  Off, the cut is static, so results are bit-reproducible from launch to
+  // launch.  tuning().decode_ctas_per_sm (b200attn_set_tuning's second argument) = sixteenths, 1..12, turns it on.
+  G->pool_sixteenths = (tn.decode_ctas_per_sm <= 0 || tn.decode_ctas_per_sm >= 100) ? 0 : (tn.decode_ctas_per_sm > 12 ? 12 : tn.decode_ctas_per_sm);
   G->min_chunk = (tn.reserved & 1024) ? 1 : ((tn.reserved & 2048) ? 4 : 2);
   return B200ATTN_OK;
 }
@@ -1236,7 +1334,7 @@ int launch_variant(const b200attn_attention_params& a, const DecodeGeom& G, Deco
   P.box_slots = G.box_slots, P.boxes = G.boxes;
   P.tma_split = tn.reserved & 1;
   const int fixed = NW * 8 * D * 4 + NW * 8 * 2 * 4 + (2 * kMaxStages + kDescSlots + 2 * kFinSlots + 1) * 8 +
-                    kDescSlots * (int)sizeof(RunDesc) + (kFinSlots + kReqSlots) * (int)sizeof(FinDesc) + 16 + kMaxParts * 2;
+                    kDescSlots * (int)sizeof(RunDesc) + (kFinSlots + kReqSlots) * (int)sizeof(FinDesc) + 16 + kMaxStages * 4 + kMaxParts * 2;
   int stages = (dev.max_smem_optin - fixed) / (2 * KV_STAGE_BYTES);
   if (stages > kMaxStages) stages = kMaxStages;
   if (tn.decode_stages > 0 && tn.decode_stages < stages) stages = tn.decode_stages;
@@ -1304,10 +1402,10 @@ int launch_plan_kernel(const b200attn_attention_params& a, const DecodeGeom& G, 
 
 // The ticket counters live in a region of FIXED size at the start of the workspace: they are the only bytes
 // that must be zero between calls, and the same buffer serves calls of every shape (a batch grows and shrinks
-// from step to step), so their region may never be another shape's partial-result region.  Its last 64 bytes
-// hold the pool's chunk counter and the count of CTAs that have stopped taking chunks.
+// from step to step), so their region may never be another shape's partial-result region.  Its last KiB holds
+// the ranges' claim words (owner / thief chunk claims) and the count of CTAs that have stopped taking chunks.
 constexpr uint64_t kCounterBytes = 1ull << 20;  // one int per (sequence, head group): 262128 items
-constexpr uint64_t kPoolCounterOffset = kCounterBytes - 64;
+constexpr uint64_t kPoolCounterOffset = kCounterBytes - 1024;  // [1] CTAs done, [kDequeWord0 + c] range c's claim word
 
 uint64_t decode_plan_bytes(int num_seqs) {
   return ((sizeof(Plan) + 4ull * ((uint64_t)(num_seqs > 0 ? num_seqs : 0) + 1) + 255) / 256) * 256;
