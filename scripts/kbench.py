@@ -244,6 +244,8 @@ PREFILL_SHAPES = {
     "full2k": [(2048, 2048)] * 4,
     "full1k": [(1024, 1024)] * 8,
     "chunk": [(2048, 6144), (2048, 8192)],
+    # the multi-token sequences of C3 alone (what the tensor-bound kernels do in the mixed batch)
+    "mixed_prompts": None,
     # C3: 32 decode rows + fresh prompt + 2 chunked continuations + 4 prefix hits
     "mixed": None,
 }
@@ -272,6 +274,8 @@ def prefill_case(args, device):
     g = torch.Generator(device=device).manual_seed(0)
     hq, hkv, D, bs = args.hq or 32, args.hkv or 8, 128, args.bs or 16
     lens = PREFILL_SHAPES[args.shape] or mixed_c3()
+    if args.shape == "mixed_prompts":
+        lens = [x for x in lens if x[0] > 1]
     q_lens = [a for a, _ in lens]
     kv_lens = [b for _, b in lens]
     pages = [(n + bs - 1) // bs for n in kv_lens]
@@ -315,8 +319,8 @@ def prefill_case(args, device):
 def run_prefill(args, device):
     _, tf = peaks()
     fn, flops, cfg = prefill_case(args, device)
-    _cabi.set_tuning(0, 0, 0, args.tune)
-    cfg["tune"] = args.tune
+    _cabi.set_tuning(args.hpc, 0, 0, args.tune)
+    cfg["tune"], cfg["hpc"] = args.tune, args.hpc
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=device) if args.flush else None
     ms, n = time_fn(fn, flush=flush)
     tfs = flops / ms / 1e9

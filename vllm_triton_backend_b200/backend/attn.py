@@ -128,7 +128,8 @@ class B200AttentionMetadataBuilder(AttentionMetadataBuilder[B200AttentionMetadat
         # grid does not depend on the lengths.
         attn_metadata.seq_lens.fill_(1)
         if self.decode_plan is not None:  # the plan follows seq_lens
-            self.decode_plan.build(attn_metadata.query_start_loc, attn_metadata.seq_lens, attn_metadata.max_query_len)
+            self.decode_plan.build(attn_metadata.query_start_loc, attn_metadata.seq_lens, attn_metadata.max_query_len,
+                                   attn_metadata.num_actual_tokens)
         return attn_metadata
 
     def build(self, common_prefix_len: int, common_attn_metadata: CommonAttentionMetadata,
@@ -136,7 +137,7 @@ class B200AttentionMetadataBuilder(AttentionMetadataBuilder[B200AttentionMetadat
         m = common_attn_metadata
         self._fit_workspace(m.seq_lens.shape[0])
         if self.decode_plan is not None:
-            self.decode_plan.build(m.query_start_loc, m.seq_lens, m.max_query_len)
+            self.decode_plan.build(m.query_start_loc, m.seq_lens, m.max_query_len, m.num_actual_tokens)
         return B200AttentionMetadata(
             num_actual_tokens=m.num_actual_tokens,
             max_query_len=m.max_query_len,

@@ -1250,6 +1250,29 @@ inline int pick_hpc(int hkv, int nw, int want) {
   return hpc;
 }
 
+}  // namespace
+
+int mixed_decode_ctas(const b200attn_attention_params& a, int grid) {
+  const Tuning& tn = tuning();
+  const int forced = (tn.reserved >> 13) & 0xff;  // A/B: tuning().reserved bits 13..20 = CTAs
+  if (forced > 0) return forced < grid ? forced : grid;
+  // Only host ints are known: at most B - 1 single-token rows, at least T - B + 1 tokens in multi-token queries,
+  // and no context lengths - take them as alike.  Rows stream Hkv * D * (|K| + |V|) bytes per context token,
+  // prompt tokens cost 4 * Hq * D FLOPs per context token; with the measured peaks (6.5 TB/s, 1.2 PFLOP/s
+  // for this kernel) the rows' share of the step's time is t_rows / (t_rows + t_prompts).
+  const double rows = a.num_seqs > 1 ? a.num_seqs - 1 : 0, multi = a.num_tokens - a.num_seqs + 1;
+  if (rows <= 0 || multi <= 0) return grid;
+  const double esz = a.kv_dtype == B200ATTN_FP8_E4M3 ? 1.0 : 2.0;
+  // (x 1.15: measured best on C3 - 32 CTAs where the plain ratio gives 29)
+  const double ratio = 1.15 * rows / multi * (a.num_kv_heads * 2.0 * esz * 185.0) / (4.0 * a.num_q_heads);
+  int k = (int)(grid * ratio / (1.0 + ratio) + 0.5);
+  if (k < 8) k = 8;
+  if (k * 4 > grid * 3) return grid;  // mostly rows: they get every SM, and the prompts follow
+  return k;
+}
+
+namespace {
+
 int decode_geometry(const b200attn_attention_params& a, DecodeGeom* G) {
   const Tuning& tn = tuning();
   const DeviceInfo& dev = device_info();
@@ -1268,7 +1291,11 @@ int decode_geometry(const b200attn_attention_params& a, DecodeGeom* G) {
     // (sequence, head group) items means more outputs written directly and
     // parallel merges, but the copy engine pays per box (measured on B200,
     // profiles/r01_decode_sweep_v2.jsonl: bf16 KV is best at 4 KB boxes, fp8 at 8 KB).
-    const int min_box = G->fp8 ? 8192 : 4096;
+    // Beside the prompts of a mixed batch the rows run on a share of the SMs, and one SM alone pulls about
+    // 50 GB/s through 4 KB boxes however idle HBM is: there the box is as big as the heads allow
+    // (C3: 0.487 -> 0.440 ms from 1 to 8 kv heads per box, profiles/r02_kbench_mixed_overlap.jsonl).
+    const bool beside_prompts = a.max_seqlen_q > 1 && !(tn.reserved & 4096);
+    const int min_box = beside_prompts ? 32768 : (G->fp8 ? 8192 : 4096);
     int hpc = 1;
     while (hpc < G->nw && a.num_kv_heads % (hpc * 2) == 0) {
       const int tps = G->nw * G->tt / hpc;
@@ -1292,6 +1319,8 @@ int decode_geometry(const b200attn_attention_params& a, DecodeGeom* G) {
   // grid, and a grid that followed max_seqlen_k would differ between a captured launch and its replays.
   G->grid = dev.num_sms < kMaxDecodeCtas ? dev.num_sms : kMaxDecodeCtas;
   if (G->grid < 1) G->grid = 1;
+  // the single-token rows of a mixed batch run beside its prompts on a share of the SMs (cabi.cu)
+  if (a.max_seqlen_q > 1 && !(tn.reserved & 4096)) G->grid = mixed_decode_ctas(a, G->grid);
   // Share of every range that its owner may lose to idle CTAs (work stealing, see the producer warp), in 1/16 of
   // the range.  OFF by default: measured on B200 it levels the CTAs' finish times (end skew 10 -> 6 us on the
   // 1-kv-head C4 shard) but what the thieves pay for it - a finalize per stolen chunk at 3.6 us each, on consumers

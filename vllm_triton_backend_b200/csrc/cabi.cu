@@ -83,6 +83,33 @@ int ensure_dynamic_smem(const void* kernel, int bytes, const char* what) {
   return B200ATTN_OK;
 }
 
+// A second stream per device for the HBM-bound half of a mixed batch (see b200attn_unified_attention): created on
+// first use, never destroyed (a per-device resource like the attributes above).  nullptr if it cannot be had.
+SideStream* side_stream(bool may_create) {
+  static SideStream streams[kMaxDevices];
+  static std::mutex mu;
+  const int dev = device_info().device;
+  SideStream& ss = streams[dev];
+  if (ss.ready) return &ss;
+  if (!may_create) return nullptr;
+  std::lock_guard<std::mutex> lock(mu);
+  if (ss.ready) return &ss;
+  if (ss.failed) return nullptr;
+  int lo = 0, hi = 0;
+  cudaStream_t st = nullptr;
+  cudaEvent_t e1 = nullptr, e2 = nullptr;
+  if (cudaDeviceGetStreamPriorityRange(&lo, &hi) != cudaSuccess ||
+      cudaStreamCreateWithPriority(&st, cudaStreamNonBlocking, hi) != cudaSuccess ||
+      cudaEventCreateWithFlags(&e1, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&e2, cudaEventDisableTiming) != cudaSuccess) {
+    (void)cudaGetLastError();
+    ss.failed = true;
+    return nullptr;
+  }
+  ss.stream = st, ss.fork = e1, ss.join = e2, ss.ready = true;
+  return &ss;
+}
+
 EncodeTiledFn encode_tiled_fn() {
   static EncodeTiledFn fn = nullptr;
   static std::once_flag once;
@@ -264,6 +291,40 @@ int b200attn_unified_attention(const b200attn_attention_params* pp, b200attn_str
   // every sequence has exactly max_seqlen_q tokens <=> T == B * max_seqlen_q (true of THIS batch only: not used
   // when the launches are being captured)
   const bool uniform = !captured && (int64_t)p.num_tokens == (int64_t)p.num_seqs * p.max_seqlen_q;
+  // The single-token rows are HBM-bound, the prompts tensor-bound: run one beside the other.  The split-KV launch
+  // goes FIRST, on a second (high-priority) stream forked from this one, with its grid capped at the rows' share
+  // of the step (mixed_decode_ctas); the tcgen05 grid is persistent (one CTA per free SM, the rest of its tiles
+  // taken by cluster launch control), so it fills the SMs the rows leave and gets the others as the rows finish.
+  // The reference covers the whole mixed batch with one launch of its 2D kernel
+  // (triton_unified_attention.py:275-523); round 1 ran its three launches back to back, 0.533 ms where the
+  // tensor-bound share alone takes 0.256 (C3).  Fork and join are events, so the pattern is graph-capturable.
+  // tuning().reserved bit 12 keeps the launches on one stream.
+  bool dec_due = dec_ok && !uniform;  // a launch for the single-token rows is still to come
+  SideStream* ss = nullptr;
+  int rc_side = B200ATTN_OK;
+  if (dec_due && !(g_tuning.reserved & 4096) && mixed_decode_ctas(p, device_info().num_sms) < device_info().num_sms &&
+      (ss = side_stream(/*may_create=*/!captured)) != nullptr) {
+    if (cudaEventRecord(ss->fork, stream) == cudaSuccess && cudaStreamWaitEvent(ss->stream, ss->fork, 0) == cudaSuccess) {
+      rc_side = launch_attn_decode(p, ss->stream, /*only_single_token_seqs=*/true);
+      dec_due = false;
+    } else {
+      (void)cudaGetLastError();
+      ss = nullptr;
+    }
+  } else {
+    ss = nullptr;
+  }
+  // every way out of the mixed path: wait for the forked launch, then the rows' launch if it was not forked
+  auto finish = [&](int rc_main) {
+    if (ss) {
+      cudaEventRecord(ss->join, ss->stream);
+      cudaStreamWaitEvent(stream, ss->join, 0);
+    }
+    if (rc_main) return rc_main;
+    if (rc_side) return rc_side;
+    if (dec_due) return launch_attn_decode(p, stream, /*only_single_token_seqs=*/true);
+    return (int)B200ATTN_OK;
+  };
   if (p.kv_dtype == B200ATTN_FP8_E4M3 && !(g_tuning.reserved & 256)) {
     // FP8 cache: the sequences with long queries are dequantised once into the staging pool (the part of
     // the workspace past the decode region) and run the tcgen05 kernel on it; what does not fit the pool,
@@ -275,9 +336,9 @@ int b200attn_unified_attention(const b200attn_attention_params* pp, b200attn_str
         QLenRange r;
         r.min_q_len = prefill_tc_min_q_len(s16);
         rc = launch_kv_stage(p, st, r, stream);
-        if (rc) return rc;
+        if (rc) return finish(rc);
         rc = launch_attn_prefill_tc(s16, stream, r, st.staged_base);
-        if (rc) return rc;
+        if (rc) return finish(rc);
         QLenRange rest;  // every multi-token query that was not staged
         rest.min_q_len = dec_ok ? 2 : 0;
         // a pool that holds every sequence at full length cannot overflow: only short queries are left
@@ -286,31 +347,35 @@ int b200attn_unified_attention(const b200attn_attention_params* pp, b200attn_str
         if (fits) rest.max_q_len = r.min_q_len - 1;
         if (rest.max_q_len >= rest.min_q_len && !(uniform && fits)) {
           rc = launch_attn_prefill(p, stream, rest, st.staged_base);
-          if (rc) return rc;
+          if (rc) return finish(rc);
         }
-        if (dec_ok && !uniform) return launch_attn_decode(p, stream, /*only_single_token_seqs=*/true);
-        return B200ATTN_OK;
+        return finish(B200ATTN_OK);
       }
     }
   }
-  int short_max = 0x7fffffff;  // longest query the mma.sync launch takes
-  if (prefill_tc_supported(p, &why) && (captured || p.max_seqlen_q >= prefill_tc_min_q_len(p))) {
+  // Long queries: tcgen05.  What it leaves - short extends - runs the mma.sync kernel; like the rows they are short
+  // on arithmetic, so when the rows were forked they go with them (their launch needs nothing from this stream).
+  const bool tc = prefill_tc_supported(p, &why) && (captured || p.max_seqlen_q >= prefill_tc_min_q_len(p));
+  if (!tc && uniform) return finish(launch_attn_prefill(p, stream));
+  QLenRange r_short;
+  r_short.min_q_len = dec_ok ? 2 : 0;
+  r_short.max_q_len = tc ? prefill_tc_min_q_len(p) - 1 : 0x7fffffff;
+  const bool short_due = r_short.max_q_len >= r_short.min_q_len && !(tc && uniform);
+  if (short_due && ss) {
+    rc = launch_attn_prefill(p, ss->stream, r_short);
+    if (rc) return finish(rc);
+  }
+  if (tc) {
     QLenRange r;
     r.min_q_len = prefill_tc_min_q_len(p);
     rc = launch_attn_prefill_tc(p, stream, r);
-    if (rc || uniform) return rc;
-    short_max = r.min_q_len - 1;
+    if (rc) return finish(rc);
   }
-  if (uniform) return launch_attn_prefill(p, stream);
-  QLenRange r;
-  r.min_q_len = dec_ok ? 2 : 0;
-  r.max_q_len = short_max;
-  if (short_max >= r.min_q_len) {
-    rc = launch_attn_prefill(p, stream, r);
-    if (rc) return rc;
+  if (short_due && !ss) {
+    rc = launch_attn_prefill(p, stream, r_short);
+    if (rc) return finish(rc);
   }
-  if (dec_ok) return launch_attn_decode(p, stream, /*only_single_token_seqs=*/true);
-  return B200ATTN_OK;
+  return finish(B200ATTN_OK);
 }
 
 }  // extern "C"

@@ -40,6 +40,16 @@ const DeviceInfo& device_info();  // of the calling thread's current device
 int ensure_dynamic_smem(const void* kernel, int bytes, const char* what);
 constexpr int kMaxDecodeCtas = 160;  // decode grid = min(#SMs, this); the split-KV workspace is sized for it
 
+struct SideStream {
+  cudaStream_t stream = nullptr;
+  cudaEvent_t fork = nullptr, join = nullptr;
+  bool ready = false, failed = false;
+};
+SideStream* side_stream(bool may_create);
+// CTAs the split-KV kernel gets for the single-token rows of a mixed batch when they run beside the prompts
+// (b200attn_unified_attention); == the full grid when running beside them is not worth it.  Host ints only.
+int mixed_decode_ctas(const b200attn_attention_params& p, int grid);
+
 // cuTensorMapEncodeTiled resolved through cudaGetDriverEntryPoint (no -lcuda, so
 // the library also loads on machines without a driver).
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,

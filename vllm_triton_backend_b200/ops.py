@@ -105,8 +105,10 @@ class DecodePlan:
         p.q_stride0, p.q_stride1 = num_q_heads * head_size, head_size
         self._p, self._key_out, self._fn, self.key, self._keep = p, ctypes.c_uint64(0), lib.b200attn_decode_plan, 0, None
 
-    def build(self, cu_seqlens_q: torch.Tensor, seqused_k: torch.Tensor, max_seqlen_q: int) -> int:
-        """Launches the plan kernel on the current stream; returns the key (0: nothing to plan for this shape)."""
+    def build(self, cu_seqlens_q: torch.Tensor, seqused_k: torch.Tensor, max_seqlen_q: int, num_tokens: int = 0) -> int:
+        """Launches the plan kernel on the current stream; returns the key (0: nothing to plan for this shape).
+        `num_tokens` (query tokens of the step) matters for mixed batches only: it sizes the share of the SMs the
+        single-token rows get beside the prompts."""
         n = seqused_k.shape[0]
         if n > self.max_seqs:
             if torch.cuda.is_current_stream_capturing():
@@ -119,6 +121,7 @@ class DecodePlan:
         p = self._p
         p.seq_lens, p.cu_seqlens_q, p.num_seqs = seqused_k.data_ptr(), cu_seqlens_q.data_ptr(), n
         p.max_seqlen_q = int(max_seqlen_q)
+        p.num_tokens = int(num_tokens) if num_tokens else n
         rc = self._fn(ctypes.byref(p), self.buf.data_ptr(), self.buf.numel(), ctypes.byref(self._key_out),
                       torch.cuda.current_stream(self.buf.device).cuda_stream)
         if rc:
