@@ -272,7 +272,7 @@ def mixed_c3(seed=0):
 
 def prefill_case(args, device):
     g = torch.Generator(device=device).manual_seed(0)
-    hq, hkv, D, bs = args.hq or 32, args.hkv or 8, 128, args.bs or 16
+    hq, hkv, D, bs = args.hq or 32, args.hkv or 8, getattr(args, "d", 0) or 128, args.bs or 16
     lens = PREFILL_SHAPES[args.shape] or mixed_c3()
     if args.shape == "mixed_prompts":
         lens = [x for x in lens if x[0] > 1]
@@ -367,6 +367,7 @@ def main():
     ap.add_argument("--batch", type=int, default=0)
     ap.add_argument("--ctx", type=int, default=0)
     ap.add_argument("--bs", type=int, default=0)
+    ap.add_argument("--d", type=int, default=0, help="prefill: head size (default 128)")
     ap.add_argument("--tokens", type=int, default=8192)
     ap.add_argument("--fp8", action="store_true")
     ap.add_argument("--flush", action="store_true")

@@ -256,21 +256,40 @@ TC_CASES = [
 @pytest.mark.parametrize("lens,Hq,Hkv,bs", TC_CASES)
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
 @pytest.mark.parametrize("interleaved", [False, True])
-def test_prefill_tc_matches_oracle(lens, Hq, Hkv, bs, dtype, interleaved):
-    """Every sequence forced through the tcgen05 kernel (force_selection=4)."""
-    inp = make_paged_inputs(lens, Hq, Hkv, 128, bs, dtype=dtype, seed=Hq + bs, interleaved=interleaved)
-    scale = 128 ** -0.5
+@pytest.mark.parametrize("D", [128, 64])
+def test_prefill_tc_matches_oracle(lens, Hq, Hkv, bs, dtype, interleaved, D):
+    """Every sequence forced through the tcgen05 kernel (force_selection=4), head sizes 128 and 64."""
+    inp = make_paged_inputs(lens, Hq, Hkv, D, bs, dtype=dtype, seed=Hq + bs, interleaved=interleaved)
+    scale = D ** -0.5
     out, kern = _run(inp, scale, PREFILL_TC)
     assert kern == "attn_prefill_tc", kern
     assert_close(out, _oracle(inp, scale), atol=BF16_ATOL, rtol=BF16_RTOL, what="prefill_tc")
     assert not torch.isnan(out).any()
 
 
+@pytest.mark.parametrize("Hq,Hkv", [(40, 8), (6, 2), (12, 4), (7, 1), (48, 4), (36, 3), (10, 1)])
+@pytest.mark.parametrize("D", [128, 64])
+@pytest.mark.parametrize("forced", [True, False])
+def test_prefill_tc_groups_that_are_not_powers_of_two(Hq, Hkv, D, forced):
+    """GQA groups of 5, 3, 7, 12, 10: the Q tile pads the group to the next power of two (the padding rows hold the
+    next kv head's queries, or nothing past the last head, and are never stored).  Forced and through AUTO, where
+    these shapes must now reach the tcgen05 kernel (reference head / group coverage: one kernel serves them all,
+    ibm-triton-lib/ibm_triton_lib/kernels/triton_unified_attention.py:275-523)."""
+    lens = [(300, 300), (64, 1064), (1, 555), (5, 40), (513, 2049), (129, 129)]
+    inp = make_paged_inputs(lens, Hq, Hkv, D, 16, dtype=torch.bfloat16, seed=Hq * 7 + D)
+    scale = D ** -0.5
+    out, kern = _run(inp, scale, PREFILL_TC if forced else DECODE_OR_AUTO)
+    assert kern == "attn_prefill_tc", kern
+    assert_close(out, _oracle(inp, scale), atol=BF16_ATOL, rtol=BF16_RTOL, what=f"prefill_tc g={Hq // Hkv} D={D}")
+    assert not torch.isnan(out).any()
+
+
 @pytest.mark.parametrize("window", [64, 128, 300])
-def test_prefill_tc_sliding_window(window):
+@pytest.mark.parametrize("D", [128, 64])
+def test_prefill_tc_sliding_window(window, D):
     lens = [(1, 1328), (129, 463), (300, 300), (700, 1500)]
-    inp = make_paged_inputs(lens, 8, 2, 128, 16, dtype=torch.bfloat16, seed=23)
-    scale = 128 ** -0.5
+    inp = make_paged_inputs(lens, 8, 2, D, 16, dtype=torch.bfloat16, seed=23)
+    scale = D ** -0.5
     out, kern = _run(inp, scale, PREFILL_TC, window=window)
     assert kern == "attn_prefill_tc"
     assert_close(out, _oracle(inp, scale, window), atol=BF16_ATOL, rtol=BF16_RTOL, what=f"window {window}")
@@ -281,12 +300,13 @@ def test_prefill_tc_sliding_window(window):
     (0.0, False, 0, True), (30.0, False, 200, True),
 ])
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
-def test_prefill_tc_softcap_alibi_and_sinks(softcap, sinks, window, alibi, dtype):
+@pytest.mark.parametrize("D,Hkv", [(128, 2), (64, 2), (64, 1), (128, 8)])
+def test_prefill_tc_softcap_alibi_and_sinks(softcap, sinks, window, alibi, dtype, D, Hkv):
     """Softcap (tanh of S before masking), ALiBi (slope * (key position - context length)) and attention
     sinks (epilogue only) inside the tcgen05 kernel; large logits so that the cap actually bends them."""
     lens = [(1, 1328), (129, 463), (300, 300), (700, 1500), (5, 40)]
-    Hq = 8
-    inp = make_paged_inputs(lens, Hq, 2, 128, 16, dtype=dtype, seed=37)
+    Hq = 8 if Hkv < 8 else 40  # (40q / 8kv: a padded group of 5)
+    inp = make_paged_inputs(lens, Hq, Hkv, D, 16, dtype=dtype, seed=37)
     inp["q"] = inp["q"] * 3
     sink_t = torch.linspace(-2.0, 6.0, Hq, dtype=torch.float32) if sinks else None
     slopes = torch.tensor([2.0 ** (-(i + 1) * 8.0 / Hq) for i in range(Hq)], dtype=torch.float32) if alibi else None

@@ -21,7 +21,7 @@ def _case(seed):
     r = random.Random(1000 + seed)
     D = r.choice([64, 128, 128, 128, 256])
     Hkv = r.choice([1, 2, 4, 8])
-    g = r.choice([1, 2, 4, 8] + ([16] if D <= 128 else []))
+    g = r.choice([1, 2, 3, 4, 4, 5, 6, 8, 8] + ([12, 16] if D <= 128 else []))
     bs = r.choice([16, 16, 32, 64, 128])
     fp8 = r.random() < 0.35
     dtype = r.choice([torch.bfloat16, torch.float16])

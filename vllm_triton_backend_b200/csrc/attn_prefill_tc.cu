@@ -34,19 +34,26 @@
 namespace b200attn {
 namespace {
 
-constexpr int kD = 128;
 constexpr int kBN = 128;                        // kv tokens per tile
 constexpr int kKStages = 3;                     // K is needed right after PV of the previous tile: prefetch deeper
 constexpr int kVStages = 2;
 constexpr int kSubtileBytes = 128 * 128;        // [128 rows][128 B]: one 64-element chunk of 128 rows
-constexpr int kTileBytes = 2 * kSubtileBytes;   // 128 rows x 128 dims x 2 B
 constexpr int kThreads = 384;
-// TMEM columns: S0 | S1 | O0 | O1 (subtile w: S at 128 w, O at 256 + 128 w)
+// Head size kD is 64 or 128: a tile of 128 rows is kD / 64 sub-tiles of [128 rows][128 B].
+// TMEM columns: S0 | S1 | O0 | O1 (subtile w: S at 128 w, O at 256 + kD w)
 __host__ __device__ constexpr uint32_t col_s(int w) { return 128u * (uint32_t)w; }
-__host__ __device__ constexpr uint32_t col_o(int w) { return 256u + 128u * (uint32_t)w; }
-constexpr int kSmemQ = 0;
-constexpr int kSmemK = 2 * kTileBytes;
-constexpr int kSmemV = kSmemK + kKStages * kTileBytes;
+template <int kD> __host__ __device__ constexpr uint32_t col_o(int w) { return 256u + (uint32_t)kD * (uint32_t)w; }
+template <int kD> struct Smem {
+  static constexpr int kTileBytes = (kD / 64) * kSubtileBytes;  // 128 rows x kD dims x 2 B
+  static constexpr int kQ = 0;
+  static constexpr int kK = 2 * kTileBytes;
+  static constexpr int kV = kK + kKStages * kTileBytes;
+  static constexpr int kBar = kV + kVStages * kTileBytes;
+  static constexpr int kBarBytes = 256;                 // NUM_BARS * 8 = 208, tmem pointer behind them
+  static constexpr int kItems = kBar + kBarBytes;       // 2 x Item
+  static constexpr int kClc = kItems + 2 * 64;          // 16-byte try_cancel response
+  static constexpr int kBytes = kClc + 64 + 1024;       // + alignment slack
+};
 constexpr float kRescaleThreshold = 8.0f;          // log2 units
 
 #ifdef B200ATTN_TC_TRACE
@@ -73,8 +80,10 @@ __device__ __forceinline__ long long tc_globaltimer() {
 
 struct TcParams {
   b200attn_attention_params a;
-  int group;      // query heads per kv head (power of two, <= 128)
-  int block_q;    // tokens per 128-row subtile
+  int group;      // query heads per kv head
+  int group_pad;  // rows per token in a Q tile: the next power of two (rows of heads >= group are padding: they hold
+                  // the next kv head's query heads, or zeros past the last, and are never stored)
+  int block_q;    // tokens per 128-row subtile = 128 / group_pad
   int min_q_len, max_q_len;
   int box_slots;  // tokens per TMA box = min(block_size, 128)
   const int32_t* staged_base;  // FP8 staging (kv_stage.cu): page p of sequence b is staged_base[b] + p of the
@@ -273,11 +282,6 @@ enum Bar {
   Q_FULL = 0, Q_EMPTY = 1, K_FULL = 2, K_EMPTY = 5, V_FULL = 8, V_EMPTY = 10, S_FULL = 12, P_FULL = 14, P_FULLB = 16,
   O_DONE = 18, V_FIX = 20, ITEM_FULL = 21, ITEM_EMPTY = 23, CLC_DONE = 25, NUM_BARS = 26
 };
-constexpr int kSmemBar = kSmemV + kVStages * kTileBytes;
-constexpr int kBarBytes = 256;                       // NUM_BARS * 8 = 208, tmem pointer behind them
-constexpr int kSmemItems = kSmemBar + kBarBytes;     // 2 x Item
-constexpr int kSmemClc = kSmemItems + 2 * 64;        // 16-byte try_cancel response
-constexpr int kSmemBytes = kSmemClc + 64 + 1024;     // + alignment slack
 constexpr int kConsumerWarps = 11;                   // warps 0..10 read every item
 
 // kEmuNum of every kEmuDen exponential pairs are computed by ex2_poly2, the rest on the MUFU.
@@ -287,23 +291,27 @@ constexpr int kConsumerWarps = 11;                   // warps 0..10 read every i
 //   1  cap * tanh(S * scale / cap)                    (tanh() replaces S, one MUFU op; `cap` rides in the FFMA)
 //   2  either of the above + slope * (key position - context length) for ALiBi (:481-482), formed in place in
 //      log2 units; the max / exp2 code then runs with a scale of 1.
-template <bool kBf16, int kEmuNum, int kEmuDen, int kLogits = 0>
+template <int kD, bool kBf16, int kEmuNum, int kEmuDen, int kLogits = 0>
 __global__ void __launch_bounds__(kThreads, 1)
 attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CUtensorMap k_map,
                        const __grid_constant__ CUtensorMap v_map) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* sQ = smem + kSmemQ;
-  uint8_t* sK = smem + kSmemK;
-  uint8_t* sV = smem + kSmemV;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kSmemBar);
+  using L = Smem<kD>;
+  constexpr int kTileBytes = L::kTileBytes;
+  constexpr int kNDC = kD / 64;  // 128-byte chunks of a row
+  static_assert(kD == 64 || kD == 128, "head size");
+  uint8_t* sQ = smem + L::kQ;
+  uint8_t* sK = smem + L::kK;
+  uint8_t* sV = smem + L::kV;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::kBar);
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + NUM_BARS);
-  Item* items = reinterpret_cast<Item*>(smem + kSmemItems);
-  uint4* clc_resp = reinterpret_cast<uint4*>(smem + kSmemClc);
+  Item* items = reinterpret_cast<Item*>(smem + L::kItems);
+  uint4* clc_resp = reinterpret_cast<uint4*>(smem + L::kClc);
 
   const b200attn_attention_params& a = P.a;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int g = P.group;
+  const int g = P.group, gp = P.group_pad;
   const int BQ = 2 * P.block_q;  // query tokens per CTA tile
   const int window = a.sliding_window;
 #ifdef B200ATTN_TC_TRACE
@@ -386,14 +394,14 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
       // ============================ softmax warpgroups ====================================
       const int w = warp >> 2;                  // Q subtile
       const int row = (warp & 3) * 32 + lane;   // row of the subtile == TMEM lane
-      const int qpos = it.qpos0 + (w * 128 + row) / g;
-      const int head = row % g;                 // 128 % g == 0
-      const bool row_valid = qpos < it.q_len;
+      const int qpos = it.qpos0 + (w * 128 + row) / gp;
+      const int head = row % gp;                // 128 % gp == 0; heads >= g are padding rows
+      const bool row_valid = qpos < it.q_len && head < g;
       const int limit = row_valid ? it.ctx + qpos + 1 : 0;                        // visible keys: [lo, limit)
       const int lo = (window > 0 && row_valid) ? max(0, it.ctx + qpos - window + 1) : 0;
       const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
       const uint32_t s_tmem = tmem_base + lane_base + col_s(w);
-      const uint32_t o_tmem = tmem_base + lane_base + col_o(w);
+      const uint32_t o_tmem = tmem_base + lane_base + col_o<kD>(w);
       float m_used = -INFINITY, l_sum = 0.f;
 
       for (int j = 0; j < n_tiles; ++j) {
@@ -428,7 +436,7 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
               for (int i = 0; i < 32; ++i) s[c][i] = __float_as_uint(__uint_as_float(s[c][i]) * sl2);
           }
           if (a.alibi_slopes) {
-            const float slope = a.alibi_slopes[kvh * g + head] * kLog2e;
+            const float slope = (head < g ? a.alibi_slopes[kvh * g + head] : 0.f) * kLog2e;
             const float b0 = slope * (float)(n0 - it.ctx);
 #pragma unroll
             for (int c = 0; c < 4; ++c)
@@ -465,7 +473,7 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
           tc_fence_after();
           // (8 columns at a time: all 128 S values are live here)
 #pragma unroll 1
-          for (int c = 0; c < 16; ++c) {
+          for (int c = 0; c < kD / 8; ++c) {
             uint32_t t[8];
             tmem_ld8(o_tmem + c * 8, t);
             tmem_ld_wait();
@@ -528,7 +536,7 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
       char* orow = static_cast<char*>(a.out) +
                    ((int64_t)(it.q_start + (row_valid ? qpos : 0)) * a.out_stride0 + (int64_t)(kvh * g + head) * a.out_stride1) * (out_fp8 ? 1 : 2);
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
+      for (int c = 0; c < kD / 32; ++c) {
         uint32_t t[32];
         tmem_ld32(o_tmem + c * 32, t);
         tmem_ld_wait();
@@ -599,11 +607,11 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
         if (zero_rows) {
           // nothing visible (seq_len <= 0): rows get zeros like the reference's reduce (:828)
           for (int r = lane; r < 256; r += 32) {
-            const int qpos = it.qpos0 + r / g;
-            if (qpos < it.q_len) {
+            const int qpos = it.qpos0 + r / gp;
+            if (qpos < it.q_len && r % gp < g) {
               const int osz = a.out_scale ? 1 : 2;
               int2* orow = reinterpret_cast<int2*>(static_cast<char*>(a.out) +
-                                                   ((int64_t)(it.q_start + qpos) * a.out_stride0 + (int64_t)(it.kvh * g + r % g) * a.out_stride1) * osz);
+                                                   ((int64_t)(it.q_start + qpos) * a.out_stride0 + (int64_t)(it.kvh * g + r % gp) * a.out_stride1) * osz);
               for (int i = 0; i < kD * osz / 8; ++i) orow[i] = make_int2(0, 0);
             }
           }
@@ -656,7 +664,7 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
         // compile-time offset in the 14-bit address field.  (A `lane == 0` version cost ~130
         // cycles per MMA in scalar address arithmetic and R2UR loops - twice the MMA itself.)
         constexpr uint32_t idesc_qk = umma_idesc(kBf16, false, 128, 128);
-        constexpr uint32_t idesc_pv = umma_idesc(kBf16, true, 128, 128);
+        constexpr uint32_t idesc_pv = umma_idesc(kBf16, true, 128, kD);
         auto issue_qk = [&](int w, int st) {
           const uint64_t ad = q_desc0 + (uint64_t)((w * kTileBytes) >> 4), bd = k_desc0 + (uint64_t)((st * kTileBytes) >> 4);
           if (leader) {
@@ -678,7 +686,7 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
               TC_TRACE(t, 10 + w * 3 + h);
 #pragma unroll
               for (int kk = 4 * h; kk < 4 * h + 4; ++kk)
-                umma_ts(tm + col_o(w), tm + col_s(w) + kk * 8, bd + (uint64_t)((kk * 2048) >> 4), idesc_pv, (acc || kk > 0) ? 1u : 0u);
+                umma_ts(tm + col_o<kD>(w), tm + col_s(w) + kk * 8, bd + (uint64_t)((kk * 2048) >> 4), idesc_pv, (acc || kk > 0) ? 1u : 0u);
             }
           }
         };
@@ -750,8 +758,8 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
           mbar_wait(&bars[Q_EMPTY], (n_items & 1) ^ 1);
           if (lane == 0) mbar_arrive_expect_tx(&bars[Q_FULL], 2 * kTileBytes);
           __syncwarp();
-          if (lane < 4) {
-            const int w = lane >> 1, dc = lane & 1;
+          if (lane < 2 * kNDC) {
+            const int w = lane / kNDC, dc = lane % kNDC;
             tma_load_4d(sQ + w * kTileBytes + dc * kSubtileBytes, &q_map, &bars[Q_FULL], 0, dc, kvh * g,
                         it.q_start + it.qpos0 + w * P.block_q);
           }
@@ -761,7 +769,7 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
         const uint32_t box_bytes = (uint32_t)P.box_slots * 128;
         const int32_t* bt = a.block_tables + (int64_t)it.b * a.bt_stride0;
         const int staged0 = (P.staged_base && n_tiles > 0) ? P.staged_base[it.b] : -1;
-        const int my_box = lane >> 1, my_dc = lane & 1;
+        const int my_box = lane / kNDC, my_dc = lane % kNDC;
         // page id of this lane's box, fetched one tile ahead of its use
         auto lookup = [&](int j) {
           const int tok = (tile0 + j) * kBN + my_box * P.box_slots;
@@ -787,7 +795,7 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
           const uint32_t dst_off = (uint32_t)(st * kTileBytes + my_dc * kSubtileBytes) + (uint32_t)my_box * box_bytes;
           mbar_wait(&bars[empty0 + st], ph ^ 1);
           if (lane == 0) TC_TRACE(t_run + j, is_k ? 19 : 20);
-          if (lane == 0) mbar_arrive_expect_tx(&bars[full0 + st], (uint32_t)nbox * 2 * box_bytes);
+          if (lane == 0) mbar_arrive_expect_tx(&bars[full0 + st], (uint32_t)(nbox * kNDC) * box_bytes);
           __syncwarp();
           if (active) tma_load_5d_nohint(ring + dst_off, map, &bars[full0 + st], 0, slot0, my_dc, kvh, page);
           last_st = st, last_ph = ph;
@@ -800,9 +808,9 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
         if (!is_k && need_fix) {
           mbar_wait(&bars[V_FULL + last_st], last_ph);
           uint8_t* vt = sV + last_st * kTileBytes;
-          const int n16 = (kBN - last_valid) * 16;  // 16-byte pieces: 2 chunks x 8 per row
+          const int n16 = (kBN - last_valid) * 8 * kNDC;  // 16-byte pieces: kNDC chunks x 8 per row
           for (int idx = lane; idx < n16; idx += 32) {
-            const int r = last_valid + (idx >> 4), dc = (idx >> 3) & 1, c = idx & 7;
+            const int r = last_valid + idx / (8 * kNDC), dc = (idx >> 3) % kNDC, c = idx & 7;
             *reinterpret_cast<int4*>(vt + dc * kSubtileBytes + r * 128 + c * 16) = make_int4(0, 0, 0, 0);
           }
           fence_proxy_async();
@@ -848,12 +856,12 @@ int prefill_tc_min_q_len(const b200attn_attention_params& p) {
 bool prefill_tc_supported(const b200attn_attention_params& p, const char** why) {
   auto no = [&](const char* w) { if (why) *why = w; return false; };
   if (device_info().cc_major < 10) return no("needs sm_100a");
-  if (p.head_size != kD) return no("head_size != 128");
+  if (p.head_size != 64 && p.head_size != 128) return no("head_size not 64 or 128");
   if (p.q_dtype != B200ATTN_BF16 && p.q_dtype != B200ATTN_F16) return no("query dtype must be bf16/f16");
   if (p.kv_dtype != p.q_dtype) return no("kv dtype must equal the query dtype");
   if (p.num_kv_heads <= 0 || p.num_q_heads % p.num_kv_heads) return no("heads");
   const int g = p.num_q_heads / p.num_kv_heads;
-  if (!pow2(g) || g > 128) return no("GQA group not a power of two <= 128");
+  if (g > 128) return no("GQA group > 128");  // (any other group: the Q tile pads it to the next power of two)
   if (!pow2(p.block_size) || p.block_size < 16) return no("block_size not a power of two >= 16");
   if (p.softcap < 0.f) return no("softcap < 0");
   if (!(p.softmax_scale > 0.f)) return no("softmax_scale <= 0");
@@ -877,40 +885,47 @@ int launch_attn_prefill_tc(const b200attn_attention_params& a, cudaStream_t stre
   TcParams P;
   P.a = a;
   P.group = a.num_q_heads / a.num_kv_heads;
-  P.block_q = 128 / P.group;
+  for (P.group_pad = 1; P.group_pad < P.group; P.group_pad *= 2) {}
+  P.block_q = 128 / P.group_pad;
   P.min_q_len = range.min_q_len, P.max_q_len = range.max_q_len;
   P.staged_base = staged_base;
   P.box_slots = a.block_size < kBN ? a.block_size : kBN;
+  const int D = a.head_size;
   CUtensorMap qmap, kmap, vmap;
-  int rc = make_thd_map(&qmap, a.q, kD, a.num_q_heads, a.num_tokens, a.q_stride0, a.q_stride1, P.group, P.block_q);
+  int rc = make_thd_map(&qmap, a.q, D, a.num_q_heads, a.num_tokens, a.q_stride0, a.q_stride1, P.group_pad, P.block_q);
   if (rc) return rc;
-  rc = make_kv_map(&kmap, a.k_cache, 2, kD, a.block_size, a.num_kv_heads, a.num_blocks, a.kc_block_stride, a.kc_slot_stride,
+  rc = make_kv_map(&kmap, a.k_cache, 2, D, a.block_size, a.num_kv_heads, a.num_blocks, a.kc_block_stride, a.kc_slot_stride,
                    a.kc_head_stride, P.box_slots, 1, 1);
   if (rc) return rc;
-  rc = make_kv_map(&vmap, a.v_cache, 2, kD, a.block_size, a.num_kv_heads, a.num_blocks, a.vc_block_stride, a.vc_slot_stride,
+  rc = make_kv_map(&vmap, a.v_cache, 2, D, a.block_size, a.num_kv_heads, a.num_blocks, a.vc_block_stride, a.vc_slot_stride,
                    a.vc_head_stride, P.box_slots, 1, 1);
   if (rc) return rc;
   const bool bf16 = a.q_dtype == B200ATTN_BF16;
   // fraction of the exponentials taken off the MUFU (tuning().reserved bits 4..7; 0 = default)
   using Kern = void (*)(const TcParams, const CUtensorMap, const CUtensorMap, const CUtensorMap);
-#define TCV(B) {attn_prefill_tc_kernel<B, 0, 1>, attn_prefill_tc_kernel<B, 0, 1>, attn_prefill_tc_kernel<B, 1, 4>, \
-                attn_prefill_tc_kernel<B, 1, 3>, attn_prefill_tc_kernel<B, 1, 2>, attn_prefill_tc_kernel<B, 0, 1, 1>, \
-                attn_prefill_tc_kernel<B, 1, 2, 1>, attn_prefill_tc_kernel<B, 0, 1, 2>}
+#define TCV(DD, B) {attn_prefill_tc_kernel<DD, B, 0, 1>, attn_prefill_tc_kernel<DD, B, 0, 1>, attn_prefill_tc_kernel<DD, B, 1, 4>, \
+                    attn_prefill_tc_kernel<DD, B, 1, 3>, attn_prefill_tc_kernel<DD, B, 1, 2>, attn_prefill_tc_kernel<DD, B, 0, 1, 1>, \
+                    attn_prefill_tc_kernel<DD, B, 1, 2, 1>, attn_prefill_tc_kernel<DD, B, 0, 1, 2>}
   // softcap alone (variants 5, 6): the tanh doubles the MUFU work; moving half the exps to the FMA pipe (6) measured
   // slower than leaving them (5): 8k prompt 0.705 ms vs 0.671 ms (profiles/r01_kbench_softcap_tc.jsonl).
   // ALiBi, with or without softcap: variant 7.
   constexpr int kNumVariants = 8, kSoftcapVariant = 5, kGeneralVariant = 7;
-  static const Kern kVariants[2][kNumVariants] = {TCV(false), TCV(true)};
+  static const Kern kVariants[2][2][kNumVariants] = {{TCV(64, false), TCV(64, true)}, {TCV(128, false), TCV(128, true)}};
 #undef TCV
   int variant = (tuning().reserved >> 4) & 15;
   if (variant >= kSoftcapVariant) variant = 0;
+  // D = 64 halves the MMA work per exponential: the MUFU (16 ex2/clk/SM) then needs twice the tensor pipe's time for a
+  // tile, so a third of the exponentials go to the FMA pipe by default (ex2_poly2).  8k prompt, 64 q heads:
+  // none 772, 1/4 825, 1/3 839, 1/2 702 TFLOP/s (profiles/r02_kbench_tc_d64.jsonl)
+  if (variant == 0 && D == 64) variant = 3;
   if (a.alibi_slopes) variant = kGeneralVariant;
-  else if (a.softcap > 0.f) variant = (((tuning().reserved >> 4) & 15) == 6) ? 6 : kSoftcapVariant;
-  Kern kern = kVariants[bf16 ? 1 : 0][variant];
-  if (int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(kern), kSmemBytes, "prefill_tc")) return rc;
+  else if (a.softcap > 0.f) variant = (((tuning().reserved >> 4) & 15) == 6 || D == 64) ? 6 : kSoftcapVariant;
+  Kern kern = kVariants[D == 128 ? 1 : 0][bf16 ? 1 : 0][variant];
+  const int smem_bytes = D == 128 ? Smem<128>::kBytes : Smem<64>::kBytes;
+  if (int rc2 = ensure_dynamic_smem(reinterpret_cast<const void*>(kern), smem_bytes, "prefill_tc")) return rc2;
   const int BQ = 2 * P.block_q;
   const dim3 grid((unsigned)a.num_kv_heads, (unsigned)(a.num_tokens / BQ + a.num_seqs));
-  kern<<<grid, kThreads, kSmemBytes, stream>>>(P, qmap, kmap, vmap);
+  kern<<<grid, kThreads, smem_bytes, stream>>>(P, qmap, kmap, vmap);
   note_launch("attn_prefill_tc");
   return check_launch("attn_prefill_tc");
 }
