@@ -148,6 +148,13 @@ typedef struct b200attn_attention_params {
                                   S[query i of a sequence][key j] += qq_bias[i][j - context_len] for
                                   0 <= j - context_len < qq_bias_stride0.  Served by the SIMT kernel only.   */
   int64_t qq_bias_stride0;
+  float* lse;                  /* NULL, or [T, lse_stride0 >= Hq] fp32: every kernel also writes the natural-log sum of
+                                  exponentials of each (token, head) row's logits (sink included; -inf when no key is
+                                  visible, sink or not) - what a caller needs to combine partial attention over disjoint key sets
+                                  (decode context parallelism: AttentionImpl.can_return_lse_for_decode,
+                                  vllm/vllm/attention/backends/abstract.py:130-153).  The kernels hold (max, exp-sum)
+                                  per row in their epilogues; the reference's own kernels do not export it.        */
+  int64_t lse_stride0;
   const void* decode_plan;     /* NULL, or a plan written by b200attn_decode_plan for THIS step's seq_lens /
                                   cu_seqlens_q (all layers of a step share it; the metadata builder makes it once).
                                   Without one the split-KV launch plans for itself (one more small launch).   */

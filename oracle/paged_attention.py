@@ -66,7 +66,8 @@ def unified_attention_ref(
     output_scale: Optional[float] = None,  # static per-tensor FP8 output quantisation; result is float8_e4m3fn
     local_chunk: int = 0,  # chunked local attention: a query only sees keys of its own chunk of positions
     qq_bias: Optional[torch.Tensor] = None,  # [q, n] fp32: bias between the query tokens of a step
-) -> torch.Tensor:
+    return_lse: bool = False,  # also return fp32 [T, Hq]: ln sum_j exp(s_ij) (+ exp(sink)); -inf where nothing is visible
+):
     """`qq_bias` (upstream, vllm/v1/attention/ops/triton_unified_attention.py:526-528 with
     triton_attention_helpers.py:344-357): after masking and ALiBi, S[query i][key j] += qq_bias[i][j - ctx] for
     0 <= j - ctx < qq_bias.stride(0), the same matrix for every sequence and head.
@@ -87,6 +88,7 @@ def unified_attention_ref(
     cu = [int(x) for x in cu_seqlens_q]
     sl = [int(x) for x in seq_lens]
     out = torch.zeros(T, Hq, D, dtype=torch.float32)
+    lse_out = torch.full((T, Hq), float("-inf"), dtype=torch.float32)
     cdt = q.dtype
     for b in range(len(sl)):
         q0, q1 = cu[b], cu[b + 1]
@@ -129,10 +131,15 @@ def unified_attention_ref(
             p = p.to(round_p_to).to(torch.float32)
         o = torch.einsum("hqk,khd->qhd", p, v) / l.permute(1, 0, 2)  # :508-511
         out[q0:q1] = o
+        # what FlashAttention calls softmax_lse (the quantity decode context parallelism combines partial results
+        # with, vllm/vllm/attention/backends/abstract.py:130-153): ln of the softmax denominator in natural units
+        lse_out[q0:q1] = torch.where(l > 0, m + torch.log(l), torch.full_like(l, float("-inf"))).squeeze(-1).T
     if output_scale is not None:
         inv = 1.0 / torch.tensor(float(output_scale), dtype=torch.float32)  # fp32 reciprocal, as `1 / output_scale`
-        return (out * inv).clamp(-448.0, 448.0).to(torch.float8_e4m3fn)
-    return out.to(out_dtype or q.dtype)
+        res = (out * inv).clamp(-448.0, 448.0).to(torch.float8_e4m3fn)
+    else:
+        res = out.to(out_dtype or q.dtype)
+    return (res, lse_out) if return_lse else res
 
 
 def paged_attn_torch_ref(

@@ -61,6 +61,7 @@ class AttentionParams(Structure):
         ("workspace", c_void_p), ("workspace_bytes", c_uint64),
         ("out_scale", c_void_p),
         ("qq_bias", c_void_p), ("qq_bias_stride0", c_int64),
+        ("lse", c_void_p), ("lse_stride0", c_int64),
         ("decode_plan", c_void_p), ("decode_plan_key", c_uint64),
     ]
 

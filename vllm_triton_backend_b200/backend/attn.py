@@ -253,6 +253,12 @@ def split_kv_cache(kv_cache: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor]:
 
 
 class B200AttentionImpl(AttentionImpl):
+    # Every kernel can write the softmax log-sum-exp of its rows (`softmax_lse=` of ops.unified_attention / of the
+    # per-layer plan; vllm/attention/backends/abstract.py:130-153).  The collective that decode context parallelism
+    # builds on it is outside this path: forward() refuses to run with dcp_world_size > 1 rather than return
+    # un-combined partial attention.
+    can_return_lse_for_decode: bool = True
+
     def __init__(
         self,
         num_heads: int,
@@ -385,6 +391,9 @@ class B200AttentionImpl(AttentionImpl):
         if attn_metadata is None:
             return output.fill_(0)  # profiling run (reference :374-376)
         assert attn_metadata.use_cascade is False
+        if getattr(self, "dcp_world_size", 1) > 1:
+            raise NotImplementedError("B200AttentionImpl: decode context parallelism (the cross-rank LSE combine) is not "
+                                      "implemented; the kernels export the LSE (softmax_lse=) for a caller that combines")
 
         n = attn_metadata.num_actual_tokens
         q = query[:n].view(-1, self.num_heads, self.head_size)

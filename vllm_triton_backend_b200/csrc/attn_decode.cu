@@ -776,6 +776,8 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
       const int ql = P.a.cu_seqlens_q ? (P.a.cu_seqlens_q[b + 1] - P.a.cu_seqlens_q[b]) : 1;
       if (sl <= 0 && ql == 1) {
         const int tq = P.a.cu_seqlens_q ? P.a.cu_seqlens_q[b] : b;
+        if (P.a.lse)
+          for (int h = threadIdx.x; h < P.a.num_q_heads; h += NW * 32) P.a.lse[(int64_t)tq * P.a.lse_stride0 + h] = -INFINITY;
         for (int e = threadIdx.x; e < P.a.num_q_heads * D; e += NW * 32) {
           const int osz = P.a.out_scale ? 1 : 2;  // fp8 output: one byte per element, 0x00 == +0
           char* orow = static_cast<char*>(P.a.out) + ((int64_t)tq * P.a.out_stride0 + (int64_t)(e / D) * P.a.out_stride1) * osz;
@@ -868,8 +870,10 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
       }
       const int hq = f.hg * rec_heads + hq_in;
       float fsink = 1.f;
+      const bool seen = M != -INFINITY;
       if (P.a.sinks) fsink = sink_rescale<true>(P.a.sinks[hq], M, L);  // once per item, here (upstream: segment 0 only)
       const float inv = (L > 0.f) ? fsink * v_scale / L : 0.f;  // 0 when nothing is visible (reference :828)
+      if (P.a.lse && d4 == 0) P.a.lse[(int64_t)f.tq * P.a.lse_stride0 + hq] = seen ? row_lse<true>(M, L) : -INFINITY;
       const int64_t oel = (int64_t)f.tq * P.a.out_stride0 + (int64_t)hq * P.a.out_stride1;
       const float o4[4] = {val.x * inv, val.y * inv, val.z * inv, val.w * inv};
       if (P.a.out_scale) {
@@ -1198,8 +1202,10 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
           const int hq_in_cta = hl * P.group + nt * 8 + col;  // query head within the CTA's head group
           if (direct) {
             const int hq = hg_done * P.hpc * P.group + hq_in_cta;
+            const bool seen = M != -INFINITY;  // some key was visible (a sink alone does not make an LSE)
             if (P.a.sinks) val *= sink_rescale<true>(P.a.sinks[hq], M, L);
             const float o = (L > 0.f) ? val * v_scale / L : 0.f;
+            if (P.a.lse && d == 0) P.a.lse[(int64_t)tq * P.a.lse_stride0 + hq] = seen ? row_lse<true>(M, L) : -INFINITY;
             const int64_t oel = (int64_t)tq * P.a.out_stride0 + (int64_t)hq * P.a.out_stride1;
             if (P.a.out_scale) {  // fused e4m3 output quantisation (b200attn.h: out_scale)
               static_cast<uint8_t*>(P.a.out)[oel + d] = fp8_out(o * out_quant_factor(P.a.out_scale));

@@ -117,8 +117,10 @@ __global__ void __launch_bounds__(128) attn_generic_kernel(b200attn_attention_pa
   const int64_t oel = (int64_t)t * p.out_stride0 + (int64_t)h * p.out_stride1;
   // L == 0 happens only when no key is visible; the reference's reduce returns 0 there (:828)
   float f = 1.f;
+  const bool seen = m != -INFINITY;  // some key was visible (a sink alone does not make an LSE)
   if (p.sinks) f = sink_rescale<false>(p.sinks[h], m, l);
   const float inv_l = l > 0.f ? f / l : 0.f;
+  if (p.lse && lane == 0) p.lse[(int64_t)t * p.lse_stride0 + h] = seen ? row_lse<false>(m, l) : -INFINITY;
   if (p.out_scale) {  // fused e4m3 output quantisation (b200attn.h: out_scale)
     const float oq = out_quant_factor(p.out_scale);
     uint8_t* orow = static_cast<uint8_t*>(p.out) + oel;

@@ -372,8 +372,10 @@ attn_prefill_kernel(const b200attn_attention_params p, const int block_q, const 
     const int r = warp * 16 + gid + 8 * ri;
     const int hq = kvh * group + r % group;
     float f = 1.f;
+    const bool seen = m_run[ri] != -INFINITY;  // some key was visible (a sink alone does not make an LSE)
     if (p.sinks) f = sink_rescale<true>(p.sinks[hq], m_run[ri], l);
     const float inv = (l > 0.f) ? f * v_scale / l : 0.f;
+    if (p.lse && t4 == 0) p.lse[(int64_t)(q_start + row_qpos[ri]) * p.lse_stride0 + hq] = seen ? row_lse<true>(m_run[ri], l) : -INFINITY;
     const int64_t oel = (int64_t)(q_start + row_qpos[ri]) * p.out_stride0 + (int64_t)hq * p.out_stride1;
     if (p.out_scale) {  // fused e4m3 output quantisation (b200attn.h: out_scale)
       const float oq = inv * out_quant_factor(p.out_scale);

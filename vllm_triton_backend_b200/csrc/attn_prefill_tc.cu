@@ -529,8 +529,10 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
       mbar_wait(&bars[O_DONE + w], (t_run + (uint32_t)last_tile) & 1);
       tc_fence_after();
       float fs = 1.f;
+      const bool seen = m_used != -INFINITY;  // some key was visible (a sink alone does not make an LSE)
       if (a.sinks && row_valid) fs = sink_rescale<true>(a.sinks[kvh * g + head], m_used, l_sum);  // once per row, after the last tile
       const float inv = (l_sum > 0.f) ? fs / l_sum : 0.f;
+      if (a.lse && row_valid) a.lse[(int64_t)(it.q_start + qpos) * a.lse_stride0 + kvh * g + head] = seen ? row_lse<true>(m_used, l_sum) : -INFINITY;
       const bool out_fp8 = a.out_scale != nullptr;  // fused e4m3 output quantisation (b200attn.h: out_scale)
       const float oq = inv * out_quant_factor(a.out_scale);
       char* orow = static_cast<char*>(a.out) +
@@ -609,6 +611,7 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
           for (int r = lane; r < 256; r += 32) {
             const int qpos = it.qpos0 + r / gp;
             if (qpos < it.q_len && r % gp < g) {
+              if (a.lse) a.lse[(int64_t)(it.q_start + qpos) * a.lse_stride0 + it.kvh * g + r % gp] = -INFINITY;
               const int osz = a.out_scale ? 1 : 2;
               int2* orow = reinterpret_cast<int2*>(static_cast<char*>(a.out) +
                                                    ((int64_t)(it.q_start + qpos) * a.out_stride0 + (int64_t)(it.kvh * g + r % gp) * a.out_stride1) * osz);

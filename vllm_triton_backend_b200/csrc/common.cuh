@@ -184,7 +184,7 @@ __device__ __forceinline__ float tanh_approx(float x) {
 // one extra key per head with logit `sink` (natural units, not scaled) and a zero value row.
 // Applied once, after the last KV tile: `m` is the final running max (`m_is_log2`: in log2
 // units) and `l` the running sum; returns the factor for the un-normalised accumulator.
-template <bool m_is_log2> __device__ __forceinline__ float sink_rescale(float sink, float m, float& l) {
+template <bool m_is_log2> __device__ __forceinline__ float sink_rescale(float sink, float& m, float& l) {
   const float s = m_is_log2 ? sink * kLog2e : sink;
   const float mx = fmaxf(m, s);
   if (mx == -INFINITY) {
@@ -193,7 +193,16 @@ template <bool m_is_log2> __device__ __forceinline__ float sink_rescale(float si
   }
   const float f = (m == -INFINITY) ? 0.f : (m_is_log2 ? exp2f(m - mx) : __expf(m - mx));
   l = l * f + (m_is_log2 ? exp2f(s - mx) : __expf(s - mx));
+  m = mx;  // (m, l) describe the row with the sink in it from here on
   return f;
+}
+
+// Natural-log sum of exponentials of a row's logits (b200attn_attention_params::lse) from the running maximum
+// (log2 units when m_is_log2) and the exp-sum relative to it, as they stand after the last KV tile (and the sink).
+// Nothing visible: -inf.
+template <bool m_is_log2> __device__ __forceinline__ float row_lse(float m, float l) {
+  if (!(l > 0.f)) return -INFINITY;
+  return (m_is_log2 ? m * 0.6931471805599453f : m) + __logf(l);
 }
 
 // ---- fused FP8 output quantisation (b200attn_attention_params::out_scale) -----

@@ -230,6 +230,7 @@ def _check_out(out, q_dtype, output_scale) -> None:
 def build_attention_params(
     q, k, v, out, cu_seqlens_q, max_seqlen_q, seqused_k, max_seqlen_k, softmax_scale, window_size, block_table,
     softcap, k_descale, v_descale, alibi_slopes, path, workspace, sinks=None, output_scale=None, qq_bias=None,
+    softmax_lse=None,
 ) -> AttentionParams:
     if q.dim() != 3 or k.dim() != 4 or v.dim() != 4:
         raise ValueError("q must be [T, Hq, D]; k, v must be [NB, bs, Hkv, D]")
@@ -263,6 +264,11 @@ def build_attention_params(
         if qq_bias.shape[0] < int(max_seqlen_q):
             raise ValueError("qq_bias needs one row per query position of the longest sequence")
         p.qq_bias, p.qq_bias_stride0 = qq_bias.data_ptr(), qq_bias.stride(0)
+    if softmax_lse is not None:
+        if (softmax_lse.dtype != torch.float32 or softmax_lse.dim() != 2 or softmax_lse.stride(1) != 1 or not softmax_lse.is_cuda
+                or softmax_lse.shape[0] < q.shape[0] or softmax_lse.shape[1] < q.shape[1]):
+            raise ValueError("softmax_lse must be a float32 CUDA tensor [num_tokens, num_q_heads] with a contiguous last dimension")
+        p.lse, p.lse_stride0 = softmax_lse.data_ptr(), softmax_lse.stride(0)
     p.softmax_scale = float(softmax_scale)
     p.softcap = float(softcap or 0.0)
     p.sliding_window = int(1 + window_size[0]) if window_size is not None else 0  # reference :915
@@ -310,6 +316,7 @@ def unified_attention(
     output_scale: Optional[torch.Tensor] = None,  # upstream keyword: `out` is e4m3, out = quant(o / output_scale)
     qq_bias: Optional[torch.Tensor] = None,  # upstream keyword: [q, q] fp32 bias between a step's query tokens (SIMT kernel)
     decode_plan: Optional["DecodePlan"] = None,  # this step's split-KV plan (DecodePlan.build), shared by all layers
+    softmax_lse: Optional[torch.Tensor] = None,  # out: fp32 [T, Hq], natural-log sum of exponentials of every row's logits
     # Pure tuning inputs of upstream's launcher (vLLM 0.22 vllm/v1/attention/ops/triton_unified_attention.py):
     # where its split-KV partials live and when it splits.  They do not change the result; this library sizes
     # and owns its workspace itself, so they are accepted and unused.
@@ -372,7 +379,7 @@ def unified_attention(
         workspace = get_workspace(q.device, need)
     p = build_attention_params(
         q, k, v, out, cu_seqlens_q, max_seqlen_q, seqused_k, max_seqlen_k, softmax_scale, window_size, block_table,
-        softcap, k_descale, v_descale, alibi_slopes, path, workspace, sinks, output_scale, qq_bias,
+        softcap, k_descale, v_descale, alibi_slopes, path, workspace, sinks, output_scale, qq_bias, softmax_lse,
     )
     if decode_plan is not None and decode_plan.key:
         p.decode_plan, p.decode_plan_key = decode_plan.buf.data_ptr(), decode_plan.key
@@ -427,7 +434,7 @@ class AttentionPlan:
         self.num_q_heads, self.head_size, self.q_dtype = num_q_heads, head_size, q_dtype
 
     def __call__(self, q, out, cu_seqlens_q, max_seqlen_q, seqused_k, max_seqlen_k, block_table, workspace,
-                 output_scale=None, decode_plan=None) -> None:
+                 output_scale=None, decode_plan=None, softmax_lse=None) -> None:
         """q/out: [T, Hq, D] views (innermost contiguous); metadata tensors int32 on the device.
         `output_scale`: one-element fp32 device tensor => `out` is float8_e4m3fn (fused output quant)."""
         if q.dtype != self.q_dtype or not q.is_cuda:
@@ -448,6 +455,13 @@ class AttentionPlan:
             p.decode_plan, p.decode_plan_key = decode_plan.buf.data_ptr(), decode_plan.key
         else:
             p.decode_plan, p.decode_plan_key = None, 0
+        if softmax_lse is not None:
+            if softmax_lse.dtype != torch.float32 or softmax_lse.dim() != 2 or softmax_lse.stride(1) != 1 or \
+                    softmax_lse.shape[0] < q.shape[0] or softmax_lse.shape[1] < self.num_q_heads:
+                raise ValueError("softmax_lse must be float32 [num_tokens, num_q_heads]")
+            p.lse, p.lse_stride0 = softmax_lse.data_ptr(), softmax_lse.stride(0)
+        else:
+            p.lse, p.lse_stride0 = None, 0
         wp = workspace.data_ptr()
         if wp != self._ws_ptr:
             p.workspace, p.workspace_bytes, self._ws_ptr = wp, workspace.numel() * workspace.element_size(), wp
