@@ -146,7 +146,7 @@ typedef struct b200attn_attention_params {
                                   speculative-decoding masks; vllm/v1/attention/ops/triton_unified_attention.py:376,
                                   526-528, triton_attention_helpers.py:344-357): after masking and ALiBi,
                                   S[query i of a sequence][key j] += qq_bias[i][j - context_len] for
-                                  0 <= j - context_len < qq_bias_stride0.  Served by the SIMT kernel only.   */
+                                  0 <= j - context_len < qq_bias_stride0.  Every kernel applies it.               */
   int64_t qq_bias_stride0;
   float* lse;                  /* NULL, or [T, lse_stride0 >= Hq] fp32: every kernel also writes the natural-log sum of
                                   exponentials of each (token, head) row's logits (sink included; -inf when no key is

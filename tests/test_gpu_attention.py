@@ -608,9 +608,13 @@ def test_fp8_prefill_staging_in_a_cuda_graph():
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
 @pytest.mark.parametrize("D", [64, 128])
-def test_qq_bias_between_the_query_tokens_of_a_step(dtype, D):
+@pytest.mark.parametrize("force,kernel", [(None, "attn_decode_split_kv"), (22, "attn_prefill_mma"), (4, "attn_prefill_tc"), (1, "attn_generic")])
+def test_qq_bias_between_the_query_tokens_of_a_step(dtype, D, force, kernel):
     """Upstream `qq_bias` (tree / speculative-decoding masks): a [q, q] bias on the logits between a step's own
-    query tokens, the same for every sequence and head; -inf entries cut a query off from a sibling branch."""
+    query tokens, the same for every sequence and head; -inf entries cut a query off from a sibling branch.
+    Applied inside every kernel (the reference applies it inside its one kernel,
+    vllm/attention/ops/triton_unified_attention.py:66-79, 176-177, 301-307): AUTO sends the 8-token rows to the
+    mma.sync kernel and the single-token row to the split-KV kernel."""
     from vllm_triton_backend_b200 import _cabi, ops
 
     lens = [(8, 700), (8, 8), (8, 33), (5, 1200), (1, 90)]
@@ -620,6 +624,7 @@ def test_qq_bias_between_the_query_tokens_of_a_step(dtype, D):
     bias = torch.randn(8, 8, generator=g)
     bias[torch.rand(8, 8, generator=g) < 0.3] = float("-inf")
     bias.fill_diagonal_(0.0)  # a token always sees itself
+    bias[0, 0] = 0.75         # (and the single-token row must pick up [0][0])
     scale = D ** -0.5
     dev = "cuda"
     out = torch.full_like(inp["q"], float("nan")).to(dev)
@@ -627,15 +632,37 @@ def test_qq_bias_between_the_query_tokens_of_a_step(dtype, D):
         q=inp["q"].to(dev), k=inp["k_cache"].to(dev), v=inp["v_cache"].to(dev), out=out, cu_seqlens_q=inp["cu_seqlens_q"].to(dev),
         max_seqlen_q=8, seqused_k=inp["seq_lens"].to(dev), max_seqlen_k=1200, softmax_scale=scale, causal=True,
         window_size=(-1, -1), block_table=inp["block_table"].to(dev), softcap=0, q_descale=None, k_descale=None,
-        v_descale=None, qq_bias=bias.to(dev))
+        v_descale=None, qq_bias=bias.to(dev), force_selection=force)
     torch.cuda.synchronize()
-    assert _cabi.last_kernel() == "attn_generic"
+    assert _cabi.last_kernel() == kernel
     ref = unified_attention_ref(inp["q"], inp["k_cache"], inp["v_cache"], inp["cu_seqlens_q"], inp["seq_lens"],
                                 inp["block_table"], scale, out_dtype=torch.float32, qq_bias=bias)
-    assert_close(out.cpu(), ref, atol=BF16_ATOL, rtol=BF16_RTOL, what="qq_bias")
-    with pytest.raises(_cabi.B200AttnError, match="generic kernel only"):
+    assert_close(out.cpu(), ref, atol=BF16_ATOL, rtol=BF16_RTOL, what=f"qq_bias via {kernel}")
+
+
+def test_qq_bias_with_long_trees_and_other_features():
+    """qq_bias together with a sliding window, softcap and FP8 KV, on queries long enough for the tcgen05 kernel."""
+    from vllm_triton_backend_b200 import _cabi, ops
+
+    lens = [(40, 700), (33, 33), (1, 90), (64, 2000), (7, 300)]
+    Hq, Hkv, D, bs = 16, 4, 128, 16
+    dev = "cuda"
+    for fp8 in (False, True):
+        inp = make_paged_inputs(lens, Hq, Hkv, D, bs, dtype=torch.bfloat16, seed=62, kv_dtype=torch.float8_e4m3fn if fp8 else None,
+                                k_scale=0.5, v_scale=0.5)
+        g = torch.Generator().manual_seed(8)
+        bias = torch.randn(64, 64, generator=g)
+        bias[torch.rand(64, 64, generator=g) < 0.3] = float("-inf")
+        bias.fill_diagonal_(0.0)
+        sc = torch.tensor([0.5], dtype=torch.float32, device=dev) if fp8 else None
+        out = torch.full_like(inp["q"], float("nan")).to(dev)
         ops.unified_attention(
-            q=inp["q"].to(dev), k=inp["k_cache"].to(dev), v=inp["v_cache"].to(dev), out=out,
-            cu_seqlens_q=inp["cu_seqlens_q"].to(dev), max_seqlen_q=8, seqused_k=inp["seq_lens"].to(dev), max_seqlen_k=1200,
-            softmax_scale=scale, causal=True, window_size=(-1, -1), block_table=inp["block_table"].to(dev), softcap=0,
-            q_descale=None, k_descale=None, v_descale=None, qq_bias=bias.to(dev), force_selection=22)
+            q=inp["q"].to(dev), k=inp["k_cache"].to(dev), v=inp["v_cache"].to(dev), out=out, cu_seqlens_q=inp["cu_seqlens_q"].to(dev),
+            max_seqlen_q=64, seqused_k=inp["seq_lens"].to(dev), max_seqlen_k=2000, softmax_scale=0.2, causal=True,
+            window_size=(511, 0), block_table=inp["block_table"].to(dev), softcap=30.0, q_descale=None, k_descale=sc,
+            v_descale=sc, qq_bias=bias.to(dev))
+        torch.cuda.synchronize()
+        ref = unified_attention_ref(inp["q"], inp["k_cache"], inp["v_cache"], inp["cu_seqlens_q"], inp["seq_lens"],
+                                    inp["block_table"], 0.2, sliding_window=512, softcap=30.0, k_scale=0.5 if fp8 else 1.0,
+                                    v_scale=0.5 if fp8 else 1.0, out_dtype=torch.float32, qq_bias=bias)
+        assert_close(out.cpu(), ref, atol=FP8_ATOL if fp8 else BF16_ATOL, rtol=BF16_RTOL, what=f"qq_bias + features fp8={fp8}")

@@ -1036,6 +1036,12 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
             sv[sb][0] += slope[nt][0] * p0 * kLog2e, sv[sb][1] += slope[nt][1] * p0 * kLog2e;
             sv[sb][2] += slope[nt][0] * p1 * kLog2e, sv[sb][3] += slope[nt][1] * p1 * kLog2e;
           }
+          if (P.a.qq_bias) {
+            // a single-token row is query 0 of its step and its own key is the sequence's last: qq_bias[0][0]
+            const float b00 = P.a.qq_bias[0] * kLog2e;
+            if (tok0 + tr == cur.seq_len - 1) sv[sb][0] += b00, sv[sb][1] += b00;
+            if (tok0 + tr + 8 == cur.seq_len - 1) sv[sb][2] += b00, sv[sb][3] += b00;
+          }
           if (partial) {
             const bool ok0 = tr < valid && tr >= win_lo, ok1 = tr + 8 < valid && tr + 8 >= win_lo;
             if (!ok0) sv[sb][0] = sv[sb][1] = -INFINITY;

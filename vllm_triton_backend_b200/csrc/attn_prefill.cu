@@ -281,6 +281,13 @@ attn_prefill_kernel(const b200attn_attention_params p, const int block_q, const 
           for (int i = 0; i < 4; ++i) {
             float x = has_cap ? cap_log2 * tanh_approx(sacc[nt][i] * pre) : sacc[nt][i] * scale_log2;
             if (p.alibi_slopes) x = fmaf(row_slope[i >> 1] * kLog2e, (float)(n0 + nt * 8 + 2 * t4 + (i & 1) - ctx), x);
+            if (p.qq_bias) {
+              // bias between this step's own query tokens (upstream qq_bias, triton_unified_attention.py:301-307 of
+              // the vLLM copy): the keys at positions ctx .. ctx + stride - 1 are the step's tokens 0 .. stride - 1
+              const int rel = n0 + nt * 8 + 2 * t4 + (i & 1) - ctx;
+              if (rel >= 0 && rel < (int)p.qq_bias_stride0 && row_ok[i >> 1])
+                x += p.qq_bias[(int64_t)row_qpos[i >> 1] * p.qq_bias_stride0 + rel] * kLog2e;
+            }
             sacc[nt][i] = x;
           }
         }
@@ -460,7 +467,7 @@ int launch_attn_prefill(const b200attn_attention_params& a, cudaStream_t stream,
     return B200ATTN_E_UNSUPPORTED;
   }
   // the scale of an FP8 cache is a device scalar: it is taken as positive (a quantisation scale always is)
-  const bool plain = a.softcap == 0.f && !a.alibi_slopes && a.softmax_scale > 0.f;
+  const bool plain = a.softcap == 0.f && !a.alibi_slopes && !a.qq_bias && a.softmax_scale > 0.f;
   switch (a.head_size) {
     case 64: return plain ? dispatch_types<64, true>(a, stream, range, skip_staged) : dispatch_types<64, false>(a, stream, range, skip_staged);
     case 128: return plain ? dispatch_types<128, true>(a, stream, range, skip_staged) : dispatch_types<128, false>(a, stream, range, skip_staged);

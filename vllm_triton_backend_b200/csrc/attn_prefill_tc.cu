@@ -443,6 +443,18 @@ attn_prefill_tc_kernel(const TcParams P, const __grid_constant__ CUtensorMap q_m
 #pragma unroll
               for (int i = 0; i < 32; ++i) s[c][i] = __float_as_uint(fmaf(slope, (float)(c * 32 + i), __uint_as_float(s[c][i]) + b0));
           }
+          if (a.qq_bias && row_valid && n0 + kBN > it.ctx) {
+            // bias between the step's own query tokens: keys ctx .. ctx + stride - 1 are its tokens 0 .. stride - 1
+            const float* brow = a.qq_bias + (int64_t)qpos * a.qq_bias_stride0;
+            const int nrel = (int)a.qq_bias_stride0;
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+#pragma unroll
+              for (int i = 0; i < 32; ++i) {
+                const int rel = n0 + c * 32 + i - it.ctx;
+                if (rel >= 0 && rel < nrel) s[c][i] = __float_as_uint(fmaf(brow[rel], kLog2e, __uint_as_float(s[c][i])));
+              }
+          }
         }
         if (n0 + kBN > limit || n0 < lo) {
 #pragma unroll
@@ -921,7 +933,7 @@ int launch_attn_prefill_tc(const b200attn_attention_params& a, cudaStream_t stre
   // tile, so a third of the exponentials go to the FMA pipe by default (ex2_poly2).  8k prompt, 64 q heads:
   // none 772, 1/4 825, 1/3 839, 1/2 702 TFLOP/s (profiles/r02_kbench_tc_d64.jsonl)
   if (variant == 0 && D == 64) variant = 3;
-  if (a.alibi_slopes) variant = kGeneralVariant;
+  if (a.alibi_slopes || a.qq_bias) variant = kGeneralVariant;
   else if (a.softcap > 0.f) variant = (((tuning().reserved >> 4) & 15) == 6 || D == 64) ? 6 : kSoftcapVariant;
   Kern kern = kVariants[D == 128 ? 1 : 0][bf16 ? 1 : 0][variant];
   const int smem_bytes = D == 128 ? Smem<128>::kBytes : Smem<64>::kBytes;

@@ -242,13 +242,6 @@ int b200attn_unified_attention(const b200attn_attention_params* pp, b200attn_str
   int rc = validate_attention(p);
   if (rc) return rc;
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(s);
-  if (p.qq_bias) {  // query-query bias: the SIMT kernel is the only one that carries it
-    if (p.path != B200ATTN_PATH_AUTO && p.path != B200ATTN_PATH_GENERIC) {
-      set_error("unified_attention: qq_bias is served by the generic kernel only (path %d requested)", p.path);
-      return B200ATTN_E_UNSUPPORTED;
-    }
-    return launch_attn_generic(p, stream);
-  }
   switch (p.path) {
     case B200ATTN_PATH_GENERIC: return launch_attn_generic(p, stream);
     case B200ATTN_PATH_PREFILL: return launch_attn_prefill(p, stream);

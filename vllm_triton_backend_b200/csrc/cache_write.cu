@@ -63,56 +63,110 @@ struct CacheWriteArgs {
   int num_kv_heads, head_size, block_size;
 };
 
-// Copy path: 16-byte vectors of kElemBytes-sized elements.
+// A CTA takes kTokPerCta consecutive tokens (K and V rows of each) when there are enough tokens to fill the GPU that
+// way: with one (token, K|V) row per CTA - 128 threads moving 16 bytes each - a prompt-sized write was 16 384 tiny CTAs
+// and ran at half the HBM rate (8192 tokens: 20.5 us, profiles/r02_kbench_baseline.jsonl).  Decode-sized writes keep
+// one token per CTA (they are launch latency either way).
+constexpr int kMaxTokPerCta = 8;
+
+struct RowRef {
+  const char* src;
+  char* dst;
+};
+
+// Copy path: 16-byte vectors of kElemBytes-sized elements, 4 vectors in flight per thread.
 template <int kElemBytes>
-__global__ void __launch_bounds__(256) cache_copy_vec_kernel(CacheWriteArgs a) {
+__global__ void __launch_bounds__(256) cache_copy_vec_kernel(CacheWriteArgs a, int tok_per_cta, int64_t num_tokens) {
   pdl_launch_dependents();  // the attention launch behind us may start its prologue now (common.cuh)
   pdl_wait();               // ... and this grid may itself have been scheduled early: wait for the kernel in front
   constexpr int kVec = 16 / kElemBytes;
-  const int64_t token = blockIdx.x;
-  const int which = blockIdx.y;
-  const int64_t slot = a.slot_mapping[token];
-  if (slot < 0) return;  // padded token
-  const int64_t blk = slot / a.block_size, off = slot % a.block_size;
-  const char* src = static_cast<const char*>(a.src[which]) + token * a.src_stride0[which] * kElemBytes;
-  char* dst = static_cast<char*>(a.dst[which]) + (blk * a.block_stride[which] + off * a.slot_stride[which]) * kElemBytes;
+  __shared__ int64_t s_slot[kMaxTokPerCta];
+  const int64_t t0 = (int64_t)blockIdx.x * tok_per_cta;
+  const int ntok = (int)min((int64_t)tok_per_cta, num_tokens - t0);
+  if (threadIdx.x < ntok) s_slot[threadIdx.x] = a.slot_mapping[t0 + threadIdx.x];
+  __syncthreads();
   const int vec_per_head = a.head_size / kVec;
-  const int n_vec = a.num_kv_heads * vec_per_head;
-  for (int v = threadIdx.x; v < n_vec; v += blockDim.x) {
+  const int n_vec = a.num_kv_heads * vec_per_head;  // vectors of one row
+  const int total = ntok * 2 * n_vec;
+  auto locate = [&](int u, const char*& src, char*& dst) {  // false: padded token
+    const int tok = u / (2 * n_vec), r = u - tok * 2 * n_vec, which = r / n_vec, v = r - which * n_vec;
+    const int64_t slot = s_slot[tok];
+    if (slot < 0) return false;
+    const int64_t blk = slot / a.block_size, off = slot % a.block_size;
     const int h = v / vec_per_head, dv = v - h * vec_per_head;
-    int4 x = ld_nc_v4(src + (int64_t)v * 16);
-    st_v4(dst + ((int64_t)h * a.head_stride[which]) * kElemBytes + (int64_t)dv * 16, x);
+    src = static_cast<const char*>(a.src[which]) + (t0 + tok) * a.src_stride0[which] * kElemBytes + (int64_t)v * 16;
+    dst = static_cast<char*>(a.dst[which]) +
+          (blk * a.block_stride[which] + off * a.slot_stride[which] + (int64_t)h * a.head_stride[which]) * kElemBytes + (int64_t)dv * 16;
+    return true;
+  };
+  for (int u0 = threadIdx.x; u0 < total; u0 += 4 * blockDim.x) {
+    int4 x[4];
+    char* dst[4];
+    bool ok[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int u = u0 + i * blockDim.x;
+      const char* src = nullptr;
+      dst[i] = nullptr;
+      ok[i] = u < total && locate(u, src, dst[i]);
+      if (ok[i]) x[i] = ld_nc_v4(src);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      if (ok[i]) st_v4(dst[i], x[i]);
   }
 }
 
-// FP8 path, 16 elements per thread: two 16-byte loads, one 16-byte store.
+// FP8 path, 16 elements per thread and unit: two 16-byte loads, one 16-byte store; 2 units in flight per thread.
 template <typename SrcT>
-__global__ void __launch_bounds__(256) cache_quant_vec16_kernel(CacheWriteArgs a) {
+__global__ void __launch_bounds__(256) cache_quant_vec16_kernel(CacheWriteArgs a, int tok_per_cta, int64_t num_tokens) {
   pdl_launch_dependents();  // the attention launch behind us may start its prologue now (common.cuh)
   pdl_wait();               // ... and this grid may itself have been scheduled early: wait for the kernel in front
-  const int64_t token = blockIdx.x;
-  const int which = blockIdx.y;
-  const int64_t slot = a.slot_mapping[token];
-  if (slot < 0) return;
-  const float scale = *a.scale[which];
-  const int64_t blk = slot / a.block_size, off = slot % a.block_size;
-  const SrcT* src = static_cast<const SrcT*>(a.src[which]) + token * a.src_stride0[which];
-  uint8_t* dst = static_cast<uint8_t*>(a.dst[which]) + blk * a.block_stride[which] + off * a.slot_stride[which];
+  __shared__ int64_t s_slot[kMaxTokPerCta];
+  const int64_t t0 = (int64_t)blockIdx.x * tok_per_cta;
+  const int ntok = (int)min((int64_t)tok_per_cta, num_tokens - t0);
+  if (threadIdx.x < ntok) s_slot[threadIdx.x] = a.slot_mapping[t0 + threadIdx.x];
+  __syncthreads();
+  const float scale[2] = {*a.scale[0], *a.scale[1]};
   const int vec_per_head = a.head_size / 16;
   const int n_vec = a.num_kv_heads * vec_per_head;
-  for (int v = threadIdx.x; v < n_vec; v += blockDim.x) {
-    const int h = v / vec_per_head, dv = v - h * vec_per_head;
-    int4 lo = ld_nc_v4(src + (int64_t)v * 16);
-    int4 hi = ld_nc_v4(src + (int64_t)v * 16 + 8);
-    float f[16];
-    unpack8<SrcT>(lo, *reinterpret_cast<float(*)[8]>(&f[0]));
-    unpack8<SrcT>(hi, *reinterpret_cast<float(*)[8]>(&f[8]));
-    uint32_t w[4];
+  const int total = ntok * 2 * n_vec;
+  for (int u0 = threadIdx.x; u0 < total; u0 += 2 * blockDim.x) {
+    int4 lo[2], hi[2];
+    uint8_t* dst[2];
+    float sc[2];
+    bool ok[2];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      w[i] = (uint32_t)quant2(f[4 * i], f[4 * i + 1], scale) | ((uint32_t)quant2(f[4 * i + 2], f[4 * i + 3], scale) << 16);
+    for (int i = 0; i < 2; ++i) {
+      const int u = u0 + i * blockDim.x;
+      ok[i] = false;
+      if (u < total) {
+        const int tok = u / (2 * n_vec), r = u - tok * 2 * n_vec, which = r / n_vec, v = r - which * n_vec;
+        const int64_t slot = s_slot[tok];
+        if (slot >= 0) {
+          const int64_t blk = slot / a.block_size, off = slot % a.block_size;
+          const int h = v / vec_per_head, dv = v - h * vec_per_head;
+          const SrcT* src = static_cast<const SrcT*>(a.src[which]) + (t0 + tok) * a.src_stride0[which] + (int64_t)v * 16;
+          dst[i] = static_cast<uint8_t*>(a.dst[which]) + blk * a.block_stride[which] + off * a.slot_stride[which] +
+                   (int64_t)h * a.head_stride[which] + dv * 16;
+          lo[i] = ld_nc_v4(src), hi[i] = ld_nc_v4(src + 8);
+          sc[i] = scale[which];
+          ok[i] = true;
+        }
+      }
     }
-    st_v4(dst + (int64_t)h * a.head_stride[which] + dv * 16, make_int4(w[0], w[1], w[2], w[3]));
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      if (!ok[i]) continue;
+      float f[16];
+      unpack8<SrcT>(lo[i], *reinterpret_cast<float(*)[8]>(&f[0]));
+      unpack8<SrcT>(hi[i], *reinterpret_cast<float(*)[8]>(&f[8]));
+      uint32_t w[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        w[j] = (uint32_t)quant2(f[4 * j], f[4 * j + 1], sc[i]) | ((uint32_t)quant2(f[4 * j + 2], f[4 * j + 3], sc[i]) << 16);
+      st_v4(dst[i], make_int4(w[0], w[1], w[2], w[3]));
+    }
   }
 }
 
@@ -163,6 +217,12 @@ __global__ void __launch_bounds__(256) scaled_fp8_quant_kernel(uint8_t* out, con
 }
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+// tokens per CTA of the vector kernels: one while that still gives every SM a few CTAs, up to kMaxTokPerCta
+inline int tok_per_cta(int64_t num_tokens) {
+  const int64_t want = num_tokens / (4 * (device_info().num_sms > 0 ? device_info().num_sms : 148));
+  return want < 1 ? 1 : (want > kMaxTokPerCta ? kMaxTokPerCta : (int)want);
+}
 
 }  // namespace
 
@@ -222,11 +282,14 @@ int launch_cache_write(const void* key, const void* value, void* k_cache, void* 
                         mult(kc_block_stride, vec) && mult(kc_slot_stride, vec) && mult(kc_head_stride, vec) &&
                         mult(vc_block_stride, vec) && mult(vc_slot_stride, vec) && mult(vc_head_stride, vec);
     if (vec_ok) {
-      int threads = n_elems / vec;
+      const int units = 2 * n_elems / vec;  // 16-byte vectors of one token (K and V)
+      const int tpc = tok_per_cta(num_tokens);
+      int threads = (tpc * units + 3) / 4;
       threads = threads < 32 ? 32 : (threads > 256 ? 256 : ((threads + 31) / 32) * 32);
-      if (sb == 2) launch_pdl(cache_copy_vec_kernel<2>, grid, threads, 0, stream, pdl, a);
-      else if (sb == 4) launch_pdl(cache_copy_vec_kernel<4>, grid, threads, 0, stream, pdl, a);
-      else launch_pdl(cache_copy_vec_kernel<1>, grid, threads, 0, stream, pdl, a);
+      const dim3 vgrid((unsigned)((num_tokens + tpc - 1) / tpc));
+      if (sb == 2) launch_pdl(cache_copy_vec_kernel<2>, vgrid, threads, 0, stream, pdl, a, tpc, num_tokens);
+      else if (sb == 4) launch_pdl(cache_copy_vec_kernel<4>, vgrid, threads, 0, stream, pdl, a, tpc, num_tokens);
+      else launch_pdl(cache_copy_vec_kernel<1>, vgrid, threads, 0, stream, pdl, a, tpc, num_tokens);
       note_launch("cache_copy_vec");
     } else {
       int threads = n_elems > 256 ? 256 : ((n_elems + 31) / 32) * 32;
@@ -242,10 +305,13 @@ int launch_cache_write(const void* key, const void* value, void* k_cache, void* 
                         mult(kc_block_stride, 16) && mult(kc_slot_stride, 16) && mult(kc_head_stride, 16) &&
                         mult(vc_block_stride, 16) && mult(vc_slot_stride, 16) && mult(vc_head_stride, 16);
     if (vec_ok) {
-      int threads = n_elems / 16;
+      const int units = 2 * n_elems / 16;  // 16-element groups of one token (K and V)
+      const int tpc = tok_per_cta(num_tokens);
+      int threads = (tpc * units + 1) / 2;
       threads = threads < 32 ? 32 : (threads > 256 ? 256 : ((threads + 31) / 32) * 32);
-      if (src_dtype == B200ATTN_BF16) launch_pdl(cache_quant_vec16_kernel<__nv_bfloat16>, grid, threads, 0, stream, pdl, a);
-      else launch_pdl(cache_quant_vec16_kernel<__half>, grid, threads, 0, stream, pdl, a);
+      const dim3 vgrid((unsigned)((num_tokens + tpc - 1) / tpc));
+      if (src_dtype == B200ATTN_BF16) launch_pdl(cache_quant_vec16_kernel<__nv_bfloat16>, vgrid, threads, 0, stream, pdl, a, tpc, num_tokens);
+      else launch_pdl(cache_quant_vec16_kernel<__half>, vgrid, threads, 0, stream, pdl, a, tpc, num_tokens);
       note_launch("cache_quant_vec16");
     } else {
       int threads = n_elems > 256 ? 256 : ((n_elems + 31) / 32) * 32;
