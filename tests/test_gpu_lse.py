@@ -51,8 +51,9 @@ def _check_lse(lse, ref_lse, what):
     (AUTO, [(1, 700), (300, 300), (5, 18), (1, 77), (129, 463), (12, 900)]),     # mixed: three kernels, one LSE tensor
 ])
 @pytest.mark.parametrize("feature", ["plain", "window", "softcap", "sinks", "fp8"])
-def test_lse_matches_oracle(force, lens, feature):
-    Hq, Hkv, D = 16, 4, 128
+@pytest.mark.parametrize("D", [128, 256])
+def test_lse_matches_oracle(force, lens, feature, D):
+    Hq, Hkv = 16, 4
     fp8 = feature == "fp8"
     if fp8 and force in (GENERIC, PREFILL_TC):
         pytest.skip("fp8 KV reaches the tcgen05 kernel through staging (the mixed AUTO case); the SIMT kernel adds nothing")

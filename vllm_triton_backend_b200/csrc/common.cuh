@@ -106,6 +106,9 @@ bool prefill_supported(const b200attn_attention_params& p, const char** why);
 int launch_attn_prefill_tc(const b200attn_attention_params& p, cudaStream_t stream, QLenRange range = QLenRange(),
                            const int32_t* staged_base = nullptr);
 bool prefill_tc_supported(const b200attn_attention_params& p, const char** why);
+// head size 256 (attn_prefill_tc256.cu); launch_attn_prefill_tc / prefill_tc_supported route to these
+int launch_attn_prefill_tc256(const b200attn_attention_params& p, cudaStream_t stream, QLenRange range, const int32_t* staged_base);
+bool prefill_tc256_supported(const b200attn_attention_params& p, const char** why);
 int prefill_tc_min_q_len(const b200attn_attention_params& p);  // shortest query the tcgen05 tile is worth using for
 
 #ifdef __CUDACC__
