@@ -68,6 +68,8 @@ def run(args) -> dict:
     os.environ.setdefault("TRANSFORMERS_OFFLINE", "1")
     os.environ.setdefault("VLLM_NO_USAGE_STATS", "1")
     os.environ.setdefault("VLLM_LOGGING_LEVEL", "WARNING")
+    if args.tp > 1:
+        args.mp = True  # tensor parallelism runs one worker process per GPU
     if not args.mp:
         os.environ["VLLM_ENABLE_V1_MULTIPROCESSING"] = "0"  # engine core in this process: kernel launch counts visible
     if args.backend == "b200":
@@ -85,6 +87,11 @@ def run(args) -> dict:
               kv_cache_dtype=args.kv_cache_dtype, generation_config="vllm")
     if backend is not None:
         kw["attention_backend"] = backend
+    if args.tp > 1:
+        # the path shards by KV head exactly as vLLM's tensor parallelism does (vllm/config/model.py:1348-1363): every
+        # worker process loads the plugin and runs the kernels on its own heads; the only collective is vLLM's
+        # all-reduce behind o_proj, outside this path
+        kw.update(tensor_parallel_size=args.tp, distributed_executor_backend="mp")
     t0 = time.perf_counter()
     llm = LLM(**kw)
     t_init = time.perf_counter() - t0
@@ -146,7 +153,7 @@ def run(args) -> dict:
                    "num_prompts": args.num_prompts, "input_len": args.input_len, "output_len": args.output_len,
                    "prefix_caching": args.prefix_caching, "shared_prefix": args.shared_prefix,
                    "kv_cache_dtype": args.kv_cache_dtype, "enforce_eager": args.eager,
-                   "engine_core": "subprocess" if args.mp else "in-process"},
+                   "engine_core": "subprocess" if args.mp else "in-process", "tensor_parallel_size": args.tp},
     }
     if args.save:
         with open(args.save, "w") as f:
@@ -192,6 +199,7 @@ def main():
     ap.add_argument("--ragged", action="store_true", help="random prompt / generation lengths (batch size changes every few steps)")
     ap.add_argument("--max-num-seqs", type=int, default=0, help="batch slots (default: --num-prompts)")
     ap.add_argument("--mp", action="store_true", help="engine core in a subprocess (vLLM default); plugin via entry point")
+    ap.add_argument("--tp", type=int, default=1, help="tensor_parallel_size (KV heads sharded over the GPUs of one node)")
     ap.add_argument("--repeats", type=int, default=3, help="timed generate() calls; the median is reported")
     ap.add_argument("--save", default=None)
     ap.add_argument("--compare", nargs=2, default=None)
