@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 4
+#define B200ATTN_ABI_VERSION 5
 
 #if defined(__GNUC__)
 #define B200ATTN_API __attribute__((visibility("default")))
@@ -40,7 +40,8 @@ enum b200attn_dtype {
   B200ATTN_BF16 = 0,
   B200ATTN_F16 = 1,
   B200ATTN_F32 = 2,
-  B200ATTN_FP8_E4M3 = 3
+  B200ATTN_FP8_E4M3 = 3,
+  B200ATTN_INT8 = 4 /* KV cache only, and only with per-(token, head) scales (k_scale_cache / v_scale_cache) */
 };
 
 enum b200attn_status {
@@ -86,6 +87,29 @@ B200ATTN_API int b200attn_reshape_and_cache_flash(
     int64_t vc_head_stride, int32_t src_dtype, int32_t kv_dtype,
     const float* k_scale, const float* v_scale, b200attn_stream_t stream);
 
+/* K1 with dynamic per-(token, head) quantisation.  Replaces
+ * triton_reshape_and_cache_flash_per_token_head_quant (vLLM 0.22
+ * vllm/v1/attention/ops/triton_reshape_and_cache_flash.py:138-236, called at
+ * vllm/v1/attention/backends/triton_attn.py:733-748), the cache write of kv_cache_dtype
+ * "fp8_per_token_head" / "int8_per_token_head".  For every token i with slot >= 0 and every kv head h:
+ *   s = max(absmax(key[i][h][:]) / QMAX, 1e-6)           fp32; QMAX = 448 (FP8_E4M3) or 127 (INT8)
+ *   k_scale_cache[slot / bs][slot % bs][h] = s
+ *   k_cache[...][h][d] = Q(clamp(float(key[i][h][d]) * (1.0f / s), QMIN, QMAX))
+ * Q = round to nearest even to e4m3, or truncation toward zero to int8 (what storing an fp32 value through an
+ * int8 pointer does in the upstream kernel); QMIN = -448 / -128.  The same for value.  Strides in elements
+ * (scale caches: in floats); key / value rows innermost-contiguous. */
+B200ATTN_API int b200attn_reshape_and_cache_flash_per_token_head(
+    const void* key, const void* value, void* k_cache, void* v_cache,
+    float* k_scale_cache, float* v_scale_cache,
+    const int64_t* slot_mapping, int64_t num_tokens, int32_t num_kv_heads,
+    int32_t head_size, int32_t block_size,
+    int64_t key_stride0, int64_t key_stride1, int64_t value_stride0, int64_t value_stride1,
+    int64_t kc_block_stride, int64_t kc_slot_stride, int64_t kc_head_stride,
+    int64_t vc_block_stride, int64_t vc_slot_stride, int64_t vc_head_stride,
+    int64_t ks_block_stride, int64_t ks_slot_stride, int64_t ks_head_stride,
+    int64_t vs_block_stride, int64_t vs_slot_stride, int64_t vs_head_stride,
+    int32_t src_dtype, int32_t kv_dtype, b200attn_stream_t stream);
+
 /* ---- K2/K3: paged attention -----------------------------------------------
  * Replaces `unified_attention` (triton_unified_attention.py:839-1030): the 2D
  * kernel (:275-523), the 3D split-KV kernel (:526-754) and `reduce_segments`
@@ -118,7 +142,7 @@ typedef struct b200attn_attention_params {
   int32_t max_seqlen_q;
   int32_t max_seqlen_k;
   int32_t q_dtype;             /* enum b200attn_dtype: BF16 / F16 (F32: generic)   */
-  int32_t kv_dtype;            /* == q_dtype, or FP8_E4M3                          */
+  int32_t kv_dtype;            /* == q_dtype, or FP8_E4M3; INT8 with scale caches  */
   int32_t path;                /* enum b200attn_path                               */
   int32_t reserved0;
   int64_t num_blocks;          /* NB (extent of the cache views)                   */
@@ -160,6 +184,17 @@ typedef struct b200attn_attention_params {
                                   Without one the split-KV launch plans for itself (one more small launch).   */
   uint64_t decode_plan_key;    /* the key b200attn_decode_plan returned; a plan whose key does not match the
                                   launch's own geometry (other head counts, window, ...) is ignored            */
+  const float* k_scale_cache;  /* both NULL, or fp32 views [NB, bs, Hkv] (strides below, in floats): one scale per cached
+                                  (token, kv head), written by b200attn_reshape_and_cache_flash_per_token_head - upstream's
+                                  KVQuantMode.FP8_PER_TOKEN_HEAD / INT8_PER_TOKEN_HEAD (vLLM 0.22
+                                  vllm/v1/attention/ops/triton_unified_attention.py:469-489, 505-508, 539-544):
+                                  K and V are cast to the query dtype as they are, the logit of key j is
+                                  dot(q, K_j) * (softmax_scale * k_scale_cache[j]) and P_ij * v_scale_cache[j], rounded to
+                                  the query dtype, multiplies V_j.  kv_dtype is FP8_E4M3 or INT8; k_scale / v_scale are
+                                  not used.                                                                     */
+  const float* v_scale_cache;
+  int64_t ks_block_stride, ks_slot_stride, ks_head_stride;
+  int64_t vs_block_stride, vs_slot_stride, vs_head_stride;
 } b200attn_attention_params;
 
 /* Bytes of workspace b200attn_unified_attention may need for this shape

@@ -103,6 +103,44 @@ def reshape_and_cache_flash_ref(
             vc[b, o] = value[i]
 
 
+def per_token_head_quant_ref(x: torch.Tensor, kv_dtype: torch.dtype):
+    """Dynamic per-(token, head) quantisation of one [T, H, D] tensor.  The algorithm lives in a third-party dependency
+    of the reference, vLLM (pinned here: the installed vllm 0.22.0, `_reshape_cache_per_token_head`,
+    vllm/v1/attention/ops/triton_reshape_and_cache_flash.py:138-236; `ibm-triton-lib` is a plugin for that vLLM and its
+    backend sits where `TritonAttentionImpl.do_kv_cache_update`, vllm/v1/attention/backends/triton_attn.py:733-748,
+    calls it):
+        scale = max(absmax(x[t, h, :]) / QMAX, 1e-6)                    (:190, :218)
+        q     = clamp(x * (1.0 / scale), QMIN, QMAX) stored through the cache pointer   (:199-208)
+    QMAX, QMIN = 448, -448 for e4m3 (round to nearest even) and 127, -128 for int8 (the store of an fp32 value through
+    an int8 pointer converts with truncation toward zero).  Returns (q as `kv_dtype`, scale fp32 [T, H])."""
+    qmax, qmin = (448.0, -448.0) if kv_dtype == _FP8 else (127.0, -128.0)
+    xf = x.to(torch.float32)
+    scale = torch.clamp(xf.abs().amax(dim=-1) / torch.tensor(qmax, dtype=torch.float32), min=1e-6)
+    inv = torch.tensor(1.0, dtype=torch.float32) / scale
+    y = (xf * inv.unsqueeze(-1)).clamp(qmin, qmax)
+    q = y.to(_FP8) if kv_dtype == _FP8 else y.trunc().to(torch.int8)
+    return q, scale
+
+
+def reshape_and_cache_flash_per_token_head_ref(key, value, key_cache, value_cache, k_scale_cache, v_scale_cache,
+                                               slot_mapping) -> None:
+    """`triton_reshape_and_cache_flash_per_token_head_quant` (vLLM 0.22
+    vllm/v1/attention/ops/triton_reshape_and_cache_flash.py:247-320): quantise every (token, head) row of key and
+    value with its own scale, scatter the rows into the paged caches and the scales into the scale caches
+    ([num_blocks, block_size, num_kv_heads] fp32, any strides).  In place."""
+    bs = key_cache.shape[1]
+    kq, ks = per_token_head_quant_ref(key, key_cache.dtype)
+    vq, vs = per_token_head_quant_ref(value, value_cache.dtype)
+    for i, slot in enumerate(int(x) for x in slot_mapping.tolist()):
+        if slot < 0:
+            continue
+        b, o = slot // bs, slot % bs
+        key_cache[b, o] = kq[i]
+        value_cache[b, o] = vq[i]
+        k_scale_cache[b, o] = ks[i]
+        v_scale_cache[b, o] = vs[i]
+
+
 def reshape_and_cache_flash_c(key, value, key_cache, value_cache, slot_mapping) -> None:
     """Plain-C scatter for 16-bit element types (copy path), contiguous NHD."""
     lib = load_c_lib()

@@ -67,8 +67,13 @@ def unified_attention_ref(
     local_chunk: int = 0,  # chunked local attention: a query only sees keys of its own chunk of positions
     qq_bias: Optional[torch.Tensor] = None,  # [q, n] fp32: bias between the query tokens of a step
     return_lse: bool = False,  # also return fp32 [T, Hq]: ln sum_j exp(s_ij) (+ exp(sink)); -inf where nothing is visible
+    k_scale_cache: Optional[torch.Tensor] = None,  # [NB, bs, Hkv] fp32: per-(token, head) scales (fp8 or int8 cache)
+    v_scale_cache: Optional[torch.Tensor] = None,
 ):
-    """`qq_bias` (upstream, vllm/v1/attention/ops/triton_unified_attention.py:526-528 with
+    """`k_scale_cache` / `v_scale_cache` (upstream KVQuantMode.FP8_PER_TOKEN_HEAD / INT8_PER_TOKEN_HEAD, vLLM 0.22
+    vllm/v1/attention/ops/triton_unified_attention.py:39-55, 469-489, 505-508, 539-544): K and V are cast to the query
+    dtype as stored, S = dot(Q, K) * (softmax_scale * k_scale[key]) and acc += (P * v_scale[key]).to(q dtype) @ V.
+    `qq_bias` (upstream, vllm/v1/attention/ops/triton_unified_attention.py:526-528 with
     triton_attention_helpers.py:344-357): after masking and ALiBi, S[query i][key j] += qq_bias[i][j - ctx] for
     0 <= j - ctx < qq_bias.stride(0), the same matrix for every sequence and head.
     `local_chunk` states chunked local attention (iRoPE / Llama-4) directly as a mask: position p
@@ -97,11 +102,23 @@ def unified_attention_ref(
             continue  # nothing visible: output stays 0 (reduce_segments :828)
         ctx = kv_len - q_len  # :374
         qb = q[q0:q1].to(torch.float32)  # [q, Hq, D]
-        k = _dequant(gather_kv(k_cache, block_table[b], kv_len), k_scale, cdt)
-        v = _dequant(gather_kv(v_cache, block_table[b], kv_len), v_scale, cdt)
+        per_token_head = k_scale_cache is not None
+        if per_token_head:
+            k = gather_kv(k_cache, block_table[b], kv_len).to(torch.float32)  # plain cast (_cast_kv_tile)
+            v = gather_kv(v_cache, block_table[b], kv_len).to(torch.float32)
+            ks = gather_kv(k_scale_cache.unsqueeze(-1), block_table[b], kv_len)[..., 0].to(torch.float32)  # [kv, Hkv]
+            vs = gather_kv(v_scale_cache.unsqueeze(-1), block_table[b], kv_len)[..., 0].to(torch.float32)
+            ks = ks.repeat_interleave(g, dim=1).T.unsqueeze(1)  # [Hq, 1, kv]
+            vs = vs.repeat_interleave(g, dim=1).T.unsqueeze(1)
+        else:
+            k = _dequant(gather_kv(k_cache, block_table[b], kv_len), k_scale, cdt)
+            v = _dequant(gather_kv(v_cache, block_table[b], kv_len), v_scale, cdt)
         k = k.repeat_interleave(g, dim=1)  # [kv, Hq, D]
         v = v.repeat_interleave(g, dim=1)
-        s = softmax_scale * torch.einsum("qhd,khd->hqk", qb, k)  # :465 (scale after the dot)
+        if per_token_head:
+            s = torch.einsum("qhd,khd->hqk", qb, k) * (torch.tensor(softmax_scale, dtype=torch.float32) * ks)
+        else:
+            s = softmax_scale * torch.einsum("qhd,khd->hqk", qb, k)  # :465 (scale after the dot)
         if softcap > 0:
             s = _softcap(s, softcap)  # :467-468, before masking
         qpos = torch.arange(q_len).view(1, q_len, 1)
@@ -127,6 +144,8 @@ def unified_attention_ref(
         l = p.sum(dim=-1, keepdim=True)
         if sinks is not None:
             l = l + torch.exp(sinks.to(torch.float32).view(Hq, 1, 1) - m)
+        if per_token_head:
+            p = p * vs
         if round_p_to is not None:
             p = p.to(round_p_to).to(torch.float32)
         o = torch.einsum("hqk,khd->qhd", p, v) / l.permute(1, 0, 2)  # :508-511

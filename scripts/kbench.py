@@ -143,7 +143,7 @@ def decode_case(args, device):
         ctx = args.ctx
     if args.bs:
         bs = args.bs
-    if args.fp8:
+    if args.fp8 or args.pth:
         fp8 = True
     if args.workload == "c2var":
         pat = [0.1, 0.4, 0.5, 1.0, 0.2]  # reference scripts/benchmark.py:115
@@ -166,6 +166,17 @@ def decode_case(args, device):
     ws = torch.zeros(ops.workspace_bytes(B, B, hq, hkv, D), dtype=torch.uint8, device=device)
     sc = torch.tensor([0.5], dtype=torch.float32, device=device) if fp8 else None
     nbytes = decode_bytes(lens, hq, hkv, D, bs, 1 if fp8 else 2)
+    pth_kw = {}
+    if args.pth:
+        # scale caches [NB, bs, Hkv] laid out [Hkv][bs] inside a block, as in the plugin's allocation
+        # (ops.per_token_head_cache_views); their bytes count as traffic too
+        if args.pth == "int8":
+            kc, vc = kc.view(torch.int8), vc.view(torch.int8)
+        ksc = (torch.rand(NB, hkv, bs, device=device, generator=g) * 0.01 + 0.001).transpose(1, 2)
+        vsc = (torch.rand(NB, hkv, bs, device=device, generator=g) * 0.01 + 0.001).transpose(1, 2)
+        pth_kw = dict(kv_quant_mode=2 if args.pth == "int8" else 3, k_scale_cache=ksc, v_scale_cache=vsc)
+        sc = None
+        nbytes += sum(lens) * hkv * 2 * 4
     plan = None
     if getattr(args, "plan", False):
         # what the metadata builder does once per step: the split-KV work plan, shared by every layer's launch
@@ -177,14 +188,15 @@ def decode_case(args, device):
         ops.unified_attention(q=q, k=kc, v=vc, out=out, cu_seqlens_q=cu, max_seqlen_q=1, seqused_k=sl,
                               max_seqlen_k=max(lens), softmax_scale=D ** -0.5, causal=True, window_size=(-1, -1),
                               block_table=bt, softcap=0, q_descale=None, k_descale=sc, v_descale=sc, workspace=ws,
-                              force_selection=args.force, decode_plan=plan)
+                              force_selection=args.force, decode_plan=plan, **pth_kw)
     if getattr(args, "impl", "ours") == "triton":
         tri = triton_reference().TritonReference(B, hq, D, device)
 
         def fn():  # noqa: F811 - the reference kernels on the same tensors
-            tri(q, kc, vc, out, cu, 1, sl, max(lens), D ** -0.5, bt, k_scale=sc, v_scale=sc, use_3d=args.force != 2)
+            tri(q, kc, vc, out, cu, 1, sl, max(lens), D ** -0.5, bt, k_scale=sc, v_scale=sc, use_3d=args.force != 2,
+                k_scale_cache=pth_kw.get("k_scale_cache"), v_scale_cache=pth_kw.get("v_scale_cache"))
     return fn, nbytes, dict(B=B, ctx=ctx, hq=hq, hkv=hkv, D=D, bs=bs, fp8=fp8, workload=args.workload, layout=args.layout,
-                            plan=plan is not None)
+                            plan=plan is not None, per_token_head=args.pth)
 
 
 def decode_trace(fn, device):
@@ -343,12 +355,29 @@ def run_cache(args, device):
 
     def fn():
         ops.reshape_and_cache_flash(key, val, kc, vc, slots, "fp8" if args.fp8 else "auto", sc, sc)
+    if args.pth:
+        kc, vc = make_kv(NB, bs, hkv, D, True, device, g, args.layout)
+        if args.pth == "int8":
+            kc, vc = kc.view(torch.int8), vc.view(torch.int8)
+        ksc = torch.ones(NB, hkv, bs, device=device).transpose(1, 2)
+        vsc = torch.ones(NB, hkv, bs, device=device).transpose(1, 2)
+        nbytes = cache_write_bytes(T, hkv, D, 2, 1) + T * hkv * 2 * 4
+
+        def fn():  # noqa: F811
+            ops.reshape_and_cache_flash_per_token_head(key, val, kc, vc, ksc, vsc, slots)
+        if args.impl == "triton":
+            from vllm.v1.attention.ops.triton_reshape_and_cache_flash import (
+                triton_reshape_and_cache_flash_per_token_head_quant as theirs,
+            )
+
+            def fn():  # noqa: F811
+                theirs(key, val, kc, vc, ksc, vsc, slots)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=device) if args.flush else None
     ms, n = time_fn(fn, flush=flush)
     gbs = nbytes / ms / 1e6
     print(json.dumps(dict(kind="cache_write", tokens=T, hkv=hkv, D=D, bs=bs, fp8=bool(args.fp8), ms=round(ms, 5),
-                          gbs=round(gbs, 1), frac_measured=round(gbs / hbm, 4), iters=n, kernel=_cabi.last_kernel(),
-                          flush=bool(args.flush))), flush=True)
+                          gbs=round(gbs, 1), frac_measured=round(gbs / hbm, 4), iters=n, kernel=kernel_name(args),
+                          flush=bool(args.flush), per_token_head=args.pth, impl=args.impl)), flush=True)
 
 
 def main():
@@ -370,6 +399,8 @@ def main():
     ap.add_argument("--d", type=int, default=0, help="prefill: head size (default 128)")
     ap.add_argument("--tokens", type=int, default=8192)
     ap.add_argument("--fp8", action="store_true")
+    ap.add_argument("--pth", default="", choices=["", "fp8", "int8"],
+                    help="decode / cache: per-(token, head) quantised cache (one fp32 scale per cached row)")
     ap.add_argument("--flush", action="store_true")
     ap.add_argument("--layout", default="planes", choices=["planes", "interleaved"])
     ap.add_argument("--force", type=int, default=None)

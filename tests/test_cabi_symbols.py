@@ -39,7 +39,7 @@ def test_every_declared_symbol_is_exported(lib):
 def test_abi_version_and_host_only_calls(lib):
     from vllm_triton_backend_b200 import _cabi as cabi
 
-    assert lib.b200attn_abi_version() == cabi.ABI_VERSION == 4
+    assert lib.b200attn_abi_version() == cabi.ABI_VERSION == 5
     # workspace size is a function of host ints only
     a = lib.b200attn_workspace_bytes(64, 64, 32, 8, 128)
     b = lib.b200attn_workspace_bytes(128, 128, 32, 8, 128)

@@ -97,7 +97,8 @@ class TritonReference:
         self.segm_expsum = torch.empty_like(self.segm_max)
 
     def __call__(self, q, k_cache, v_cache, out, cu_seqlens_q, max_seqlen_q, seq_lens, max_seqlen_k, scale,
-                 block_table, window=0, softcap=0.0, alibi_slopes=None, k_scale=None, v_scale=None, use_3d=True, sinks=None):
+                 block_table, window=0, softcap=0.0, alibi_slopes=None, k_scale=None, v_scale=None, use_3d=True, sinks=None,
+                 k_scale_cache=None, v_scale_cache=None):
         from vllm.v1.attention.ops.triton_unified_attention import unified_attention
 
         from vllm.v1.kv_cache_interface import KVQuantMode
@@ -108,8 +109,11 @@ class TritonReference:
         mode = KVQuantMode.FP8_PER_TENSOR if k_cache.dtype == torch.float8_e4m3fn else KVQuantMode.NONE
         one = torch.ones(1, dtype=torch.float32, device=dev)
         kw = {}
+        if k_scale_cache is not None:  # per-(token, head) scales: upstream modes 2 (int8) and 3 (e4m3)
+            mode = KVQuantMode.INT8_PER_TOKEN_HEAD if k_cache.dtype == torch.int8 else KVQuantMode.FP8_PER_TOKEN_HEAD
+            kw.update(k_scale_cache=k_scale_cache, v_scale_cache=v_scale_cache)
         if use_3d and max_seqlen_q == 1 and seq_lens.shape[0] <= self.max_seqs:
-            kw = dict(seq_threshold_3D=self.max_seqs, num_par_softmax_segments=self.NUM_SEGMENTS,
+            kw.update(seq_threshold_3D=self.max_seqs, num_par_softmax_segments=self.NUM_SEGMENTS,
                       softmax_segm_output=self.segm_output, softmax_segm_max=self.segm_max,
                       softmax_segm_expsum=self.segm_expsum)
         unified_attention(

@@ -13,7 +13,7 @@ _PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_PKG_DIR, "libb200attn.so")
 
 # enum b200attn_dtype
-BF16, F16, F32, FP8_E4M3 = 0, 1, 2, 3
+BF16, F16, F32, FP8_E4M3, INT8 = 0, 1, 2, 3, 4
 # enum b200attn_path
 PATH_AUTO, PATH_GENERIC, PATH_PREFILL, PATH_DECODE, PATH_PREFILL_TC = 0, 1, 2, 3, 4
 
@@ -22,10 +22,11 @@ STATUS_NAMES = {
     6: "E_CUDA", 7: "E_NULL",
 }
 
-ABI_VERSION = 4  # include/b200attn.h B200ATTN_ABI_VERSION
+ABI_VERSION = 5  # include/b200attn.h B200ATTN_ABI_VERSION
 
 EXPORTED_SYMBOLS = [
     "b200attn_reshape_and_cache_flash",
+    "b200attn_reshape_and_cache_flash_per_token_head",
     "b200attn_workspace_bytes",
     "b200attn_unified_attention",
     "b200attn_decode_plan_bytes",
@@ -63,6 +64,9 @@ class AttentionParams(Structure):
         ("qq_bias", c_void_p), ("qq_bias_stride0", c_int64),
         ("lse", c_void_p), ("lse_stride0", c_int64),
         ("decode_plan", c_void_p), ("decode_plan_key", c_uint64),
+        ("k_scale_cache", c_void_p), ("v_scale_cache", c_void_p),
+        ("ks_block_stride", c_int64), ("ks_slot_stride", c_int64), ("ks_head_stride", c_int64),
+        ("vs_block_stride", c_int64), ("vs_slot_stride", c_int64), ("vs_head_stride", c_int64),
     ]
 
 
@@ -105,6 +109,10 @@ def load_library() -> ctypes.CDLL:
     lib.b200attn_reshape_and_cache_flash.restype = c_int32
     lib.b200attn_reshape_and_cache_flash.argtypes = (
         [c_void_p] * 5 + [c_int64, c_int32, c_int32, c_int32] + [c_int64] * 8 + [c_int32, c_int32, c_void_p, c_void_p, c_void_p]
+    )
+    lib.b200attn_reshape_and_cache_flash_per_token_head.restype = c_int32
+    lib.b200attn_reshape_and_cache_flash_per_token_head.argtypes = (
+        [c_void_p] * 7 + [c_int64, c_int32, c_int32, c_int32] + [c_int64] * 16 + [c_int32, c_int32, c_void_p]
     )
     lib.b200attn_workspace_bytes.restype = c_uint64
     lib.b200attn_workspace_bytes.argtypes = [c_int32] * 5

@@ -78,7 +78,7 @@ class B200AttentionMetadataBuilder(AttentionMetadataBuilder[B200AttentionMetadat
         self._ws_seqs = max_num_seqs
         nbytes = ops.workspace_bytes(max_num_seqs, max_num_seqs, self.num_heads_q, self.num_heads_kv, self.headdim)
         cache_dtype = str(getattr(vllm_config.cache_config, "cache_dtype", "auto"))
-        if cache_dtype.startswith("fp8"):
+        if cache_dtype.startswith("fp8") or cache_dtype in PER_TOKEN_HEAD_DTYPES:
             # FP8 cache: staging pool that lets long prefills run the tcgen05 kernel (csrc/kv_stage.cu).  It sits
             # outside vLLM's KV-cache budget (gpu_memory_utilization does not see it), so it is bounded: one
             # sequence of max_model_len, at most B200ATTN_FP8_STAGING_MIB (default 256) MiB; what does not fit
@@ -103,6 +103,8 @@ class B200AttentionMetadataBuilder(AttentionMetadataBuilder[B200AttentionMetadat
         # is assumed here (another sliding window) ignores it and plans for itself (the key does not match).
         q_dtype = model_config.dtype
         kv_dtype = torch.float8_e4m3fn if cache_dtype.startswith("fp8") else q_dtype
+        if cache_dtype in PER_TOKEN_HEAD_DTYPES:
+            kv_dtype = PER_TOKEN_HEAD_DTYPES[cache_dtype]
         self.decode_plan = None
         if q_dtype in (torch.bfloat16, torch.float16):
             self.decode_plan = ops.DecodePlan(device, max_num_seqs, self.num_heads_q, self.num_heads_kv, self.headdim,
@@ -156,7 +158,8 @@ class B200AttentionMetadataBuilder(AttentionMetadataBuilder[B200AttentionMetadat
 class B200AttentionBackend(AttentionBackend):
     accept_output_buffer: bool = True
     supported_dtypes: ClassVar[list] = [torch.float16, torch.bfloat16]
-    supported_kv_cache_dtypes: ClassVar[list] = ["auto", "float16", "bfloat16", "fp8", "fp8_e4m3"]
+    supported_kv_cache_dtypes: ClassVar[list] = ["auto", "float16", "bfloat16", "fp8", "fp8_e4m3", "fp8_per_token_head",
+                                                 "int8_per_token_head"]
     # vLLM >= 0.11 calls do_kv_cache_update before forward
     forward_includes_kv_cache_update: bool = False
 
@@ -205,6 +208,12 @@ class B200AttentionBackend(AttentionBackend):
         # K and V planes are separate: each (page, kv-head-group) tile the decode
         # kernel streams is one contiguous TMA box, and K/V of a page do not share
         # DRAM rows.  (The reference plugin used this layout too, :277.)
+        if cache_dtype_str in PER_TOKEN_HEAD_DTYPES:
+            # the bytes vLLM budgets for this mode: every (token, head) row plus one fp32 scale
+            # (AttentionSpec.page_size_bytes; upstream's backend declares the same padded shape,
+            # vllm/v1/attention/backends/triton_attn.py:319-333).  Inside a block the data comes first and the
+            # scales behind it (ops.per_token_head_cache_views), not inline behind every row.
+            return (2, num_blocks, block_size, num_kv_heads, head_size + ops.PER_TOKEN_HEAD_SCALE_PAD_BYTES)
         return (2, num_blocks, block_size, num_kv_heads, head_size)
 
     @staticmethod
@@ -237,6 +246,10 @@ class B200AttentionBackend(AttentionBackend):
     @classmethod
     def supports_sink(cls) -> bool:
         return True  # every kernel applies the sink in its epilogue (decode: direct epilogue or the merge)
+
+
+# kv_cache_dtype strings of upstream's dynamically quantised caches (vllm/v1/kv_cache_interface.py:57-64) -> element type
+PER_TOKEN_HEAD_DTYPES = {"fp8_per_token_head": torch.float8_e4m3fn, "int8_per_token_head": torch.int8}
 
 
 def split_kv_cache(kv_cache: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor]:
@@ -311,15 +324,27 @@ class B200AttentionImpl(AttentionImpl):
         self.attn_type = attn_type
         self.supports_quant_query_input = False
         self._plans: dict = {}
-        if kv_cache_dtype.startswith("fp8") and kv_cache_dtype not in ("fp8", "fp8_e4m3"):
+        self._per_token_head = kv_cache_dtype in PER_TOKEN_HEAD_DTYPES
+        self._pth_filled: set = set()
+        if kv_cache_dtype.startswith("fp8") and kv_cache_dtype not in ("fp8", "fp8_e4m3") and not self._per_token_head:
             raise NotImplementedError(f"kv_cache_dtype {kv_cache_dtype!r}: only fp8_e4m3 is implemented")
 
     def _views(self, kv_cache: torch.Tensor):
         key_cache, value_cache = split_kv_cache(kv_cache)
+        if self._per_token_head:
+            raise RuntimeError("per-token-head caches are read through _per_token_head_views")
         if self.kv_cache_dtype.startswith("fp8") and key_cache.dtype != torch.float8_e4m3fn:
             key_cache = key_cache.view(torch.float8_e4m3fn)  # reference :407-409
             value_cache = value_cache.view(torch.float8_e4m3fn)
         return key_cache, value_cache
+
+    def _per_token_head_views(self, kv_cache: torch.Tensor):
+        """(K data, V data, K scales, V scales) of a cache allocated with the padded shape of get_kv_cache_shape."""
+        k_plane, v_plane = split_kv_cache(kv_cache)
+        dt = PER_TOKEN_HEAD_DTYPES[self.kv_cache_dtype]
+        key_cache, k_scales = ops.per_token_head_cache_views(k_plane, self.head_size, dt)
+        value_cache, v_scales = ops.per_token_head_cache_views(v_plane, self.head_size, dt)
+        return key_cache, value_cache, k_scales, v_scales
 
     def _plans_for(self, layer, kv_cache: torch.Tensor, q_dtype: torch.dtype):
         """(cache-write plan, attention plan) of this layer's cache tensor: the argument
@@ -327,6 +352,24 @@ class B200AttentionImpl(AttentionImpl):
         filled in once (ops.AttentionPlan / ops.CacheWritePlan)."""
         key = (kv_cache.data_ptr(), q_dtype)
         plans = self._plans.get(key)
+        if plans is None and self._per_token_head:
+            if self._alibi_slopes_host is not None and self.alibi_slopes is None:
+                self.alibi_slopes = self._alibi_slopes_host.to(kv_cache.device)
+            key_cache, value_cache, k_scales, v_scales = self._per_token_head_views(kv_cache)
+            # Upstream fills its scale views with 1.0 when it first sees a cache (triton_attn.py:441,452).  The kernels
+            # here never read the scale of a slot that has not been written (they stop at seq_len), so this is
+            # hygiene only - and done once per allocation: a re-made plan must not wipe live scales.
+            if kv_cache.data_ptr() not in self._pth_filled:
+                self._pth_filled.add(kv_cache.data_ptr())
+                k_scales.fill_(1.0)
+                v_scales.fill_(1.0)
+            plans = (
+                ops.PerTokenHeadCacheWritePlan(key_cache, value_cache, k_scales, v_scales, q_dtype),
+                ops.AttentionPlan(key_cache, value_cache, q_dtype, self.num_heads, self.head_size, self.scale,
+                                  self.sliding_window, self.logits_soft_cap, self.alibi_slopes, None, None,
+                                  sinks=self.sinks, k_scale_cache=k_scales, v_scale_cache=v_scales),
+            )
+            self._plans[key] = plans
         if plans is None:
             key_cache, value_cache = self._views(kv_cache)
             if self._alibi_slopes_host is not None and self.alibi_slopes is None:
@@ -363,7 +406,7 @@ class B200AttentionImpl(AttentionImpl):
     def fused_rope_kvcache_supported(self) -> bool:
         """RoPE + cache write in one launch (ops.rope_and_cache_flash); vLLM's
         RopeKVCacheFusionPass asks before rewriting the graph."""
-        return self.kv_sharing_target_layer_name is None and self.head_size % 8 == 0
+        return self.kv_sharing_target_layer_name is None and self.head_size % 8 == 0 and not self._per_token_head
 
     def do_rope_and_kv_cache_update(self, layer, query, key, value, positions, cos_sin_cache, is_neox, kv_cache,
                                     layer_slot_mapping) -> None:

@@ -306,10 +306,14 @@ __global__ void __launch_bounds__(kPlanThreads) decode_plan_kernel(const PlanArg
   }
 }
 
-template <int D, bool KV_FP8, bool MMA_BF16, bool Q_BF16, int NT, int NW, int TT>
+// KVQ: 0 = 16-bit cache, 1 = e4m3 with per-tensor scales, 2 = e4m3 and 3 = int8 with per-(token, head) scales
+template <int D, int KVQ, bool MMA_BF16, bool Q_BF16, int NT, int NW, int TT>
 __global__ void __launch_bounds__((NW + 2) * 32, 1)
 attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_map,
                    const __grid_constant__ CUtensorMap v_map) {
+  constexpr bool KV_FP8 = KVQ != 0;  // one-byte cache elements (the name predates int8)
+  constexpr bool PTH = KVQ >= 2;     // per-(token, head) scales
+  constexpr bool KV_I8 = KVQ == 3;
   constexpr int ESZ = KV_FP8 ? 1 : 2;
   constexpr int NDC = D * ESZ / 128;      // 128-byte chunks per row
   constexpr int KSTEPS = D / 16;          // k16 steps of S = K Q^T
@@ -691,6 +695,42 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
   const float qk_scale = P.a.softmax_scale * k_scale;  // natural units
   const bool has_alibi = P.a.alibi_slopes != nullptr;
 
+  // Per-(token, head) scales (KVQ >= 2): rows gid and gid + 8 of each 16-token sub-tile need the key's and the
+  // value's scale.  The consumers fetch them themselves - the stage ring has no room left for them - straight from
+  // the scale caches: the page of each sub-tile is looked up one step ahead (block table: an L2 hit behind the
+  // producer's own lookups), the four scales are requested at the top of the step and first used after the
+  // S = K Q^T pass, so their latency hides behind the wait for the stage and the first MMA pass.
+  int pg_cur[SUB], pg_nxt[SUB];
+  float ksc[SUB][2], vsc[SUB][2];
+#pragma unroll
+  for (int sb = 0; sb < SUB; ++sb) pg_cur[sb] = pg_nxt[sb] = -1, ksc[sb][0] = ksc[sb][1] = vsc[sb][0] = vsc[sb][1] = 1.f;
+  const int bs_mask = P.a.block_size - 1;
+  auto load_pages = [&](int item, int step, int seq_len, int (&pg)[SUB]) {
+    const int32_t* bt = P.a.block_tables + (int64_t)(item / P.head_groups) * P.a.bt_stride0;
+#pragma unroll
+    for (int sb = 0; sb < SUB; ++sb) {
+      const int tok = step * P.tps + tok_off + 16 * sb;  // 16-aligned and block_size >= 16: one page per sub-tile
+      pg[sb] = tok < seq_len ? __ldg(bt + (tok >> P.bs_shift)) : -1;
+    }
+  };
+  auto load_scales = [&](int hg, int step, int seq_len) {
+    const int head = hg * P.hpc + h_local;
+#pragma unroll
+    for (int sb = 0; sb < SUB; ++sb) {
+#pragma unroll
+      for (int hf = 0; hf < 2; ++hf) {
+        const int tok = step * P.tps + tok_off + 16 * sb + gid + 8 * hf;
+        float kq = 1.f, vq = 1.f;
+        if (tok < seq_len) {  // (then pg_cur[sb] >= 0)
+          const int slot = tok & bs_mask;
+          kq = __ldg(P.a.k_scale_cache + (int64_t)pg_cur[sb] * P.a.ks_block_stride + (int64_t)slot * P.a.ks_slot_stride + (int64_t)head * P.a.ks_head_stride);
+          vq = __ldg(P.a.v_scale_cache + (int64_t)pg_cur[sb] * P.a.vs_block_stride + (int64_t)slot * P.a.vs_slot_stride + (int64_t)head * P.a.vs_head_stride);
+        }
+        ksc[sb][hf] = kq, vsc[sb][hf] = vq;
+      }
+    }
+  };
+
   // ldmatrix lane geometry
   const int lrow = (lane & 7);
   uint32_t k_lane_off, v_lane_off;  // byte offsets inside a [rows][128B] sub-tile, before the chunk XOR
@@ -936,6 +976,7 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
   cur.hg = run.hg, cur.step = run.step0, cur.seq_len = run.seq_len;
   reset_state();
   load_q(run.tq, run.hg);
+  if constexpr (PTH) load_pages(run.item, cur.step, cur.seq_len, pg_cur);
   bool first_stage = true;
   int steps_done = 0;  // of the current run
 
@@ -943,6 +984,10 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
   uint32_t phase = 0;
   while (true) {
     const int tok0 = cur.step * P.tps + tok_off;  // first token of this warp's tile
+    if constexpr (PTH) {
+      load_scales(cur.hg, cur.step, cur.seq_len);
+      load_pages(run.item, cur.step + 1, cur.seq_len, pg_nxt);
+    }
     {
       const long long t0 = trace ? clock64() : 0;
       mbar_wait(&full_bar[stage], phase);
@@ -995,10 +1040,10 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
 #pragma unroll
                 for (int half = 0; half < 2; ++half) {
                   uint32_t a[4];
-                  a[0] = e4m3x2_to_f16x2((uint16_t)(r[2 * half] & 0xffffu));
-                  a[1] = e4m3x2_to_f16x2((uint16_t)(r[2 * half + 1] & 0xffffu));
-                  a[2] = e4m3x2_to_f16x2((uint16_t)(r[2 * half] >> 16));
-                  a[3] = e4m3x2_to_f16x2((uint16_t)(r[2 * half + 1] >> 16));
+                  a[0] = kv8x2_to_f16x2<KV_I8>((uint16_t)(r[2 * half] & 0xffffu));
+                  a[1] = kv8x2_to_f16x2<KV_I8>((uint16_t)(r[2 * half + 1] & 0xffffu));
+                  a[2] = kv8x2_to_f16x2<KV_I8>((uint16_t)(r[2 * half] >> 16));
+                  a[3] = kv8x2_to_f16x2<KV_I8>((uint16_t)(r[2 * half + 1] >> 16));
                   const int ks = dc * 8 + c2 * 2 + half;
 #pragma unroll
                   for (int nt = 0; nt < NT; ++nt)
@@ -1025,7 +1070,9 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
         for (int sb = 0; sb < SUB; ++sb) {
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
-            float x = sacc[sb][nt][i] * qk_scale;
+            float x;
+            if constexpr (PTH) x = sacc[sb][nt][i] * (qk_scale * ksc[sb][i >> 1]);  // upstream: dot * (scale * k_scale[key])
+            else x = sacc[sb][nt][i] * qk_scale;
             if (has_cap) x = softcap_fn(x, P.a.softcap, inv_cap);
             sv[sb][i] = x * kLog2e;
           }
@@ -1064,8 +1111,13 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
           const float p0 = ex2(sv[sb][0] - mu0), p1 = ex2(sv[sb][1] - mu1), p2 = ex2(sv[sb][2] - mu0), p3 = ex2(sv[sb][3] - mu1);
           ls0 += p0 + p2, ls1 += p1 + p3;
           // P^T fragments: transpose the two 8x8 (token x head) blocks
-          pb[sb][nt][0] = movmatrix_trans(pack2<MMA_BF16>(p0, p1));
-          pb[sb][nt][1] = movmatrix_trans(pack2<MMA_BF16>(p2, p3));
+          if constexpr (PTH) {  // upstream: (P * v_scale[key]).to(V.dtype); the exp-sum above takes P itself
+            pb[sb][nt][0] = movmatrix_trans(pack2<MMA_BF16>(p0 * vsc[sb][0], p1 * vsc[sb][0]));
+            pb[sb][nt][1] = movmatrix_trans(pack2<MMA_BF16>(p2 * vsc[sb][1], p3 * vsc[sb][1]));
+          } else {
+            pb[sb][nt][0] = movmatrix_trans(pack2<MMA_BF16>(p0, p1));
+            pb[sb][nt][1] = movmatrix_trans(pack2<MMA_BF16>(p2, p3));
+          }
         }
         l_run[nt][0] = l_run[nt][0] * alpha[nt][0] + ls0;
         l_run[nt][1] = l_run[nt][1] * alpha[nt][1] + ls1;
@@ -1124,10 +1176,10 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
                 const uint32_t x0 = __byte_perm(r[2 * half], 0, 0x3120);      // [t d0, t+1 d0 | t d1, t+1 d1]
                 const uint32_t x1 = __byte_perm(r[2 * half + 1], 0, 0x3120);
                 uint32_t a[4];
-                a[0] = e4m3x2_to_f16x2((uint16_t)(x0 & 0xffffu));  // row gid   <-> d0, tokens 2t,2t+1
-                a[1] = e4m3x2_to_f16x2((uint16_t)(x0 >> 16));      // row gid+8 <-> d1
-                a[2] = e4m3x2_to_f16x2((uint16_t)(x1 & 0xffffu));  // tokens 2t+8, 2t+9
-                a[3] = e4m3x2_to_f16x2((uint16_t)(x1 >> 16));
+                a[0] = kv8x2_to_f16x2<KV_I8>((uint16_t)(x0 & 0xffffu));  // row gid   <-> d0, tokens 2t,2t+1
+                a[1] = kv8x2_to_f16x2<KV_I8>((uint16_t)(x0 >> 16));      // row gid+8 <-> d1
+                a[2] = kv8x2_to_f16x2<KV_I8>((uint16_t)(x1 & 0xffffu));  // tokens 2t+8, 2t+9
+                a[3] = kv8x2_to_f16x2<KV_I8>((uint16_t)(x1 >> 16));
                 if (partial) a[0] &= vm_lo, a[1] &= vm_lo, a[2] &= vm_hi, a[3] &= vm_hi;
                 const int mt = dc * 8 + c2 * 2 + half;
 #pragma unroll
@@ -1143,6 +1195,10 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
     if (++stage == P.stages) stage = 0, phase ^= 1;
 
     ++cur.step, ++steps_done;
+    if constexpr (PTH) {
+#pragma unroll
+      for (int sb = 0; sb < SUB; ++sb) pg_cur[sb] = pg_nxt[sb];
+    }
     if (run_ends) {
       // ---------------- finalise this run ------------------
       const long long t_fin = trace ? clock64() : 0;
@@ -1158,6 +1214,9 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
       const RunDesc nx = descs[nd & (kDescSlots - 1)];
       const bool last = nx.kind == 0;
       if (!last) load_q(nx.tq, nx.hg);
+      if constexpr (PTH) {
+        if (!last) load_pages(nx.item, nx.step0, nx.seq_len, pg_cur);  // in flight while this run is finalised
+      }
       if (trace && threadIdx.x == 0) {
         if (last) trace[4] = clock64();
         trace[7] += 1;
@@ -1274,7 +1333,7 @@ int mixed_decode_ctas(const b200attn_attention_params& a, int grid) {
   // for this kernel) the rows' share of the step's time is t_rows / (t_rows + t_prompts).
   const double rows = a.num_seqs > 1 ? a.num_seqs - 1 : 0, multi = a.num_tokens - a.num_seqs + 1;
   if (rows <= 0 || multi <= 0) return grid;
-  const double esz = a.kv_dtype == B200ATTN_FP8_E4M3 ? 1.0 : 2.0;
+  const double esz = dtype_bytes(a.kv_dtype) == 1 ? 1.0 : 2.0;
   // (x 1.15: measured best on C3 - 32 CTAs where the plain ratio gives 29)
   const double ratio = 1.15 * rows / multi * (a.num_kv_heads * 2.0 * esz * 185.0) / (4.0 * a.num_q_heads);
   int k = (int)(grid * ratio / (1.0 + ratio) + 0.5);
@@ -1289,7 +1348,7 @@ int decode_geometry(const b200attn_attention_params& a, DecodeGeom* G) {
   const Tuning& tn = tuning();
   const DeviceInfo& dev = device_info();
   const int group = a.num_q_heads / a.num_kv_heads;
-  G->D = a.head_size, G->fp8 = a.kv_dtype == B200ATTN_FP8_E4M3 ? 1 : 0;
+  G->D = a.head_size, G->fp8 = dtype_bytes(a.kv_dtype) == 1 ? 1 : 0;  // one-byte cache elements (e4m3 or int8)
   G->nt = group > 8 ? 2 : 1;
   G->nw = a.head_size == 256 ? 4 : 8;
   // fp8: two 16-token sub-tiles per warp and step (a stage of 8 x 32 tokens is the size a bf16
@@ -1353,8 +1412,9 @@ uint64_t decode_plan_key(const b200attn_attention_params& a, const DecodeGeom& G
   return h | 1ull;  // never 0: 0 means "no plan"
 }
 
-template <int D, bool KV_FP8, bool MMA_BF16, bool Q_BF16, int NT, int NW, int TT>
+template <int D, int KVQ, bool MMA_BF16, bool Q_BF16, int NT, int NW, int TT>
 int launch_variant(const b200attn_attention_params& a, const DecodeGeom& G, DecodeParams& P, cudaStream_t stream) {
+  constexpr bool KV_FP8 = KVQ != 0;  // one-byte cache elements
   constexpr int ESZ = KV_FP8 ? 1 : 2;
   constexpr int NDC = D * ESZ / 128;
   constexpr int KV_STAGE_BYTES = NW * TT * D * ESZ;
@@ -1396,7 +1456,7 @@ int launch_variant(const b200attn_attention_params& a, const DecodeGeom& G, Deco
                    a.vc_slot_stride, a.vc_head_stride, P.box_slots, box_heads, box_dc);
   if (rc) return rc;
 
-  auto kern = attn_decode_kernel<D, KV_FP8, MMA_BF16, Q_BF16, NT, NW, TT>;
+  auto kern = attn_decode_kernel<D, KVQ, MMA_BF16, Q_BF16, NT, NW, TT>;
   if (int rc2 = ensure_dynamic_smem(reinterpret_cast<const void*>(kern), dev.max_smem_optin, "decode")) return rc2;
   // Programmatic dependent launch: lets this grid's launch and prologue overlap the kernel in front of it
   // (the cache write, the plan kernel or the previous decode launch - each releases its dependents early;
@@ -1415,18 +1475,25 @@ int launch_variant(const b200attn_attention_params& a, const DecodeGeom& G, Deco
 template <int D, int NT, int NW>
 int dispatch_types(const b200attn_attention_params& a, const DecodeGeom& G, DecodeParams& P, cudaStream_t stream) {
   const bool qbf = a.q_dtype == B200ATTN_BF16;
-  if (a.kv_dtype == B200ATTN_FP8_E4M3) {
+  if (dtype_bytes(a.kv_dtype) == 1) {
     if constexpr (D >= 128) {
       constexpr int TT = (D == 128 && NT == 1) ? 32 : 16;  // decode_geometry()
-      return qbf ? launch_variant<D, true, false, true, NT, NW, TT>(a, G, P, stream)
-                 : launch_variant<D, true, false, false, NT, NW, TT>(a, G, P, stream);
+      if (per_token_head(a)) {
+        if (a.kv_dtype == B200ATTN_INT8)
+          return qbf ? launch_variant<D, 3, false, true, NT, NW, TT>(a, G, P, stream)
+                     : launch_variant<D, 3, false, false, NT, NW, TT>(a, G, P, stream);
+        return qbf ? launch_variant<D, 2, false, true, NT, NW, TT>(a, G, P, stream)
+                   : launch_variant<D, 2, false, false, NT, NW, TT>(a, G, P, stream);
+      }
+      return qbf ? launch_variant<D, 1, false, true, NT, NW, TT>(a, G, P, stream)
+                 : launch_variant<D, 1, false, false, NT, NW, TT>(a, G, P, stream);
     } else {
       set_error("decode: fp8 KV needs head_size >= 128");
       return B200ATTN_E_UNSUPPORTED;
     }
   }
-  return qbf ? launch_variant<D, false, true, true, NT, NW, 16>(a, G, P, stream)
-             : launch_variant<D, false, false, false, NT, NW, 16>(a, G, P, stream);
+  return qbf ? launch_variant<D, 0, true, true, NT, NW, 16>(a, G, P, stream)
+             : launch_variant<D, 0, false, false, NT, NW, 16>(a, G, P, stream);
 }
 
 int launch_plan_kernel(const b200attn_attention_params& a, const DecodeGeom& G, bool only_q1, void* plan, cudaStream_t stream) {
@@ -1471,14 +1538,15 @@ bool decode_supported(const b200attn_attention_params& p, const char** why, bool
   auto no = [&](const char* w) { if (why) *why = w; return false; };
   if (p.max_seqlen_q != 1 && !mixed_batch) return no("max_seqlen_q != 1");
   if (p.q_dtype != B200ATTN_BF16 && p.q_dtype != B200ATTN_F16) return no("query dtype must be bf16/f16");
-  if (p.kv_dtype != p.q_dtype && p.kv_dtype != B200ATTN_FP8_E4M3) return no("kv dtype");
+  const bool kv8 = dtype_bytes(p.kv_dtype) == 1;  // e4m3, or (with per-token-head scales) int8
+  if (p.kv_dtype != p.q_dtype && !kv8) return no("kv dtype");
   if (p.head_size != 64 && p.head_size != 128 && p.head_size != 256) return no("head_size not in {64,128,256}");
-  if (p.kv_dtype == B200ATTN_FP8_E4M3 && p.head_size < 128) return no("fp8 KV needs head_size >= 128");
+  if (kv8 && p.head_size < 128) return no("fp8 / int8 KV needs head_size >= 128");
   if (p.num_kv_heads <= 0 || p.num_q_heads % p.num_kv_heads) return no("heads");
   const int g = p.num_q_heads / p.num_kv_heads;
   if (g > 16 || (g > 8 && p.head_size == 256)) return no("GQA group too large for the decode kernel");
   if (!pow2(p.block_size) || p.block_size < 16 || p.block_size > 256) return no("block_size not a power of two in [16,256]");
-  const int esz = p.kv_dtype == B200ATTN_FP8_E4M3 ? 1 : 2;
+  const int esz = kv8 ? 1 : 2;
   auto m16 = [&](int64_t s) { return (s * esz) % 16 == 0; };
   if (!m16(p.kc_block_stride) || !m16(p.kc_slot_stride) || !m16(p.kc_head_stride) || !m16(p.vc_block_stride) ||
       !m16(p.vc_slot_stride) || !m16(p.vc_head_stride))

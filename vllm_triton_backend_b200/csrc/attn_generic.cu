@@ -9,6 +9,8 @@
 // context mask (:460), sliding window (:474-479), ALiBi (:481-482), online
 // softmax with the all-masked guard (:486-492), P rounded to V's dtype before
 // PV (:508), fp8 K/V dequantised as round_to_q_dtype(float(x) * scale) (:438).
+// Per-(token, head) scales (b200attn.h k_scale_cache; upstream KVQuantMode 2 / 3): K and V are used as stored, the
+// key's scale multiplies the softmax scale and the value's multiplies P before its rounding.
 #include "common.cuh"
 
 namespace b200attn {
@@ -58,6 +60,7 @@ __global__ void __launch_bounds__(128) attn_generic_kernel(b200attn_attention_pa
   const KVT* vc = static_cast<const KVT*>(p.v_cache);
   const int32_t* bt = p.block_tables + (int64_t)b * p.bt_stride0;
   constexpr bool kFp8 = sizeof(KVT) == 1;
+  const bool pth = kFp8 && p.k_scale_cache != nullptr;
 
   float acc[kMaxDPerLane];
 #pragma unroll
@@ -69,18 +72,26 @@ __global__ void __launch_bounds__(128) attn_generic_kernel(b200attn_attention_pa
     const bool valid = pos < limit && pos >= first;
     float s = -INFINITY;
     int64_t voff = 0;
+    float vs_tok = 1.f;
     if (valid) {
       const int64_t page = bt[pos / p.block_size];
       const int slot = pos % p.block_size;
+      float ks_tok = 1.f;
+      if (pth) {
+        ks_tok = p.k_scale_cache[page * p.ks_block_stride + (int64_t)slot * p.ks_slot_stride + (int64_t)kvh * p.ks_head_stride];
+        vs_tok = p.v_scale_cache[page * p.vs_block_stride + (int64_t)slot * p.vs_slot_stride + (int64_t)kvh * p.vs_head_stride];
+      }
       const KVT* krow = kc + page * p.kc_block_stride + (int64_t)slot * p.kc_slot_stride + (int64_t)kvh * p.kc_head_stride;
       voff = page * p.vc_block_stride + (int64_t)slot * p.vc_slot_stride + (int64_t)kvh * p.vc_head_stride;
       float dot = 0.f;
       for (int d = 0; d < D; ++d) {
         float kx = to_float<KVT>(krow[d]);
-        if constexpr (kFp8) kx = to_float<QT>(from_float<QT>(kx * k_scale));
+        if constexpr (kFp8) {
+          if (!pth) kx = to_float<QT>(from_float<QT>(kx * k_scale));
+        }
         dot = fmaf(qs[d], kx, dot);
       }
-      s = dot * p.softmax_scale;
+      s = pth ? dot * (p.softmax_scale * ks_tok) : dot * p.softmax_scale;
       if (p.softcap > 0.f) s = softcap_fn(s, p.softcap, inv_cap);
       if (p.alibi_slopes) s += slope * (float)(pos - ctx);
       if (p.qq_bias) {  // bias between this step's query tokens (upstream load_qq_bias_tile)
@@ -94,7 +105,7 @@ __global__ void __launch_bounds__(128) attn_generic_kernel(b200attn_attention_pa
     const float alpha = __expf(m - m_use);  // m == -inf -> 0
     l = l * alpha + warp_sum(pr);
     m = m_new;
-    pr = to_float<QT>(from_float<QT>(pr));  // P is cast to V's (= Q's) dtype before PV
+    pr = to_float<QT>(from_float<QT>(pr * vs_tok));  // P (times the value's own scale) is cast to V's (= Q's) dtype before PV
 #pragma unroll
     for (int i = 0; i < kMaxDPerLane; ++i) acc[i] *= alpha;
     const unsigned live = __ballot_sync(0xffffffffu, valid);
@@ -108,7 +119,9 @@ __global__ void __launch_bounds__(128) attn_generic_kernel(b200attn_attention_pa
         const int d = lane + 32 * i;
         if (d < D) {
           float vx = to_float<KVT>(vrow[d]);
-          if constexpr (kFp8) vx = to_float<QT>(from_float<QT>(vx * v_scale));
+          if constexpr (kFp8) {
+            if (!pth) vx = to_float<QT>(from_float<QT>(vx * v_scale));
+          }
           acc[i] = fmaf(pj, vx, acc[i]);
         }
       }
@@ -146,6 +159,8 @@ int dispatch_kv(const b200attn_attention_params& p, cudaStream_t stream) {
   const size_t smem = 4 * p.head_size * sizeof(float);
   if (p.kv_dtype == B200ATTN_FP8_E4M3) {
     attn_generic_kernel<QT, __nv_fp8_e4m3><<<grid, 128, smem, stream>>>(p);
+  } else if (p.kv_dtype == B200ATTN_INT8) {
+    attn_generic_kernel<QT, int8_t><<<grid, 128, smem, stream>>>(p);
   } else if (p.kv_dtype == p.q_dtype) {
     attn_generic_kernel<QT, QT><<<grid, 128, smem, stream>>>(p);
   } else {

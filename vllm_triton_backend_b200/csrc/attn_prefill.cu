@@ -50,6 +50,8 @@ attn_prefill_kernel(const b200attn_attention_params p, const int block_q, const 
   uint8_t* sQ = smem;                   // [BM][ROWB]
   uint8_t* sK = sQ + BM * ROWB;         // [2][BN][ROWB]
   uint8_t* sV = sK + 2 * TILE_B;        // [2][BN][ROWB]
+  float* sKs = reinterpret_cast<float*>(sV + 2 * TILE_B);  // [2][BN] per-(token, head) key scales (pth only)
+  float* sVs = sKs + 2 * BN;                               // [2][BN] value scales
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int gid = lane >> 2, t4 = lane & 3;
@@ -88,8 +90,12 @@ attn_prefill_kernel(const b200attn_attention_params p, const int block_q, const 
   const int n_tiles = (kv_limit + BN - 1) / BN - tile0;
 
   const int32_t* bt = p.block_tables + (int64_t)b * p.bt_stride0;
-  const float k_scale = (KV_FP8 && p.k_scale) ? *p.k_scale : 1.0f;
-  const float v_scale = (KV_FP8 && p.v_scale) ? *p.v_scale : 1.0f;
+  // per-(token, head) scales (b200attn.h k_scale_cache; general-logits variant only): K and V are used as stored,
+  // every key's own scale multiplies its logit and every value's own scale multiplies P before the rounding
+  const bool pth = KV_FP8 && !kPlain && p.k_scale_cache != nullptr;
+  const bool kv_i8 = KV_FP8 && p.kv_dtype == B200ATTN_INT8;
+  const float k_scale = (KV_FP8 && !pth && p.k_scale) ? *p.k_scale : 1.0f;
+  const float v_scale = (KV_FP8 && !pth && p.v_scale) ? *p.v_scale : 1.0f;
   const bool has_cap = p.softcap > 0.f;
   const float inv_cap = has_cap ? 1.f / p.softcap : 0.f;
   const float qk_scale = p.softmax_scale * k_scale;
@@ -159,13 +165,22 @@ attn_prefill_kernel(const b200attn_attention_params p, const int block_q, const 
         }
         const uint32_t* kw = reinterpret_cast<const uint32_t*>(&kraw);
         const uint32_t* vw = reinterpret_cast<const uint32_t*>(&vraw);
+        if (pth && ld_c == 0) {  // one thread per row also brings the row's two scales
+          float kq = 1.f, vq = 1.f;
+          if (ok) {
+            kq = p.k_scale_cache[(int64_t)page * p.ks_block_stride + (int64_t)slot * p.ks_slot_stride + (int64_t)kvh * p.ks_head_stride];
+            vq = p.v_scale_cache[(int64_t)page * p.vs_block_stride + (int64_t)slot * p.vs_slot_stride + (int64_t)kvh * p.vs_head_stride];
+          }
+          sKs[buf * BN + r] = kq, sVs[buf * BN + r] = vq;
+        }
+        auto cv = [&](uint32_t x) { return kv_i8 ? s8x2_to_f16x2((uint16_t)x) : e4m3x2_to_f16x2((uint16_t)x); };
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
           int4 ko, vo;
-          ko.x = e4m3x2_to_f16x2((uint16_t)(kw[2 * h] & 0xffff)), ko.y = e4m3x2_to_f16x2((uint16_t)(kw[2 * h] >> 16));
-          ko.z = e4m3x2_to_f16x2((uint16_t)(kw[2 * h + 1] & 0xffff)), ko.w = e4m3x2_to_f16x2((uint16_t)(kw[2 * h + 1] >> 16));
-          vo.x = e4m3x2_to_f16x2((uint16_t)(vw[2 * h] & 0xffff)), vo.y = e4m3x2_to_f16x2((uint16_t)(vw[2 * h] >> 16));
-          vo.z = e4m3x2_to_f16x2((uint16_t)(vw[2 * h + 1] & 0xffff)), vo.w = e4m3x2_to_f16x2((uint16_t)(vw[2 * h + 1] >> 16));
+          ko.x = cv(kw[2 * h] & 0xffff), ko.y = cv(kw[2 * h] >> 16);
+          ko.z = cv(kw[2 * h + 1] & 0xffff), ko.w = cv(kw[2 * h + 1] >> 16);
+          vo.x = cv(vw[2 * h] & 0xffff), vo.y = cv(vw[2 * h] >> 16);
+          vo.z = cv(vw[2 * h + 1] & 0xffff), vo.w = cv(vw[2 * h + 1] >> 16);
           *reinterpret_cast<int4*>(dK + swz_off<ROWB>(r, 2 * ld_c + h)) = ko;
           *reinterpret_cast<int4*>(dV + swz_off<ROWB>(r, 2 * ld_c + h)) = vo;
         }
@@ -279,7 +294,8 @@ attn_prefill_kernel(const b200attn_attention_params p, const int block_q, const 
         for (int nt = 0; nt < BN / 8; ++nt) {
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
-            float x = has_cap ? cap_log2 * tanh_approx(sacc[nt][i] * pre) : sacc[nt][i] * scale_log2;
+            const float kq = pth ? sKs[buf * BN + nt * 8 + 2 * t4 + (i & 1)] : 1.f;  // upstream: dot * (scale * k_scale[key])
+            float x = has_cap ? cap_log2 * tanh_approx(sacc[nt][i] * (pre * kq)) : sacc[nt][i] * (scale_log2 * kq);
             if (p.alibi_slopes) x = fmaf(row_slope[i >> 1] * kLog2e, (float)(n0 + nt * 8 + 2 * t4 + (i & 1) - ctx), x);
             if (p.qq_bias) {
               // bias between this step's own query tokens (upstream qq_bias, triton_unified_attention.py:301-307 of
@@ -336,6 +352,12 @@ attn_prefill_kernel(const b200attn_attention_params p, const int block_q, const 
           p2 = ex2f(sacc[nt][2] - mu[1]), p3 = ex2f(sacc[nt][3] - mu[1]);
         }
         ls[0] += p0 + p1, ls[1] += p2 + p3;
+        if constexpr (!kPlain) {
+          if (pth) {  // upstream: (P * v_scale[key]).to(V.dtype); the exp-sum takes P itself
+            const float v0 = sVs[buf * BN + nt * 8 + 2 * t4], v1 = sVs[buf * BN + nt * 8 + 2 * t4 + 1];
+            p0 *= v0, p1 *= v1, p2 *= v0, p3 *= v1;
+          }
+        }
         // C fragments of n-tiles (2j, 2j+1) are the A fragment of k16 step j
         pa[nt >> 1][(nt & 1) * 2 + 0] = pack2<MMA_BF16>(p0, p1);
         pa[nt >> 1][(nt & 1) * 2 + 1] = pack2<MMA_BF16>(p2, p3);
@@ -405,7 +427,7 @@ template <int D, bool MMA_BF16, bool Q_BF16, bool KV_FP8, bool kPlain>
 int launch_variant(const b200attn_attention_params& a, cudaStream_t stream, QLenRange range, const int32_t* skip_staged) {
   const int group = a.num_q_heads / a.num_kv_heads;
   const int block_q = BM / group;
-  const int smem = BM * D * 2 + 4 * BN * D * 2;
+  const int smem = BM * D * 2 + 4 * BN * D * 2 + (KV_FP8 && !kPlain ? 4 * BN * 4 : 0);  // + the tiles' scale rows
   auto kern = attn_prefill_kernel<D, MMA_BF16, Q_BF16, KV_FP8, kPlain>;
   int bs_shift = -1;
   if ((a.block_size & (a.block_size - 1)) == 0)
@@ -429,7 +451,7 @@ int launch_variant(const b200attn_attention_params& a, cudaStream_t stream, QLen
 template <int D, bool kPlain>
 int dispatch_types(const b200attn_attention_params& a, cudaStream_t stream, QLenRange range, const int32_t* skip) {
   const bool qbf = a.q_dtype == B200ATTN_BF16;
-  if (a.kv_dtype == B200ATTN_FP8_E4M3)
+  if (dtype_bytes(a.kv_dtype) == 1)  // e4m3, or int8 with per-(token, head) scales
     return qbf ? launch_variant<D, false, true, true, kPlain>(a, stream, range, skip)
                : launch_variant<D, false, false, true, kPlain>(a, stream, range, skip);
   return qbf ? launch_variant<D, true, true, false, kPlain>(a, stream, range, skip)
@@ -441,11 +463,12 @@ int dispatch_types(const b200attn_attention_params& a, cudaStream_t stream, QLen
 bool prefill_supported(const b200attn_attention_params& p, const char** why) {
   auto no = [&](const char* w) { if (why) *why = w; return false; };
   if (p.q_dtype != B200ATTN_BF16 && p.q_dtype != B200ATTN_F16) return no("query dtype must be bf16/f16");
-  if (p.kv_dtype != p.q_dtype && p.kv_dtype != B200ATTN_FP8_E4M3) return no("kv dtype");
+  const bool kv8 = dtype_bytes(p.kv_dtype) == 1;
+  if (p.kv_dtype != p.q_dtype && !kv8) return no("kv dtype");
   if (p.head_size != 64 && p.head_size != 128 && p.head_size != 256) return no("head_size not in {64,128,256}");
   if (p.num_kv_heads <= 0 || p.num_q_heads % p.num_kv_heads) return no("heads");
   if (p.num_q_heads / p.num_kv_heads > BM) return no("GQA group > 64");
-  const int esz = p.kv_dtype == B200ATTN_FP8_E4M3 ? 1 : 2;
+  const int esz = kv8 ? 1 : 2;
   auto m16 = [&](int64_t s) { return (s * esz) % 16 == 0; };
   if (!m16(p.kc_block_stride) || !m16(p.kc_slot_stride) || !m16(p.kc_head_stride) || !m16(p.vc_block_stride) ||
       !m16(p.vc_slot_stride) || !m16(p.vc_head_stride))
@@ -467,7 +490,7 @@ int launch_attn_prefill(const b200attn_attention_params& a, cudaStream_t stream,
     return B200ATTN_E_UNSUPPORTED;
   }
   // the scale of an FP8 cache is a device scalar: it is taken as positive (a quantisation scale always is)
-  const bool plain = a.softcap == 0.f && !a.alibi_slopes && !a.qq_bias && a.softmax_scale > 0.f;
+  const bool plain = a.softcap == 0.f && !a.alibi_slopes && !a.qq_bias && a.softmax_scale > 0.f && !per_token_head(a);
   switch (a.head_size) {
     case 64: return plain ? dispatch_types<64, true>(a, stream, range, skip_staged) : dispatch_types<64, false>(a, stream, range, skip_staged);
     case 128: return plain ? dispatch_types<128, true>(a, stream, range, skip_staged) : dispatch_types<128, false>(a, stream, range, skip_staged);

@@ -141,8 +141,17 @@ int validate_attention(const b200attn_attention_params& p) {
     set_error("unified_attention: query dtype %d not supported (bf16, f16, f32)", p.q_dtype);
     return B200ATTN_E_BAD_DTYPE;
   }
-  if (p.kv_dtype != p.q_dtype && p.kv_dtype != B200ATTN_FP8_E4M3) {
-    set_error("unified_attention: kv dtype %d must equal the query dtype or be fp8_e4m3", p.kv_dtype);
+  if ((p.k_scale_cache == nullptr) != (p.v_scale_cache == nullptr)) {
+    set_error("unified_attention: k_scale_cache and v_scale_cache come together");
+    return B200ATTN_E_NULL;
+  }
+  if (per_token_head(p)) {
+    if (p.kv_dtype != B200ATTN_FP8_E4M3 && p.kv_dtype != B200ATTN_INT8) {
+      set_error("unified_attention: per-(token, head) scales need an fp8_e4m3 or int8 cache (kv dtype %d)", p.kv_dtype);
+      return B200ATTN_E_BAD_DTYPE;
+    }
+  } else if (p.kv_dtype != p.q_dtype && p.kv_dtype != B200ATTN_FP8_E4M3) {
+    set_error("unified_attention: kv dtype %d must equal the query dtype or be fp8_e4m3 (int8: with scale caches)", p.kv_dtype);
     return B200ATTN_E_BAD_DTYPE;
   }
   if (p.head_size > 256) {
@@ -196,6 +205,29 @@ int b200attn_reshape_and_cache_flash(const void* key, const void* value, void* k
                             block_size, key_stride0, value_stride0, kc_block_stride, kc_slot_stride, kc_head_stride,
                             vc_block_stride, vc_slot_stride, vc_head_stride, src_dtype, kv_dtype, k_scale, v_scale,
                             reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b200attn_reshape_and_cache_flash_per_token_head(
+    const void* key, const void* value, void* k_cache, void* v_cache, float* k_scale_cache, float* v_scale_cache,
+    const int64_t* slot_mapping, int64_t num_tokens, int32_t num_kv_heads, int32_t head_size, int32_t block_size,
+    int64_t key_stride0, int64_t key_stride1, int64_t value_stride0, int64_t value_stride1, int64_t kc_block_stride,
+    int64_t kc_slot_stride, int64_t kc_head_stride, int64_t vc_block_stride, int64_t vc_slot_stride, int64_t vc_head_stride,
+    int64_t ks_block_stride, int64_t ks_slot_stride, int64_t ks_head_stride, int64_t vs_block_stride, int64_t vs_slot_stride,
+    int64_t vs_head_stride, int32_t src_dtype, int32_t kv_dtype, b200attn_stream_t stream) {
+  PerTokenHeadWriteArgs a;
+  a.src[0] = key, a.src[1] = value, a.dst[0] = k_cache, a.dst[1] = v_cache;
+  a.scales[0] = k_scale_cache, a.scales[1] = v_scale_cache;
+  a.slot_mapping = slot_mapping, a.num_tokens = num_tokens;
+  a.src_stride0[0] = key_stride0, a.src_stride0[1] = value_stride0, a.src_stride1[0] = key_stride1, a.src_stride1[1] = value_stride1;
+  a.block_stride[0] = kc_block_stride, a.block_stride[1] = vc_block_stride;
+  a.slot_stride[0] = kc_slot_stride, a.slot_stride[1] = vc_slot_stride;
+  a.head_stride[0] = kc_head_stride, a.head_stride[1] = vc_head_stride;
+  a.s_block_stride[0] = ks_block_stride, a.s_block_stride[1] = vs_block_stride;
+  a.s_slot_stride[0] = ks_slot_stride, a.s_slot_stride[1] = vs_slot_stride;
+  a.s_head_stride[0] = ks_head_stride, a.s_head_stride[1] = vs_head_stride;
+  a.num_kv_heads = num_kv_heads, a.head_size = head_size, a.block_size = block_size;
+  a.src_dtype = src_dtype, a.kv_dtype = kv_dtype;
+  return launch_cache_write_per_token_head(a, reinterpret_cast<cudaStream_t>(stream));
 }
 
 int b200attn_rope_and_cache_flash(const b200attn_rope_cache_params* p, b200attn_stream_t stream) {
@@ -318,7 +350,7 @@ int b200attn_unified_attention(const b200attn_attention_params* pp, b200attn_str
     if (dec_due) return launch_attn_decode(p, stream, /*only_single_token_seqs=*/true);
     return (int)B200ATTN_OK;
   };
-  if (p.kv_dtype == B200ATTN_FP8_E4M3 && !(g_tuning.reserved & 256)) {
+  if (dtype_bytes(p.kv_dtype) == 1 && !(g_tuning.reserved & 256)) {
     // FP8 cache: the sequences with long queries are dequantised once into the staging pool (the part of
     // the workspace past the decode region) and run the tcgen05 kernel on it; what does not fit the pool,
     // short extends and decode rows keep reading the FP8 cache.  (tuning().reserved bit 8 switches it off.)

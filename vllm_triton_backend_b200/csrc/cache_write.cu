@@ -324,6 +324,132 @@ int launch_cache_write(const void* key, const void* value, void* k_cache, void* 
   return check_launch("reshape_and_cache_flash");
 }
 
+// ---- K1 with dynamic per-(token, head) quantisation -------------------------------------------------------------
+// One warp per (token, kv head, K|V) row: the row is read once into registers (lane l holds elements 4l .. 4l+3 of
+// every 128-element group), the absmax goes through five shuffles, and the row leaves as 4-byte stores of e4m3 or
+// int8 codes plus one fp32 scale.  Arithmetic as the upstream Triton kernel states it (vLLM 0.22
+// vllm/v1/attention/ops/triton_reshape_and_cache_flash.py:186-236; oracle/cache_write.py per_token_head_quant_ref):
+// scale = max(absmax / QMAX, 1e-6), code = Q(clamp(x * (1 / scale), QMIN, QMAX)) with IEEE division, e4m3 by
+// round-to-nearest-even, int8 by truncation toward zero.
+template <typename SrcT, bool kInt8, bool kVec>
+__global__ void __launch_bounds__(256) cache_quant_per_token_head_kernel(const PerTokenHeadWriteArgs a) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);  // (token, head, K|V)
+  const int64_t rows = a.num_tokens * a.num_kv_heads * 2;
+  if (row >= rows) return;
+  const int w = (int)(row & 1);
+  const int h = (int)((row >> 1) % a.num_kv_heads);
+  const int64_t t = (row >> 1) / a.num_kv_heads;
+  const int64_t slot = a.slot_mapping[t];
+  if (slot < 0) return;  // padding token (:171-173)
+  const int64_t blk = slot / a.block_size, off = slot % a.block_size;
+  const SrcT* src = static_cast<const SrcT*>(a.src[w]) + t * a.src_stride0[w] + (int64_t)h * a.src_stride1[w];
+  uint8_t* dst = static_cast<uint8_t*>(a.dst[w]) + blk * a.block_stride[w] + off * a.slot_stride[w] + (int64_t)h * a.head_stride[w];
+  const int D = a.head_size;
+  constexpr float kQMax = kInt8 ? 127.f : 448.f, kQMin = kInt8 ? -128.f : -448.f;
+  constexpr int kGroups = 2;  // head_size <= 256
+  float x[kGroups][4];
+  float amax = 0.f;
+#pragma unroll
+  for (int g = 0; g < kGroups; ++g) {
+    const int d0 = kVec ? (g * 32 + lane) * 4 : 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int d = kVec ? d0 + i : (g * 4 + i) * 32 + lane;
+      x[g][i] = 0.f;
+      if constexpr (!kVec) {
+        if (d < D) x[g][i] = to_float<SrcT>(src[d]);
+      }
+    }
+    if constexpr (kVec) {
+      if (d0 < D) {
+        if constexpr (sizeof(SrcT) == 2) {
+          const uint2 raw = *reinterpret_cast<const uint2*>(src + d0);
+          const SrcT* e = reinterpret_cast<const SrcT*>(&raw);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) x[g][i] = to_float<SrcT>(e[i]);
+        } else {
+          const float4 raw = *reinterpret_cast<const float4*>(src + d0);
+          x[g][0] = raw.x, x[g][1] = raw.y, x[g][2] = raw.z, x[g][3] = raw.w;
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) amax = fmaxf(amax, fabsf(x[g][i]));
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+  const float scale = fmaxf(__fdiv_rn(amax, kQMax), 1e-6f);
+  const float inv = __fdiv_rn(1.0f, scale);
+  if (lane == 0) a.scales[w][blk * a.s_block_stride[w] + off * a.s_slot_stride[w] + (int64_t)h * a.s_head_stride[w]] = scale;
+  auto code = [&](float v) -> uint32_t {
+    const float y = fminf(fmaxf(v * inv, kQMin), kQMax);
+    if constexpr (kInt8) return (uint32_t)(uint8_t)(int8_t)__float2int_rz(y);
+    else return (uint32_t)fp8_out(y);
+  };
+#pragma unroll
+  for (int g = 0; g < kGroups; ++g) {
+    if constexpr (kVec) {
+      const int d0 = (g * 32 + lane) * 4;
+      if (d0 < D)
+        *reinterpret_cast<uint32_t*>(dst + d0) = code(x[g][0]) | (code(x[g][1]) << 8) | (code(x[g][2]) << 16) | (code(x[g][3]) << 24);
+    } else {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int d = (g * 4 + i) * 32 + lane;
+        if (d < D) dst[d] = (uint8_t)code(x[g][i]);
+      }
+    }
+  }
+}
+
+template <typename SrcT>
+static void launch_pth(const PerTokenHeadWriteArgs& a, bool vec, cudaStream_t stream) {
+  const int64_t rows = a.num_tokens * a.num_kv_heads * 2;
+  const dim3 grid((unsigned)((rows + 7) / 8));
+  const bool pdl = !(tuning().reserved & 512);
+  const bool i8 = a.kv_dtype == B200ATTN_INT8;
+  if (i8 && vec) launch_pdl(cache_quant_per_token_head_kernel<SrcT, true, true>, grid, 256, 0, stream, pdl, a);
+  else if (i8) launch_pdl(cache_quant_per_token_head_kernel<SrcT, true, false>, grid, 256, 0, stream, pdl, a);
+  else if (vec) launch_pdl(cache_quant_per_token_head_kernel<SrcT, false, true>, grid, 256, 0, stream, pdl, a);
+  else launch_pdl(cache_quant_per_token_head_kernel<SrcT, false, false>, grid, 256, 0, stream, pdl, a);
+}
+
+int launch_cache_write_per_token_head(const PerTokenHeadWriteArgs& a, cudaStream_t stream) {
+  if (a.num_tokens == 0) return B200ATTN_OK;
+  if (!a.src[0] || !a.src[1] || !a.dst[0] || !a.dst[1] || !a.scales[0] || !a.scales[1] || !a.slot_mapping) {
+    set_error("reshape_and_cache_flash_per_token_head: null pointer argument");
+    return B200ATTN_E_NULL;
+  }
+  if (a.num_kv_heads <= 0 || a.head_size <= 0 || a.head_size > 256 || a.block_size <= 0 || a.num_tokens < 0) {
+    set_error("reshape_and_cache_flash_per_token_head: bad shape (Hkv=%d D=%d bs=%d; head_size <= 256)", a.num_kv_heads,
+              a.head_size, a.block_size);
+    return B200ATTN_E_BAD_SHAPE;
+  }
+  if (a.kv_dtype != B200ATTN_FP8_E4M3 && a.kv_dtype != B200ATTN_INT8) {
+    set_error("reshape_and_cache_flash_per_token_head: cache dtype %d must be fp8_e4m3 or int8", a.kv_dtype);
+    return B200ATTN_E_BAD_DTYPE;
+  }
+  const int sb = dtype_bytes(a.src_dtype);
+  if (a.src_dtype != B200ATTN_BF16 && a.src_dtype != B200ATTN_F16 && a.src_dtype != B200ATTN_F32) {
+    set_error("reshape_and_cache_flash_per_token_head: unsupported source dtype %d", a.src_dtype);
+    return B200ATTN_E_BAD_DTYPE;
+  }
+  bool vec = a.head_size % 4 == 0;
+  for (int w = 0; w < 2; ++w) {
+    vec = vec && (reinterpret_cast<uintptr_t>(a.src[w]) % (4 * sb) == 0) && a.src_stride0[w] % 4 == 0 && a.src_stride1[w] % 4 == 0 &&
+          (reinterpret_cast<uintptr_t>(a.dst[w]) % 4 == 0) && a.block_stride[w] % 4 == 0 && a.slot_stride[w] % 4 == 0 &&
+          a.head_stride[w] % 4 == 0;
+  }
+  if (a.src_dtype == B200ATTN_BF16) launch_pth<__nv_bfloat16>(a, vec, stream);
+  else if (a.src_dtype == B200ATTN_F16) launch_pth<__half>(a, vec, stream);
+  else launch_pth<float>(a, vec, stream);
+  note_launch(vec ? "cache_quant_per_token_head_vec" : "cache_quant_per_token_head");
+  return check_launch("reshape_and_cache_flash_per_token_head");
+}
+
 int launch_scaled_fp8_quant(void* out, const void* in, int64_t rows, int64_t row_elems, int64_t in_row_stride,
                             int src_dtype, const float* scale, cudaStream_t stream) {
   if (rows == 0 || row_elems == 0) return B200ATTN_OK;

@@ -91,6 +91,18 @@ int launch_cache_write(const void* key, const void* value, void* k_cache, void* 
                        int64_t value_stride0, int64_t kc_block_stride, int64_t kc_slot_stride, int64_t kc_head_stride,
                        int64_t vc_block_stride, int64_t vc_slot_stride, int64_t vc_head_stride, int src_dtype,
                        int kv_dtype, const float* k_scale, const float* v_scale, cudaStream_t stream);
+struct PerTokenHeadWriteArgs {
+  const void* src[2];  // key, value
+  void* dst[2];        // k_cache, v_cache
+  float* scales[2];    // k_scale_cache, v_scale_cache
+  const int64_t* slot_mapping;
+  int64_t num_tokens;
+  int64_t src_stride0[2], src_stride1[2];
+  int64_t block_stride[2], slot_stride[2], head_stride[2];
+  int64_t s_block_stride[2], s_slot_stride[2], s_head_stride[2];
+  int num_kv_heads, head_size, block_size, src_dtype, kv_dtype;
+};
+int launch_cache_write_per_token_head(const PerTokenHeadWriteArgs& a, cudaStream_t stream);
 int launch_scaled_fp8_quant(void* out, const void* in, int64_t rows, int64_t row_elems, int64_t in_row_stride,
                             int src_dtype, const float* scale, cudaStream_t stream);
 int launch_rope_cache(const b200attn_rope_cache_params& p, cudaStream_t stream);
@@ -128,12 +140,16 @@ inline void launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t sme
 }
 #endif
 
+// per-(token, head) scales (b200attn.h: k_scale_cache / v_scale_cache)
+static inline bool per_token_head(const b200attn_attention_params& p) { return p.k_scale_cache != nullptr; }
+
 static inline int dtype_bytes(int dt) {
   switch (dt) {
     case B200ATTN_BF16:
     case B200ATTN_F16: return 2;
     case B200ATTN_F32: return 4;
-    case B200ATTN_FP8_E4M3: return 1;
+    case B200ATTN_FP8_E4M3:
+    case B200ATTN_INT8: return 1;
     default: return 0;
   }
 }
@@ -151,6 +167,7 @@ template <> __device__ __forceinline__ float to_float<float>(float x) { return x
 template <> __device__ __forceinline__ float to_float<__half>(__half x) { return __half2float(x); }
 template <> __device__ __forceinline__ float to_float<__nv_bfloat16>(__nv_bfloat16 x) { return __bfloat162float(x); }
 template <> __device__ __forceinline__ float to_float<__nv_fp8_e4m3>(__nv_fp8_e4m3 x) { return float(x); }
+template <> __device__ __forceinline__ float to_float<int8_t>(int8_t x) { return (float)x; }
 
 template <typename T> __device__ __forceinline__ T from_float(float x);
 template <> __device__ __forceinline__ float from_float<float>(float x) { return x; }
@@ -339,12 +356,22 @@ template <bool kBf16> __device__ __forceinline__ uint32_t pack2(float lo, float 
   }
 }
 
+// two int8 bytes -> f16x2 (exact): 0x6400 | (b ^ 0x80) is the half 1152 + b
+__device__ __forceinline__ uint32_t s8x2_to_f16x2(uint16_t x) {
+  const uint32_t t = __byte_perm((uint32_t)x ^ 0x8080u, 0x64646464u, 0x4140);
+  const __half2 bias = __halves2half2(__ushort_as_half((unsigned short)0x6480), __ushort_as_half((unsigned short)0x6480));
+  const __half2 r = __hsub2(*reinterpret_cast<const __half2*>(&t), bias);
+  return *reinterpret_cast<const uint32_t*>(&r);
+}
+template <bool kInt8> __device__ __forceinline__ uint32_t kv8x2_to_f16x2(uint16_t x);
 // two e4m3 bytes (low 16 bits of x) -> f16x2 (exact)
 __device__ __forceinline__ uint32_t e4m3x2_to_f16x2(uint16_t x) {
   uint32_t r;
   asm volatile("cvt.rn.f16x2.e4m3x2 %0, %1;" : "=r"(r) : "h"(x));
   return r;
 }
+template <> __device__ __forceinline__ uint32_t kv8x2_to_f16x2<false>(uint16_t x) { return e4m3x2_to_f16x2(x); }
+template <> __device__ __forceinline__ uint32_t kv8x2_to_f16x2<true>(uint16_t x) { return s8x2_to_f16x2(x); }
 
 __device__ __forceinline__ void cp_async_16(uint32_t smem_addr, const void* gptr, bool pred) {
   int sz = pred ? 16 : 0;

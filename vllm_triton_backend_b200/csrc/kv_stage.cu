@@ -1,4 +1,4 @@
-// K6: FP8 KV pages -> 16-bit staging pages for the tcgen05 prefill kernel.
+// K6: FP8 (or int8) KV pages -> 16-bit staging pages for the tcgen05 prefill kernel.
 //
 // tcgen05.mma kind::f16 takes 16-bit operands from shared memory, so an FP8-e4m3 cache cannot
 // feed it directly.  For the sequences of a batch that the tcgen05 kernel takes (query length in
@@ -30,6 +30,10 @@ struct StageArgs {
   const int32_t* cu_seqlens_q;
   const float* k_scale;
   const float* v_scale;
+  const float* k_scale_cache;  // per-(token, head) scales (b200attn.h), or nullptr
+  const float* v_scale_cache;
+  int64_t ks_block_stride, ks_slot_stride, ks_head_stride, vs_block_stride, vs_slot_stride, vs_head_stride;
+  int kv_int8;
   int32_t* staged_base;
   void* k_stage;
   void* v_stage;
@@ -82,14 +86,18 @@ __global__ void __launch_bounds__(256) stage_dequant_kernel(const StageArgs a) {
     const int s = uu / per_slot, r = uu - s * per_slot, h = r / d16, c = r - h * d16;
     const uint8_t* src = is_v ? a.vc + page * a.vc_block_stride + (int64_t)s * a.vc_slot_stride + (int64_t)h * a.vc_head_stride
                               : a.kc + page * a.kc_block_stride + (int64_t)s * a.kc_slot_stride + (int64_t)h * a.kc_head_stride;
-    const int4 raw = *reinterpret_cast<const int4*>(src + c * 16);
-    const float sc = is_v ? vs : ks;
+    int4 raw = *reinterpret_cast<const int4*>(src + c * 16);
+    if (p * bs + s >= seq_len) raw = make_int4(0, 0, 0, 0);  // slots past the end were never written: stage zeros, not whatever bytes (NaN patterns) lie there
+    float sc = is_v ? vs : ks;
+    if (a.k_scale_cache && p * bs + s < seq_len)  // the row's own scale; the staged value is round_to_q_dtype(float(x) * scale) as for a per-tensor scale
+      sc = is_v ? a.v_scale_cache[page * a.vs_block_stride + (int64_t)s * a.vs_slot_stride + (int64_t)h * a.vs_head_stride]
+                : a.k_scale_cache[page * a.ks_block_stride + (int64_t)s * a.ks_slot_stride + (int64_t)h * a.ks_head_stride];
     const uint32_t w[4] = {(uint32_t)raw.x, (uint32_t)raw.y, (uint32_t)raw.z, (uint32_t)raw.w};
     uint32_t o[8];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-      const uint32_t lo_bits = e4m3x2_to_f16x2((uint16_t)(w[i] & 0xffffu));  // exact
-      const uint32_t hi_bits = e4m3x2_to_f16x2((uint16_t)(w[i] >> 16));
+      const uint32_t lo_bits = a.kv_int8 ? s8x2_to_f16x2((uint16_t)(w[i] & 0xffffu)) : e4m3x2_to_f16x2((uint16_t)(w[i] & 0xffffu));  // exact
+      const uint32_t hi_bits = a.kv_int8 ? s8x2_to_f16x2((uint16_t)(w[i] >> 16)) : e4m3x2_to_f16x2((uint16_t)(w[i] >> 16));
       const __half2 lo = *reinterpret_cast<const __half2*>(&lo_bits), hi = *reinterpret_cast<const __half2*>(&hi_bits);
       const float2 fl = __half22float2(lo), fh = __half22float2(hi);
       o[2 * i] = pack_t<T>(fl.x * sc, fl.y * sc);
@@ -136,6 +144,7 @@ b200attn_attention_params staged_params(const b200attn_attention_params& p, cons
   s.k_cache = st.k_stage, s.v_cache = st.v_stage;
   s.kv_dtype = p.q_dtype;
   s.k_scale = nullptr, s.v_scale = nullptr;
+  s.k_scale_cache = nullptr, s.v_scale_cache = nullptr;
   s.num_blocks = st.cap_pages;
   s.kc_head_stride = s.vc_head_stride = p.head_size;
   s.kc_slot_stride = s.vc_slot_stride = (int64_t)p.num_kv_heads * p.head_size;
@@ -144,7 +153,7 @@ b200attn_attention_params staged_params(const b200attn_attention_params& p, cons
 }
 
 int launch_kv_stage(const b200attn_attention_params& p, const KvStage& st, QLenRange range, cudaStream_t stream) {
-  if (p.kv_dtype != B200ATTN_FP8_E4M3 || (p.q_dtype != B200ATTN_BF16 && p.q_dtype != B200ATTN_F16) || p.head_size % 16) {
+  if (dtype_bytes(p.kv_dtype) != 1 || (p.q_dtype != B200ATTN_BF16 && p.q_dtype != B200ATTN_F16) || p.head_size % 16) {
     set_error("kv_stage: needs an fp8 cache, bf16/f16 queries and head_size %% 16 == 0");
     return B200ATTN_E_UNSUPPORTED;
   }
@@ -154,6 +163,10 @@ int launch_kv_stage(const b200attn_attention_params& p, const KvStage& st, QLenR
   a.vc_block_stride = p.vc_block_stride, a.vc_slot_stride = p.vc_slot_stride, a.vc_head_stride = p.vc_head_stride;
   a.block_tables = p.block_tables, a.bt_stride0 = p.bt_stride0, a.seq_lens = p.seq_lens, a.cu_seqlens_q = p.cu_seqlens_q;
   a.k_scale = p.k_scale, a.v_scale = p.v_scale;
+  a.k_scale_cache = p.k_scale_cache, a.v_scale_cache = p.v_scale_cache;
+  a.ks_block_stride = p.ks_block_stride, a.ks_slot_stride = p.ks_slot_stride, a.ks_head_stride = p.ks_head_stride;
+  a.vs_block_stride = p.vs_block_stride, a.vs_slot_stride = p.vs_slot_stride, a.vs_head_stride = p.vs_head_stride;
+  a.kv_int8 = p.kv_dtype == B200ATTN_INT8 ? 1 : 0;
   a.staged_base = st.staged_base, a.k_stage = st.k_stage, a.v_stage = st.v_stage;
   a.num_seqs = p.num_seqs, a.min_q_len = range.min_q_len, a.max_q_len = range.max_q_len;
   a.block_size = p.block_size, a.num_kv_heads = p.num_kv_heads, a.head_size = p.head_size, a.cap_pages = st.cap_pages;

@@ -27,11 +27,13 @@ _DTYPE = {
     torch.float32: _cabi.F32,
     torch.float8_e4m3fn: _cabi.FP8_E4M3,
     torch.uint8: _cabi.FP8_E4M3,  # vLLM allocates fp8 caches as uint8
+    torch.int8: _cabi.INT8,  # KV cache only, with per-(token, head) scale caches
 }
 
-# upstream KVQuantMode values whose scales are the per-tensor k_descale / v_descale this library takes
-# (vllm/v1/kv_cache_interface.py: NONE = 0, FP8_PER_TENSOR = 1)
+# upstream KVQuantMode (vllm/v1/kv_cache_interface.py): NONE = 0 and FP8_PER_TENSOR = 1 take the per-tensor
+# k_descale / v_descale; INT8_PER_TOKEN_HEAD = 2 and FP8_PER_TOKEN_HEAD = 3 take k_scale_cache / v_scale_cache
 _PER_TENSOR_KV_MODES = (0, 1)
+_PER_TOKEN_HEAD_KV_MODES = (2, 3)
 
 _workspaces: dict = {}
 _retired_workspaces: list = []
@@ -199,6 +201,50 @@ def reshape_and_cache_flash(
     )
 
 
+def reshape_and_cache_flash_per_token_head(
+    key: torch.Tensor,  # [>=T, Hkv, D]
+    value: torch.Tensor,
+    key_cache: torch.Tensor,  # [NB, bs, Hkv, D] float8_e4m3fn / uint8 (e4m3) or int8 view
+    value_cache: torch.Tensor,
+    k_scale_cache: torch.Tensor,  # [NB, bs, Hkv] float32 view (any strides)
+    v_scale_cache: torch.Tensor,
+    slot_mapping: torch.Tensor,  # int64 [T]
+) -> None:
+    """Cache write of kv_cache_dtype "fp8_per_token_head" / "int8_per_token_head": every (token, head) row is quantised
+    with its own scale absmax / QMAX, which goes to the scale cache (upstream
+    `triton_reshape_and_cache_flash_per_token_head_quant`, vLLM 0.22
+    vllm/v1/attention/ops/triton_reshape_and_cache_flash.py:247-320; same argument order)."""
+    _require_cuda(key, value, key_cache, value_cache, k_scale_cache, v_scale_cache, slot_mapping)
+    if slot_mapping.dtype != torch.int64:
+        raise ValueError("slot_mapping must be int64")
+    if key.dim() != 3 or key_cache.dim() != 4 or k_scale_cache.dim() != 3 or v_scale_cache.dim() != 3:
+        raise ValueError("key must be [T, Hkv, D], key_cache [NB, bs, Hkv, D] and the scale caches [NB, bs, Hkv]")
+    if key.stride(2) != 1 or value.stride(2) != 1 or key_cache.stride(3) != 1 or value_cache.stride(3) != 1:
+        raise ValueError("head_dim must be the contiguous dimension of key, value and the caches")
+    if k_scale_cache.dtype != torch.float32 or v_scale_cache.dtype != torch.float32:
+        raise ValueError("scale caches must be float32")
+    if key_cache.dtype != value_cache.dtype or key_cache.element_size() != 1:
+        raise ValueError(f"per-token-head caches are 1-byte tensors (float8_e4m3fn / uint8, or int8); got {key_cache.dtype}")
+    src_dt, kv_dt = _DTYPE.get(key.dtype), _DTYPE[key_cache.dtype]
+    if src_dt not in (_cabi.BF16, _cabi.F16, _cabi.F32) or value.dtype != key.dtype:
+        raise ValueError(f"unsupported key/value dtype {key.dtype}/{value.dtype}")
+    _, bs, hkv, d = key_cache.shape
+    if tuple(k_scale_cache.shape) != tuple(key_cache.shape[:3]) or tuple(v_scale_cache.shape) != tuple(value_cache.shape[:3]):
+        raise ValueError("scale caches must be [num_blocks, block_size, num_kv_heads] like their caches")
+    _cabi.check(
+        _cabi.load_library().b200attn_reshape_and_cache_flash_per_token_head(
+            key.data_ptr(), value.data_ptr(), key_cache.data_ptr(), value_cache.data_ptr(), k_scale_cache.data_ptr(),
+            v_scale_cache.data_ptr(), slot_mapping.data_ptr(), slot_mapping.shape[0], hkv, d, bs,
+            key.stride(0), key.stride(1), value.stride(0), value.stride(1),
+            key_cache.stride(0), key_cache.stride(1), key_cache.stride(2),
+            value_cache.stride(0), value_cache.stride(1), value_cache.stride(2),
+            k_scale_cache.stride(0), k_scale_cache.stride(1), k_scale_cache.stride(2),
+            v_scale_cache.stride(0), v_scale_cache.stride(1), v_scale_cache.stride(2),
+            src_dt, kv_dt, _stream_ptr(key),
+        )
+    )
+
+
 def scaled_fp8_quant(x: torch.Tensor, scale: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
     """Static per-tensor FP8 quantisation (`ops.scaled_fp8_quant(x, scale)`,
     reference triton_attn.py:417). x: [rows, n]."""
@@ -230,7 +276,7 @@ def _check_out(out, q_dtype, output_scale) -> None:
 def build_attention_params(
     q, k, v, out, cu_seqlens_q, max_seqlen_q, seqused_k, max_seqlen_k, softmax_scale, window_size, block_table,
     softcap, k_descale, v_descale, alibi_slopes, path, workspace, sinks=None, output_scale=None, qq_bias=None,
-    softmax_lse=None,
+    softmax_lse=None, k_scale_cache=None, v_scale_cache=None,
 ) -> AttentionParams:
     if q.dim() != 3 or k.dim() != 4 or v.dim() != 4:
         raise ValueError("q must be [T, Hq, D]; k, v must be [NB, bs, Hkv, D]")
@@ -287,7 +333,27 @@ def build_attention_params(
         p.workspace, p.workspace_bytes = workspace.data_ptr(), workspace.numel() * workspace.element_size()
     else:
         p.workspace, p.workspace_bytes = None, 0
+    _set_scale_caches(p, k, v, k_scale_cache, v_scale_cache)
     return p
+
+
+def _set_scale_caches(p: AttentionParams, k, v, k_scale_cache, v_scale_cache) -> None:
+    """Per-(token, head) scale caches (upstream `k_scale_cache` / `v_scale_cache`): [NB, bs, Hkv] float32 views."""
+    if k_scale_cache is None and v_scale_cache is None:
+        if k.dtype == torch.int8:
+            raise ValueError("an int8 kv cache needs k_scale_cache / v_scale_cache (kv_quant_mode INT8_PER_TOKEN_HEAD)")
+        return
+    if k_scale_cache is None or v_scale_cache is None:
+        raise ValueError("k_scale_cache and v_scale_cache come together")
+    if k.element_size() != 1:
+        raise ValueError("per-token-head scale caches need a 1-byte kv cache (float8_e4m3fn / uint8 or int8)")
+    for sc, c in ((k_scale_cache, k), (v_scale_cache, v)):
+        if sc.dtype != torch.float32 or not sc.is_cuda or tuple(sc.shape) != tuple(c.shape[:3]):
+            raise ValueError("scale caches must be float32 CUDA tensors [num_blocks, block_size, num_kv_heads]")
+    p.k_scale, p.v_scale = None, None  # not used in this mode (b200attn.h)
+    p.k_scale_cache, p.v_scale_cache = k_scale_cache.data_ptr(), v_scale_cache.data_ptr()
+    p.ks_block_stride, p.ks_slot_stride, p.ks_head_stride = k_scale_cache.stride()
+    p.vs_block_stride, p.vs_slot_stride, p.vs_head_stride = v_scale_cache.stride()
 
 
 def unified_attention(
@@ -330,10 +396,12 @@ def unified_attention(
     # silently computing plain causal attention.
     mm_prefix_range=None,
     use_alibi_sqrt: bool = False,
-    kv_quant_mode=None,
-    k_scale_cache=None,
-    v_scale_cache=None,
     chunk_lookback: int = -1,
+    # upstream's per-(token, head) quantised caches: kv_quant_mode INT8_PER_TOKEN_HEAD (2) / FP8_PER_TOKEN_HEAD (3)
+    # with one fp32 scale per cached (token, kv head) in k_scale_cache / v_scale_cache [NB, bs, Hkv]
+    kv_quant_mode=None,
+    k_scale_cache: Optional[torch.Tensor] = None,
+    v_scale_cache: Optional[torch.Tensor] = None,
 ) -> None:
     if mm_prefix_range is not None:
         raise NotImplementedError("b200attn: mm_prefix_range (PrefixLM bidirectional ranges) is not implemented")
@@ -342,10 +410,17 @@ def unified_attention(
     if chunk_lookback is not None and int(chunk_lookback) >= 0:
         raise NotImplementedError("b200attn: chunk_lookback (chunked attention with lookback) is not implemented; "
                                   "chunked local attention runs through vLLM's virtual batches")
-    if kv_quant_mode is not None and int(getattr(kv_quant_mode, "value", kv_quant_mode)) not in _PER_TENSOR_KV_MODES:
-        raise NotImplementedError(f"b200attn: kv_quant_mode={kv_quant_mode!r} (per-token-head scale caches) is not implemented")
-    if k_scale_cache is not None or v_scale_cache is not None:
-        raise NotImplementedError("b200attn: k_scale_cache / v_scale_cache (per-token-head KV scales) are not implemented")
+    mode = 0 if kv_quant_mode is None else int(getattr(kv_quant_mode, "value", kv_quant_mode))
+    if mode in _PER_TOKEN_HEAD_KV_MODES:
+        if k_scale_cache is None or v_scale_cache is None:
+            raise AssertionError(f"kv_quant_mode={kv_quant_mode!r} requires k_scale_cache / v_scale_cache")  # upstream :814
+        if (mode == 2) != (k.dtype == torch.int8):
+            raise ValueError(f"kv_quant_mode={kv_quant_mode!r} does not match the cache dtype {k.dtype}")
+    elif mode in _PER_TENSOR_KV_MODES:
+        if kv_quant_mode is not None and (k_scale_cache is not None or v_scale_cache is not None):
+            raise ValueError(f"scale caches passed with kv_quant_mode={kv_quant_mode!r}")
+    else:
+        raise NotImplementedError(f"b200attn: kv_quant_mode={kv_quant_mode!r} is not implemented")
     if not causal:
         raise AssertionError("Only causal attention is supported")  # reference :861
     if q_descale is not None:
@@ -380,6 +455,7 @@ def unified_attention(
     p = build_attention_params(
         q, k, v, out, cu_seqlens_q, max_seqlen_q, seqused_k, max_seqlen_k, softmax_scale, window_size, block_table,
         softcap, k_descale, v_descale, alibi_slopes, path, workspace, sinks, output_scale, qq_bias, softmax_lse,
+        k_scale_cache, v_scale_cache,
     )
     if decode_plan is not None and decode_plan.key:
         p.decode_plan, p.decode_plan_key = decode_plan.buf.data_ptr(), decode_plan.key
@@ -400,8 +476,8 @@ class AttentionPlan:
     __slots__ = ("p", "_ref", "_fn", "_keep", "_ws_ptr", "num_q_heads", "head_size", "q_dtype")
 
     def __init__(self, k, v, q_dtype, num_q_heads, head_size, softmax_scale, window_size, softcap, alibi_slopes,
-                 k_descale, v_descale, sinks=None):
-        _require_cuda(k, v, alibi_slopes, k_descale, v_descale, sinks)
+                 k_descale, v_descale, sinks=None, k_scale_cache=None, v_scale_cache=None):
+        _require_cuda(k, v, alibi_slopes, k_descale, v_descale, sinks, k_scale_cache, v_scale_cache)
         if sinks is not None:
             if sinks.shape[0] != num_q_heads:
                 raise ValueError("sinks must have one entry per query head")
@@ -427,9 +503,11 @@ class AttentionPlan:
         p.num_blocks = k.shape[0]
         p.kc_block_stride, p.kc_slot_stride, p.kc_head_stride = k.stride(0), k.stride(1), k.stride(2)
         p.vc_block_stride, p.vc_slot_stride, p.vc_head_stride = v.stride(0), v.stride(1), v.stride(2)
+        _set_scale_caches(p, k, v, k_scale_cache, v_scale_cache)
         self.p, self._ref = p, ctypes.byref(p)
         self._fn = _cabi.load_library().b200attn_unified_attention
-        self._keep = (k, v, alibi_slopes, k_descale, v_descale, sinks)  # the struct holds raw pointers into these
+        # the struct holds raw pointers into these
+        self._keep = (k, v, alibi_slopes, k_descale, v_descale, sinks, k_scale_cache, v_scale_cache)
         self._ws_ptr = None
         self.num_q_heads, self.head_size, self.q_dtype = num_q_heads, head_size, q_dtype
 
@@ -515,6 +593,73 @@ class CacheWritePlan:
                       torch.cuda.current_stream(key.device).cuda_stream)
         if rc:
             _cabi.check(rc)
+
+
+class PerTokenHeadCacheWritePlan:
+    """`b200attn_reshape_and_cache_flash_per_token_head` with the cache side of the argument list fixed."""
+
+    __slots__ = ("_fn", "_head", "_shape", "_tail", "_keep", "_src_dtype")
+
+    def __init__(self, key_cache, value_cache, k_scale_cache, v_scale_cache, src_dtype):
+        _require_cuda(key_cache, value_cache, k_scale_cache, v_scale_cache)
+        if key_cache.dim() != 4 or key_cache.stride(3) != 1 or value_cache.stride(3) != 1 or key_cache.element_size() != 1:
+            raise ValueError("caches must be 1-byte [NB, bs, Hkv, D] views with a contiguous head_dim")
+        if k_scale_cache.dtype != torch.float32 or v_scale_cache.dtype != torch.float32 or \
+                tuple(k_scale_cache.shape) != tuple(key_cache.shape[:3]) or tuple(v_scale_cache.shape) != tuple(value_cache.shape[:3]):
+            raise ValueError("scale caches must be float32 [NB, bs, Hkv]")
+        src_dt = _DTYPE.get(src_dtype)
+        if src_dt not in (_cabi.BF16, _cabi.F16, _cabi.F32):
+            raise ValueError(f"unsupported key dtype {src_dtype}")
+        _, bs, hkv, d = key_cache.shape
+        self._fn = _cabi.load_library().b200attn_reshape_and_cache_flash_per_token_head
+        self._head = (key_cache.data_ptr(), value_cache.data_ptr(), k_scale_cache.data_ptr(), v_scale_cache.data_ptr())
+        self._shape = (hkv, d, bs)
+        self._tail = (*key_cache.stride()[:3], *value_cache.stride()[:3], *k_scale_cache.stride(), *v_scale_cache.stride(),
+                      src_dt, _DTYPE[key_cache.dtype])
+        self._keep = (key_cache, value_cache, k_scale_cache, v_scale_cache)
+        self._src_dtype = src_dtype
+
+    def __call__(self, key, value, slot_mapping) -> None:
+        if key.dtype != self._src_dtype or value.dtype != key.dtype or not key.is_cuda or slot_mapping.dtype != torch.int64:
+            raise ValueError("key dtype/device differs from the plan, or slot_mapping is not int64")
+        ks, vs = key.stride(), value.stride()
+        if ks[2] != 1 or vs[2] != 1:
+            raise ValueError("key/value rows must be contiguous in head_dim")
+        rc = self._fn(key.data_ptr(), value.data_ptr(), *self._head, slot_mapping.data_ptr(), slot_mapping.shape[0],
+                      *self._shape, ks[0], ks[1], vs[0], vs[1], *self._tail, torch.cuda.current_stream(key.device).cuda_stream)
+        if rc:
+            _cabi.check(rc)
+
+
+PER_TOKEN_HEAD_SCALE_PAD_BYTES = 4  # one fp32 scale per (token, head) row, budgeted by vLLM as head_size + 4 / elem size
+
+
+def per_token_head_cache_views(plane: torch.Tensor, head_size: int, kv_dtype: torch.dtype):
+    """Data and scale views of one plane (K or V) of a per-(token, head) quantised cache.
+
+    `plane`: [NB, bs, Hkv, head_size + 4] one-byte elements, each block contiguous - the bytes vLLM budgets for this
+    mode (`AttentionSpec.page_size_bytes`, vllm/v1/kv_cache_interface.py:150-160: the data plus one fp32 per (token,
+    head)).  Upstream's Triton backend keeps each row's scale INLINE behind the row (rows of head_size + 4 bytes,
+    triton_attn.py:401-452): a 132-byte row pitch that no TMA descriptor can express (strides must be 16-byte
+    multiples).  Here a block holds its data first, [bs][Hkv][head_size] dense as in the unquantised layout, and
+    behind it the block's scales as [Hkv][bs] fp32 - the same bytes, TMA-able rows, and a warp of the decode kernel
+    finds the 16 scales of its 16 tokens in one 64-byte line.
+
+    Returns (data [NB, bs, Hkv, head_size] as `kv_dtype`, scales [NB, bs, Hkv] float32 with strides (block, 1, bs))."""
+    if plane.dim() != 4 or plane.element_size() != 1 or plane.shape[3] != head_size + PER_TOKEN_HEAD_SCALE_PAD_BYTES:
+        raise ValueError("plane must be [NB, bs, Hkv, head_size + 4] one-byte elements")
+    nb, bs, hkv, dp = plane.shape
+    blk = bs * hkv * dp
+    if plane.stride() != (plane.stride(0), hkv * dp, dp, 1) or plane.stride(0) % 16 or (bs * hkv * head_size) % 16:
+        raise ValueError("per-token-head cache blocks must be contiguous (NHD) with 16-byte aligned block strides")
+    if plane.storage_offset() % 16:
+        raise ValueError("per-token-head cache plane must start 16-byte aligned")
+    u8 = plane.view(torch.uint8)
+    data = u8.as_strided((nb, bs, hkv, head_size), (plane.stride(0), hkv * head_size, head_size, 1), plane.storage_offset())
+    raw = torch.empty(0, dtype=torch.float32, device=plane.device).set_(plane.untyped_storage())
+    scales = raw.as_strided((nb, bs, hkv), (plane.stride(0) // 4, 1, bs), (plane.storage_offset() + bs * hkv * head_size) // 4)
+    assert blk >= bs * hkv * head_size + 4 * bs * hkv
+    return data.view(kv_dtype), scales
 
 
 def rope_and_cache_flash(
