@@ -697,38 +697,64 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
 
   // Per-(token, head) scales (KVQ >= 2): rows gid and gid + 8 of each 16-token sub-tile need the key's and the
   // value's scale.  The consumers fetch them themselves - the stage ring has no room left for them - straight from
-  // the scale caches: the page of each sub-tile is looked up one step ahead (block table: an L2 hit behind the
-  // producer's own lookups), the four scales are requested at the top of the step and first used after the
-  // S = K Q^T pass, so their latency hides behind the wait for the stage and the first MMA pass.
-  int pg_cur[SUB], pg_nxt[SUB];
-  float ksc[SUB][2], vsc[SUB][2];
+  // the scale caches: a sub-tile has 16 key and 16 value scales, ONE per lane (lanes 0-15 the keys' of tokens
+  // 0-15, lanes 16-31 the values'), handed to the lanes that need them by shuffles when the step begins.  Two
+  // loads deep: at the top of step s the scales of step s + 1 are requested (their page ids were requested a step
+  // earlier) and the page ids of step s + 2, so neither the block-table lookup nor the scale load is waited for
+  // before a whole step has gone by.  (First version: every lane fetched its own four values at the top of the
+  // step that used them - half the per-tensor kernel's rate, profiles/r02_kbench_per_token_head_v1.jsonl; with the
+  // prefetch but four loads and their 64-bit addresses per lane, 190 instructions a step on top of 700.)
+  int pg_a[SUB], pg_b[SUB];                 // page of each sub-tile, steps s + 1 and s + 2
+  float ksc[SUB][2], vsc[SUB][2];           // scales of step s (rows gid, gid + 8)
+  float sc_n[SUB];                          // step s + 1, in flight: this lane's one scale per sub-tile
 #pragma unroll
-  for (int sb = 0; sb < SUB; ++sb) pg_cur[sb] = pg_nxt[sb] = -1, ksc[sb][0] = ksc[sb][1] = vsc[sb][0] = vsc[sb][1] = 1.f;
+  for (int sb = 0; sb < SUB; ++sb) {
+    pg_a[sb] = pg_b[sb] = -1, sc_n[sb] = 1.f;
+    ksc[sb][0] = ksc[sb][1] = vsc[sb][0] = vsc[sb][1] = 1.f;
+  }
   const int bs_mask = P.a.block_size - 1;
-  auto load_pages = [&](int item, int step, int seq_len, int (&pg)[SUB]) {
-    const int32_t* bt = P.a.block_tables + (int64_t)(item / P.head_groups) * P.a.bt_stride0;
+  const int32_t* bt_run = P.a.block_tables;  // block-table row of the current run's sequence
+  auto load_pages = [&](int step, int seq_len, int (&pg)[SUB]) {
+    const int32_t* bt = bt_run;
 #pragma unroll
     for (int sb = 0; sb < SUB; ++sb) {
       const int tok = step * P.tps + tok_off + 16 * sb;  // 16-aligned and block_size >= 16: one page per sub-tile
       pg[sb] = tok < seq_len ? __ldg(bt + (tok >> P.bs_shift)) : -1;
     }
   };
-  auto load_scales = [&](int hg, int step, int seq_len) {
-    const int head = hg * P.hpc + h_local;
+  // this lane's cache (K or V), its strides and its fixed offset inside a sub-tile, once
+  const float* sc_lane = nullptr;
+  int64_t sc_block_stride = 0, sc_head_stride = 0;
+  int sc_slot_stride = 0;
+  if constexpr (PTH) {
+    const bool is_v = lane >= 16;
+    sc_block_stride = is_v ? P.a.vs_block_stride : P.a.ks_block_stride;
+    sc_head_stride = is_v ? P.a.vs_head_stride : P.a.ks_head_stride;
+    sc_slot_stride = (int)(is_v ? P.a.vs_slot_stride : P.a.ks_slot_stride);
+    sc_lane = (is_v ? P.a.v_scale_cache : P.a.k_scale_cache) + (int64_t)(lane & 15) * sc_slot_stride + (int64_t)h_local * sc_head_stride;
+  }
+  auto load_scales = [&](int hg, int step, int seq_len, const int (&pg)[SUB]) {  // -> sc_n
+    const float* hp = sc_lane + (int64_t)(hg * P.hpc) * sc_head_stride;
 #pragma unroll
     for (int sb = 0; sb < SUB; ++sb) {
-#pragma unroll
-      for (int hf = 0; hf < 2; ++hf) {
-        const int tok = step * P.tps + tok_off + 16 * sb + gid + 8 * hf;
-        float kq = 1.f, vq = 1.f;
-        if (tok < seq_len) {  // (then pg_cur[sb] >= 0)
-          const int slot = tok & bs_mask;
-          kq = __ldg(P.a.k_scale_cache + (int64_t)pg_cur[sb] * P.a.ks_block_stride + (int64_t)slot * P.a.ks_slot_stride + (int64_t)head * P.a.ks_head_stride);
-          vq = __ldg(P.a.v_scale_cache + (int64_t)pg_cur[sb] * P.a.vs_block_stride + (int64_t)slot * P.a.vs_slot_stride + (int64_t)head * P.a.vs_head_stride);
-        }
-        ksc[sb][hf] = kq, vsc[sb][hf] = vq;
-      }
+      const int tok = step * P.tps + tok_off + 16 * sb;  // sub-tile's first token
+      const float* sp = hp + (int64_t)pg[sb] * sc_block_stride + (tok & bs_mask) * sc_slot_stride;
+      sc_n[sb] = (tok + (lane & 15) < seq_len) ? __ldg(sp) : 1.f;  // (then pg[sb] >= 0)
     }
+  };
+  auto take_scales = [&]() {  // sc_n (requested a step ago) -> ksc / vsc of the rows this lane works on
+#pragma unroll
+    for (int sb = 0; sb < SUB; ++sb) {
+      ksc[sb][0] = __shfl_sync(0xffffffffu, sc_n[sb], gid), ksc[sb][1] = __shfl_sync(0xffffffffu, sc_n[sb], gid + 8);
+      vsc[sb][0] = __shfl_sync(0xffffffffu, sc_n[sb], gid + 16), vsc[sb][1] = __shfl_sync(0xffffffffu, sc_n[sb], gid + 24);
+    }
+  };
+  // start of a run: pages of its first three steps, then (once the first have landed) the first step's scales
+  auto prime_pages = [&](int item, int step0, int seq_len, int (&pg0)[SUB]) {
+    bt_run = P.a.block_tables + (int64_t)(item / P.head_groups) * P.a.bt_stride0;  // (a division: once per run)
+    load_pages(step0, seq_len, pg0);
+    load_pages(step0 + 1, seq_len, pg_a);
+    load_pages(step0 + 2, seq_len, pg_b);
   };
 
   // ldmatrix lane geometry
@@ -976,7 +1002,11 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
   cur.hg = run.hg, cur.step = run.step0, cur.seq_len = run.seq_len;
   reset_state();
   load_q(run.tq, run.hg);
-  if constexpr (PTH) load_pages(run.item, cur.step, cur.seq_len, pg_cur);
+  if constexpr (PTH) {
+    int pg0[SUB];
+    prime_pages(run.item, cur.step, cur.seq_len, pg0);
+    load_scales(cur.hg, cur.step, cur.seq_len, pg0);
+  }
   bool first_stage = true;
   int steps_done = 0;  // of the current run
 
@@ -985,8 +1015,11 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
   while (true) {
     const int tok0 = cur.step * P.tps + tok_off;  // first token of this warp's tile
     if constexpr (PTH) {
-      load_scales(cur.hg, cur.step, cur.seq_len);
-      load_pages(run.item, cur.step + 1, cur.seq_len, pg_nxt);
+      take_scales();  // this step's, requested a step ago
+      load_scales(cur.hg, cur.step + 1, cur.seq_len, pg_a);
+#pragma unroll
+      for (int sb = 0; sb < SUB; ++sb) pg_a[sb] = pg_b[sb];
+      load_pages(cur.step + 3, cur.seq_len, pg_b);
     }
     {
       const long long t0 = trace ? clock64() : 0;
@@ -1040,10 +1073,8 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
 #pragma unroll
                 for (int half = 0; half < 2; ++half) {
                   uint32_t a[4];
-                  a[0] = kv8x2_to_f16x2<KV_I8>((uint16_t)(r[2 * half] & 0xffffu));
-                  a[1] = kv8x2_to_f16x2<KV_I8>((uint16_t)(r[2 * half + 1] & 0xffffu));
-                  a[2] = kv8x2_to_f16x2<KV_I8>((uint16_t)(r[2 * half] >> 16));
-                  a[3] = kv8x2_to_f16x2<KV_I8>((uint16_t)(r[2 * half + 1] >> 16));
+                  kv8x4_to_f16x2<KV_I8, false>(r[2 * half], a[0], a[2]);
+                  kv8x4_to_f16x2<KV_I8, false>(r[2 * half + 1], a[1], a[3]);
                   const int ks = dc * 8 + c2 * 2 + half;
 #pragma unroll
                   for (int nt = 0; nt < NT; ++nt)
@@ -1173,13 +1204,10 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
               // each: [tok 2t: d0 d1 | tok 2t+1: d0 d1] with d0 = 16c + 2gid
 #pragma unroll
               for (int half = 0; half < 2; ++half) {
-                const uint32_t x0 = __byte_perm(r[2 * half], 0, 0x3120);      // [t d0, t+1 d0 | t d1, t+1 d1]
-                const uint32_t x1 = __byte_perm(r[2 * half + 1], 0, 0x3120);
+                // bytes [t d0, t d1, t+1 d0, t+1 d1] -> (t d0, t+1 d0) and (t d1, t+1 d1)
                 uint32_t a[4];
-                a[0] = kv8x2_to_f16x2<KV_I8>((uint16_t)(x0 & 0xffffu));  // row gid   <-> d0, tokens 2t,2t+1
-                a[1] = kv8x2_to_f16x2<KV_I8>((uint16_t)(x0 >> 16));      // row gid+8 <-> d1
-                a[2] = kv8x2_to_f16x2<KV_I8>((uint16_t)(x1 & 0xffffu));  // tokens 2t+8, 2t+9
-                a[3] = kv8x2_to_f16x2<KV_I8>((uint16_t)(x1 >> 16));
+                kv8x4_to_f16x2<KV_I8, true>(r[2 * half], a[0], a[1]);      // row gid <-> d0 and row gid+8 <-> d1, tokens 2t, 2t+1
+                kv8x4_to_f16x2<KV_I8, true>(r[2 * half + 1], a[2], a[3]);  // tokens 2t+8, 2t+9
                 if (partial) a[0] &= vm_lo, a[1] &= vm_lo, a[2] &= vm_hi, a[3] &= vm_hi;
                 const int mt = dc * 8 + c2 * 2 + half;
 #pragma unroll
@@ -1195,10 +1223,6 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
     if (++stage == P.stages) stage = 0, phase ^= 1;
 
     ++cur.step, ++steps_done;
-    if constexpr (PTH) {
-#pragma unroll
-      for (int sb = 0; sb < SUB; ++sb) pg_cur[sb] = pg_nxt[sb];
-    }
     if (run_ends) {
       // ---------------- finalise this run ------------------
       const long long t_fin = trace ? clock64() : 0;
@@ -1214,8 +1238,9 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
       const RunDesc nx = descs[nd & (kDescSlots - 1)];
       const bool last = nx.kind == 0;
       if (!last) load_q(nx.tq, nx.hg);
+      int pg0[SUB];
       if constexpr (PTH) {
-        if (!last) load_pages(nx.item, nx.step0, nx.seq_len, pg_cur);  // in flight while this run is finalised
+        if (!last) prime_pages(nx.item, nx.step0, nx.seq_len, pg0);  // in flight while this run is finalised
       }
       if (trace && threadIdx.x == 0) {
         if (last) trace[4] = clock64();
@@ -1295,6 +1320,7 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
       run = nx;
       cur.hg = run.hg, cur.step = run.step0, cur.seq_len = run.seq_len;
       steps_done = 0;
+      if constexpr (PTH) load_scales(cur.hg, cur.step, cur.seq_len, pg0);
     }
   }
   publish_fin(0, 0, 0, 0, 0);  // no more partials from this CTA
@@ -1542,6 +1568,10 @@ bool decode_supported(const b200attn_attention_params& p, const char** why, bool
   if (p.kv_dtype != p.q_dtype && !kv8) return no("kv dtype");
   if (p.head_size != 64 && p.head_size != 128 && p.head_size != 256) return no("head_size not in {64,128,256}");
   if (kv8 && p.head_size < 128) return no("fp8 / int8 KV needs head_size >= 128");
+  if (per_token_head(p)) {  // the consumers index a block's scales in 32 bits
+    auto small = [&](int64_t s) { return s >= 0 && s * p.block_size < (int64_t(1) << 31); };
+    if (!small(p.ks_slot_stride) || !small(p.vs_slot_stride)) return no("scale cache slot stride");
+  }
   if (p.num_kv_heads <= 0 || p.num_q_heads % p.num_kv_heads) return no("heads");
   const int g = p.num_q_heads / p.num_kv_heads;
   if (g > 16 || (g > 8 && p.head_size == 256)) return no("GQA group too large for the decode kernel");

@@ -372,6 +372,23 @@ __device__ __forceinline__ uint32_t e4m3x2_to_f16x2(uint16_t x) {
 }
 template <> __device__ __forceinline__ uint32_t kv8x2_to_f16x2<false>(uint16_t x) { return e4m3x2_to_f16x2(x); }
 template <> __device__ __forceinline__ uint32_t kv8x2_to_f16x2<true>(uint16_t x) { return s8x2_to_f16x2(x); }
+// Four one-byte elements (b0 b1 b2 b3 of w, e4m3 or int8) -> two f16x2, exact.  kTranspose = false: lo = (b0, b1),
+// hi = (b2, b3); true: lo = (b0, b2), hi = (b1, b3) - the V^T fragments of the decode kernel.  int8 costs five
+// instructions per word this way (one XOR, two PRMT that also do the transposition, two HADD2) where converting
+// 16 bits at a time cost ten.
+template <bool kInt8, bool kTranspose> __device__ __forceinline__ void kv8x4_to_f16x2(uint32_t w, uint32_t& lo, uint32_t& hi) {
+  if constexpr (kInt8) {
+    const uint32_t x = w ^ 0x80808080u;
+    const uint32_t l = __byte_perm(x, 0x64646464u, kTranspose ? 0x4240 : 0x4140);
+    const uint32_t h = __byte_perm(x, 0x64646464u, kTranspose ? 0x4341 : 0x4342);
+    const __half2 bias = __halves2half2(__ushort_as_half((unsigned short)0x6480), __ushort_as_half((unsigned short)0x6480));
+    const __half2 lr = __hsub2(*reinterpret_cast<const __half2*>(&l), bias), hr = __hsub2(*reinterpret_cast<const __half2*>(&h), bias);
+    lo = *reinterpret_cast<const uint32_t*>(&lr), hi = *reinterpret_cast<const uint32_t*>(&hr);
+  } else {
+    const uint32_t x = kTranspose ? __byte_perm(w, 0, 0x3120) : w;
+    lo = e4m3x2_to_f16x2((uint16_t)(x & 0xffffu)), hi = e4m3x2_to_f16x2((uint16_t)(x >> 16));
+  }
+}
 
 __device__ __forceinline__ void cp_async_16(uint32_t smem_addr, const void* gptr, bool pred) {
   int sz = pred ? 16 : 0;
