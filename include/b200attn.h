@@ -221,6 +221,26 @@ B200ATTN_API uint64_t b200attn_decode_plan_bytes(int32_t num_seqs);
 B200ATTN_API int b200attn_decode_plan(const b200attn_attention_params* p, void* plan, uint64_t plan_bytes,
                                       uint64_t* key_out_host, b200attn_stream_t stream);
 
+/* Decode attention for callers that cannot allocate device memory (code under CUDA-graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same arithmetic and kernel as b200attn_unified_attention with path = B200ATTN_PATH_DECODE, but the
+ * split-KV scratch (ticket counters, partial records, the work plan when `decode_plan` is not given) lives in a
+ * file-scope device array of B200ATTN_STATIC_SCRATCH_BYTES inside the library - every GPU that loads the library
+ * holds it until the process exits - instead of the caller's `workspace` (`workspace`, `workspace_bytes` and `path`
+ * of `p` are ignored).  The call allocates nothing (no cudaMalloc / cudaFree / allocating library routine): it
+ * clears the first MiB of the array on `stream` and launches.
+ *   - decode batches only: max_seqlen_q == 1 and a configuration the split-KV kernel takes
+ *     (B200ATTN_E_UNSUPPORTED otherwise);
+ *   - limit: b200attn_workspace_bytes(...) of the shape must not exceed B200ATTN_STATIC_SCRATCH_BYTES (24 MiB:
+ *     e.g. up to 32 query heads at head size 128 with 8 kv heads, or a 1-2 kv-head shard of a 64-head model);
+ *     larger shapes return B200ATTN_E_WORKSPACE with a message naming both sizes;
+ *   - the array is shared by all calls on a GPU and keeps the last call's contents; calls that overlap on the GPU
+ *     (other streams, other threads) race on it: serialise them or use b200attn_unified_attention with a
+ *     workspace per stream. */
+#define B200ATTN_STATIC_SCRATCH_BYTES (24u << 20)
+B200ATTN_API int b200attn_decode_attention_static_scratch(const b200attn_attention_params* p,
+                                                          b200attn_stream_t stream);
+
 /* ---- K4 (optional): static per-tensor FP8 quantisation of Q ----------------
  * Replaces ops.scaled_fp8_quant(query, layer._q_scale) at triton_attn.py:417
  * (vllm/csrc/quantization/w8a8/fp8/common.cu:11-29):

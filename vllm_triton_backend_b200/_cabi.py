@@ -31,6 +31,7 @@ EXPORTED_SYMBOLS = [
     "b200attn_unified_attention",
     "b200attn_decode_plan_bytes",
     "b200attn_decode_plan",
+    "b200attn_decode_attention_static_scratch",
     "b200attn_scaled_fp8_quant",
     "b200attn_rope_and_cache_flash",
     "b200attn_abi_version",
@@ -122,6 +123,8 @@ def load_library() -> ctypes.CDLL:
     lib.b200attn_decode_plan_bytes.argtypes = [c_int32]
     lib.b200attn_decode_plan.restype = c_int32
     lib.b200attn_decode_plan.argtypes = [POINTER(AttentionParams), c_void_p, c_uint64, POINTER(c_uint64), c_void_p]
+    lib.b200attn_decode_attention_static_scratch.restype = c_int32
+    lib.b200attn_decode_attention_static_scratch.argtypes = [POINTER(AttentionParams), c_void_p]
     lib.b200attn_rope_and_cache_flash.restype = c_int32
     lib.b200attn_rope_and_cache_flash.argtypes = [POINTER(RopeCacheParams), c_void_p]
     lib.b200attn_scaled_fp8_quant.restype = c_int32

@@ -20,7 +20,7 @@ CSRC = os.path.join(PKG_DIR, "csrc")
 BUILD_DIR = os.path.join(PKG_DIR, "_build")
 LIB_PATH = os.path.join(PKG_DIR, "libb200attn.so")
 SOURCES = ["cabi.cu", "tma_maps.cu", "cache_write.cu", "rope_cache_write.cu", "kv_stage.cu", "attn_generic.cu", "attn_decode.cu", "attn_prefill.cu",
-           "attn_prefill_tc.cu", "attn_prefill_tc256.cu"]
+           "attn_prefill_tc.cu", "attn_prefill_tc256.cu", "static_scratch.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
