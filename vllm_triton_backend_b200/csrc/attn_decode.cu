@@ -132,6 +132,7 @@ struct DecodeParams {
   int paired;      // 1: one TMA box carries the K and the V rows of a page ([head][k|v][slot][128 B]); fp8 D=128
   int group;       // query heads per kv head
   int only_q1;     // mixed batch: only sequences with exactly one query token are this kernel's
+  int out_vec;     // 1: 16-bit output rows are 8-byte aligned (four elements leave as one store)
   const Plan* plan;
   float* ws_acc;   // [slots][hpc*group][D]
   float* ws_ml;    // [slots][hpc*group][2]  (max in log2 units, exp-sum)
@@ -712,34 +713,45 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
     pg_a[sb] = pg_b[sb] = -1, sc_n[sb] = 1.f;
     ksc[sb][0] = ksc[sb][1] = vsc[sb][0] = vsc[sb][1] = 1.f;
   }
+  // Per step this costs the consumers ~40 instructions: everything that does not change with the step is folded
+  // into per-run state (block-table row, the head's base address) or per-kernel state (this lane's cache, its
+  // strides in BYTES as 32-bit values, so that page * block_stride + base is ONE 32 x 32 + 64-bit multiply-add),
+  // and the token positions of steps s + 1 / s + 3 are sums, not products.  (With 64-bit strides and the
+  // positions recomputed from the step number it was ~110: profiles/r02_ncu_decode_per_token_head.txt.)
   const int bs_mask = P.a.block_size - 1;
   const int32_t* bt_run = P.a.block_tables;  // block-table row of the current run's sequence
-  auto load_pages = [&](int step, int seq_len, int (&pg)[SUB]) {
-    const int32_t* bt = bt_run;
+  auto load_pages = [&](int tok_first, int seq_len, int (&pg)[SUB]) {  // tok_first: this warp's first token of that step
 #pragma unroll
     for (int sb = 0; sb < SUB; ++sb) {
-      const int tok = step * P.tps + tok_off + 16 * sb;  // 16-aligned and block_size >= 16: one page per sub-tile
-      pg[sb] = tok < seq_len ? __ldg(bt + (tok >> P.bs_shift)) : -1;
+      const int tok = tok_first + 16 * sb;  // 16-aligned and block_size >= 16: one page per sub-tile
+      int v = 0;
+      if (tok < seq_len) v = __ldg(bt_run + (tok >> P.bs_shift));
+      pg[sb] = v;
     }
   };
-  // this lane's cache (K or V), its strides and its fixed offset inside a sub-tile, once
-  const float* sc_lane = nullptr;
-  int64_t sc_block_stride = 0, sc_head_stride = 0;
-  int sc_slot_stride = 0;
+  const char* sc_lane = nullptr;   // this lane's cache (keys' or values' scales) + its row inside a sub-tile + the warp's head
+  const char* sc_head = nullptr;   // ... + the run's head group
+  uint32_t sc_block_bytes = 0, sc_slot_bytes = 0;
+  int64_t sc_group_bytes = 0;      // bytes between head groups
+  const int l15 = lane & 15;
   if constexpr (PTH) {
     const bool is_v = lane >= 16;
-    sc_block_stride = is_v ? P.a.vs_block_stride : P.a.ks_block_stride;
-    sc_head_stride = is_v ? P.a.vs_head_stride : P.a.ks_head_stride;
-    sc_slot_stride = (int)(is_v ? P.a.vs_slot_stride : P.a.ks_slot_stride);
-    sc_lane = (is_v ? P.a.v_scale_cache : P.a.k_scale_cache) + (int64_t)(lane & 15) * sc_slot_stride + (int64_t)h_local * sc_head_stride;
+    const int64_t hs = is_v ? P.a.vs_head_stride : P.a.ks_head_stride;
+    sc_block_bytes = (uint32_t)(is_v ? P.a.vs_block_stride : P.a.ks_block_stride) * 4u;  // < 2^31: decode_supported()
+    sc_slot_bytes = (uint32_t)(is_v ? P.a.vs_slot_stride : P.a.ks_slot_stride) * 4u;
+    sc_group_bytes = (int64_t)P.hpc * hs * 4;
+    sc_lane = reinterpret_cast<const char*>(is_v ? P.a.v_scale_cache : P.a.k_scale_cache) + (int64_t)l15 * sc_slot_bytes +
+              (int64_t)h_local * hs * 4;
+    sc_head = sc_lane;
   }
-  auto load_scales = [&](int hg, int step, int seq_len, const int (&pg)[SUB]) {  // -> sc_n
-    const float* hp = sc_lane + (int64_t)(hg * P.hpc) * sc_head_stride;
+  auto load_scales = [&](int tok_first, int seq_len, const int (&pg)[SUB]) {  // -> sc_n
 #pragma unroll
     for (int sb = 0; sb < SUB; ++sb) {
-      const int tok = step * P.tps + tok_off + 16 * sb;  // sub-tile's first token
-      const float* sp = hp + (int64_t)pg[sb] * sc_block_stride + (tok & bs_mask) * sc_slot_stride;
-      sc_n[sb] = (tok + (lane & 15) < seq_len) ? __ldg(sp) : 1.f;  // (then pg[sb] >= 0)
+      const int tok = tok_first + 16 * sb;  // sub-tile's first token
+      const char* sp = sc_head + (uint64_t)(uint32_t)pg[sb] * sc_block_bytes + (uint32_t)(tok & bs_mask) * sc_slot_bytes;
+      float v = 1.f;
+      if (tok + l15 < seq_len) v = __ldg(reinterpret_cast<const float*>(sp));
+      sc_n[sb] = v;
     }
   };
   auto take_scales = [&]() {  // sc_n (requested a step ago) -> ksc / vsc of the rows this lane works on
@@ -749,12 +761,14 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
       vsc[sb][0] = __shfl_sync(0xffffffffu, sc_n[sb], gid + 16), vsc[sb][1] = __shfl_sync(0xffffffffu, sc_n[sb], gid + 24);
     }
   };
-  // start of a run: pages of its first three steps, then (once the first have landed) the first step's scales
-  auto prime_pages = [&](int item, int step0, int seq_len, int (&pg0)[SUB]) {
+  // start of a run: its block-table row and head base, the pages of its first three steps
+  auto prime_pages = [&](int item, int hg, int step0, int seq_len, int (&pg0)[SUB]) {
     bt_run = P.a.block_tables + (int64_t)(item / P.head_groups) * P.a.bt_stride0;  // (a division: once per run)
-    load_pages(step0, seq_len, pg0);
-    load_pages(step0 + 1, seq_len, pg_a);
-    load_pages(step0 + 2, seq_len, pg_b);
+    sc_head = sc_lane + (int64_t)hg * sc_group_bytes;
+    const int t0 = step0 * P.tps + tok_off;
+    load_pages(t0, seq_len, pg0);
+    load_pages(t0 + P.tps, seq_len, pg_a);
+    load_pages(t0 + 2 * P.tps, seq_len, pg_b);
   };
 
   // ldmatrix lane geometry
@@ -1004,8 +1018,8 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
   load_q(run.tq, run.hg);
   if constexpr (PTH) {
     int pg0[SUB];
-    prime_pages(run.item, cur.step, cur.seq_len, pg0);
-    load_scales(cur.hg, cur.step, cur.seq_len, pg0);
+    prime_pages(run.item, run.hg, cur.step, cur.seq_len, pg0);
+    load_scales(cur.step * P.tps + tok_off, cur.seq_len, pg0);
   }
   bool first_stage = true;
   int steps_done = 0;  // of the current run
@@ -1016,10 +1030,10 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
     const int tok0 = cur.step * P.tps + tok_off;  // first token of this warp's tile
     if constexpr (PTH) {
       take_scales();  // this step's, requested a step ago
-      load_scales(cur.hg, cur.step + 1, cur.seq_len, pg_a);
+      load_scales(tok0 + P.tps, cur.seq_len, pg_a);
 #pragma unroll
       for (int sb = 0; sb < SUB; ++sb) pg_a[sb] = pg_b[sb];
-      load_pages(cur.step + 3, cur.seq_len, pg_b);
+      load_pages(tok0 + 3 * P.tps, cur.seq_len, pg_b);
     }
     {
       const long long t0 = trace ? clock64() : 0;
@@ -1240,7 +1254,7 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
       if (!last) load_q(nx.tq, nx.hg);
       int pg0[SUB];
       if constexpr (PTH) {
-        if (!last) prime_pages(nx.item, nx.step0, nx.seq_len, pg0);  // in flight while this run is finalised
+        if (!last) prime_pages(nx.item, nx.hg, nx.step0, nx.seq_len, pg0);  // in flight while this run is finalised
       }
       if (trace && threadIdx.x == 0) {
         if (last) trace[4] = clock64();
@@ -1257,56 +1271,85 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
           l1 += __shfl_xor_sync(0xffffffffu, l1, o);
         }
         if (nt > 0) asm volatile("bar.sync 1, %0;" ::"r"(NW * 32));
+        // Each warp's O^T columns go to mbuf[warp][8 heads][D].  The four lanes t4 of a row group write rows 2 t4
+        // (and 2 t4 + 1), D floats apart - the same bank - so the row's position inside its line is XORed with
+        // 8 t4 (two float4 groups per step of t4): conflict-free for the 16-bit layout, two-way for the fp8 one.
         float* mb = mbuf + warp * 8 * D;
+        const int swz = 8 * t4;
 #pragma unroll
         for (int mt = 0; mt < MTILES; ++mt) {
           int d0, d1;
           if constexpr (!KV_FP8) d0 = 16 * mt + gid, d1 = d0 + 8;
           else d0 = 16 * mt + 2 * gid, d1 = d0 + 1;
-          mb[(2 * t4) * D + d0] = oacc[mt][nt][0];
-          mb[(2 * t4 + 1) * D + d0] = oacc[mt][nt][1];
-          mb[(2 * t4) * D + d1] = oacc[mt][nt][2];
-          mb[(2 * t4 + 1) * D + d1] = oacc[mt][nt][3];
+          mb[(2 * t4) * D + (d0 ^ swz)] = oacc[mt][nt][0];
+          mb[(2 * t4 + 1) * D + (d0 ^ swz)] = oacc[mt][nt][1];
+          mb[(2 * t4) * D + (d1 ^ swz)] = oacc[mt][nt][2];
+          mb[(2 * t4 + 1) * D + (d1 ^ swz)] = oacc[mt][nt][3];
         }
         if (gid == 0) {
           ml_buf[(warp * 8 + 2 * t4) * 2] = m_run[nt][0], ml_buf[(warp * 8 + 2 * t4) * 2 + 1] = l0;
           ml_buf[(warp * 8 + 2 * t4 + 1) * 2] = m_run[nt][1], ml_buf[(warp * 8 + 2 * t4 + 1) * 2 + 1] = l1;
         }
         asm volatile("bar.sync 1, %0;" ::"r"(NW * 32));
-        // combine the warps that share a kv head; NW*32 threads cover hpc*8*D values
+        // Combine the warps that share a kv head.  A task is four consecutive d of one (kv head, query head) row:
+        // the row's (max, exp-sum) pairs and the wph rescale factors are formed once per task, the accumulators
+        // come as float4.  (Per element, as this loop first was, a run's epilogue took 2.5 us of the consumers'
+        // time - 4 runs per CTA at 640-token contexts: profiles/r02_kbench_short_ctx_trace.jsonl.)  The sums run
+        // over the warps in the same order as before, so results are bit for bit what they were.
         const int nheads = min(8, P.group - nt * 8);
-        const int tid = threadIdx.x;
-        for (int e = tid; e < P.hpc * 8 * D; e += NW * 32) {
-          const int hl = e / (8 * D), col = (e / D) & 7, d = e % D;
+        constexpr int G4 = D / 4;
+        for (int e4 = threadIdx.x; e4 < P.hpc * 8 * G4; e4 += NW * 32) {
+          const int row = e4 / G4, g4 = e4 % G4;
+          const int hl = row >> 3, col = row & 7;
           if (col >= nheads) continue;
+          const int pg4 = g4 ^ (((col >> 1) & 3) * 2);  // where the writers put this group
           float M = -INFINITY;
           for (int j = 0; j < wph; ++j) M = fmaxf(M, ml_buf[((hl + P.hpc * j) * 8 + col) * 2]);
-          float val = 0.f, L = 0.f;
+          float4 val = make_float4(0.f, 0.f, 0.f, 0.f);
+          float L = 0.f;
           for (int j = 0; j < wph; ++j) {
             const int w = hl + P.hpc * j;
-            const float mw = ml_buf[(w * 8 + col) * 2];
-            const float sc = (mw == -INFINITY) ? 0.f : ex2(mw - M);
-            val += mbuf[(w * 8 + col) * D + d] * sc;
-            L += ml_buf[(w * 8 + col) * 2 + 1] * sc;
+            const float2 ml = *reinterpret_cast<const float2*>(&ml_buf[(w * 8 + col) * 2]);
+            const float sc = (ml.x == -INFINITY) ? 0.f : ex2(ml.x - M);
+            const float4 a = *reinterpret_cast<const float4*>(&mbuf[(w * 8 + col) * D + 4 * pg4]);
+            val.x += a.x * sc, val.y += a.y * sc, val.z += a.z * sc, val.w += a.w * sc;
+            L += ml.y * sc;
           }
+          const int d = 4 * g4;
           const int hq_in_cta = hl * P.group + nt * 8 + col;  // query head within the CTA's head group
           if (direct) {
             const int hq = hg_done * P.hpc * P.group + hq_in_cta;
             const bool seen = M != -INFINITY;  // some key was visible (a sink alone does not make an LSE)
-            if (P.a.sinks) val *= sink_rescale<true>(P.a.sinks[hq], M, L);
-            const float o = (L > 0.f) ? val * v_scale / L : 0.f;
+            if (P.a.sinks) {
+              const float f = sink_rescale<true>(P.a.sinks[hq], M, L);
+              val.x *= f, val.y *= f, val.z *= f, val.w *= f;
+            }
             if (P.a.lse && d == 0) P.a.lse[(int64_t)tq * P.a.lse_stride0 + hq] = seen ? row_lse<true>(M, L) : -INFINITY;
+            // (a multiplication and a division per element, as before: the same roundings)
+            float o[4] = {val.x, val.y, val.z, val.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i) o[i] = (L > 0.f) ? o[i] * v_scale / L : 0.f;
             const int64_t oel = (int64_t)tq * P.a.out_stride0 + (int64_t)hq * P.a.out_stride1;
-            if (P.a.out_scale) {  // fused e4m3 output quantisation (b200attn.h: out_scale)
-              static_cast<uint8_t*>(P.a.out)[oel + d] = fp8_out(o * out_quant_factor(P.a.out_scale));
+            if (P.a.out_scale) {  // fused e4m3 output quantisation (b200attn.h: out_scale; rows 8-byte aligned)
+              const float oq = out_quant_factor(P.a.out_scale);
+              const uint32_t w = (uint32_t)fp8_out(o[0] * oq) | ((uint32_t)fp8_out(o[1] * oq) << 8) |
+                                 ((uint32_t)fp8_out(o[2] * oq) << 16) | ((uint32_t)fp8_out(o[3] * oq) << 24);
+              *reinterpret_cast<uint32_t*>(static_cast<uint8_t*>(P.a.out) + oel + d) = w;
             } else {
-              char* orow = static_cast<char*>(P.a.out) + oel * 2;
-              if constexpr (Q_BF16) reinterpret_cast<__nv_bfloat16*>(orow)[d] = __float2bfloat16_rn(o);
-              else reinterpret_cast<__half*>(orow)[d] = __float2half_rn(o);
+              char* orow = static_cast<char*>(P.a.out) + (oel + d) * 2;
+              if (P.out_vec) {
+                *reinterpret_cast<uint2*>(orow) = make_uint2(pack2<Q_BF16>(o[0], o[1]), pack2<Q_BF16>(o[2], o[3]));
+              } else {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                  if constexpr (Q_BF16) reinterpret_cast<__nv_bfloat16*>(orow)[i] = __float2bfloat16_rn(o[i]);
+                  else reinterpret_cast<__half*>(orow)[i] = __float2half_rn(o[i]);
+                }
+              }
             }
           } else {
             const int64_t rec = (int64_t)run.slot * (P.hpc * P.group) + hq_in_cta;
-            P.ws_acc[rec * D + d] = val;
+            *reinterpret_cast<float4*>(&P.ws_acc[rec * D + d]) = val;
             if (d == 0) P.ws_ml[rec * 2] = M, P.ws_ml[rec * 2 + 1] = L;
           }
         }
@@ -1320,7 +1363,7 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
       run = nx;
       cur.hg = run.hg, cur.step = run.step0, cur.seq_len = run.seq_len;
       steps_done = 0;
-      if constexpr (PTH) load_scales(cur.hg, cur.step, cur.seq_len, pg0);
+      if constexpr (PTH) load_scales(cur.step * P.tps + tok_off, cur.seq_len, pg0);
     }
   }
   publish_fin(0, 0, 0, 0, 0);  // no more partials from this CTA
@@ -1569,8 +1612,11 @@ bool decode_supported(const b200attn_attention_params& p, const char** why, bool
   if (p.head_size != 64 && p.head_size != 128 && p.head_size != 256) return no("head_size not in {64,128,256}");
   if (kv8 && p.head_size < 128) return no("fp8 / int8 KV needs head_size >= 128");
   if (per_token_head(p)) {  // the consumers index a block's scales in 32 bits
-    auto small = [&](int64_t s) { return s >= 0 && s * p.block_size < (int64_t(1) << 31); };
-    if (!small(p.ks_slot_stride) || !small(p.vs_slot_stride)) return no("scale cache slot stride");
+    // the consumers hold the scale caches' block and slot strides in bytes as 32-bit values
+    auto small = [&](int64_t s) { return s >= 0 && s * 4 < (int64_t(1) << 31); };
+    if (!small(p.ks_slot_stride * p.block_size) || !small(p.vs_slot_stride * p.block_size) || !small(p.ks_block_stride) ||
+        !small(p.vs_block_stride))
+      return no("scale cache strides >= 2 GiB");
   }
   if (p.num_kv_heads <= 0 || p.num_q_heads % p.num_kv_heads) return no("heads");
   const int g = p.num_q_heads / p.num_kv_heads;
@@ -1628,6 +1674,7 @@ int launch_attn_decode(const b200attn_attention_params& a, cudaStream_t stream, 
   P.a = a;
   P.group = a.num_q_heads / a.num_kv_heads;
   P.only_q1 = only_single_token_seqs ? 1 : 0;
+  P.out_vec = (!(reinterpret_cast<uintptr_t>(a.out) & 7) && a.out_stride0 % 4 == 0 && a.out_stride1 % 4 == 0) ? 1 : 0;
   P.trace = decode_trace_buffer();
   // carve the workspace: ticket counters first (fixed region, zero between calls), then ml, acc and the
   // launcher's own plan
