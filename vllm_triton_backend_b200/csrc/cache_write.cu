@@ -331,93 +331,130 @@ int launch_cache_write(const void* key, const void* value, void* k_cache, void* 
 // vllm/v1/attention/ops/triton_reshape_and_cache_flash.py:186-236; oracle/cache_write.py per_token_head_quant_ref):
 // scale = max(absmax / QMAX, 1e-6), code = Q(clamp(x * (1 / scale), QMIN, QMAX)) with IEEE division, e4m3 by
 // round-to-nearest-even, int8 by truncation toward zero.
-template <typename SrcT, bool kInt8, bool kVec>
+// R rows per warp, all of their loads issued before the first reduction (one row per warp left the kernel waiting on
+// a single 8-byte load per lane: 8192 tokens took 34 us, twice the per-tensor quantising write).
+template <typename SrcT, bool kInt8, bool kVec, int R>
 __global__ void __launch_bounds__(256) cache_quant_per_token_head_kernel(const PerTokenHeadWriteArgs a) {
   pdl_launch_dependents();
   pdl_wait();
   const int lane = threadIdx.x & 31;
-  const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);  // (token, head, K|V)
-  const int64_t rows = a.num_tokens * a.num_kv_heads * 2;
-  if (row >= rows) return;
-  const int w = (int)(row & 1);
-  const int h = (int)((row >> 1) % a.num_kv_heads);
-  const int64_t t = (row >> 1) / a.num_kv_heads;
-  const int64_t slot = a.slot_mapping[t];
-  if (slot < 0) return;  // padding token (:171-173)
-  const int64_t blk = slot / a.block_size, off = slot % a.block_size;
-  const SrcT* src = static_cast<const SrcT*>(a.src[w]) + t * a.src_stride0[w] + (int64_t)h * a.src_stride1[w];
-  uint8_t* dst = static_cast<uint8_t*>(a.dst[w]) + blk * a.block_stride[w] + off * a.slot_stride[w] + (int64_t)h * a.head_stride[w];
+  // 32-bit index arithmetic (the launcher checks that the row count fits): with 64-bit divisions for the token, the
+  // head and the page of every row, the index arithmetic was five times the quantisation itself
+  const uint32_t row0 = (blockIdx.x * 8u + (threadIdx.x >> 5)) * (uint32_t)R;  // (token, head, K|V), K|V fastest
+  const uint32_t rows = (uint32_t)(a.num_tokens * a.num_kv_heads * 2);
+  const uint32_t hkv = (uint32_t)a.num_kv_heads;
   const int D = a.head_size;
   constexpr float kQMax = kInt8 ? 127.f : 448.f, kQMin = kInt8 ? -128.f : -448.f;
   constexpr int kGroups = 2;  // head_size <= 256
-  float x[kGroups][4];
-  float amax = 0.f;
+  float x[R][kGroups][4];
+  uint8_t* dst[R];
+  float* sdst[R];
+  bool live[R];
 #pragma unroll
-  for (int g = 0; g < kGroups; ++g) {
-    const int d0 = kVec ? (g * 32 + lane) * 4 : 0;
+  for (int j = 0; j < R; ++j) {
+    const uint32_t row = row0 + j;
+    live[j] = false, dst[j] = nullptr, sdst[j] = nullptr;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int d = kVec ? d0 + i : (g * 4 + i) * 32 + lane;
-      x[g][i] = 0.f;
-      if constexpr (!kVec) {
-        if (d < D) x[g][i] = to_float<SrcT>(src[d]);
-      }
-    }
-    if constexpr (kVec) {
-      if (d0 < D) {
-        if constexpr (sizeof(SrcT) == 2) {
-          const uint2 raw = *reinterpret_cast<const uint2*>(src + d0);
-          const SrcT* e = reinterpret_cast<const SrcT*>(&raw);
+    for (int g = 0; g < kGroups; ++g) x[j][g][0] = x[j][g][1] = x[j][g][2] = x[j][g][3] = 0.f;
+    if (row >= rows) continue;
+    const int w = (int)(row & 1u);
+    const uint32_t t = (row >> 1) / hkv;
+    const int h = (int)((row >> 1) - t * hkv);
+    const int64_t slot = a.slot_mapping[t];
+    if (slot < 0) continue;  // padding token (:171-173)
+    live[j] = true;
+    int64_t blk, off;
+    if (a.bs_shift >= 0) blk = slot >> a.bs_shift, off = slot & (a.block_size - 1);
+    else if (slot < (int64_t(1) << 31)) blk = (uint32_t)slot / (uint32_t)a.block_size, off = (uint32_t)slot - (uint32_t)blk * (uint32_t)a.block_size;
+    else blk = slot / a.block_size, off = slot % a.block_size;
+    const SrcT* src = static_cast<const SrcT*>(a.src[w]) + (int64_t)t * a.src_stride0[w] + (int64_t)h * a.src_stride1[w];
+    dst[j] = static_cast<uint8_t*>(a.dst[w]) + blk * a.block_stride[w] + off * a.slot_stride[w] + (int64_t)h * a.head_stride[w];
+    sdst[j] = a.scales[w] + blk * a.s_block_stride[w] + off * a.s_slot_stride[w] + (int64_t)h * a.s_head_stride[w];
 #pragma unroll
-          for (int i = 0; i < 4; ++i) x[g][i] = to_float<SrcT>(e[i]);
-        } else {
-          const float4 raw = *reinterpret_cast<const float4*>(src + d0);
-          x[g][0] = raw.x, x[g][1] = raw.y, x[g][2] = raw.z, x[g][3] = raw.w;
+    for (int g = 0; g < kGroups; ++g) {
+      if constexpr (kVec) {
+        const int d0 = (g * 32 + lane) * 4;
+        if (d0 < D) {
+          if constexpr (sizeof(SrcT) == 2) {
+            const uint2 raw = *reinterpret_cast<const uint2*>(src + d0);
+            const SrcT* e = reinterpret_cast<const SrcT*>(&raw);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) x[j][g][i] = to_float<SrcT>(e[i]);
+          } else {
+            const float4 raw = *reinterpret_cast<const float4*>(src + d0);
+            x[j][g][0] = raw.x, x[j][g][1] = raw.y, x[j][g][2] = raw.z, x[j][g][3] = raw.w;
+          }
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int d = (g * 4 + i) * 32 + lane;
+          if (d < D) x[j][g][i] = to_float<SrcT>(src[d]);
         }
       }
     }
-#pragma unroll
-    for (int i = 0; i < 4; ++i) amax = fmaxf(amax, fabsf(x[g][i]));
   }
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
-  const float scale = fmaxf(__fdiv_rn(amax, kQMax), 1e-6f);
-  const float inv = __fdiv_rn(1.0f, scale);
-  if (lane == 0) a.scales[w][blk * a.s_block_stride[w] + off * a.s_slot_stride[w] + (int64_t)h * a.s_head_stride[w]] = scale;
-  auto code = [&](float v) -> uint32_t {
-    const float y = fminf(fmaxf(v * inv, kQMin), kQMax);
-    if constexpr (kInt8) return (uint32_t)(uint8_t)(int8_t)__float2int_rz(y);
-    else return (uint32_t)fp8_out(y);
-  };
+  for (int j = 0; j < R; ++j) {
+    float amax = 0.f;
 #pragma unroll
-  for (int g = 0; g < kGroups; ++g) {
-    if constexpr (kVec) {
-      const int d0 = (g * 32 + lane) * 4;
-      if (d0 < D)
-        *reinterpret_cast<uint32_t*>(dst + d0) = code(x[g][0]) | (code(x[g][1]) << 8) | (code(x[g][2]) << 16) | (code(x[g][3]) << 24);
-    } else {
+    for (int g = 0; g < kGroups; ++g)
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int d = (g * 4 + i) * 32 + lane;
-        if (d < D) dst[d] = (uint8_t)code(x[g][i]);
+      for (int i = 0; i < 4; ++i) amax = fmaxf(amax, fabsf(x[j][g][i]));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+    if (!live[j]) continue;  // (warp-uniform)
+    const float scale = fmaxf(__fdiv_rn(amax, kQMax), 1e-6f);
+    const float inv = __fdiv_rn(1.0f, scale);
+    if (lane == 0) *sdst[j] = scale;
+    auto code = [&](float v) -> uint32_t {
+      const float y = fminf(fmaxf(v * inv, kQMin), kQMax);
+      if constexpr (kInt8) return (uint32_t)(uint8_t)(int8_t)__float2int_rz(y);
+      else return (uint32_t)fp8_out(y);
+    };
+#pragma unroll
+    for (int g = 0; g < kGroups; ++g) {
+      if constexpr (kVec) {
+        const int d0 = (g * 32 + lane) * 4;
+        if (d0 < D)
+          *reinterpret_cast<uint32_t*>(dst[j] + d0) =
+              code(x[j][g][0]) | (code(x[j][g][1]) << 8) | (code(x[j][g][2]) << 16) | (code(x[j][g][3]) << 24);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int d = (g * 4 + i) * 32 + lane;
+          if (d < D) dst[j][d] = (uint8_t)code(x[j][g][i]);
+        }
       }
     }
   }
+}
+
+template <typename SrcT, int R>
+static void launch_pth_r(const PerTokenHeadWriteArgs& a, bool vec, cudaStream_t stream) {
+  const int64_t rows = a.num_tokens * a.num_kv_heads * 2;
+  const dim3 grid((unsigned)((rows + 8 * R - 1) / (8 * R)));
+  const bool pdl = !(tuning().reserved & 512);
+  const bool i8 = a.kv_dtype == B200ATTN_INT8;
+  if (i8 && vec) launch_pdl(cache_quant_per_token_head_kernel<SrcT, true, true, R>, grid, 256, 0, stream, pdl, a);
+  else if (i8) launch_pdl(cache_quant_per_token_head_kernel<SrcT, true, false, R>, grid, 256, 0, stream, pdl, a);
+  else if (vec) launch_pdl(cache_quant_per_token_head_kernel<SrcT, false, true, R>, grid, 256, 0, stream, pdl, a);
+  else launch_pdl(cache_quant_per_token_head_kernel<SrcT, false, false, R>, grid, 256, 0, stream, pdl, a);
 }
 
 template <typename SrcT>
 static void launch_pth(const PerTokenHeadWriteArgs& a, bool vec, cudaStream_t stream) {
+  // decode-sized writes (a few hundred rows) keep one row per warp: they are latency, and more warps hide more of it
   const int64_t rows = a.num_tokens * a.num_kv_heads * 2;
-  const dim3 grid((unsigned)((rows + 7) / 8));
-  const bool pdl = !(tuning().reserved & 512);
-  const bool i8 = a.kv_dtype == B200ATTN_INT8;
-  if (i8 && vec) launch_pdl(cache_quant_per_token_head_kernel<SrcT, true, true>, grid, 256, 0, stream, pdl, a);
-  else if (i8) launch_pdl(cache_quant_per_token_head_kernel<SrcT, true, false>, grid, 256, 0, stream, pdl, a);
-  else if (vec) launch_pdl(cache_quant_per_token_head_kernel<SrcT, false, true>, grid, 256, 0, stream, pdl, a);
-  else launch_pdl(cache_quant_per_token_head_kernel<SrcT, false, false>, grid, 256, 0, stream, pdl, a);
+  if (rows >= 4 * 8 * 2 * (int64_t)device_info().num_sms) launch_pth_r<SrcT, 2>(a, vec, stream);
+  else launch_pth_r<SrcT, 1>(a, vec, stream);
 }
 
-int launch_cache_write_per_token_head(const PerTokenHeadWriteArgs& a, cudaStream_t stream) {
+int launch_cache_write_per_token_head(const PerTokenHeadWriteArgs& a_in, cudaStream_t stream) {
+  PerTokenHeadWriteArgs a = a_in;
+  a.bs_shift = -1;
+  if (a.block_size > 0 && (a.block_size & (a.block_size - 1)) == 0)
+    for (a.bs_shift = 0; (1 << a.bs_shift) < a.block_size; ++a.bs_shift) {}
   if (a.num_tokens == 0) return B200ATTN_OK;
   if (!a.src[0] || !a.src[1] || !a.dst[0] || !a.dst[1] || !a.scales[0] || !a.scales[1] || !a.slot_mapping) {
     set_error("reshape_and_cache_flash_per_token_head: null pointer argument");
@@ -436,6 +473,11 @@ int launch_cache_write_per_token_head(const PerTokenHeadWriteArgs& a, cudaStream
   if (a.src_dtype != B200ATTN_BF16 && a.src_dtype != B200ATTN_F16 && a.src_dtype != B200ATTN_F32) {
     set_error("reshape_and_cache_flash_per_token_head: unsupported source dtype %d", a.src_dtype);
     return B200ATTN_E_BAD_DTYPE;
+  }
+  if (a.num_tokens * a.num_kv_heads * 2 >= (int64_t(1) << 31)) {
+    set_error("reshape_and_cache_flash_per_token_head: %lld tokens x %d heads exceed 2^30 rows per call", (long long)a.num_tokens,
+              a.num_kv_heads);
+    return B200ATTN_E_BAD_SHAPE;
   }
   bool vec = a.head_size % 4 == 0;
   for (int w = 0; w < 2; ++w) {

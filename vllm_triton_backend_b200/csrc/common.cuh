@@ -101,6 +101,7 @@ struct PerTokenHeadWriteArgs {
   int64_t block_stride[2], slot_stride[2], head_stride[2];
   int64_t s_block_stride[2], s_slot_stride[2], s_head_stride[2];
   int num_kv_heads, head_size, block_size, src_dtype, kv_dtype;
+  int bs_shift;  // log2(block_size) when it is a power of two, else -1 (filled in by the launcher)
 };
 int launch_cache_write_per_token_head(const PerTokenHeadWriteArgs& a, cudaStream_t stream);
 int launch_scaled_fp8_quant(void* out, const void* in, int64_t rows, int64_t row_elems, int64_t in_row_stride,
