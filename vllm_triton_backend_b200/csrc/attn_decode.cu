@@ -960,8 +960,16 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
         const float oq = out_quant_factor(P.a.out_scale);
         *reinterpret_cast<uint32_t*>(static_cast<char*>(P.a.out) + oel + d4) = fp8x4_out(o4[0] * oq, o4[1] * oq, o4[2] * oq, o4[3] * oq);
       } else {
-        char* orow = static_cast<char*>(P.a.out) + oel * 2;
-        *reinterpret_cast<uint2*>(orow + d4 * 2) = make_uint2(pack2<Q_BF16>(o4[0], o4[1]), pack2<Q_BF16>(o4[2], o4[3]));
+        char* orow = static_cast<char*>(P.a.out) + (oel + d4) * 2;
+        if (P.out_vec) {
+          *reinterpret_cast<uint2*>(orow) = make_uint2(pack2<Q_BF16>(o4[0], o4[1]), pack2<Q_BF16>(o4[2], o4[3]));
+        } else {  // rows that are not 8-byte aligned (a view into a wider buffer): element stores
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            if constexpr (Q_BF16) reinterpret_cast<__nv_bfloat16*>(orow)[i] = __float2bfloat16_rn(o4[i]);
+            else reinterpret_cast<__half*>(orow)[i] = __float2half_rn(o4[i]);
+          }
+        }
       }
     }
     if (threadIdx.x == 0) P.ws_cnt[f.item] = 0;  // self-cleaning: ready for the next call
