@@ -373,9 +373,11 @@ def run_cache(args, device):
             def fn():  # noqa: F811
                 theirs(key, val, kc, vc, ksc, vsc, slots)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=device) if args.flush else None
+    _cabi.set_tuning(0, 0, 0, args.tune)
     ms, n = time_fn(fn, flush=flush)
+    _cabi.set_tuning(0, 0, 0, 0)
     gbs = nbytes / ms / 1e6
-    print(json.dumps(dict(kind="cache_write", tokens=T, hkv=hkv, D=D, bs=bs, fp8=bool(args.fp8), ms=round(ms, 5),
+    print(json.dumps(dict(kind="cache_write", tune=args.tune, tokens=T, hkv=hkv, D=D, bs=bs, fp8=bool(args.fp8), ms=round(ms, 5),
                           gbs=round(gbs, 1), frac_measured=round(gbs / hbm, 4), iters=n, kernel=kernel_name(args),
                           flush=bool(args.flush), per_token_head=args.pth, impl=args.impl)), flush=True)
 
