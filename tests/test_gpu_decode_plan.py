@@ -21,7 +21,9 @@ def _read_plan(plan):
     size, off = raw[32:48].view(np.int16).astype(int), raw[48:64].view(np.int16).astype(int)
     cur = raw[64:64 + 32 * (MAX_CTAS + MAX_CHUNKS)].view(np.int32).reshape(-1, 8)
     h = dict(total=int(hdr[0]), per=int(hdr[1]), per_static=int(hdr[2]), n_rounds=int(hdr[3]), n_chunks=int(hdr[4]),
-             grid=int(hdr[5]), has_zero_rows=int(hdr[6]))
+             grid=int(hdr[5]), has_zero_rows=int(hdr[6]), snapped=int(hdr[7]))
+    o = 64 + 32 * (MAX_CTAS + MAX_CHUNKS)
+    h["bound"] = raw[o:o + 4 * (MAX_CTAS + 8)].view(np.int32).astype(int)  # Plan::bound (meaningful when snapped)
     return h, size, off, cur[:MAX_CTAS], cur[MAX_CTAS:]
 
 
@@ -73,9 +75,26 @@ def _check_plan(plan, q_lens, kv_lens, window, only_q1):
     assert sum(size[:T]) == per - ps and all(size[r] >= 1 for r in range(T))
     assert all(off[r] == sum(size[:r]) for r in range(T)) and all(size[r] <= size[r - 1] for r in range(1, T))
     covered = np.zeros(h["total"], dtype=np.int32)
+    assert h["snapped"] == (1 if (T == 0 and per >= 4) else 0)
+    if h["snapped"]:
+        # boundaries one step inside an item have moved onto the item's edge; all others are where the division puts them
+        bound = h["bound"]
+        starts = set((prefix[:-1, None] * HG + np.arange(HG)[None, :] * np.array(n)[:, None]).flatten().tolist()) | {h["total"]}
+        assert bound[0] == 0 and bound[grid] == h["total"]
+        for c in range(grid + 1):
+            f = min(c * per, h["total"])
+            assert abs(bound[c] - f) <= 1 and (c == 0 or bound[c] >= bound[c - 1])
+            if bound[c] != f:
+                assert bound[c] in starts, (c, f, bound[c])
+            if 0 < bound[c] < h["total"]:
+                b_, hg_, st_ = resolve(bound[c])
+                o_ = st_ - first[b_]
+                assert n[b_] <= 2 or (o_ != 1 and o_ != n[b_] - 1) or (bound[c] in starts), (c, bound[c], o_, n[b_])
     for c in range(grid):
         r0, r1 = c * per, min((c + 1) * per, h["total"])
-        b, e = r0, min(r0 + ps, r1)
+        if h["snapped"]:
+            r0, r1 = int(h["bound"][c]), int(h["bound"][c + 1])
+        b, e = r0, (r1 if h["snapped"] else min(r0 + ps, r1))
         check_cursor(cta[c], b, b < e)
         covered[b:max(b, e)] += 1
         for r in range(T):

@@ -62,7 +62,7 @@ struct PlanHeader {  // 64 bytes
   int n_chunks;       // n_rounds * grid
   int grid;
   int has_zero_rows;  // some sequence has one query token and no visible key (its output rows are zeros)
-  int pad;
+  int snapped;        // 1: the ranges' boundaries are Plan::bound[] (moved onto item boundaries they were one step from)
   short size[8];      // chunk of round r: [c * per + per_static + off[r], + size[r]) within range c
   short off[8];
 };
@@ -77,11 +77,19 @@ struct Plan {
   PlanHeader hdr;
   PlanCursor cta[kMaxDecodeCtas];
   PlanCursor chunk[kMaxPoolChunks];
+  int bound[kMaxDecodeCtas + 8];  // hdr.snapped: range c is [bound[c], bound[c + 1])
   // int prefix[num_seqs + 1] follows (scratch of the plan kernel)
 };
 
 // Part j of range c: j = 0 the static part, j >= 1 the pool chunk of round j - 1.  [b, e) may be empty.
-__device__ __forceinline__ void part_range(const PlanHeader& h, int c, int j, int& b, int& e) {
+// A boundary that falls one step inside an item would cost a run of one step - an epilogue, a partial record, a ticket
+// and a share of a merge for 1.5 us of streaming - so the plan moves it onto the item's edge (hdr.snapped; static split
+// only).  Ranges then differ by a step or two, and what they are is data: Plan::bound[].
+__device__ __forceinline__ void part_range(const PlanHeader& h, const int* bound, int c, int j, int& b, int& e) {
+  if (h.snapped) {  // (no pool: j == 0 is the whole range)
+    b = __ldg(bound + c), e = j == 0 ? __ldg(bound + c + 1) : b;
+    return;
+  }
   const int r0 = c * h.per, r1 = min(r0 + h.per, h.total);
   if (j == 0) {
     b = r0, e = min(r0 + h.per_static, r1);
@@ -206,6 +214,7 @@ struct PlanArgs {
   int num_seqs, only_q1, window, tps_shift, head_groups, grid;
   int pool_sixteenths;  // share of a CTA's steps that goes to the pool, in 1/16
   int min_chunk;        // smallest chunk, steps
+  int no_snap;          // A/B: keep the ranges' boundaries where the division puts them
 };
 
 constexpr int kPlanThreads = 1024;
@@ -277,30 +286,50 @@ __global__ void __launch_bounds__(kPlanThreads) decode_plan_kernel(const PlanArg
       rem -= c, ++nr;
     }
     h.n_rounds = nr, h.n_chunks = nr * A.grid;
+    h.snapped = (pool_per == 0 && h.per >= 4 && !A.no_snap) ? 1 : 0;
     s_hdr = h;
     A.plan->hdr = h;
   }
   __syncthreads();
   const PlanHeader h = s_hdr;
+  // the item a flat position lies in: sequence, its steps, and the position's offset from the sequence's first item
+  auto locate = [&](int f, int& b, int& sl, int& first, int& n, int& tq, int& rem) {
+    // largest b with prefix[b] * HG <= f; sequences without steps share their successor's prefix and
+    // are skipped by taking the LAST such b... they have n = 0, so take the last b whose range is not empty
+    int lo = 0, hi = A.num_seqs;  // invariant: prefix[lo] * HG <= f < prefix[hi] * HG
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if ((long long)prefix[mid] * A.head_groups <= f) lo = mid; else hi = mid;
+    }
+    seq_steps(A.seq_lens, A.cu_seqlens_q, A.only_q1, A.window, A.tps_shift, lo, sl, first, n, tq);
+    b = lo, rem = f - prefix[lo] * A.head_groups;  // < n * HG
+  };
+  if (h.snapped) {
+    for (int c = tid; c <= A.grid; c += kPlanThreads) {
+      long long fl = (long long)c * h.per;
+      int f = fl > h.total ? h.total : (int)fl;
+      if (f > 0 && f < h.total) {
+        int b, sl, first, n, tq, rem;
+        locate(f, b, sl, first, n, tq, rem);
+        const int off = rem % n;          // steps of the item in front of f
+        if (off == 1) f -= 1;             // the item begins one step earlier: the range takes all of it
+        else if (off == n - 1) f += 1;    // the item ends one step later: the range in front keeps all of it
+      }
+      A.plan->bound[c] = f;
+    }
+    __syncthreads();  // (the block's own global writes are visible to it after the barrier)
+  }
   // ---- resolve the start of every CTA's static part and of every pool chunk
   for (int t = tid; t < A.grid + h.n_chunks; t += kPlanThreads) {
     int f, e;
-    if (t < A.grid) part_range(h, t, 0, f, e);
-    else part_range(h, (t - A.grid) % A.grid, 1 + (t - A.grid) / A.grid, f, e);
+    if (t < A.grid) part_range(h, A.plan->bound, t, 0, f, e);
+    else part_range(h, A.plan->bound, (t - A.grid) % A.grid, 1 + (t - A.grid) / A.grid, f, e);
     const bool any = f < e;
     PlanCursor c;
     c.b = -1, c.hg = 0, c.step = 0, c.seq_len = 0, c.first = 0, c.n = 0, c.tq = 0, c.flat = f;
     if (any) {
-      // largest b with prefix[b] * HG <= f; sequences without steps share their successor's prefix and
-      // are skipped by taking the LAST such b... they have n = 0, so take the last b whose range is not empty
-      int lo = 0, hi = A.num_seqs;  // invariant: prefix[lo] * HG <= f < prefix[hi] * HG
-      while (hi - lo > 1) {
-        const int mid = (lo + hi) >> 1;
-        if ((long long)prefix[mid] * A.head_groups <= f) lo = mid; else hi = mid;
-      }
-      int sl, first, n, tq;
-      seq_steps(A.seq_lens, A.cu_seqlens_q, A.only_q1, A.window, A.tps_shift, lo, sl, first, n, tq);
-      const int rem = f - prefix[lo] * A.head_groups;  // < n * HG
+      int lo, sl, first, n, tq, rem;
+      locate(f, lo, sl, first, n, tq, rem);
       c.b = lo, c.hg = rem / n, c.step = first + rem % n, c.seq_len = sl, c.first = first, c.n = n, c.tq = tq;
     }
     (t < A.grid ? A.plan->cta[t] : A.plan->chunk[t - A.grid]) = c;
@@ -426,7 +455,7 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
       int n = 0;
       for (int j = 1; j <= T; ++j) {
         int pb, pe;
-        part_range(hdr, c, j, pb, pe);
+        part_range(hdr, P.plan->bound, c, j, pb, pe);
         n += pb < pe ? 1 : 0;
       }
       return n;
@@ -532,7 +561,7 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
       const int c = (int)blockIdx.x;
       int extent_end;
       load_cursor(&P.plan->cta[c], cur);
-      part_range(hdr, c, 0, slot_b, extent_end);
+      part_range(hdr, P.plan->bound, c, 0, slot_b, extent_end);
       slot_c = c, slot_j = 0;
       if (cur.b >= 0 && cur.flat < extent_end) {
         const int tc = pooled ? chunks_of(c) : 0;
@@ -558,7 +587,7 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
             claim_pending = false;
             if (ok) {
               int pb, pe;
-              part_range(hdr, c, 1 + own_next, pb, pe);  // begins where the extent ends
+              part_range(hdr, P.plan->bound, c, 1 + own_next, pb, pe);  // begins where the extent ends
               extent_end = pe;
               ++own_next;
               claim();
@@ -606,7 +635,7 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
       j = __shfl_sync(0xffffffffu, j, 0);
       if (j < 0) continue;  // lost the race: look again
       int cb, ce;
-      part_range(hdr, v, 1 + j, cb, ce);
+      part_range(hdr, P.plan->bound, v, 1 + j, cb, ce);
       load_cursor(&P.plan->chunk[j * hdr.grid + v], cur);
       slot_c = v, slot_j = 1 + j, slot_b = cb;
       if (trace && lane == 0) trace[11] += (unsigned long long)(clock64() - t_sw);
@@ -885,7 +914,10 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
       const int T = hdr.n_rounds, J = 1 + T;
       const int* deque = P.ws_pool + kDequeWord0;
       const int i0 = f.i0, i1 = f.i0 + f.n;
-      const int ca = i0 / hdr.per, ncand = ((i1 - 1) / hdr.per - ca + 1) * J;
+      // (snapped boundaries lie within one step of c * per: one more candidate range on either side)
+      const int ca = hdr.snapped ? max(0, (i0 - 1) / hdr.per) : i0 / hdr.per;
+      const int cb = hdr.snapped ? min(hdr.grid - 1, i1 / hdr.per) : (i1 - 1) / hdr.per;
+      const int ncand = (cb - ca + 1) * J;
       int np = 0;
       for (int base = 0; base < ncand; base += 32) {
         const int idx = base + lane;
@@ -895,12 +927,12 @@ attn_decode_kernel(const DecodeParams P, const __grid_constant__ CUtensorMap k_m
           const int c = ca + idx / J, j = idx % J;
           const int stolen = T > 0 ? (__ldcg(&deque[c]) >> 16) & 0xff : 0;
           int pb, pe;
-          part_range(hdr, c, j, pb, pe);
+          part_range(hdr, P.plan->bound, c, j, pb, pe);
           hit = max(pb, i0) < min(pe, i1);
           if (j == 0) {
             for (int r = 1; r <= T; ++r) {
               int qb, qe;
-              part_range(hdr, c, r, qb, qe);
+              part_range(hdr, P.plan->bound, c, r, qb, qe);
               hit = hit || (!((stolen >> (r - 1)) & 1) && max(qb, i0) < min(qe, i1));
             }
           } else {
@@ -1578,6 +1610,7 @@ int launch_plan_kernel(const b200attn_attention_params& a, const DecodeGeom& G, 
   A.seq_lens = a.seq_lens, A.cu_seqlens_q = a.cu_seqlens_q, A.plan = static_cast<Plan*>(plan);
   A.num_seqs = a.num_seqs, A.only_q1 = only_q1 ? 1 : 0, A.window = a.sliding_window, A.tps_shift = G.tps_shift;
   A.head_groups = G.head_groups, A.grid = G.grid, A.pool_sixteenths = G.pool_sixteenths, A.min_chunk = G.min_chunk;
+  A.no_snap = (tuning().reserved & (1 << 22)) ? 1 : 0;
   decode_plan_kernel<<<1, kPlanThreads, 0, stream>>>(A);
   note_launch("decode_plan");
   return check_launch("decode_plan");
