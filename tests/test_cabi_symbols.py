@@ -86,3 +86,18 @@ def test_struct_sizes_agree_with_the_compiled_library(lib):
     assert lib.b200attn_params_size(0) == ctypes.sizeof(AttentionParams)
     assert lib.b200attn_params_size(1) == ctypes.sizeof(RopeCacheParams)
     assert lib.b200attn_params_size(7) == 0
+
+
+def test_static_scratch_limit_matches_what_the_header_promises(lib):
+    """include/b200attn.h: b200attn_decode_attention_static_scratch takes shapes whose workspace fits 24 MiB, 'e.g. up to 32
+    query heads at head size 128 with 8 kv heads, or a 1-2 kv-head shard of a 64-head model' (host-int arithmetic only)."""
+    text = open(os.path.join(ROOT, "include", "b200attn.h")).read()
+    m = re.search(r"#define\s+B200ATTN_STATIC_SCRATCH_BYTES\s+\((\d+)u\s*<<\s*(\d+)\)", text)
+    limit = int(m.group(1)) << int(m.group(2))
+    assert limit == 24 << 20
+    fits = [(64, 32, 8, 128), (256, 32, 8, 128), (64, 8, 1, 128), (64, 16, 2, 128), (64, 32, 4, 64), (1024, 8, 8, 128)]
+    too_big = [(64, 64, 8, 128), (4, 64, 8, 128), (64, 32, 8, 256)]
+    for b, hq, hkv, d in fits:
+        assert lib.b200attn_workspace_bytes(b, b, hq, hkv, d) <= limit, (b, hq, hkv, d)
+    for b, hq, hkv, d in too_big:
+        assert lib.b200attn_workspace_bytes(b, b, hq, hkv, d) > limit, (b, hq, hkv, d)
